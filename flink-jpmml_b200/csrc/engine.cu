@@ -1,0 +1,360 @@
+// engine.cu -- engine, device model table and the extern "C" boundary declared in include/fjpmml.h.
+//
+// Stands where the reference keeps per-operator JVM state:
+//   the lazily loaded evaluator     S/api/functions/EvaluationFunction.scala:43-48
+//   servingModels (model cache)     S/api/functions/EvaluationCoFunction.scala:66-67, 98-131
+//   PmmlModel.predict per event     S/api/PmmlModel.scala:109-119     (here: per micro-batch, on the GPU)
+// (S/ = flink-jpmml-scala/src/main/scala/io/radicalbit/flink/pmml/scala/)
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <condition_variable>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/fjpmml.h"
+#include "kernels.h"
+#include "model.h"
+
+using namespace fjp;
+
+static thread_local std::string g_last_error;
+static int fail(const std::string& msg, char* err = nullptr, size_t cap = 0) {
+  g_last_error = msg;
+  if (err && cap) { strncpy(err, msg.c_str(), cap - 1); err[cap - 1] = 0; }
+  return -1;
+}
+#define CK(call)                                                                                      \
+  do {                                                                                                \
+    cudaError_t e_ = (call);                                                                          \
+    if (e_ != cudaSuccess) return fail(std::string(#call) + ": " + cudaGetErrorString(e_));           \
+  } while (0)
+
+struct fjp_model {
+  CompiledModel cm;
+  std::atomic<int> refs{1};
+  int device = -1;
+  void* d_blob = nullptr;
+  DeviceModel dev{};
+  std::string describe;
+};
+
+static void rebase(fjp_model* m) {
+  m->dev = m->cm.dev;
+  for (auto& fx : m->cm.fixups) {
+    const void* p = static_cast<const uint8_t*>(m->d_blob) + fx.off;
+    memcpy(reinterpret_cast<uint8_t*>(&m->dev) + fx.field_off, &p, sizeof(p));
+  }
+}
+
+static void make_describe(fjp_model* m) {
+  const DeviceModel& d = m->cm.dev; std::string s = "family=" + m->cm.family;
+  if (d.kind == MK_FOREST) {
+    s += " trees=" + std::to_string(d.forest.n_trees) + " format=" + (d.forest.format == FOREST_COMPLETE ? "complete" : "general") +
+         " depth=" + std::to_string(d.forest.depth) + " enc=" + (d.forest.enc == ENC_FLOAT ? "float" : "rank") +
+         " method=" + std::to_string(d.forest.method) + " nodes=" + std::to_string(m->cm.n_nodes);
+    ForestLaunch fl;
+    if (m->d_blob && d.forest.method != FM_SINGLE && plan_forest_complete(d, &fl))
+      s += " tile_events=" + std::to_string(fl.events_per_cta) + " trees_per_stage=" + std::to_string(fl.trees_per_stage) +
+           " smem=" + std::to_string(fl.smem_bytes);
+  } else if (d.kind == MK_CLUSTERING) s += " k=" + std::to_string(d.cluster.k) + " fields=" + std::to_string(d.cluster.nf) + " fast=" + std::to_string(d.cluster.fast);
+  else if (d.kind == MK_REGRESSION) s += " tables=" + std::to_string(d.reg.n_tables) + " dense=" + std::to_string(d.reg.dense) + " norm=" + std::to_string(d.reg.norm);
+  else if (d.kind == MK_NEURAL) s += " inputs=" + std::to_string(d.nn.n_inputs) + " layers=" + std::to_string(d.nn.n_layers) + " max_width=" + std::to_string(d.nn.max_width);
+  s += " F=" + std::to_string(d.F) + " prep_simple=" + std::to_string(d.prep_simple) + " blob_bytes=" + std::to_string(m->cm.blob.size());
+  m->describe = s;
+}
+
+struct Table {
+  std::map<std::pair<std::string, int64_t>, fjp_model*> models;
+  uint64_t epoch = 0;
+  Table() = default;
+  Table(const Table& o) : models(o.models), epoch(o.epoch) { for (auto& kv : models) fjp_model_retain(kv.second); }
+  ~Table() { for (auto& kv : models) fjp_model_release(kv.second); }
+};
+
+static constexpr int NSLOT = 4;
+struct Slot {
+  cudaStream_t s = nullptr; cudaEvent_t done = nullptr;
+  uint8_t* buf = nullptr; size_t cap = 0;   // one device arena per slot, carved per call
+  bool busy = false; fjp_model* held = nullptr;
+};
+
+struct fjp_engine {
+  int device = 0;
+  Slot slots[NSLOT];
+  std::mutex slot_mu; std::condition_variable slot_cv;
+  std::mutex table_mu; std::shared_ptr<const Table> table{std::make_shared<Table>()};
+  std::atomic<long> launches{0};
+};
+
+static int acquire_slot(fjp_engine* e) {
+  std::unique_lock<std::mutex> lk(e->slot_mu);
+  for (;;) {
+    for (int i = 0; i < NSLOT; i++) if (!e->slots[i].busy) { e->slots[i].busy = true; return i; }
+    e->slot_cv.wait(lk);
+  }
+}
+static int try_acquire_slot(fjp_engine* e) {
+  std::lock_guard<std::mutex> lk(e->slot_mu);
+  for (int i = 0; i < NSLOT; i++) if (!e->slots[i].busy) { e->slots[i].busy = true; return i; }
+  return -1;
+}
+static void release_slot(fjp_engine* e, int i) {
+  { std::lock_guard<std::mutex> lk(e->slot_mu); e->slots[i].busy = false; }
+  e->slot_cv.notify_one();
+}
+static int slot_reserve(Slot& s, size_t bytes) {
+  if (bytes <= s.cap) return 0;
+  if (s.buf) { CK(cudaStreamSynchronize(s.s)); CK(cudaFree(s.buf)); s.buf = nullptr; s.cap = 0; }
+  size_t cap = (bytes + (size_t(1) << 20)) & ~((size_t(1) << 20) - 1);
+  CK(cudaMalloc(&s.buf, cap));
+  s.cap = cap;
+  return 0;
+}
+
+struct Carve {  // sub-allocation inside a slot arena
+  size_t off = 0;
+  size_t take(size_t bytes) { size_t o = off; off = (off + bytes + 255) & ~size_t(255); return o; }
+};
+struct HostBatch {
+  const double* X; const uint32_t* present; const double* replace; long n; int vec_size;
+  double* score; uint8_t* status; int32_t* aux; int32_t* node_ids; int node_stride; double* probs; int prob_stride;
+};
+
+// enqueue H2D + kernel + D2H for rows [lo, hi) of hb on slot s
+static int enqueue_chunk(fjp_engine* e, fjp_model* m, Slot& s, const HostBatch& hb, long lo, long hi) {
+  const long n = hi - lo; const int F = hb.vec_size, W = (F + 31) / 32;
+  Carve c;
+  size_t oX = c.take((size_t)n * F * 8), oP = hb.present ? c.take((size_t)n * W * 4) : 0, oR = hb.replace ? c.take((size_t)n * 8) : 0;
+  size_t oS = c.take((size_t)n * 8), oT = c.take((size_t)n), oA = hb.aux ? c.take((size_t)n * 4) : 0;
+  size_t oN = hb.node_ids ? c.take((size_t)n * hb.node_stride * 4) : 0, oQ = hb.probs ? c.take((size_t)n * hb.prob_stride * 8) : 0;
+  if (slot_reserve(s, c.off)) return -1;
+  BatchArgs a{};
+  a.X = reinterpret_cast<double*>(s.buf + oX); a.n = n; a.present_stride = W;
+  CK(cudaMemcpyAsync(s.buf + oX, hb.X + lo * (long)F, (size_t)n * F * 8, cudaMemcpyHostToDevice, s.s));
+  if (hb.present) { a.present = reinterpret_cast<uint32_t*>(s.buf + oP); CK(cudaMemcpyAsync(s.buf + oP, hb.present + lo * (long)W, (size_t)n * W * 4, cudaMemcpyHostToDevice, s.s)); }
+  if (hb.replace) { a.replace = reinterpret_cast<double*>(s.buf + oR); CK(cudaMemcpyAsync(s.buf + oR, hb.replace + lo, (size_t)n * 8, cudaMemcpyHostToDevice, s.s)); }
+  a.score = reinterpret_cast<double*>(s.buf + oS); a.status = s.buf + oT;
+  a.aux = hb.aux ? reinterpret_cast<int32_t*>(s.buf + oA) : nullptr;
+  a.node_ids = hb.node_ids ? reinterpret_cast<int32_t*>(s.buf + oN) : nullptr; a.node_stride = hb.node_stride;
+  a.probs = hb.probs ? reinterpret_cast<double*>(s.buf + oQ) : nullptr; a.prob_stride = hb.prob_stride;
+  if (hb.node_ids) CK(cudaMemsetAsync(s.buf + oN, 0xFF, (size_t)n * hb.node_stride * 4, s.s));
+  if (hb.probs) CK(cudaMemsetAsync(s.buf + oQ, 0xFF, (size_t)n * hb.prob_stride * 8, s.s));
+  int launches = 0;
+  CK(launch_score(m->dev, a, s.s, &launches));
+  e->launches += launches;
+  CK(cudaMemcpyAsync(hb.score + lo, s.buf + oS, (size_t)n * 8, cudaMemcpyDeviceToHost, s.s));
+  CK(cudaMemcpyAsync(hb.status + lo, s.buf + oT, (size_t)n, cudaMemcpyDeviceToHost, s.s));
+  if (hb.aux) CK(cudaMemcpyAsync(hb.aux + lo, s.buf + oA, (size_t)n * 4, cudaMemcpyDeviceToHost, s.s));
+  if (hb.node_ids) CK(cudaMemcpyAsync(hb.node_ids + lo * (long)hb.node_stride, s.buf + oN, (size_t)n * hb.node_stride * 4, cudaMemcpyDeviceToHost, s.s));
+  if (hb.probs) CK(cudaMemcpyAsync(hb.probs + lo * (long)hb.prob_stride, s.buf + oQ, (size_t)n * hb.prob_stride * 8, cudaMemcpyDeviceToHost, s.s));
+  return 0;
+}
+
+// whole-batch outcomes that need no device work: empty model (5) and size mismatch (1)
+static bool host_short_circuit(fjp_model* m, const HostBatch& hb) {
+  int st = -1;
+  if (!m) st = ST_NOMODEL;
+  else if (hb.vec_size != m->cm.dev.F) st = ST_SIZE;
+  if (st < 0) return false;
+  uint64_t nanbits = 0x7FF8000000000000ULL; double nanv; memcpy(&nanv, &nanbits, 8);
+  for (long i = 0; i < hb.n; i++) { hb.score[i] = nanv; hb.status[i] = (uint8_t)st; if (hb.aux) hb.aux[i] = -1; }
+  return true;
+}
+
+extern "C" {
+
+const char* fjp_version(void) { return "flink-jpmml-b200 0.1 (sm_100a)"; }
+const char* fjp_last_error(void) { return g_last_error.c_str(); }
+int fjp_max_inflight(void) { return NSLOT - 1; }
+
+int fjp_engine_create(int device, fjp_engine** out, char* err, size_t errcap) {
+  int count = 0;
+  cudaError_t ce = cudaGetDeviceCount(&count);
+  if (ce != cudaSuccess || count == 0)
+    return fail(std::string("no CUDA device available (") + cudaGetErrorString(ce) + "): this engine has no CPU scoring path", err, errcap);
+  if (device < 0 || device >= count) return fail("device ordinal out of range", err, errcap);
+  if (cudaSetDevice(device) != cudaSuccess) return fail("cudaSetDevice failed", err, errcap);
+  auto* e = new fjp_engine(); e->device = device;
+  for (int i = 0; i < NSLOT; i++) {
+    if (cudaStreamCreateWithFlags(&e->slots[i].s, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&e->slots[i].done, cudaEventDisableTiming) != cudaSuccess) {
+      delete e; return fail("stream/event creation failed", err, errcap);
+    }
+  }
+  *out = e; return 0;
+}
+
+void fjp_engine_destroy(fjp_engine* e) {
+  if (!e) return;
+  cudaSetDevice(e->device);
+  for (auto& s : e->slots) { if (s.s) cudaStreamSynchronize(s.s); if (s.held) fjp_model_release(s.held); if (s.buf) cudaFree(s.buf); if (s.done) cudaEventDestroy(s.done); if (s.s) cudaStreamDestroy(s.s); }
+  { std::lock_guard<std::mutex> lk(e->table_mu); e->table.reset(); }
+  delete e;
+}
+int fjp_engine_device(const fjp_engine* e) { return e->device; }
+int fjp_engine_sync(fjp_engine* e) { CK(cudaSetDevice(e->device)); for (auto& s : e->slots) CK(cudaStreamSynchronize(s.s)); return 0; }
+long fjp_engine_launch_count(const fjp_engine* e) { return e->launches.load(); }
+
+int fjp_model_compile(fjp_engine* e, const char* pmml, size_t len, fjp_model** out, char* err, size_t errcap) {
+  std::unique_ptr<fjp_model> m(new fjp_model());
+  try { m->cm = compile_pmml(pmml, len); }
+  catch (std::exception& ex) { return fail(ex.what(), err, errcap); }
+  if (e) {
+    if (cudaSetDevice(e->device) != cudaSuccess) return fail("cudaSetDevice failed", err, errcap);
+    m->device = e->device;
+    size_t bytes = std::max<size_t>(m->cm.blob.size(), 256);
+    cudaError_t ce = cudaMalloc(&m->d_blob, bytes);
+    if (ce != cudaSuccess) return fail(std::string("cudaMalloc(model): ") + cudaGetErrorString(ce), err, errcap);
+    // upload on a slot stream so that scoring on the other streams is not stalled
+    cudaStream_t st = e->slots[NSLOT - 1].s;
+    ce = cudaMemcpyAsync(m->d_blob, m->cm.blob.data(), m->cm.blob.size(), cudaMemcpyHostToDevice, st);
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(st);
+    if (ce != cudaSuccess) { cudaFree(m->d_blob); return fail(std::string("model upload: ") + cudaGetErrorString(ce), err, errcap); }
+    rebase(m.get());
+  }
+  make_describe(m.get());
+  *out = m.release(); return 0;
+}
+
+void fjp_model_retain(fjp_model* m) { if (m) m->refs.fetch_add(1); }
+void fjp_model_release(fjp_model* m) {
+  if (!m) return;
+  if (m->refs.fetch_sub(1) == 1) {
+    if (m->d_blob) { int cur = 0; cudaGetDevice(&cur); cudaSetDevice(m->device); cudaFree(m->d_blob); cudaSetDevice(cur); }
+    delete m;
+  }
+}
+
+int fjp_model_replicate(fjp_engine* dst, const fjp_model* src, fjp_model** out, char* err, size_t errcap) {
+  if (!src || !src->d_blob) return fail("source model is not device-resident", err, errcap);
+  std::unique_ptr<fjp_model> m(new fjp_model());
+  m->cm = src->cm; m->device = dst->device;
+  if (cudaSetDevice(dst->device) != cudaSuccess) return fail("cudaSetDevice failed", err, errcap);
+  size_t bytes = std::max<size_t>(m->cm.blob.size(), 256);
+  cudaError_t ce = cudaMalloc(&m->d_blob, bytes);
+  if (ce != cudaSuccess) return fail(std::string("cudaMalloc(model): ") + cudaGetErrorString(ce), err, errcap);
+  cudaStream_t st = dst->slots[NSLOT - 1].s;
+  ce = cudaMemcpyPeerAsync(m->d_blob, dst->device, src->d_blob, src->device, m->cm.blob.size(), st);
+  if (ce == cudaSuccess) ce = cudaStreamSynchronize(st);
+  if (ce != cudaSuccess) { cudaFree(m->d_blob); return fail(std::string("peer copy: ") + cudaGetErrorString(ce), err, errcap); }
+  rebase(m.get()); make_describe(m.get());
+  *out = m.release(); return 0;
+}
+
+int fjp_model_num_fields(const fjp_model* m) { return m->cm.dev.F; }
+const char* fjp_model_field_name(const fjp_model* m, int i) { return (i >= 0 && i < (int)m->cm.active_names.size()) ? m->cm.active_names[i].c_str() : nullptr; }
+const char* fjp_model_name(const fjp_model* m) { return m->cm.model_name.c_str(); }
+const char* fjp_model_family(const fjp_model* m) { return m->cm.family.c_str(); }
+int fjp_model_num_labels(const fjp_model* m) { return (int)m->cm.labels.size(); }
+const char* fjp_model_label(const fjp_model* m, int i) { return (i >= 0 && i < (int)m->cm.labels.size()) ? m->cm.labels[i].c_str() : nullptr; }
+int fjp_model_num_segments(const fjp_model* m) { return m->cm.dev.kind == MK_FOREST ? m->cm.dev.forest.n_trees : 0; }
+const char* fjp_model_describe(const fjp_model* m) { return m->describe.c_str(); }
+size_t fjp_model_device_bytes(const fjp_model* m) { return m->d_blob ? m->cm.blob.size() : 0; }
+
+int fjp_table_add(fjp_engine* e, const char* name, int64_t version, fjp_model* m) {
+  if (!m) return fail("fjp_table_add: null model");
+  std::lock_guard<std::mutex> lk(e->table_mu);
+  auto cur = std::atomic_load(&e->table);
+  auto key = std::make_pair(std::string(name), version);
+  if (cur->models.count(key)) return 1;
+  auto next = std::make_shared<Table>(*cur);
+  fjp_model_retain(m); next->models[key] = m; next->epoch = cur->epoch + 1;
+  std::atomic_store(&e->table, std::shared_ptr<const Table>(next));
+  return 0;
+}
+int fjp_table_del(fjp_engine* e, const char* name, int64_t version) {
+  std::lock_guard<std::mutex> lk(e->table_mu);
+  auto cur = std::atomic_load(&e->table);
+  auto key = std::make_pair(std::string(name), version);
+  if (!cur->models.count(key)) return 1;
+  auto next = std::make_shared<Table>(*cur);
+  fjp_model_release(next->models[key]); next->models.erase(key); next->epoch = cur->epoch + 1;
+  std::atomic_store(&e->table, std::shared_ptr<const Table>(next));
+  return 0;
+}
+fjp_model* fjp_table_get(fjp_engine* e, const char* name, int64_t version) {
+  auto cur = std::atomic_load(&e->table);  // the snapshot keeps its models alive while we look
+  auto it = cur->models.find(std::make_pair(std::string(name), version));
+  if (it == cur->models.end()) return nullptr;
+  fjp_model_retain(it->second); return it->second;
+}
+int fjp_table_size(const fjp_engine* e) { return (int)std::atomic_load(&e->table)->models.size(); }
+uint64_t fjp_table_epoch(const fjp_engine* e) { return std::atomic_load(&e->table)->epoch; }
+
+void* fjp_host_alloc(size_t bytes) { void* p = nullptr; if (cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) return nullptr; return p; }
+void fjp_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+int fjp_score_batch_ex(fjp_engine* e, fjp_model* m, const double* X, const uint32_t* present, const double* replace,
+                       long n, int vec_size, double* score, uint8_t* status, int32_t* aux,
+                       int32_t* node_ids, int node_stride, double* probs, int prob_stride) {
+  if (n <= 0) return 0;
+  HostBatch hb{X, present, replace, n, vec_size, score, status, aux, node_ids, node_stride, probs, prob_stride};
+  if (host_short_circuit(m, hb)) return 0;
+  if (!m->d_blob) return fail("model was compiled without an engine: it cannot score");
+  CK(cudaSetDevice(e->device));
+  if (m->device != e->device) return fail("model lives on another device; use fjp_model_replicate");
+  // chunked 2-slot pipeline: copy-in of chunk i+1 overlaps the kernel and copy-out of chunk i
+  long rows = (long)((size_t(24) << 20) / ((size_t)vec_size * 8 + 16));
+  if (rows < 4096) rows = 4096; if (rows > (1 << 18)) rows = 1 << 18;
+  int s0 = acquire_slot(e), s1 = n > rows ? try_acquire_slot(e) : -1;
+  int used[2] = {s0, s1}; int ns = s1 >= 0 ? 2 : 1; int rc = 0; long k = 0;
+  for (long lo = 0; lo < n && rc == 0; lo += rows, k++) rc = enqueue_chunk(e, m, e->slots[used[k % ns]], hb, lo, std::min(n, lo + rows));
+  for (int i = 0; i < ns; i++) { cudaError_t ce = cudaStreamSynchronize(e->slots[used[i]].s); if (ce != cudaSuccess && rc == 0) rc = fail(std::string("scoring failed: ") + cudaGetErrorString(ce)); release_slot(e, used[i]); }
+  return rc;
+}
+
+int fjp_score_batch(fjp_engine* e, fjp_model* m, const double* X, const uint32_t* present, const double* replace,
+                    long n, int vec_size, double* score, uint8_t* status, int32_t* aux) {
+  return fjp_score_batch_ex(e, m, X, present, replace, n, vec_size, score, status, aux, nullptr, 0, nullptr, 0);
+}
+
+int fjp_score_device(fjp_engine* e, fjp_model* m, const double* dX, const uint32_t* dpresent, const double* dreplace,
+                     long n, int vec_size, double* dscore, uint8_t* dstatus, int32_t* daux, void* cuda_stream) {
+  if (n <= 0) return 0;
+  CK(cudaSetDevice(e->device));
+  cudaStream_t st = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : e->slots[0].s;
+  BatchArgs a{}; a.X = dX; a.present = dpresent; a.replace = dreplace; a.n = n; a.present_stride = (vec_size + 31) / 32;
+  a.score = dscore; a.status = dstatus; a.aux = daux;
+  int launches = 0;
+  if (!m) { CK(launch_fill_status(a, ST_NOMODEL, st, &launches)); }
+  else if (vec_size != m->cm.dev.F) { CK(launch_fill_status(a, ST_SIZE, st, &launches)); }
+  else {
+    if (!m->d_blob) return fail("model was compiled without an engine: it cannot score");
+    if (m->device != e->device) return fail("model lives on another device; use fjp_model_replicate");
+    CK(launch_score(m->dev, a, st, &launches));
+  }
+  e->launches += launches;
+  return 0;
+}
+
+int fjp_submit(fjp_engine* e, fjp_model* m, const double* X, const uint32_t* present, const double* replace,
+               long n, int vec_size, double* score, uint8_t* status, int32_t* aux, int* ticket) {
+  HostBatch hb{X, present, replace, n, vec_size, score, status, aux, nullptr, 0, nullptr, 0};
+  CK(cudaSetDevice(e->device));
+  int si = acquire_slot(e); Slot& s = e->slots[si];
+  *ticket = si;
+  if (n <= 0 || host_short_circuit(m, hb)) return 0;
+  if (!m->d_blob || m->device != e->device) { release_slot(e, si); return fail("model is not resident on this engine's device"); }
+  fjp_model_retain(m); s.held = m;  // the batch keeps its model alive across a concurrent fjp_table_del
+  if (enqueue_chunk(e, m, s, hb, 0, n)) { fjp_model_release(m); s.held = nullptr; release_slot(e, si); return -1; }
+  CK(cudaEventRecord(s.done, s.s));
+  return 0;
+}
+
+int fjp_wait(fjp_engine* e, int ticket) {
+  if (ticket < 0 || ticket >= NSLOT) return fail("bad ticket");
+  Slot& s = e->slots[ticket];
+  CK(cudaSetDevice(e->device));
+  cudaError_t ce = cudaStreamSynchronize(s.s);
+  if (s.held) { fjp_model_release(s.held); s.held = nullptr; }
+  release_slot(e, ticket);
+  if (ce != cudaSuccess) return fail(std::string("scoring failed: ") + cudaGetErrorString(ce));
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,780 @@
+// kernels.cu -- the scoring kernels (sm_100a).  Together they replace, for a whole micro-batch at once, what the
+// reference does per event in PmmlModel.predict
+//   flink-jpmml-scala/src/main/scala/io/radicalbit/flink/pmml/scala/api/PmmlModel.scala:109-174
+// i.e. prepareInput (:143-152, JPMML EvaluatorUtil.prepare), evaluateInput (:159-160, JPMML ModelEvaluator.evaluate
+// for ClusteringModel / TreeModel / MiningModel / RegressionModel / NeuralNetwork) and extractTarget (:167-174,
+// Pipeline.scala:61-98).  Input preparation and target extraction are fused into every kernel.
+//
+// Arithmetic follows the JVM: double accumulation in document order, no fused multiply-add (built with -fmad=false),
+// comparisons in java.lang.Double.compareTo's total order where JPMML compares through Comparable.
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "kernels.h"
+
+namespace fjp {
+
+// ================================================================================================ helpers
+__device__ __forceinline__ bool java_eq(double a, double b) {  // Double.equals
+  return __double_as_longlong(a) == __double_as_longlong(b) || (a != a && b != b);
+}
+__device__ __forceinline__ int java_cmp(double a, double b) {  // Double.compare
+  if (a < b) return -1;
+  if (a > b) return 1;
+  if (a == b) {
+    if (a == 0.0) { long long x = __double_as_longlong(a), y = __double_as_longlong(b); return x == y ? 0 : (x < 0 ? -1 : 1); }
+    return 0;
+  }
+  bool an = a != a, bn = b != b;
+  return an == bn ? 0 : (an ? 1 : -1);
+}
+__device__ __forceinline__ bool total_less(double a, double b) { return java_cmp(a, b) < 0; }
+
+// JPMML FieldValueUtil.prepareInputValue for a Double input (SURVEY.md App. A "Input preparation").
+// returns 0: value in `out`; 1: missing; 2: preparation failure (InputPreparationException)
+__device__ int prep_value(const PrepField& pf, const double* __restrict__ pool, bool present, double raw, double& out) {
+  if (present) {
+    bool castable = true; double v = raw;
+    switch (pf.dtype) {
+      case DT_DOUBLE: break;
+      case DT_FLOAT: v = (double)(float)raw; break;
+      case DT_INTEGER: castable = isfinite(raw) && raw == floor(raw) && fabs(raw) <= 2147483647.0; break;
+      case DT_BOOLEAN: castable = raw == 0.0 || raw == 1.0; break;
+      default: castable = false;  // string & friends: a Double cannot be cast (api/PmmlModelSpec.scala:131-136)
+    }
+    int st = 0;  // 0 valid, 1 invalid, 2 missing
+    if (!castable) st = 1;
+    else {
+      const double* p = pool + pf.pool_off + 3 * pf.n_intervals;
+      bool matched = false;
+      for (int i = 0; i < pf.n_missing; i++) if (java_eq(v, p[pf.n_valid + pf.n_invalid + i])) { st = 2; matched = true; break; }
+      if (!matched) for (int i = 0; i < pf.n_invalid; i++) if (java_eq(v, p[pf.n_valid + i])) { st = 1; matched = true; break; }
+      if (!matched && pf.has_valid_space) {
+        bool ok = false;
+        for (int i = 0; i < pf.n_valid; i++) if (java_eq(v, p[i])) { ok = true; break; }
+        st = ok ? 0 : 1; matched = true;
+      }
+      if (!matched && pf.continuous && pf.n_intervals) {
+        const double* iv = pool + pf.pool_off; bool in = false;
+        for (int i = 0; i < pf.n_intervals; i++) {
+          int fl = (int)iv[3 * i + 2];
+          bool lo = !(fl & 1) || ((fl & 4) ? v > iv[3 * i] : v >= iv[3 * i]);
+          bool hi = !(fl & 2) || ((fl & 8) ? v < iv[3 * i + 1] : v <= iv[3 * i + 1]);
+          if (lo && hi) { in = true; break; }
+        }
+        st = in ? 0 : 1;
+      }
+    }
+    if (st == 0) {
+      if (pf.outlier != OT_AS_IS) {
+        if (pf.has_low && v < pf.low) { if (pf.outlier == OT_AS_MISSING) goto missing; v = pf.low; }
+        else if (pf.has_high && v > pf.high) { if (pf.outlier == OT_AS_MISSING) goto missing; v = pf.high; }
+      }
+      out = v; return 0;
+    }
+    if (st == 1) {
+      if (pf.ivt == IVT_RETURN_INVALID) return 2;
+      if (pf.ivt == IVT_AS_IS) { if (!castable) return 2; out = v; return 0; }
+    }
+  }
+missing:
+  if (pf.has_repl == 1) { out = pf.repl; return 0; }
+  return pf.has_repl == 2 ? 2 : 1;
+}
+
+// one event's slot f: applies replaceNan (api/PmmlModel.scala:148) then the preparation above
+__device__ __forceinline__ int load_field(const DeviceModel& m, const BatchArgs& a, long row, int f, double& out) {
+  double raw = a.X[row * (long)m.F + f];
+  bool present = a.present ? ((a.present[row * (long)a.present_stride + (f >> 5)] >> (f & 31)) & 1u) : true;
+  if (!present && a.replace) { double r = a.replace[row]; if (r == r) { raw = r; present = true; } }
+  if (m.prep_simple) {
+    if (!present) return 1;
+    out = m.prep[f].dtype == DT_FLOAT ? (double)(float)raw : raw;
+    return 0;
+  }
+  return prep_value(m.prep[f], m.prep_pool, present, raw, out);
+}
+
+__device__ __forceinline__ double apply_target(const TargetXform& t, double v) {
+  if (t.has_min && v < t.mn) v = t.mn;
+  if (t.has_max && v > t.mx) v = t.mx;
+  v = v * t.factor + t.constant;
+  if (t.cast == 1) v = (double)llround(v); else if (t.cast == 2) v = ceil(v); else if (t.cast == 3) v = floor(v);
+  return v;
+}
+
+__device__ __forceinline__ void write_out(const BatchArgs& a, long row, double score, int status, int aux) {
+  a.score[row] = status == ST_OK ? score : __longlong_as_double(0x7FF8000000000000LL);
+  a.status[row] = (uint8_t)status;
+  if (a.aux) a.aux[row] = aux;
+}
+// classification / clustering winner -> (score, status) through the label table (Pipeline.scala:94-98)
+__device__ __forceinline__ void write_label(const DeviceModel& m, const BatchArgs& a, long row, int label, int aux) {
+  int st = m.target_status ? m.target_status : m.label_status[label];
+  write_out(a, row, m.label_value[label], st, aux);
+}
+
+// ---- key encodings for tree tests (model.h ForestDesc) -------------------------------------------------
+__device__ __forceinline__ uint32_t ordkey(float f) {
+  uint32_t u = __float_as_uint(f);
+  return (f != f) ? 0xFFC00000u : ((u & 0x80000000u) ? ~u : (u | 0x80000000u));
+}
+__device__ __forceinline__ uint32_t enc_float(double v, int mode) {
+  float f = mode == 1 ? __double2float_ru(v) : (mode == 2 ? __double2float_rd(v) : (float)v);
+  return ordkey(f);
+}
+__device__ __forceinline__ uint32_t enc_rank(double v, const double* __restrict__ t, int n) {
+  int lo = 0, hi = n;
+  while (lo < hi) { int mid = (lo + hi) >> 1; if (total_less(t[mid], v)) lo = mid + 1; else hi = mid; }
+  bool eq = lo < n && !total_less(v, t[lo]);
+  return eq ? 2u * lo + 2u : 2u * lo + 1u;
+}
+__device__ __forceinline__ uint32_t encode_key(const ForestDesc& fd, int f, double v) {
+  if (fd.enc == ENC_FLOAT) return enc_float(v, fd.feat_mode[f]);
+  return enc_rank(v, fd.rank_thr + fd.rank_off[f], fd.rank_off[f + 1] - fd.rank_off[f]);
+}
+
+// ---- mbarrier + bulk async copy (TMA unit, 1-D) ----------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// ================================================================================================ forest, complete trees
+// One CTA scores a tile of E = blockDim.x events (one event per thread) against ALL trees:
+//   phase A  rows are read coalesced from HBM, prepared, turned into 32-bit order keys and written TRANSPOSED into
+//            shared memory (keys[f][e]) so that the per-lane gather in phase B is bank-conflict free;
+//   phase B  tree blobs (nodes+leaves, 2^(D+1) x 8 B each) stream through a 2-stage shared-memory ring filled by
+//            bulk async copies (cp.async.bulk + mbarrier) from the L2-resident model; every warp walks the same tree
+//            for 32 different events, TI trees interleaved per thread for ILP; leaf values accumulate in double in
+//            segment order (bit-identical to a sequential sum).
+// Shared memory:  keys F*E*4 | ring 2*G*blob | row stage 32*S*8 | votes (classification) | barriers
+template <int D, bool CLASSIFY>
+__global__ void __launch_bounds__(512, 1)
+forest_complete_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, const ForestLaunch fl) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  const ForestDesc& fd = m.forest;
+  const int E = blockDim.x, F = m.F, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = E >> 5;
+  const int depth = D ? D : fd.depth;
+  const uint32_t blob_words = 2u << depth, blob_bytes = blob_words * 8u;
+  const int G = fl.trees_per_stage, S = fl.row_stride;
+  uint32_t* keys = reinterpret_cast<uint32_t*>(smem);
+  uint64_t* ring = reinterpret_cast<uint64_t*>(smem + fl.off_ring);
+  double* xs = reinterpret_cast<double*>(smem + fl.off_rows);
+  uint16_t* votes = reinterpret_cast<uint16_t*>(smem + fl.off_votes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + fl.off_bars);
+  uint8_t* row_fail = smem + fl.off_fail;
+  const int T = fd.n_trees, NG = (T + G - 1) / G;
+  const long ntiles = (a.n + E - 1) / E;
+
+  if (tid == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+  __syncthreads();
+
+  uint32_t q_issue = 0, q_wait = 0;  // running stage counters (producer: thread 0 only)
+  auto issue = [&](int g) {  // thread 0: fill ring slot q_issue&1 with tree group g
+    uint32_t slot = q_issue & 1u; int t0 = g * G; int nt = min(G, T - t0); uint32_t bytes = (uint32_t)nt * blob_bytes;
+    mbar_expect_tx(&bars[slot], bytes);
+    bulk_g2s(ring + (size_t)slot * G * blob_words, fd.blobs + (size_t)t0 * blob_words, bytes, &bars[slot]);
+    q_issue++;
+  };
+
+  for (long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const long row0 = tile * E;
+    if (tid == 0) { fence_proxy_async(); issue(0); if (NG > 1) issue(1); }
+    row_fail[tid] = 0;
+    // ---------------- phase A: load, prepare, encode, transpose
+    for (int rb = 0; rb < E; rb += 32) {
+      for (int r = warp; r < 32; r += nwarps) {
+        long row = row0 + rb + r;
+        if (row < a.n) {
+          const double* src = a.X + row * (long)F;
+          for (int f = lane; f < F; f += 32) xs[r * S + f] = __ldcs(src + f);
+        }
+      }
+      __syncthreads();
+      {
+        long row = row0 + rb + lane;
+        if (row < a.n) {
+          double rep = 0; bool has_rep = false;
+          if (a.replace) { rep = a.replace[row]; has_rep = rep == rep; }
+          uint32_t pw = 0xFFFFFFFFu; int pw_idx = -1;
+          for (int f = warp; f < F; f += nwarps) {
+            double raw = xs[lane * S + f]; bool present = true;
+            if (a.present) { int wi = f >> 5; if (wi != pw_idx) { pw = a.present[row * (long)a.present_stride + wi]; pw_idx = wi; } present = (pw >> (f & 31)) & 1u; }
+            if (!present && has_rep) { raw = rep; present = true; }
+            double v; int st;
+            if (m.prep_simple) { st = present ? 0 : 1; v = raw; if (fd.enc != ENC_FLOAT && m.prep[f].dtype == DT_FLOAT) v = (double)(float)raw; }
+            else st = prep_value(m.prep[f], m.prep_pool, present, raw, v);
+            uint32_t key = 0;
+            if (st == 0) key = encode_key(fd, f, v); else if (st == 2) row_fail[rb + lane] = 1;
+            keys[f * E + rb + lane] = key;
+          }
+        }
+      }
+      __syncthreads();
+    }
+    // ---------------- phase B: walk all trees
+    const uint32_t* kp = keys + tid;
+    double sum = 0.0, wsum = 0.0;
+    if (CLASSIFY) for (int l = 0; l < m.n_labels; l++) { votes[l * E + tid] = 0; votes[(m.n_labels + l) * E + tid] = 0xFFFF; }
+    uint32_t seen = 0;  // classification: number of distinct labels seen so far (insertion order)
+
+    for (int g = 0; g < NG; g++) {
+      uint32_t slot = q_wait & 1u;
+      mbar_wait(&bars[slot], (q_wait >> 1) & 1u); q_wait++;
+      const uint64_t* base = ring + (size_t)slot * G * blob_words;
+      const int nt = min(G, T - g * G);
+      constexpr int TI = 4;
+      for (int t = 0; t < nt; t += TI) {
+        uint32_t idx[TI]; const uint2* bl[TI];
+#pragma unroll
+        for (int k = 0; k < TI; k++) { idx[k] = 1; bl[k] = reinterpret_cast<const uint2*>(base + (size_t)min(t + k, nt - 1) * blob_words); }
+#pragma unroll
+        for (int d = 0; d < (D ? D : 16); d++) {
+          if (!D && d >= depth) break;
+#pragma unroll
+          for (int k = 0; k < TI; k++) {
+            uint2 nd = bl[k][idx[k]];
+            uint32_t key = kp[(nd.x & 0x7FFFFFFFu) * E];
+            idx[k] = 2u * idx[k] + ((key - (nd.x >> 31)) > nd.y ? 1u : 0u);
+          }
+        }
+#pragma unroll
+        for (int k = 0; k < TI; k++) {
+          if (t + k < nt) {
+            const double* bd = reinterpret_cast<const double*>(bl[k]);
+            if (!CLASSIFY) {
+              double v = bd[idx[k]];
+              if (fd.method == FM_WSUM || fd.method == FM_WAVERAGE) { double w = bd[0]; sum += w * v; wsum += w; } else sum += v;
+            } else {
+              int lab = (int)bl[k][idx[k]].x;
+              // majorityVote counts are exact integers; weighted votes are not supported in the on-chip path
+              uint16_t c = votes[lab * E + tid];
+              if (c == 0) votes[(m.n_labels + lab) * E + tid] = (uint16_t)seen++;
+              votes[lab * E + tid] = c + 1;
+            }
+            if (a.node_ids && row0 + tid < a.n) a.node_ids[(row0 + tid) * (long)a.node_stride + g * G + t + k] =
+                fd.leaf_node_id[((size_t)(g * G + t + k) << depth) + (idx[k] - (1u << depth))];
+          }
+        }
+      }
+      __syncthreads();  // everyone is done with this ring slot
+      if (tid == 0 && g + 2 < NG) { fence_proxy_async(); issue(g + 2); }
+    }
+    // ---------------- epilogue: combine, Targets, extraction
+    long row = row0 + tid;
+    if (row < a.n) {
+      if (row_fail[tid]) write_out(a, row, 0, ST_PREP, -1);
+      else if (!CLASSIFY) {
+        double v = sum;
+        if (fd.method == FM_AVERAGE) v = sum / (double)T; else if (fd.method == FM_WAVERAGE) v = sum / wsum;
+        int aux = -1;
+        if (fd.method == FM_SINGLE && a.node_ids == nullptr && a.aux) aux = 0;  // single-tree aux is filled by the general path
+        write_out(a, row, apply_target(m.tx, v), m.target_status, aux);
+      } else {
+        int best = -1; uint32_t bc = 0, bo = 0;
+        for (int l = 0; l < m.n_labels; l++) {
+          uint32_t c = votes[l * E + tid], o = votes[(m.n_labels + l) * E + tid];
+          if (c && (best < 0 || c > bc || (c == bc && o < bo))) { best = l; bc = c; bo = o; }  // first maximal in insertion order
+        }
+        write_label(m, a, row, best, best);
+      }
+    }
+    __syncthreads();  // keys / votes / row_fail are reused by the next tile
+  }
+}
+
+// ================================================================================================ forest, general form
+// Thread per event, nodes and features straight from global memory (L1/L2).  Handles every compiled tree shape:
+// explicit successors, null predictions, last-prediction leaves; also the fallback when a key tile does not fit on chip.
+__global__ void __launch_bounds__(256) forest_general_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a) {
+  const ForestDesc& fd = m.forest;
+  long row = blockIdx.x * (long)blockDim.x + threadIdx.x;
+  if (row >= a.n) return;
+  const int T = fd.n_trees; const bool classify = fd.classify;
+  double sum = 0, wsum = 0; bool fail = false, null_result = false;
+  constexpr int MAXL = 64;
+  double votes[MAXL]; int order[MAXL]; int seen = 0;
+  if (classify) for (int l = 0; l < m.n_labels && l < MAXL; l++) { votes[l] = 0; order[l] = -1; }
+  int last_node_id = -1;
+  for (int t = 0; t < T && !fail; t++) {
+    int32_t s = fd.troot[t];
+    while (s >= 0) {
+      GNode nd = fd.gnodes[s];
+      double v; int st = load_field(m, a, row, (int)nd.feat, v);
+      if (st == 2) { fail = true; break; }
+      if (st == 1) s = nd.on_missing;
+      else s = encode_key(fd, (int)nd.feat, v) <= nd.k ? nd.on_true : nd.on_false;
+    }
+    if (fail) break;
+    if (a.node_ids) a.node_ids[row * (long)a.node_stride + t] = s == LEAF_NULL ? 0 : fd.gleaf_node_id[~s];
+    if (s == LEAF_NULL) { null_result = true; continue; }
+    int leaf = ~s; last_node_id = fd.gleaf_node_id[leaf];
+    double w = fd.tweight[t];
+    if (!classify) {
+      double v = fd.gleaf_value[leaf];
+      if (fd.method == FM_WSUM || fd.method == FM_WAVERAGE) { sum += w * v; wsum += w; } else sum += v;
+    } else {
+      int lab = fd.gleaf_label[leaf];
+      if (order[lab] < 0) order[lab] = seen++;
+      votes[lab] += (fd.method == FM_WVOTE) ? w : 1.0; wsum += (fd.method == FM_WVOTE) ? w : 1.0;
+    }
+  }
+  if (fail) { write_out(a, row, 0, ST_PREP, -1); return; }
+  if (null_result) { write_out(a, row, 0, m.target_status ? m.target_status : ST_EVAL, -1); return; }  // null prediction / failed aggregation
+  if (!classify) {
+    double v = sum;
+    if (fd.method == FM_AVERAGE) v = sum / (double)T; else if (fd.method == FM_WAVERAGE) v = sum / wsum;
+    write_out(a, row, apply_target(m.tx, v), m.target_status, fd.method == FM_SINGLE ? last_node_id : -1);
+  } else {
+    int best = -1;
+    for (int l = 0; l < m.n_labels; l++) {
+      if (order[l] < 0) continue;
+      if (best < 0) { best = l; continue; }
+      int c = java_cmp(votes[l], votes[best]);
+      if (c > 0 || (c == 0 && order[l] < order[best])) best = l;
+    }
+    write_label(m, a, row, best, fd.method == FM_SINGLE ? last_node_id : best);
+  }
+}
+
+// ================================================================================================ clustering (J1)
+// CTA = 256 threads = 64 events x 4 cluster groups.  The tile's prepared field values sit transposed in shared
+// memory (xs[f][e]); centres are broadcast-loaded through L1.  Distances accumulate in double in ClusteringField order.
+constexpr int CL_E = 64, CL_G = 4, CL_XS = CL_E + 1, CL_SS = CL_E + 4;
+template <bool FAST>
+__global__ void __launch_bounds__(CL_E* CL_G) cluster_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  const ClusterDesc& cd = m.cluster; const int nf = cd.nf, K = cd.k;
+  double* xs = reinterpret_cast<double*>(smem);                    // nf x CL_XS  (padded: conflict-free both ways)
+  uint8_t* st_s = smem + (size_t)nf * CL_XS * 8;                   // nf x CL_SS  (0 value, 1 missing, 2 fail)
+  double* bd = reinterpret_cast<double*>(st_s + (((size_t)nf * CL_SS + 15) & ~size_t(15)));  // CL_G x CL_E
+  int* bc = reinterpret_cast<int*>(bd + CL_G * CL_E);
+  const int tid = threadIdx.x, e = tid & (CL_E - 1), g = tid / CL_E;
+  const long row0 = blockIdx.x * (long)CL_E;
+  // load + prepare: consecutive threads take consecutive clustering fields of one row
+  for (int i = tid; i < nf * CL_E; i += blockDim.x) {
+    int r = i / nf, f = i - r * nf; long row = row0 + r;
+    double v = 0; int st = 1;
+    if (row < a.n) { int slot = cd.slot[f]; if (slot >= 0) st = load_field(m, a, row, slot, v); }
+    xs[f * CL_XS + r] = v; st_s[f * CL_SS + r] = (uint8_t)st;
+  }
+  __syncthreads();
+  const long row = row0 + e;
+  bool fail = false; double adj = 1.0;
+  {
+    double sum_q = 0, sum_nm = 0;
+    for (int f = 0; f < nf; f++) { int st = st_s[f * CL_SS + e]; if (st == 2) fail = true; double q = cd.q[f]; sum_q += q; sum_nm += st == 0 ? q : 0.0; }
+    adj = sum_q / sum_nm;
+  }
+  int best = -1; double bestd = 0;
+  for (int c = g; c < K; c += CL_G) {
+    const double* ctr = cd.centers + (size_t)c * nf;
+    double acc = 0;
+    for (int f = 0; f < nf; f++) {
+      if (st_s[f * CL_SS + e] != 0) continue;  // missing fields are skipped
+      double x = xs[f * CL_XS + e], y = __ldg(ctr + f), term;
+      if (FAST) { double z = fabs(x - y); term = z * z; }
+      else {
+        double z; int cf = cd.compare[f];
+        if (cf == CF_ABSDIFF) z = fabs(x - y);
+        else if (cf == CF_GAUSSSIM) { double s = cd.sim_scale[f], dd = x - y; z = exp(-log(2.0) * dd * dd / (s * s)); }
+        else if (cf == CF_DELTA) z = java_eq(x, y) ? 0.0 : 1.0;
+        else z = java_eq(x, y) ? 1.0 : 0.0;
+        double p = (cd.measure == CM_EUCLIDEAN || cd.measure == CM_SQEUCLIDEAN) ? z * z
+                 : (cd.measure == CM_MINKOWSKI ? (cd.p == 2.0 ? z * z : (cd.p == 1.0 ? z : pow(z, cd.p))) : z);
+        term = cd.weight[f] * p;
+      }
+      if (!FAST && cd.measure == CM_CHEBYCHEV) acc = fmax(acc, term); else acc += term;
+    }
+    double t = acc * adj, d;
+    if (cd.measure == CM_EUCLIDEAN) d = sqrt(t);
+    else if (cd.measure == CM_MINKOWSKI) d = cd.p == 1.0 ? t : (cd.p == 2.0 ? sqrt(t) : pow(t, 1.0 / cd.p));
+    else d = t;
+    if (best < 0 || java_cmp(d, bestd) < 0) { best = c; bestd = d; }  // strictly smaller wins: first cluster kept on ties
+  }
+  bd[g * CL_E + e] = bestd; bc[g * CL_E + e] = best;
+  __syncthreads();
+  if (g == 0 && row < a.n) {
+    for (int gg = 1; gg < CL_G; gg++) {
+      int c2 = bc[gg * CL_E + e]; if (c2 < 0) continue; double d2 = bd[gg * CL_E + e];
+      int cmp = best < 0 ? -1 : java_cmp(d2, bestd);
+      if (cmp < 0 || (cmp == 0 && c2 < best)) { best = c2; bestd = d2; }
+    }
+    if (fail) write_out(a, row, 0, ST_PREP, -1);
+    else write_label(m, a, row, best, best + 1);
+    if (a.probs) a.probs[row * (long)a.prob_stride] = bestd;
+  }
+}
+
+// ================================================================================================ regression (J4)
+__device__ __forceinline__ double link_fn(int norm, double y) {
+  switch (norm) {
+    case NORM_NONE: return y;
+    case NORM_SOFTMAX: case NORM_LOGIT: return 1.0 / (1.0 + exp(-y));
+    case NORM_EXP: return exp(y);
+    case NORM_PROBIT: return 0.5 * erfc(-y / sqrt(2.0));
+    case NORM_CLOGLOG: return 1.0 - exp(-exp(y));
+    case NORM_LOGLOG: return exp(-exp(-y));
+    case NORM_CAUCHIT: return 0.5 + atan(y) / 3.14159265358979323846;
+    default: return y;
+  }
+}
+__device__ __forceinline__ double ipow(double x, int e) {  // Math.pow(x, integer) for the small exponents PMML uses
+  if (e == 1) return x; if (e == 0) return 1.0; if (e == 2) return x * x;
+  return pow(x, (double)e);
+}
+
+// classification epilogue shared by regression / NN: y[0..C) in (strided) memory -> probabilities -> first maximal label
+template <class Get, class Set>
+__device__ void normalize_classes(int norm, int C, Get y, Set p) {
+  if (norm == NORM_SOFTMAX) { double s = 0; for (int i = 0; i < C; i++) { double e = exp(y(i)); p(i, e); s += e; } for (int i = 0; i < C; i++) p(i, y(i) / s); }
+  else if (norm == NORM_SIMPLEMAX) { double s = 0; for (int i = 0; i < C; i++) s += y(i); for (int i = 0; i < C; i++) p(i, y(i) / s); }
+  else if (norm == NORM_NONE) { double s = 0; for (int i = 0; i + 1 < C; i++) s += y(i); p(C - 1, 1.0 - s); }
+  else { double s = 0; for (int i = 0; i + 1 < C; i++) { double v = link_fn(norm, y(i)); p(i, v); s += v; } p(C - 1, 1.0 - s); }
+}
+
+// Generic: thread per event, predictor lists in document order (CSR), values prepared on the fly.
+constexpr int REG_MAXC = 64;
+__global__ void __launch_bounds__(128) regression_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a) {
+  const RegressionDesc& rd = m.reg;
+  long row = blockIdx.x * (long)blockDim.x + threadIdx.x;
+  if (row >= a.n) return;
+  double y[REG_MAXC]; bool fail = false, null_result = false;
+  for (int t = 0; t < rd.n_tables && !fail; t++) {
+    double acc = rd.intercept[t];
+    for (int i = rd.term_off[t]; i < rd.term_off[t + 1]; i++) {
+      RegTerm tm = rd.terms[i]; double v; int st = tm.slot < 0 ? 1 : load_field(m, a, row, tm.slot, v);
+      if (st == 2) { fail = true; break; }
+      if (st == 1) { null_result = true; continue; }  // missing numeric predictor: the table has no result
+      acc += tm.coef * ipow(v, tm.exponent);
+    }
+    for (int i = rd.cat_off[t]; i < rd.cat_off[t + 1] && !fail; i++) {
+      RegCat c = rd.cats[i]; double v; int st = c.slot < 0 ? 1 : load_field(m, a, row, c.slot, v);
+      if (st == 2) { fail = true; break; }
+      if (st == 0 && java_eq(v, c.value)) acc += c.coef;
+    }
+    y[t] = acc;
+  }
+  if (fail) { write_out(a, row, 0, ST_PREP, -1); return; }
+  if (null_result) { write_out(a, row, 0, m.target_status ? m.target_status : ST_EVAL, -1); return; }
+  if (!rd.classify) { write_out(a, row, apply_target(m.tx, link_fn(rd.norm, y[0])), m.target_status, -1); return; }
+  const int C = rd.n_tables;
+  normalize_classes(rd.norm, C, [&](int i) { return y[i]; }, [&](int i, double v) { y[i] = v; });
+  int best = 0; for (int i = 1; i < C; i++) if (java_cmp(y[i], y[best]) > 0) best = i;
+  write_label(m, a, row, best, best);
+  if (a.probs) for (int i = 0; i < C && i < a.prob_stride; i++) a.probs[row * (long)a.prob_stride + i] = y[i];
+}
+
+// Dense: every table uses all F fields in slot order (multinomial logistic, config C3).  A CTA takes RD_E events; the
+// input tile streams through shared memory in chunks of RD_FC features (read coalesced from HBM, stored transposed);
+// each thread owns one event and keeps the C running sums in registers; coefficients are warp-broadcast loads (L1).
+constexpr int RD_E = 128, RD_FC = 32, RD_MAXC = 32;
+__global__ void __launch_bounds__(RD_E) regression_dense_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a) {
+  __shared__ double xs[RD_FC][RD_E + 1];
+  __shared__ uint8_t sts[RD_FC][RD_E];
+  const RegressionDesc& rd = m.reg; const int F = m.F, C = rd.n_tables, tid = threadIdx.x;
+  const long row0 = blockIdx.x * (long)RD_E, row = row0 + tid;
+  double y[RD_MAXC];
+#pragma unroll
+  for (int c = 0; c < RD_MAXC; c++) y[c] = c < C ? rd.intercept[c] : 0.0;
+  bool fail = false, null_result = false;
+  for (int f0 = 0; f0 < F; f0 += RD_FC) {
+    const int nfc = min(RD_FC, F - f0);
+    for (int i = tid; i < RD_E * RD_FC; i += RD_E) {
+      int r = i / RD_FC, f = i - r * RD_FC; long rr = row0 + r;
+      double v = 0; int st = 1;
+      if (rr < a.n && f < nfc) st = load_field(m, a, rr, f0 + f, v);
+      xs[f][r] = v; sts[f][r] = (uint8_t)st;
+    }
+    __syncthreads();
+    for (int f = 0; f < nfc; f++) {
+      int st = sts[f][tid]; double x = xs[f][tid];
+      if (st == 2) fail = true; else if (st == 1) null_result = true;
+      const double* w = rd.dense_w + (f0 + f);
+#pragma unroll
+      for (int c = 0; c < RD_MAXC; c++) if (c < C) y[c] += __ldg(w + (size_t)c * F) * x;
+    }
+    __syncthreads();
+  }
+  if (row >= a.n) return;
+  if (fail) { write_out(a, row, 0, ST_PREP, -1); return; }
+  if (null_result) { write_out(a, row, 0, m.target_status ? m.target_status : ST_EVAL, -1); return; }
+  if (!rd.classify) { write_out(a, row, apply_target(m.tx, link_fn(rd.norm, y[0])), m.target_status, -1); return; }
+  double p[RD_MAXC];
+#pragma unroll
+  for (int c = 0; c < RD_MAXC; c++) p[c] = y[c];
+  // same arithmetic as normalize_classes, on registers
+  if (rd.norm == NORM_SOFTMAX) {
+    double s = 0;
+#pragma unroll
+    for (int c = 0; c < RD_MAXC; c++) if (c < C) { p[c] = exp(y[c]); s += p[c]; }
+#pragma unroll
+    for (int c = 0; c < RD_MAXC; c++) if (c < C) p[c] = p[c] / s;
+  } else if (rd.norm == NORM_SIMPLEMAX) {
+    double s = 0;
+#pragma unroll
+    for (int c = 0; c < RD_MAXC; c++) if (c < C) s += y[c];
+#pragma unroll
+    for (int c = 0; c < RD_MAXC; c++) if (c < C) p[c] = y[c] / s;
+  } else {
+    double s = 0;
+#pragma unroll
+    for (int c = 0; c < RD_MAXC; c++) if (c + 1 < C) { p[c] = rd.norm == NORM_NONE ? y[c] : link_fn(rd.norm, y[c]); s += p[c]; }
+#pragma unroll
+    for (int c = 0; c < RD_MAXC; c++) if (c == C - 1) p[c] = 1.0 - s;
+  }
+  int best = 0; double bp = p[0];
+#pragma unroll
+  for (int c = 1; c < RD_MAXC; c++) if (c < C && java_cmp(p[c], bp) > 0) { best = c; bp = p[c]; }
+  write_label(m, a, row, best, best);
+  if (a.probs) {
+#pragma unroll
+    for (int c = 0; c < RD_MAXC; c++) if (c < C && c < a.prob_stride) a.probs[row * (long)a.prob_stride + c] = p[c];
+  }
+}
+
+// ================================================================================================ neural network (J6)
+__device__ __forceinline__ double activate(int act, double z, double thr) {
+  switch (act) {
+    case ACT_THRESHOLD: return z > thr ? 1.0 : 0.0;
+    case ACT_LOGISTIC: return 1.0 / (1.0 + exp(-z));
+    case ACT_TANH: return tanh(z);
+    case ACT_IDENTITY: return z;
+    case ACT_EXPONENTIAL: return exp(z);
+    case ACT_RECIPROCAL: return 1.0 / z;
+    case ACT_SQUARE: return z * z;
+    case ACT_GAUSS: return exp(-(z * z));
+    case ACT_SINE: return sin(z);
+    case ACT_COSINE: return cos(z);
+    case ACT_ELLIOTT: return z / (1.0 + fabs(z));
+    case ACT_ARCTAN: return 2.0 * atan(z) / 3.14159265358979323846;
+    default: return fmax(0.0, z);  // rectifier
+  }
+}
+__device__ double norm_cont(const double* __restrict__ pts, int n, int outliers, double x, bool& missing) {
+  auto interp = [&](int i) { double a0 = pts[2 * i], b0 = pts[2 * i + 1], a1 = pts[2 * i + 2], b1 = pts[2 * i + 3]; return b0 + (x - a0) / (a1 - a0) * (b1 - b0); };
+  if (x < pts[0]) { if (outliers == 1) { missing = true; return 0; } if (outliers == 2) return pts[1]; return interp(0); }
+  if (x > pts[2 * (n - 1)]) { if (outliers == 1) { missing = true; return 0; } if (outliers == 2) return pts[2 * (n - 1) + 1]; return interp(n - 2); }
+  int i = 0; while (i + 2 < n && x > pts[2 * (i + 1)]) i++;
+  return interp(i);
+}
+
+// CTA = 256 threads (8 warps) x NN_E = 32 events (lane <-> event).  Activations ping-pong between two transposed
+// shared-memory buffers act[neuron][event]; a warp produces 4 neurons at a time, weights are warp-broadcast loads.
+// Accumulation runs in connection order in double, as JPMML's NeuralNetworkEvaluator does.
+constexpr int NN_E = 32, NN_WARPS = 8, NN_J = 4;
+__global__ void __launch_bounds__(NN_E* NN_WARPS) neural_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  const NeuralDesc& nd = m.nn; const int W = nd.max_width;
+  double* act0 = reinterpret_cast<double*>(smem); double* act1 = act0 + (size_t)W * NN_E;
+  __shared__ int flags[NN_E];  // bit0: preparation failure, bit1: missing input (no result)
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const long row = blockIdx.x * (long)NN_E + lane;
+  if (warp == 0) flags[lane] = 0;
+  __syncthreads();
+  for (int i = warp; i < nd.n_inputs; i += NN_WARPS) {
+    NeuralInput in = nd.inputs[i]; double out = 0; int fl = 0;
+    if (row < a.n) {
+      if (in.kind == NI_CONSTANT) out = in.value;
+      else {
+        double v; int st = in.slot < 0 ? 1 : load_field(m, a, row, in.slot, v);
+        if (st == 2) fl = 1;
+        else if (st == 1) { if (in.has_map_missing) out = in.map_missing; else fl = 2; }
+        else if (in.kind == NI_FIELDREF) out = v;
+        else if (in.kind == NI_NORMDISC) out = java_eq(v, in.value) ? 1.0 : 0.0;
+        else { bool miss = false; out = norm_cont(nd.pts + 2 * in.pts_off, in.n_pts, in.outliers, v, miss); if (miss) fl = 2; }
+      }
+    }
+    act0[i * NN_E + lane] = out;
+    if (fl) atomicOr(&flags[lane], fl);
+  }
+  __syncthreads();
+  double* cur = act0; double* nxt = act1;
+  for (int l = 0; l < nd.n_layers; l++) {
+    const NeuralLayer L = nd.layers[l];
+    const double* Wm = nd.weights + L.w_off; const double* B = nd.biases + L.b_off;
+    for (int j0 = warp * NN_J; j0 < L.n_out; j0 += NN_WARPS * NN_J) {
+      double z[NN_J];
+#pragma unroll
+      for (int k = 0; k < NN_J; k++) z[k] = B[min(j0 + k, L.n_out - 1)];
+      for (int i = 0; i < L.n_in; i++) {
+        double x = cur[i * NN_E + lane];
+#pragma unroll
+        for (int k = 0; k < NN_J; k++) z[k] += __ldg(Wm + (size_t)min(j0 + k, L.n_out - 1) * L.n_in + i) * x;
+      }
+#pragma unroll
+      for (int k = 0; k < NN_J; k++) if (j0 + k < L.n_out) nxt[(j0 + k) * NN_E + lane] = activate(L.act, z[k], L.threshold);
+    }
+    __syncthreads();
+    if (L.norm != NORM_NONE && warp == 0) {
+      if (L.norm == NORM_SOFTMAX) {
+        double s = 0; for (int j = 0; j < L.n_out; j++) { double e = exp(nxt[j * NN_E + lane]); nxt[j * NN_E + lane] = e; s += e; }
+        for (int j = 0; j < L.n_out; j++) nxt[j * NN_E + lane] /= s;
+      } else {
+        double s = 0; for (int j = 0; j < L.n_out; j++) s += nxt[j * NN_E + lane];
+        for (int j = 0; j < L.n_out; j++) nxt[j * NN_E + lane] /= s;
+      }
+    }
+    __syncthreads();
+    double* t = cur; cur = nxt; nxt = t;
+  }
+  if (warp != 0 || row >= a.n) return;
+  int fl = flags[lane];
+  if (fl & 1) { write_out(a, row, 0, ST_PREP, -1); return; }
+  if (fl & 2) { write_out(a, row, 0, m.target_status ? m.target_status : ST_EVAL, -1); return; }
+  if (!nd.classify) {
+    double y = cur[nd.out_neuron[0] * NN_E + lane];
+    if (nd.out_denorm_n) {
+      const double* pts = nd.pts + 2 * nd.out_denorm_off; int n = nd.out_denorm_n, i = 0;
+      while (i + 2 < n && y > pts[2 * (i + 1) + 1]) i++;
+      double a0 = pts[2 * i], b0 = pts[2 * i + 1], a1 = pts[2 * i + 2], b1 = pts[2 * i + 3];
+      y = (y - b0) / (b1 - b0) * (a1 - a0) + a0;
+    }
+    write_out(a, row, apply_target(m.tx, y), m.target_status, -1);
+    return;
+  }
+  int best = -1; double bp = 0;
+  for (int o = 0; o < nd.n_outputs; o++) {
+    double p = cur[nd.out_neuron[o] * NN_E + lane];
+    if (a.probs && o < a.prob_stride) a.probs[row * (long)a.prob_stride + o] = p;
+    if (best < 0 || java_cmp(p, bp) > 0) { best = o; bp = p; }  // first maximal NeuralOutput
+  }
+  write_label(m, a, row, best, best);
+}
+
+// ================================================================================================ launchers
+static int g_smem_optin = 0, g_num_sms = 0;
+static void query_device() {
+  if (g_num_sms) return;
+  int dev = 0; cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&g_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+  cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+}
+
+template <int D, bool C>
+static cudaError_t launch_fc(const DeviceModel& m, const BatchArgs& a, const ForestLaunch& fl, int grid, int block, cudaStream_t s) {
+  auto k = forest_complete_kernel<D, C>;
+  cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fl.smem_bytes);
+  if (e != cudaSuccess) return e;
+  k<<<grid, block, fl.smem_bytes, s>>>(m, a, fl);
+  return cudaGetLastError();
+}
+
+// Picks the tile geometry for the on-chip forest kernel; returns false when no tile of >= 64 events fits.
+bool plan_forest_complete(const DeviceModel& m, ForestLaunch* out) {
+  query_device();
+  const ForestDesc& fd = m.forest;
+  if (fd.format != FOREST_COMPLETE) return false;
+  if (fd.classify && (fd.method != FM_VOTE && fd.method != FM_SINGLE)) return false;
+  if (fd.classify && m.n_labels > 64) return false;
+  const size_t budget = (size_t)g_smem_optin - 1024;
+  const size_t blob = (size_t)(2u << fd.depth) * 8;
+  const int S = (m.F | 1) + 0;  // odd row stride (in doubles): conflict-free column reads of the row stage
+  static const int Es[] = {512, 384, 256, 192, 128, 64};
+  for (int E : Es) {
+    size_t keys = (size_t)m.F * E * 4;
+    size_t rows = (size_t)32 * S * 8;
+    size_t votes = fd.classify ? (size_t)2 * m.n_labels * E * 2 : 0;
+    size_t fixed = keys + rows + votes + 64 + E + 256;
+    if (fixed + 2 * 4 * blob > budget) continue;
+    int G = (int)((budget - fixed) / (2 * blob)); G = (G / 4) * 4; if (G > 16) G = 16;
+    if (G > ((fd.n_trees + 3) / 4) * 4) G = ((fd.n_trees + 3) / 4) * 4;
+    ForestLaunch fl{}; fl.events_per_cta = E; fl.trees_per_stage = G; fl.row_stride = S;
+    size_t off = keys; off = (off + 127) & ~size_t(127);
+    fl.off_ring = (uint32_t)off; off += 2 * (size_t)G * blob;
+    fl.off_rows = (uint32_t)off; off += rows;
+    fl.off_votes = (uint32_t)off; off += votes; off = (off + 15) & ~size_t(15);
+    fl.off_bars = (uint32_t)off; off += 64;
+    fl.off_fail = (uint32_t)off; off += E;
+    fl.smem_bytes = (uint32_t)((off + 127) & ~size_t(127));
+    *out = fl; return true;
+  }
+  return false;
+}
+
+cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t s, int* launches) {
+  query_device();
+  if (a.n <= 0) return cudaSuccess;
+  if (launches) (*launches)++;
+  switch (m.kind) {
+    case MK_FOREST: {
+      ForestLaunch fl;
+      // single trees go through the general path (it reports node ids in aux); ensembles through the on-chip path
+      if (m.forest.method != FM_SINGLE && plan_forest_complete(m, &fl)) {
+        long ntiles = (a.n + fl.events_per_cta - 1) / fl.events_per_cta;
+        int grid = (int)(ntiles < g_num_sms ? ntiles : g_num_sms);
+        const bool c = m.forest.classify; const int d = m.forest.depth;
+#define FJP_FC(DD) (c ? launch_fc<DD, true>(m, a, fl, grid, fl.events_per_cta, s) : launch_fc<DD, false>(m, a, fl, grid, fl.events_per_cta, s))
+        if (d == 8) return FJP_FC(8);
+        if (d == 6) return FJP_FC(6);
+        if (d == 4) return FJP_FC(4);
+        return FJP_FC(0);
+#undef FJP_FC
+      }
+      if (m.forest.classify && m.n_labels > 64) return cudaErrorInvalidValue;
+      forest_general_kernel<<<(unsigned)((a.n + 255) / 256), 256, 0, s>>>(m, a);
+      return cudaGetLastError();
+    }
+    case MK_CLUSTERING: {
+      const int nf = m.cluster.nf;
+      size_t sm = (size_t)nf * CL_XS * 8 + (((size_t)nf * CL_SS + 15) & ~size_t(15)) + CL_G * CL_E * 12;
+      if (sm > (size_t)g_smem_optin) return cudaErrorInvalidValue;
+      unsigned grid = (unsigned)((a.n + CL_E - 1) / CL_E);
+      if (m.cluster.fast) {
+        cudaFuncSetAttribute(cluster_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+        cluster_kernel<true><<<grid, CL_E * CL_G, sm, s>>>(m, a);
+      } else {
+        cudaFuncSetAttribute(cluster_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+        cluster_kernel<false><<<grid, CL_E * CL_G, sm, s>>>(m, a);
+      }
+      return cudaGetLastError();
+    }
+    case MK_REGRESSION: {
+      if (m.reg.n_tables > REG_MAXC) return cudaErrorInvalidValue;
+      if (m.reg.dense && m.reg.n_tables <= RD_MAXC) regression_dense_kernel<<<(unsigned)((a.n + RD_E - 1) / RD_E), RD_E, 0, s>>>(m, a);
+      else regression_kernel<<<(unsigned)((a.n + 127) / 128), 128, 0, s>>>(m, a);
+      return cudaGetLastError();
+    }
+    case MK_NEURAL: {
+      size_t sm = (size_t)2 * m.nn.max_width * NN_E * 8;
+      if (sm > (size_t)g_smem_optin) return cudaErrorInvalidValue;
+      cudaFuncSetAttribute(neural_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+      neural_kernel<<<(unsigned)((a.n + NN_E - 1) / NN_E), NN_E * NN_WARPS, sm, s>>>(m, a);
+      return cudaGetLastError();
+    }
+  }
+  return cudaErrorInvalidValue;
+}
+
+// Fills status for a whole batch without looking at the data: size mismatch (1) and unknown model (5).
+__global__ void fill_status_kernel(BatchArgs a, int status) {
+  long row = blockIdx.x * (long)blockDim.x + threadIdx.x;
+  if (row < a.n) write_out(a, row, 0, status, -1);
+}
+cudaError_t launch_fill_status(const BatchArgs& a, int status, cudaStream_t s, int* launches) {
+  if (a.n <= 0) return cudaSuccess;
+  if (launches) (*launches)++;
+  fill_status_kernel<<<(unsigned)((a.n + 255) / 256), 256, 0, s>>>(a, status);
+  return cudaGetLastError();
+}
+
+}  // namespace fjp

@@ -1,0 +1,36 @@
+// kernels.h -- launch interface between the engine (host) and the CUDA kernels.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "model.h"
+
+namespace fjp {
+
+// One micro-batch.  All pointers are DEVICE pointers.
+struct BatchArgs {
+  const double* X;           // n x F row-major (the Flink Vector payloads, api/converter/VectorConverter.scala:68-86)
+  const uint32_t* present;   // n x present_stride words, bit i of row = slot i present (sparse-absent = 0); NULL = dense
+  const double* replace;     // n, NaN = none (replaceNan of PmmlModel.predict, api/PmmlModel.scala:109); NULL = none
+  long n;
+  int present_stride;
+  double* score;             // n   Score.value (NaN when status != 0)
+  uint8_t* status;           // n   0 = Score, else EmptyScore with the reason (model.h ST_*)
+  int32_t* aux;              // n   optional: 1-based cluster position / node id (single tree) / winning label index
+  int32_t* node_ids;         // n x node_stride optional: per-segment node ids of an ensemble
+  int node_stride;
+  double* probs;             // n x prob_stride optional: class probabilities (regression, NN) / winning distance
+  int prob_stride;
+};
+
+struct ForestLaunch {  // tile geometry of forest_complete_kernel
+  int events_per_cta, trees_per_stage, row_stride;
+  uint32_t off_ring, off_rows, off_votes, off_bars, off_fail, smem_bytes;
+};
+
+bool plan_forest_complete(const DeviceModel& m, ForestLaunch* out);
+cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t s, int* launches);
+cudaError_t launch_fill_status(const BatchArgs& a, int status, cudaStream_t s, int* launches);
+
+}  // namespace fjp

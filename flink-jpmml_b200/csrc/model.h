@@ -1,0 +1,152 @@
+// model.h -- compiled (flattened) model representation shared by the PMML compiler, the engine and the kernels.
+//
+// What the reference keeps as a JPMML object graph behind `Evaluator` (api/Evaluator.scala:49-91) becomes a set of
+// flat arrays that live in HBM for as long as the model is in the engine's table.  Device-visible structs are PODs.
+#pragma once
+#include <climits>
+#include <cstdint>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+namespace fjp {
+
+// ---- per-event status byte (SURVEY.md §8b "Error convention"); 0 <=> Prediction(Score(d)), !=0 <=> EmptyScore
+enum : uint8_t {
+  ST_OK = 0,        // Score
+  ST_SIZE = 1,      // InputValidationException  (api/PmmlModel.scala:127-134)
+  ST_PREP = 2,      // InputPreparationException (api/PmmlModel.scala:143-152, api/pipeline/Pipeline.scala:49-54)
+  ST_EVAL = 3,      // JPMML EvaluationException / null prediction
+  ST_EXTRACT = 4,   // JPMMLExtractionException / non-Double target (api/pipeline/Pipeline.scala:94-98)
+  ST_NOMODEL = 5,   // EmptyEvaluatorException (api/Evaluator.scala:69-77)
+};
+
+enum : uint8_t { DT_STRING = 0, DT_INTEGER = 1, DT_FLOAT = 2, DT_DOUBLE = 3, DT_BOOLEAN = 4, DT_OTHER = 5 };
+enum : uint8_t { IVT_RETURN_INVALID = 0, IVT_AS_IS = 1, IVT_AS_MISSING = 2 };
+enum : uint8_t { OT_AS_IS = 0, OT_AS_MISSING = 1, OT_AS_EXTREME = 2 };
+
+// One entry per active MiningField, in vector-slot order (api/converter/VectorConverter.scala:68-73,97-98).
+// Encodes JPMML's FieldValueUtil.prepareInputValue for a java.lang.Double input.
+struct PrepField {
+  double repl, low, high;
+  uint32_t pool_off;  // doubles in prep_pool: n_intervals*(lo,hi,flags) then valid, invalid, missing value lists
+  uint16_t n_intervals, n_valid, n_invalid, n_missing;
+  uint8_t dtype, continuous, ivt, outlier;
+  uint8_t has_repl;   // 1: missingValueReplacement present; 2: present but unusable -> preparation failure
+  uint8_t has_low, has_high;
+  uint8_t has_valid_space;  // DataField lists property="valid" values: anything else is invalid
+};
+
+struct TargetXform {  // <Targets><Target rescaleFactor rescaleConstant min max castInteger>
+  double factor, constant, mn, mx;
+  int has_min, has_max, cast;  // cast: 0 none, 1 round, 2 ceiling, 3 floor
+};
+
+enum ModelKind : int { MK_CLUSTERING = 0, MK_FOREST = 1, MK_REGRESSION = 2, MK_NEURAL = 3 };
+
+// ---- tree ensembles -----------------------------------------------------------------------------
+enum : int { FOREST_COMPLETE = 0, FOREST_GENERAL = 1 };
+enum : int { ENC_FLOAT = 0, ENC_RANK = 1 };
+enum : int { FM_SINGLE = 0, FM_SUM = 1, FM_AVERAGE = 2, FM_WSUM = 3, FM_WAVERAGE = 4, FM_VOTE = 5, FM_WVOTE = 6 };
+
+// General decision node: key = key(x[feat]); key == 0 (missing) -> on_missing, key <= k -> on_true, else on_false.
+// Successors >= 0 are node indices, < 0 are ~leaf index, LEAF_NULL is "null prediction".
+struct GNode {
+  uint32_t feat;
+  uint32_t k;
+  int32_t on_true, on_false, on_missing;
+};
+static constexpr int32_t LEAF_NULL = INT32_MIN;  // successor meaning "null prediction"
+
+struct ForestDesc {
+  int n_trees, depth, format, enc, method, classify;
+  // FOREST_COMPLETE: n_trees blobs of 2^(depth+1) 8-byte words: [0] = segment weight (double), [1 .. 2^d-1] = nodes
+  // in heap order {lo: feat | a<<31, hi: ka}, [2^d .. 2^(d+1)-1] = leaves (double value, or label index as u64)
+  const uint64_t* blobs;
+  const int32_t* leaf_node_id;  // complete: n_trees * 2^depth PMML node ids (aux output)
+  // FOREST_GENERAL
+  const GNode* gnodes; const int32_t* troot; const double* gleaf_value; const int32_t* gleaf_label; const double* tweight;
+  const int32_t* gleaf_node_id;
+  // ENC_FLOAT: per feature 0 = value is a float already, 1 = round up to float, 2 = round down
+  const uint8_t* feat_mode;
+  // ENC_RANK: per active feature sorted distinct thresholds
+  const int32_t* rank_off; const double* rank_thr;
+};
+
+// ---- clustering ----------------------------------------------------------------------------------
+enum : int { CM_EUCLIDEAN = 0, CM_SQEUCLIDEAN = 1, CM_CHEBYCHEV = 2, CM_CITYBLOCK = 3, CM_MINKOWSKI = 4 };
+enum : int { CF_ABSDIFF = 0, CF_GAUSSSIM = 1, CF_DELTA = 2, CF_EQUAL = 3 };
+struct ClusterDesc {
+  int k, nf, measure, fast;  // fast: absDiff everywhere, weights 1, q all 1, (squared)Euclidean
+  double p;
+  const int32_t* slot;      // nf: active-field index of each ClusteringField
+  const double* weight;     // nf
+  const double* q;          // nf missing-value weights
+  const int32_t* compare;   // nf
+  const double* sim_scale;  // nf
+  const double* centers;    // k x nf
+};
+
+// ---- regression / neural network ---------------------------------------------------------------------
+enum : int { NORM_NONE = 0, NORM_SIMPLEMAX = 1, NORM_SOFTMAX = 2, NORM_LOGIT = 3, NORM_PROBIT = 4, NORM_CLOGLOG = 5,
+             NORM_EXP = 6, NORM_LOGLOG = 7, NORM_CAUCHIT = 8 };
+struct RegTerm { int32_t slot; int32_t exponent; double coef; };           // NumericPredictor
+struct RegCat { int32_t slot; int32_t pad; double value; double coef; };   // CategoricalPredictor on a numeric field
+struct RegressionDesc {
+  int n_tables, classify, norm, dense;  // dense: every table lists all F active fields in slot order, exponent 1
+  const double* intercept;    // n_tables
+  const int32_t* term_off;    // n_tables+1
+  const RegTerm* terms;
+  const int32_t* cat_off;     // n_tables+1
+  const RegCat* cats;
+  const double* dense_w;      // n_tables x F (dense only)
+};
+
+enum : int { ACT_THRESHOLD = 0, ACT_LOGISTIC, ACT_TANH, ACT_IDENTITY, ACT_EXPONENTIAL, ACT_RECIPROCAL, ACT_SQUARE,
+             ACT_GAUSS, ACT_SINE, ACT_COSINE, ACT_ELLIOTT, ACT_ARCTAN, ACT_RECTIFIER };
+enum : int { NI_FIELDREF = 0, NI_NORMCONT = 1, NI_NORMDISC = 2, NI_CONSTANT = 3 };
+struct NeuralInput {  // DerivedField of a NeuralInput
+  int32_t kind, slot, pts_off, n_pts, outliers, has_map_missing;  // outliers: 0 asIs, 1 asMissingValues, 2 asExtremeValues
+  double value, map_missing;
+};
+struct NeuralLayer { int32_t n_in, n_out, act, norm; double threshold; int64_t w_off, b_off; };
+static constexpr int MAX_LAYERS = 8;
+struct NeuralDesc {
+  int n_inputs, n_layers, classify, n_outputs, max_width;
+  NeuralLayer layers[MAX_LAYERS];
+  const NeuralInput* inputs;
+  const double* pts;          // LinearNorm (orig, norm) pairs
+  const double* weights;      // per layer row-major [n_out][n_in]
+  const double* biases;
+  const int32_t* out_neuron;  // n_outputs: index into the last layer
+  int out_denorm_off, out_denorm_n;  // regression: NormContinuous of the output to invert (n = 0: none)
+};
+
+struct DeviceModel {
+  int kind, F, prep_simple, n_labels;
+  int target_status;  // 0, or ST_EXTRACT when no result can ever be extracted (no named target / non-double target)
+  const PrepField* prep; const double* prep_pool;
+  const double* label_value; const uint8_t* label_status;  // class label / cluster id -> Double (String.toDouble)
+  TargetXform tx;
+  ForestDesc forest; ClusterDesc cluster; RegressionDesc reg; NeuralDesc nn;
+};
+
+// ---- host side ---------------------------------------------------------------------------------------
+struct CompileError : std::runtime_error { using std::runtime_error::runtime_error; };
+
+// Host copy of everything; pointers inside `dev` are rebased onto the device blob by the engine.
+struct CompiledModel {
+  std::string model_name, family;
+  std::vector<std::string> active_names;
+  std::vector<std::string> labels;
+  DeviceModel dev{};            // scalar fields valid; pointer fields filled at upload
+  // one byte blob + (offset-from-blob, address-of-pointer-field) fixups
+  std::vector<uint8_t> blob;
+  struct Fixup { size_t off; size_t field_off; };  // field_off: byte offset of the pointer inside DeviceModel
+  std::vector<Fixup> fixups;
+  size_t n_nodes = 0;           // statistics
+};
+
+CompiledModel compile_pmml(const char* data, size_t len);
+
+}  // namespace fjp

@@ -1,0 +1,729 @@
+// pmml_compile.cc -- the PMML compiler "in the model reader": PMML bytes -> flat, device-ready arrays.
+//
+// Replaces the model-load step of the reference,
+//   PmmlModel.fromReader  flink-jpmml-scala/src/main/scala/io/radicalbit/flink/pmml/scala/api/PmmlModel.scala:53-61
+//   (JAXBUtil.unmarshalPMML + ModelEvaluatorFactory.newModelEvaluator from org.jpmml:pmml-evaluator:1.3.9),
+// and pre-computes everything the per-event pipeline (PmmlModel.scala:109-174, Pipeline.scala:61-98) decides from the
+// document alone: active-field order, per-field input preparation, and how the first target field turns into a Double.
+//
+// This file is host-only C++; it shares no code with oracle/.
+#include <algorithm>
+#include <charconv>
+#include <cmath>
+#include <cstring>
+#include <functional>
+#include <limits>
+#include <map>
+#include <stdexcept>
+#include <unordered_map>
+
+#include "model.h"
+#include "xml.h"
+
+namespace fjp {
+namespace {
+
+using sv = std::string_view;
+
+[[noreturn]] void unsupported(const std::string& what) { throw CompileError("unsupported PMML feature: " + what); }
+[[noreturn]] void malformed(const std::string& what) { throw CompileError("malformed PMML: " + what); }
+
+sv trim(sv s) {
+  while (!s.empty() && (unsigned char)s.front() <= ' ') s.remove_prefix(1);
+  while (!s.empty() && (unsigned char)s.back() <= ' ') s.remove_suffix(1);
+  return s;
+}
+
+// Text -> double with java.lang.Double.parseDouble's grammar (what String.toDouble uses, Pipeline.scala:95).
+bool parse_double(sv raw, double* out) {
+  sv s = trim(raw);
+  if (s.empty()) return false;
+  bool neg = false;
+  if (s[0] == '+' || s[0] == '-') { neg = s[0] == '-'; s.remove_prefix(1); }
+  if (s.empty()) return false;
+  if (s == "NaN") { *out = std::numeric_limits<double>::quiet_NaN(); return true; }
+  if (s == "Infinity") { *out = neg ? -INFINITY : INFINITY; return true; }
+  bool hex = s.size() > 2 && s[0] == '0' && (s[1] == 'x' || s[1] == 'X');
+  if (!hex) { char l = s.back(); if (l == 'd' || l == 'D' || l == 'f' || l == 'F') s.remove_suffix(1); }
+  if (s.empty()) return false;
+  double v;
+  if (hex) {
+    std::string tmp(s); char* e = nullptr; v = strtod(tmp.c_str(), &e);
+    if (!e || *e) return false;
+  } else {
+    if (!((s[0] >= '0' && s[0] <= '9') || s[0] == '.')) return false;  // no "inf"/"nan" spellings
+    auto r = std::from_chars(s.data(), s.data() + s.size(), v, std::chars_format::general);
+    if (r.ptr != s.data() + s.size()) return false;
+    if (r.ec == std::errc::result_out_of_range) { std::string tmp(s); v = strtod(tmp.c_str(), nullptr); }
+  }
+  *out = neg ? -v : v;
+  return true;
+}
+bool parse_float(sv raw, double* out) {  // Float.parseFloat: one rounding from decimal text to float
+  sv s = trim(raw);
+  double d;
+  if (!parse_double(s, &d)) return false;
+  bool neg = false; sv t = s;
+  if (!t.empty() && (t[0] == '+' || t[0] == '-')) { neg = t[0] == '-'; t.remove_prefix(1); }
+  if (!t.empty()) { char l = t.back(); if (l == 'd' || l == 'D' || l == 'f' || l == 'F') t.remove_suffix(1); }
+  float f;
+  auto r = std::from_chars(t.data(), t.data() + t.size(), f, std::chars_format::general);
+  if (r.ptr == t.data() + t.size() && r.ec == std::errc()) { *out = neg ? -(double)f : (double)f; return true; }
+  *out = (double)(float)d;
+  return true;
+}
+double need_double(sv s, const char* what) {
+  double v; if (!parse_double(s, &v)) malformed(std::string("bad number for ") + what + ": '" + std::string(s) + "'");
+  return v;
+}
+uint8_t dtype_of(sv s) {
+  if (s == "string") return DT_STRING; if (s == "integer") return DT_INTEGER; if (s == "float") return DT_FLOAT;
+  if (s == "double") return DT_DOUBLE; if (s == "boolean") return DT_BOOLEAN; return DT_OTHER;
+}
+// parse `text` the way a value of a field with dataType dt is parsed; false when it does not parse
+bool parse_in_dtype(uint8_t dt, sv text, double* out) {
+  switch (dt) {
+    case DT_DOUBLE: return parse_double(text, out);
+    case DT_FLOAT: return parse_float(text, out);
+    case DT_INTEGER: { double v; if (!parse_double(text, &v) || v != std::floor(v) || std::fabs(v) > 2147483647.0) return false; *out = v; return true; }
+    case DT_BOOLEAN: { sv t = trim(text); if (t == "true" || t == "TRUE" || t == "True") { *out = 1; return true; }
+                       if (t == "false" || t == "FALSE" || t == "False") { *out = 0; return true; }
+                       double v; if (parse_double(t, &v) && (v == 0 || v == 1)) { *out = v; return true; } return false; }
+    default: return false;
+  }
+}
+
+std::vector<std::string> split_array(const XNode& arr) {
+  std::vector<std::string> out; sv t = arr.text; size_t i = 0;
+  while (i < t.size()) {
+    while (i < t.size() && (unsigned char)t[i] <= ' ') i++;
+    if (i >= t.size()) break;
+    std::string tok;
+    if (t[i] == '"') { i++; while (i < t.size() && t[i] != '"') { if (t[i] == '\\' && i + 1 < t.size()) i++; tok += t[i++]; } i++; }
+    else while (i < t.size() && (unsigned char)t[i] > ' ') tok += t[i++];
+    out.push_back(std::move(tok));
+  }
+  return out;
+}
+
+struct Field { std::string name; uint8_t dtype; bool continuous; const XNode* node; };
+
+struct Builder {
+  CompiledModel cm;
+  std::vector<Field> dict; std::unordered_map<std::string, int> dict_idx;
+  std::unordered_map<std::string, int> active_slot;   // field name -> vector slot
+  std::vector<uint8_t> slot_dtype;
+  std::string target_name; bool has_target = false; uint8_t target_dtype = DT_DOUBLE;
+
+  template <class T> void put(const T* const* field_addr, const std::vector<T>& v) {
+    size_t off = (cm.blob.size() + 255) & ~size_t(255);
+    cm.blob.resize(off + std::max<size_t>(v.size() * sizeof(T), 16));
+    if (!v.empty()) memcpy(cm.blob.data() + off, v.data(), v.size() * sizeof(T));
+    cm.fixups.push_back({off, (size_t)((const char*)field_addr - (const char*)&cm.dev)});
+  }
+  int slot_of(sv name) const {  // -1: not an active field of the top-level schema -> always missing
+    auto it = active_slot.find(std::string(name));
+    if (it != active_slot.end()) return it->second;
+    if (!dict_idx.count(std::string(name))) malformed("reference to unknown field '" + std::string(name) + "'");
+    return -1;
+  }
+  const Field& dict_field(sv name) const {
+    auto it = dict_idx.find(std::string(name));
+    if (it == dict_idx.end()) malformed("unknown field '" + std::string(name) + "'");
+    return dict[it->second];
+  }
+
+  // class label / cluster id -> what Pipeline.extractTargetValue (Pipeline.scala:94-98) makes of it
+  void set_labels(const std::vector<std::string>& labels, bool clustering) {
+    cm.labels = labels;
+    std::vector<double> val(labels.size()); std::vector<uint8_t> st(labels.size());
+    uint8_t tdt = clustering ? (uint8_t)DT_STRING : target_dtype;  // entity ids are always strings
+    for (size_t i = 0; i < labels.size(); i++) {
+      double v = std::numeric_limits<double>::quiet_NaN(); uint8_t s = ST_EXTRACT;
+      if ((tdt == DT_STRING || tdt == DT_DOUBLE) && parse_double(labels[i], &v)) s = ST_OK;  // String.toDouble / Double
+      val[i] = s == ST_OK ? v : std::numeric_limits<double>::quiet_NaN(); st[i] = s;
+    }
+    cm.dev.n_labels = (int)labels.size();
+    put(&cm.dev.label_value, val); put(&cm.dev.label_status, st);
+  }
+};
+
+// ---------------------------------------------------------------------------------------------- schema + prep
+void read_dictionary(const XNode& root, Builder& b) {
+  const XNode* dd = root.child("DataDictionary");
+  if (!dd) malformed("no DataDictionary");
+  dd->each("DataField", [&](const XNode& f) {
+    Field fl{std::string(f.attr("name")), dtype_of(f.attr("dataType")), f.attr("optype") == "continuous", &f};
+    b.dict_idx[fl.name] = (int)b.dict.size(); b.dict.push_back(fl);
+  });
+  if (const XNode* td = root.child("TransformationDictionary")) if (td->first) unsupported("TransformationDictionary");
+}
+
+void check_nested_schema(const XNode& model) {
+  if (const XNode* lt = model.child("LocalTransformations")) if (lt->first) unsupported("LocalTransformations");
+  if (const XNode* ms = model.child("MiningSchema"))
+    ms->each("MiningField", [&](const XNode& f) {
+      if (f.has("missingValueReplacement") || f.attr("outliers", "asIs") != "asIs" ||
+          (f.has("invalidValueTreatment") && f.attr("invalidValueTreatment") != "returnInvalid" && f.attr("invalidValueTreatment") != "asIs"))
+        unsupported("value treatments on a nested MiningSchema");
+    });
+}
+
+void read_schema(const XNode& model, Builder& b) {
+  const XNode* ms = model.child("MiningSchema");
+  if (!ms) malformed("no MiningSchema");
+  if (const XNode* lt = model.child("LocalTransformations")) if (lt->first) unsupported("LocalTransformations");
+  std::vector<PrepField> prep; std::vector<double> pool; bool simple = true;
+  ms->each("MiningField", [&](const XNode& f) {
+    sv usage = f.attr("usageType", "active");
+    std::string name(f.attr("name"));
+    if (usage == "target" || usage == "predicted") {
+      if (!b.has_target) { b.has_target = true; b.target_name = name; b.target_dtype = b.dict_field(name).dtype; }
+      return;
+    }
+    if (usage != "active") return;
+    const Field& df = b.dict_field(name);
+    PrepField p{}; p.dtype = df.dtype; p.continuous = df.continuous; p.pool_off = (uint32_t)pool.size();
+    sv ivt = f.attr("invalidValueTreatment", "returnInvalid");
+    p.ivt = ivt == "asIs" ? IVT_AS_IS : ivt == "asMissing" ? IVT_AS_MISSING : IVT_RETURN_INVALID;
+    sv ot = f.attr("outliers", "asIs");
+    p.outlier = ot == "asMissingValues" ? OT_AS_MISSING : ot == "asExtremeValues" ? OT_AS_EXTREME : OT_AS_IS;
+    if (f.has("lowValue")) { p.has_low = 1; p.low = need_double(f.attr("lowValue"), "lowValue"); }
+    if (f.has("highValue")) { p.has_high = 1; p.high = need_double(f.attr("highValue"), "highValue"); }
+    if (f.has("missingValueReplacement")) {
+      double v;
+      if (parse_in_dtype(df.dtype, f.attr("missingValueReplacement"), &v)) { p.has_repl = 1; p.repl = v; }
+      else if (df.dtype == DT_STRING) unsupported("missingValueReplacement on a string field");
+      else p.has_repl = 2;  // replacement text does not parse in the field's dataType -> preparation fails
+    }
+    bool numeric = df.dtype == DT_DOUBLE || df.dtype == DT_FLOAT || df.dtype == DT_INTEGER || df.dtype == DT_BOOLEAN;
+    if (numeric) {
+      if (df.continuous) df.node->each("Interval", [&](const XNode& iv) {
+        sv c = iv.attr("closure"); double flags = 0, lo = 0, hi = 0;
+        if (iv.has("leftMargin")) { flags += 1; lo = need_double(iv.attr("leftMargin"), "leftMargin"); }
+        if (iv.has("rightMargin")) { flags += 2; hi = need_double(iv.attr("rightMargin"), "rightMargin"); }
+        if (c.substr(0, 4) == "open") flags += 4;
+        if (c.size() >= 4 && c.substr(c.size() - 4) == "Open") flags += 8;
+        pool.push_back(lo); pool.push_back(hi); pool.push_back(flags); p.n_intervals++;
+      });
+      // a listed value that does not parse in the field's dataType can never equal an input: dropped, but a
+      // non-empty valid list still defines the valid space
+      std::vector<double> valid, invalid, missing; bool any_valid = false;
+      df.node->each("Value", [&](const XNode& v) {
+        sv prop = v.attr("property", "valid"); double x; bool ok = parse_in_dtype(df.dtype, v.attr("value"), &x);
+        if (prop == "valid") { any_valid = true; if (ok) valid.push_back(x); }
+        else if (ok) (prop == "invalid" ? invalid : missing).push_back(x);
+      });
+      p.has_valid_space = any_valid ? 1 : 0;
+      p.n_valid = (uint16_t)valid.size(); p.n_invalid = (uint16_t)invalid.size(); p.n_missing = (uint16_t)missing.size();
+      pool.insert(pool.end(), valid.begin(), valid.end());
+      pool.insert(pool.end(), invalid.begin(), invalid.end());
+      pool.insert(pool.end(), missing.begin(), missing.end());
+    }
+    bool plain = (df.dtype == DT_DOUBLE || df.dtype == DT_FLOAT) && p.n_intervals == 0 && !p.has_valid_space && p.n_invalid == 0 &&
+                 p.n_missing == 0 && p.has_repl == 0 && p.outlier == OT_AS_IS;
+    simple = simple && plain;
+    b.active_slot[name] = (int)prep.size(); b.slot_dtype.push_back(df.dtype);
+    b.cm.active_names.push_back(name); prep.push_back(p);
+  });
+  b.cm.dev.F = (int)prep.size(); b.cm.dev.prep_simple = simple ? 1 : 0;
+  b.put(&b.cm.dev.prep, prep); b.put(&b.cm.dev.prep_pool, pool);
+  // <Targets>
+  TargetXform tx{1.0, 0.0, 0.0, 0.0, 0, 0, 0};
+  if (const XNode* ts = model.child("Targets")) {
+    bool done = false;
+    ts->each("Target", [&](const XNode& t) {
+      if (done) return;
+      if (t.has("field") && b.has_target && t.attr("field") != b.target_name) return;
+      if (t.has("rescaleFactor")) tx.factor = need_double(t.attr("rescaleFactor"), "rescaleFactor");
+      if (t.has("rescaleConstant")) tx.constant = need_double(t.attr("rescaleConstant"), "rescaleConstant");
+      if (t.has("min")) { tx.has_min = 1; tx.mn = need_double(t.attr("min"), "min"); }
+      if (t.has("max")) { tx.has_max = 1; tx.mx = need_double(t.attr("max"), "max"); }
+      sv c = t.attr("castInteger"); tx.cast = c == "round" ? 1 : c == "ceiling" ? 2 : c == "floor" ? 3 : 0;
+      done = true;
+    });
+  }
+  b.cm.dev.tx = tx;
+}
+
+// ---------------------------------------------------------------------------------------------- clustering
+void compile_clustering(const XNode& m, Builder& b) {
+  b.cm.family = "ClusteringModel"; b.cm.dev.kind = MK_CLUSTERING;
+  if (m.attr("modelClass") != "centerBased") unsupported("distribution-based ClusteringModel");
+  const XNode* cmz = m.child("ComparisonMeasure"); if (!cmz) malformed("no ComparisonMeasure");
+  if (cmz->attr("kind") != "distance") unsupported("similarity ComparisonMeasure");
+  sv dflt_cmp = cmz->attr("compareFunction", "absDiff");
+  ClusterDesc& d = b.cm.dev.cluster; d.p = 2; d.measure = -1;
+  for (const XNode* k = cmz->first; k; k = k->next) {
+    if (k->name == "Extension") continue;
+    if (k->name == "euclidean") d.measure = CM_EUCLIDEAN; else if (k->name == "squaredEuclidean") d.measure = CM_SQEUCLIDEAN;
+    else if (k->name == "chebychev") d.measure = CM_CHEBYCHEV; else if (k->name == "cityBlock") d.measure = CM_CITYBLOCK;
+    else if (k->name == "minkowski") { d.measure = CM_MINKOWSKI; d.p = need_double(k->attr("p-parameter"), "p-parameter"); }
+    else unsupported("comparison measure " + std::string(k->name));
+  }
+  if (d.measure < 0) malformed("ComparisonMeasure without a measure");
+  std::vector<int32_t> slot, cmp; std::vector<double> w, q, scale;
+  m.each("ClusteringField", [&](const XNode& cf) {
+    if (cf.attr("isCenterField", "true") != "true") return;
+    slot.push_back(b.slot_of(cf.attr("field")));
+    w.push_back(need_double(cf.attr("fieldWeight", "1"), "fieldWeight"));
+    sv c = cf.attr("compareFunction", dflt_cmp);
+    cmp.push_back(c == "absDiff" ? CF_ABSDIFF : c == "gaussSim" ? CF_GAUSSSIM : c == "delta" ? CF_DELTA : c == "equal" ? CF_EQUAL : -1);
+    if (cmp.back() < 0) unsupported("compareFunction " + std::string(c));
+    scale.push_back(cf.has("similarityScale") ? need_double(cf.attr("similarityScale"), "similarityScale") : 0.0);
+  });
+  size_t nf = slot.size(); if (!nf) malformed("no ClusteringField");
+  if (const XNode* mw = m.child("MissingValueWeights")) { if (const XNode* a = mw->child("Array")) for (auto& t : split_array(*a)) q.push_back(need_double(t, "MissingValueWeights")); }
+  if (q.empty()) q.assign(nf, 1.0);
+  if (q.size() != nf) malformed("MissingValueWeights size mismatch");
+  std::vector<double> centers; std::vector<std::string> ids; int pos = 0;
+  m.each("Cluster", [&](const XNode& c) {
+    pos++; ids.push_back(c.has("id") ? std::string(c.attr("id")) : std::to_string(pos));  // EntityUtil.getId: 1-based position
+    const XNode* a = c.child("Array"); if (!a) malformed("Cluster without Array");
+    auto toks = split_array(*a); if (toks.size() != nf) malformed("Cluster Array size mismatch");
+    for (auto& t : toks) centers.push_back(need_double(t, "Cluster Array"));
+  });
+  if (ids.empty()) malformed("no Cluster");
+  d.k = (int)ids.size(); d.nf = (int)nf;
+  bool fast = d.measure == CM_SQEUCLIDEAN || d.measure == CM_EUCLIDEAN;
+  for (size_t i = 0; i < nf; i++) fast = fast && cmp[i] == CF_ABSDIFF && w[i] == 1.0 && q[i] == 1.0 && slot[i] >= 0;
+  d.fast = fast ? 1 : 0;
+  b.put(&d.slot, slot); b.put(&d.weight, w); b.put(&d.q, q); b.put(&d.compare, cmp); b.put(&d.sim_scale, scale); b.put(&d.centers, centers);
+  b.set_labels(ids, true);
+  b.cm.dev.target_status = b.has_target ? ST_OK : ST_EXTRACT;  // no named target field -> nothing to extract
+}
+
+// ---------------------------------------------------------------------------------------------- trees
+struct Thr { int slot; double value; bool strict; };  // test: x <= value (strict: x < value)
+struct TNode { int thr; int32_t on_true, on_false, on_missing; };  // thr index; thr<0: "always true when present"
+struct TLeaf { double value; int32_t label; int32_t node_id; };
+
+struct ForestBuilder {
+  Builder& b; bool classify;
+  std::vector<Thr> thr; std::vector<TNode> nodes; std::vector<int> node_slot; std::vector<TLeaf> leaves; std::vector<int32_t> roots;
+  std::vector<double> weights; std::vector<std::string> labels; std::unordered_map<std::string, int> label_idx;
+  explicit ForestBuilder(Builder& bb, bool c) : b(bb), classify(c) {}
+
+  int label_of(sv s) { std::string k(s); auto it = label_idx.find(k); if (it != label_idx.end()) return it->second; int i = (int)labels.size(); labels.push_back(k); label_idx[k] = i; return i; }
+
+  struct TreeCtx {
+    int mvs;  // 0 none, 1 defaultChild, 2 lastPrediction, 3 nullPrediction
+    bool last_on_no_true; int counter = 0; TargetXform sub_tx; bool has_sub_tx = false;
+    std::unordered_map<const XNode*, int> number; std::unordered_map<const XNode*, int32_t> entered, leafref;
+    std::map<std::pair<const XNode*, int>, int32_t> chained;
+  };
+
+  static const XNode* pred_of(const XNode& n) {
+    for (const XNode* k = n.first; k; k = k->next)
+      if (k->name == "True" || k->name == "False" || k->name == "SimplePredicate" || k->name == "SimpleSetPredicate" || k->name == "CompoundPredicate") return k;
+    malformed("Node/Segment without predicate");
+  }
+  void number_nodes(const XNode& n, TreeCtx& cx) {
+    cx.counter++; double v; sv id = n.attr("id");
+    cx.number[&n] = (!id.empty() && parse_double(id, &v) && v == std::floor(v) && std::fabs(v) < 2e9) ? (int)v : cx.counter;
+    n.each("Node", [&](const XNode& k) { number_nodes(k, cx); });
+  }
+  int32_t leaf_for(const XNode& n, TreeCtx& cx) {  // successor for "the result is node n's score"
+    if (!n.has("score")) return LEAF_NULL;
+    auto it = cx.leafref.find(&n); if (it != cx.leafref.end()) return it->second;
+    TLeaf lf{0.0, -1, cx.number[&n]};
+    if (classify) lf.label = label_of(n.attr("score"));
+    else {
+      if (!parse_double(n.attr("score"), &lf.value)) unsupported("non-numeric regression score '" + std::string(n.attr("score")) + "'");
+      if (cx.has_sub_tx) {  // a segment model's own <Targets> act on its result before aggregation
+        const TargetXform& t = cx.sub_tx; double v = lf.value;
+        if (t.has_min && v < t.mn) v = t.mn; if (t.has_max && v > t.mx) v = t.mx; v = v * t.factor + t.constant;
+        if (t.cast == 1) v = (double)std::llround(v); else if (t.cast == 2) v = std::ceil(v); else if (t.cast == 3) v = std::floor(v);
+        lf.value = v;
+      }
+    }
+    leaves.push_back(lf); int32_t s = ~(int32_t)(leaves.size() - 1); cx.leafref[&n] = s; return s;
+  }
+  int32_t add_test(int slot, double value, bool strict, int32_t t, int32_t f, int32_t m) {
+    if (slot < 0) return m;  // field is never supplied -> always UNKNOWN
+    thr.push_back({slot, value, strict}); nodes.push_back({(int)thr.size() - 1, t, f, m}); node_slot.push_back(slot); return (int32_t)nodes.size() - 1;
+  }
+  int32_t enter(const XNode& n, int32_t last, TreeCtx& cx) {
+    auto it = cx.entered.find(&n); if (it != cx.entered.end()) return it->second;
+    int32_t r;
+    if (!n.child("Node")) r = leaf_for(n, cx);
+    else { int32_t l2 = n.has("score") ? leaf_for(n, cx) : last; r = chain(n, 0, l2, cx); }
+    cx.entered[&n] = r; return r;
+  }
+  // successor for "children i.. of parent are still to be tried"
+  int32_t chain(const XNode& parent, int i, int32_t last, TreeCtx& cx) {
+    auto key = std::make_pair(&parent, i);
+    auto it = cx.chained.find(key); if (it != cx.chained.end()) return it->second;
+    std::vector<const XNode*> kids; parent.each("Node", [&](const XNode& k) { kids.push_back(&k); });
+    int32_t r;
+    if (i >= (int)kids.size()) r = cx.last_on_no_true ? last : LEAF_NULL;
+    else {
+      const XNode& kid = *kids[i]; const XNode& p = *pred_of(kid);
+      if (p.name == "True") r = enter(kid, last, cx);
+      else if (p.name == "False") r = chain(parent, i + 1, last, cx);
+      else if (p.name == "SimplePredicate") {
+        int32_t s_true = enter(kid, last, cx), s_false = chain(parent, i + 1, last, cx), s_miss;
+        switch (cx.mvs) {
+          case 0: s_miss = s_false; break;
+          case 1: { sv dc = parent.attr("defaultChild"); const XNode* d = nullptr;
+                    for (auto* k : kids) if (!dc.empty() && k->attr("id") == dc) d = k;
+                    if (!d) unsupported("missingValueStrategy=defaultChild without a resolvable defaultChild");
+                    s_miss = enter(*d, last, cx); break; }
+          case 2: s_miss = last; break;
+          default: s_miss = LEAF_NULL; break;
+        }
+        sv op = p.attr("operator"); sv fname = p.attr("field"); int slot = b.slot_of(fname);
+        uint8_t dt = b.dict_field(fname).dtype;
+        // thr = -1: "passes whenever present"; the missing successor is the failing branch
+        if (op == "isMissing") { if (slot < 0) r = s_true; else { r = add_test(slot, 0, false, s_false, s_true, s_true); nodes[r].thr = -1; } }
+        else if (op == "isNotMissing") { if (slot < 0) r = s_false; else { r = add_test(slot, 0, false, s_true, s_false, s_false); nodes[r].thr = -1; } }
+        else {
+          if (dt == DT_STRING || dt == DT_OTHER) unsupported("SimplePredicate on a non-numeric field");
+          double v; if (!parse_in_dtype(dt, p.attr("value"), &v)) unsupported("SimplePredicate value '" + std::string(p.attr("value")) + "' does not parse in the field's dataType");
+          if (op == "lessOrEqual") r = add_test(slot, v, false, s_true, s_false, s_miss);
+          else if (op == "lessThan") r = add_test(slot, v, true, s_true, s_false, s_miss);
+          else if (op == "greaterThan") r = add_test(slot, v, false, s_false, s_true, s_miss);
+          else if (op == "greaterOrEqual") r = add_test(slot, v, true, s_false, s_true, s_miss);
+          else if (op == "equal") { int32_t n2 = add_test(slot, v, true, s_false, s_true, s_miss); r = add_test(slot, v, false, n2, s_false, s_miss); }
+          else if (op == "notEqual") { int32_t n2 = add_test(slot, v, true, s_true, s_false, s_miss); r = add_test(slot, v, false, n2, s_true, s_miss); }
+          else malformed("bad operator " + std::string(op));
+        }
+      } else unsupported(std::string(p.name) + " in a TreeModel");
+    }
+    cx.chained[key] = r; return r;
+  }
+
+  void add_tree(const XNode& tm, double weight) {
+    check_nested_schema(tm);
+    TreeCtx cx; sv mvs = tm.attr("missingValueStrategy", "none");
+    cx.mvs = mvs == "none" ? 0 : mvs == "defaultChild" ? 1 : mvs == "lastPrediction" ? 2 : mvs == "nullPrediction" ? 3 : -1;
+    if (cx.mvs < 0) unsupported("missingValueStrategy " + std::string(mvs));
+    cx.last_on_no_true = tm.attr("noTrueChildStrategy", "returnNullPrediction") == "returnLastPrediction";
+    if (classify != (tm.attr("functionName") == "classification")) unsupported("TreeModel functionName differs from the ensemble's");
+    if (const XNode* ts = tm.child("Targets")) if (const XNode* t = ts->child("Target")) {
+      if (classify) unsupported("Targets on a classification tree");
+      TargetXform x{1, 0, 0, 0, 0, 0, 0};
+      if (t->has("rescaleFactor")) x.factor = need_double(t->attr("rescaleFactor"), "rescaleFactor");
+      if (t->has("rescaleConstant")) x.constant = need_double(t->attr("rescaleConstant"), "rescaleConstant");
+      if (t->has("min")) { x.has_min = 1; x.mn = need_double(t->attr("min"), "min"); }
+      if (t->has("max")) { x.has_max = 1; x.mx = need_double(t->attr("max"), "max"); }
+      sv c = t->attr("castInteger"); x.cast = c == "round" ? 1 : c == "ceiling" ? 2 : c == "floor" ? 3 : 0;
+      cx.sub_tx = x; cx.has_sub_tx = true;
+    }
+    const XNode* root = tm.child("Node"); if (!root) malformed("TreeModel without Node");
+    number_nodes(*root, cx);
+    const XNode& rp = *pred_of(*root);
+    int32_t r;
+    if (rp.name == "True") r = enter(*root, LEAF_NULL, cx);
+    else if (rp.name == "False") r = LEAF_NULL;
+    else unsupported("root Node predicate other than True/False");
+    roots.push_back(r); weights.push_back(weight);
+  }
+
+  // ---- emit
+  static uint32_t ordkey(float f) {
+    if (f != f) return 0xFFC00000u;
+    uint32_t u; memcpy(&u, &f, 4);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+  }
+  // total order of java.lang.Double.compareTo
+  static bool total_less(double a, double b) {
+    if (a < b) return true; if (a > b) return false;
+    if (a == b) return a == 0.0 && std::signbit(a) && !std::signbit(b);
+    return !std::isnan(a) && std::isnan(b);
+  }
+
+  void emit(int method) {
+    ForestDesc& fd = b.cm.dev.forest; int F = b.cm.dev.F;
+    fd.n_trees = (int)roots.size(); fd.method = method; fd.classify = classify ? 1 : 0;
+    b.cm.n_nodes = nodes.size();
+    // Encoding.  ENC_FLOAT: the key of a feature is the order-preserving integer image of ONE float per value.
+    // For a float-typed field that float is the value itself.  For a double/integer field it is the value rounded
+    // up (tests are all `x <= t`) or down (tests are all `x < t`) to float, which decides every test exactly iff
+    // each threshold is itself a finite float:  x <= t  <=>  RU(x) <= t,   x < t  <=>  RD(x) < t.
+    // Anything else (non-float thresholds, both kinds of test on one double feature) falls back to ENC_RANK.
+    bool float_ok = true; std::vector<uint8_t> used(thr.size(), 0);
+    for (auto& n : nodes) if (n.thr >= 0) used[n.thr] = 1;
+    std::vector<uint8_t> has_strict(F, 0), has_loose(F, 0), feat_mode(F + 1, 0);
+    for (size_t i = 0; i < thr.size(); i++) {
+      if (!used[i]) continue; const Thr& t = thr[i];
+      if (!std::isfinite(t.value) || std::fabs(t.value) > 3.0e38) { float_ok = false; break; }
+      if (b.slot_dtype[t.slot] != DT_FLOAT && (double)(float)t.value != t.value) { float_ok = false; break; }
+      (t.strict ? has_strict : has_loose)[t.slot] = 1;
+    }
+    for (int f = 0; f < F && float_ok; f++) {
+      if (b.slot_dtype[f] == DT_FLOAT) feat_mode[f] = 0;
+      else if (has_strict[f] && has_loose[f]) float_ok = false;
+      else feat_mode[f] = has_strict[f] ? 2 : 1;
+    }
+    fd.enc = float_ok ? ENC_FLOAT : ENC_RANK;
+    b.put(&fd.feat_mode, feat_mode);
+    std::vector<uint32_t> K(thr.size());
+    std::vector<int32_t> rank_off(F + 1, 0); std::vector<double> rank_thr;
+    if (float_ok) {
+      for (size_t i = 0; i < thr.size(); i++) { uint32_t k = ordkey((float)thr[i].value); K[i] = thr[i].strict ? k - 1 : k; }
+    } else {
+      std::vector<std::vector<double>> per(F);
+      for (size_t i = 0; i < thr.size(); i++) if (used[i]) per[thr[i].slot].push_back(thr[i].value);
+      for (int f = 0; f < F; f++) {
+        auto& v = per[f]; std::sort(v.begin(), v.end(), total_less);
+        v.erase(std::unique(v.begin(), v.end(), [](double a, double c) { return !total_less(a, c) && !total_less(c, a); }), v.end());
+        rank_off[f] = (int32_t)rank_thr.size(); rank_thr.insert(rank_thr.end(), v.begin(), v.end());
+      }
+      rank_off[F] = (int32_t)rank_thr.size();
+      for (size_t i = 0; i < thr.size(); i++) {
+        if (!used[i]) continue;
+        const double* base = rank_thr.data() + rank_off[thr[i].slot]; int n = rank_off[thr[i].slot + 1] - rank_off[thr[i].slot];
+        int j = (int)(std::lower_bound(base, base + n, thr[i].value, total_less) - base);
+        K[i] = thr[i].strict ? 2u * j + 1u : 2u * j + 2u;
+      }
+    }
+    b.put(&fd.rank_off, rank_off); b.put(&fd.rank_thr, rank_thr);
+    auto feat_of = [&](const TNode& n) { return node_slot[&n - nodes.data()]; };
+
+    // complete-tree detection: uniform depth, no sharing, missing goes to one of the two children
+    int depth = -1; bool complete = !roots.empty();
+    std::vector<int> dep_memo(nodes.size(), -1);
+    std::function<int(int32_t)> dep = [&](int32_t s) -> int {  // -2: not complete
+      if (s < 0) return s == LEAF_NULL ? -2 : 0;
+      if (dep_memo[s] != -1) return dep_memo[s];
+      const TNode& n = nodes[s]; int r;
+      if (n.on_missing != n.on_true && n.on_missing != n.on_false) r = -2;
+      else { int a = dep(n.on_true), c = dep(n.on_false); r = (a < 0 || c < 0 || a != c) ? -2 : a + 1; }
+      return dep_memo[s] = r;
+    };
+    for (int32_t r : roots) { int dd = dep(r); if (dd < 1 || dd > 10 || (depth >= 0 && dd != depth)) { complete = false; break; } depth = dd; }
+    if (complete) {  // every node used exactly once?
+      std::vector<uint8_t> seen(nodes.size(), 0); std::vector<uint8_t> lseen(leaves.size(), 0);
+      std::function<void(int32_t)> mark = [&](int32_t s) { if (s < 0) { if (lseen[~s]++) complete = false; return; } if (seen[s]++) { complete = false; return; } mark(nodes[s].on_true); if (complete) mark(nodes[s].on_false); };
+      for (int32_t r : roots) if (complete) mark(r);
+    }
+    std::vector<int32_t> leaf_ids;
+    if (complete) {
+      fd.format = FOREST_COMPLETE; fd.depth = depth;
+      size_t W = size_t(1) << (depth + 1); std::vector<uint64_t> blobs(roots.size() * W, 0);
+      leaf_ids.assign(roots.size() << depth, 0);
+      for (size_t t = 0; t < roots.size(); t++) {
+        uint64_t* bl = blobs.data() + t * W; memcpy(&bl[0], &weights[t], 8);
+        std::function<void(int32_t, size_t)> place = [&](int32_t s, size_t h) {
+          if (s < 0) {
+            const TLeaf& lf = leaves[~s];
+            if (classify) bl[h] = (uint64_t)(uint32_t)lf.label; else memcpy(&bl[h], &lf.value, 8);
+            leaf_ids[(t << depth) + (h - (size_t(1) << depth))] = lf.node_id; return;
+          }
+          const TNode& n = nodes[s]; uint32_t a = (n.on_missing == n.on_false && n.on_true != n.on_false) ? 1u : 0u;
+          uint32_t kk = n.thr >= 0 ? K[n.thr] : 0xFFFFFFFFu; uint32_t lo = (uint32_t)feat_of(n) | (a << 31), hi = kk - a;
+          bl[h] = (uint64_t)lo | ((uint64_t)hi << 32);
+          place(n.on_true, 2 * h); place(n.on_false, 2 * h + 1);
+        };
+        place(roots[t], 1);
+      }
+      b.put(&fd.blobs, blobs);
+    } else {
+      fd.format = FOREST_GENERAL; fd.depth = 0;
+      std::vector<uint64_t> blobs; b.put(&fd.blobs, blobs);
+    }
+    b.put(&fd.leaf_node_id, leaf_ids);
+    {  // the general form is always emitted: the engine falls back to it when a tile of keys does not fit on chip
+      std::vector<GNode> g(nodes.size());
+      for (size_t i = 0; i < nodes.size(); i++) {
+        const TNode& n = nodes[i];
+        g[i] = GNode{(uint32_t)feat_of(n), n.thr >= 0 ? K[n.thr] : 0xFFFFFFFFu, n.on_true, n.on_false, n.on_missing};
+      }
+      std::vector<double> gv(leaves.size()); std::vector<int32_t> gl(leaves.size()), gid(leaves.size());
+      for (size_t i = 0; i < leaves.size(); i++) { gv[i] = leaves[i].value; gl[i] = leaves[i].label; gid[i] = leaves[i].node_id; }
+      b.put(&fd.gnodes, g); b.put(&fd.troot, roots); b.put(&fd.gleaf_value, gv); b.put(&fd.gleaf_label, gl); b.put(&fd.tweight, weights);
+      b.put(&fd.gleaf_node_id, gid);
+    }
+  }
+};
+
+void finish_target(Builder& b, bool classify) {
+  // regression results are delivered in the target field's dataType; only java.lang.Double is matched
+  // (Pipeline.scala:94-98); classification labels go through set_labels()
+  if (!b.has_target) b.cm.dev.target_status = ST_EXTRACT;
+  else if (!classify && b.target_dtype != DT_DOUBLE) b.cm.dev.target_status = ST_EXTRACT;
+  else b.cm.dev.target_status = ST_OK;
+}
+
+void compile_tree(const XNode& m, Builder& b) {
+  b.cm.family = "TreeModel"; b.cm.dev.kind = MK_FOREST;
+  bool classify = m.attr("functionName") == "classification";
+  ForestBuilder fb(b, classify); fb.add_tree(m, 1.0); fb.emit(FM_SINGLE);
+  b.set_labels(fb.labels, false); finish_target(b, classify);
+}
+
+void compile_mining(const XNode& m, Builder& b) {
+  b.cm.family = "MiningModel"; b.cm.dev.kind = MK_FOREST;
+  const XNode* sg = m.child("Segmentation"); if (!sg) malformed("MiningModel without Segmentation");
+  bool classify = m.attr("functionName") == "classification"; sv mm = sg->attr("multipleModelMethod");
+  int method = -1;
+  if (!classify) method = mm == "sum" ? FM_SUM : mm == "average" ? FM_AVERAGE : mm == "weightedSum" ? FM_WSUM : mm == "weightedAverage" ? FM_WAVERAGE : -1;
+  else method = mm == "majorityVote" ? FM_VOTE : mm == "weightedMajorityVote" ? FM_WVOTE : -1;
+  if (method < 0) unsupported("multipleModelMethod " + std::string(mm) + " for " + (classify ? "classification" : "regression"));
+  ForestBuilder fb(b, classify);
+  sg->each("Segment", [&](const XNode& s) {
+    const XNode& p = *ForestBuilder::pred_of(s);
+    if (p.name == "False") return;
+    if (p.name != "True") unsupported("Segment predicate other than True/False");
+    const XNode* tm = s.child("TreeModel");
+    if (!tm) unsupported("Segment model other than TreeModel");
+    fb.add_tree(*tm, need_double(s.attr("weight", "1"), "weight"));
+  });
+  if (fb.roots.empty()) unsupported("Segmentation without active segments");
+  fb.emit(method); b.set_labels(fb.labels, false); finish_target(b, classify);
+}
+
+// ---------------------------------------------------------------------------------------------- regression
+int norm_of(sv s) {
+  if (s.empty() || s == "none") return NORM_NONE; if (s == "simplemax") return NORM_SIMPLEMAX; if (s == "softmax") return NORM_SOFTMAX;
+  if (s == "logit") return NORM_LOGIT; if (s == "probit") return NORM_PROBIT; if (s == "cloglog") return NORM_CLOGLOG;
+  if (s == "exp") return NORM_EXP; if (s == "loglog") return NORM_LOGLOG; if (s == "cauchit") return NORM_CAUCHIT;
+  unsupported("normalizationMethod " + std::string(s));
+}
+
+void compile_regression(const XNode& m, Builder& b) {
+  b.cm.family = "RegressionModel"; b.cm.dev.kind = MK_REGRESSION;
+  RegressionDesc& d = b.cm.dev.reg; bool classify = m.attr("functionName") == "classification";
+  d.classify = classify; d.norm = norm_of(m.attr("normalizationMethod", "none"));
+  std::vector<double> icpt; std::vector<int32_t> toff{0}, coff{0}; std::vector<RegTerm> terms; std::vector<RegCat> cats; std::vector<std::string> labels;
+  int F = b.cm.dev.F; bool dense = true;
+  m.each("RegressionTable", [&](const XNode& t) {
+    icpt.push_back(need_double(t.attr("intercept"), "intercept")); labels.push_back(std::string(t.attr("targetCategory")));
+    size_t t0 = terms.size();
+    t.each("NumericPredictor", [&](const XNode& n) {
+      double e = need_double(n.attr("exponent", "1"), "exponent");
+      if (e != std::floor(e)) unsupported("non-integer exponent");
+      sv fname = n.attr("name"); uint8_t dt = b.dict_field(fname).dtype;
+      if (dt == DT_STRING || dt == DT_OTHER) unsupported("NumericPredictor on a non-numeric field");
+      terms.push_back({b.slot_of(fname), (int32_t)e, need_double(n.attr("coefficient"), "coefficient")});
+    });
+    t.each("CategoricalPredictor", [&](const XNode& n) {
+      sv fname = n.attr("name"); uint8_t dt = b.dict_field(fname).dtype; double v;
+      if (dt == DT_STRING || dt == DT_OTHER) unsupported("CategoricalPredictor on a string field");
+      if (!parse_in_dtype(dt, n.attr("value"), &v)) unsupported("CategoricalPredictor value does not parse in the field's dataType");
+      cats.push_back({b.slot_of(fname), 0, v, need_double(n.attr("coefficient"), "coefficient")});
+    });
+    if (t.child("PredictorTerm")) unsupported("PredictorTerm");
+    if ((int)(terms.size() - t0) != F) dense = false;
+    else for (int i = 0; i < F; i++) if (terms[t0 + i].slot != i || terms[t0 + i].exponent != 1) { dense = false; break; }
+    toff.push_back((int32_t)terms.size()); coff.push_back((int32_t)cats.size());
+  });
+  if (icpt.empty()) malformed("no RegressionTable");
+  if (!classify && icpt.size() != 1) unsupported("regression with several RegressionTables");
+  d.n_tables = (int)icpt.size(); dense = dense && cats.empty(); d.dense = dense ? 1 : 0;
+  std::vector<double> w;
+  if (dense) { w.resize(icpt.size() * (size_t)F); for (size_t t = 0; t < icpt.size(); t++) for (int i = 0; i < F; i++) w[t * F + i] = terms[toff[t] + i].coef; }
+  b.put(&d.intercept, icpt); b.put(&d.term_off, toff); b.put(&d.terms, terms); b.put(&d.cat_off, coff); b.put(&d.cats, cats); b.put(&d.dense_w, w);
+  if (classify) b.set_labels(labels, false); else b.set_labels({}, false);
+  finish_target(b, classify);
+}
+
+// ---------------------------------------------------------------------------------------------- neural network
+int act_of(sv s) {
+  static const char* names[] = {"threshold", "logistic", "tanh", "identity", "exponential", "reciprocal", "square", "Gauss", "sine", "cosine", "Elliott", "arctan", "rectifier"};
+  for (int i = 0; i < 13; i++) if (s == names[i]) return i;
+  unsupported("activationFunction " + std::string(s));
+}
+
+void compile_neural(const XNode& m, Builder& b) {
+  b.cm.family = "NeuralNetwork"; b.cm.dev.kind = MK_NEURAL;
+  NeuralDesc& d = b.cm.dev.nn; bool classify = m.attr("functionName") == "classification"; d.classify = classify;
+  sv dflt_act = m.attr("activationFunction", "logistic"), dflt_norm = m.attr("normalizationMethod", "none");
+  double dflt_thr = m.has("threshold") ? need_double(m.attr("threshold"), "threshold") : 0.0;
+  std::vector<NeuralInput> inputs; std::vector<double> pts; std::vector<std::string> prev_ids;
+  auto read_expr = [&](const XNode& df, NeuralInput& in, bool is_output) {
+    for (const XNode* k = df.first; k; k = k->next) {
+      if (k->name == "FieldRef") { in.kind = NI_FIELDREF; in.slot = is_output ? -1 : b.slot_of(k->attr("field"));
+        if (k->has("mapMissingTo")) { in.has_map_missing = 1; in.map_missing = need_double(k->attr("mapMissingTo"), "mapMissingTo"); } return; }
+      if (k->name == "Constant") { in.kind = NI_CONSTANT; in.value = need_double(k->text, "Constant"); return; }
+      if (k->name == "NormDiscrete") {
+        in.kind = NI_NORMDISC;
+        if (!is_output) { sv fname = k->attr("field"); in.slot = b.slot_of(fname); uint8_t dt = b.dict_field(fname).dtype;
+          if (!parse_in_dtype(dt, k->attr("value"), &in.value)) unsupported("NormDiscrete input on a non-numeric field"); }
+        return; }
+      if (k->name == "NormContinuous") {
+        in.kind = NI_NORMCONT; in.slot = is_output ? -1 : b.slot_of(k->attr("field")); in.pts_off = (int32_t)pts.size() / 2;
+        sv o = k->attr("outliers", "asIs"); in.outliers = o == "asMissingValues" ? 1 : o == "asExtremeValues" ? 2 : 0;
+        if (k->has("mapMissingTo")) { in.has_map_missing = 1; in.map_missing = need_double(k->attr("mapMissingTo"), "mapMissingTo"); }
+        k->each("LinearNorm", [&](const XNode& ln) { pts.push_back(need_double(ln.attr("orig"), "orig")); pts.push_back(need_double(ln.attr("norm"), "norm")); in.n_pts++; });
+        if (in.n_pts < 2) malformed("NormContinuous needs two LinearNorm"); return; }
+    }
+    unsupported("DerivedField expression in NeuralNetwork");
+  };
+  const XNode* ni = m.child("NeuralInputs"); if (!ni) malformed("no NeuralInputs");
+  ni->each("NeuralInput", [&](const XNode& in) {
+    const XNode* df = in.child("DerivedField"); if (!df) malformed("NeuralInput without DerivedField");
+    NeuralInput x{}; read_expr(*df, x, false); inputs.push_back(x); prev_ids.push_back(std::string(in.attr("id")));
+  });
+  d.n_inputs = (int)inputs.size(); d.max_width = d.n_inputs;
+  std::vector<double> W, B; int nl = 0;
+  m.each("NeuralLayer", [&](const XNode& L) {
+    if (nl >= MAX_LAYERS) unsupported("more than 8 NeuralLayers");
+    NeuralLayer& ly = d.layers[nl]; ly.n_in = (int)prev_ids.size(); ly.act = act_of(L.attr("activationFunction", dflt_act));
+    sv nm = L.attr("normalizationMethod", dflt_norm); ly.norm = nm == "softmax" ? NORM_SOFTMAX : nm == "simplemax" ? NORM_SIMPLEMAX : NORM_NONE;
+    if (nm != "none" && ly.norm == NORM_NONE) unsupported("layer normalizationMethod " + std::string(nm));
+    ly.threshold = L.has("threshold") ? need_double(L.attr("threshold"), "threshold") : dflt_thr;
+    ly.w_off = (int64_t)W.size(); ly.b_off = (int64_t)B.size();
+    std::vector<std::string> ids;
+    L.each("Neuron", [&](const XNode& n) {
+      ids.push_back(std::string(n.attr("id"))); B.push_back(need_double(n.attr("bias", "0"), "bias"));
+      size_t i = 0;
+      n.each("Con", [&](const XNode& c) {
+        // the accumulation order is the Con order; only "every neuron of the previous layer, in order" is flattened
+        if (i >= prev_ids.size() || c.attr("from") != prev_ids[i]) unsupported("NeuralNetwork that is not layer-wise fully connected in neuron order");
+        W.push_back(need_double(c.attr("weight"), "weight")); i++;
+      });
+      if (i != prev_ids.size()) unsupported("NeuralNetwork that is not layer-wise fully connected in neuron order");
+    });
+    ly.n_out = (int)ids.size(); if (!ly.n_out) malformed("empty NeuralLayer");
+    d.max_width = std::max(d.max_width, ly.n_out); prev_ids = ids; nl++;
+  });
+  if (!nl) malformed("no NeuralLayer");
+  d.n_layers = nl;
+  const XNode* no = m.child("NeuralOutputs"); if (!no) malformed("no NeuralOutputs");
+  std::vector<int32_t> out_neuron; std::vector<std::string> labels; d.out_denorm_n = 0; d.out_denorm_off = 0;
+  no->each("NeuralOutput", [&](const XNode& o) {
+    const XNode* df = o.child("DerivedField"); if (!df) malformed("NeuralOutput without DerivedField");
+    int idx = -1; for (size_t i = 0; i < prev_ids.size(); i++) if (prev_ids[i] == o.attr("outputNeuron")) idx = (int)i;
+    if (idx < 0) unsupported("NeuralOutput not attached to the last layer");
+    NeuralInput x{}; read_expr(*df, x, true);
+    if (classify) { if (x.kind != NI_NORMDISC) unsupported("classification NeuralOutput without NormDiscrete"); labels.push_back(std::string(df->child("NormDiscrete")->attr("value"))); }
+    else if (out_neuron.empty() && x.kind == NI_NORMCONT) { d.out_denorm_off = x.pts_off; d.out_denorm_n = x.n_pts; }
+    else if (!classify && x.kind != NI_FIELDREF && x.kind != NI_NORMCONT) unsupported("regression NeuralOutput expression");
+    out_neuron.push_back(idx);
+  });
+  if (out_neuron.empty()) malformed("no NeuralOutput");
+  d.n_outputs = (int)out_neuron.size();
+  b.put(&d.inputs, inputs); b.put(&d.pts, pts); b.put(&d.weights, W); b.put(&d.biases, B); b.put(&d.out_neuron, out_neuron);
+  b.set_labels(labels, false); finish_target(b, classify);
+}
+
+}  // namespace
+
+CompiledModel compile_pmml(const char* data, size_t len) {
+  XmlDoc doc;
+  try { xml_parse(data, len, doc); } catch (XmlError& e) { throw CompileError(e.what()); }
+  const XNode& root = *doc.root;
+  if (root.name != "PMML") malformed("root element is not PMML");
+  Builder b; memset(&b.cm.dev, 0, sizeof(b.cm.dev));
+  read_dictionary(root, b);
+  const XNode* me = nullptr;
+  for (const XNode* k = root.first; k && !me; k = k->next) {
+    sv n = k->name;
+    if (n == "ClusteringModel" || n == "TreeModel" || n == "MiningModel" || n == "RegressionModel" || n == "NeuralNetwork") me = k;
+    else if (n.size() > 5 && n.substr(n.size() - 5) == "Model") unsupported("model element " + std::string(n));
+    else if (n == "Scorecard" || n == "RuleSetModel" || n == "NaiveBayesModel") unsupported("model element " + std::string(n));
+  }
+  if (!me) malformed("no model element");
+  b.cm.model_name = std::string(me->attr("modelName"));
+  read_schema(*me, b);
+  if (me->name == "ClusteringModel") compile_clustering(*me, b);
+  else if (me->name == "TreeModel") compile_tree(*me, b);
+  else if (me->name == "MiningModel") compile_mining(*me, b);
+  else if (me->name == "RegressionModel") compile_regression(*me, b);
+  else compile_neural(*me, b);
+  return std::move(b.cm);
+}
+
+}  // namespace fjp

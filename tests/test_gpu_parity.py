@@ -1,0 +1,146 @@
+"""GPU parity: the CUDA path, called through the C ABI, against the CPU oracle on the same seeded inputs.
+
+Bar (BASELINE.json north_star): cluster ids, class labels, node ids and statuses bit-exact; continuous scores and
+probabilities within 1e-6 relative (they are in fact expected to be bit-identical for sums, the tolerance is the
+contract).  Reference-pinned vectors: api/PmmlModelSpec.scala:50-83 (k-means only)."""
+import numpy as np
+import pytest
+
+from conftest import golden_bytes, vector_to_batch
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-6
+
+
+def compare(res, ref, rtol=RTOL, exact_scores=False):
+    assert np.array_equal(res["status"], ref["status"]), (res["status"][:20], ref["status"][:20])
+    ok = ref["status"] == 0
+    if exact_scores:
+        assert np.array_equal(res["score"][ok], ref["score"][ok])
+    else:
+        np.testing.assert_allclose(res["score"][ok], ref["score"][ok], rtol=rtol, atol=0)
+    assert np.isnan(res["score"][~ok]).all()
+
+
+def test_golden_vectors_through_c_abi(engine, oracle, gen, golden_vectors):
+    for v in golden_vectors["predict"]:
+        m = engine.compile(golden_bytes(v["model"]))
+        X, pb, rep = vector_to_batch(gen, v)
+        r = engine.score(m, X, pb, rep)
+        if v["score"] is None:
+            assert r["status"][0] != 0 and np.isnan(r["score"][0]), v
+        else:
+            assert r["status"][0] == 0 and r["score"][0] == v["score"], (v, r)
+
+
+@pytest.mark.parametrize("name", ["iris_kmeans43.pmml", "iris_kmeans42.pmml", "iris_kmeans41.pmml", "iris_kmeans40.pmml",
+                                  "iris_kmeans32.pmml", "iris_kmeans_nooutput.pmml", "iris_kmeans_nooutput_notarget.pmml",
+                                  "iris_kmeans_stringfields.pmml"])
+def test_iris_models_vs_oracle(engine, oracle, gen, name):
+    pm = golden_bytes(name)
+    m, om = engine.compile(pm), oracle.OracleModel(pm)
+    assert m.active_fields == om.active_fields and m.model_name == om.model_name
+    X = gen.iris_events(5000)
+    rng = np.random.default_rng(7)
+    pres = rng.random(X.shape) > 0.2
+    pb = gen.pack_present(pres)
+    for args in [(X, None, None), (X, pb, None), (X, pb, 0.0)]:
+        r, o = engine.score(m, *args), om.predict(*args)
+        compare(r, o, exact_scores=True)
+        assert np.array_equal(r["aux"][o["status"] == 0], o["aux"][o["status"] == 0])
+
+
+def test_c2_kmeans_k64_f128(engine, oracle, gen):
+    pm, arr = gen.config_c2()
+    m, om = engine.compile(pm), oracle.OracleModel(pm)
+    for p_missing in (0.0, 0.05):
+        X, pres, pb = gen.events(8192, 128, gen.SEED_BASE + 2, p_missing)
+        r, o = engine.score(m, X, pb), om.predict(X, pb, nthreads=8)
+        compare(r, o, exact_scores=True)
+        assert np.array_equal(r["aux"], o["aux"])
+        assert np.array_equal(r["score"], gen.kmeans_numpy(arr["centroids"], X, pres))
+
+
+@pytest.mark.parametrize("dtype,method", [("double", "sum"), ("float", "sum"), ("double", "average")])
+def test_gbt_small_vs_oracle(engine, oracle, gen, dtype, method):
+    pm, arr = gen.gbt_pmml(T=37, depth=5, F=13, seed=11, dtype=dtype, method=method)
+    m, om = engine.compile(pm), oracle.OracleModel(pm)
+    assert "format=complete" in m.describe and "enc=float" in m.describe
+    X, pres, pb = gen.events(20000, 13, 12, 0.15)
+    X[::97, 3] = np.nan            # present NaN: greatest in compareTo order
+    X[::89, 5] = np.inf
+    X[::83, 7] = -0.0
+    r = engine.score(m, X, pb, node_ids=True)
+    o = om.predict(X, pb, node_ids=True, nthreads=8)
+    compare(r, o, exact_scores=True)
+    assert np.array_equal(r["node_ids"], o["node_ids"])   # leaf ids bit-exact
+    np.testing.assert_allclose(r["score"], gen.gbt_numpy(arr, np.nan_to_num(X, nan=np.inf), pres), rtol=1e-12)
+
+
+def test_c4_gbt_500_trees_vs_oracle_and_numpy(engine, oracle, gen):
+    pm, arr = gen.gbt_pmml()
+    m, om = engine.compile(pm), oracle.OracleModel(pm)
+    X, pres, pb = gen.events(4096, 100, gen.SEED_BASE + 4, 0.10)
+    r = engine.score(m, X, pb, node_ids=True)
+    o = om.predict(X, pb, node_ids=True, nthreads=8)
+    compare(r, o, exact_scores=True)
+    assert np.array_equal(r["node_ids"], o["node_ids"])
+    # size-independent check at a larger size: numpy restatement of the same walk
+    X, pres, pb = gen.events(1 << 17, 100, 99, 0.10)
+    r = engine.score(m, X, pb)
+    assert (r["status"] == 0).all()
+    assert np.array_equal(r["score"], gen.gbt_numpy(arr, X, pres))
+
+
+def test_rf_majority_vote(engine, oracle, gen):
+    pm, arr = gen.rf_pmml(T=50, depth=6, F=20, n_labels=4, seed=21)
+    m, om = engine.compile(pm), oracle.OracleModel(pm)
+    X, pres, pb = gen.events(20000, 20, 22, 0.1)
+    r, o = engine.score(m, X, pb, node_ids=True), om.predict(X, pb, node_ids=True, nthreads=8)
+    compare(r, o, exact_scores=True)
+    assert np.array_equal(r["node_ids"], o["node_ids"])
+    assert np.array_equal(r["score"], gen.rf_numpy(arr, X, pres))
+
+
+def test_c3_multinomial_regression(engine, oracle, gen):
+    pm, arr = gen.regression_pmml()
+    m, om = engine.compile(pm), oracle.OracleModel(pm)
+    X, pres, pb = gen.events(2048, 1000, gen.SEED_BASE + 3)
+    r, o = engine.score(m, X, n_probs=20), om.predict(X, n_probs=20, nthreads=8)
+    compare(r, o, exact_scores=True)                       # labels bit-exact
+    np.testing.assert_allclose(r["probs"], o["probs"], rtol=RTOL)
+
+
+def test_regression_generic_and_missing(engine, oracle, gen):
+    pm, arr = gen.linear_regression_pmml(F=8, seed=7, normalization="none", exponents=True)
+    m, om = engine.compile(pm), oracle.OracleModel(pm)
+    X, pres, pb = gen.events(4000, 8, 5, 0.05)
+    r, o = engine.score(m, X, pb), om.predict(X, pb)
+    compare(r, o)
+    assert (o["status"] == 3).any() and (o["status"] == 0).any()   # a missing predictor leaves no result
+
+
+def test_neural_network(engine, oracle, gen):
+    pm, arr = gen.nn_pmml()   # 64 -> 256 -> 256 -> 8
+    m, om = engine.compile(pm), oracle.OracleModel(pm)
+    X, pres, pb = gen.events(4096, 64, gen.SEED_BASE + 5)
+    r, o = engine.score(m, X, n_probs=8), om.predict(X, n_probs=8, nthreads=8)
+    compare(r, o, exact_scores=True)
+    np.testing.assert_allclose(r["probs"], o["probs"], rtol=RTOL)
+    for act in ("tanh", "logistic"):
+        pm, arr = gen.nn_pmml(n_in=10, hidden=(12,), n_out=3, seed=3, activation=act)
+        m, om = engine.compile(pm), oracle.OracleModel(pm)
+        X, pres, pb = gen.events(1000, 10, 4)
+        r, o = engine.score(m, X, n_probs=3), om.predict(X, n_probs=3)
+        compare(r, o, exact_scores=True)
+        np.testing.assert_allclose(r["probs"], o["probs"], rtol=RTOL)
+
+
+def test_empty_model_and_size_mismatch(engine, gen):
+    X = np.ones((5, 4))
+    r = engine.score(None, X)
+    assert (r["status"] == 5).all() and np.isnan(r["score"]).all()
+    m = engine.compile(golden_bytes("iris_kmeans43.pmml"))
+    r = engine.score(m, np.ones((3, 3)))
+    assert (r["status"] == 1).all()
+    assert engine.launch_count > 0
