@@ -1,0 +1,306 @@
+#!/usr/bin/env python3
+"""bench.py -- headline benchmark: scored events/sec for the 500-tree GBT PMML (BASELINE.json config C4).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+  (N > 1: python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...)
+
+A "step" is one pass of the hot path (PmmlModel.predict for every event of a micro-batch, reference:
+flink-jpmml-scala/src/main/scala/io/radicalbit/flink/pmml/scala/api/PmmlModel.scala:109-119) over one batch of 2^22
+synthetic events per GPU.  Events are sharded across ranks; there is no collective on the scoring path (weak scaling).
+Rank 0 prints ONE JSON line.
+
+  value      whole-job events/s, inputs resident in HBM, timed with CUDA events on the launching stream
+  e2e        same metric through the C ABI with pinned HOST buffers (H2D + kernel + D2H inside the timed region)
+  roofline   HBM roofline of the forest kernel (algorithmic 824 B/event) + the gather rooflines
+  cpu_baseline  the oracle port (oracle/oracle.cc) on the box's host cores, bounded sample (reported, not the target)
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+F, TREES, DEPTH, P_MISSING = 100, 500, 8, 0.10
+EVENTS_PER_GPU = 1 << 22          # N = 2^22 per GPU
+E2E_EVENTS_PER_GPU = 1 << 21      # per step through the host-buffer entry point
+ALGO_HBM_BYTES = 824              # 100*8 features + 16 present bits + 8 score   
+ALGO_GATHER_BYTES = 32000         # 500 trees * 8 levels * 8 B node record       
+SEED = 20261106 + 4
+WORKLOAD = "C4: MiningModel GBT sum, 500 complete trees depth 8, 100 double features, 10% missing"
+
+
+def peaks():
+    p = {"hbm_gbs": 6650.0, "source": "fallback (B200_PROFILING.md)"}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            m = json.load(f)
+        p = {"hbm_gbs": float(m["hbm_gbs"]), "source": "measured (MEASURED_PEAKS.json)"}
+    except Exception:
+        pass
+    try:
+        with open(os.path.join(ROOT, "profiles", "microbench_r01.json")) as f:
+            p["micro"] = json.load(f)
+    except Exception:
+        p["micro"] = {}
+    return p
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        pw = [float(r[2]) for r in self.rows if len(r) > 2 and r[2].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 3 + i and r[3 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": reasons}
+
+
+def make_model_bytes():
+    from flink_jpmml_b200 import pmmlgen
+    return pmmlgen.gbt_pmml(T=TREES, depth=DEPTH, F=F, seed=SEED)
+
+
+def device_events(torch, n, seed, device):
+    """x ~ N(0,1)^100 doubles, each slot missing w.p. 0.10 (present-bit cleared), generated on the device."""
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    X = torch.randn(n, F, generator=g, device=device, dtype=torch.float64)
+    W = (F + 31) // 32
+    P = torch.empty(n, W, dtype=torch.int32, device=device)
+    shifts = torch.arange(32, device=device, dtype=torch.int64)
+    step = 1 << 18
+    for lo in range(0, n, step):
+        hi = min(n, lo + step)
+        bits = torch.zeros(hi - lo, W * 32, dtype=torch.int64, device=device)
+        bits[:, :F] = (torch.rand(hi - lo, F, generator=g, device=device) >= P_MISSING).to(torch.int64)
+        w = (bits.view(hi - lo, W, 32) << shifts).sum(-1)
+        P[lo:hi] = torch.where(w >= 2 ** 31, w - 2 ** 32, w).to(torch.int32)
+    return X, P
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path.  JPMML/Flink cannot run here (no JVM on the box), so this is the
+    oracle port (oracle/oracle.cc: literal per-event interpreter) on all host cores, same metric / config."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import numpy as np
+    from flink_jpmml_b200 import pmmlgen
+    from oracle import oracle
+    pm, _ = make_model_bytes()
+    om = oracle.OracleModel(pm)
+    cores = os.cpu_count() or 1
+    # calibrate: ~3 s of CPU work per step
+    X, pres, pb = pmmlgen.events(4096, F, SEED, P_MISSING)
+    t = time.perf_counter(); om.predict(X, pb, nthreads=cores); rate = 4096 / (time.perf_counter() - t)
+    n = int(max(4096, min(1 << 20, rate * 3.0)))
+    X, pres, pb = pmmlgen.events(n, F, SEED + 1, P_MISSING)
+    for _ in range(args.warmup):
+        om.predict(X[:4096], pb[:4096], nthreads=cores)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        om.predict(X, pb, nthreads=cores)
+    dt = time.perf_counter() - t0
+    v = n * args.steps / dt
+    line = {"impl": "reference", "metric": "scored events/sec", "value": v, "unit": "events/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic", "config": {"workload": WORKLOAD, "events_per_step": n},
+            "cpu_baseline": {"value": v, "unit": "events/s", "cores": cores, "kind": "port",
+                             "sample": f"{n} events/step x {args.steps} steps, oracle/oracle.cc with {cores} threads (JPMML/Flink not runnable: no JVM)"},
+            "e2e": {"value": v, "unit": "events/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--events", type=int, default=EVENTS_PER_GPU, help="events per GPU per step (default 2^22)")
+    ap.add_argument("--no-latency", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import numpy as np
+    import torch
+    from flink_jpmml_b200 import capi
+
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    L = capi.lib()
+    eng = capi.Engine(local)
+    pm, arrays = make_model_bytes()
+    model = eng.compile(pm)
+
+    n = args.events
+    X, P = device_events(torch, n, SEED + 1000 * rank, dev)
+    score = torch.empty(n, dtype=torch.float64, device=dev); status = torch.empty(n, dtype=torch.uint8, device=dev)
+    stream = torch.cuda.Stream(device=dev)
+
+    def step_device():
+        rc = L.fjp_score_device(eng._h, model._h, X.data_ptr(), P.data_ptr(), None, n, F, score.data_ptr(), status.data_ptr(), None, C.c_void_p(stream.cuda_stream))
+        if rc != 0:
+            raise RuntimeError(L.fjp_last_error().decode())
+
+    def barrier():
+        if dist:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    # ------------------------------------------------------------------ device-resident throughput ("value")
+    for _ in range(args.warmup):
+        step_device()
+    barrier()
+    sampler = ClockSampler(local); sampler.start(); time.sleep(0.3)
+    launches0 = eng.launch_count
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with torch.cuda.stream(stream):
+        ev0.record(stream)
+        for _ in range(args.steps):
+            step_device()
+        ev1.record(stream)
+    barrier()
+    ms_dev = ev0.elapsed_time(ev1)
+    launches = eng.launch_count - launches0
+    ok_rows = int((status == 0).sum().item())
+
+    # ------------------------------------------------------------------ end to end through the host-buffer entry point
+    ne = min(E2E_EVENTS_PER_GPU, n); W = (F + 31) // 32
+    hX = torch.empty(ne, F, dtype=torch.float64).pin_memory(); hP = torch.empty(ne, W, dtype=torch.int32).pin_memory()
+    hX.copy_(X[:ne]); hP.copy_(P[:ne])
+    hS = torch.empty(ne, dtype=torch.float64).pin_memory(); hT = torch.empty(ne, dtype=torch.uint8).pin_memory()
+
+    def step_e2e():
+        rc = L.fjp_score_batch(eng._h, model._h, hX.data_ptr(), hP.data_ptr(), None, ne, F, hS.data_ptr(), hT.data_ptr(), None)
+        if rc != 0:
+            raise RuntimeError(L.fjp_last_error().decode())
+
+    for _ in range(2):
+        step_e2e()
+    barrier()
+    e2e_steps = max(3, min(args.steps, 10))
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        step_e2e()
+    torch.cuda.synchronize(dev)
+    t_e2e = time.perf_counter() - t0
+    clocks = sampler.stop()
+    e2e_match = bool(torch.equal(hS[:4096], score[:4096].cpu()))
+
+    # ------------------------------------------------------------------ max over ranks
+    t = torch.tensor([ms_dev, t_e2e * 1e3], dtype=torch.float64, device=dev)
+    if dist:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_dev_max, ms_e2e_max = float(t[0]), float(t[1])
+
+    # ------------------------------------------------------------------ latency sweep + CPU baseline: rank 0 only
+    latency, cpu = None, None
+    if rank == 0 and not args.no_latency:
+        latency = {}
+        ticket = C.c_int()
+        for b in (1, 64, 1024, 16384, 262144):
+            reps = 1000 if b <= 16384 else 200
+            ts = []
+            for _ in range(reps):
+                t1 = time.perf_counter()
+                L.fjp_submit(eng._h, model._h, hX.data_ptr(), hP.data_ptr(), None, b, F, hS.data_ptr(), hT.data_ptr(), None, C.byref(ticket))
+                L.fjp_wait(eng._h, ticket.value)
+                ts.append((time.perf_counter() - t1) * 1e3)
+            ts.sort()
+            latency[str(b)] = {"p50_ms": round(ts[len(ts) // 2], 4), "p99_ms": round(ts[int(len(ts) * 0.99) - 1], 4)}
+    if rank == 0 and world == 1 and not args.no_cpu:
+        from oracle import oracle   # cpu_baseline leg: the one place bench.py may execute the oracle
+        cores = os.cpu_count() or 1
+        om = oracle.OracleModel(pm)
+        xs = hX[:4096].numpy(); ps = hP[:4096].numpy().view(np.uint32)
+        t1 = time.perf_counter(); om.predict(xs, ps, nthreads=cores); rate = 4096 / (time.perf_counter() - t1)
+        ns = int(max(4096, min(ne, rate * 12.0)))
+        xs = hX[:ns].numpy(); ps = hP[:ns].numpy().view(np.uint32)
+        t1 = time.perf_counter(); o = om.predict(xs, ps, nthreads=cores); dt = time.perf_counter() - t1
+        t1 = time.perf_counter(); om.predict(xs[:2048], ps[:2048], nthreads=1); dt1 = time.perf_counter() - t1
+        cpu = {"value": ns / dt, "unit": "events/s", "cores": cores, "kind": "port",
+               "sample": f"{ns} events of the same workload, oracle/oracle.cc with {cores} threads (JPMML/Flink not runnable on this box: no JVM)",
+               "single_thread_value": 2048 / dt1,
+               "parity_on_sample": "bit-exact" if (np.array_equal(o["score"], hS[:ns].numpy()) and np.array_equal(o["status"], hT[:ns].numpy())) else "MISMATCH"}
+
+    if rank == 0:
+        pk = peaks()
+        total = n * world * args.steps
+        value = total / (ms_dev_max / 1e3)
+        per_launch_s = ms_dev_max / 1e3 / args.steps
+        achieved = n * ALGO_HBM_BYTES / per_launch_s / 1e9
+        micro = pk.get("micro", {})
+        gather = n * ALGO_GATHER_BYTES / per_launch_s / 1e9
+        roof = {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": achieved / pk["hbm_gbs"],
+                "traffic": micro.get("forest_kernel_dram_bytes_per_launch"), "peak_source": pk["source"],
+                "kernel": "forest_complete_kernel<8,false>", "algorithmic_bytes_per_event": ALGO_HBM_BYTES,
+                "note": "the walk is bound by shared-memory gathers / issue, not HBM: see gather",
+                "gather": {"algorithmic_bytes_per_event": ALGO_GATHER_BYTES, "achieved_gbs": gather,
+                           "l2_gather_peak_gbs": micro.get("l2_gather_8B_2MB_GBs"), "smem_gather_peak_gbs": micro.get("smem_gather_8B_random_GBs"),
+                           "frac_of_l2_gather": (gather / micro["l2_gather_8B_2MB_GBs"]) if micro.get("l2_gather_8B_2MB_GBs") else None,
+                           "frac_of_smem_gather": (gather / micro["smem_gather_8B_random_GBs"]) if micro.get("smem_gather_8B_random_GBs") else None}}
+        e2e_value = ne * world * e2e_steps / (ms_e2e_max / 1e3)
+        line = {"metric": "scored events/sec", "value": value, "unit": "events/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms_dev_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+                "data": "synthetic (torch philox on device, seed 20261110+1000*rank)",
+                "config": {"workload": WORKLOAD, "events_per_gpu_per_step": n, "l2_policy": "inputs (3.4 GB/GPU) larger than L2",
+                           "model": model.describe, "parallelism": f"events sharded over {world} GPU(s), model replicated, no collective"},
+                "e2e": {"value": e2e_value, "unit": "events/s", "h2d_bytes_per_step": ne * (F * 8 + W * 4), "d2h_bytes_per_step": ne * 9,
+                        "events_per_gpu_per_step": ne, "steps": e2e_steps, "matches_device_path": e2e_match,
+                        "api": "fjp_score_batch (pinned host buffers, chunked copy/compute overlap)"},
+                "gpu_launches": launches, "rows_scored_ok": ok_rows, "roofline": roof, "cpu_baseline": cpu, "clocks": clocks,
+                "latency_ms": latency}
+        print(json.dumps(line), flush=True)
+    if dist:
+        dist.barrier()
+        dist.destroy_process_group()
+    eng.close()
+
+
+if __name__ == "__main__":
+    main()

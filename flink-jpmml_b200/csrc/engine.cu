@@ -59,7 +59,7 @@ static void make_describe(fjp_model* m) {
          " method=" + std::to_string(d.forest.method) + " nodes=" + std::to_string(m->cm.n_nodes);
     ForestLaunch fl;
     if (m->d_blob && d.forest.method != FM_SINGLE && plan_forest_complete(d, &fl))
-      s += " tile_events=" + std::to_string(fl.events_per_cta) + " trees_per_stage=" + std::to_string(fl.trees_per_stage) +
+      s += " tile_events=" + std::to_string(fl.events_per_cta) + " trees_per_stage=" + std::to_string(fl.trees_per_stage) + " interleave=" + std::to_string(fl.trees_interleaved) +
            " smem=" + std::to_string(fl.smem_bytes);
   } else if (d.kind == MK_CLUSTERING) s += " k=" + std::to_string(d.cluster.k) + " fields=" + std::to_string(d.cluster.nf) + " fast=" + std::to_string(d.cluster.fast);
   else if (d.kind == MK_REGRESSION) s += " tables=" + std::to_string(d.reg.n_tables) + " dense=" + std::to_string(d.reg.dense) + " norm=" + std::to_string(d.reg.norm);

@@ -10,6 +10,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <cstdlib>
 
 #include "kernels.h"
 
@@ -160,14 +161,17 @@ __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.
 
 // ================================================================================================ forest, complete trees
 // One CTA scores a tile of E = blockDim.x events (one event per thread) against ALL trees:
-//   phase A  rows are read coalesced from HBM, prepared, turned into 32-bit order keys and written TRANSPOSED into
-//            shared memory (keys[f][e]) so that the per-lane gather in phase B is bank-conflict free;
+//   phase A  rows are read coalesced from HBM (software-pipelined through registers), prepared, turned into 32-bit
+//            order keys and written TRANSPOSED into shared memory (keys[f][e]) so that the per-lane gather in phase B
+//            is bank-conflict free;
 //   phase B  tree blobs (nodes+leaves, 2^(D+1) x 8 B each) stream through a 2-stage shared-memory ring filled by
 //            bulk async copies (cp.async.bulk + mbarrier) from the L2-resident model; every warp walks the same tree
 //            for 32 different events, TI trees interleaved per thread for ILP; leaf values accumulate in double in
 //            segment order (bit-identical to a sequential sum).
-// Shared memory:  keys F*E*4 | ring 2*G*blob | row stage 32*S*8 | votes (classification) | barriers
-template <int D, bool CLASSIFY>
+// Shared memory:  keys F*E*4 | ring 2*G*blob (phase A's row stage aliases it when it fits) | votes | barriers
+// MODE: 0 sum/average, 1 weighted sum/average, 2 majority vote.  DBG: also write per-tree node ids.
+constexpr int FC_RMAX = 10;  // row-stage elements a thread keeps in flight
+template <int D, int TI, int MODE, bool DBG>
 __global__ void __launch_bounds__(512, 1)
 forest_complete_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, const ForestLaunch fl) {
   extern __shared__ __align__(128) uint8_t smem[];
@@ -184,6 +188,8 @@ forest_complete_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a,
   uint8_t* row_fail = smem + fl.off_fail;
   const int T = fd.n_trees, NG = (T + G - 1) / G;
   const long ntiles = (a.n + E - 1) / E;
+  const bool rows_alias_ring = fl.off_rows == fl.off_ring;
+  const uint32_t inv_f = 0xFFFFFFFFu / (uint32_t)F + 1u;  // i / F == umulhi(i, inv_f) for i < 2^16
 
   if (tid == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
   __syncthreads();
@@ -198,19 +204,31 @@ forest_complete_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a,
 
   for (long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const long row0 = tile * E;
-    if (tid == 0) { fence_proxy_async(); issue(0); if (NG > 1) issue(1); }
+    if (!rows_alias_ring && tid == 0) { fence_proxy_async(); issue(0); if (NG > 1) issue(1); }
     row_fail[tid] = 0;
-    // ---------------- phase A: load, prepare, encode, transpose
-    for (int rb = 0; rb < E; rb += 32) {
-      for (int r = warp; r < 32; r += nwarps) {
-        long row = row0 + rb + r;
-        if (row < a.n) {
-          const double* src = a.X + row * (long)F;
-          for (int f = lane; f < F; f += 32) xs[r * S + f] = __ldcs(src + f);
+    // ---------------- phase A: load, prepare, encode, transpose (32 rows per chunk; lane <-> row when encoding)
+    {
+      double v[FC_RMAX];
+      auto chunk_cnt = [&](int rb) -> int { long left = a.n - (row0 + rb); int rows = left >= 32 ? 32 : (left > 0 ? (int)left : 0); return rows * F; };
+      auto load_chunk = [&](int rb) {
+        const double* src = a.X + (row0 + rb) * (long)F; const int cnt = chunk_cnt(rb);
+#pragma unroll
+        for (int k = 0; k < FC_RMAX; k++) { int i = tid + k * E; if (i < cnt) v[k] = __ldcs(src + i); }
+      };
+      load_chunk(0);
+      for (int rb = 0; rb < E; rb += 32) {
+        const int cnt = chunk_cnt(rb);
+#pragma unroll
+        for (int k = 0; k < FC_RMAX; k++) {
+          int i = tid + k * E;
+          if (i < cnt) { int r = (int)__umulhi((uint32_t)i, inv_f); xs[r * S + (i - r * F)] = v[k]; }
         }
-      }
-      __syncthreads();
-      {
+        {  // wide rows: the part that does not fit the register batch
+          const double* src = a.X + (row0 + rb) * (long)F;
+          for (int i = tid + FC_RMAX * E; i < cnt; i += E) { int r = (int)__umulhi((uint32_t)i, inv_f); xs[r * S + (i - r * F)] = __ldcs(src + i); }
+        }
+        __syncthreads();
+        if (rb + 32 < E) load_chunk(rb + 32);  // in flight while this chunk is encoded
         long row = row0 + rb + lane;
         if (row < a.n) {
           double rep = 0; bool has_rep = false;
@@ -220,58 +238,62 @@ forest_complete_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a,
             double raw = xs[lane * S + f]; bool present = true;
             if (a.present) { int wi = f >> 5; if (wi != pw_idx) { pw = a.present[row * (long)a.present_stride + wi]; pw_idx = wi; } present = (pw >> (f & 31)) & 1u; }
             if (!present && has_rep) { raw = rep; present = true; }
-            double v; int st;
-            if (m.prep_simple) { st = present ? 0 : 1; v = raw; if (fd.enc != ENC_FLOAT && m.prep[f].dtype == DT_FLOAT) v = (double)(float)raw; }
-            else st = prep_value(m.prep[f], m.prep_pool, present, raw, v);
+            double val; int st;
+            if (m.prep_simple) { st = present ? 0 : 1; val = raw; if (fd.enc != ENC_FLOAT && m.prep[f].dtype == DT_FLOAT) val = (double)(float)raw; }
+            else st = prep_value(m.prep[f], m.prep_pool, present, raw, val);
             uint32_t key = 0;
-            if (st == 0) key = encode_key(fd, f, v); else if (st == 2) row_fail[rb + lane] = 1;
+            if (st == 0) key = encode_key(fd, f, val); else if (st == 2) row_fail[rb + lane] = 1;
             keys[f * E + rb + lane] = key;
           }
         }
+        __syncthreads();
       }
-      __syncthreads();
     }
+    if (rows_alias_ring && tid == 0) { fence_proxy_async(); issue(0); if (NG > 1) issue(1); }
     // ---------------- phase B: walk all trees
-    const uint32_t* kp = keys + tid;
+    const uint32_t kbase = smem_u32(keys) + 4u * tid;   // byte address of this event's key column
+    const uint32_t E4 = 4u * E;
     double sum = 0.0, wsum = 0.0;
-    if (CLASSIFY) for (int l = 0; l < m.n_labels; l++) { votes[l * E + tid] = 0; votes[(m.n_labels + l) * E + tid] = 0xFFFF; }
     uint32_t seen = 0;  // classification: number of distinct labels seen so far (insertion order)
-
+    if (MODE == 2) for (int l = 0; l < m.n_labels; l++) { votes[l * E + tid] = 0; votes[(m.n_labels + l) * E + tid] = 0xFFFF; }
     for (int g = 0; g < NG; g++) {
       uint32_t slot = q_wait & 1u;
       mbar_wait(&bars[slot], (q_wait >> 1) & 1u); q_wait++;
-      const uint64_t* base = ring + (size_t)slot * G * blob_words;
+      const uint32_t base = smem_u32(ring + (size_t)slot * G * blob_words);
       const int nt = min(G, T - g * G);
-      constexpr int TI = 4;
       for (int t = 0; t < nt; t += TI) {
-        uint32_t idx[TI]; const uint2* bl[TI];
+        uint32_t idx[TI], bl[TI];
 #pragma unroll
-        for (int k = 0; k < TI; k++) { idx[k] = 1; bl[k] = reinterpret_cast<const uint2*>(base + (size_t)min(t + k, nt - 1) * blob_words); }
+        for (int k = 0; k < TI; k++) { idx[k] = 1; bl[k] = base + (uint32_t)min(t + k, nt - 1) * blob_bytes; }
 #pragma unroll
         for (int d = 0; d < (D ? D : 16); d++) {
           if (!D && d >= depth) break;
 #pragma unroll
           for (int k = 0; k < TI; k++) {
-            uint2 nd = bl[k][idx[k]];
-            uint32_t key = kp[(nd.x & 0x7FFFFFFFu) * E];
-            idx[k] = 2u * idx[k] + ((key - (nd.x >> 31)) > nd.y ? 1u : 0u);
+            uint32_t nx, ny, key;
+            asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(nx), "=r"(ny) : "r"(bl[k] + idx[k] * 8u));
+            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(key) : "r"(kbase + (nx & 0x7FFFFFFFu) * E4));
+            uint32_t vv = key - (nx >> 31);
+            // ny holds ~ka: vv + ~ka carries out exactly when vv > ka ("go right"), and the carry is added
+            // into idx + idx:  idx = 2*idx + (vv > ka)  in two integer instructions
+            asm("{\n\t.reg .u32 t;\n\tadd.cc.u32 t, %2, %3;\n\taddc.u32 %0, %1, %1;\n\t}" : "=r"(idx[k]) : "r"(idx[k]), "r"(ny), "r"(vv));
           }
         }
 #pragma unroll
         for (int k = 0; k < TI; k++) {
           if (t + k < nt) {
-            const double* bd = reinterpret_cast<const double*>(bl[k]);
-            if (!CLASSIFY) {
-              double v = bd[idx[k]];
-              if (fd.method == FM_WSUM || fd.method == FM_WAVERAGE) { double w = bd[0]; sum += w * v; wsum += w; } else sum += v;
+            if (MODE != 2) {
+              double lv, w;
+              asm volatile("ld.shared.f64 %0, [%1];" : "=d"(lv) : "r"(bl[k] + idx[k] * 8u));
+              if (MODE == 1) { asm volatile("ld.shared.f64 %0, [%1];" : "=d"(w) : "r"(bl[k])); sum += w * lv; wsum += w; } else sum += lv;
             } else {
-              int lab = (int)bl[k][idx[k]].x;
-              // majorityVote counts are exact integers; weighted votes are not supported in the on-chip path
+              uint32_t lab;
+              asm volatile("ld.shared.u32 %0, [%1];" : "=r"(lab) : "r"(bl[k] + idx[k] * 8u));
               uint16_t c = votes[lab * E + tid];
               if (c == 0) votes[(m.n_labels + lab) * E + tid] = (uint16_t)seen++;
               votes[lab * E + tid] = c + 1;
             }
-            if (a.node_ids && row0 + tid < a.n) a.node_ids[(row0 + tid) * (long)a.node_stride + g * G + t + k] =
+            if (DBG) if (a.node_ids && row0 + tid < a.n) a.node_ids[(row0 + tid) * (long)a.node_stride + g * G + t + k] =
                 fd.leaf_node_id[((size_t)(g * G + t + k) << depth) + (idx[k] - (1u << depth))];
           }
         }
@@ -283,12 +305,10 @@ forest_complete_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a,
     long row = row0 + tid;
     if (row < a.n) {
       if (row_fail[tid]) write_out(a, row, 0, ST_PREP, -1);
-      else if (!CLASSIFY) {
+      else if (MODE != 2) {
         double v = sum;
         if (fd.method == FM_AVERAGE) v = sum / (double)T; else if (fd.method == FM_WAVERAGE) v = sum / wsum;
-        int aux = -1;
-        if (fd.method == FM_SINGLE && a.node_ids == nullptr && a.aux) aux = 0;  // single-tree aux is filled by the general path
-        write_out(a, row, apply_target(m.tx, v), m.target_status, aux);
+        write_out(a, row, apply_target(m.tx, v), m.target_status, -1);
       } else {
         int best = -1; uint32_t bc = 0, bo = 0;
         for (int l = 0; l < m.n_labels; l++) {
@@ -298,7 +318,7 @@ forest_complete_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a,
         write_label(m, a, row, best, best);
       }
     }
-    __syncthreads();  // keys / votes / row_fail are reused by the next tile
+    __syncthreads();  // keys / votes / row_fail / ring (row stage) are reused by the next tile
   }
 }
 
@@ -670,16 +690,19 @@ static void query_device() {
   cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
 }
 
-template <int D, bool C>
+template <int D, int TI, int MODE, bool DBG>
 static cudaError_t launch_fc(const DeviceModel& m, const BatchArgs& a, const ForestLaunch& fl, int grid, int block, cudaStream_t s) {
-  auto k = forest_complete_kernel<D, C>;
+  auto k = forest_complete_kernel<D, TI, MODE, DBG>;
   cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fl.smem_bytes);
   if (e != cudaSuccess) return e;
   k<<<grid, block, fl.smem_bytes, s>>>(m, a, fl);
   return cudaGetLastError();
 }
 
+static int env_int(const char* name, int dflt) { const char* v = getenv(name); return v && *v ? atoi(v) : dflt; }
+
 // Picks the tile geometry for the on-chip forest kernel; returns false when no tile of >= 64 events fits.
+// FJP_FOREST_E / FJP_FOREST_G / FJP_FOREST_TI override the choice (tuning aid).
 bool plan_forest_complete(const DeviceModel& m, ForestLaunch* out) {
   query_device();
   const ForestDesc& fd = m.forest;
@@ -688,20 +711,29 @@ bool plan_forest_complete(const DeviceModel& m, ForestLaunch* out) {
   if (fd.classify && m.n_labels > 64) return false;
   const size_t budget = (size_t)g_smem_optin - 1024;
   const size_t blob = (size_t)(2u << fd.depth) * 8;
-  const int S = (m.F | 1) + 0;  // odd row stride (in doubles): conflict-free column reads of the row stage
-  static const int Es[] = {512, 384, 256, 192, 128, 64};
-  for (int E : Es) {
-    size_t keys = (size_t)m.F * E * 4;
-    size_t rows = (size_t)32 * S * 8;
+  const int S = m.F | 1;  // odd row stride (in doubles): conflict-free column reads of the row stage
+  const size_t rows = (size_t)32 * S * 8;
+  const int ti = env_int("FJP_FOREST_TI", 8) >= 8 ? 8 : 4;
+  const int force_e = env_int("FJP_FOREST_E", 0), force_g = env_int("FJP_FOREST_G", 0);
+  const int t_round = ((fd.n_trees + ti - 1) / ti) * ti;
+  for (int E = 512; E >= 64; E -= 32) {
+    if (force_e && E != force_e) continue;
+    size_t keys = ((size_t)m.F * E * 4 + 127) & ~size_t(127);
     size_t votes = fd.classify ? (size_t)2 * m.n_labels * E * 2 : 0;
-    size_t fixed = keys + rows + votes + 64 + E + 256;
-    if (fixed + 2 * 4 * blob > budget) continue;
-    int G = (int)((budget - fixed) / (2 * blob)); G = (G / 4) * 4; if (G > 16) G = 16;
-    if (G > ((fd.n_trees + 3) / 4) * 4) G = ((fd.n_trees + 3) / 4) * 4;
-    ForestLaunch fl{}; fl.events_per_cta = E; fl.trees_per_stage = G; fl.row_stride = S;
-    size_t off = keys; off = (off + 127) & ~size_t(127);
-    fl.off_ring = (uint32_t)off; off += 2 * (size_t)G * blob;
-    fl.off_rows = (uint32_t)off; off += rows;
+    size_t fixed = keys + votes + 64 + E + 256;
+    if (fixed + 2 * ti * blob > budget) continue;
+    int G = (int)((budget - fixed) / (2 * blob)); G = (G / ti) * ti; if (G > 16) G = 16 / ti * ti;
+    if (force_g) G = force_g;
+    if (G > t_round) G = t_round;
+    if (G < ti || fixed + 2 * (size_t)G * blob > budget) continue;
+    size_t ring = 2 * (size_t)G * blob;
+    bool alias = rows <= ring;
+    if (!alias && fixed + ring + rows > budget) continue;
+    // prefer more resident warps, but never fewer than 8 trees in the ring
+    ForestLaunch fl{}; fl.events_per_cta = E; fl.trees_per_stage = G; fl.row_stride = S; fl.trees_interleaved = ti;
+    size_t off = keys;
+    fl.off_ring = (uint32_t)off; off += ring;
+    if (alias) fl.off_rows = fl.off_ring; else { fl.off_rows = (uint32_t)off; off += rows; }
     fl.off_votes = (uint32_t)off; off += votes; off = (off + 15) & ~size_t(15);
     fl.off_bars = (uint32_t)off; off += 64;
     fl.off_fail = (uint32_t)off; off += E;
@@ -723,11 +755,14 @@ cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t 
         long ntiles = (a.n + fl.events_per_cta - 1) / fl.events_per_cta;
         int grid = (int)(ntiles < g_num_sms ? ntiles : g_num_sms);
         const bool c = m.forest.classify; const int d = m.forest.depth;
-#define FJP_FC(DD) (c ? launch_fc<DD, true>(m, a, fl, grid, fl.events_per_cta, s) : launch_fc<DD, false>(m, a, fl, grid, fl.events_per_cta, s))
+#define FJP_FC2(DD, TT, MM) (a.node_ids ? launch_fc<DD, 4, MM, true>(m, a, fl, grid, fl.events_per_cta, s) : launch_fc<DD, TT, MM, false>(m, a, fl, grid, fl.events_per_cta, s))
+#define FJP_FC1(DD, MM) (fl.trees_interleaved >= 8 ? FJP_FC2(DD, 8, MM) : FJP_FC2(DD, 4, MM))
+#define FJP_FC(DD) (c ? FJP_FC1(DD, 2) : ((m.forest.method == FM_WSUM || m.forest.method == FM_WAVERAGE) ? FJP_FC1(DD, 1) : FJP_FC1(DD, 0)))
         if (d == 8) return FJP_FC(8);
         if (d == 6) return FJP_FC(6);
-        if (d == 4) return FJP_FC(4);
         return FJP_FC(0);
+#undef FJP_FC2
+#undef FJP_FC1
 #undef FJP_FC
       }
       if (m.forest.classify && m.n_labels > 64) return cudaErrorInvalidValue;

@@ -25,7 +25,7 @@ struct BatchArgs {
 };
 
 struct ForestLaunch {  // tile geometry of forest_complete_kernel
-  int events_per_cta, trees_per_stage, row_stride;
+  int events_per_cta, trees_per_stage, row_stride, trees_interleaved;
   uint32_t off_ring, off_rows, off_votes, off_bars, off_fail, smem_bytes;
 };
 

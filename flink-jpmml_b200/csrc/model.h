@@ -61,7 +61,8 @@ static constexpr int32_t LEAF_NULL = INT32_MIN;  // successor meaning "null pred
 struct ForestDesc {
   int n_trees, depth, format, enc, method, classify;
   // FOREST_COMPLETE: n_trees blobs of 2^(depth+1) 8-byte words: [0] = segment weight (double), [1 .. 2^d-1] = nodes
-  // in heap order {lo: feat | a<<31, hi: ka}, [2^d .. 2^(d+1)-1] = leaves (double value, or label index as u64)
+  // in heap order {lo: feat | a<<31, hi: ~ka}, [2^d .. 2^(d+1)-1] = leaves (double value, or label index as u64);
+  // the walk goes right iff key(x[feat]) - a > ka (unsigned; key 0 = missing, a = 1 sends missing right)
   const uint64_t* blobs;
   const int32_t* leaf_node_id;  // complete: n_trees * 2^depth PMML node ids (aux output)
   // FOREST_GENERAL

@@ -512,7 +512,7 @@ struct ForestBuilder {
             leaf_ids[(t << depth) + (h - (size_t(1) << depth))] = lf.node_id; return;
           }
           const TNode& n = nodes[s]; uint32_t a = (n.on_missing == n.on_false && n.on_true != n.on_false) ? 1u : 0u;
-          uint32_t kk = n.thr >= 0 ? K[n.thr] : 0xFFFFFFFFu; uint32_t lo = (uint32_t)feat_of(n) | (a << 31), hi = kk - a;
+          uint32_t kk = n.thr >= 0 ? K[n.thr] : 0xFFFFFFFFu; uint32_t lo = (uint32_t)feat_of(n) | (a << 31), hi = ~(kk - a);
           bl[h] = (uint64_t)lo | ((uint64_t)hi << 32);
           place(n.on_true, 2 * h); place(n.on_false, 2 * h + 1);
         };
