@@ -1,0 +1,182 @@
+// flinkjpmml.hpp -- host-side mirror (C++17) of the reference's user-facing types and its two Flink operators,
+// written above the C ABI (include/fjpmml.h).  The reference is Scala (no JVM toolchain in this image), so this is
+// the compiled-language restatement a Scala/JNI shim would follow; names, argument meaning and error behaviour are
+// the reference's.  S/ = flink-jpmml-scala/src/main/scala/io/radicalbit/flink/pmml/scala/
+//
+//   Vector / DenseVector / SparseVector      org.apache.flink.ml.math (input type of S/api/PmmlModel.scala:109)
+//   Target / Score / EmptyScore / Prediction S/models/prediction/Target.scala:40-84, Prediction.scala:29-57
+//   exceptions                               S/api/exceptions/package.scala:27-53
+//   ModelId / ModelInfo                      S/models/core/ModelId.scala:26-48, ModelInfo.scala:26
+//   AddMessage / DelMessage                  S/models/control/ServingMessage.scala:24-44
+//   MetadataManager / ModelsManager          S/api/managers/MetadataManager.scala:34-61, ModelsManager.scala:34-47
+//   ModelReader                              S/api/reader/ModelReader.scala:27, FsReader.scala:41-49 (local files only)
+//   PmmlModel                                S/api/PmmlModel.scala:24-157
+//   EvaluationFunction                       S/api/functions/EvaluationFunction.scala:31-42 + S/package.scala:44-50, 73-80
+//   EvaluationCoFunction                     S/api/functions/EvaluationCoFunction.scala:42-120 + S/package.scala:57-69
+//
+// What is different on purpose: the operators buffer events into pinned-host micro-batches and emit predictions in
+// arrival order when the batch is flushed (size reached, flush(), snapshotState(), close()).  Every buffered event
+// holds the model it was bound to when it arrived, so control messages keep their "takes effect between events"
+// meaning (T/RichConnectedStreamSpec.scala:83-95, 187-204) without flushing.
+#pragma once
+#include <cmath>
+#include <cstdint>
+#include <map>
+#include <memory>
+#include <optional>
+#include <stdexcept>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "../../../include/fjpmml.h"
+
+namespace flinkjpmml {
+
+// ---------------------------------------------------------------------------------------- exceptions
+struct InputValidationException : std::runtime_error { using std::runtime_error::runtime_error; };
+struct InputPreparationException : std::runtime_error { using std::runtime_error::runtime_error; };
+struct JPMMLExtractionException : std::runtime_error { using std::runtime_error::runtime_error; };
+struct EmptyEvaluatorException : std::runtime_error { using std::runtime_error::runtime_error; };
+struct ModelLoadingException : std::runtime_error { using std::runtime_error::runtime_error; };   // job-fatal
+struct WrongModelIdFormat : std::runtime_error { using std::runtime_error::runtime_error; };       // job-fatal
+
+// ---------------------------------------------------------------------------------------- vectors
+struct Vector {
+  int size = 0;
+  bool sparse = false;
+  std::vector<double> data;     // dense: size values; sparse: one value per index
+  std::vector<int> indices;     // sparse only
+  static Vector dense(std::vector<double> v) { Vector r; r.size = (int)v.size(); r.data = std::move(v); return r; }
+  static Vector sparseOf(int size, std::vector<int> idx, std::vector<double> val) {
+    Vector r; r.size = size; r.sparse = true; r.indices = std::move(idx); r.data = std::move(val); return r;
+  }
+};
+
+// ---------------------------------------------------------------------------------------- prediction ADT
+struct Target {
+  bool empty = true; double value = 0;
+  static Target score(double v) { Target t; t.empty = false; t.value = v; return t; }
+  double get() const { if (empty) throw std::out_of_range("EmptyScore.nan"); return value; }   // Target.scala:45-47
+  double getOrElse(double dflt) const { return empty ? dflt : value; }                           // Target.scala:31-35
+  bool operator==(const Target& o) const { return empty == o.empty && (empty || value == o.value); }
+};
+struct Prediction {
+  Target value; uint8_t status = FJP_ST_NOMODEL;  // status: why it is empty (diagnostics; the reference logs instead)
+  bool operator==(const Prediction& o) const { return value == o.value; }
+};
+
+// ---------------------------------------------------------------------------------------- ids and control messages
+struct ModelId {
+  std::string name; int64_t version = 0;
+  static constexpr const char* separatorSymbol = "_";
+  static ModelId fromIdentifier(const std::string& id);   // throws WrongModelIdFormat (ModelId.scala:36-40)
+  std::string identifier() const { return name + separatorSymbol + std::to_string(version); }
+  int32_t hashCode() const;                               // (name + "_" + version).hashCode (ModelId.scala:46)
+  bool operator<(const ModelId& o) const { return name != o.name ? name < o.name : version < o.version; }
+  bool operator==(const ModelId& o) const { return name == o.name && version == o.version; }
+};
+int32_t javaStringHashCode(const std::string& s);
+struct ModelInfo { std::string path; };
+
+struct ServingMessage {
+  enum Kind { Add, Del } kind; std::string name; int64_t version; std::string path; int64_t occurredOn;
+  ModelId modelId() const { return ModelId{name, version}; }
+  ModelInfo modelInfo() const { return ModelInfo{path}; }
+};
+inline ServingMessage AddMessage(std::string name, int64_t version, std::string path, int64_t occurredOn) { return {ServingMessage::Add, std::move(name), version, std::move(path), occurredOn}; }
+inline ServingMessage DelMessage(std::string name, int64_t version, int64_t occurredOn) { return {ServingMessage::Del, std::move(name), version, "", occurredOn}; }
+
+using Metadata = std::map<ModelId, ModelInfo>;   // immutable.Map[ModelId, ModelInfo] / CheckpointType.scala:29-32
+struct MetadataManager {  // Add on an existing id is ignored; Del removes (MetadataManager.scala:41-59)
+  static Metadata apply(const ServingMessage& m, const Metadata& md);
+};
+
+// ---------------------------------------------------------------------------------------- reader + model
+struct ModelReader {
+  std::string sourcePath;
+  explicit ModelReader(std::string p) : sourcePath(std::move(p)) {}
+  std::string buildDistributedPath() const;   // whole file as a string; throws std::runtime_error
+};
+
+class Engine;  // thin RAII over fjp_engine
+
+class PmmlModel {
+ public:
+  PmmlModel() = default;                                   // PmmlModel.empty (EmptyEvaluator)
+  PmmlModel(fjp_engine* e, fjp_model* m) : engine_(e), model_(m, &fjp_model_release) {}
+  static PmmlModel fromReader(fjp_engine* e, const ModelReader& reader);   // throws ModelLoadingException
+  static PmmlModel empty() { return PmmlModel(); }
+  bool isEmpty() const { return !model_; }
+  std::string modelName() const;                           // throws EmptyEvaluatorException on the empty model
+  int activeFields() const { return model_ ? fjp_model_num_fields(model_.get()) : 0; }
+  // One event, synchronously (a micro-batch of one): the literal drop-in for S/api/PmmlModel.scala:109-119.
+  Prediction predict(const Vector& v, std::optional<double> replaceNan = std::nullopt) const;
+  fjp_model* handle() const { return model_.get(); }
+  fjp_engine* engine() const { return engine_; }
+ private:
+  fjp_engine* engine_ = nullptr;
+  std::shared_ptr<fjp_model> model_;
+};
+
+// ---------------------------------------------------------------------------------------- micro-batch buffer
+// Rows of one model packed for fjp_score_batch / fjp_submit: pinned X (dense slots), present bits, replace values.
+class MicroBatch {
+ public:
+  MicroBatch(int n_fields, int capacity);
+  ~MicroBatch();
+  MicroBatch(const MicroBatch&) = delete;
+  bool full() const { return n_ >= cap_; }
+  int size() const { return n_; }
+  int append(const Vector& v, std::optional<double> replaceNan);   // returns the row index
+  void clear() { n_ = 0; any_sparse_ = false; any_replace_ = false; }
+  int score(fjp_engine* e, fjp_model* m);                         // fills score()/status()
+  const double* scores() const { return score_; }
+  const uint8_t* statuses() const { return status_; }
+ private:
+  int F_, W_, cap_, n_ = 0; bool any_sparse_ = false, any_replace_ = false;
+  double* X_; uint32_t* present_; double* replace_; double* score_; uint8_t* status_;
+};
+
+// ---------------------------------------------------------------------------------------- fixed-model operator
+// stream.evaluate(reader)(f) / quickEvaluate(reader): S/package.scala:44-50, 73-80.
+class EvaluationFunction {
+ public:
+  EvaluationFunction(fjp_engine* e, ModelReader reader, int maxBatch) : engine_(e), reader_(std::move(reader)), max_batch_(maxBatch) {}
+  void open();                                             // loads the model; failure -> ModelLoadingException
+  const PmmlModel& evaluator() const { return model_; }
+  // buffer one event; predictions come back through drain() in arrival order
+  void processElement(const Vector& v, std::optional<double> replaceNan = std::nullopt);
+  void flush();
+  std::vector<Prediction> drain() { std::vector<Prediction> r; r.swap(out_); return r; }
+  void close() { flush(); }
+ private:
+  fjp_engine* engine_; ModelReader reader_; int max_batch_; PmmlModel model_;
+  std::unique_ptr<MicroBatch> batch_; std::vector<Prediction> out_;
+  std::vector<int> pending_;   // per buffered event: row in batch_, or -1 = size mismatch (EmptyScore at once)
+};
+
+// ---------------------------------------------------------------------------------------- dynamic operator
+// events.withSupportStream(ctrl).evaluate(f): S/package.scala:57-69, S/api/functions/EvaluationCoFunction.scala:42-120.
+class EvaluationCoFunction {
+ public:
+  EvaluationCoFunction(fjp_engine* e, int maxBatch) : engine_(e), max_batch_(maxBatch) {}
+  void initializeState(const std::vector<Metadata>& restored);   // union of the restored maps (:68-83)
+  Metadata snapshotState();                                      // flushes, then returns the metadata (:63-66)
+  void processElement1(const std::string& modelId, const Vector& v, std::optional<double> replaceNan = std::nullopt);
+  void processElement2(const ServingMessage& control);           // manageModels then manageMetadata (:56-61)
+  void flush();
+  std::vector<Prediction> drain() { std::vector<Prediction> r; r.swap(out_); return r; }
+  PmmlModel fromMetadata(const std::string& modelId);            // (:93-97)
+  PmmlModel loadModel(const std::string& path);                  // (:85-91)
+  const Metadata& servingMetadata() const { return metadata_; }
+  int servingModels() const { return engine_ ? fjp_table_size(engine_) : 0; }
+ private:
+  struct Pending { int bucket; int row; };
+  struct Bucket { PmmlModel model; std::unique_ptr<MicroBatch> batch; };
+  fjp_engine* engine_; int max_batch_; Metadata metadata_;
+  std::vector<Bucket> buckets_; std::vector<Pending> pending_; std::vector<Prediction> out_;
+  int bucket_for(const PmmlModel& m);
+};
+
+}  // namespace flinkjpmml

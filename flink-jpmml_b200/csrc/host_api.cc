@@ -1,0 +1,303 @@
+// host_api.cc -- implementation of host/flinkjpmml.hpp and the extern "C" operator-emulator entry points declared in
+// include/fjpmml_host.h (what pytest drives in place of a Flink mini-cluster; T/utils/FlinkTestKits.scala:32-67).
+#include <cstring>
+#include <fstream>
+#include <limits>
+#include <sstream>
+
+#include "../../include/fjpmml_host.h"
+#include "host/flinkjpmml.hpp"
+
+namespace flinkjpmml {
+
+// ---------------------------------------------------------------------------------------- ModelId
+int32_t javaStringHashCode(const std::string& s) {
+  uint32_t h = 0;  // java.lang.String.hashCode over UTF-16 units; ids are ASCII
+  for (unsigned char c : s) h = 31u * h + c;
+  return (int32_t)h;
+}
+int32_t ModelId::hashCode() const { return javaStringHashCode(identifier()); }
+
+// RegexParsers semantics of S/models/core/ModelId.scala:30-40: whitespace is skipped before every token; the name is
+// a lowercase-hex UUID; the version token must be all digits up to the end of the input.
+ModelId ModelId::fromIdentifier(const std::string& id) {
+  size_t p = 0;
+  auto skip_ws = [&] { while (p < id.size() && (id[p] == ' ' || id[p] == '\t' || id[p] == '\n' || id[p] == '\r' || id[p] == '\f' || id[p] == '\v')) p++; };
+  auto hex = [&](size_t n) { for (size_t i = 0; i < n; i++, p++) { if (p >= id.size()) return false; char c = id[p]; if (!((c >= '0' && c <= '9') || (c >= 'a' && c <= 'f'))) return false; } return true; };
+  auto dash = [&] { if (p < id.size() && id[p] == '-') { p++; return true; } return false; };
+  skip_ws();
+  size_t start = p;
+  bool ok = hex(8) && dash() && hex(4) && dash() && hex(4) && dash() && hex(4) && dash() && hex(12);
+  if (!ok) throw WrongModelIdFormat("string matching regex `[0-9a-f]{8}-[0-9a-f]{4}-[0-9a-f]{4}-[0-9a-f]{4}-[0-9a-f]{12}' expected");
+  std::string name = id.substr(start, p - start);
+  skip_ws();
+  if (p >= id.size() || id[p] != '_') throw WrongModelIdFormat("`_' expected");
+  p++;
+  skip_ws();
+  if (p >= id.size()) throw WrongModelIdFormat("string matching regex `^\\d+$' expected");
+  int64_t v = 0;
+  for (size_t q = p; q < id.size(); q++) {
+    if (id[q] < '0' || id[q] > '9') throw WrongModelIdFormat("string matching regex `^\\d+$' expected");
+    if (v > (std::numeric_limits<int64_t>::max() - (id[q] - '0')) / 10) throw WrongModelIdFormat("version does not fit a Long");
+    v = v * 10 + (id[q] - '0');
+  }
+  return ModelId{name, v};
+}
+
+Metadata MetadataManager::apply(const ServingMessage& m, const Metadata& md) {
+  Metadata out = md;
+  if (m.kind == ServingMessage::Add) { if (!out.count(m.modelId())) out[m.modelId()] = m.modelInfo(); }  // existing id: ignored (+WARN in the reference)
+  else out.erase(m.modelId());
+  return out;
+}
+
+// ---------------------------------------------------------------------------------------- reader + model
+std::string ModelReader::buildDistributedPath() const {
+  std::ifstream f(sourcePath, std::ios::binary);
+  if (!f) throw std::runtime_error("cannot open " + sourcePath);
+  std::ostringstream ss; ss << f.rdbuf();
+  return ss.str();
+}
+
+PmmlModel PmmlModel::fromReader(fjp_engine* e, const ModelReader& reader) {
+  std::string text;
+  try { text = reader.buildDistributedPath(); } catch (std::exception& ex) { throw ModelLoadingException(ex.what()); }
+  fjp_model* m = nullptr; char err[512] = {0};
+  if (fjp_model_compile(e, text.data(), text.size(), &m, err, sizeof err) != 0) throw ModelLoadingException(err);
+  return PmmlModel(e, m);
+}
+std::string PmmlModel::modelName() const {
+  if (!model_) throw EmptyEvaluatorException("EmptyEvaluator.None");
+  return fjp_model_name(model_.get());
+}
+Prediction PmmlModel::predict(const Vector& v, std::optional<double> replaceNan) const {
+  Prediction p;
+  if (!model_) { p.status = FJP_ST_NOMODEL; return p; }                 // EmptyEvaluatorException -> EmptyScore
+  if (v.size != activeFields()) { p.status = FJP_ST_SIZE; return p; }     // InputValidationException -> EmptyScore
+  MicroBatch mb(v.size, 1);
+  mb.append(v, replaceNan);
+  if (mb.score(engine_, model_.get()) != 0) throw std::runtime_error(fjp_last_error());
+  p.status = mb.statuses()[0];
+  if (p.status == FJP_ST_SCORE) p.value = Target::score(mb.scores()[0]);
+  return p;
+}
+
+// ---------------------------------------------------------------------------------------- micro-batch
+MicroBatch::MicroBatch(int n_fields, int capacity) : F_(n_fields), W_((n_fields + 31) / 32), cap_(capacity) {
+  size_t bx = (size_t)cap_ * F_ * 8, bp = (size_t)cap_ * W_ * 4, b8 = (size_t)cap_ * 8;
+  X_ = static_cast<double*>(fjp_host_alloc(bx ? bx : 8)); present_ = static_cast<uint32_t*>(fjp_host_alloc(bp ? bp : 8));
+  replace_ = static_cast<double*>(fjp_host_alloc(b8)); score_ = static_cast<double*>(fjp_host_alloc(b8));
+  status_ = static_cast<uint8_t*>(fjp_host_alloc(cap_));
+  if (!X_ || !present_ || !replace_ || !score_ || !status_) throw std::runtime_error("pinned host allocation failed");
+}
+MicroBatch::~MicroBatch() { fjp_host_free(X_); fjp_host_free(present_); fjp_host_free(replace_); fjp_host_free(score_); fjp_host_free(status_); }
+
+int MicroBatch::append(const Vector& v, std::optional<double> replaceNan) {
+  int r = n_++;
+  double* x = X_ + (size_t)r * F_; uint32_t* p = present_ + (size_t)r * W_;
+  if (!v.sparse) {  // DenseVector: every slot present (VectorConverter.scala:49-54)
+    memcpy(x, v.data.data(), (size_t)F_ * 8);
+    for (int w = 0; w < W_; w++) p[w] = 0xFFFFFFFFu;
+  } else {          // SparseVector: only listed indices are present (VectorConverter.scala:61-67, 81-84)
+    any_sparse_ = true;
+    memset(x, 0, (size_t)F_ * 8); memset(p, 0, (size_t)W_ * 4);
+    for (size_t k = 0; k < v.indices.size(); k++) { int i = v.indices[k]; if (i >= 0 && i < F_) { x[i] = v.data[k]; p[i >> 5] |= 1u << (i & 31); } }
+  }
+  replace_[r] = replaceNan ? *replaceNan : std::numeric_limits<double>::quiet_NaN();
+  if (replaceNan) any_replace_ = true;
+  return r;
+}
+int MicroBatch::score(fjp_engine* e, fjp_model* m) {
+  if (n_ == 0) return 0;
+  return fjp_score_batch(e, m, X_, any_sparse_ ? present_ : nullptr, any_replace_ ? replace_ : nullptr, n_, F_, score_, status_, nullptr);
+}
+
+static Prediction make_prediction(uint8_t status, double score) {
+  Prediction p; p.status = status;
+  if (status == FJP_ST_SCORE) p.value = Target::score(score);
+  return p;
+}
+
+// ---------------------------------------------------------------------------------------- EvaluationFunction
+void EvaluationFunction::open() {
+  model_ = PmmlModel::fromReader(engine_, reader_);   // ModelLoadingException propagates: the job fails (EvaluationFunction.scala:37-40)
+  batch_ = std::make_unique<MicroBatch>(model_.activeFields(), max_batch_);
+}
+void EvaluationFunction::processElement(const Vector& v, std::optional<double> replaceNan) {
+  if (model_.isEmpty()) open();   // `lazy val evaluator`
+  if (v.size != model_.activeFields()) pending_.push_back(-1);
+  else pending_.push_back(batch_->append(v, replaceNan));
+  if (batch_->full()) flush();
+}
+void EvaluationFunction::flush() {
+  if (pending_.empty()) return;
+  if (batch_->score(engine_, model_.handle()) != 0) throw std::runtime_error(fjp_last_error());
+  for (int r : pending_) out_.push_back(r < 0 ? make_prediction(FJP_ST_SIZE, 0) : make_prediction(batch_->statuses()[r], batch_->scores()[r]));
+  pending_.clear(); batch_->clear();
+}
+
+// ---------------------------------------------------------------------------------------- EvaluationCoFunction
+void EvaluationCoFunction::initializeState(const std::vector<Metadata>& restored) {
+  metadata_.clear();
+  for (auto& m : restored) for (auto& kv : m) metadata_.insert(kv);   // union list state: every subtask's map
+}
+Metadata EvaluationCoFunction::snapshotState() { flush(); return metadata_; }
+
+PmmlModel EvaluationCoFunction::loadModel(const std::string& path) { return PmmlModel::fromReader(engine_, ModelReader(path)); }
+
+PmmlModel EvaluationCoFunction::fromMetadata(const std::string& modelId) {
+  ModelId id = ModelId::fromIdentifier(modelId);                       // WrongModelIdFormat is not caught: job-fatal
+  auto it = metadata_.find(id);
+  if (it == metadata_.end()) return PmmlModel::empty();
+  PmmlModel loaded = loadModel(it->second.path);                       // lazy load on the first event for this id
+  fjp_table_add(engine_, id.name.c_str(), id.version, loaded.handle()); // servingModels += (id -> model), keyed by the full id
+  return loaded;
+}
+
+int EvaluationCoFunction::bucket_for(const PmmlModel& m) {
+  for (size_t i = 0; i < buckets_.size(); i++) if (buckets_[i].model.handle() == m.handle()) return (int)i;
+  buckets_.push_back(Bucket{m, std::make_unique<MicroBatch>(m.activeFields(), max_batch_)});
+  return (int)buckets_.size() - 1;
+}
+
+void EvaluationCoFunction::processElement1(const std::string& modelId, const Vector& v, std::optional<double> replaceNan) {
+  // servingModels.getOrElse(event.modelId.hashCode, fromMetadata(event.modelId))   (S/package.scala:62)
+  PmmlModel model;
+  fjp_model* cached = nullptr;
+  {
+    // the reference looks the cache up by the raw id's hashCode first; an id that was never parsed cannot be cached,
+    // so parsing first is equivalent except that a malformed id fails here instead of in fromMetadata -- same outcome
+    ModelId id = ModelId::fromIdentifier(modelId);
+    if (!engine_) throw std::runtime_error("no engine: scoring needs a CUDA device (there is no CPU path)");
+    cached = fjp_table_get(engine_, id.name.c_str(), id.version);
+  }
+  if (cached) model = PmmlModel(engine_, cached); else model = fromMetadata(modelId);
+  if (model.isEmpty()) { pending_.push_back({-1, FJP_ST_NOMODEL}); }
+  else if (v.size != model.activeFields()) { pending_.push_back({-1, FJP_ST_SIZE}); }
+  else {
+    int b = bucket_for(model);
+    int row = buckets_[b].batch->append(v, replaceNan);
+    pending_.push_back({b, row});
+    if (buckets_[b].batch->full()) flush();
+  }
+  if ((int)pending_.size() >= max_batch_) flush();
+}
+
+void EvaluationCoFunction::processElement2(const ServingMessage& control) {
+  // manageModels first, then manageMetadata (EvaluationCoFunction.scala:56-61, Appendix B of SURVEY.md)
+  if (control.kind == ServingMessage::Del && engine_) fjp_table_del(engine_, control.name.c_str(), control.version);
+  metadata_ = MetadataManager::apply(control, metadata_);
+  // buffered events keep the model they were bound to (each bucket holds a reference), so nothing is flushed here
+}
+
+void EvaluationCoFunction::flush() {
+  if (pending_.empty()) return;
+  for (auto& b : buckets_) if (b.batch->size() && b.batch->score(engine_, b.model.handle()) != 0) throw std::runtime_error(fjp_last_error());
+  for (auto& p : pending_) {
+    if (p.bucket < 0) out_.push_back(make_prediction((uint8_t)p.row, 0));
+    else out_.push_back(make_prediction(buckets_[p.bucket].batch->statuses()[p.row], buckets_[p.bucket].batch->scores()[p.row]));
+  }
+  pending_.clear(); buckets_.clear();   // dropping the buckets releases models deleted in the meantime
+}
+
+}  // namespace flinkjpmml
+
+// ============================================================================================ C wrappers
+using namespace flinkjpmml;
+
+struct fjh_eval_function { std::unique_ptr<EvaluationFunction> op; };
+struct fjh_cofunction { std::unique_ptr<EvaluationCoFunction> op; };
+
+static void set_err(char* err, size_t cap, const char* msg) { if (err && cap) { strncpy(err, msg, cap - 1); err[cap - 1] = 0; } }
+static Vector make_vector(const double* values, int size, const int* indices, int nnz) {
+  if (!indices) return Vector::dense(std::vector<double>(values, values + size));
+  return Vector::sparseOf(size, std::vector<int>(indices, indices + nnz), std::vector<double>(values, values + nnz));
+}
+static std::optional<double> opt(double r) { return std::isnan(r) ? std::nullopt : std::optional<double>(r); }
+static long poll_out(std::vector<Prediction>& buf, std::vector<Prediction> fresh, double* scores, uint8_t* status, long cap) {
+  buf.insert(buf.end(), fresh.begin(), fresh.end());
+  long n = std::min<long>(cap, (long)buf.size());
+  for (long i = 0; i < n; i++) { scores[i] = buf[i].value.empty ? std::numeric_limits<double>::quiet_NaN() : buf[i].value.value; status[i] = buf[i].status; }
+  buf.erase(buf.begin(), buf.begin() + n);
+  return n;
+}
+template <class F> static int guarded(char* err, size_t cap, F&& f) {
+  try { f(); return FJH_OK; }
+  catch (WrongModelIdFormat& e) { set_err(err, cap, e.what()); return FJH_WRONG_MODEL_ID_FORMAT; }
+  catch (ModelLoadingException& e) { set_err(err, cap, e.what()); return FJH_MODEL_LOADING; }
+  catch (std::exception& e) { set_err(err, cap, e.what()); return FJH_ENGINE_ERROR; }
+}
+
+extern "C" {
+
+int fjh_model_id_parse(const char* id, char* name_out, size_t name_cap, int64_t* version_out) {
+  try { ModelId m = ModelId::fromIdentifier(id); if (name_out && name_cap) { strncpy(name_out, m.name.c_str(), name_cap - 1); name_out[name_cap - 1] = 0; } if (version_out) *version_out = m.version; return FJH_OK; }
+  catch (WrongModelIdFormat&) { return FJH_WRONG_MODEL_ID_FORMAT; }
+}
+int32_t fjh_model_id_hash(const char* name, int64_t version) { return ModelId{name, version}.hashCode(); }
+
+int fjh_predict(fjp_engine* e, fjp_model* m, const double* values, int size, const int* indices, int nnz, double replace_nan,
+                double* score, uint8_t* status) {
+  try {
+    PmmlModel model; if (m) { fjp_model_retain(m); model = PmmlModel(e, m); }
+    Prediction p = model.predict(make_vector(values, size, indices, nnz), opt(replace_nan));
+    *score = p.value.empty ? std::numeric_limits<double>::quiet_NaN() : p.value.value; *status = p.status; return FJH_OK;
+  } catch (std::exception&) { return FJH_ENGINE_ERROR; }
+}
+
+fjh_eval_function* fjh_eval_function_open(fjp_engine* e, const char* path, int max_batch, char* err, size_t errcap) {
+  auto h = std::make_unique<fjh_eval_function>();
+  h->op = std::make_unique<EvaluationFunction>(e, ModelReader(path), max_batch);
+  if (guarded(err, errcap, [&] { h->op->open(); }) != FJH_OK) return nullptr;
+  return h.release();
+}
+const char* fjh_eval_function_model_name(fjh_eval_function* h) { static thread_local std::string s; s = h->op->evaluator().modelName(); return s.c_str(); }
+int fjh_eval_function_process(fjh_eval_function* h, const double* values, int size, const int* indices, int nnz, double replace_nan) {
+  return guarded(nullptr, 0, [&] { h->op->processElement(make_vector(values, size, indices, nnz), opt(replace_nan)); });
+}
+int fjh_eval_function_flush(fjh_eval_function* h) { return guarded(nullptr, 0, [&] { h->op->flush(); }); }
+long fjh_eval_function_poll(fjh_eval_function* h, double* scores, uint8_t* status, long cap) {
+  static std::unordered_map<fjh_eval_function*, std::vector<Prediction>> bufs;
+  return poll_out(bufs[h], h->op->drain(), scores, status, cap);
+}
+void fjh_eval_function_close(fjh_eval_function* h) { if (h) { try { h->op->close(); } catch (...) {} delete h; } }
+
+fjh_cofunction* fjh_cofunction_create(fjp_engine* e, int max_batch) {
+  auto h = new fjh_cofunction(); h->op = std::make_unique<EvaluationCoFunction>(e, max_batch); h->op->initializeState({}); return h;
+}
+int fjh_cofunction_process_event(fjh_cofunction* h, const char* model_id, const double* values, int size, const int* indices, int nnz,
+                                 double replace_nan, char* err, size_t errcap) {
+  return guarded(err, errcap, [&] { h->op->processElement1(model_id, make_vector(values, size, indices, nnz), opt(replace_nan)); });
+}
+int fjh_cofunction_process_control(fjh_cofunction* h, int is_add, const char* name, int64_t version, const char* path, int64_t occurred_on) {
+  return guarded(nullptr, 0, [&] { h->op->processElement2(is_add ? AddMessage(name, version, path ? path : "", occurred_on) : DelMessage(name, version, occurred_on)); });
+}
+int fjh_cofunction_flush(fjh_cofunction* h, char* err, size_t errcap) { return guarded(err, errcap, [&] { h->op->flush(); }); }
+long fjh_cofunction_poll(fjh_cofunction* h, double* scores, uint8_t* status, long cap) {
+  static std::unordered_map<fjh_cofunction*, std::vector<Prediction>> bufs;
+  return poll_out(bufs[h], h->op->drain(), scores, status, cap);
+}
+// snapshot format: one "name_version<TAB>path<LF>" line per entry (the checkpointed HashMap[ModelId, ModelInfo])
+long fjh_cofunction_snapshot(fjh_cofunction* h, char* buf, long cap) {
+  std::string s;
+  try { for (auto& kv : h->op->snapshotState()) s += kv.first.identifier() + "\t" + kv.second.path + "\n"; } catch (std::exception&) { return -1; }
+  if ((long)s.size() + 1 > cap) return -(long)s.size() - 1;
+  memcpy(buf, s.c_str(), s.size() + 1);
+  return (long)s.size();
+}
+int fjh_cofunction_restore(fjh_cofunction* h, const char* const* snapshots, int n_snapshots) {
+  return guarded(nullptr, 0, [&] {
+    std::vector<Metadata> all;
+    for (int k = 0; k < n_snapshots; k++) {
+      Metadata md; std::istringstream in(snapshots[k]); std::string line;
+      while (std::getline(in, line)) { size_t tab = line.find('\t'); if (tab == std::string::npos) continue; md[ModelId::fromIdentifier(line.substr(0, tab))] = ModelInfo{line.substr(tab + 1)}; }
+      all.push_back(std::move(md));
+    }
+    h->op->initializeState(all);
+  });
+}
+int fjh_cofunction_metadata_size(fjh_cofunction* h) { return (int)h->op->servingMetadata().size(); }
+int fjh_cofunction_cached_models(fjh_cofunction* h) { return h->op->servingModels(); }
+void fjh_cofunction_destroy(fjh_cofunction* h) { delete h; }
+
+}  // extern "C"

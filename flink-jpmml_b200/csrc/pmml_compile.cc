@@ -393,14 +393,14 @@ struct ForestBuilder {
     cx.chained[key] = r; return r;
   }
 
-  void add_tree(const XNode& tm, double weight) {
-    check_nested_schema(tm);
+  void add_tree(const XNode& tm, double weight, bool nested) {
+    if (nested) check_nested_schema(tm);
     TreeCtx cx; sv mvs = tm.attr("missingValueStrategy", "none");
     cx.mvs = mvs == "none" ? 0 : mvs == "defaultChild" ? 1 : mvs == "lastPrediction" ? 2 : mvs == "nullPrediction" ? 3 : -1;
     if (cx.mvs < 0) unsupported("missingValueStrategy " + std::string(mvs));
     cx.last_on_no_true = tm.attr("noTrueChildStrategy", "returnNullPrediction") == "returnLastPrediction";
     if (classify != (tm.attr("functionName") == "classification")) unsupported("TreeModel functionName differs from the ensemble's");
-    if (const XNode* ts = tm.child("Targets")) if (const XNode* t = ts->child("Target")) {
+    if (nested) if (const XNode* ts = tm.child("Targets")) if (const XNode* t = ts->child("Target")) {
       if (classify) unsupported("Targets on a classification tree");
       TargetXform x{1, 0, 0, 0, 0, 0, 0};
       if (t->has("rescaleFactor")) x.factor = need_double(t->attr("rescaleFactor"), "rescaleFactor");
@@ -549,7 +549,7 @@ void finish_target(Builder& b, bool classify) {
 void compile_tree(const XNode& m, Builder& b) {
   b.cm.family = "TreeModel"; b.cm.dev.kind = MK_FOREST;
   bool classify = m.attr("functionName") == "classification";
-  ForestBuilder fb(b, classify); fb.add_tree(m, 1.0); fb.emit(FM_SINGLE);
+  ForestBuilder fb(b, classify); fb.add_tree(m, 1.0, false); fb.emit(FM_SINGLE);
   b.set_labels(fb.labels, false); finish_target(b, classify);
 }
 
@@ -568,7 +568,7 @@ void compile_mining(const XNode& m, Builder& b) {
     if (p.name != "True") unsupported("Segment predicate other than True/False");
     const XNode* tm = s.child("TreeModel");
     if (!tm) unsupported("Segment model other than TreeModel");
-    fb.add_tree(*tm, need_double(s.attr("weight", "1"), "weight"));
+    fb.add_tree(*tm, need_double(s.attr("weight", "1"), "weight"), true);
   });
   if (fb.roots.empty()) unsupported("Segmentation without active segments");
   fb.emit(method); b.set_labels(fb.labels, false); finish_target(b, classify);

@@ -1,0 +1,71 @@
+/* fjpmml_host.h -- C entry points of the host-side mirror of the reference's operators (libfjpmml.so).
+ *
+ * The reference's operators are Scala classes run by Flink; there is no JVM in this image, so their behaviour is
+ * restated in C++ (flink-jpmml_b200/csrc/host/flinkjpmml.hpp) above the scoring ABI (fjpmml.h) and exposed here so
+ * that the reference's operator tests can be replayed from pytest.  A Scala/JNI shim would not bind these: it would
+ * keep its own EvaluationFunction / EvaluationCoFunction and call fjpmml.h.
+ * S/ = flink-jpmml-scala/src/main/scala/io/radicalbit/flink/pmml/scala/
+ */
+#ifndef FJPMML_HOST_H
+#define FJPMML_HOST_H
+
+#include "fjpmml.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* return codes: the two job-fatal exceptions of the reference (S/api/exceptions/package.scala:42-43, 53) */
+#define FJH_OK 0
+#define FJH_ENGINE_ERROR (-1)
+#define FJH_WRONG_MODEL_ID_FORMAT (-2)   /* WrongModelIdFormat  */
+#define FJH_MODEL_LOADING (-3)           /* ModelLoadingException */
+
+typedef struct fjh_eval_function fjh_eval_function;
+typedef struct fjh_cofunction fjh_cofunction;
+
+/* ModelId.fromIdentifier / ModelId.hashCode  (S/models/core/ModelId.scala:36-40, 46). */
+int fjh_model_id_parse(const char* id, char* name_out, size_t name_cap, int64_t* version_out);
+int32_t fjh_model_id_hash(const char* name, int64_t version);
+
+/* PmmlModel.predict for ONE event, synchronously (S/api/PmmlModel.scala:109-119).  indices == NULL: DenseVector of
+ * `size` values; otherwise SparseVector(size, indices[nnz], values[nnz]).  replace_nan: NaN = None. */
+int fjh_predict(fjp_engine* e, fjp_model* m, const double* values, int size, const int* indices, int nnz, double replace_nan,
+                double* score, uint8_t* status);
+
+/* ---- fixed-model operator: stream.evaluate(reader)(f) / quickEvaluate(reader)   (S/package.scala:44-50, 73-80,
+ * S/api/functions/EvaluationFunction.scala:31-42).  open() loads the model: NULL + message = ModelLoadingException
+ * (the job fails, T/RichDataStreamSpec.scala:82-105).  Events are buffered into a pinned micro-batch of `max_batch`
+ * rows; predictions are emitted in arrival order when the batch fills or on flush/close. */
+fjh_eval_function* fjh_eval_function_open(fjp_engine* e, const char* path, int max_batch, char* err, size_t errcap);
+const char* fjh_eval_function_model_name(fjh_eval_function* op);
+int fjh_eval_function_process(fjh_eval_function* op, const double* values, int size, const int* indices, int nnz, double replace_nan);
+int fjh_eval_function_flush(fjh_eval_function* op);
+long fjh_eval_function_poll(fjh_eval_function* op, double* scores, uint8_t* status, long cap);
+void fjh_eval_function_close(fjh_eval_function* op);
+
+/* ---- dynamic operator: events.withSupportStream(ctrl).evaluate(f)   (S/package.scala:57-69,
+ * S/api/functions/EvaluationCoFunction.scala:42-120).
+ * process_event  = processElement1: binds the event to the model its id names at this moment (cache, else metadata
+ *                  -> lazy load, else the empty model), buffers it.  FJH_WRONG_MODEL_ID_FORMAT / FJH_MODEL_LOADING are
+ *                  the job-fatal outcomes (T/api/functions/EvaluationCoFunctionSpec.scala:132-144,
+ *                  T/RichConnectedStreamSpec.scala:288-300).
+ * process_control = processElement2: Del evicts the cached model, then the metadata map is updated
+ *                  (Add on a known id is ignored).
+ * snapshot / restore = snapshotState / initializeState: the metadata map only; models reload lazily. */
+fjh_cofunction* fjh_cofunction_create(fjp_engine* e, int max_batch);
+int fjh_cofunction_process_event(fjh_cofunction* op, const char* model_id, const double* values, int size, const int* indices, int nnz,
+                                 double replace_nan, char* err, size_t errcap);
+int fjh_cofunction_process_control(fjh_cofunction* op, int is_add, const char* name, int64_t version, const char* path, int64_t occurred_on);
+int fjh_cofunction_flush(fjh_cofunction* op, char* err, size_t errcap);
+long fjh_cofunction_poll(fjh_cofunction* op, double* scores, uint8_t* status, long cap);
+long fjh_cofunction_snapshot(fjh_cofunction* op, char* buf, long cap);
+int fjh_cofunction_restore(fjh_cofunction* op, const char* const* snapshots, int n_snapshots);
+int fjh_cofunction_metadata_size(fjh_cofunction* op);
+int fjh_cofunction_cached_models(fjh_cofunction* op);
+void fjh_cofunction_destroy(fjh_cofunction* op);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FJPMML_HOST_H */

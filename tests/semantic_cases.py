@@ -1,0 +1,121 @@
+"""Adversarial small documents with hand-derived answers (PMML 4.3 spec read the way JPMML 1.3.x implements it,
+SURVEY.md Appendix A).  Each case: (name, pmml bytes, X rows, present mask or None, replace or None,
+expected list of (status, score-or-None, aux-or-None))."""
+import numpy as np
+
+from hand_pmml import AB, SMALL_TREE, doc, schema, tree_model
+
+NAN = float("nan")
+
+
+def _rows(*rows):
+    X = np.array([[0.0 if v is None else v for v in r] for r in rows], dtype=np.float64)
+    P = np.array([[v is not None for v in r] for r in rows], dtype=bool)
+    return X, P
+
+
+def cases():
+    out = []
+    X, P = _rows((0, 5), (2, -1), (2, 3), (None, 1), (2, None), (1, 0), (NAN, -1))
+    t = lambda **kw: doc(AB, tree_model(["a", "b"], SMALL_TREE, **kw))
+    #                         a<=1     R,b<0    R,b>=0   a missing          b missing        a==1     NaN is greatest: a>1
+    out.append(("tree/none/null", t(strategy="none"), X, P, None,
+                [(0, 1.5, 2), (0, -2.0, 4), (0, 7.0, 5), (3, None, None), (3, None, None), (0, 1.5, 2), (0, -2.0, 4)]))
+    out.append(("tree/none/last", t(strategy="none", no_true="returnLastPrediction"), X, P, None,
+                [(0, 1.5, 2), (0, -2.0, 4), (0, 7.0, 5), (0, 10.0, 1), (0, 20.0, 3), (0, 1.5, 2), (0, -2.0, 4)]))
+    out.append(("tree/defaultChild", t(strategy="defaultChild"), X, P, None,
+                [(0, 1.5, 2), (0, -2.0, 4), (0, 7.0, 5), (0, 7.0, 5), (0, -2.0, 4), (0, 1.5, 2), (0, -2.0, 4)]))
+    out.append(("tree/lastPrediction", t(strategy="lastPrediction"), X, P, None,
+                [(0, 1.5, 2), (0, -2.0, 4), (0, 7.0, 5), (0, 10.0, 1), (0, 20.0, 3), (0, 1.5, 2), (0, -2.0, 4)]))
+    out.append(("tree/nullPrediction", t(strategy="nullPrediction"), X, P, None,
+                [(0, 1.5, 2), (0, -2.0, 4), (0, 7.0, 5), (3, None, None), (3, None, None), (0, 1.5, 2), (0, -2.0, 4)]))
+    # replaceNan fills the absent slot before preparation (api/PmmlModel.scala:148)
+    out.append(("tree/replaceNan", t(strategy="nullPrediction"), X, P, 0.5,
+                [(0, 1.5, 2), (0, -2.0, 4), (0, 7.0, 5), (0, 1.5, 2), (0, 7.0, 5), (0, 1.5, 2), (0, -2.0, 4)]))
+    # Targets: clamp to [min,max] first, then rescale, then cast
+    tg = '<Targets><Target field="y" min="0" max="5" rescaleFactor="2" rescaleConstant="0.25" castInteger="floor"/></Targets>'
+    out.append(("tree/targets", t(strategy="defaultChild", extra=tg), X, P, None,
+                [(0, 3.0, 2), (0, 0.0, 4), (0, 10.0, 5), (0, 10.0, 5), (0, 0.0, 4), (0, 3.0, 2), (0, 0.0, 4)]))
+    # equality / set membership of missing, isMissing
+    eq = ('<Node id="1"><True/>'
+          '<Node id="2" score="1"><SimplePredicate field="a" operator="isMissing"/></Node>'
+          '<Node id="3" score="2"><SimplePredicate field="a" operator="equal" value="3"/></Node>'
+          '<Node id="4" score="3"><SimplePredicate field="b" operator="notEqual" value="0"/></Node>'
+          '<Node id="5" score="4"><True/></Node></Node>')
+    X2, P2 = _rows((None, 1), (3, 1), (2, 1), (2, 0), (2, None), (-0.0, 0.0), (2, -0.0))
+    #   b == 0 tests use Double.equals: -0.0 != 0.0
+    out.append(("tree/equal-missing", doc(AB, tree_model(["a", "b"], eq)), X2, P2, None,
+                [(0, 1.0, 2), (0, 2.0, 3), (0, 3.0, 4), (0, 4.0, 5), (0, 4.0, 5), (0, 4.0, 5), (0, 3.0, 4)]))
+    # classification tree: labels become doubles only when they parse; integer-typed target never extracts
+    cls = ('<Node id="1"><True/><Node id="2" score="7"><SimplePredicate field="a" operator="lessThan" value="0"/></Node>'
+           '<Node id="3" score="setosa"><True/></Node></Node>')
+    X3, P3 = _rows((-1, 0), (1, 0))
+    tgt = ("y", "categorical", "string", ("7", "setosa"))
+    out.append(("tree/classification-labels", doc(AB, tree_model(["a", "b"], cls, function="classification"), target=tgt), X3, P3, None,
+                [(0, 7.0, 2), (4, None, 3)]))
+    tgt_i = ("y", "categorical", "integer", ("7", "8"))
+    out.append(("tree/integer-target", doc(AB, tree_model(["a", "b"], cls.replace("setosa", "8"), function="classification"), target=tgt_i), X3, P3, None,
+                [(4, None, 2), (4, None, 3)]))
+    out.append(("tree/float-regression-target", doc(AB, tree_model(["a", "b"], SMALL_TREE, strategy="defaultChild"), target=("y", "continuous", "float", ())),
+                X[:3], P[:3], None, [(4, None, 2), (4, None, 4), (4, None, 5)]))
+    # ---- input preparation (JPMML FieldValueUtil.prepareInputValue)
+    iv = '<Interval closure="closedOpen" leftMargin="0" rightMargin="10"/>'
+    fields = [("a", "continuous", "double", iv), ("b", "continuous", "double")]
+    X4, P4 = _rows((5, 1), (10, 1), (-1, 1), (0, 1), (None, 1))
+    mk = lambda attr: doc(fields, tree_model(["a", "b"], SMALL_TREE, strategy="nullPrediction", attrs={"a": attr}))
+    out.append(("prep/returnInvalid", mk(""), X4, P4, None, [(0, 7.0, 5), (2, None, None), (2, None, None), (0, 1.5, 2), (3, None, None)]))
+    out.append(("prep/asIs", mk('invalidValueTreatment="asIs"'), X4, P4, None, [(0, 7.0, 5), (0, 7.0, 5), (0, 1.5, 2), (0, 1.5, 2), (3, None, None)]))
+    out.append(("prep/asMissing+replacement", mk('invalidValueTreatment="asMissing" missingValueReplacement="0.5"'), X4, P4, None,
+                [(0, 7.0, 5), (0, 1.5, 2), (0, 1.5, 2), (0, 1.5, 2), (0, 1.5, 2)]))
+    out.append(("prep/outliers-extreme", doc(AB, tree_model(["a", "b"], SMALL_TREE, strategy="nullPrediction",
+                                                             attrs={"a": 'outliers="asExtremeValues" lowValue="1.5" highValue="3"'})),
+                X4, P4, None, [(0, 7.0, 5), (0, 7.0, 5), (0, 7.0, 5), (0, 7.0, 5), (3, None, None)]))
+    out.append(("prep/outliers-missing", doc(AB, tree_model(["a", "b"], SMALL_TREE, strategy="nullPrediction",
+                                                             attrs={"a": 'outliers="asMissingValues" lowValue="-5" highValue="8"'})),
+                X4, P4, None, [(0, 7.0, 5), (3, None, None), (0, 1.5, 2), (0, 1.5, 2), (3, None, None)]))
+    vals = '<Value value="1"/><Value value="2"/><Value value="9" property="missing"/><Value value="8" property="invalid"/>'
+    fields_i = [("a", "categorical", "integer", vals), ("b", "continuous", "double")]
+    X5, P5 = _rows((1, 1), (2, 1), (3, 1), (9, 1), (8, 1), (1.5, 1))
+    out.append(("prep/integer-values", doc(fields_i, tree_model(["a", "b"], SMALL_TREE, strategy="nullPrediction")), X5, P5, None,
+                [(0, 1.5, 2), (0, 7.0, 5), (2, None, None), (3, None, None), (2, None, None), (2, None, None)]))
+    # ---- ensembles
+    seg = lambda i, w, nodes: f'<Segment id="{i}" weight="{w}"><True/>{tree_model(["a", "b"], nodes, strategy="defaultChild", target=None)}</Segment>'
+    t2 = ('<Node id="1" defaultChild="2"><True/><Node id="2" score="100"><SimplePredicate field="b" operator="lessOrEqual" value="0"/></Node>'
+          '<Node id="3" score="200"><SimplePredicate field="b" operator="greaterThan" value="0"/></Node></Node>')
+    mm = lambda method: doc(AB, f'<MiningModel functionName="regression">{schema(["a", "b"])}<Segmentation multipleModelMethod="{method}">'
+                            f'{seg(1, 1, SMALL_TREE)}{seg(2, 3, t2)}</Segmentation></MiningModel>')
+    X6, P6 = _rows((0, 5), (2, -1), (None, None))
+    out.append(("mining/sum", mm("sum"), X6, P6, None, [(0, 201.5, None), (0, 98.0, None), (0, 98.0, None)]))
+    out.append(("mining/average", mm("average"), X6, P6, None, [(0, 100.75, None), (0, 49.0, None), (0, 49.0, None)]))
+    out.append(("mining/weightedSum", mm("weightedSum"), X6, P6, None, [(0, 601.5, None), (0, 298.0, None), (0, 298.0, None)]))
+    out.append(("mining/weightedAverage", mm("weightedAverage"), X6, P6, None, [(0, 150.375, None), (0, 74.5, None), (0, 74.5, None)]))
+    # majority vote: tie between "1" and "0" -> the label seen first in segment order wins
+    cseg = lambda i, w, lab_l, lab_r: (f'<Segment id="{i}" weight="{w}"><True/>' + tree_model(["a", "b"],
+                                       f'<Node id="1" defaultChild="3"><True/><Node id="2" score="{lab_l}"><SimplePredicate field="a" operator="lessOrEqual" value="0"/></Node>'
+                                       f'<Node id="3" score="{lab_r}"><True/></Node></Node>', function="classification", strategy="defaultChild", target=None) + '</Segment>')
+    vote = lambda method: doc(AB, f'<MiningModel functionName="classification">{schema(["a", "b"])}<Segmentation multipleModelMethod="{method}">'
+                              f'{cseg(1, 1, "1", "0")}{cseg(2, 1, "0", "1")}{cseg(3, 5, "2", "2")}{cseg(4, 1, "2", "0")}</Segmentation></MiningModel>',
+                              target=("y", "categorical", "string", ("0", "1", "2")))
+    X7, P7 = _rows((-1, 0), (1, 0))
+    #  a<=0: votes 1,0,2,2 -> "2"(2 votes).   a>0: votes 0,1,2,0 -> "0"(2 votes)
+    out.append(("mining/majorityVote", vote("majorityVote"), X7, P7, None, [(0, 2.0, None), (0, 0.0, None)]))
+    #  weighted: a<=0: 1:1, 0:1, 2:6 -> "2";  a>0: 0:2, 1:1, 2:5 -> "2"
+    out.append(("mining/weightedMajorityVote", vote("weightedMajorityVote"), X7, P7, None, [(0, 2.0, None), (0, 2.0, None)]))
+    tie = lambda: doc(AB, f'<MiningModel functionName="classification">{schema(["a", "b"])}<Segmentation multipleModelMethod="majorityVote">'
+                      f'{cseg(1, 1, "1", "0")}{cseg(2, 1, "0", "1")}</Segmentation></MiningModel>', target=("y", "categorical", "string", ("0", "1")))
+    out.append(("mining/vote-tie-first-seen", tie(), X7, P7, None, [(0, 1.0, None), (0, 0.0, None)]))
+    # ---- clustering variants: 1-D centres 0 and 10 plus a second field; cluster ids "5" and "x"
+    def clu(measure, compare="absDiff", extra="", ids=("5", "x"), weights=""):
+        body = (f'<ClusteringModel modelName="c" functionName="clustering" modelClass="centerBased" numberOfClusters="2">'
+                f'<MiningSchema><MiningField name="a"/><MiningField name="b"/><MiningField name="y" usageType="predicted"/></MiningSchema>'
+                f'<ComparisonMeasure kind="distance" compareFunction="{compare}"><{measure}/></ComparisonMeasure>'
+                f'<ClusteringField field="a"{weights}/><ClusteringField field="b"/>{extra}'
+                f'<Cluster id="{ids[0]}"><Array n="2" type="real">0 0</Array></Cluster><Cluster id="{ids[1]}"><Array n="2" type="real">10 1</Array></Cluster></ClusteringModel>')
+        return doc(AB, body, target=("y", "categorical", "string", ()))
+    X8, P8 = _rows((1, 0), (9, 0), (5, 0.5), (None, 0.9), (None, None))
+    # ids: first cluster "5" -> 5.0; second "x" does not parse -> status 4; exact tie (5,0.5) -> first cluster
+    out.append(("cluster/squaredEuclidean-ids", clu("squaredEuclidean"), X8, P8, None, [(0, 5.0, 1), (4, None, 2), (0, 5.0, 1), (4, None, 2), (0, 5.0, 1)]))
+    out.append(("cluster/chebychev", clu("chebychev", ids=("1", "2")), X8, P8, None, [(0, 1.0, 1), (0, 2.0, 2), (0, 1.0, 1), (0, 2.0, 2), (0, 1.0, 1)]))
+    out.append(("cluster/cityBlock-weighted", clu("cityBlock", ids=("1", "2"), weights=' fieldWeight="0.01"'), X8, P8, None,
+                [(0, 1.0, 1), (0, 1.0, 1), (0, 1.0, 1), (0, 2.0, 2), (0, 1.0, 1)]))
+    return out

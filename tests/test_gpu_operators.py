@@ -1,0 +1,199 @@
+"""GPU: the reference's operator specs replayed against the batching operators through the C ABI.
+
+  T/RichConnectedStreamSpec.scala:71-335   every lifecycle sequence, (1,1,1,1) <-> Score(3.0) / EmptyScore
+  T/QuickDataStreamSpec.scala:62-105       fixed-model operator, dense + sparse mix keeps order
+  T/RichDataStreamSpec.scala:73-105        bad path / empty PMML fail the job (ModelLoadingException)
+  T/api/functions/EvaluationCoFunctionSpec.scala:122-144
+(T/ = flink-jpmml-scala/src/test/scala/io/radicalbit/flink/pmml/scala/)
+Each sequence runs twice: flushing after every element (the reference's per-event timing) and with one flush at the end
+(everything in one micro-batch) -- the outputs must be identical."""
+import os
+import uuid
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN
+from flink_jpmml_b200 import api
+
+pytestmark = pytest.mark.gpu
+
+KMEANS = os.path.join(GOLDEN, "iris_kmeans43.pmml")
+NO_TARGET = os.path.join(GOLDEN, "iris_kmeans_nooutput_notarget.pmml")
+EMPTY_DOC = os.path.join(GOLDEN, "iris_kmeans_empty.pmml")
+MISSING = "/not/existing/path.pmml"
+N1, N2 = str(uuid.UUID(int=1)), str(uuid.UUID(int=2))
+ID1, ID2 = f"{N1}_1", f"{N2}_1"
+DEFAULT, EMPTY = api.Prediction(api.Score(3.0)), api.Prediction(api.EmptyScore)
+ONES = api.DenseVector([1.0, 1.0, 1.0, 1.0])
+
+
+def ev(mid, vec=ONES):
+    return ("event", mid, vec)
+
+
+def add(name, path=KMEANS):
+    return ("ctrl", api.AddMessage(name, 1, path))
+
+
+def dele(name):
+    return ("ctrl", api.DelMessage(name, 1))
+
+
+SEQUENCES = {
+    "model->event": ([add(N1), ev(ID1)], [DEFAULT]),                                                           # :71-81
+    "event->model->event": ([ev(ID1), add(N1), ev(ID1)], [EMPTY, DEFAULT]),                                      # :83-95
+    "two models, second without target": ([add(N1), add(N2, NO_TARGET), ev(ID1), ev(ID2)], [DEFAULT, EMPTY]),  # :97-116
+    "interleaved": ([ev(ID1), add(N1), ev(ID2), add(N2), ev(ID1), ev(ID2)], [EMPTY, EMPTY, DEFAULT, DEFAULT]),  # :118-139
+    "only events": ([ev(ID1), ev(ID2)], [EMPTY, EMPTY]),                                                        # :141-153
+    "only models": ([add(N1), add(N2, NO_TARGET)], []),                                                         # :155-172
+    "del with no model": ([dele(N1), ev(ID1)], [EMPTY]),                                                        # :174-185
+    "del current model": ([add(N1), ev(ID1), dele(N1), ev(ID1)], [DEFAULT, EMPTY]),                             # :187-204
+    "del other model": ([add(N1), ev(ID1), dele(N2), ev(ID1)], [DEFAULT, DEFAULT]),                             # :206-223
+    "add-del-add": ([add(N1), ev(ID1), dele(N1), ev(ID1), add(N1), ev(ID1)], [DEFAULT, EMPTY, DEFAULT]),        # :225-244
+    "del-add-del": ([dele(N1), ev(ID1), add(N1), ev(ID1), dele(N1), ev(ID1)], [EMPTY, DEFAULT, EMPTY]),         # :246-265
+    "add on same id is discarded": ([add(N1), ev(ID1), add(N1, NO_TARGET), ev(ID1)], [DEFAULT, DEFAULT]),       # :267-286
+    "wrong-size input": ([add(N1), ev(ID1, api.DenseVector([1.0, 1.0]))], [EMPTY]),                             # :302-320
+}
+
+
+@pytest.mark.parametrize("name", list(SEQUENCES))
+@pytest.mark.parametrize("mode", ["flush-each", "one-batch"])
+def test_connected_stream_sequences(engine, name, mode):
+    ops, expected = SEQUENCES[name]
+    op = api.EvaluationCoFunction(engine, max_batch=64)
+    try:
+        for o in ops:
+            if o[0] == "event":
+                op.processElement1(o[1], o[2])
+            else:
+                op.processElement2(o[1])
+            if mode == "flush-each":
+                op.flush()
+        op.flush()
+        assert op.collect() == expected
+    finally:
+        op.close()
+    engine.table_del(N1, 1), engine.table_del(N2, 1)   # operators of later tests start from an empty cache
+
+
+def test_unloadable_model_fails_the_job_on_the_first_event(engine):
+    # :288-300 (missing path) and :322-335 (empty PMML): Add succeeds, the first event for that id is fatal
+    for path in (MISSING, EMPTY_DOC):
+        op = api.EvaluationCoFunction(engine)
+        op.processElement2(api.AddMessage(N1, 1, path))
+        with pytest.raises(api.ModelLoadingException):
+            op.processElement1(ID1, ONES)
+        op.close()
+
+
+def test_from_metadata_edge_cases(engine):
+    # EvaluationCoFunctionSpec.scala:122-144: empty metadata -> empty model; malformed id -> WrongModelIdFormat
+    op = api.EvaluationCoFunction(engine)
+    op.processElement1(ID1, ONES)
+    op.flush()
+    assert op.collect() == [EMPTY]
+    with pytest.raises(api.WrongModelIdFormat):
+        op.processElement1("23441-_1", ONES)
+    op.close()
+
+
+def test_buffered_events_keep_the_model_they_arrived_under(engine):
+    """Control messages act between events even though nothing is flushed: 200 events, Del in the middle."""
+    op = api.EvaluationCoFunction(engine, max_batch=1024)
+    op.processElement2(api.AddMessage(N1, 1, KMEANS))
+    for _ in range(100):
+        op.processElement1(ID1, ONES)
+    op.processElement2(api.DelMessage(N1, 1))
+    for _ in range(100):
+        op.processElement1(ID1, ONES)
+    assert op.servingModels == 0            # evicted at once ...
+    op.flush()
+    out = op.collect()
+    assert out == [DEFAULT] * 100 + [EMPTY] * 100   # ... yet the buffered events still scored against it
+    op.close()
+
+
+def test_checkpoint_restore_reloads_models_lazily(engine):
+    op = api.EvaluationCoFunction(engine)
+    op.processElement2(api.AddMessage(N1, 1, KMEANS))
+    op.processElement1(ID1, ONES)
+    snap = op.snapshotState()               # flushes the pending micro-batch first
+    assert op.collect() == [DEFAULT]
+    op.close()
+    engine.table_del(N1, 1)
+    op2 = api.EvaluationCoFunction(engine)
+    op2.initializeState([snap])
+    assert op2.servingMetadata == 1 and op2.servingModels == 0
+    op2.processElement1(ID1, ONES)
+    op2.flush()
+    assert op2.collect() == [DEFAULT] and op2.servingModels == 1
+    op2.close()
+    engine.table_del(N1, 1)
+
+
+def test_quick_evaluate_keeps_order_on_heterogeneous_input(engine):
+    # QuickDataStreamSpec.scala:62-66: Seq(dense (1,1,1,1), sparse idx 0-3 (1,2,3,4)) -> Seq(3.0, 4.0)
+    fn = api.EvaluationFunction(engine, KMEANS, max_batch=3)
+    assert fn.modelName == "k-means"
+    seq = [ONES, api.SparseVector(4, [0, 1, 2, 3], [1.0, 2.0, 3.0, 4.0]), api.SparseVector(2, [0, 3], [1.0, 1.0]), ONES,
+           api.SparseVector(4, [0, 2], [1.0, 2.0])]
+    for v in seq:
+        fn.processElement(v)
+    fn.flush()
+    assert fn.collect() == [DEFAULT, api.Prediction(api.Score(4.0)), EMPTY, DEFAULT, DEFAULT]
+    fn.close()
+    for bad in (MISSING, EMPTY_DOC):        # RichDataStreamSpec.scala:82-105
+        with pytest.raises(api.ModelLoadingException):
+            api.EvaluationFunction(engine, bad)
+
+
+def test_pmml_model_predict_single_event(engine, golden_vectors):
+    # api/PmmlModelSpec.scala:50-83 through PmmlModel.predict (one event at a time, the literal drop-in)
+    model = api.PmmlModel.fromReader(engine, KMEANS)
+    assert model.predict(ONES) == DEFAULT
+    assert model.predict(api.SparseVector(4, [0, 1, 2, 3], [1.0, 2.0, 3.0, 4.0])) == api.Prediction(api.Score(4.0))
+    assert model.predict(api.SparseVector(4, [0, 2], [1.0, 2.0]), 0.0) == DEFAULT
+    assert model.predict(api.SparseVector(4, [0, 2], [1.0, 2.0])) == DEFAULT
+    assert model.predict(api.DenseVector([1.0, 2.0, 3.0])) == EMPTY
+    assert api.PmmlModel.empty(engine).predict(ONES) == EMPTY
+    with pytest.raises(api.ModelLoadingException):
+        api.PmmlModel.fromReader(engine, MISSING)
+    assert DEFAULT.value.get() == 3.0 and EMPTY.value.getOrElse(-1.0) == -1.0
+    with pytest.raises(LookupError):
+        EMPTY.value.get()                    # TargetSpec.scala:42-44
+
+
+def test_hot_swap_under_load(engine, gen, oracle, tmp_path):
+    """Config C5 in miniature: several ModelIds (RF + MLP), events interleaved with Del / Add(version+1)."""
+    rng = np.random.default_rng(5)
+    files, oracles = {}, {}
+    for k in range(4):
+        pm = gen.rf_pmml(T=20, depth=4, F=16, n_labels=4, seed=100 + k)[0] if k % 2 == 0 else gen.nn_pmml(n_in=16, hidden=(32, 32), n_out=4, seed=100 + k)[0]
+        p = tmp_path / f"m{k}.pmml"
+        p.write_bytes(pm)
+        files[k], oracles[k] = str(p), oracle.OracleModel(pm)
+    names = [str(uuid.UUID(int=100 + k)) for k in range(4)]
+    version = [1] * 4
+    op = api.EvaluationCoFunction(engine, max_batch=256)
+    for k in range(4):
+        op.processElement2(api.AddMessage(names[k], 1, files[k]))
+    expected = []
+    X = rng.standard_normal((3000, 16))
+    for i in range(3000):
+        k = int(rng.integers(4))
+        if i % 97 == 96:                     # hot swap: Del then Add(version + 1)
+            op.processElement2(api.DelMessage(names[k], version[k]))
+            version[k] += 1
+            op.processElement2(api.AddMessage(names[k], version[k], files[k]))
+        stale = rng.random() < 0.05          # an event still addressed to the previous version: EmptyScore
+        v = version[k] - 1 if (stale and version[k] > 1) else version[k]
+        op.processElement1(f"{names[k]}_{v}", api.DenseVector(X[i]))
+        if v == version[k]:
+            r = oracles[k].predict(X[i:i + 1])
+            expected.append(api.Prediction.of(r["score"][0], r["status"][0]))
+        else:
+            expected.append(EMPTY)
+    op.flush()
+    assert op.collect() == expected
+    op.close()
