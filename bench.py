@@ -163,15 +163,11 @@ def main():
     import torch
     from flink_jpmml_b200 import capi
 
-    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        torch.cuda.set_device(local)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from flink_jpmml_b200 import dist as D
+    rank, world, local = D.env_rank()
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    dist = D.init("nccl", dev)   # plumbing only: barrier + max-over-ranks of the timings; no collective while scoring
     L = capi.lib()
     eng = capi.Engine(local)
     pm, arrays = make_model_bytes()
@@ -233,10 +229,7 @@ def main():
     e2e_match = bool(torch.equal(hS[:4096], score[:4096].cpu()))
 
     # ------------------------------------------------------------------ max over ranks
-    t = torch.tensor([ms_dev, t_e2e * 1e3], dtype=torch.float64, device=dev)
-    if dist:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_dev_max, ms_e2e_max = float(t[0]), float(t[1])
+    ms_dev_max, ms_e2e_max = D.max_over_ranks(dist, [ms_dev, t_e2e * 1e3], dev)
 
     # ------------------------------------------------------------------ latency sweep + CPU baseline: rank 0 only
     latency, cpu = None, None
@@ -270,21 +263,21 @@ def main():
 
     if rank == 0:
         pk = peaks()
-        total = n * world * args.steps
-        value = total / (ms_dev_max / 1e3)
+        value = D.whole_job_rate(n, world, args.steps, ms_dev_max)
         per_launch_s = ms_dev_max / 1e3 / args.steps
         achieved = n * ALGO_HBM_BYTES / per_launch_s / 1e9
         micro = pk.get("micro", {})
         gather = n * ALGO_GATHER_BYTES / per_launch_s / 1e9
         roof = {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": achieved / pk["hbm_gbs"],
-                "traffic": micro.get("forest_kernel_dram_bytes_per_launch"), "peak_source": pk["source"],
-                "kernel": "forest_complete_kernel<8,false>", "algorithmic_bytes_per_event": ALGO_HBM_BYTES,
+                "traffic": (micro["forest_kernel_dram_bytes_per_event"] * n) if micro.get("forest_kernel_dram_bytes_per_event") else None,
+                "traffic_source": "ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum per event x events per launch (profiles/ncu_forest_r01.txt)", "peak_source": pk["source"],
+                "kernel": "forest_complete_kernel<8,8,0,false>", "algorithmic_bytes_per_event": ALGO_HBM_BYTES,
                 "note": "the walk is bound by shared-memory gathers / issue, not HBM: see gather",
                 "gather": {"algorithmic_bytes_per_event": ALGO_GATHER_BYTES, "achieved_gbs": gather,
                            "l2_gather_peak_gbs": micro.get("l2_gather_8B_2MB_GBs"), "smem_gather_peak_gbs": micro.get("smem_gather_8B_random_GBs"),
                            "frac_of_l2_gather": (gather / micro["l2_gather_8B_2MB_GBs"]) if micro.get("l2_gather_8B_2MB_GBs") else None,
                            "frac_of_smem_gather": (gather / micro["smem_gather_8B_random_GBs"]) if micro.get("smem_gather_8B_random_GBs") else None}}
-        e2e_value = ne * world * e2e_steps / (ms_e2e_max / 1e3)
+        e2e_value = D.whole_job_rate(ne, world, e2e_steps, ms_e2e_max)
         line = {"metric": "scored events/sec", "value": value, "unit": "events/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_dev_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
                 "data": "synthetic (torch philox on device, seed 20261110+1000*rank)",
