@@ -209,11 +209,18 @@ forest_complete_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a,
     // ---------------- phase A: load, prepare, encode, transpose (32 rows per chunk; lane <-> row when encoding)
     {
       double v[FC_RMAX];
+      uint32_t pw_next[4] = {~0u, ~0u, ~0u, ~0u}, pw_cur[4];   // this lane's row: present words (rows with <= 128 fields)
+      const bool pw_regs = a.present != nullptr && a.present_stride <= 4;
       auto chunk_cnt = [&](int rb) -> int { long left = a.n - (row0 + rb); int rows = left >= 32 ? 32 : (left > 0 ? (int)left : 0); return rows * F; };
       auto load_chunk = [&](int rb) {
         const double* src = a.X + (row0 + rb) * (long)F; const int cnt = chunk_cnt(rb);
 #pragma unroll
         for (int k = 0; k < FC_RMAX; k++) { int i = tid + k * E; if (i < cnt) v[k] = __ldcs(src + i); }
+        if (pw_regs && row0 + rb + lane < a.n) {
+          const uint32_t* pp = a.present + (row0 + rb + lane) * (long)a.present_stride;
+#pragma unroll
+          for (int w = 0; w < 4; w++) if (w < a.present_stride) pw_next[w] = __ldg(pp + w);
+        }
       };
       load_chunk(0);
       for (int rb = 0; rb < E; rb += 32) {
@@ -228,6 +235,8 @@ forest_complete_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a,
           for (int i = tid + FC_RMAX * E; i < cnt; i += E) { int r = (int)__umulhi((uint32_t)i, inv_f); xs[r * S + (i - r * F)] = __ldcs(src + i); }
         }
         __syncthreads();
+#pragma unroll
+        for (int w = 0; w < 4; w++) pw_cur[w] = pw_next[w];
         if (rb + 32 < E) load_chunk(rb + 32);  // in flight while this chunk is encoded
         long row = row0 + rb + lane;
         if (row < a.n) {
@@ -236,7 +245,8 @@ forest_complete_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a,
           uint32_t pw = 0xFFFFFFFFu; int pw_idx = -1;
           for (int f = warp; f < F; f += nwarps) {
             double raw = xs[lane * S + f]; bool present = true;
-            if (a.present) { int wi = f >> 5; if (wi != pw_idx) { pw = a.present[row * (long)a.present_stride + wi]; pw_idx = wi; } present = (pw >> (f & 31)) & 1u; }
+            if (pw_regs) { int wi = f >> 5; uint32_t wv = wi == 0 ? pw_cur[0] : (wi == 1 ? pw_cur[1] : (wi == 2 ? pw_cur[2] : pw_cur[3])); present = (wv >> (f & 31)) & 1u; }
+            else if (a.present) { int wi = f >> 5; if (wi != pw_idx) { pw = a.present[row * (long)a.present_stride + wi]; pw_idx = wi; } present = (pw >> (f & 31)) & 1u; }
             if (!present && has_rep) { raw = rep; present = true; }
             double val; int st;
             if (m.prep_simple) { st = present ? 0 : 1; val = raw; if (fd.enc != ENC_FLOAT && m.prep[f].dtype == DT_FLOAT) val = (double)(float)raw; }
@@ -442,6 +452,90 @@ __global__ void __launch_bounds__(CL_E* CL_G) cluster_kernel(const __grid_consta
     if (fail) write_out(a, row, 0, ST_PREP, -1);
     else write_label(m, a, row, best, best + 1);
     if (a.probs) a.probs[row * (long)a.prob_stride] = bestd;
+  }
+}
+
+// ---- fast centre-based path (squaredEuclidean / euclidean, absDiff, unit weights): config C1 / C2 ----------
+// Register tile: every thread owns ONE event and CK_TC = 8 clusters (8 running sums); a warp = 32 events x 8 clusters.
+// CTA = 16 warps = (16 / groups) event blocks x `groups` cluster groups, persistent over tiles.  Centres sit in shared
+// memory transposed [field][cluster] so the 8 centres a thread needs for one field are 4 broadcast LDS.128; the
+// tile's prepared inputs sit transposed [field][event] (one conflict-free LDS.64 per field).  Per field and thread:
+// 1 + 4 shared loads feed 24 double-precision instructions (sub, mul, add x 8), so the FP64 pipe is the limiter.
+// Sums run over the fields in ClusteringField order in double, unfused: bit-identical to the per-event interpreter.
+constexpr int CK_TC = 8, CK_WARPS = 16;
+struct ClusterPlan { int groups, event_blocks, events, chunk, kp; uint32_t off_x, off_st, off_best, smem_bytes; };
+template <bool HASMISS>
+__global__ void __launch_bounds__(CK_WARPS * 32, 1) cluster_fast_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, const ClusterPlan pl) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  const ClusterDesc& cd = m.cluster; const int nf = cd.nf, K = cd.k, KP = pl.kp, E = pl.events, EP = E + 1;
+  double* cent = reinterpret_cast<double*>(smem);                       // nf x KP   [f][c]
+  double* xs = reinterpret_cast<double*>(smem + pl.off_x);               // chunk x EP
+  uint8_t* sts = smem + pl.off_st;                                       // chunk x (E + 4)
+  double* bestd = reinterpret_cast<double*>(smem + pl.off_best);         // groups x E
+  int* bestc = reinterpret_cast<int*>(bestd + pl.groups * E);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int eb = warp % pl.event_blocks, cg0 = warp / pl.event_blocks;   // event block, first cluster group of this warp
+  const int warps_per_eb = CK_WARPS / pl.event_blocks;
+  const int e = eb * 32 + lane;
+  const double INF = __longlong_as_double(0x7FF0000000000000LL);
+  for (int i = tid; i < nf * KP; i += blockDim.x) { int f = i / KP, c = i - f * KP; cent[i] = c < K ? cd.centers[(size_t)c * nf + f] : 0.0; }
+  const long ntiles = (a.n + E - 1) / E;
+  for (long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const long row0 = tile * E, row = row0 + e;
+    int bc = -1; double bd = 0; bool fail = false;
+    const int passes = (pl.groups + warps_per_eb - 1) / warps_per_eb;   // uniform trip count: every warp joins the barriers
+    for (int pass = 0; pass < passes; pass++) {
+      const int cg = cg0 + pass * warps_per_eb; const bool active = cg < pl.groups;
+      double acc[CK_TC];
+#pragma unroll
+      for (int k = 0; k < CK_TC; k++) acc[k] = 0.0;
+      double nmiss_q = 0, all_q = 0;
+      for (int f0 = 0; f0 < nf; f0 += pl.chunk) {
+        const int nfc = min(pl.chunk, nf - f0);
+        __syncthreads();   // previous chunk fully consumed (and the centres written) before xs is overwritten
+        for (int i = tid; i < E * nfc; i += blockDim.x) {
+          int r = i / nfc, f = i - r * nfc; long rr = row0 + r; double v = 0; int st = 1;
+          if (rr < a.n) { int slot = cd.slot[f0 + f]; st = load_field(m, a, rr, slot, v); }
+          xs[f * EP + r] = v; if (HASMISS) sts[f * (E + 4) + r] = (uint8_t)st;
+        }
+        __syncthreads();
+        const double* cp = cent + (size_t)f0 * KP + (active ? cg : 0) * CK_TC;
+        if (active) for (int f = 0; f < nfc; f++, cp += KP) {
+          double x = xs[f * EP + e];
+          bool present = true;
+          if (HASMISS) { int st = sts[f * (E + 4) + e]; present = st == 0; fail = fail || st == 2; all_q += 1.0; nmiss_q += present ? 1.0 : 0.0; }
+          const double2* c2 = reinterpret_cast<const double2*>(cp);
+#pragma unroll
+          for (int k = 0; k < CK_TC / 2; k++) {
+            double2 z = c2[k];
+            double d0 = fabs(x - z.x), d1 = fabs(x - z.y);
+            double t0 = d0 * d0, t1 = d1 * d1;
+            if (HASMISS) { t0 = present ? t0 : 0.0; t1 = present ? t1 : 0.0; }   // a skipped field adds nothing (sums are >= +0)
+            acc[2 * k] += t0; acc[2 * k + 1] += t1;
+          }
+        }
+      }
+      const double adj = HASMISS ? all_q / nmiss_q : 1.0;
+#pragma unroll
+      for (int k = 0; k < CK_TC; k++) {
+        int c = cg * CK_TC + k;
+        if (active && c < K) {
+          double t = acc[k] * adj, d = cd.measure == CM_EUCLIDEAN ? sqrt(t) : t;
+          if (bc < 0 || java_cmp(d, bd) < 0) { bc = c; bd = d; }
+        }
+      }
+    }
+    bestd[cg0 * E + e] = bc < 0 ? INF : bd; bestc[cg0 * E + e] = bc;
+    __syncthreads();
+    if (cg0 == 0 && row < a.n) {
+      for (int g = 1; g < warps_per_eb; g++) {
+        int c2 = bestc[g * E + e]; if (c2 < 0) continue; double d2 = bestd[g * E + e];
+        int cmp = bc < 0 ? -1 : java_cmp(d2, bd);
+        if (cmp < 0 || (cmp == 0 && c2 < bc)) { bc = c2; bd = d2; }
+      }
+      if (fail) write_out(a, row, 0, ST_PREP, -1); else write_label(m, a, row, bc, bc + 1);
+      if (a.probs) a.probs[row * (long)a.prob_stride] = bd;
+    }
   }
 }
 
@@ -713,7 +807,7 @@ bool plan_forest_complete(const DeviceModel& m, ForestLaunch* out) {
   const size_t blob = (size_t)(2u << fd.depth) * 8;
   const int S = m.F | 1;  // odd row stride (in doubles): conflict-free column reads of the row stage
   const size_t rows = (size_t)32 * S * 8;
-  const int ti = env_int("FJP_FOREST_TI", 8) >= 8 ? 8 : 4;
+  int ti = env_int("FJP_FOREST_TI", 8); ti = ti >= 8 ? 8 : (ti >= 6 ? 6 : 4);
   const int force_e = env_int("FJP_FOREST_E", 0), force_g = env_int("FJP_FOREST_G", 0);
   const int t_round = ((fd.n_trees + ti - 1) / ti) * ti;
   for (int E = 512; E >= 64; E -= 32) {
@@ -722,7 +816,7 @@ bool plan_forest_complete(const DeviceModel& m, ForestLaunch* out) {
     size_t votes = fd.classify ? (size_t)2 * m.n_labels * E * 2 : 0;
     size_t fixed = keys + votes + 64 + E + 256;
     if (fixed + 2 * ti * blob > budget) continue;
-    int G = (int)((budget - fixed) / (2 * blob)); G = (G / ti) * ti; if (G > 16) G = 16 / ti * ti;
+    int G = (int)((budget - fixed) / (2 * blob)); G = (G / ti) * ti; if (G > 16) G = 16 / ti * ti; if (G > 2 * ti) G = 2 * ti;
     if (force_g) G = force_g;
     if (G > t_round) G = t_round;
     if (G < ti || fixed + 2 * (size_t)G * blob > budget) continue;
@@ -756,7 +850,7 @@ cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t 
         int grid = (int)(ntiles < g_num_sms ? ntiles : g_num_sms);
         const bool c = m.forest.classify; const int d = m.forest.depth;
 #define FJP_FC2(DD, TT, MM) (a.node_ids ? launch_fc<DD, 4, MM, true>(m, a, fl, grid, fl.events_per_cta, s) : launch_fc<DD, TT, MM, false>(m, a, fl, grid, fl.events_per_cta, s))
-#define FJP_FC1(DD, MM) (fl.trees_interleaved >= 8 ? FJP_FC2(DD, 8, MM) : FJP_FC2(DD, 4, MM))
+#define FJP_FC1(DD, MM) (fl.trees_interleaved >= 8 ? FJP_FC2(DD, 8, MM) : (fl.trees_interleaved >= 6 ? FJP_FC2(DD, 6, MM) : FJP_FC2(DD, 4, MM)))
 #define FJP_FC(DD) (c ? FJP_FC1(DD, 2) : ((m.forest.method == FM_WSUM || m.forest.method == FM_WAVERAGE) ? FJP_FC1(DD, 1) : FJP_FC1(DD, 0)))
         if (d == 8) return FJP_FC(8);
         if (d == 6) return FJP_FC(6);
@@ -771,6 +865,28 @@ cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t 
     }
     case MK_CLUSTERING: {
       const int nf = m.cluster.nf;
+      if (m.cluster.fast && (m.cluster.measure == CM_SQEUCLIDEAN || m.cluster.measure == CM_EUCLIDEAN)) {
+        ClusterPlan pl{}; pl.kp = ((m.cluster.k + CK_TC - 1) / CK_TC) * CK_TC; pl.groups = pl.kp / CK_TC;
+        pl.event_blocks = pl.groups >= CK_WARPS ? 1 : CK_WARPS / pl.groups;
+        while (CK_WARPS % pl.event_blocks) pl.event_blocks--;
+        pl.events = 32 * pl.event_blocks;
+        size_t cent = ((size_t)nf * pl.kp * 8 + 127) & ~size_t(127);
+        size_t room = (size_t)g_smem_optin - 2048 - cent - (size_t)(CK_WARPS / pl.event_blocks) * pl.events * 12;
+        if (cent + 16384 < (size_t)g_smem_optin) {
+          int chunk = (int)(room / ((size_t)(pl.events + 1) * 8 + pl.events + 4)); if (chunk > nf) chunk = nf; if (chunk > 128) chunk = 128;
+          if (chunk >= 1) {
+            pl.chunk = chunk; size_t off = cent; pl.off_x = (uint32_t)off; off += (size_t)chunk * (pl.events + 1) * 8;
+            pl.off_st = (uint32_t)off; off += (size_t)chunk * (pl.events + 4); off = (off + 15) & ~size_t(15);
+            pl.off_best = (uint32_t)off; off += (size_t)(CK_WARPS / pl.event_blocks) * pl.events * 12;
+            pl.smem_bytes = (uint32_t)((off + 127) & ~size_t(127));
+            long ntiles = (a.n + pl.events - 1) / pl.events; int grid = (int)(ntiles < g_num_sms ? ntiles : g_num_sms);
+            const bool hasmiss = a.present != nullptr || a.replace != nullptr || !m.prep_simple;
+            if (hasmiss) { cudaFuncSetAttribute(cluster_fast_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes); cluster_fast_kernel<true><<<grid, CK_WARPS * 32, pl.smem_bytes, s>>>(m, a, pl); }
+            else { cudaFuncSetAttribute(cluster_fast_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes); cluster_fast_kernel<false><<<grid, CK_WARPS * 32, pl.smem_bytes, s>>>(m, a, pl); }
+            return cudaGetLastError();
+          }
+        }
+      }
       size_t sm = (size_t)nf * CL_XS * 8 + (((size_t)nf * CL_SS + 15) & ~size_t(15)) + CL_G * CL_E * 12;
       if (sm > (size_t)g_smem_optin) return cudaErrorInvalidValue;
       unsigned grid = (unsigned)((a.n + CL_E - 1) / CL_E);
