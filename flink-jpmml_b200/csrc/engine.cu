@@ -63,6 +63,7 @@ static void make_describe(fjp_model* m) {
            " smem=" + std::to_string(fl.smem_bytes);
   } else if (d.kind == MK_CLUSTERING) s += " k=" + std::to_string(d.cluster.k) + " fields=" + std::to_string(d.cluster.nf) + " fast=" + std::to_string(d.cluster.fast);
   else if (d.kind == MK_REGRESSION) s += " tables=" + std::to_string(d.reg.n_tables) + " dense=" + std::to_string(d.reg.dense) + " norm=" + std::to_string(d.reg.norm);
+  else if (d.kind == MK_GENERAL_REGRESSION) s += " params=" + std::to_string(d.greg.n_params) + " rows=" + std::to_string(d.greg.n_rows) + " type=" + std::to_string(d.greg.model_type) + " link=" + std::to_string(d.greg.link);
   else if (d.kind == MK_NEURAL) s += " inputs=" + std::to_string(d.nn.n_inputs) + " layers=" + std::to_string(d.nn.n_layers) + " max_width=" + std::to_string(d.nn.max_width);
   s += " F=" + std::to_string(d.F) + " prep_simple=" + std::to_string(d.prep_simple) + " blob_bytes=" + std::to_string(m->cm.blob.size());
   m->describe = s;

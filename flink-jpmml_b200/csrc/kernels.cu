@@ -9,6 +9,7 @@
 // comparisons in java.lang.Double.compareTo's total order where JPMML compares through Comparable.
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cstdint>
 #include <cstdlib>
 
@@ -493,10 +494,12 @@ __global__ void __launch_bounds__(CK_WARPS * 32, 1) cluster_fast_kernel(const __
       for (int f0 = 0; f0 < nf; f0 += pl.chunk) {
         const int nfc = min(pl.chunk, nf - f0);
         __syncthreads();   // previous chunk fully consumed (and the centres written) before xs is overwritten
+        const int sh = 31 - __clz(nfc); const bool pow2 = (nfc & (nfc - 1)) == 0;
         for (int i = tid; i < E * nfc; i += blockDim.x) {
-          int r = i / nfc, f = i - r * nfc; long rr = row0 + r; double v = 0; int st = 1;
-          if (rr < a.n) { int slot = cd.slot[f0 + f]; st = load_field(m, a, rr, slot, v); }
-          xs[f * EP + r] = v; if (HASMISS) sts[f * (E + 4) + r] = (uint8_t)st;
+          int r = pow2 ? (i >> sh) : (i / nfc), f = i - r * nfc; long rr = row0 + r; double v = 0; int st = 1;
+          if (HASMISS) { if (rr < a.n) st = load_field(m, a, rr, cd.slot[f0 + f], v); sts[f * (E + 4) + r] = (uint8_t)st; }
+          else if (rr < a.n) v = __ldcs(a.X + rr * (long)m.F + cd.slot[f0 + f]);   // plain doubles, all present
+          xs[f * EP + r] = v;
         }
         __syncthreads();
         const double* cp = cent + (size_t)f0 * KP + (active ? cg : 0) * CK_TC;
@@ -598,72 +601,123 @@ __global__ void __launch_bounds__(128) regression_kernel(const __grid_constant__
   if (a.probs) for (int i = 0; i < C && i < a.prob_stride; i++) a.probs[row * (long)a.prob_stride + i] = y[i];
 }
 
-// Dense: every table uses all F fields in slot order (multinomial logistic, config C3).  A CTA takes RD_E events; the
-// input tile streams through shared memory in chunks of RD_FC features (read coalesced from HBM, stored transposed);
-// each thread owns one event and keeps the C running sums in registers; coefficients are warp-broadcast loads (L1).
-constexpr int RD_E = 128, RD_FC = 32, RD_MAXC = 32;
-__global__ void __launch_bounds__(RD_E) regression_dense_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a) {
-  __shared__ double xs[RD_FC][RD_E + 1];
-  __shared__ uint8_t sts[RD_FC][RD_E];
-  const RegressionDesc& rd = m.reg; const int F = m.F, C = rd.n_tables, tid = threadIdx.x;
-  const long row0 = blockIdx.x * (long)RD_E, row = row0 + tid;
-  double y[RD_MAXC];
+// ---- dense tables, register-tiled (multinomial logistic, config C3) -------------------------------------------
+// Same tiling as cluster_fast_kernel: a thread owns one event and 8 tables; a warp = 32 events x 8 tables; the CTA's
+// warps = event blocks x table groups.  Inputs and the transposed coefficient block [field][table] stream through
+// shared memory in chunks of fields; y[c] accumulates in double, unfused, in field order (= NumericPredictor order).
+struct DensePlan { int groups, event_blocks, events, chunk, kp, warps; uint32_t off_x, off_st, off_y, off_flags, smem_bytes; };
+template <bool HASMISS>
+__global__ void __launch_bounds__(256, 3) regression_tile_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, const DensePlan pl) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  const RegressionDesc& rd = m.reg; const int F = m.F, C = rd.n_tables, KP = pl.kp, E = pl.events, EP = E + 1;
+  double* wt = reinterpret_cast<double*>(smem);                          // chunk x KP  [f][c]
+  double* xs = reinterpret_cast<double*>(smem + pl.off_x);               // chunk x EP
+  uint8_t* sts = smem + pl.off_st;                                       // chunk x (E + 4)
+  double* ys = reinterpret_cast<double*>(smem + pl.off_y);               // KP x EP
+  int* eflags = reinterpret_cast<int*>(smem + pl.off_flags);             // E: bit0 preparation failure, bit1 missing predictor
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int eb = warp % pl.event_blocks, cg = warp / pl.event_blocks, e = eb * 32 + lane;
+  if (tid < E) eflags[tid] = 0;
+  const long ntiles = (a.n + E - 1) / E;
+  for (long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const long row0 = tile * E, row = row0 + e;
+    double acc[CK_TC]; int flags = 0;  // bit0 preparation failure, bit1 missing predictor
 #pragma unroll
-  for (int c = 0; c < RD_MAXC; c++) y[c] = c < C ? rd.intercept[c] : 0.0;
-  bool fail = false, null_result = false;
-  for (int f0 = 0; f0 < F; f0 += RD_FC) {
-    const int nfc = min(RD_FC, F - f0);
-    for (int i = tid; i < RD_E * RD_FC; i += RD_E) {
-      int r = i / RD_FC, f = i - r * RD_FC; long rr = row0 + r;
-      double v = 0; int st = 1;
-      if (rr < a.n && f < nfc) st = load_field(m, a, rr, f0 + f, v);
-      xs[f][r] = v; sts[f][r] = (uint8_t)st;
-    }
-    __syncthreads();
-    for (int f = 0; f < nfc; f++) {
-      int st = sts[f][tid]; double x = xs[f][tid];
-      if (st == 2) fail = true; else if (st == 1) null_result = true;
-      const double* w = rd.dense_w + (f0 + f);
+    for (int k = 0; k < CK_TC; k++) { int c = cg * CK_TC + k; acc[k] = c < C ? rd.intercept[c] : 0.0; }
+    for (int f0 = 0; f0 < F; f0 += pl.chunk) {
+      const int nfc = min(pl.chunk, F - f0);
+      __syncthreads();
+      for (int i = tid; i < nfc * KP; i += blockDim.x) wt[i] = rd.dense_wt[(size_t)f0 * KP + i];
+      const int sh = 31 - __clz(nfc); const bool pow2 = (nfc & (nfc - 1)) == 0;
+      for (int i = tid; i < E * nfc; i += blockDim.x) {
+        int r = pow2 ? (i >> sh) : (i / nfc), f = i - r * nfc; long rr = row0 + r; double v = 0; int st = 0;
+        if (HASMISS) { if (rr < a.n) st = load_field(m, a, rr, f0 + f, v); sts[f * (E + 4) + r] = (uint8_t)st; }
+        else if (rr < a.n) v = __ldcs(a.X + rr * (long)F + f0 + f);   // plain doubles, all present
+        xs[f * EP + r] = v;
+      }
+      __syncthreads();
+      const double* wp = wt + cg * CK_TC;
+      for (int f = 0; f < nfc; f++, wp += KP) {
+        double x = xs[f * EP + e];
+        if (HASMISS) { int st = sts[f * (E + 4) + e]; flags |= st == 2 ? 1 : (st == 1 ? 2 : 0); }
+        const double2* w2 = reinterpret_cast<const double2*>(wp);
 #pragma unroll
-      for (int c = 0; c < RD_MAXC; c++) if (c < C) y[c] += __ldg(w + (size_t)c * F) * x;
+        for (int k = 0; k < CK_TC / 2; k++) { double2 w = w2[k]; acc[2 * k] += w.x * x; acc[2 * k + 1] += w.y * x; }
+      }
     }
+#pragma unroll
+    for (int k = 0; k < CK_TC; k++) ys[(cg * CK_TC + k) * EP + e] = acc[k];
+    if (HASMISS) { if (flags) atomicOr(eflags + e, flags); }
     __syncthreads();
+    if (cg == 0 && row < a.n) {
+      int fl = HASMISS ? eflags[e] : 0;
+      if (fl & 1) write_out(a, row, 0, ST_PREP, -1);
+      else if (fl & 2) write_out(a, row, 0, m.target_status ? m.target_status : ST_EVAL, -1);
+      else if (!rd.classify) write_out(a, row, apply_target(m.tx, link_fn(rd.norm, ys[e])), m.target_status, -1);
+      else {
+        normalize_classes(rd.norm, C, [&](int i) { return ys[i * EP + e]; }, [&](int i, double v) { ys[i * EP + e] = v; });
+        int best = 0; double bp = ys[e];
+        for (int i = 1; i < C; i++) { double p = ys[i * EP + e]; if (java_cmp(p, bp) > 0) { best = i; bp = p; } }
+        write_label(m, a, row, best, best);
+        if (a.probs) for (int i = 0; i < C && i < a.prob_stride; i++) a.probs[row * (long)a.prob_stride + i] = ys[i * EP + e];
+      }
+    }
+    if (HASMISS) { __syncthreads(); if (tid < E) eflags[tid] = 0; }
   }
+}
+
+// ================================================================================================ general regression (J5)
+// Thread per event: design vector from the PPMatrix (factor indicators, covariate powers, products), one dot product
+// per ParamMatrix row in PCell order, link / multinomial softmax, first maximal category.
+__device__ __forceinline__ double inv_link(int link, double p, double eta) {
+  switch (link) {
+    case GL_IDENTITY: return eta;
+    case GL_LOG: return exp(eta);
+    case GL_LOGIT: return 1.0 / (1.0 + exp(-eta));
+    case GL_PROBIT: return 0.5 * erfc(-eta / sqrt(2.0));
+    case GL_CLOGLOG: return 1.0 - exp(-exp(eta));
+    case GL_LOGLOG: return exp(-exp(-eta));
+    case GL_LOGC: return 1.0 - exp(eta);
+    case GL_CAUCHIT: return 0.5 + atan(eta) / 3.14159265358979323846;
+    case GL_POWER: return p == 0.0 ? exp(eta) : pow(eta, 1.0 / p);
+    default: return 1.0 / (p * (exp(-eta) - 1.0));  // negbin
+  }
+}
+__global__ void __launch_bounds__(128) general_regression_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a) {
+  const GeneralRegDesc& gd = m.greg;
+  long row = blockIdx.x * (long)blockDim.x + threadIdx.x;
   if (row >= a.n) return;
+  double x[GR_MAX_PARAMS]; bool fail = false, null_result = false;
+  for (int p = 0; p < gd.n_params; p++) {
+    double v = 1.0;
+    for (int i = gd.cell_off[p]; i < gd.cell_off[p + 1]; i++) {
+      GCell c = gd.cells[i]; double f; int st = c.slot < 0 ? 1 : load_field(m, a, row, c.slot, f);
+      if (st == 2) fail = true; else if (st == 1) null_result = true;
+      else v *= c.is_factor ? (java_eq(f, c.value) ? 1.0 : 0.0) : (c.value == 1.0 ? f : pow(f, c.value));
+    }
+    x[p] = v;
+  }
   if (fail) { write_out(a, row, 0, ST_PREP, -1); return; }
   if (null_result) { write_out(a, row, 0, m.target_status ? m.target_status : ST_EVAL, -1); return; }
-  if (!rd.classify) { write_out(a, row, apply_target(m.tx, link_fn(rd.norm, y[0])), m.target_status, -1); return; }
-  double p[RD_MAXC];
-#pragma unroll
-  for (int c = 0; c < RD_MAXC; c++) p[c] = y[c];
-  // same arithmetic as normalize_classes, on registers
-  if (rd.norm == NORM_SOFTMAX) {
+  auto dot = [&](int r) { double s = 0; for (int i = gd.beta_off[r]; i < gd.beta_off[r + 1]; i++) s += gd.beta[i] * x[gd.beta_param[i]]; return s; };
+  if (!gd.classify) {
+    double eta = dot(0) + gd.offset;
+    double v = gd.model_type == GR_GENERAL_LINEAR ? inv_link(gd.link, gd.link_param, eta) : eta;
+    write_out(a, row, apply_target(m.tx, v), m.target_status, -1);
+    return;
+  }
+  double p[GR_MAX_CATS]; const int C = gd.n_cats;
+  if (gd.model_type == GR_MULTINOMIAL) {
     double s = 0;
-#pragma unroll
-    for (int c = 0; c < RD_MAXC; c++) if (c < C) { p[c] = exp(y[c]); s += p[c]; }
-#pragma unroll
-    for (int c = 0; c < RD_MAXC; c++) if (c < C) p[c] = p[c] / s;
-  } else if (rd.norm == NORM_SIMPLEMAX) {
-    double s = 0;
-#pragma unroll
-    for (int c = 0; c < RD_MAXC; c++) if (c < C) s += y[c];
-#pragma unroll
-    for (int c = 0; c < RD_MAXC; c++) if (c < C) p[c] = y[c] / s;
+    for (int c = 0; c < C; c++) { double eta = 0; for (int r = 0; r < gd.n_rows; r++) if (gd.row_cat[r] == c) eta = dot(r); p[c] = exp(eta); s += p[c]; }
+    for (int c = 0; c < C; c++) p[c] /= s;
   } else {
-    double s = 0;
-#pragma unroll
-    for (int c = 0; c < RD_MAXC; c++) if (c + 1 < C) { p[c] = rd.norm == NORM_NONE ? y[c] : link_fn(rd.norm, y[c]); s += p[c]; }
-#pragma unroll
-    for (int c = 0; c < RD_MAXC; c++) if (c == C - 1) p[c] = 1.0 - s;
+    double q = inv_link(gd.link, gd.link_param, dot(0) + gd.offset);
+    for (int c = 0; c < C; c++) p[c] = c == gd.row_cat[0] ? q : (C == 2 ? 1.0 - q : 0.0);
   }
-  int best = 0; double bp = p[0];
-#pragma unroll
-  for (int c = 1; c < RD_MAXC; c++) if (c < C && java_cmp(p[c], bp) > 0) { best = c; bp = p[c]; }
+  int best = 0; for (int c = 1; c < C; c++) if (java_cmp(p[c], p[best]) > 0) best = c;
   write_label(m, a, row, best, best);
-  if (a.probs) {
-#pragma unroll
-    for (int c = 0; c < RD_MAXC; c++) if (c < C && c < a.prob_stride) a.probs[row * (long)a.prob_stride + c] = p[c];
-  }
+  if (a.probs) for (int c = 0; c < C && c < a.prob_stride; c++) a.probs[row * (long)a.prob_stride + c] = p[c];
 }
 
 // ================================================================================================ neural network (J6)
@@ -775,6 +829,135 @@ __global__ void __launch_bounds__(NN_E* NN_WARPS) neural_kernel(const __grid_con
   write_label(m, a, row, best, best);
 }
 
+// ---- layer-wise register-tiled MLP with streamed weights (config C5-MLP) -------------------------------------------
+// CTA = 8 warps x 32 events (lane <-> event).  Activations ping-pong in shared memory, transposed [neuron][event].
+// The transposed weight matrix of every layer streams L2 -> shared memory in row chunks through a 2-slot ring of
+// bulk async copies (cp.async.bulk + mbarrier), the same producer scheme as the forest kernel.  A warp owns up to
+// 4 groups of 8 output neurons (32 running sums in registers); per input neuron it does one conflict-free LDS.64 of the
+// activation and 4 broadcast LDS.128 per group, feeding 16 double-precision instructions per group.
+// z accumulates from the bias in connection order, unfused, in double (JPMML NeuralNetworkEvaluator order).
+constexpr int NT_E = 32, NT_WARPS = 8, NT_G = 4, NT_RING = 32 * 1024;
+struct NeuralPlan { uint32_t off_act1, off_ring, off_bars, off_flags, smem_bytes; int width; };
+__global__ void __launch_bounds__(NT_E* NT_WARPS, 1) neural_tile_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, const NeuralPlan pl) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  const NeuralDesc& nd = m.nn;
+  double* act0 = reinterpret_cast<double*>(smem); double* act1 = reinterpret_cast<double*>(smem + pl.off_act1);
+  double* ring = reinterpret_cast<double*>(smem + pl.off_ring);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + pl.off_bars);
+  int* flags = reinterpret_cast<int*>(smem + pl.off_flags);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+  __syncthreads();
+  uint32_t q_issue = 0, q_wait = 0; int il = 0, ic = 0;   // producer cursor (thread 0): layer, first row of the next chunk
+  auto rows_per_chunk = [&](const NeuralLayer& L) { int r = NT_RING / (L.n_out_pad * 8); return r < 1 ? 1 : (r > L.n_in ? L.n_in : r); };
+  auto issue_next = [&]() {   // thread 0: next chunk of the per-tile sequence into ring slot q_issue & 1; false at the end
+    if (il >= nd.n_layers) return false;
+    const NeuralLayer& L = nd.layers[il]; int rpc = rows_per_chunk(L); int rows = min(rpc, L.n_in - ic);
+    uint32_t bytes = (uint32_t)rows * L.n_out_pad * 8u, slot = q_issue & 1u;
+    mbar_expect_tx(&bars[slot], bytes);
+    bulk_g2s(ring + (size_t)slot * (NT_RING / 8), nd.weights_t + L.wt_off + (size_t)ic * L.n_out_pad, bytes, &bars[slot]);
+    q_issue++; ic += rows; if (ic >= L.n_in) { ic = 0; il++; }
+    return true;
+  };
+  const long ntiles = (a.n + NT_E - 1) / NT_E;
+  for (long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const long row = tile * NT_E + lane;
+    if (tid == 0) { il = 0; ic = 0; fence_proxy_async(); issue_next(); issue_next(); }
+    if (warp == 0) flags[lane] = 0;
+    __syncthreads();
+    for (int i = warp; i < nd.n_inputs; i += NT_WARPS) {
+      NeuralInput in = nd.inputs[i]; double out = 0; int fl = 0;
+      if (row < a.n) {
+        if (in.kind == NI_CONSTANT) out = in.value;
+        else {
+          double v; int st = in.slot < 0 ? 1 : load_field(m, a, row, in.slot, v);
+          if (st == 2) fl = 1;
+          else if (st == 1) { if (in.has_map_missing) out = in.map_missing; else fl = 2; }
+          else if (in.kind == NI_FIELDREF) out = v;
+          else if (in.kind == NI_NORMDISC) out = java_eq(v, in.value) ? 1.0 : 0.0;
+          else { bool miss = false; out = norm_cont(nd.pts + 2 * in.pts_off, in.n_pts, in.outliers, v, miss); if (miss) fl = 2; }
+        }
+      }
+      act0[i * NT_E + lane] = out;
+      if (fl) atomicOr(&flags[lane], fl);
+    }
+    __syncthreads();
+    double* cur = act0; double* nxt = act1;
+    for (int l = 0; l < nd.n_layers; l++) {
+      const NeuralLayer L = nd.layers[l]; const double* B = nd.biases + L.b_off;
+      const int groups = L.n_out_pad / 8, rpc = rows_per_chunk(L);
+      double z[NT_G][8];
+#pragma unroll
+      for (int g = 0; g < NT_G; g++) {
+        int jg = warp + g * NT_WARPS;
+#pragma unroll
+        for (int k = 0; k < 8; k++) { int j = jg * 8 + k; z[g][k] = (jg < groups && j < L.n_out) ? B[j] : 0.0; }
+      }
+      for (int i0 = 0; i0 < L.n_in; i0 += rpc) {
+        const int rows = min(rpc, L.n_in - i0);
+        uint32_t slot = q_wait & 1u; mbar_wait(&bars[slot], (q_wait >> 1) & 1u); q_wait++;
+        const double* wbase = ring + (size_t)slot * (NT_RING / 8);
+        for (int r = 0; r < rows; r++) {
+          const double x = cur[(i0 + r) * NT_E + lane];
+          const double2* w2 = reinterpret_cast<const double2*>(wbase + (size_t)r * L.n_out_pad);
+#pragma unroll
+          for (int g = 0; g < NT_G; g++) {
+            int jg = warp + g * NT_WARPS;
+            if (jg < groups) {
+#pragma unroll
+              for (int k = 0; k < 4; k++) { double2 w = w2[jg * 4 + k]; z[g][2 * k] += w.x * x; z[g][2 * k + 1] += w.y * x; }
+            }
+          }
+        }
+        __syncthreads();   // ring slot consumed
+        if (tid == 0) { fence_proxy_async(); issue_next(); }
+      }
+#pragma unroll
+      for (int g = 0; g < NT_G; g++) {
+        int jg = warp + g * NT_WARPS;
+#pragma unroll
+        for (int k = 0; k < 8; k++) { int j = jg * 8 + k; if (jg < groups && j < L.n_out) nxt[j * NT_E + lane] = activate(L.act, z[g][k], L.threshold); }
+      }
+      __syncthreads();
+      if (L.norm != NORM_NONE && warp == 0) {
+        if (L.norm == NORM_SOFTMAX) {
+          double s = 0; for (int j = 0; j < L.n_out; j++) { double ex = exp(nxt[j * NT_E + lane]); nxt[j * NT_E + lane] = ex; s += ex; }
+          for (int j = 0; j < L.n_out; j++) nxt[j * NT_E + lane] /= s;
+        } else {
+          double s = 0; for (int j = 0; j < L.n_out; j++) s += nxt[j * NT_E + lane];
+          for (int j = 0; j < L.n_out; j++) nxt[j * NT_E + lane] /= s;
+        }
+      }
+      __syncthreads();
+      double* t = cur; cur = nxt; nxt = t;
+    }
+    if (warp == 0 && row < a.n) {
+      int fl = flags[lane];
+      if (fl & 1) write_out(a, row, 0, ST_PREP, -1);
+      else if (fl & 2) write_out(a, row, 0, m.target_status ? m.target_status : ST_EVAL, -1);
+      else if (!nd.classify) {
+        double y = cur[nd.out_neuron[0] * NT_E + lane];
+        if (nd.out_denorm_n) {
+          const double* pts = nd.pts + 2 * nd.out_denorm_off; int n = nd.out_denorm_n, i = 0;
+          while (i + 2 < n && y > pts[2 * (i + 1) + 1]) i++;
+          double a0 = pts[2 * i], b0 = pts[2 * i + 1], a1 = pts[2 * i + 2], b1 = pts[2 * i + 3];
+          y = (y - b0) / (b1 - b0) * (a1 - a0) + a0;
+        }
+        write_out(a, row, apply_target(m.tx, y), m.target_status, -1);
+      } else {
+        int best = -1; double bp = 0;
+        for (int o = 0; o < nd.n_outputs; o++) {
+          double p = cur[nd.out_neuron[o] * NT_E + lane];
+          if (a.probs && o < a.prob_stride) a.probs[row * (long)a.prob_stride + o] = p;
+          if (best < 0 || java_cmp(p, bp) > 0) { best = o; bp = p; }
+        }
+        write_label(m, a, row, best, best);
+      }
+    }
+    __syncthreads();   // activations / flags are reused by the next tile
+  }
+}
+
 // ================================================================================================ launchers
 static int g_smem_optin = 0, g_num_sms = 0;
 static void query_device() {
@@ -880,7 +1063,7 @@ cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t 
             pl.off_best = (uint32_t)off; off += (size_t)(CK_WARPS / pl.event_blocks) * pl.events * 12;
             pl.smem_bytes = (uint32_t)((off + 127) & ~size_t(127));
             long ntiles = (a.n + pl.events - 1) / pl.events; int grid = (int)(ntiles < g_num_sms ? ntiles : g_num_sms);
-            const bool hasmiss = a.present != nullptr || a.replace != nullptr || !m.prep_simple;
+            const bool hasmiss = a.present != nullptr || a.replace != nullptr || !m.prep_identity;
             if (hasmiss) { cudaFuncSetAttribute(cluster_fast_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes); cluster_fast_kernel<true><<<grid, CK_WARPS * 32, pl.smem_bytes, s>>>(m, a, pl); }
             else { cudaFuncSetAttribute(cluster_fast_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes); cluster_fast_kernel<false><<<grid, CK_WARPS * 32, pl.smem_bytes, s>>>(m, a, pl); }
             return cudaGetLastError();
@@ -901,11 +1084,46 @@ cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t 
     }
     case MK_REGRESSION: {
       if (m.reg.n_tables > REG_MAXC) return cudaErrorInvalidValue;
-      if (m.reg.dense && m.reg.n_tables <= RD_MAXC) regression_dense_kernel<<<(unsigned)((a.n + RD_E - 1) / RD_E), RD_E, 0, s>>>(m, a);
-      else regression_kernel<<<(unsigned)((a.n + 127) / 128), 128, 0, s>>>(m, a);
+      if (m.reg.dense) {
+        DensePlan pl{}; pl.kp = ((m.reg.n_tables + CK_TC - 1) / CK_TC) * CK_TC; pl.groups = pl.kp / CK_TC;   // <= 8 groups (64 tables)
+        pl.event_blocks = pl.groups >= 8 ? 1 : 8 / pl.groups; pl.warps = pl.event_blocks * pl.groups; pl.events = 32 * pl.event_blocks;
+        const int EP = pl.events + 1;
+        int chunk = 64; while (chunk > m.F && chunk > 1) chunk /= 2;   // power of two: cheap row/column split
+        for (;; chunk /= 2) {
+          size_t off = ((size_t)chunk * pl.kp * 8 + 127) & ~size_t(127); pl.off_x = (uint32_t)off; off += (size_t)chunk * EP * 8;
+          pl.off_st = (uint32_t)off; off += (size_t)chunk * (pl.events + 4); off = (off + 15) & ~size_t(15);
+          pl.off_y = (uint32_t)off; off += (size_t)pl.kp * EP * 8; pl.off_flags = (uint32_t)off; off += (size_t)pl.events * 4; pl.smem_bytes = (uint32_t)((off + 127) & ~size_t(127));
+          if (pl.smem_bytes <= 72 * 1024u || chunk == 1) break;   // three CTAs per SM: one loads while the others compute
+        }
+        pl.chunk = chunk;
+        long ntiles = (a.n + pl.events - 1) / pl.events; int grid = (int)(ntiles < 3L * g_num_sms ? ntiles : 3L * g_num_sms);
+        const bool hasmiss = a.present != nullptr || a.replace != nullptr || !m.prep_identity;
+        if (hasmiss) { cudaFuncSetAttribute(regression_tile_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes); regression_tile_kernel<true><<<grid, pl.warps * 32, pl.smem_bytes, s>>>(m, a, pl); }
+        else { cudaFuncSetAttribute(regression_tile_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes); regression_tile_kernel<false><<<grid, pl.warps * 32, pl.smem_bytes, s>>>(m, a, pl); }
+        return cudaGetLastError();
+      }
+      regression_kernel<<<(unsigned)((a.n + 127) / 128), 128, 0, s>>>(m, a);
+      return cudaGetLastError();
+    }
+    case MK_GENERAL_REGRESSION: {
+      general_regression_kernel<<<(unsigned)((a.n + 127) / 128), 128, 0, s>>>(m, a);
       return cudaGetLastError();
     }
     case MK_NEURAL: {
+      bool tiled = true;   // the streamed path keeps <= 4 groups of 8 outputs per warp: layers up to 256 neurons
+      for (int l = 0; l < m.nn.n_layers; l++) tiled = tiled && m.nn.layers[l].n_out_pad <= 8 * NT_G * NT_WARPS && m.nn.layers[l].n_out_pad * 8 <= NT_RING;
+      if (tiled) {
+        NeuralPlan pl{}; pl.width = m.nn.max_width; size_t act = ((size_t)m.nn.max_width * NT_E * 8 + 127) & ~size_t(127);
+        pl.off_act1 = (uint32_t)act; pl.off_ring = (uint32_t)(2 * act); pl.off_bars = pl.off_ring + 2 * NT_RING; pl.off_flags = pl.off_bars + 64;
+        pl.smem_bytes = pl.off_flags + 128;
+        if (pl.smem_bytes <= (uint32_t)g_smem_optin) {
+          long ntiles = (a.n + NT_E - 1) / NT_E; int per_sm = (int)((size_t)g_smem_optin / pl.smem_bytes); if (per_sm < 1) per_sm = 1; if (per_sm > 4) per_sm = 4;
+          int grid = (int)(ntiles < (long)per_sm * g_num_sms ? ntiles : (long)per_sm * g_num_sms);
+          cudaFuncSetAttribute(neural_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes);
+          neural_tile_kernel<<<grid, NT_E * NT_WARPS, pl.smem_bytes, s>>>(m, a, pl);
+          return cudaGetLastError();
+        }
+      }
       size_t sm = (size_t)2 * m.nn.max_width * NN_E * 8;
       if (sm > (size_t)g_smem_optin) return cudaErrorInvalidValue;
       cudaFuncSetAttribute(neural_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);

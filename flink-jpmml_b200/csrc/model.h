@@ -42,7 +42,7 @@ struct TargetXform {  // <Targets><Target rescaleFactor rescaleConstant min max 
   int has_min, has_max, cast;  // cast: 0 none, 1 round, 2 ceiling, 3 floor
 };
 
-enum ModelKind : int { MK_CLUSTERING = 0, MK_FOREST = 1, MK_REGRESSION = 2, MK_NEURAL = 3 };
+enum ModelKind : int { MK_CLUSTERING = 0, MK_FOREST = 1, MK_REGRESSION = 2, MK_NEURAL = 3, MK_GENERAL_REGRESSION = 4 };
 
 // ---- tree ensembles -----------------------------------------------------------------------------
 enum : int { FOREST_COMPLETE = 0, FOREST_GENERAL = 1 };
@@ -100,7 +100,23 @@ struct RegressionDesc {
   const RegTerm* terms;
   const int32_t* cat_off;     // n_tables+1
   const RegCat* cats;
-  const double* dense_w;      // n_tables x F (dense only)
+  const double* dense_wt;     // dense only: F x KP transposed, KP = n_tables rounded up to 8, zero padded
+};
+
+// ---- GeneralRegressionModel (PPMatrix x ParamMatrix) -------------------------------------------------------
+enum : int { GR_REGRESSION = 0, GR_GENERAL_LINEAR = 1, GR_MULTINOMIAL = 2 };
+enum : int { GL_IDENTITY = 0, GL_LOG, GL_LOGIT, GL_PROBIT, GL_CLOGLOG, GL_LOGLOG, GL_LOGC, GL_CAUCHIT, GL_POWER, GL_NEGBIN };
+struct GCell { int32_t slot; int32_t is_factor; double value; };  // factor: indicator [x == value]; covariate: x ^ value
+static constexpr int GR_MAX_PARAMS = 64, GR_MAX_CATS = 32;
+struct GeneralRegDesc {
+  int n_params, n_rows, n_cats, classify, model_type, link;
+  double link_param, offset;
+  const int32_t* cell_off;    // n_params + 1
+  const GCell* cells;
+  const int32_t* beta_off;    // n_rows + 1
+  const int32_t* beta_param;  // parameter index per PCell
+  const double* beta;
+  const int32_t* row_cat;     // n_rows: index of the row's targetCategory among the labels (-1: regression)
 };
 
 enum : int { ACT_THRESHOLD = 0, ACT_LOGISTIC, ACT_TANH, ACT_IDENTITY, ACT_EXPONENTIAL, ACT_RECIPROCAL, ACT_SQUARE,
@@ -110,7 +126,7 @@ struct NeuralInput {  // DerivedField of a NeuralInput
   int32_t kind, slot, pts_off, n_pts, outliers, has_map_missing;  // outliers: 0 asIs, 1 asMissingValues, 2 asExtremeValues
   double value, map_missing;
 };
-struct NeuralLayer { int32_t n_in, n_out, act, norm; double threshold; int64_t w_off, b_off; };
+struct NeuralLayer { int32_t n_in, n_out, act, norm; double threshold; int64_t w_off, b_off; int64_t wt_off; int32_t n_out_pad, pad; };
 static constexpr int MAX_LAYERS = 8;
 struct NeuralDesc {
   int n_inputs, n_layers, classify, n_outputs, max_width;
@@ -118,6 +134,7 @@ struct NeuralDesc {
   const NeuralInput* inputs;
   const double* pts;          // LinearNorm (orig, norm) pairs
   const double* weights;      // per layer row-major [n_out][n_in]
+  const double* weights_t;    // per layer transposed [n_in][n_out_pad] (n_out rounded up to 8, zero padded): streamed in row chunks
   const double* biases;
   const int32_t* out_neuron;  // n_outputs: index into the last layer
   int out_denorm_off, out_denorm_n;  // regression: NormContinuous of the output to invert (n = 0: none)
@@ -125,11 +142,12 @@ struct NeuralDesc {
 
 struct DeviceModel {
   int kind, F, prep_simple, n_labels;
+  int prep_identity;  // every active field is a plain double: a present value is used as is
   int target_status;  // 0, or ST_EXTRACT when no result can ever be extracted (no named target / non-double target)
   const PrepField* prep; const double* prep_pool;
   const double* label_value; const uint8_t* label_status;  // class label / cluster id -> Double (String.toDouble)
   TargetXform tx;
-  ForestDesc forest; ClusterDesc cluster; RegressionDesc reg; NeuralDesc nn;
+  ForestDesc forest; ClusterDesc cluster; RegressionDesc reg; NeuralDesc nn; GeneralRegDesc greg;
 };
 
 // ---- host side ---------------------------------------------------------------------------------------

@@ -173,7 +173,7 @@ void read_schema(const XNode& model, Builder& b) {
   const XNode* ms = model.child("MiningSchema");
   if (!ms) malformed("no MiningSchema");
   if (const XNode* lt = model.child("LocalTransformations")) if (lt->first) unsupported("LocalTransformations");
-  std::vector<PrepField> prep; std::vector<double> pool; bool simple = true;
+  std::vector<PrepField> prep; std::vector<double> pool; bool simple = true, identity = true;
   ms->each("MiningField", [&](const XNode& f) {
     sv usage = f.attr("usageType", "active");
     std::string name(f.attr("name"));
@@ -222,11 +222,11 @@ void read_schema(const XNode& model, Builder& b) {
     }
     bool plain = (df.dtype == DT_DOUBLE || df.dtype == DT_FLOAT) && p.n_intervals == 0 && !p.has_valid_space && p.n_invalid == 0 &&
                  p.n_missing == 0 && p.has_repl == 0 && p.outlier == OT_AS_IS;
-    simple = simple && plain;
+    simple = simple && plain; identity = identity && plain && df.dtype == DT_DOUBLE;
     b.active_slot[name] = (int)prep.size(); b.slot_dtype.push_back(df.dtype);
     b.cm.active_names.push_back(name); prep.push_back(p);
   });
-  b.cm.dev.F = (int)prep.size(); b.cm.dev.prep_simple = simple ? 1 : 0;
+  b.cm.dev.F = (int)prep.size(); b.cm.dev.prep_simple = simple ? 1 : 0; b.cm.dev.prep_identity = identity ? 1 : 0;
   b.put(&b.cm.dev.prep, prep); b.put(&b.cm.dev.prep_pool, pool);
   // <Targets>
   TargetXform tx{1.0, 0.0, 0.0, 0.0, 0, 0, 0};
@@ -613,10 +613,74 @@ void compile_regression(const XNode& m, Builder& b) {
   if (!classify && icpt.size() != 1) unsupported("regression with several RegressionTables");
   d.n_tables = (int)icpt.size(); dense = dense && cats.empty(); d.dense = dense ? 1 : 0;
   std::vector<double> w;
-  if (dense) { w.resize(icpt.size() * (size_t)F); for (size_t t = 0; t < icpt.size(); t++) for (int i = 0; i < F; i++) w[t * F + i] = terms[toff[t] + i].coef; }
-  b.put(&d.intercept, icpt); b.put(&d.term_off, toff); b.put(&d.terms, terms); b.put(&d.cat_off, coff); b.put(&d.cats, cats); b.put(&d.dense_w, w);
+  if (dense) { size_t KP = (icpt.size() + 7) / 8 * 8; w.assign(KP * (size_t)F, 0.0); for (size_t t = 0; t < icpt.size(); t++) for (int i = 0; i < F; i++) w[(size_t)i * KP + t] = terms[toff[t] + i].coef; }
+  b.put(&d.intercept, icpt); b.put(&d.term_off, toff); b.put(&d.terms, terms); b.put(&d.cat_off, coff); b.put(&d.cats, cats); b.put(&d.dense_wt, w);
   if (classify) b.set_labels(labels, false); else b.set_labels({}, false);
   finish_target(b, classify);
+}
+
+// ---------------------------------------------------------------------------------------------- general regression
+void compile_general_regression(const XNode& m, Builder& b) {
+  b.cm.family = "GeneralRegressionModel"; b.cm.dev.kind = MK_GENERAL_REGRESSION;
+  GeneralRegDesc& d = b.cm.dev.greg; bool classify = m.attr("functionName") == "classification"; d.classify = classify;
+  sv mt = m.attr("modelType");
+  if (mt == "regression") d.model_type = GR_REGRESSION;
+  else if (mt == "generalLinear" || mt == "generalizedLinear") d.model_type = GR_GENERAL_LINEAR;
+  else if (mt == "multinomialLogistic") d.model_type = GR_MULTINOMIAL;
+  else unsupported("GeneralRegressionModel modelType " + std::string(mt));
+  if (d.model_type == GR_MULTINOMIAL && !classify) unsupported("multinomialLogistic regression");
+  static const char* links[] = {"identity", "log", "logit", "probit", "cloglog", "loglog", "logc", "cauchit", "power", "negbin"};
+  sv lk = m.attr("linkFunction", "identity"); d.link = -1;
+  for (int i = 0; i < 10; i++) if (lk == links[i]) d.link = i;
+  if (d.link < 0) unsupported("linkFunction " + std::string(lk));
+  d.link_param = m.has("linkParameter") ? need_double(m.attr("linkParameter"), "linkParameter") : 0.0;
+  d.offset = m.has("offsetValue") ? need_double(m.attr("offsetValue"), "offsetValue") : 0.0;
+  if (m.has("offsetVariable") || m.has("trialsVariable") || m.has("trialsValue")) unsupported("offsetVariable / trials");
+  std::unordered_map<std::string, int> pidx; std::unordered_map<std::string, bool> is_factor;
+  if (const XNode* pl = m.child("ParameterList")) pl->each("Parameter", [&](const XNode& p) { int i = (int)pidx.size(); pidx[std::string(p.attr("name"))] = i; });
+  if (pidx.empty()) malformed("empty ParameterList");
+  if ((int)pidx.size() > GR_MAX_PARAMS) unsupported("more than 64 parameters in a GeneralRegressionModel");
+  if (const XNode* fl = m.child("FactorList")) fl->each("Predictor", [&](const XNode& p) { is_factor[std::string(p.attr("name"))] = true; });
+  if (const XNode* cl = m.child("CovariateList")) cl->each("Predictor", [&](const XNode& p) { is_factor[std::string(p.attr("name"))] = false; });
+  std::vector<std::vector<GCell>> per(pidx.size());
+  if (const XNode* pp = m.child("PPMatrix")) pp->each("PPCell", [&](const XNode& c) {
+    auto it = pidx.find(std::string(c.attr("parameterName"))); if (it == pidx.end()) malformed("PPCell for an unknown parameter");
+    std::string pn(c.attr("predictorName")); bool fac = is_factor.count(pn) ? is_factor[pn] : false;
+    uint8_t dt = b.dict_field(pn).dtype; if (dt == DT_STRING || dt == DT_OTHER) unsupported("GeneralRegression predictor on a non-numeric field");
+    GCell cell{b.slot_of(pn), fac ? 1 : 0, 1.0};
+    if (fac) { if (!parse_in_dtype(dt, c.attr("value"), &cell.value)) unsupported("factor value does not parse in the field's dataType"); }
+    else cell.value = need_double(c.attr("value", "1"), "PPCell value");
+    per[it->second].push_back(cell);
+  });
+  std::vector<int32_t> cell_off{0}; std::vector<GCell> cells;
+  for (auto& v : per) { cells.insert(cells.end(), v.begin(), v.end()); cell_off.push_back((int32_t)cells.size()); }
+  // target categories: the target DataField's valid values, in document order
+  std::vector<std::string> cats;
+  if (classify) {
+    if (!b.has_target) unsupported("classification GeneralRegressionModel without a target field");
+    b.dict_field(b.target_name).node->each("Value", [&](const XNode& v) { if (v.attr("property", "valid") == "valid") cats.push_back(std::string(v.attr("value"))); });
+    if (cats.empty()) unsupported("target field declares no categories");
+    if ((int)cats.size() > GR_MAX_CATS) unsupported("more than 32 target categories");
+  }
+  std::vector<std::string> row_names; std::vector<std::vector<std::pair<int, double>>> rows;
+  if (const XNode* pm = m.child("ParamMatrix")) pm->each("PCell", [&](const XNode& c) {
+    std::string cat(c.attr("targetCategory")); size_t r = 0;
+    for (; r < row_names.size(); r++) if (row_names[r] == cat) break;
+    if (r == row_names.size()) { row_names.push_back(cat); rows.emplace_back(); }
+    auto it = pidx.find(std::string(c.attr("parameterName"))); if (it == pidx.end()) malformed("PCell for an unknown parameter");
+    rows[r].emplace_back(it->second, need_double(c.attr("beta"), "beta"));
+  });
+  if (rows.empty()) malformed("empty ParamMatrix");
+  std::vector<int32_t> beta_off{0}, beta_param, row_cat; std::vector<double> beta;
+  for (size_t r = 0; r < rows.size(); r++) {
+    for (auto& pb : rows[r]) { beta_param.push_back(pb.first); beta.push_back(pb.second); }
+    beta_off.push_back((int32_t)beta.size());
+    int ci = -1; for (size_t k = 0; k < cats.size(); k++) if (cats[k] == row_names[r]) ci = (int)k;
+    row_cat.push_back(ci);
+  }
+  d.n_params = (int)pidx.size(); d.n_rows = (int)rows.size(); d.n_cats = (int)cats.size();
+  b.put(&d.cell_off, cell_off); b.put(&d.cells, cells); b.put(&d.beta_off, beta_off); b.put(&d.beta_param, beta_param); b.put(&d.beta, beta); b.put(&d.row_cat, row_cat);
+  b.set_labels(cats, false); finish_target(b, classify);
 }
 
 // ---------------------------------------------------------------------------------------------- neural network
@@ -695,7 +759,13 @@ void compile_neural(const XNode& m, Builder& b) {
   });
   if (out_neuron.empty()) malformed("no NeuralOutput");
   d.n_outputs = (int)out_neuron.size();
-  b.put(&d.inputs, inputs); b.put(&d.pts, pts); b.put(&d.weights, W); b.put(&d.biases, B); b.put(&d.out_neuron, out_neuron);
+  std::vector<double> WT;
+  for (int l = 0; l < nl; l++) {
+    NeuralLayer& ly = d.layers[l]; ly.n_out_pad = (ly.n_out + 7) / 8 * 8; ly.wt_off = (int64_t)WT.size();
+    WT.resize(WT.size() + (size_t)ly.n_in * ly.n_out_pad, 0.0);
+    for (int j = 0; j < ly.n_out; j++) for (int i = 0; i < ly.n_in; i++) WT[(size_t)ly.wt_off + (size_t)i * ly.n_out_pad + j] = W[(size_t)ly.w_off + (size_t)j * ly.n_in + i];
+  }
+  b.put(&d.inputs, inputs); b.put(&d.pts, pts); b.put(&d.weights, W); b.put(&d.weights_t, WT); b.put(&d.biases, B); b.put(&d.out_neuron, out_neuron);
   b.set_labels(labels, false); finish_target(b, classify);
 }
 
@@ -711,7 +781,7 @@ CompiledModel compile_pmml(const char* data, size_t len) {
   const XNode* me = nullptr;
   for (const XNode* k = root.first; k && !me; k = k->next) {
     sv n = k->name;
-    if (n == "ClusteringModel" || n == "TreeModel" || n == "MiningModel" || n == "RegressionModel" || n == "NeuralNetwork") me = k;
+    if (n == "ClusteringModel" || n == "TreeModel" || n == "MiningModel" || n == "RegressionModel" || n == "NeuralNetwork" || n == "GeneralRegressionModel") me = k;
     else if (n.size() > 5 && n.substr(n.size() - 5) == "Model") unsupported("model element " + std::string(n));
     else if (n == "Scorecard" || n == "RuleSetModel" || n == "NaiveBayesModel") unsupported("model element " + std::string(n));
   }
@@ -722,6 +792,7 @@ CompiledModel compile_pmml(const char* data, size_t len) {
   else if (me->name == "TreeModel") compile_tree(*me, b);
   else if (me->name == "MiningModel") compile_mining(*me, b);
   else if (me->name == "RegressionModel") compile_regression(*me, b);
+  else if (me->name == "GeneralRegressionModel") compile_general_regression(*me, b);
   else compile_neural(*me, b);
   return std::move(b.cm);
 }

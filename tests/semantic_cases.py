@@ -1,6 +1,8 @@
 """Adversarial small documents with hand-derived answers (PMML 4.3 spec read the way JPMML 1.3.x implements it,
 SURVEY.md Appendix A).  Each case: (name, pmml bytes, X rows, present mask or None, replace or None,
 expected list of (status, score-or-None, aux-or-None))."""
+import math
+
 import numpy as np
 
 from hand_pmml import AB, SMALL_TREE, doc, schema, tree_model
@@ -118,4 +120,32 @@ def cases():
     out.append(("cluster/chebychev", clu("chebychev", ids=("1", "2")), X8, P8, None, [(0, 1.0, 1), (0, 2.0, 2), (0, 1.0, 1), (0, 2.0, 2), (0, 1.0, 1)]))
     out.append(("cluster/cityBlock-weighted", clu("cityBlock", ids=("1", "2"), weights=' fieldWeight="0.01"'), X8, P8, None,
                 [(0, 1.0, 1), (0, 1.0, 1), (0, 1.0, 1), (0, 2.0, 2), (0, 1.0, 1)]))
+    # ---- GeneralRegressionModel: p0 = intercept, p1 = a, p2 = a^2 * [b == 1]; beta = 0.5, 2, -1
+    def greg(model_type, function="regression", link="", cats=(), pcells=None, target_dtype="double"):
+        pc = pcells or '<PCell parameterName="p0" beta="0.5"/><PCell parameterName="p1" beta="2"/><PCell parameterName="p2" beta="-1"/>'
+        body = (f'<GeneralRegressionModel modelName="g" functionName="{function}" modelType="{model_type}"{link}>{schema(["a", "b"])}'
+                '<ParameterList><Parameter name="p0"/><Parameter name="p1"/><Parameter name="p2"/></ParameterList>'
+                '<FactorList><Predictor name="b"/></FactorList><CovariateList><Predictor name="a"/></CovariateList>'
+                '<PPMatrix><PPCell value="1" predictorName="a" parameterName="p1"/><PPCell value="2" predictorName="a" parameterName="p2"/>'
+                '<PPCell value="1" predictorName="b" parameterName="p2"/></PPMatrix>'
+                f'<ParamMatrix>{pc}</ParamMatrix></GeneralRegressionModel>')
+        tgt = ("y", "categorical", target_dtype, cats) if cats else ("y", "continuous", "double", ())
+        return doc(AB, body, target=tgt)
+    X9, P9 = _rows((2, 1), (2, 0), (-1, 1), (None, 1), (3, None))
+    out.append(("greg/regression-identity", greg("regression"), X9, P9, None, [(0, 0.5, None), (0, 4.5, None), (0, -2.5, None), (3, None, None), (3, None, None)]))
+    out.append(("greg/link-log", greg("generalLinear", link=' linkFunction="log"'), X9, P9, None,
+                [(0, math.exp(0.5), None), (0, math.exp(4.5), None), (0, math.exp(-2.5), None), (3, None, None), (3, None, None)]))
+    out.append(("greg/link-logit-offset", greg("generalLinear", link=' linkFunction="logit" offsetValue="1"'), X9, P9, None,
+                [(0, 1 / (1 + math.exp(-1.5)), None), (0, 1 / (1 + math.exp(-5.5)), None), (0, 1 / (1 + math.exp(1.5)), None), (3, None, None), (3, None, None)]))
+    # multinomial: eta("0") = 0.5 + 2a - a^2[b==1], eta("1") = 1 (p0 only, beta 1), "2" is the reference (eta 0)
+    pc = ('<PCell targetCategory="0" parameterName="p0" beta="0.5"/><PCell targetCategory="0" parameterName="p1" beta="2"/>'
+          '<PCell targetCategory="0" parameterName="p2" beta="-1"/><PCell targetCategory="1" parameterName="p0" beta="1"/>')
+    #  (2,1): eta0 = 0.5 -> "1" wins (eta 1);  (2,0): eta0 = 4.5 -> "0";  (-1,1): eta0 = -2.5 -> "1";  a = 0.25,b=0: eta0 = 1.0 == eta1 -> tie, first ("0")
+    X10, P10 = _rows((2, 1), (2, 0), (-1, 1), (0.25, 0), (None, 0))
+    out.append(("greg/multinomial", greg("multinomialLogistic", function="classification", cats=("0", "1", "2"), pcells=pc, target_dtype="string"), X10, P10, None,
+                [(0, 1.0, 1), (0, 0.0, 0), (0, 1.0, 1), (0, 0.0, 0), (3, None, None)]))
     return out
+
+
+# cases whose expected scores go through exp(): compared with a relative tolerance instead of bit-exactly
+TOLERANT = {"greg/link-log": 1e-12, "greg/link-logit-offset": 1e-12}

@@ -16,10 +16,15 @@ def test_gpu_hand_derived(engine, oracle, gen, case):
     o = oracle.OracleModel(pm).predict(X, pb, rep)
     assert np.array_equal(r["status"], o["status"]), (name, r["status"], o["status"])
     ok = o["status"] == 0
-    assert np.array_equal(r["score"][ok], o["score"][ok]), (name, r["score"], o["score"])
+    if name in semantic_cases.TOLERANT:
+        np.testing.assert_allclose(r["score"][ok], o["score"][ok], rtol=1e-9)
+    else:
+        assert np.array_equal(r["score"][ok], o["score"][ok]), (name, r["score"], o["score"])
     for i, (st, score, aux) in enumerate(expected):
         assert r["status"][i] == st, (name, i, r["status"])
-        if st == 0:
+        if st == 0 and name in semantic_cases.TOLERANT:
+            assert abs(r["score"][i] - score) <= 1e-9 * abs(score)
+        elif st == 0:
             assert r["score"][i] == score
         if aux is not None:
             assert r["aux"][i] == aux, (name, i, r["aux"], o["aux"])
