@@ -158,6 +158,9 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
+__device__ __forceinline__ void cp_async8(void* dst_smem, const void* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(dst_smem)), "l"(src) : "memory");
+}
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 // ================================================================================================ forest, complete trees
@@ -624,26 +627,39 @@ __global__ void __launch_bounds__(256, 3) regression_tile_kernel(const __grid_co
     double acc[CK_TC]; int flags = 0;  // bit0 preparation failure, bit1 missing predictor
 #pragma unroll
     for (int k = 0; k < CK_TC; k++) { int c = cg * CK_TC + k; acc[k] = c < C ? rd.intercept[c] : 0.0; }
-    for (int f0 = 0; f0 < F; f0 += pl.chunk) {
+    // double-buffered chunks: the copies of chunk c+1 (cp.async, 8 B each, written straight into the transposed
+    // position) are in flight while chunk c is multiplied
+    const int nchunks = (F + pl.chunk - 1) / pl.chunk;
+    auto fill = [&](int buf, int f0) {
       const int nfc = min(pl.chunk, F - f0);
-      __syncthreads();
-      for (int i = tid; i < nfc * KP; i += blockDim.x) wt[i] = rd.dense_wt[(size_t)f0 * KP + i];
+      double* wb = wt + (size_t)buf * pl.chunk * KP; double* xb = xs + (size_t)buf * pl.chunk * EP; uint8_t* sb = sts + (size_t)buf * pl.chunk * (E + 4);
+      for (int i = tid; i < nfc * KP; i += blockDim.x) cp_async8(wb + i, rd.dense_wt + (size_t)f0 * KP + i);
       const int sh = 31 - __clz(nfc); const bool pow2 = (nfc & (nfc - 1)) == 0;
       for (int i = tid; i < E * nfc; i += blockDim.x) {
-        int r = pow2 ? (i >> sh) : (i / nfc), f = i - r * nfc; long rr = row0 + r; double v = 0; int st = 0;
-        if (HASMISS) { if (rr < a.n) st = load_field(m, a, rr, f0 + f, v); sts[f * (E + 4) + r] = (uint8_t)st; }
-        else if (rr < a.n) v = __ldcs(a.X + rr * (long)F + f0 + f);   // plain doubles, all present
-        xs[f * EP + r] = v;
+        int r = pow2 ? (i >> sh) : (i / nfc), f = i - r * nfc; long rr = row0 + r;
+        if (HASMISS) { double v = 0; int st = 0; if (rr < a.n) st = load_field(m, a, rr, f0 + f, v); sb[f * (E + 4) + r] = (uint8_t)st; xb[f * EP + r] = v; }
+        else if (rr < a.n) cp_async8(xb + f * EP + r, a.X + rr * (long)F + f0 + f);   // plain doubles, all present
+        else xb[f * EP + r] = 0.0;
       }
+      asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    __syncthreads();   // the previous tile's epilogue is done with ys / the buffers
+    fill(0, 0);
+    for (int c = 0; c < nchunks; c++) {
+      const int f0 = c * pl.chunk, nfc = min(pl.chunk, F - f0), buf = c & 1;
+      if (c + 1 < nchunks) { fill(buf ^ 1, f0 + pl.chunk); asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+      else asm volatile("cp.async.wait_group 0;" ::: "memory");
       __syncthreads();
-      const double* wp = wt + cg * CK_TC;
+      const double* wp = wt + (size_t)buf * pl.chunk * KP + cg * CK_TC; const double* xb = xs + (size_t)buf * pl.chunk * EP;
+      const uint8_t* sb = sts + (size_t)buf * pl.chunk * (E + 4);
       for (int f = 0; f < nfc; f++, wp += KP) {
-        double x = xs[f * EP + e];
-        if (HASMISS) { int st = sts[f * (E + 4) + e]; flags |= st == 2 ? 1 : (st == 1 ? 2 : 0); }
+        double x = xb[f * EP + e];
+        if (HASMISS) { int st = sb[f * (E + 4) + e]; flags |= st == 2 ? 1 : (st == 1 ? 2 : 0); }
         const double2* w2 = reinterpret_cast<const double2*>(wp);
 #pragma unroll
         for (int k = 0; k < CK_TC / 2; k++) { double2 w = w2[k]; acc[2 * k] += w.x * x; acc[2 * k + 1] += w.y * x; }
       }
+      __syncthreads();   // buffer `buf` may be refilled by the next iteration's fill
     }
 #pragma unroll
     for (int k = 0; k < CK_TC; k++) ys[(cg * CK_TC + k) * EP + e] = acc[k];
@@ -838,6 +854,21 @@ __global__ void __launch_bounds__(NN_E* NN_WARPS) neural_kernel(const __grid_con
 // z accumulates from the bias in connection order, unfused, in double (JPMML NeuralNetworkEvaluator order).
 constexpr int NT_E = 32, NT_WARPS = 8, NT_G = 4, NT_RING = 32 * 1024;
 struct NeuralPlan { uint32_t off_act1, off_ring, off_bars, off_flags, smem_bytes; int width; };
+// rows of one weight chunk times one activation column: NG groups of 8 running sums per thread
+template <int NG>
+__device__ __forceinline__ void nt_rows(double (&z)[4][8], const double* __restrict__ xcol, const double* __restrict__ wbase, int rows, int n_out_pad, int warp) {
+#pragma unroll 2
+  for (int r = 0; r < rows; r++) {
+    const double x = xcol[r * 32];
+    const double2* w2 = reinterpret_cast<const double2*>(wbase + (size_t)r * n_out_pad);
+#pragma unroll
+    for (int g = 0; g < NG; g++) {
+      const int jg = warp + g * 8;
+#pragma unroll
+      for (int k = 0; k < 4; k++) { double2 w = w2[jg * 4 + k]; z[g][2 * k] += w.x * x; z[g][2 * k + 1] += w.y * x; }
+    }
+  }
+}
 __global__ void __launch_bounds__(NT_E* NT_WARPS, 1) neural_tile_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, const NeuralPlan pl) {
   extern __shared__ __align__(128) uint8_t smem[];
   const NeuralDesc& nd = m.nn;
@@ -897,17 +928,14 @@ __global__ void __launch_bounds__(NT_E* NT_WARPS, 1) neural_tile_kernel(const __
         const int rows = min(rpc, L.n_in - i0);
         uint32_t slot = q_wait & 1u; mbar_wait(&bars[slot], (q_wait >> 1) & 1u); q_wait++;
         const double* wbase = ring + (size_t)slot * (NT_RING / 8);
-        for (int r = 0; r < rows; r++) {
-          const double x = cur[(i0 + r) * NT_E + lane];
-          const double2* w2 = reinterpret_cast<const double2*>(wbase + (size_t)r * L.n_out_pad);
-#pragma unroll
-          for (int g = 0; g < NT_G; g++) {
-            int jg = warp + g * NT_WARPS;
-            if (jg < groups) {
-#pragma unroll
-              for (int k = 0; k < 4; k++) { double2 w = w2[jg * 4 + k]; z[g][2 * k] += w.x * x; z[g][2 * k + 1] += w.y * x; }
-            }
-          }
+        const double* xcol = cur + (size_t)i0 * NT_E + lane;
+        const int ng = groups > warp ? min(NT_G, (groups - warp + NT_WARPS - 1) / NT_WARPS) : 0;   // warp-uniform
+        switch (ng) {  // no branches inside the row loop
+          case 4: nt_rows<4>(z, xcol, wbase, rows, L.n_out_pad, warp); break;
+          case 3: nt_rows<3>(z, xcol, wbase, rows, L.n_out_pad, warp); break;
+          case 2: nt_rows<2>(z, xcol, wbase, rows, L.n_out_pad, warp); break;
+          case 1: nt_rows<1>(z, xcol, wbase, rows, L.n_out_pad, warp); break;
+          default: break;
         }
         __syncthreads();   // ring slot consumed
         if (tid == 0) { fence_proxy_async(); issue_next(); }
@@ -1090,8 +1118,8 @@ cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t 
         const int EP = pl.events + 1;
         int chunk = 64; while (chunk > m.F && chunk > 1) chunk /= 2;   // power of two: cheap row/column split
         for (;; chunk /= 2) {
-          size_t off = ((size_t)chunk * pl.kp * 8 + 127) & ~size_t(127); pl.off_x = (uint32_t)off; off += (size_t)chunk * EP * 8;
-          pl.off_st = (uint32_t)off; off += (size_t)chunk * (pl.events + 4); off = (off + 15) & ~size_t(15);
+          size_t off = ((size_t)2 * chunk * pl.kp * 8 + 127) & ~size_t(127); pl.off_x = (uint32_t)off; off += (size_t)2 * chunk * EP * 8;
+          pl.off_st = (uint32_t)off; off += (size_t)2 * chunk * (pl.events + 4); off = (off + 15) & ~size_t(15);
           pl.off_y = (uint32_t)off; off += (size_t)pl.kp * EP * 8; pl.off_flags = (uint32_t)off; off += (size_t)pl.events * 4; pl.smem_bytes = (uint32_t)((off + 127) & ~size_t(127));
           if (pl.smem_bytes <= 72 * 1024u || chunk == 1) break;   // three CTAs per SM: one loads while the others compute
         }
