@@ -852,18 +852,18 @@ __global__ void __launch_bounds__(NN_E* NN_WARPS) neural_kernel(const __grid_con
 // 4 groups of 8 output neurons (32 running sums in registers); per input neuron it does one conflict-free LDS.64 of the
 // activation and 4 broadcast LDS.128 per group, feeding 16 double-precision instructions per group.
 // z accumulates from the bias in connection order, unfused, in double (JPMML NeuralNetworkEvaluator order).
-constexpr int NT_E = 32, NT_WARPS = 8, NT_G = 4, NT_RING = 32 * 1024;
 struct NeuralPlan { uint32_t off_act1, off_ring, off_bars, off_flags, smem_bytes; int width; };
 // rows of one weight chunk times one activation column: NG groups of 8 running sums per thread
+constexpr int NT_E = 32, NT_WARPS = 16, NT_G = 2, NT_RING = 32 * 1024;
 template <int NG>
-__device__ __forceinline__ void nt_rows(double (&z)[4][8], const double* __restrict__ xcol, const double* __restrict__ wbase, int rows, int n_out_pad, int warp) {
-#pragma unroll 2
+__device__ __forceinline__ void nt_rows(double (&z)[NT_G][8], const double* __restrict__ xcol, const double* __restrict__ wbase, int rows, int n_out_pad, int warp) {
+#pragma unroll 4
   for (int r = 0; r < rows; r++) {
     const double x = xcol[r * 32];
     const double2* w2 = reinterpret_cast<const double2*>(wbase + (size_t)r * n_out_pad);
 #pragma unroll
     for (int g = 0; g < NG; g++) {
-      const int jg = warp + g * 8;
+      const int jg = warp + g * NT_WARPS;
 #pragma unroll
       for (int k = 0; k < 4; k++) { double2 w = w2[jg * 4 + k]; z[g][2 * k] += w.x * x; z[g][2 * k + 1] += w.y * x; }
     }
@@ -931,8 +931,6 @@ __global__ void __launch_bounds__(NT_E* NT_WARPS, 1) neural_tile_kernel(const __
         const double* xcol = cur + (size_t)i0 * NT_E + lane;
         const int ng = groups > warp ? min(NT_G, (groups - warp + NT_WARPS - 1) / NT_WARPS) : 0;   // warp-uniform
         switch (ng) {  // no branches inside the row loop
-          case 4: nt_rows<4>(z, xcol, wbase, rows, L.n_out_pad, warp); break;
-          case 3: nt_rows<3>(z, xcol, wbase, rows, L.n_out_pad, warp); break;
           case 2: nt_rows<2>(z, xcol, wbase, rows, L.n_out_pad, warp); break;
           case 1: nt_rows<1>(z, xcol, wbase, rows, L.n_out_pad, warp); break;
           default: break;
