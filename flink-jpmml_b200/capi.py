@@ -70,6 +70,7 @@ def lib():
         "fjp_host_free": (None, [vp]),
         "fjp_score_batch": (i32, [vp, vp, vp, vp, vp, lng, i32, vp, vp, vp]),
         "fjp_score_batch_ex": (i32, [vp, vp, vp, vp, vp, lng, i32, vp, vp, vp, vp, i32, vp, i32]),
+        "fjp_score_sparse": (i32, [vp, vp, vp, vp, vp, vp, lng, i32, vp, vp, vp]),
         "fjp_score_device": (i32, [vp, vp, vp, vp, vp, lng, i32, vp, vp, vp, vp]),
         "fjp_submit": (i32, [vp, vp, vp, vp, vp, lng, i32, vp, vp, vp, C.POINTER(i32)]),
         "fjp_wait": (i32, [vp, i32]),
@@ -86,7 +87,7 @@ EXPORTS = ["fjp_version", "fjp_last_error", "fjp_max_inflight", "fjp_engine_crea
            "fjp_model_replicate", "fjp_model_num_fields", "fjp_model_field_name", "fjp_model_name", "fjp_model_family",
            "fjp_model_num_labels", "fjp_model_label", "fjp_model_num_segments", "fjp_model_describe", "fjp_model_device_bytes",
            "fjp_table_add", "fjp_table_del", "fjp_table_get", "fjp_table_size", "fjp_table_epoch", "fjp_host_alloc",
-           "fjp_host_free", "fjp_score_batch", "fjp_score_batch_ex", "fjp_score_device", "fjp_submit", "fjp_wait"]
+           "fjp_host_free", "fjp_score_batch", "fjp_score_batch_ex", "fjp_score_sparse", "fjp_score_device", "fjp_submit", "fjp_wait"]
 
 
 def _ptr(a):
@@ -194,6 +195,16 @@ class Engine:
 
     def sync(self):
         _check(lib().fjp_engine_sync(self._h))
+
+    def score_sparse(self, model, row_ptr, indices, values, vec_size, replace=None):
+        """CSR rows (SparseVector batch) through fjp_score_sparse."""
+        row_ptr = np.ascontiguousarray(row_ptr, dtype=np.int64); indices = np.ascontiguousarray(indices, dtype=np.int32)
+        values = np.ascontiguousarray(values, dtype=np.float64); n = len(row_ptr) - 1
+        rp = None if replace is None else np.ascontiguousarray(np.broadcast_to(np.asarray(replace, dtype=np.float64), (n,)))
+        score = np.empty(n, dtype=np.float64); status = np.empty(n, dtype=np.uint8); aux = np.empty(n, dtype=np.int32)
+        _check(lib().fjp_score_sparse(self._h, model._h if model else None, _ptr(row_ptr), _ptr(indices), _ptr(values), _ptr(rp), n, vec_size,
+                                      _ptr(score), _ptr(status), _ptr(aux)))
+        return {"score": score, "status": status, "aux": aux}
 
     # ---- scoring (host buffers)
     def score(self, model: "Model | None", X, present_bits=None, replace=None, node_ids=False, n_probs=0, aux=True):

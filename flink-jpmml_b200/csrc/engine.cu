@@ -309,6 +309,53 @@ int fjp_score_batch_ex(fjp_engine* e, fjp_model* m, const double* X, const uint3
   return rc;
 }
 
+int fjp_score_sparse(fjp_engine* e, fjp_model* m, const int64_t* row_ptr, const int32_t* indices, const double* values,
+                     const double* replace, long n, int vec_size, double* score, uint8_t* status, int32_t* aux) {
+  if (n <= 0) return 0;
+  HostBatch hb{nullptr, nullptr, replace, n, vec_size, score, status, aux, nullptr, 0, nullptr, 0};
+  if (host_short_circuit(m, hb)) return 0;
+  if (!m->d_blob) return fail("model was compiled without an engine: it cannot score");
+  CK(cudaSetDevice(e->device));
+  if (m->device != e->device) return fail("model lives on another device; use fjp_model_replicate");
+  const int F = vec_size, W = (F + 31) / 32;
+  long rows = (long)((size_t(24) << 20) / ((size_t)F * 8 + 16)); if (rows < 4096) rows = 4096; if (rows > (1 << 18)) rows = 1 << 18;
+  int s0 = acquire_slot(e), s1 = n > rows ? try_acquire_slot(e) : -1;
+  int used[2] = {s0, s1}; int ns = s1 >= 0 ? 2 : 1; int rc = 0; long k = 0;
+  for (long lo = 0; lo < n && rc == 0; lo += rows, k++) {
+    Slot& s = e->slots[used[k % ns]];
+    const long hi = std::min(n, lo + rows), cn = hi - lo; const int64_t nz0 = row_ptr[lo], nnz = row_ptr[hi] - nz0;
+    Carve c;
+    size_t oRp = c.take((size_t)(cn + 1) * 8), oIx = c.take((size_t)std::max<int64_t>(nnz, 1) * 4), oVl = c.take((size_t)std::max<int64_t>(nnz, 1) * 8);
+    size_t oX = c.take((size_t)cn * F * 8), oP = c.take((size_t)cn * W * 4), oR = replace ? c.take((size_t)cn * 8) : 0;   // oX, oP: scratch for the expanded rows
+    size_t oS = c.take((size_t)cn * 8), oT = c.take((size_t)cn), oA = aux ? c.take((size_t)cn * 4) : 0;
+    if (slot_reserve(s, c.off)) { rc = -1; break; }
+    // row_ptr is re-based on the device side by passing shifted index / value pointers
+    rc = [&]() -> int {
+      CK(cudaMemcpyAsync(s.buf + oRp, row_ptr + lo, (size_t)(cn + 1) * 8, cudaMemcpyHostToDevice, s.s));
+      if (nnz > 0) {
+        CK(cudaMemcpyAsync(s.buf + oIx, indices + nz0, (size_t)nnz * 4, cudaMemcpyHostToDevice, s.s));
+        CK(cudaMemcpyAsync(s.buf + oVl, values + nz0, (size_t)nnz * 8, cudaMemcpyHostToDevice, s.s));
+      }
+      if (replace) CK(cudaMemcpyAsync(s.buf + oR, replace + lo, (size_t)cn * 8, cudaMemcpyHostToDevice, s.s));
+      int launches = 0;
+      CK(launch_expand_sparse(reinterpret_cast<const long long*>(s.buf + oRp), reinterpret_cast<const int32_t*>(s.buf + oIx) - nz0,
+                              reinterpret_cast<const double*>(s.buf + oVl) - nz0, cn, F, reinterpret_cast<double*>(s.buf + oX),
+                              reinterpret_cast<uint32_t*>(s.buf + oP), s.s, &launches));
+      BatchArgs a{}; a.X = reinterpret_cast<double*>(s.buf + oX); a.present = reinterpret_cast<uint32_t*>(s.buf + oP); a.present_stride = W;
+      a.replace = replace ? reinterpret_cast<double*>(s.buf + oR) : nullptr; a.n = cn;
+      a.score = reinterpret_cast<double*>(s.buf + oS); a.status = s.buf + oT; a.aux = aux ? reinterpret_cast<int32_t*>(s.buf + oA) : nullptr;
+      CK(launch_score(m->dev, a, s.s, &launches));
+      e->launches += launches;
+      CK(cudaMemcpyAsync(score + lo, s.buf + oS, (size_t)cn * 8, cudaMemcpyDeviceToHost, s.s));
+      CK(cudaMemcpyAsync(status + lo, s.buf + oT, (size_t)cn, cudaMemcpyDeviceToHost, s.s));
+      if (aux) CK(cudaMemcpyAsync(aux + lo, s.buf + oA, (size_t)cn * 4, cudaMemcpyDeviceToHost, s.s));
+      return 0;
+    }();
+  }
+  for (int i = 0; i < ns; i++) { cudaError_t ce = cudaStreamSynchronize(e->slots[used[i]].s); if (ce != cudaSuccess && rc == 0) rc = fail(std::string("scoring failed: ") + cudaGetErrorString(ce)); release_slot(e, used[i]); }
+  return rc;
+}
+
 int fjp_score_batch(fjp_engine* e, fjp_model* m, const double* X, const uint32_t* present, const double* replace,
                     long n, int vec_size, double* score, uint8_t* status, int32_t* aux) {
   return fjp_score_batch_ex(e, m, X, present, replace, n, vec_size, score, status, aux, nullptr, 0, nullptr, 0);

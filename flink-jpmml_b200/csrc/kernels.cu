@@ -1160,6 +1160,35 @@ cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t 
   return cudaErrorInvalidValue;
 }
 
+// ================================================================================================ sparse ingest
+// SparseVector rows arrive as CSR (row_ptr, indices, values) and are expanded ON THE DEVICE into the dense row +
+// present-bit form every scoring kernel reads (absent index = cleared bit = missing value; an explicit 0.0 is present:
+// api/converter/VectorConverter.scala:61-67, 81-84).  One warp per row; the expanded rows live in scratch memory that
+// the caller provides (n x F doubles + n x ceil(F/32) words).  Indices outside [0, F) match no slot and are dropped, as
+// in the reference's `(0 until size).map(indices.contains)`.
+__global__ void __launch_bounds__(256) expand_sparse_kernel(const long long* __restrict__ row_ptr, const int32_t* __restrict__ idx,
+                                                            const double* __restrict__ val, long n, int F, int W,
+                                                            double* __restrict__ X, uint32_t* __restrict__ present) {
+  const int lane = threadIdx.x & 31; const long row = (blockIdx.x * (long)blockDim.x + threadIdx.x) >> 5;
+  if (row >= n) return;
+  double* xr = X + row * (long)F; uint32_t* pr = present + row * (long)W;
+  for (int f = lane; f < F; f += 32) xr[f] = 0.0;
+  for (int w = lane; w < W; w += 32) pr[w] = 0u;
+  __syncwarp();
+  const long long lo = row_ptr[row], hi = row_ptr[row + 1];
+  for (long long k = lo + lane; k < hi; k += 32) {
+    int i = idx[k];
+    if (i >= 0 && i < F) { xr[i] = val[k]; atomicOr(&pr[i >> 5], 1u << (i & 31)); }
+  }
+}
+cudaError_t launch_expand_sparse(const long long* row_ptr, const int32_t* idx, const double* val, long n, int F,
+                                 double* X, uint32_t* present, cudaStream_t s, int* launches) {
+  if (n <= 0) return cudaSuccess;
+  if (launches) (*launches)++;
+  expand_sparse_kernel<<<(unsigned)((n * 32 + 255) / 256), 256, 0, s>>>(row_ptr, idx, val, n, F, (F + 31) / 32, X, present);
+  return cudaGetLastError();
+}
+
 // Fills status for a whole batch without looking at the data: size mismatch (1) and unknown model (5).
 __global__ void fill_status_kernel(BatchArgs a, int status) {
   long row = blockIdx.x * (long)blockDim.x + threadIdx.x;

@@ -31,6 +31,8 @@ struct ForestLaunch {  // tile geometry of forest_complete_kernel
 
 bool plan_forest_complete(const DeviceModel& m, ForestLaunch* out);
 cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t s, int* launches);
+cudaError_t launch_expand_sparse(const long long* row_ptr, const int32_t* idx, const double* val, long n, int F,
+                                 double* X, uint32_t* present, cudaStream_t s, int* launches);
 cudaError_t launch_fill_status(const BatchArgs& a, int status, cudaStream_t s, int* launches);
 
 }  // namespace fjp

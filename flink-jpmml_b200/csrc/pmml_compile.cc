@@ -343,6 +343,65 @@ struct ForestBuilder {
     if (slot < 0) return m;  // field is never supplied -> always UNKNOWN
     thr.push_back({slot, value, strict}); nodes.push_back({(int)thr.size() - 1, t, f, m}); node_slot.push_back(slot); return (int32_t)nodes.size() - 1;
   }
+  // x == v on slot:  (x <= v) and not (x < v)
+  int32_t emit_eq(int slot, double v, int32_t sT, int32_t sF, int32_t sU) {
+    int32_t n2 = add_test(slot, v, true, sF, sT, sU);
+    return add_test(slot, v, false, n2, sF, sU);
+  }
+  // Decision sub-graph for one predicate with three-valued logic: routes to sT / sF / sU (TRUE / FALSE / UNKNOWN).
+  // CompoundPredicate becomes a small automaton over its operands (state = operand index + what was seen so far).
+  int32_t emit_pred(const XNode& p, int32_t sT, int32_t sF, int32_t sU) {
+    if (p.name == "True") return sT;
+    if (p.name == "False") return sF;
+    if (p.name == "SimplePredicate") {
+      sv op = p.attr("operator"); sv fname = p.attr("field"); int slot = b.slot_of(fname);
+      uint8_t dt = b.dict_field(fname).dtype;
+      // thr = -1: "passes whenever present"; the missing successor is the failing branch
+      if (op == "isMissing") { if (slot < 0) return sT; int32_t r = add_test(slot, 0, false, sF, sT, sT); nodes[r].thr = -1; return r; }
+      if (op == "isNotMissing") { if (slot < 0) return sF; int32_t r = add_test(slot, 0, false, sT, sF, sF); nodes[r].thr = -1; return r; }
+      if (dt == DT_STRING || dt == DT_OTHER) unsupported("SimplePredicate on a non-numeric field");
+      double v; if (!parse_in_dtype(dt, p.attr("value"), &v)) unsupported("SimplePredicate value '" + std::string(p.attr("value")) + "' does not parse in the field's dataType");
+      if (op == "lessOrEqual") return add_test(slot, v, false, sT, sF, sU);
+      if (op == "lessThan") return add_test(slot, v, true, sT, sF, sU);
+      if (op == "greaterThan") return add_test(slot, v, false, sF, sT, sU);
+      if (op == "greaterOrEqual") return add_test(slot, v, true, sF, sT, sU);
+      if (op == "equal") return emit_eq(slot, v, sT, sF, sU);
+      if (op == "notEqual") return emit_eq(slot, v, sF, sT, sU);
+      malformed("bad operator " + std::string(op));
+    }
+    if (p.name == "SimpleSetPredicate") {
+      sv fname = p.attr("field"); int slot = b.slot_of(fname); uint8_t dt = b.dict_field(fname).dtype;
+      if (dt == DT_STRING || dt == DT_OTHER) unsupported("SimpleSetPredicate on a non-numeric field");
+      sv bop = p.attr("booleanOperator"); bool in = bop == "isIn"; if (!in && bop != "isNotIn") malformed("bad booleanOperator " + std::string(bop));
+      if (slot < 0) return sU;
+      const XNode* arr = p.child("Array"); std::vector<double> vals;
+      if (arr) for (auto& t : split_array(*arr)) { double v; if (!parse_in_dtype(dt, t, &v)) unsupported("set member does not parse in the field's dataType"); vals.push_back(v); }
+      int32_t hit = in ? sT : sF, miss = in ? sF : sT, next = miss;
+      if (vals.empty()) { int32_t r = add_test(slot, 0, false, miss, miss, sU); nodes[r].thr = -1; return r; }
+      for (size_t k = vals.size(); k-- > 0;) next = emit_eq(slot, vals[k], hit, next, sU);   // membership: a chain of equalities
+      return next;
+    }
+    if (p.name == "CompoundPredicate") {
+      std::vector<const XNode*> ops;
+      for (const XNode* k = p.first; k; k = k->next) if (k->name != "Extension") ops.push_back(k);
+      if (ops.size() < 2) malformed("CompoundPredicate needs two operands");
+      sv bop = p.attr("booleanOperator"); const int n = (int)ops.size();
+      std::map<std::pair<int, int>, int32_t> memo;   // (operand index, state) -> successor
+      std::function<int32_t(int, int)> go = [&](int i, int state) -> int32_t {
+        auto key = std::make_pair(i, state); auto it = memo.find(key); if (it != memo.end()) return it->second;
+        int32_t r;
+        if (bop == "surrogate") r = i == n ? sU : emit_pred(*ops[i], sT, sF, go(i + 1, 0));
+        else if (bop == "and") r = i == n ? (state ? sU : sT) : emit_pred(*ops[i], go(i + 1, state), sF, go(i + 1, 1));      // state: an UNKNOWN was seen
+        else if (bop == "or") r = i == n ? (state ? sU : sF) : emit_pred(*ops[i], sT, go(i + 1, state), go(i + 1, 1));
+        else if (bop == "xor") r = i == n ? (state & 2 ? sU : (state & 1 ? sT : sF))                                          // bit0 parity, bit1 unknown
+                                        : emit_pred(*ops[i], go(i + 1, state ^ 1), go(i + 1, state), go(i + 1, state | 2));
+        else malformed("bad booleanOperator " + std::string(bop));
+        memo[key] = r; return r;
+      };
+      return go(0, 0);
+    }
+    unsupported(std::string(p.name) + " in a TreeModel");
+  }
   int32_t enter(const XNode& n, int32_t last, TreeCtx& cx) {
     auto it = cx.entered.find(&n); if (it != cx.entered.end()) return it->second;
     int32_t r;
@@ -361,7 +420,7 @@ struct ForestBuilder {
       const XNode& kid = *kids[i]; const XNode& p = *pred_of(kid);
       if (p.name == "True") r = enter(kid, last, cx);
       else if (p.name == "False") r = chain(parent, i + 1, last, cx);
-      else if (p.name == "SimplePredicate") {
+      else {
         int32_t s_true = enter(kid, last, cx), s_false = chain(parent, i + 1, last, cx), s_miss;
         switch (cx.mvs) {
           case 0: s_miss = s_false; break;
@@ -372,23 +431,8 @@ struct ForestBuilder {
           case 2: s_miss = last; break;
           default: s_miss = LEAF_NULL; break;
         }
-        sv op = p.attr("operator"); sv fname = p.attr("field"); int slot = b.slot_of(fname);
-        uint8_t dt = b.dict_field(fname).dtype;
-        // thr = -1: "passes whenever present"; the missing successor is the failing branch
-        if (op == "isMissing") { if (slot < 0) r = s_true; else { r = add_test(slot, 0, false, s_false, s_true, s_true); nodes[r].thr = -1; } }
-        else if (op == "isNotMissing") { if (slot < 0) r = s_false; else { r = add_test(slot, 0, false, s_true, s_false, s_false); nodes[r].thr = -1; } }
-        else {
-          if (dt == DT_STRING || dt == DT_OTHER) unsupported("SimplePredicate on a non-numeric field");
-          double v; if (!parse_in_dtype(dt, p.attr("value"), &v)) unsupported("SimplePredicate value '" + std::string(p.attr("value")) + "' does not parse in the field's dataType");
-          if (op == "lessOrEqual") r = add_test(slot, v, false, s_true, s_false, s_miss);
-          else if (op == "lessThan") r = add_test(slot, v, true, s_true, s_false, s_miss);
-          else if (op == "greaterThan") r = add_test(slot, v, false, s_false, s_true, s_miss);
-          else if (op == "greaterOrEqual") r = add_test(slot, v, true, s_false, s_true, s_miss);
-          else if (op == "equal") { int32_t n2 = add_test(slot, v, true, s_false, s_true, s_miss); r = add_test(slot, v, false, n2, s_false, s_miss); }
-          else if (op == "notEqual") { int32_t n2 = add_test(slot, v, true, s_true, s_false, s_miss); r = add_test(slot, v, false, n2, s_true, s_miss); }
-          else malformed("bad operator " + std::string(op));
-        }
-      } else unsupported(std::string(p.name) + " in a TreeModel");
+        r = emit_pred(p, s_true, s_false, s_miss);
+      }
     }
     cx.chained[key] = r; return r;
   }

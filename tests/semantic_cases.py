@@ -48,6 +48,24 @@ def cases():
     #   b == 0 tests use Double.equals: -0.0 != 0.0
     out.append(("tree/equal-missing", doc(AB, tree_model(["a", "b"], eq)), X2, P2, None,
                 [(0, 1.0, 2), (0, 2.0, 3), (0, 3.0, 4), (0, 4.0, 5), (0, 4.0, 5), (0, 4.0, 5), (0, 3.0, 4)]))
+    # compound / set predicates, three-valued logic (strategy none: UNKNOWN counts as "not true")
+    sp = lambda f, op, v=None: f'<SimplePredicate field="{f}" operator="{op}"' + (f' value="{v}"/>' if v is not None else '/>')
+    comp = ('<Node id="1"><True/>'
+            f'<Node id="2" score="1"><CompoundPredicate booleanOperator="and">{sp("a", "lessThan", 1)}{sp("b", "lessThan", 1)}</CompoundPredicate></Node>'
+            f'<Node id="3" score="2"><CompoundPredicate booleanOperator="or">{sp("a", "greaterThan", 5)}{sp("b", "isMissing")}</CompoundPredicate></Node>'
+            '<Node id="4" score="3"><SimpleSetPredicate field="a" booleanOperator="isIn"><Array n="2" type="real">2 3</Array></SimpleSetPredicate></Node>'
+            f'<Node id="5" score="4"><CompoundPredicate booleanOperator="surrogate">{sp("a", "greaterOrEqual", 4)}{sp("b", "greaterOrEqual", 0)}</CompoundPredicate></Node>'
+            f'<Node id="6" score="5"><CompoundPredicate booleanOperator="xor">{sp("a", "greaterThan", 0)}{sp("b", "greaterThan", 0)}</CompoundPredicate></Node>'
+            '<Node id="7" score="6"><True/></Node></Node>')
+    Xc, Pc = _rows((0, 0), (0, 2), (0, None), (None, 0), (3, 5), (6, 2), (4.5, -1), (1, -1), (-1, 2), (1, 1), (None, None), (None, 2))
+    out.append(("tree/compound-and-set", doc(AB, tree_model(["a", "b"], comp)), Xc, Pc, None,
+                [(0, 1.0, 2), (0, 5.0, 6), (0, 2.0, 3), (0, 4.0, 5), (0, 3.0, 4), (0, 2.0, 3), (0, 4.0, 5), (0, 5.0, 6), (0, 5.0, 6), (0, 6.0, 7),
+                 (0, 2.0, 3), (0, 4.0, 5)]))
+    notin = ('<Node id="1"><True/><Node id="2" score="1"><SimpleSetPredicate field="a" booleanOperator="isNotIn"><Array n="3" type="real">1 2 3</Array></SimpleSetPredicate></Node>'
+             '<Node id="3" score="2"><True/></Node></Node>')
+    Xn, Pn = _rows((2, 0), (2.5, 0), (None, 0))
+    out.append(("tree/isNotIn-nullPrediction", doc(AB, tree_model(["a", "b"], notin, strategy="nullPrediction")), Xn, Pn, None,
+                [(0, 2.0, 3), (0, 1.0, 2), (3, None, None)]))
     # classification tree: labels become doubles only when they parse; integer-typed target never extracts
     cls = ('<Node id="1"><True/><Node id="2" score="7"><SimplePredicate field="a" operator="lessThan" value="0"/></Node>'
            '<Node id="3" score="setosa"><True/></Node></Node>')

@@ -72,10 +72,10 @@ def test_compiled_layouts(capi, gen):
     assert "layers=2" in capi.compile_model(pm).describe
 
 
-def test_unsupported_features_are_load_errors_not_wrong_answers(capi):
-    from hand_pmml import doc, tree_model, AB
-    compound = ('<Node id="1" score="1"><True/><Node id="2" score="2"><CompoundPredicate booleanOperator="and">'
-                '<SimplePredicate field="a" operator="lessThan" value="1"/><SimplePredicate field="b" operator="lessThan" value="1"/>'
-                '</CompoundPredicate></Node></Node>')
-    with pytest.raises(capi.ModelLoadingException, match="unsupported"):
-        capi.compile_model(doc(AB, tree_model(["a", "b"], compound)))
+def test_unsupported_features_are_load_errors_not_wrong_answers(capi, gen):
+    pm, _ = gen.gbt_pmml(T=3, depth=2, F=4, seed=1)
+    for bad in (pm.replace(b'multipleModelMethod="sum"', b'multipleModelMethod="modelChain"'),
+                pm.replace(b'multipleModelMethod="sum"', b'multipleModelMethod="median"'),
+                pm.replace(b'missingValueStrategy="defaultChild"', b'missingValueStrategy="weightedConfidence"')):
+        with pytest.raises(capi.ModelLoadingException, match="unsupported"):
+            capi.compile_model(bad)

@@ -144,3 +144,29 @@ def test_empty_model_and_size_mismatch(engine, gen):
     r = engine.score(m, np.ones((3, 3)))
     assert (r["status"] == 1).all()
     assert engine.launch_count > 0
+
+
+def test_sparse_csr_ingest_matches_dense_path(engine, oracle, gen):
+    """SparseVector batches as CSR: expanded on the device, same answers as the dense + present-bits path."""
+    pm, arr = gen.gbt_pmml(T=40, depth=6, F=70, seed=31)
+    m = engine.compile(pm)
+    rng = np.random.default_rng(3)
+    n, F = 30000, 70
+    X, pres, pb = gen.events(n, F, 32, 0.6)            # 60 % of the slots absent
+    X[pres & (rng.random(X.shape) < 0.1)] = 0.0         # explicit zeros stay present
+    counts = pres.sum(1)
+    row_ptr = np.concatenate([[0], np.cumsum(counts)])
+    rows, cols = np.nonzero(pres)
+    indices, values = cols.astype(np.int32), X[rows, cols]
+    # out-of-range indices are ignored (T/QuickDataStreamSpec.scala:89-93 builds such a vector)
+    indices = np.concatenate([indices, [F + 5, -1]]); values = np.concatenate([values, [9.0, 9.0]]); row_ptr[-1] += 2
+    dense = engine.score(m, X, pb)
+    for rep in (None, 0.25):
+        dense = engine.score(m, X, pb, rep)
+        sparse = engine.score_sparse(m, row_ptr, indices, values, F, rep)
+        assert np.array_equal(dense["status"], sparse["status"]) and np.array_equal(dense["score"], sparse["score"])
+    o = oracle.OracleModel(pm).predict(X[:4000], pb[:4000], 0.25, nthreads=8)
+    assert np.array_equal(sparse["score"][:4000], o["score"])
+    empty = engine.score_sparse(m, np.zeros(4, dtype=np.int64), np.zeros(0, dtype=np.int32), np.zeros(0), F)   # three all-missing rows
+    assert np.array_equal(empty["score"], engine.score(m, np.zeros((3, F)), np.zeros((3, 3), dtype=np.uint32))["score"])
+    assert (engine.score_sparse(m, row_ptr, indices, values, F + 1)["status"] == 1).all()                        # size mismatch
