@@ -406,3 +406,12 @@ int fjp_wait(fjp_engine* e, int ticket) {
 }
 
 }  // extern "C"
+
+// ---- internal accessors for translation units that do not see the handle layouts (declared in engine_internal.h)
+namespace fjp {
+const DeviceModel* internal_device_model(const fjp_model* m) { return (m && m->d_blob) ? &m->dev : nullptr; }
+int internal_model_device(const fjp_model* m) { return m ? m->device : -1; }
+int internal_model_fields(const fjp_model* m) { return m ? m->cm.dev.F : -1; }
+void internal_count_launches(fjp_engine* e, int launches) { if (e) e->launches += launches; }
+void internal_set_error(const char* msg) { g_last_error = msg; }
+}  // namespace fjp

@@ -119,6 +119,24 @@ int fjp_score_batch_ex(fjp_engine* e, fjp_model* m, const double* X, const uint3
  * cross PCIe.  Indices outside [0, vec_size) are ignored, as in the reference.  Host pointers, synchronous. */
 int fjp_score_sparse(fjp_engine* e, fjp_model* m, const int64_t* row_ptr, const int32_t* indices, const double* values,
                      const double* replace, long n, int vec_size, double* score, uint8_t* status, int32_t* aux);
+/* Sparse scoring that allocates nothing.  [No counterpart in the reference.]
+ * For callers that may not touch the device allocator while they score: a subtask that shares its GPU with other jobs
+ * under a fixed memory budget (a cudaMalloc may fail, or stall the whole device), or one on a latency-bound path.  The
+ * other host-pointer entry points grow their staging arenas with cudaMalloc / cudaFree on demand; this one never does.
+ *   - every pointer is a DEVICE pointer owned by the caller: CSR inputs (row_ptr n+1 entries, indices, values as for
+ *     fjp_score_sparse) and the outputs score[n], status[n];
+ *   - the dense rows the CSR input is expanded into live in an area of FJP_NOALLOC_SCRATCH_BYTES built into the library
+ *     (present on every GPU that loads it, until exit).  The call is refused, with a message in fjp_last_error(), when
+ *     n * (vec_size*8 + ceil(vec_size/32)*4) exceeds it, when vec_size is not the model's field count, or without a model;
+ *   - the area is shared by all calls and keeps the previous call's contents (nothing needs clearing: each call rewrites
+ *     what it reads).  Calls whose GPU work overlaps -- two streams, two threads -- corrupt each other: serialise them;
+ *   - the first call on a device also looks up the area's device address (once per device): make it at start-up, before
+ *     any stream capture on that device;
+ *   - asynchronous on `cuda_stream` (a cudaStream_t; NULL = the default stream). */
+#define FJP_NOALLOC_SCRATCH_BYTES (8u << 20)
+int fjp_score_sparse_noalloc(fjp_engine* e, fjp_model* m, const int64_t* d_row_ptr, const int32_t* d_indices,
+                             const double* d_values, long n, int vec_size, double* d_score, uint8_t* d_status,
+                             void* cuda_stream);
 /* Device-pointer variant: asynchronous on `cuda_stream` (a cudaStream_t, NULL = the engine's stream). */
 int fjp_score_device(fjp_engine* e, fjp_model* m, const double* dX, const uint32_t* dpresent, const double* dreplace,
                      long n, int vec_size, double* dscore, uint8_t* dstatus, int32_t* daux, void* cuda_stream);
