@@ -94,11 +94,13 @@ def _lib():
         "fjh_eval_function_open": (vp, [vp, cp, i32, cp, sz]),
         "fjh_eval_function_model_name": (cp, [vp]),
         "fjh_eval_function_process": (i32, [vp, vp, i32, vp, i32, dbl]),
+        "fjh_eval_function_process_dense": (i32, [vp, vp, lng, i32]),
         "fjh_eval_function_flush": (i32, [vp]),
         "fjh_eval_function_poll": (lng, [vp, vp, vp, lng]),
         "fjh_eval_function_close": (None, [vp]),
         "fjh_cofunction_create": (vp, [vp, i32]),
         "fjh_cofunction_process_event": (i32, [vp, cp, vp, i32, vp, i32, dbl, cp, sz]),
+        "fjh_cofunction_process_dense": (i32, [vp, C.POINTER(cp), vp, vp, lng, i32, cp, sz]),
         "fjh_cofunction_process_control": (i32, [vp, i32, cp, i64, cp, i64]),
         "fjh_cofunction_flush": (i32, [vp, cp, sz]),
         "fjh_cofunction_poll": (lng, [vp, vp, vp, lng]),
@@ -116,8 +118,8 @@ def _lib():
 
 
 HOST_EXPORTS = ["fjh_model_id_parse", "fjh_model_id_hash", "fjh_predict", "fjh_eval_function_open", "fjh_eval_function_model_name",
-                "fjh_eval_function_process", "fjh_eval_function_flush", "fjh_eval_function_poll", "fjh_eval_function_close",
-                "fjh_cofunction_create", "fjh_cofunction_process_event", "fjh_cofunction_process_control", "fjh_cofunction_flush",
+                "fjh_eval_function_process", "fjh_eval_function_process_dense", "fjh_eval_function_flush", "fjh_eval_function_poll", "fjh_eval_function_close",
+                "fjh_cofunction_create", "fjh_cofunction_process_event", "fjh_cofunction_process_dense", "fjh_cofunction_process_control", "fjh_cofunction_flush",
                 "fjh_cofunction_poll", "fjh_cofunction_snapshot", "fjh_cofunction_restore", "fjh_cofunction_metadata_size",
                 "fjh_cofunction_cached_models", "fjh_cofunction_destroy"]
 
@@ -230,6 +232,10 @@ class EvaluationFunction:
         vals, size, idx, nnz = _vec_args(vector)
         _raise(_lib().fjh_eval_function_process(self._h, capi._ptr(vals), size, capi._ptr(idx), nnz, math.nan if replaceNan is None else float(replaceNan)))
 
+    def processDense(self, X):
+        X = np.ascontiguousarray(X, dtype=np.float64)
+        _raise(_lib().fjh_eval_function_process_dense(self._h, capi._ptr(X), X.shape[0], X.shape[1]))
+
     def flush(self):
         _raise(_lib().fjh_eval_function_flush(self._h))
 
@@ -254,6 +260,13 @@ class EvaluationCoFunction:
         rc = _lib().fjh_cofunction_process_event(self._h, modelId.encode(), capi._ptr(vals), size, capi._ptr(idx), nnz,
                                                   math.nan if replaceNan is None else float(replaceNan), err, 512)
         _raise(rc, err.value)
+
+    def processDense1(self, ids: Sequence[str], id_index, X):
+        X = np.ascontiguousarray(X, dtype=np.float64)
+        idx = np.ascontiguousarray(id_index, dtype=np.int32)
+        arr = (C.c_char_p * len(ids))(*[i.encode() for i in ids])
+        err = C.create_string_buffer(512)
+        _raise(_lib().fjh_cofunction_process_dense(self._h, arr, capi._ptr(idx), capi._ptr(X), X.shape[0], X.shape[1], err, 512), err.value)
 
     def processElement2(self, msg):
         if isinstance(msg, AddMessage):

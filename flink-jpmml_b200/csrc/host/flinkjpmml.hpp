@@ -21,6 +21,7 @@
 #pragma once
 #include <cmath>
 #include <cstdint>
+#include <future>
 #include <map>
 #include <memory>
 #include <optional>
@@ -127,10 +128,14 @@ class MicroBatch {
   ~MicroBatch();
   MicroBatch(const MicroBatch&) = delete;
   bool full() const { return n_ >= cap_; }
+  int fields() const { return F_; }
+  int capacity() const { return cap_; }
   int size() const { return n_; }
   int append(const Vector& v, std::optional<double> replaceNan);   // returns the row index
+  int append_dense(const double* x);                                // DenseVector payload, no replaceNan
   void clear() { n_ = 0; any_sparse_ = false; any_replace_ = false; }
   int score(fjp_engine* e, fjp_model* m);                         // fills score()/status()
+  int submit(fjp_engine* e, fjp_model* m, int* ticket);           // asynchronous: fjp_submit; results valid after fjp_wait(ticket)
   const double* scores() const { return score_; }
   const uint8_t* statuses() const { return status_; }
  private:
@@ -147,13 +152,17 @@ class EvaluationFunction {
   const PmmlModel& evaluator() const { return model_; }
   // buffer one event; predictions come back through drain() in arrival order
   void processElement(const Vector& v, std::optional<double> replaceNan = std::nullopt);
+  void processDense(const double* x, int size);           // same for a DenseVector payload given in place
   void flush();
   std::vector<Prediction> drain() { std::vector<Prediction> r; r.swap(out_); return r; }
   void close() { flush(); }
  private:
+  // two pinned micro-batches: while the GPU scores one, the task thread packs the other (fjp_submit / fjp_wait)
   fjp_engine* engine_; ModelReader reader_; int max_batch_; PmmlModel model_;
-  std::unique_ptr<MicroBatch> batch_; std::vector<Prediction> out_;
-  std::vector<int> pending_;   // per buffered event: row in batch_, or -1 = size mismatch (EmptyScore at once)
+  std::unique_ptr<MicroBatch> batch_[2]; int cur_ = 0; int ticket_[2] = {-1, -1}; std::vector<Prediction> out_;
+  std::vector<int> pending_[2];   // per buffered event: row in its batch, or -1 = size mismatch (EmptyScore)
+  void submit_current();          // hand the current batch to the GPU, then collect the older one
+  void collect(int b);            // wait for batch b and emit its predictions in arrival order
 };
 
 // ---------------------------------------------------------------------------------------- dynamic operator
@@ -164,6 +173,9 @@ class EvaluationCoFunction {
   void initializeState(const std::vector<Metadata>& restored);   // union of the restored maps (:68-83)
   Metadata snapshotState();                                      // flushes, then returns the metadata (:63-66)
   void processElement1(const std::string& modelId, const Vector& v, std::optional<double> replaceNan = std::nullopt);
+  void processDense1(const std::string& modelId, const double* x, int size);
+  // n dense events in arrival order, event i addressed to ids[id_index[i]]; ids are resolved once per call and flush
+  void processDenseBatch(const char* const* ids, const int32_t* id_index, const double* X, long n, int size);
   void processElement2(const ServingMessage& control);           // manageModels then manageMetadata (:56-61)
   void flush();
   std::vector<Prediction> drain() { std::vector<Prediction> r; r.swap(out_); return r; }
@@ -175,8 +187,16 @@ class EvaluationCoFunction {
   struct Pending { int bucket; int row; };
   struct Bucket { PmmlModel model; std::unique_ptr<MicroBatch> batch; };
   fjp_engine* engine_; int max_batch_; Metadata metadata_;
-  std::vector<Bucket> buckets_; std::vector<Pending> pending_; std::vector<Prediction> out_;
+  std::vector<Bucket> buckets_; std::vector<Pending> pending_; std::vector<Prediction> out_; uint64_t flushes_ = 0;
+  // id string -> model bound to it right now; dropped on every control message and whenever the table changes
+  std::unordered_map<std::string, PmmlModel> resolved_; uint64_t resolved_epoch_ = ~0ull;
+  std::vector<std::unique_ptr<MicroBatch>> pool_;   // pinned micro-batches are recycled: cudaHostAlloc is far too slow for the event path
+  // Add starts the model load in the background; its outcome (model or ModelLoadingException) is consumed by the first
+  // event for that id, which is where the reference loads -- and fails -- too (T/RichConnectedStreamSpec.scala:288-300)
+  std::map<ModelId, std::shared_future<PmmlModel>> loading_;
   int bucket_for(const PmmlModel& m);
+  PmmlModel resolve(const std::string& modelId);   // servingModels.getOrElse(id.hashCode, fromMetadata(id))
+  void enqueue(const PmmlModel& model, const Vector* v, const double* dense, int size, std::optional<double> replaceNan);
 };
 
 }  // namespace flinkjpmml

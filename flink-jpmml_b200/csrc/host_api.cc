@@ -1,5 +1,6 @@
 // host_api.cc -- implementation of host/flinkjpmml.hpp and the extern "C" operator-emulator entry points declared in
 // include/fjpmml_host.h (what pytest drives in place of a Flink mini-cluster; T/utils/FlinkTestKits.scala:32-67).
+#include <algorithm>
 #include <cstring>
 #include <fstream>
 #include <limits>
@@ -107,6 +108,17 @@ int MicroBatch::append(const Vector& v, std::optional<double> replaceNan) {
   if (replaceNan) any_replace_ = true;
   return r;
 }
+int MicroBatch::append_dense(const double* x) {
+  int r = n_++;
+  memcpy(X_ + (size_t)r * F_, x, (size_t)F_ * 8);
+  uint32_t* p = present_ + (size_t)r * W_;
+  for (int w = 0; w < W_; w++) p[w] = 0xFFFFFFFFu;
+  replace_[r] = std::numeric_limits<double>::quiet_NaN();
+  return r;
+}
+int MicroBatch::submit(fjp_engine* e, fjp_model* m, int* ticket) {
+  return fjp_submit(e, m, X_, any_sparse_ ? present_ : nullptr, any_replace_ ? replace_ : nullptr, n_, F_, score_, status_, nullptr, ticket);
+}
 int MicroBatch::score(fjp_engine* e, fjp_model* m) {
   if (n_ == 0) return 0;
   return fjp_score_batch(e, m, X_, any_sparse_ ? present_ : nullptr, any_replace_ ? replace_ : nullptr, n_, F_, score_, status_, nullptr);
@@ -121,19 +133,35 @@ static Prediction make_prediction(uint8_t status, double score) {
 // ---------------------------------------------------------------------------------------- EvaluationFunction
 void EvaluationFunction::open() {
   model_ = PmmlModel::fromReader(engine_, reader_);   // ModelLoadingException propagates: the job fails (EvaluationFunction.scala:37-40)
-  batch_ = std::make_unique<MicroBatch>(model_.activeFields(), max_batch_);
+  for (auto& b : batch_) b = std::make_unique<MicroBatch>(model_.activeFields(), max_batch_);
 }
 void EvaluationFunction::processElement(const Vector& v, std::optional<double> replaceNan) {
   if (model_.isEmpty()) open();   // `lazy val evaluator`
-  if (v.size != model_.activeFields()) pending_.push_back(-1);
-  else pending_.push_back(batch_->append(v, replaceNan));
-  if (batch_->full()) flush();
+  if (v.size != model_.activeFields()) pending_[cur_].push_back(-1);
+  else pending_[cur_].push_back(batch_[cur_]->append(v, replaceNan));
+  if (batch_[cur_]->full() || (int)pending_[cur_].size() >= max_batch_) submit_current();
+}
+void EvaluationFunction::processDense(const double* x, int size) {
+  if (model_.isEmpty()) open();
+  if (size != model_.activeFields()) pending_[cur_].push_back(-1);
+  else pending_[cur_].push_back(batch_[cur_]->append_dense(x));
+  if (batch_[cur_]->full() || (int)pending_[cur_].size() >= max_batch_) submit_current();
+}
+void EvaluationFunction::collect(int b) {
+  if (ticket_[b] >= 0) { if (fjp_wait(engine_, ticket_[b]) != 0) throw std::runtime_error(fjp_last_error()); ticket_[b] = -1; }
+  for (int r : pending_[b]) out_.push_back(r < 0 ? make_prediction(FJP_ST_SIZE, 0) : make_prediction(batch_[b]->statuses()[r], batch_[b]->scores()[r]));
+  pending_[b].clear(); batch_[b]->clear();
+}
+void EvaluationFunction::submit_current() {
+  const int b = cur_;
+  if (batch_[b]->size() > 0 && batch_[b]->submit(engine_, model_.handle(), &ticket_[b]) != 0) throw std::runtime_error(fjp_last_error());
+  collect(b ^ 1);      // the older batch: its results come first, and its buffer becomes the one being packed
+  cur_ = b ^ 1;
 }
 void EvaluationFunction::flush() {
-  if (pending_.empty()) return;
-  if (batch_->score(engine_, model_.handle()) != 0) throw std::runtime_error(fjp_last_error());
-  for (int r : pending_) out_.push_back(r < 0 ? make_prediction(FJP_ST_SIZE, 0) : make_prediction(batch_->statuses()[r], batch_->scores()[r]));
-  pending_.clear(); batch_->clear();
+  if (model_.isEmpty()) return;
+  if (!pending_[cur_].empty()) submit_current();
+  collect(cur_ ^ 1);   // whatever is still in flight (submit_current already collected the batch before it)
 }
 
 // ---------------------------------------------------------------------------------------- EvaluationCoFunction
@@ -149,55 +177,115 @@ PmmlModel EvaluationCoFunction::fromMetadata(const std::string& modelId) {
   ModelId id = ModelId::fromIdentifier(modelId);                       // WrongModelIdFormat is not caught: job-fatal
   auto it = metadata_.find(id);
   if (it == metadata_.end()) return PmmlModel::empty();
-  PmmlModel loaded = loadModel(it->second.path);                       // lazy load on the first event for this id
+  PmmlModel loaded;
+  auto lf = loading_.find(id);
+  if (lf != loading_.end()) { auto fut = lf->second; loading_.erase(lf); loaded = fut.get(); }   // background load started by the Add (rethrows its failure)
+  else loaded = loadModel(it->second.path);                            // e.g. after a checkpoint restore: load on the first event
   fjp_table_add(engine_, id.name.c_str(), id.version, loaded.handle()); // servingModels += (id -> model), keyed by the full id
   return loaded;
 }
 
 int EvaluationCoFunction::bucket_for(const PmmlModel& m) {
   for (size_t i = 0; i < buckets_.size(); i++) if (buckets_[i].model.handle() == m.handle()) return (int)i;
-  buckets_.push_back(Bucket{m, std::make_unique<MicroBatch>(m.activeFields(), max_batch_)});
+  std::unique_ptr<MicroBatch> mb;
+  for (size_t i = 0; i < pool_.size(); i++)
+    if (pool_[i]->fields() == m.activeFields() && pool_[i]->capacity() == max_batch_) { mb = std::move(pool_[i]); pool_.erase(pool_.begin() + i); break; }
+  if (!mb) mb = std::make_unique<MicroBatch>(m.activeFields(), max_batch_);
+  buckets_.push_back(Bucket{m, std::move(mb)});
   return (int)buckets_.size() - 1;
 }
 
-void EvaluationCoFunction::processElement1(const std::string& modelId, const Vector& v, std::optional<double> replaceNan) {
-  // servingModels.getOrElse(event.modelId.hashCode, fromMetadata(event.modelId))   (S/package.scala:62)
+PmmlModel EvaluationCoFunction::resolve(const std::string& modelId) {
+  if (!engine_) throw std::runtime_error("no engine: scoring needs a CUDA device (there is no CPU path)");
+  const uint64_t epoch = fjp_table_epoch(engine_);
+  if (epoch != resolved_epoch_) { resolved_.clear(); resolved_epoch_ = epoch; }
+  auto hit = resolved_.find(modelId);
+  if (hit != resolved_.end()) return hit->second;
+  // the reference looks the cache up by the raw id's hashCode first; an id that was never parsed cannot be cached,
+  // so parsing first is equivalent except that a malformed id fails here instead of in fromMetadata -- same outcome
+  ModelId id = ModelId::fromIdentifier(modelId);
   PmmlModel model;
-  fjp_model* cached = nullptr;
-  {
-    // the reference looks the cache up by the raw id's hashCode first; an id that was never parsed cannot be cached,
-    // so parsing first is equivalent except that a malformed id fails here instead of in fromMetadata -- same outcome
-    ModelId id = ModelId::fromIdentifier(modelId);
-    if (!engine_) throw std::runtime_error("no engine: scoring needs a CUDA device (there is no CPU path)");
-    cached = fjp_table_get(engine_, id.name.c_str(), id.version);
-  }
-  if (cached) model = PmmlModel(engine_, cached); else model = fromMetadata(modelId);
-  if (model.isEmpty()) { pending_.push_back({-1, FJP_ST_NOMODEL}); }
-  else if (v.size != model.activeFields()) { pending_.push_back({-1, FJP_ST_SIZE}); }
+  if (fjp_model* cached = fjp_table_get(engine_, id.name.c_str(), id.version)) model = PmmlModel(engine_, cached);
+  else model = fromMetadata(modelId);
+  if (!model.isEmpty()) { resolved_epoch_ = fjp_table_epoch(engine_); resolved_[modelId] = model; }   // empty bindings are not remembered
+  return model;
+}
+
+void EvaluationCoFunction::enqueue(const PmmlModel& model, const Vector* v, const double* dense, int size, std::optional<double> replaceNan) {
+  if (model.isEmpty()) pending_.push_back({-1, FJP_ST_NOMODEL});
+  else if (size != model.activeFields()) pending_.push_back({-1, FJP_ST_SIZE});
   else {
     int b = bucket_for(model);
-    int row = buckets_[b].batch->append(v, replaceNan);
+    int row = v ? buckets_[b].batch->append(*v, replaceNan) : buckets_[b].batch->append_dense(dense);
     pending_.push_back({b, row});
     if (buckets_[b].batch->full()) flush();
   }
   if ((int)pending_.size() >= max_batch_) flush();
 }
 
+void EvaluationCoFunction::processElement1(const std::string& modelId, const Vector& v, std::optional<double> replaceNan) {
+  // servingModels.getOrElse(event.modelId.hashCode, fromMetadata(event.modelId))   (S/package.scala:62)
+  enqueue(resolve(modelId), &v, nullptr, v.size, replaceNan);
+}
+void EvaluationCoFunction::processDense1(const std::string& modelId, const double* x, int size) {
+  enqueue(resolve(modelId), nullptr, x, size, std::nullopt);
+}
+
+void EvaluationCoFunction::processDenseBatch(const char* const* ids, const int32_t* id_index, const double* X, long n, int size) {
+  int n_ids = 0; for (long i = 0; i < n; i++) n_ids = std::max(n_ids, id_index[i] + 1);
+  // per id of this call: bucket (>= 0), -1 = empty model, -2 = size mismatch, -3 = not looked at yet
+  std::vector<int> where(n_ids, -3); uint64_t seen_flush = flushes_;
+  for (long i = 0; i < n; i++) {
+    const int k = id_index[i];
+    if (seen_flush != flushes_) { std::fill(where.begin(), where.end(), -3); seen_flush = flushes_; }   // a flush dropped the buckets
+    int w = where[k];
+    if (w == -3) {
+      PmmlModel model = resolve(ids[k]);
+      w = model.isEmpty() ? -1 : (size != model.activeFields() ? -2 : bucket_for(model));
+      where[k] = w;
+    }
+    if (w < 0) pending_.push_back({-1, w == -1 ? FJP_ST_NOMODEL : FJP_ST_SIZE});
+    else {
+      pending_.push_back({w, buckets_[w].batch->append_dense(X + i * (long)size)});
+      if (buckets_[w].batch->full()) flush();
+    }
+    if ((int)pending_.size() >= max_batch_) flush();
+  }
+}
+
 void EvaluationCoFunction::processElement2(const ServingMessage& control) {
   // manageModels first, then manageMetadata (EvaluationCoFunction.scala:56-61, Appendix B of SURVEY.md)
   if (control.kind == ServingMessage::Del && engine_) fjp_table_del(engine_, control.name.c_str(), control.version);
+  const bool known = metadata_.count(control.modelId()) != 0;
   metadata_ = MetadataManager::apply(control, metadata_);
+  resolved_.clear();   // bindings are looked up again after any control message
+  if (control.kind == ServingMessage::Del) loading_.erase(control.modelId());
+  else if (!known && engine_) {   // a new id: parse + compile + upload off the task thread
+    fjp_engine* eng = engine_; std::string path = control.path;
+    loading_[control.modelId()] = std::async(std::launch::async, [eng, path] { return PmmlModel::fromReader(eng, ModelReader(path)); }).share();
+  }
   // buffered events keep the model they were bound to (each bucket holds a reference), so nothing is flushed here
 }
 
 void EvaluationCoFunction::flush() {
   if (pending_.empty()) return;
-  for (auto& b : buckets_) if (b.batch->size() && b.batch->score(engine_, b.model.handle()) != 0) throw std::runtime_error(fjp_last_error());
+  // every model's bucket is its own submission; up to fjp_max_inflight() of them overlap on the GPU
+  std::vector<int> tickets; const int maxfly = fjp_max_inflight(); size_t waited = 0;
+  for (auto& b : buckets_) {
+    if (!b.batch->size()) continue;
+    if ((int)(tickets.size() - waited) >= maxfly) { if (fjp_wait(engine_, tickets[waited++]) != 0) throw std::runtime_error(fjp_last_error()); }
+    int t = -1;
+    if (b.batch->submit(engine_, b.model.handle(), &t) != 0) throw std::runtime_error(fjp_last_error());
+    tickets.push_back(t);
+  }
+  for (; waited < tickets.size(); waited++) if (fjp_wait(engine_, tickets[waited]) != 0) throw std::runtime_error(fjp_last_error());
   for (auto& p : pending_) {
     if (p.bucket < 0) out_.push_back(make_prediction((uint8_t)p.row, 0));
     else out_.push_back(make_prediction(buckets_[p.bucket].batch->statuses()[p.row], buckets_[p.bucket].batch->scores()[p.row]));
   }
-  pending_.clear(); buckets_.clear();   // dropping the buckets releases models deleted in the meantime
+  pending_.clear(); flushes_++;
+  for (auto& b : buckets_) { b.batch->clear(); if (pool_.size() < 64) pool_.push_back(std::move(b.batch)); }
+  buckets_.clear();   // dropping the buckets releases models deleted in the meantime
 }
 
 }  // namespace flinkjpmml
@@ -255,6 +343,9 @@ const char* fjh_eval_function_model_name(fjh_eval_function* h) { static thread_l
 int fjh_eval_function_process(fjh_eval_function* h, const double* values, int size, const int* indices, int nnz, double replace_nan) {
   return guarded(nullptr, 0, [&] { h->op->processElement(make_vector(values, size, indices, nnz), opt(replace_nan)); });
 }
+int fjh_eval_function_process_dense(fjh_eval_function* h, const double* X, long n, int size) {
+  return guarded(nullptr, 0, [&] { for (long i = 0; i < n; i++) h->op->processDense(X + i * (long)size, size); });
+}
 int fjh_eval_function_flush(fjh_eval_function* h) { return guarded(nullptr, 0, [&] { h->op->flush(); }); }
 long fjh_eval_function_poll(fjh_eval_function* h, double* scores, uint8_t* status, long cap) {
   static std::unordered_map<fjh_eval_function*, std::vector<Prediction>> bufs;
@@ -268,6 +359,10 @@ fjh_cofunction* fjh_cofunction_create(fjp_engine* e, int max_batch) {
 int fjh_cofunction_process_event(fjh_cofunction* h, const char* model_id, const double* values, int size, const int* indices, int nnz,
                                  double replace_nan, char* err, size_t errcap) {
   return guarded(err, errcap, [&] { h->op->processElement1(model_id, make_vector(values, size, indices, nnz), opt(replace_nan)); });
+}
+int fjh_cofunction_process_dense(fjh_cofunction* h, const char* const* ids, const int32_t* id_index, const double* X, long n, int size,
+                                 char* err, size_t errcap) {
+  return guarded(err, errcap, [&] { h->op->processDenseBatch(ids, id_index, X, n, size); });
 }
 int fjh_cofunction_process_control(fjh_cofunction* h, int is_add, const char* name, int64_t version, const char* path, int64_t occurred_on) {
   return guarded(nullptr, 0, [&] { h->op->processElement2(is_add ? AddMessage(name, version, path ? path : "", occurred_on) : DelMessage(name, version, occurred_on)); });

@@ -40,6 +40,8 @@ int fjh_predict(fjp_engine* e, fjp_model* m, const double* values, int size, con
 fjh_eval_function* fjh_eval_function_open(fjp_engine* e, const char* path, int max_batch, char* err, size_t errcap);
 const char* fjh_eval_function_model_name(fjh_eval_function* op);
 int fjh_eval_function_process(fjh_eval_function* op, const double* values, int size, const int* indices, int nnz, double replace_nan);
+/* n DenseVector events of `size` values each, in arrival order (the task thread's inner loop without per-event FFI). */
+int fjh_eval_function_process_dense(fjh_eval_function* op, const double* X, long n, int size);
 int fjh_eval_function_flush(fjh_eval_function* op);
 long fjh_eval_function_poll(fjh_eval_function* op, double* scores, uint8_t* status, long cap);
 void fjh_eval_function_close(fjh_eval_function* op);
@@ -56,6 +58,9 @@ void fjh_eval_function_close(fjh_eval_function* op);
 fjh_cofunction* fjh_cofunction_create(fjp_engine* e, int max_batch);
 int fjh_cofunction_process_event(fjh_cofunction* op, const char* model_id, const double* values, int size, const int* indices, int nnz,
                                  double replace_nan, char* err, size_t errcap);
+/* n DenseVector events in arrival order; event i carries the model id string ids[id_index[i]]. */
+int fjh_cofunction_process_dense(fjh_cofunction* op, const char* const* ids, const int32_t* id_index, const double* X, long n, int size,
+                                 char* err, size_t errcap);
 int fjh_cofunction_process_control(fjh_cofunction* op, int is_add, const char* name, int64_t version, const char* path, int64_t occurred_on);
 int fjh_cofunction_flush(fjh_cofunction* op, char* err, size_t errcap);
 long fjh_cofunction_poll(fjh_cofunction* op, double* scores, uint8_t* status, long cap);

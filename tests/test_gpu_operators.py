@@ -197,3 +197,43 @@ def test_hot_swap_under_load(engine, gen, oracle, tmp_path):
     op.flush()
     assert op.collect() == expected
     op.close()
+
+
+def test_double_buffered_operator_keeps_order_over_many_batches(engine, gen, oracle):
+    """Fixed-model operator with small pinned micro-batches: 10 000 events cross ~40 submit/wait hand-overs; the output
+    must be the oracle's answers in arrival order, wrong-size vectors included."""
+    fn = api.EvaluationFunction(engine, KMEANS, max_batch=256)
+    X = gen.iris_events(10000)
+    o = oracle.OracleModel(open(KMEANS, "rb").read()).predict(X)
+    fn.processDense(X[:5000])
+    fn.processElement(api.DenseVector([1.0, 2.0]))          # size mismatch in the middle of the stream
+    fn.processDense(X[5000:])
+    fn.flush()
+    out = fn.collect()
+    exp = [api.Prediction.of(o["score"][i], o["status"][i]) for i in range(10000)]
+    assert out == exp[:5000] + [EMPTY] + exp[5000:]
+    fn.close()
+
+
+def test_dynamic_operator_bulk_ingest(engine, gen, oracle, tmp_path):
+    pms = [gen.rf_pmml(T=10, depth=4, F=16, n_labels=3, seed=50 + k)[0] for k in range(3)]
+    names = [str(uuid.UUID(int=500 + k)) for k in range(3)]
+    op = api.EvaluationCoFunction(engine, max_batch=512)
+    for k, pm in enumerate(pms):
+        p = tmp_path / f"d{k}.pmml"; p.write_bytes(pm)
+        op.processElement2(api.AddMessage(names[k], 1, str(p)))
+    rng = np.random.default_rng(1)
+    X = rng.standard_normal((5000, 16)); idx = rng.integers(0, 4, 5000)
+    ids = [f"{n}_1" for n in names] + [f"{names[0]}_9"]       # the 4th id is unknown -> EmptyScore
+    op.processDense1(ids, idx, X)
+    op.flush()
+    out = op.collect()
+    exp = []
+    oms = [oracle.OracleModel(pm) for pm in pms]
+    for i in range(5000):
+        if idx[i] == 3: exp.append(EMPTY)
+        else:
+            r = oms[idx[i]].predict(X[i:i + 1]); exp.append(api.Prediction.of(r["score"][0], r["status"][0]))
+    assert out == exp
+    op.close()
+    for n in names: engine.table_del(n, 1)
