@@ -170,3 +170,23 @@ def test_sparse_csr_ingest_matches_dense_path(engine, oracle, gen):
     empty = engine.score_sparse(m, np.zeros(4, dtype=np.int64), np.zeros(0, dtype=np.int32), np.zeros(0), F)   # three all-missing rows
     assert np.array_equal(empty["score"], engine.score(m, np.zeros((3, F)), np.zeros((3, 3), dtype=np.uint32))["score"])
     assert (engine.score_sparse(m, row_ptr, indices, values, F + 1)["status"] == 1).all()                        # size mismatch
+
+
+def test_model_replicate_peer_copy(gen, oracle):
+    """fjp_model_replicate: a model compiled on GPU 0 is peer-copied to GPU 1 (no re-compile) and scores identically.
+    Needs two GPUs (gpurun --gpus 2); skipped otherwise."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    from flink_jpmml_b200 import capi
+    e0, e1 = capi.Engine(0), capi.Engine(1)
+    pm, arr = gen.gbt_pmml(T=64, depth=8, F=100, seed=9)
+    m0 = e0.compile(pm)
+    m1 = e1.replicate(m0)
+    X, pres, pb = gen.events(50000, 100, 10, 0.1)
+    r0, r1 = e0.score(m0, X, pb), e1.score(m1, X, pb)
+    assert np.array_equal(r0["score"], r1["score"]) and np.array_equal(r0["status"], r1["status"])
+    assert np.array_equal(r1["score"], gen.gbt_numpy(arr, X, pres))
+    with pytest.raises(capi.EngineError, match="another device"):
+        e1.score(m0, X, pb)
+    e0.close(); e1.close()
