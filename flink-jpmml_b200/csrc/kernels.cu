@@ -609,7 +609,7 @@ __global__ void __launch_bounds__(128) regression_kernel(const __grid_constant__
 // warps = event blocks x table groups.  Inputs and the transposed coefficient block [field][table] stream through
 // shared memory in chunks of fields; y[c] accumulates in double, unfused, in field order (= NumericPredictor order).
 struct DensePlan { int groups, event_blocks, events, chunk, kp, warps; uint32_t off_x, off_st, off_y, off_flags, smem_bytes; };
-template <bool HASMISS>
+template <bool HASMISS, int TC>
 __global__ void __launch_bounds__(256, 3) regression_tile_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, const DensePlan pl) {
   extern __shared__ __align__(128) uint8_t smem[];
   const RegressionDesc& rd = m.reg; const int F = m.F, C = rd.n_tables, KP = pl.kp, E = pl.events, EP = E + 1;
@@ -624,9 +624,9 @@ __global__ void __launch_bounds__(256, 3) regression_tile_kernel(const __grid_co
   const long ntiles = (a.n + E - 1) / E;
   for (long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const long row0 = tile * E, row = row0 + e;
-    double acc[CK_TC]; int flags = 0;  // bit0 preparation failure, bit1 missing predictor
+    double acc[TC]; int flags = 0;  // bit0 preparation failure, bit1 missing predictor
 #pragma unroll
-    for (int k = 0; k < CK_TC; k++) { int c = cg * CK_TC + k; acc[k] = c < C ? rd.intercept[c] : 0.0; }
+    for (int k = 0; k < TC; k++) { int c = cg * TC + k; acc[k] = c < C ? rd.intercept[c] : 0.0; }
     // double-buffered chunks: the copies of chunk c+1 (cp.async, 8 B each, written straight into the transposed
     // position) are in flight while chunk c is multiplied
     const int nchunks = (F + pl.chunk - 1) / pl.chunk;
@@ -650,19 +650,19 @@ __global__ void __launch_bounds__(256, 3) regression_tile_kernel(const __grid_co
       if (c + 1 < nchunks) { fill(buf ^ 1, f0 + pl.chunk); asm volatile("cp.async.wait_group 1;" ::: "memory"); }
       else asm volatile("cp.async.wait_group 0;" ::: "memory");
       __syncthreads();
-      const double* wp = wt + (size_t)buf * pl.chunk * KP + cg * CK_TC; const double* xb = xs + (size_t)buf * pl.chunk * EP;
+      const double* wp = wt + (size_t)buf * pl.chunk * KP + cg * TC; const double* xb = xs + (size_t)buf * pl.chunk * EP;
       const uint8_t* sb = sts + (size_t)buf * pl.chunk * (E + 4);
       for (int f = 0; f < nfc; f++, wp += KP) {
         double x = xb[f * EP + e];
         if (HASMISS) { int st = sb[f * (E + 4) + e]; flags |= st == 2 ? 1 : (st == 1 ? 2 : 0); }
         const double2* w2 = reinterpret_cast<const double2*>(wp);
 #pragma unroll
-        for (int k = 0; k < CK_TC / 2; k++) { double2 w = w2[k]; acc[2 * k] += w.x * x; acc[2 * k + 1] += w.y * x; }
+        for (int k = 0; k < TC / 2; k++) { double2 w = w2[k]; acc[2 * k] += w.x * x; acc[2 * k + 1] += w.y * x; }
       }
       __syncthreads();   // buffer `buf` may be refilled by the next iteration's fill
     }
 #pragma unroll
-    for (int k = 0; k < CK_TC; k++) ys[(cg * CK_TC + k) * EP + e] = acc[k];
+    for (int k = 0; k < TC; k++) ys[(cg * TC + k) * EP + e] = acc[k];
     if (HASMISS) { if (flags) atomicOr(eflags + e, flags); }
     __syncthreads();
     if (cg == 0 && row < a.n) {
@@ -1111,7 +1111,10 @@ cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t 
     case MK_REGRESSION: {
       if (m.reg.n_tables > REG_MAXC) return cudaErrorInvalidValue;
       if (m.reg.dense) {
-        DensePlan pl{}; pl.kp = ((m.reg.n_tables + CK_TC - 1) / CK_TC) * CK_TC; pl.groups = pl.kp / CK_TC;   // <= 8 groups (64 tables)
+        // tables per thread: 8, 10 or 12, whichever pads the table count least (20 tables -> 2 groups of 10)
+        int tc = 8, best_pad = 1 << 30;
+        for (int cand : {8, 10, 12}) { int pad = (m.reg.n_tables + cand - 1) / cand * cand - m.reg.n_tables; if (pad < best_pad) { best_pad = pad; tc = cand; } }
+        DensePlan pl{}; pl.kp = ((m.reg.n_tables + tc - 1) / tc) * tc; pl.groups = pl.kp / tc;
         pl.event_blocks = pl.groups >= 8 ? 1 : 8 / pl.groups; pl.warps = pl.event_blocks * pl.groups; pl.events = 32 * pl.event_blocks;
         const int EP = pl.events + 1;
         int chunk = 64; while (chunk > m.F && chunk > 1) chunk /= 2;   // power of two: cheap row/column split
@@ -1124,8 +1127,11 @@ cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t 
         pl.chunk = chunk;
         long ntiles = (a.n + pl.events - 1) / pl.events; int grid = (int)(ntiles < 3L * g_num_sms ? ntiles : 3L * g_num_sms);
         const bool hasmiss = a.present != nullptr || a.replace != nullptr || !m.prep_identity;
-        if (hasmiss) { cudaFuncSetAttribute(regression_tile_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes); regression_tile_kernel<true><<<grid, pl.warps * 32, pl.smem_bytes, s>>>(m, a, pl); }
-        else { cudaFuncSetAttribute(regression_tile_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes); regression_tile_kernel<false><<<grid, pl.warps * 32, pl.smem_bytes, s>>>(m, a, pl); }
+#define FJP_RT(HM, TCV) do { cudaFuncSetAttribute(regression_tile_kernel<HM, TCV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes); \
+                             regression_tile_kernel<HM, TCV><<<grid, pl.warps * 32, pl.smem_bytes, s>>>(m, a, pl); } while (0)
+        if (hasmiss) { if (tc == 8) FJP_RT(true, 8); else if (tc == 10) FJP_RT(true, 10); else FJP_RT(true, 12); }
+        else { if (tc == 8) FJP_RT(false, 8); else if (tc == 10) FJP_RT(false, 10); else FJP_RT(false, 12); }
+#undef FJP_RT
         return cudaGetLastError();
       }
       regression_kernel<<<(unsigned)((a.n + 127) / 128), 128, 0, s>>>(m, a);

@@ -100,7 +100,7 @@ struct RegressionDesc {
   const RegTerm* terms;
   const int32_t* cat_off;     // n_tables+1
   const RegCat* cats;
-  const double* dense_wt;     // dense only: F x KP transposed, KP = n_tables rounded up to 8, zero padded
+  const double* dense_wt;     // dense only: F x KP transposed, KP = n_tables rounded up to a multiple of 8, 10 or 12 (least padding), zero padded
 };
 
 // ---- GeneralRegressionModel (PPMatrix x ParamMatrix) -------------------------------------------------------

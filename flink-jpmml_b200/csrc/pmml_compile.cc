@@ -657,7 +657,9 @@ void compile_regression(const XNode& m, Builder& b) {
   if (!classify && icpt.size() != 1) unsupported("regression with several RegressionTables");
   d.n_tables = (int)icpt.size(); dense = dense && cats.empty(); d.dense = dense ? 1 : 0;
   std::vector<double> w;
-  if (dense) { size_t KP = (icpt.size() + 7) / 8 * 8; w.assign(KP * (size_t)F, 0.0); for (size_t t = 0; t < icpt.size(); t++) for (int i = 0; i < F; i++) w[(size_t)i * KP + t] = terms[toff[t] + i].coef; }
+  // same choice as the launcher: 8, 10 or 12 tables per thread, least padding
+  size_t tcs = 8, bestpad = ~size_t(0); for (size_t cand : {size_t(8), size_t(10), size_t(12)}) { size_t pad = (icpt.size() + cand - 1) / cand * cand - icpt.size(); if (pad < bestpad) { bestpad = pad; tcs = cand; } }
+  if (dense) { size_t KP = (icpt.size() + tcs - 1) / tcs * tcs; w.assign(KP * (size_t)F, 0.0); for (size_t t = 0; t < icpt.size(); t++) for (int i = 0; i < F; i++) w[(size_t)i * KP + t] = terms[toff[t] + i].coef; }
   b.put(&d.intercept, icpt); b.put(&d.term_off, toff); b.put(&d.terms, terms); b.put(&d.cat_off, coff); b.put(&d.cats, cats); b.put(&d.dense_wt, w);
   if (classify) b.set_labels(labels, false); else b.set_labels({}, false);
   finish_target(b, classify);
