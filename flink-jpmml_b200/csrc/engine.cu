@@ -82,6 +82,7 @@ struct Slot {
   cudaStream_t s = nullptr; cudaEvent_t done = nullptr;
   uint8_t* buf = nullptr; size_t cap = 0;   // one device arena per slot, carved per call
   bool busy = false; fjp_model* held = nullptr;
+  const uint8_t* pending_status = nullptr; long pending_n = 0;   // submitted batch whose outcomes are counted at fjp_wait
 };
 
 struct fjp_engine {
@@ -90,6 +91,8 @@ struct fjp_engine {
   std::mutex slot_mu; std::condition_variable slot_cv;
   std::mutex table_mu; std::shared_ptr<const Table> table{std::make_shared<Table>()};
   std::atomic<long> launches{0};
+  std::atomic<uint64_t> status_counts[6];   // per-batch aggregation of the outcomes the reference logs one WARN line for
+  fjp_engine() { for (auto& c : status_counts) c = 0; }
 };
 
 static int acquire_slot(fjp_engine* e) {
@@ -156,6 +159,18 @@ static int enqueue_chunk(fjp_engine* e, fjp_model* m, Slot& s, const HostBatch& 
   return 0;
 }
 
+// status histogram of a finished batch (host side; rows are mostly 0, so whole zero words are skipped)
+static void count_statuses(fjp_engine* e, const uint8_t* st, long n) {
+  uint64_t c[6] = {0, 0, 0, 0, 0, 0}; long i = 0;
+  for (; i < n && (reinterpret_cast<uintptr_t>(st + i) & 7); i++) c[st[i] < 6 ? st[i] : 3]++;
+  for (; i + 8 <= n; i += 8) {
+    uint64_t w; memcpy(&w, st + i, 8);
+    if (w == 0) c[0] += 8; else for (int k = 0; k < 8; k++) c[st[i + k] < 6 ? st[i + k] : 3]++;
+  }
+  for (; i < n; i++) c[st[i] < 6 ? st[i] : 3]++;
+  for (int k = 0; k < 6; k++) if (c[k]) e->status_counts[k] += c[k];
+}
+
 // whole-batch outcomes that need no device work: empty model (5) and size mismatch (1)
 static bool host_short_circuit(fjp_model* m, const HostBatch& hb) {
   int st = -1;
@@ -200,6 +215,7 @@ void fjp_engine_destroy(fjp_engine* e) {
 int fjp_engine_device(const fjp_engine* e) { return e->device; }
 int fjp_engine_sync(fjp_engine* e) { CK(cudaSetDevice(e->device)); for (auto& s : e->slots) CK(cudaStreamSynchronize(s.s)); return 0; }
 long fjp_engine_launch_count(const fjp_engine* e) { return e->launches.load(); }
+void fjp_engine_status_counts(const fjp_engine* e, uint64_t out[6]) { for (int k = 0; k < 6; k++) out[k] = e->status_counts[k].load(); }
 
 int fjp_model_compile(fjp_engine* e, const char* pmml, size_t len, fjp_model** out, char* err, size_t errcap) {
   std::unique_ptr<fjp_model> m(new fjp_model());
@@ -295,7 +311,7 @@ int fjp_score_batch_ex(fjp_engine* e, fjp_model* m, const double* X, const uint3
                        int32_t* node_ids, int node_stride, double* probs, int prob_stride) {
   if (n <= 0) return 0;
   HostBatch hb{X, present, replace, n, vec_size, score, status, aux, node_ids, node_stride, probs, prob_stride};
-  if (host_short_circuit(m, hb)) return 0;
+  if (host_short_circuit(m, hb)) { count_statuses(e, status, n); return 0; }
   if (!m->d_blob) return fail("model was compiled without an engine: it cannot score");
   CK(cudaSetDevice(e->device));
   if (m->device != e->device) return fail("model lives on another device; use fjp_model_replicate");
@@ -306,6 +322,7 @@ int fjp_score_batch_ex(fjp_engine* e, fjp_model* m, const double* X, const uint3
   int used[2] = {s0, s1}; int ns = s1 >= 0 ? 2 : 1; int rc = 0; long k = 0;
   for (long lo = 0; lo < n && rc == 0; lo += rows, k++) rc = enqueue_chunk(e, m, e->slots[used[k % ns]], hb, lo, std::min(n, lo + rows));
   for (int i = 0; i < ns; i++) { cudaError_t ce = cudaStreamSynchronize(e->slots[used[i]].s); if (ce != cudaSuccess && rc == 0) rc = fail(std::string("scoring failed: ") + cudaGetErrorString(ce)); release_slot(e, used[i]); }
+  if (rc == 0) count_statuses(e, status, n);
   return rc;
 }
 
@@ -313,7 +330,7 @@ int fjp_score_sparse(fjp_engine* e, fjp_model* m, const int64_t* row_ptr, const 
                      const double* replace, long n, int vec_size, double* score, uint8_t* status, int32_t* aux) {
   if (n <= 0) return 0;
   HostBatch hb{nullptr, nullptr, replace, n, vec_size, score, status, aux, nullptr, 0, nullptr, 0};
-  if (host_short_circuit(m, hb)) return 0;
+  if (host_short_circuit(m, hb)) { count_statuses(e, status, n); return 0; }
   if (!m->d_blob) return fail("model was compiled without an engine: it cannot score");
   CK(cudaSetDevice(e->device));
   if (m->device != e->device) return fail("model lives on another device; use fjp_model_replicate");
@@ -353,6 +370,7 @@ int fjp_score_sparse(fjp_engine* e, fjp_model* m, const int64_t* row_ptr, const 
     }();
   }
   for (int i = 0; i < ns; i++) { cudaError_t ce = cudaStreamSynchronize(e->slots[used[i]].s); if (ce != cudaSuccess && rc == 0) rc = fail(std::string("scoring failed: ") + cudaGetErrorString(ce)); release_slot(e, used[i]); }
+  if (rc == 0) count_statuses(e, status, n);
   return rc;
 }
 
@@ -385,7 +403,7 @@ int fjp_submit(fjp_engine* e, fjp_model* m, const double* X, const uint32_t* pre
   HostBatch hb{X, present, replace, n, vec_size, score, status, aux, nullptr, 0, nullptr, 0};
   CK(cudaSetDevice(e->device));
   int si = acquire_slot(e); Slot& s = e->slots[si];
-  *ticket = si;
+  *ticket = si; s.pending_status = status; s.pending_n = n > 0 ? n : 0;
   if (n <= 0 || host_short_circuit(m, hb)) return 0;
   if (!m->d_blob || m->device != e->device) { release_slot(e, si); return fail("model is not resident on this engine's device"); }
   fjp_model_retain(m); s.held = m;  // the batch keeps its model alive across a concurrent fjp_table_del
@@ -400,6 +418,8 @@ int fjp_wait(fjp_engine* e, int ticket) {
   CK(cudaSetDevice(e->device));
   cudaError_t ce = cudaStreamSynchronize(s.s);
   if (s.held) { fjp_model_release(s.held); s.held = nullptr; }
+  if (ce == cudaSuccess && s.pending_status) count_statuses(e, s.pending_status, s.pending_n);
+  s.pending_status = nullptr; s.pending_n = 0;
   release_slot(e, ticket);
   if (ce != cudaSuccess) return fail(std::string("scoring failed: ") + cudaGetErrorString(ce));
   return 0;

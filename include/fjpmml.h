@@ -50,6 +50,10 @@ int fjp_engine_device(const fjp_engine* e);
 int fjp_engine_sync(fjp_engine* e);
 /* Number of scoring kernels launched by this engine so far (diagnostics / bench evidence). */
 long fjp_engine_launch_count(const fjp_engine* e);
+/* Events scored through the host entry points so far, by status (index = status byte).  Replaces the one WARN log line
+ * per failed prediction of S/models/prediction/Prediction.scala:47-62 with per-batch counters an operator can export
+ * as Flink metrics. */
+void fjp_engine_status_counts(const fjp_engine* e, uint64_t out[6]);
 
 /* ---- model load: PMML bytes in, device-resident flattened model out -----------------------------------------
  * Replaces PmmlModel.fromReader (S/api/PmmlModel.scala:53-61): JAXB unmarshal + ModelEvaluatorFactory.  The bytes

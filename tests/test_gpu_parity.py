@@ -144,6 +144,10 @@ def test_empty_model_and_size_mismatch(engine, gen):
     r = engine.score(m, np.ones((3, 3)))
     assert (r["status"] == 1).all()
     assert engine.launch_count > 0
+    before = engine.status_counts
+    engine.score(None, np.ones((7, 4))); engine.score(m, np.ones((3, 3))); engine.score(m, np.ones((11, 4)))
+    after = engine.status_counts
+    assert [a - b for a, b in zip(after, before)] == [11, 3, 0, 0, 0, 7]      # per-batch outcome counters
 
 
 def test_sparse_csr_ingest_matches_dense_path(engine, oracle, gen):
