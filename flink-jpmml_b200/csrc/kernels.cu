@@ -367,9 +367,19 @@ __global__ void __launch_bounds__(256) forest_general_kernel(const __grid_consta
       double v = fd.gleaf_value[leaf];
       if (fd.method == FM_WSUM || fd.method == FM_WAVERAGE) { sum += w * v; wsum += w; } else sum += v;
     } else {
-      int lab = fd.gleaf_label[leaf];
-      if (order[lab] < 0) order[lab] = seen++;
-      votes[lab] += (fd.method == FM_WVOTE) ? w : 1.0; wsum += (fd.method == FM_WVOTE) ? w : 1.0;
+      if (fd.method == FM_AVG_PROB || fd.method == FM_WAVG_PROB) {   // sum of (weighted) leaf distributions; /sum(w) does not move the winner
+        const double ww = fd.method == FM_WAVG_PROB ? w : 1.0;
+        for (int i = fd.gdist_off[leaf]; i < fd.gdist_off[leaf + 1]; i++) {
+          int lab = fd.gdist_label[i];
+          if (order[lab] < 0) order[lab] = seen++;
+          votes[lab] += ww * fd.gdist_prob[i];
+        }
+        wsum += ww;
+      } else {
+        int lab = fd.gleaf_label[leaf];
+        if (order[lab] < 0) order[lab] = seen++;
+        votes[lab] += (fd.method == FM_WVOTE) ? w : 1.0; wsum += (fd.method == FM_WVOTE) ? w : 1.0;
+      }
     }
   }
   if (fail) { write_out(a, row, 0, ST_PREP, -1); return; }

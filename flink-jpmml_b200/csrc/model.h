@@ -47,7 +47,8 @@ enum ModelKind : int { MK_CLUSTERING = 0, MK_FOREST = 1, MK_REGRESSION = 2, MK_N
 // ---- tree ensembles -----------------------------------------------------------------------------
 enum : int { FOREST_COMPLETE = 0, FOREST_GENERAL = 1 };
 enum : int { ENC_FLOAT = 0, ENC_RANK = 1 };
-enum : int { FM_SINGLE = 0, FM_SUM = 1, FM_AVERAGE = 2, FM_WSUM = 3, FM_WAVERAGE = 4, FM_VOTE = 5, FM_WVOTE = 6 };
+enum : int { FM_SINGLE = 0, FM_SUM = 1, FM_AVERAGE = 2, FM_WSUM = 3, FM_WAVERAGE = 4, FM_VOTE = 5, FM_WVOTE = 6,
+             FM_AVG_PROB = 7, FM_WAVG_PROB = 8 };  // classification average / weightedAverage of the leaves' distributions
 
 // General decision node: key = key(x[feat]); key == 0 (missing) -> on_missing, key <= k -> on_true, else on_false.
 // Successors >= 0 are node indices, < 0 are ~leaf index, LEAF_NULL is "null prediction".
@@ -68,6 +69,9 @@ struct ForestDesc {
   // FOREST_GENERAL
   const GNode* gnodes; const int32_t* troot; const double* gleaf_value; const int32_t* gleaf_label; const double* tweight;
   const int32_t* gleaf_node_id;
+  // classification leaves: ScoreDistribution as CSR (label index, probability) in document order; a leaf without one
+  // holds the single entry (its label, 1.0)
+  const int32_t* gdist_off; const int32_t* gdist_label; const double* gdist_prob;
   // ENC_FLOAT: per feature 0 = value is a float already, 1 = round up to float, 2 = round down
   const uint8_t* feat_mode;
   // ENC_RANK: per active feature sorted distinct thresholds

@@ -296,7 +296,7 @@ void compile_clustering(const XNode& m, Builder& b) {
 // ---------------------------------------------------------------------------------------------- trees
 struct Thr { int slot; double value; bool strict; };  // test: x <= value (strict: x < value)
 struct TNode { int thr; int32_t on_true, on_false, on_missing; };  // thr index; thr<0: "always true when present"
-struct TLeaf { double value; int32_t label; int32_t node_id; };
+struct TLeaf { double value; int32_t label; int32_t node_id; std::vector<std::pair<int32_t, double>> dist; };
 
 struct ForestBuilder {
   Builder& b; bool classify;
@@ -326,8 +326,20 @@ struct ForestBuilder {
   int32_t leaf_for(const XNode& n, TreeCtx& cx) {  // successor for "the result is node n's score"
     if (!n.has("score")) return LEAF_NULL;
     auto it = cx.leafref.find(&n); if (it != cx.leafref.end()) return it->second;
-    TLeaf lf{0.0, -1, cx.number[&n]};
-    if (classify) lf.label = label_of(n.attr("score"));
+    TLeaf lf{0.0, -1, cx.number[&n], {}};
+    if (classify) {
+      lf.label = label_of(n.attr("score"));
+      // ScoreDistribution: `probability` if given, else recordCount / sum (JPMML; SURVEY App. A TreeModel)
+      std::vector<std::pair<int32_t, double>> raw; bool is_prob = false; double tot = 0;
+      n.each("ScoreDistribution", [&](const XNode& sd) {
+        double v;
+        if (sd.has("probability")) { v = need_double(sd.attr("probability"), "probability"); is_prob = true; }
+        else v = need_double(sd.attr("recordCount"), "recordCount");
+        raw.emplace_back(label_of(sd.attr("value")), v); tot += v;
+      });
+      if (raw.empty()) lf.dist.emplace_back(lf.label, 1.0);
+      else for (auto& r : raw) lf.dist.emplace_back(r.first, is_prob ? r.second : r.second / tot);
+    }
     else {
       if (!parse_double(n.attr("score"), &lf.value)) unsupported("non-numeric regression score '" + std::string(n.attr("score")) + "'");
       if (cx.has_sub_tx) {  // a segment model's own <Targets> act on its result before aggregation
@@ -575,7 +587,13 @@ struct ForestBuilder {
         g[i] = GNode{(uint32_t)feat_of(n), n.thr >= 0 ? K[n.thr] : 0xFFFFFFFFu, n.on_true, n.on_false, n.on_missing};
       }
       std::vector<double> gv(leaves.size()); std::vector<int32_t> gl(leaves.size()), gid(leaves.size());
-      for (size_t i = 0; i < leaves.size(); i++) { gv[i] = leaves[i].value; gl[i] = leaves[i].label; gid[i] = leaves[i].node_id; }
+      std::vector<int32_t> doff{0}, dlab; std::vector<double> dprob;
+      for (size_t i = 0; i < leaves.size(); i++) {
+        gv[i] = leaves[i].value; gl[i] = leaves[i].label; gid[i] = leaves[i].node_id;
+        for (auto& d : leaves[i].dist) { dlab.push_back(d.first); dprob.push_back(d.second); }
+        doff.push_back((int32_t)dlab.size());
+      }
+      b.put(&fd.gdist_off, doff); b.put(&fd.gdist_label, dlab); b.put(&fd.gdist_prob, dprob);
       b.put(&fd.gnodes, g); b.put(&fd.troot, roots); b.put(&fd.gleaf_value, gv); b.put(&fd.gleaf_label, gl); b.put(&fd.tweight, weights);
       b.put(&fd.gleaf_node_id, gid);
     }
@@ -603,7 +621,7 @@ void compile_mining(const XNode& m, Builder& b) {
   bool classify = m.attr("functionName") == "classification"; sv mm = sg->attr("multipleModelMethod");
   int method = -1;
   if (!classify) method = mm == "sum" ? FM_SUM : mm == "average" ? FM_AVERAGE : mm == "weightedSum" ? FM_WSUM : mm == "weightedAverage" ? FM_WAVERAGE : -1;
-  else method = mm == "majorityVote" ? FM_VOTE : mm == "weightedMajorityVote" ? FM_WVOTE : -1;
+  else method = mm == "majorityVote" ? FM_VOTE : mm == "weightedMajorityVote" ? FM_WVOTE : mm == "average" ? FM_AVG_PROB : mm == "weightedAverage" ? FM_WAVG_PROB : -1;
   if (method < 0) unsupported("multipleModelMethod " + std::string(mm) + " for " + (classify ? "classification" : "regression"));
   ForestBuilder fb(b, classify);
   sg->each("Segment", [&](const XNode& s) {

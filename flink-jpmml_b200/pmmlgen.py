@@ -191,27 +191,52 @@ def gbt_pmml(T=500, depth=8, F=100, seed=SEED_BASE + 4, dtype="double", method="
     return "\n".join(out).encode(), arrays
 
 
-def rf_pmml(T=200, depth=8, F=64, n_labels=4, seed=SEED_BASE + 5, target_dtype="string"):
-    """MiningModel classification, majorityVote over T complete TreeModels whose leaves carry labels "0".."L-1"."""
+def rf_pmml(T=200, depth=8, F=64, n_labels=4, seed=SEED_BASE + 5, target_dtype="string", method="majorityVote"):
+    """MiningModel classification over T complete TreeModels whose leaves carry labels "0".."L-1".
+    method="majorityVote" (labels only) or "average" (scikit-learn style: every leaf has a ScoreDistribution of record
+    counts and the ensemble averages the leaf probabilities)."""
     feat, thr, dleft, rng = forest_arrays(T, depth, F, seed)
     leaf = rng.integers(0, n_labels, size=(T, 1 << depth))
+    counts = rng.integers(0, 20, size=(T, 1 << depth, n_labels)) if method != "majorityVote" else None
+    if counts is not None:
+        counts[np.arange(T)[:, None], np.arange(1 << depth)[None, :], leaf] += 21      # the leaf's label has the most records
     names = [f"x{i}" for i in range(F)]
     labels = [str(i) for i in range(n_labels)]
     out = _header()
     out += _data_dictionary([(n, "continuous", "double") for n in names], ("y", "categorical", target_dtype, labels))
     out.append(f'<MiningModel modelName="rf-{T}x{depth}" functionName="classification">')
     out += _mining_schema(names, "y")
-    out.append('<Segmentation multipleModelMethod="majorityVote">')
+    out.append(f'<Segmentation multipleModelMethod="{method}">')
     for t in range(T):
         out.append(f'<Segment id="{t + 1}"><True/>')
         out.append('<TreeModel functionName="classification" missingValueStrategy="defaultChild" '
                    'noTrueChildStrategy="returnNullPrediction" splitCharacteristic="binarySplit">')
         out += _mining_schema(names)
+        n0 = len(out)
         _complete_tree_xml(out, feat[t], thr[t], dleft[t], [labels[v] for v in leaf[t]], names, depth)
+        if counts is not None:   # splice the ScoreDistributions into the leaf elements just emitted (leaves appear left to right)
+            k = 0
+            for i in range(n0, len(out)):
+                if out[i].startswith('<Node') and ' score="' in out[i] and out[i].endswith('</Node>'):
+                    sd = "".join(f'<ScoreDistribution value="{labels[c]}" recordCount="{int(counts[t, k, c])}"/>' for c in range(n_labels))
+                    out[i] = out[i][:-len('</Node>')] + sd + '</Node>'
+                    k += 1
         out.append('</TreeModel></Segment>')
     out.append('</Segmentation></MiningModel></PMML>')
-    arrays = {"feat": feat, "thr": thr, "dleft": dleft, "leaf": leaf, "depth": depth, "n_labels": n_labels}
+    arrays = {"feat": feat, "thr": thr, "dleft": dleft, "leaf": leaf, "depth": depth, "n_labels": n_labels, "counts": counts}
     return "\n".join(out).encode(), arrays
+
+
+def rf_average_numpy(arrays, X, present=None):
+    """Averaged leaf probabilities (recordCount / total per leaf), summed in segment order; first maximal label."""
+    li = forest_leaf_index_numpy(arrays, X, present)
+    n, T = li.shape
+    c = arrays["counts"].astype(np.float64)
+    prob = c / c.sum(axis=2, keepdims=True)
+    acc = np.zeros((n, arrays["n_labels"]))
+    for t in range(T):
+        acc = acc + prob[t, li[:, t], :]
+    return acc.argmax(axis=1).astype(np.float64), acc / T
 
 
 def forest_leaf_index_numpy(arrays, X, present=None):

@@ -102,6 +102,18 @@ def test_rf_majority_vote(engine, oracle, gen):
     assert np.array_equal(r["score"], gen.rf_numpy(arr, X, pres))
 
 
+def test_rf_average_of_leaf_distributions(engine, oracle, gen):
+    # scikit-learn style random forest: ScoreDistribution per leaf, multipleModelMethod="average"
+    pm, arr = gen.rf_pmml(T=30, depth=5, F=12, n_labels=3, seed=41, method="average")
+    m, om = engine.compile(pm), oracle.OracleModel(pm)
+    X, pres, pb = gen.events(8000, 12, 42, 0.1)
+    r, o = engine.score(m, X, pb, node_ids=True), om.predict(X, pb, node_ids=True, nthreads=8)
+    compare(r, o, exact_scores=True)
+    assert np.array_equal(r["node_ids"], o["node_ids"])
+    lab, _ = gen.rf_average_numpy(arr, X, pres)
+    assert (r["score"] == lab).mean() > 0.999      # numpy sums the same terms; argmax ties aside they agree
+
+
 def test_c3_multinomial_regression(engine, oracle, gen):
     pm, arr = gen.regression_pmml()
     m, om = engine.compile(pm), oracle.OracleModel(pm)

@@ -73,6 +73,10 @@ def test_rf_regression_nn_match_numpy(oracle, gen):
     X, pres, pb = gen.events(3000, 9, 6, 0.1)
     r = oracle.OracleModel(pm).predict(X, pb)
     assert np.array_equal(r["score"], gen.rf_numpy(arr, X, pres))
+    pm, arr = gen.rf_pmml(T=15, depth=4, F=9, n_labels=3, seed=6, method="average")
+    r = oracle.OracleModel(pm).predict(X, pb, n_probs=3)
+    lab, avg = gen.rf_average_numpy(arr, X, pres)
+    assert (r["score"] == lab).all()
     pm, arr = gen.regression_pmml(F=40, C=6, seed=7)
     X, pres, pb = gen.events(1000, 40, 8)
     r = oracle.OracleModel(pm).predict(X, n_probs=6)
