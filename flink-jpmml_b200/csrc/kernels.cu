@@ -117,6 +117,54 @@ __device__ __forceinline__ void write_label(const DeviceModel& m, const BatchArg
   write_out(a, row, m.label_value[label], st, aux);
 }
 
+// ---- link functions and class normalisation (RegressionModel; also the modelChain epilogue) ------------------
+__device__ __forceinline__ double link_fn(int norm, double y) {
+  switch (norm) {
+    case NORM_NONE: return y;
+    case NORM_SOFTMAX: case NORM_LOGIT: return 1.0 / (1.0 + exp(-y));
+    case NORM_EXP: return exp(y);
+    case NORM_PROBIT: return 0.5 * erfc(-y / sqrt(2.0));
+    case NORM_CLOGLOG: return 1.0 - exp(-exp(y));
+    case NORM_LOGLOG: return exp(-exp(-y));
+    case NORM_CAUCHIT: return 0.5 + atan(y) / 3.14159265358979323846;
+    default: return y;
+  }
+}
+__device__ __forceinline__ double ipow(double x, int e) {  // Math.pow(x, integer) for the small exponents PMML uses
+  if (e == 1) return x; if (e == 0) return 1.0; if (e == 2) return x * x;
+  return pow(x, (double)e);
+}
+
+// classification epilogue shared by regression / NN: y[0..C) in (strided) memory -> probabilities -> first maximal label
+template <class Get, class Set>
+__device__ void normalize_classes(int norm, int C, Get y, Set p) {
+  if (norm == NORM_SOFTMAX) { double s = 0; for (int i = 0; i < C; i++) { double e = exp(y(i)); p(i, e); s += e; } for (int i = 0; i < C; i++) p(i, y(i) / s); }
+  else if (norm == NORM_SIMPLEMAX) { double s = 0; for (int i = 0; i < C; i++) s += y(i); for (int i = 0; i < C; i++) p(i, y(i) / s); }
+  else if (norm == NORM_NONE) { double s = 0; for (int i = 0; i + 1 < C; i++) s += y(i); p(C - 1, 1.0 - s); }
+  else { double s = 0; for (int i = 0; i + 1 < C; i++) { double v = link_fn(norm, y(i)); p(i, v); s += v; } p(C - 1, 1.0 - s); }
+}
+
+
+// modelChain epilogue: RegressionTables over the channel values of the tree segments (RegTerm.slot = channel)
+template <class GetCh>
+__device__ void chain_finish(const DeviceModel& m, const BatchArgs& a, long row, GetCh ch) {
+  const RegressionDesc& rd = m.reg; double y[64];
+  for (int t = 0; t < rd.n_tables; t++) {
+    double acc = rd.intercept[t];
+    for (int i = rd.term_off[t]; i < rd.term_off[t + 1]; i++) { RegTerm tm = rd.terms[i]; acc += tm.coef * ipow(ch(tm.slot), tm.exponent); }
+    y[t] = acc;
+  }
+  if (!rd.classify) { write_out(a, row, apply_target(m.tx, link_fn(rd.norm, y[0])), m.target_status, -1); return; }
+  const int C = rd.n_tables;
+  normalize_classes(rd.norm, C, [&](int i) { return y[i]; }, [&](int i, double v) { y[i] = v; });
+  int best = 0; for (int i = 1; i < C; i++) if (java_cmp(y[i], y[best]) > 0) best = i;
+  write_label(m, a, row, best, best);
+  if (a.probs) for (int i = 0; i < C && i < a.prob_stride; i++) a.probs[row * (long)a.prob_stride + i] = y[i];
+}
+__device__ __forceinline__ double channel_value(const ChannelSpec& cs, double sum) {
+  return apply_target(cs.tx, cs.average ? sum / (double)cs.n_trees : sum);
+}
+
 // ---- key encodings for tree tests (model.h ForestDesc) -------------------------------------------------
 __device__ __forceinline__ uint32_t ordkey(float f) {
   uint32_t u = __float_as_uint(f);
@@ -173,7 +221,8 @@ __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.
 //            for 32 different events, TI trees interleaved per thread for ILP; leaf values accumulate in double in
 //            segment order (bit-identical to a sequential sum).
 // Shared memory:  keys F*E*4 | ring 2*G*blob (phase A's row stage aliases it when it fits) | votes | barriers
-// MODE: 0 sum/average, 1 weighted sum/average, 2 majority vote.  DBG: also write per-tree node ids.
+// MODE: 0 sum/average, 1 weighted sum/average, 2 majority vote, 3 modelChain (per-channel sums -> RegressionTables).
+// DBG: also write per-tree node ids.
 constexpr int FC_RMAX = 10;  // row-stage elements a thread keeps in flight
 template <int D, int TI, int MODE, bool DBG>
 __global__ void __launch_bounds__(512, 1)
@@ -269,6 +318,8 @@ forest_complete_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a,
     const uint32_t E4 = 4u * E;
     double sum = 0.0, wsum = 0.0;
     uint32_t seen = 0;  // classification: number of distinct labels seen so far (insertion order)
+    uint32_t cur_ch = 0;   // modelChain: channel of the running sum
+    double* chv = reinterpret_cast<double*>(votes);   // modelChain: finished channel values [channel][event]
     if (MODE == 2) for (int l = 0; l < m.n_labels; l++) { votes[l * E + tid] = 0; votes[(m.n_labels + l) * E + tid] = 0xFFFF; }
     for (int g = 0; g < NG; g++) {
       uint32_t slot = q_wait & 1u;
@@ -299,7 +350,12 @@ forest_complete_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a,
             if (MODE != 2) {
               double lv, w;
               asm volatile("ld.shared.f64 %0, [%1];" : "=d"(lv) : "r"(bl[k] + idx[k] * 8u));
-              if (MODE == 1) { asm volatile("ld.shared.f64 %0, [%1];" : "=d"(w) : "r"(bl[k])); sum += w * lv; wsum += w; } else sum += lv;
+              if (MODE == 1) { asm volatile("ld.shared.f64 %0, [%1];" : "=d"(w) : "r"(bl[k])); sum += w * lv; wsum += w; }
+              else if (MODE == 3) {
+                uint32_t ch; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(ch) : "r"(bl[k]));
+                if (ch != cur_ch) { chv[cur_ch * E + tid] = channel_value(fd.channels[cur_ch], sum); sum = 0.0; cur_ch = ch; }   // trees arrive channel by channel
+                sum += lv;
+              } else sum += lv;
             } else {
               uint32_t lab;
               asm volatile("ld.shared.u32 %0, [%1];" : "=r"(lab) : "r"(bl[k] + idx[k] * 8u));
@@ -319,7 +375,10 @@ forest_complete_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a,
     long row = row0 + tid;
     if (row < a.n) {
       if (row_fail[tid]) write_out(a, row, 0, ST_PREP, -1);
-      else if (MODE != 2) {
+      else if (MODE == 3) {
+        chv[cur_ch * E + tid] = channel_value(fd.channels[cur_ch], sum);
+        chain_finish(m, a, row, [&](int c) { return chv[c * E + tid]; });
+      } else if (MODE != 2) {
         double v = sum;
         if (fd.method == FM_AVERAGE) v = sum / (double)T; else if (fd.method == FM_WAVERAGE) v = sum / wsum;
         write_out(a, row, apply_target(m.tx, v), m.target_status, -1);
@@ -349,6 +408,7 @@ __global__ void __launch_bounds__(256) forest_general_kernel(const __grid_consta
   double votes[MAXL]; int order[MAXL]; int seen = 0;
   if (classify) for (int l = 0; l < m.n_labels && l < MAXL; l++) { votes[l] = 0; order[l] = -1; }
   int last_node_id = -1;
+  double chv[MAX_CHANNELS]; int cur_ch = 0;   // modelChain: finished channel values
   for (int t = 0; t < T && !fail; t++) {
     int32_t s = fd.troot[t];
     while (s >= 0) {
@@ -365,7 +425,8 @@ __global__ void __launch_bounds__(256) forest_general_kernel(const __grid_consta
     double w = fd.tweight[t];
     if (!classify) {
       double v = fd.gleaf_value[leaf];
-      if (fd.method == FM_WSUM || fd.method == FM_WAVERAGE) { sum += w * v; wsum += w; } else sum += v;
+      if (fd.method == FM_CHAIN) { int ch = fd.tree_channel[t]; if (ch != cur_ch) { chv[cur_ch] = channel_value(fd.channels[cur_ch], sum); sum = 0.0; cur_ch = ch; } sum += v; }
+      else if (fd.method == FM_WSUM || fd.method == FM_WAVERAGE) { sum += w * v; wsum += w; } else sum += v;
     } else {
       if (fd.method == FM_AVG_PROB || fd.method == FM_WAVG_PROB) {   // sum of (weighted) leaf distributions; /sum(w) does not move the winner
         const double ww = fd.method == FM_WAVG_PROB ? w : 1.0;
@@ -384,6 +445,7 @@ __global__ void __launch_bounds__(256) forest_general_kernel(const __grid_consta
   }
   if (fail) { write_out(a, row, 0, ST_PREP, -1); return; }
   if (null_result) { write_out(a, row, 0, m.target_status ? m.target_status : ST_EVAL, -1); return; }  // null prediction / failed aggregation
+  if (fd.method == FM_CHAIN) { chv[cur_ch] = channel_value(fd.channels[cur_ch], sum); chain_finish(m, a, row, [&](int c) { return chv[c]; }); return; }
   if (!classify) {
     double v = sum;
     if (fd.method == FM_AVERAGE) v = sum / (double)T; else if (fd.method == FM_WAVERAGE) v = sum / wsum;
@@ -556,32 +618,6 @@ __global__ void __launch_bounds__(CK_WARPS * 32, 1) cluster_fast_kernel(const __
 }
 
 // ================================================================================================ regression (J4)
-__device__ __forceinline__ double link_fn(int norm, double y) {
-  switch (norm) {
-    case NORM_NONE: return y;
-    case NORM_SOFTMAX: case NORM_LOGIT: return 1.0 / (1.0 + exp(-y));
-    case NORM_EXP: return exp(y);
-    case NORM_PROBIT: return 0.5 * erfc(-y / sqrt(2.0));
-    case NORM_CLOGLOG: return 1.0 - exp(-exp(y));
-    case NORM_LOGLOG: return exp(-exp(-y));
-    case NORM_CAUCHIT: return 0.5 + atan(y) / 3.14159265358979323846;
-    default: return y;
-  }
-}
-__device__ __forceinline__ double ipow(double x, int e) {  // Math.pow(x, integer) for the small exponents PMML uses
-  if (e == 1) return x; if (e == 0) return 1.0; if (e == 2) return x * x;
-  return pow(x, (double)e);
-}
-
-// classification epilogue shared by regression / NN: y[0..C) in (strided) memory -> probabilities -> first maximal label
-template <class Get, class Set>
-__device__ void normalize_classes(int norm, int C, Get y, Set p) {
-  if (norm == NORM_SOFTMAX) { double s = 0; for (int i = 0; i < C; i++) { double e = exp(y(i)); p(i, e); s += e; } for (int i = 0; i < C; i++) p(i, y(i) / s); }
-  else if (norm == NORM_SIMPLEMAX) { double s = 0; for (int i = 0; i < C; i++) s += y(i); for (int i = 0; i < C; i++) p(i, y(i) / s); }
-  else if (norm == NORM_NONE) { double s = 0; for (int i = 0; i + 1 < C; i++) s += y(i); p(C - 1, 1.0 - s); }
-  else { double s = 0; for (int i = 0; i + 1 < C; i++) { double v = link_fn(norm, y(i)); p(i, v); s += v; } p(C - 1, 1.0 - s); }
-}
-
 // Generic: thread per event, predictor lists in document order (CSR), values prepared on the fly.
 constexpr int REG_MAXC = 64;
 __global__ void __launch_bounds__(128) regression_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a) {
@@ -1032,7 +1068,7 @@ bool plan_forest_complete(const DeviceModel& m, ForestLaunch* out) {
   for (int E = 512; E >= 64; E -= 32) {
     if (force_e && E != force_e) continue;
     size_t keys = ((size_t)m.F * E * 4 + 127) & ~size_t(127);
-    size_t votes = fd.classify ? (size_t)2 * m.n_labels * E * 2 : 0;
+    size_t votes = fd.classify ? (size_t)2 * m.n_labels * E * 2 : (fd.method == FM_CHAIN ? (size_t)fd.n_channels * E * 8 : 0);
     size_t fixed = keys + votes + 64 + E + 256;
     if (fixed + 2 * ti * blob > budget) continue;
     int G = (int)((budget - fixed) / (2 * blob)); G = (G / ti) * ti; if (G > 16) G = 16 / ti * ti; if (G > 2 * ti) G = 2 * ti;
@@ -1047,7 +1083,7 @@ bool plan_forest_complete(const DeviceModel& m, ForestLaunch* out) {
     size_t off = keys;
     fl.off_ring = (uint32_t)off; off += ring;
     if (alias) fl.off_rows = fl.off_ring; else { fl.off_rows = (uint32_t)off; off += rows; }
-    fl.off_votes = (uint32_t)off; off += votes; off = (off + 15) & ~size_t(15);
+    off = (off + 15) & ~size_t(15); fl.off_votes = (uint32_t)off; off += votes; off = (off + 15) & ~size_t(15);
     fl.off_bars = (uint32_t)off; off += 64;
     fl.off_fail = (uint32_t)off; off += E;
     fl.smem_bytes = (uint32_t)((off + 127) & ~size_t(127));
@@ -1070,7 +1106,7 @@ cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t 
         const bool c = m.forest.classify; const int d = m.forest.depth;
 #define FJP_FC2(DD, TT, MM) (a.node_ids ? launch_fc<DD, 4, MM, true>(m, a, fl, grid, fl.events_per_cta, s) : launch_fc<DD, TT, MM, false>(m, a, fl, grid, fl.events_per_cta, s))
 #define FJP_FC1(DD, MM) (fl.trees_interleaved >= 8 ? FJP_FC2(DD, 8, MM) : (fl.trees_interleaved >= 6 ? FJP_FC2(DD, 6, MM) : FJP_FC2(DD, 4, MM)))
-#define FJP_FC(DD) (c ? FJP_FC1(DD, 2) : ((m.forest.method == FM_WSUM || m.forest.method == FM_WAVERAGE) ? FJP_FC1(DD, 1) : FJP_FC1(DD, 0)))
+#define FJP_FC(DD) (c ? FJP_FC1(DD, 2) : (m.forest.method == FM_CHAIN ? FJP_FC1(DD, 3) : ((m.forest.method == FM_WSUM || m.forest.method == FM_WAVERAGE) ? FJP_FC1(DD, 1) : FJP_FC1(DD, 0))))
         if (d == 8) return FJP_FC(8);
         if (d == 6) return FJP_FC(6);
         return FJP_FC(0);

@@ -48,7 +48,10 @@ enum ModelKind : int { MK_CLUSTERING = 0, MK_FOREST = 1, MK_REGRESSION = 2, MK_N
 enum : int { FOREST_COMPLETE = 0, FOREST_GENERAL = 1 };
 enum : int { ENC_FLOAT = 0, ENC_RANK = 1 };
 enum : int { FM_SINGLE = 0, FM_SUM = 1, FM_AVERAGE = 2, FM_WSUM = 3, FM_WAVERAGE = 4, FM_VOTE = 5, FM_WVOTE = 6,
-             FM_AVG_PROB = 7, FM_WAVG_PROB = 8 };  // classification average / weightedAverage of the leaves' distributions
+             FM_AVG_PROB = 7, FM_WAVG_PROB = 8,
+             FM_CHAIN = 9 };  // modelChain: per-channel tree sums feed RegressionTables (DeviceModel::reg, slot = channel)
+static constexpr int MAX_CHANNELS = 16;
+struct ChannelSpec { TargetXform tx; int32_t n_trees; int32_t average; };  // one regression segment of a modelChain  // classification average / weightedAverage of the leaves' distributions
 
 // General decision node: key = key(x[feat]); key == 0 (missing) -> on_missing, key <= k -> on_true, else on_false.
 // Successors >= 0 are node indices, < 0 are ~leaf index, LEAF_NULL is "null prediction".
@@ -61,6 +64,7 @@ static constexpr int32_t LEAF_NULL = INT32_MIN;  // successor meaning "null pred
 
 struct ForestDesc {
   int n_trees, depth, format, enc, method, classify;
+  int n_channels; const ChannelSpec* channels; const int32_t* tree_channel;   // FM_CHAIN only
   // FOREST_COMPLETE: n_trees blobs of 2^(depth+1) 8-byte words: [0] = segment weight (double), [1 .. 2^d-1] = nodes
   // in heap order {lo: feat | a<<31, hi: ~ka}, [2^d .. 2^(d+1)-1] = leaves (double value, or label index as u64);
   // the walk goes right iff key(x[feat]) - a > ka (unsigned; key 0 = missing, a = 1 sends missing right)

@@ -302,6 +302,7 @@ struct ForestBuilder {
   Builder& b; bool classify;
   std::vector<Thr> thr; std::vector<TNode> nodes; std::vector<int> node_slot; std::vector<TLeaf> leaves; std::vector<int32_t> roots;
   std::vector<double> weights; std::vector<std::string> labels; std::unordered_map<std::string, int> label_idx;
+  std::vector<int32_t> chain_channels;   // modelChain: channel of every tree (empty otherwise)
   explicit ForestBuilder(Builder& bb, bool c) : b(bb), classify(c) {}
 
   int label_of(sv s) { std::string k(s); auto it = label_idx.find(k); if (it != label_idx.end()) return it->second; int i = (int)labels.size(); labels.push_back(k); label_idx[k] = i; return i; }
@@ -561,6 +562,7 @@ struct ForestBuilder {
       leaf_ids.assign(roots.size() << depth, 0);
       for (size_t t = 0; t < roots.size(); t++) {
         uint64_t* bl = blobs.data() + t * W; memcpy(&bl[0], &weights[t], 8);
+        if (!chain_channels.empty()) bl[0] = (uint64_t)(uint32_t)chain_channels[t];   // modelChain: word 0 carries the channel instead
         std::function<void(int32_t, size_t)> place = [&](int32_t s, size_t h) {
           if (s < 0) {
             const TLeaf& lf = leaves[~s];
@@ -615,10 +617,79 @@ void compile_tree(const XNode& m, Builder& b) {
   b.set_labels(fb.labels, false); finish_target(b, classify);
 }
 
+bool compile_regression_tables(const XNode& m, Builder& b, const std::unordered_map<std::string, int>* channels);
+TargetXform read_target_xform(const XNode& model) {
+  TargetXform x{1, 0, 0, 0, 0, 0, 0};
+  if (const XNode* ts = model.child("Targets")) if (const XNode* t = ts->child("Target")) {
+    if (t->has("rescaleFactor")) x.factor = need_double(t->attr("rescaleFactor"), "rescaleFactor");
+    if (t->has("rescaleConstant")) x.constant = need_double(t->attr("rescaleConstant"), "rescaleConstant");
+    if (t->has("min")) { x.has_min = 1; x.mn = need_double(t->attr("min"), "min"); }
+    if (t->has("max")) { x.has_max = 1; x.mx = need_double(t->attr("max"), "max"); }
+    sv c = t->attr("castInteger"); x.cast = c == "round" ? 1 : c == "ceiling" ? 2 : c == "floor" ? 3 : 0;
+  }
+  return x;
+}
+
+// multipleModelMethod="modelChain" in the shape boosted-tree exporters write: K regression segments (a TreeModel or a
+// MiningModel sum / average of TreeModels), each publishing its result as a predictedValue OutputField, followed by a
+// RegressionModel over those outputs (logit / softmax / exp ... link, or a classification label).  Each of the K
+// segments becomes a "channel" of one forest; the final tables run in the kernel epilogue.
+void compile_model_chain(const XNode& m, const XNode& sg, Builder& b) {
+  std::vector<const XNode*> segs;
+  sg.each("Segment", [&](const XNode& s) {
+    const XNode& p = *ForestBuilder::pred_of(s);
+    if (p.name != "True") unsupported("modelChain Segment predicate other than True");
+    segs.push_back(&s);
+  });
+  if (segs.size() < 2) unsupported("modelChain with fewer than two segments");
+  ForestBuilder fb(b, false);
+  std::unordered_map<std::string, int> channels; std::vector<ChannelSpec> specs; std::vector<int32_t> tree_channel;
+  for (size_t k = 0; k + 1 < segs.size(); k++) {
+    const XNode& s = *segs[k]; ChannelSpec cs{}; cs.tx = TargetXform{1, 0, 0, 0, 0, 0, 0}; cs.average = 0;
+    const XNode* inner = s.child("MiningModel"); const XNode* tm = s.child("TreeModel"); const XNode* model = inner ? inner : tm;
+    if (!model) unsupported("modelChain segment that is neither a TreeModel nor a MiningModel of TreeModels");
+    if (model->attr("functionName") != "regression") unsupported("modelChain: non-regression inner segment");
+    const XNode* out = model->child("Output"); std::string name;
+    if (out) out->each("OutputField", [&](const XNode& f) { if (name.empty() && f.attr("feature", "predictedValue") == "predictedValue") name = std::string(f.attr("name")); });
+    if (name.empty()) unsupported("modelChain segment without a predictedValue OutputField");
+    size_t before = fb.roots.size();
+    if (tm && !inner) { fb.add_tree(*tm, 1.0, true); }   // the tree's own Targets are folded into its leaves by add_tree
+    else {
+      check_nested_schema(*inner);
+      const XNode* isg = inner->child("Segmentation"); if (!isg) malformed("MiningModel without Segmentation");
+      sv imm = isg->attr("multipleModelMethod");
+      if (imm == "average") cs.average = 1; else if (imm != "sum") unsupported("modelChain: inner multipleModelMethod " + std::string(imm));
+      cs.tx = read_target_xform(*inner);
+      isg->each("Segment", [&](const XNode& is) {
+        const XNode& ip = *ForestBuilder::pred_of(is);
+        if (ip.name == "False") return;
+        if (ip.name != "True") unsupported("Segment predicate other than True/False");
+        const XNode* itm = is.child("TreeModel"); if (!itm) unsupported("Segment model other than TreeModel");
+        fb.add_tree(*itm, 1.0, true);
+      });
+    }
+    cs.n_trees = (int)(fb.roots.size() - before);
+    if (cs.n_trees == 0) unsupported("modelChain segment without trees");
+    for (int i = 0; i < cs.n_trees; i++) tree_channel.push_back((int32_t)specs.size());
+    channels[name] = (int)specs.size(); specs.push_back(cs);
+  }
+  if ((int)specs.size() > MAX_CHANNELS) unsupported("modelChain with more than 16 tree segments");
+  const XNode* last = segs.back()->child("RegressionModel");
+  if (!last) unsupported("modelChain whose last segment is not a RegressionModel");
+  check_nested_schema(*last);
+  fb.chain_channels = tree_channel;
+  fb.emit(FM_CHAIN);
+  ForestDesc& fd = b.cm.dev.forest; fd.n_channels = (int)specs.size();
+  b.put(&fd.channels, specs); b.put(&fd.tree_channel, tree_channel);
+  compile_regression_tables(*last, b, &channels);   // sets labels / target status from the final model
+  if (b.cm.dev.reg.n_tables > 64) unsupported("modelChain with more than 64 RegressionTables");
+}
+
 void compile_mining(const XNode& m, Builder& b) {
   b.cm.family = "MiningModel"; b.cm.dev.kind = MK_FOREST;
   const XNode* sg = m.child("Segmentation"); if (!sg) malformed("MiningModel without Segmentation");
   bool classify = m.attr("functionName") == "classification"; sv mm = sg->attr("multipleModelMethod");
+  if (mm == "modelChain") { compile_model_chain(m, *sg, b); return; }
   int method = -1;
   if (!classify) method = mm == "sum" ? FM_SUM : mm == "average" ? FM_AVERAGE : mm == "weightedSum" ? FM_WSUM : mm == "weightedAverage" ? FM_WAVERAGE : -1;
   else method = mm == "majorityVote" ? FM_VOTE : mm == "weightedMajorityVote" ? FM_WVOTE : mm == "average" ? FM_AVG_PROB : mm == "weightedAverage" ? FM_WAVG_PROB : -1;
@@ -644,8 +715,9 @@ int norm_of(sv s) {
   unsupported("normalizationMethod " + std::string(s));
 }
 
-void compile_regression(const XNode& m, Builder& b) {
-  b.cm.family = "RegressionModel"; b.cm.dev.kind = MK_REGRESSION;
+// `channels` != nullptr: the last segment of a modelChain -- predictors name earlier segments' output fields and
+// RegTerm.slot is a channel index instead of a vector slot
+bool compile_regression_tables(const XNode& m, Builder& b, const std::unordered_map<std::string, int>* channels) {
   RegressionDesc& d = b.cm.dev.reg; bool classify = m.attr("functionName") == "classification";
   d.classify = classify; d.norm = norm_of(m.attr("normalizationMethod", "none"));
   std::vector<double> icpt; std::vector<int32_t> toff{0}, coff{0}; std::vector<RegTerm> terms; std::vector<RegCat> cats; std::vector<std::string> labels;
@@ -656,11 +728,19 @@ void compile_regression(const XNode& m, Builder& b) {
     t.each("NumericPredictor", [&](const XNode& n) {
       double e = need_double(n.attr("exponent", "1"), "exponent");
       if (e != std::floor(e)) unsupported("non-integer exponent");
-      sv fname = n.attr("name"); uint8_t dt = b.dict_field(fname).dtype;
+      sv fname = n.attr("name");
+      if (channels) {
+        auto it = channels->find(std::string(fname));
+        if (it == channels->end()) unsupported("modelChain: the final RegressionModel may only use earlier segments' predictedValue outputs");
+        terms.push_back({it->second, (int32_t)e, need_double(n.attr("coefficient"), "coefficient")});
+        return;
+      }
+      uint8_t dt = b.dict_field(fname).dtype;
       if (dt == DT_STRING || dt == DT_OTHER) unsupported("NumericPredictor on a non-numeric field");
       terms.push_back({b.slot_of(fname), (int32_t)e, need_double(n.attr("coefficient"), "coefficient")});
     });
     t.each("CategoricalPredictor", [&](const XNode& n) {
+      if (channels) unsupported("modelChain: CategoricalPredictor in the final RegressionModel");
       sv fname = n.attr("name"); uint8_t dt = b.dict_field(fname).dtype; double v;
       if (dt == DT_STRING || dt == DT_OTHER) unsupported("CategoricalPredictor on a string field");
       if (!parse_in_dtype(dt, n.attr("value"), &v)) unsupported("CategoricalPredictor value does not parse in the field's dataType");
@@ -673,7 +753,7 @@ void compile_regression(const XNode& m, Builder& b) {
   });
   if (icpt.empty()) malformed("no RegressionTable");
   if (!classify && icpt.size() != 1) unsupported("regression with several RegressionTables");
-  d.n_tables = (int)icpt.size(); dense = dense && cats.empty(); d.dense = dense ? 1 : 0;
+  d.n_tables = (int)icpt.size(); dense = dense && cats.empty() && !channels; d.dense = dense ? 1 : 0;
   std::vector<double> w;
   // same choice as the launcher: 8, 10 or 12 tables per thread, least padding
   size_t tcs = 8, bestpad = ~size_t(0); for (size_t cand : {size_t(8), size_t(10), size_t(12)}) { size_t pad = (icpt.size() + cand - 1) / cand * cand - icpt.size(); if (pad < bestpad) { bestpad = pad; tcs = cand; } }
@@ -681,6 +761,11 @@ void compile_regression(const XNode& m, Builder& b) {
   b.put(&d.intercept, icpt); b.put(&d.term_off, toff); b.put(&d.terms, terms); b.put(&d.cat_off, coff); b.put(&d.cats, cats); b.put(&d.dense_wt, w);
   if (classify) b.set_labels(labels, false); else b.set_labels({}, false);
   finish_target(b, classify);
+  return classify;
+}
+void compile_regression(const XNode& m, Builder& b) {
+  b.cm.family = "RegressionModel"; b.cm.dev.kind = MK_REGRESSION;
+  compile_regression_tables(m, b, nullptr);
 }
 
 // ---------------------------------------------------------------------------------------------- general regression

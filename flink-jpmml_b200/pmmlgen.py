@@ -434,3 +434,65 @@ def iris_events(n, seed=SEED_BASE + 1):
     """4 doubles U[0.2,6.0] floored to one decimal (shape of examples' IrisSource.scala:32-43)."""
     rng = np.random.default_rng(seed)
     return np.floor(rng.uniform(0.2, 6.0, size=(n, 4)) * 10.0) / 10.0
+
+
+# --------------------------------------------------------------------------------------------
+# Boosted-tree CLASSIFIER as exporters write it: modelChain(sum-of-trees per class -> RegressionModel link)
+# --------------------------------------------------------------------------------------------
+
+def gbt_classifier_pmml(T=50, depth=6, F=30, n_classes=2, seed=77, learning_rate=0.1, dtype="double"):
+    """MiningModel classification, multipleModelMethod="modelChain":
+         K inner MiningModels (regression, sum of T complete trees, Targets rescaleFactor=lr rescaleConstant=init_k,
+         OutputField decisionFunction(k) feature=predictedValue), K = 1 for two classes, else K = n_classes;
+         last segment RegressionModel classification: logit (binary) or softmax over the K decision functions."""
+    K = 1 if n_classes == 2 else n_classes
+    names = [f"x{i}" for i in range(F)]
+    labels = [str(i) for i in range(n_classes)]
+    out = _header()
+    out += _data_dictionary([(n, "continuous", dtype) for n in names], ("y", "categorical", "string", labels))
+    out.append('<MiningModel modelName="gbt-classifier" functionName="classification">')
+    out += _mining_schema(names, "y")
+    out.append('<Segmentation multipleModelMethod="modelChain">')
+    chans = []
+    for k in range(K):
+        feat, thr, dleft, rng = forest_arrays(T, depth, F, seed + 13 * k)
+        leaf = rng.normal(0.0, 1.0, size=(T, 1 << depth))
+        init = float(rng.normal(0.0, 0.3))
+        chans.append({"feat": feat, "thr": thr, "dleft": dleft, "leaf": leaf, "depth": depth, "method": "sum",
+                      "rescale_constant": init, "rescale_factor": learning_rate, "dtype": dtype})
+        out.append(f'<Segment id="{k + 1}"><True/><MiningModel functionName="regression">')
+        out += _mining_schema(names)
+        out.append(f'<Output><OutputField name="decisionFunction({k})" optype="continuous" dataType="double" feature="predictedValue" isFinalResult="false"/></Output>')
+        out.append(f'<Targets><Target rescaleFactor="{_r(learning_rate)}" rescaleConstant="{_r(init)}"/></Targets>')
+        out.append('<Segmentation multipleModelMethod="sum">')
+        for t in range(T):
+            out.append(f'<Segment id="{t + 1}"><True/><TreeModel functionName="regression" missingValueStrategy="defaultChild" '
+                       'noTrueChildStrategy="returnNullPrediction" splitCharacteristic="binarySplit">')
+            out += _mining_schema(names)
+            _complete_tree_xml(out, feat[t], thr[t], dleft[t], [_r(v) for v in leaf[t]], names, depth)
+            out.append('</TreeModel></Segment>')
+        out.append('</Segmentation></MiningModel></Segment>')
+    norm = "logit" if n_classes == 2 else "softmax"
+    out.append(f'<Segment id="{K + 1}"><True/><RegressionModel functionName="classification" normalizationMethod="{norm}">')
+    out.append('<MiningSchema><MiningField name="y" usageType="target"/>' + "".join(f'<MiningField name="decisionFunction({k})"/>' for k in range(K)) + '</MiningSchema>')
+    if n_classes == 2:
+        out.append('<RegressionTable intercept="0.0" targetCategory="1"><NumericPredictor name="decisionFunction(0)" coefficient="1.0"/></RegressionTable>')
+        out.append('<RegressionTable intercept="0.0" targetCategory="0"/>')
+    else:
+        for k in range(K):
+            out.append(f'<RegressionTable intercept="0.0" targetCategory="{k}"><NumericPredictor name="decisionFunction({k})" coefficient="1.0"/></RegressionTable>')
+    out.append('</RegressionModel></Segment></Segmentation></MiningModel></PMML>')
+    return "\n".join(out).encode(), {"channels": chans, "n_classes": n_classes}
+
+
+def gbt_classifier_numpy(arrays, X, present=None):
+    """(label, probabilities in RegressionTable order) -- plain numpy restatement of the chain."""
+    dec = np.stack([gbt_numpy(ch, X, present) for ch in arrays["channels"]], axis=1)
+    if arrays["n_classes"] == 2:
+        p1 = 1.0 / (1.0 + np.exp(-(0.0 + 1.0 * dec[:, 0])))
+        probs = np.stack([p1, 1.0 - p1], axis=1)            # table order: "1", then "0"
+        label = np.where(probs[:, 0] >= probs[:, 1], 1.0, 0.0)  # first maximal entry wins ties
+        return label, probs
+    e = np.exp(dec)
+    probs = e / e.sum(axis=1, keepdims=True)
+    return probs.argmax(axis=1).astype(np.float64), probs

@@ -320,6 +320,7 @@ struct Model {
   std::string model_name, function;
   std::vector<MiningField> mining;
   std::vector<TargetSpec> targets;
+  std::vector<std::pair<int, std::string>> outputs;  // <Output> fields: (context slot, feature) -- feed later modelChain segments
   virtual ~Model() = default;
   virtual Result evaluate(const Ctx& cx, std::vector<int>* node_ids) const = 0;
   const MiningField* target_field() const {
@@ -734,6 +735,23 @@ struct MiningModel : Model {
 
   Result evaluate(const Ctx& cx, std::vector<int>* node_ids) const override {
     Result r;
+    if (method == "modelChain") {
+      // segments run in order; a segment's predictedValue output fields become inputs of the later ones; the result is
+      // the last evaluated segment's (this is how boosted-tree classifiers are exported: trees -> link function)
+      Ctx chain = cx; Result last;
+      for (auto& s : segments) {
+        if (eval_pred(s.pred, chain) != T_TRUE) continue;
+        Result sr = s.model->evaluate(chain, nullptr);
+        if (sr.has_value && !sr.is_class) sr.value = apply_target(*s.model, sr.value);
+        for (auto& o : s.model->outputs) {
+          if (o.second != "predictedValue") continue;
+          chain.v[o.first] = !sr.has_value ? FV::missing() : (sr.is_class ? FV::string(sr.label) : FV::number(DT_DOUBLE, sr.value));
+        }
+        last = std::move(sr);
+      }
+      if (node_ids) node_ids->push_back(last.aux);
+      return last;
+    }
     std::vector<std::pair<const Segment*, Result>> res;
     for (auto& s : segments) {
       if (eval_pred(s.pred, cx) != T_TRUE) { if (node_ids) node_ids->push_back(-1); continue; }
@@ -747,7 +765,7 @@ struct MiningModel : Model {
       res.emplace_back(&s, std::move(sr));
     }
     if (method == "selectFirst") return r;  // no segment matched
-    if (method == "selectAll" || method == "modelChain") throw EvalError("unsupported multipleModelMethod " + method);
+    if (method == "selectAll") throw EvalError("unsupported multipleModelMethod " + method);
     if (res.empty()) return r;
     if (function == "regression") {
       // a segment without a result makes the aggregation fail (SURVEY App. A [R]) -> evaluation error
@@ -853,7 +871,10 @@ static const Xml* find_pred(const Xml& e) {
   return nullptr;
 }
 
+static thread_local const Doc* g_doc = nullptr;  // dictionary of the document being loaded (Output fields resolve against it)
 static void load_common(const Xml& e, Model& m) {
+  if (auto* out = e.child("Output"))
+    for (auto* f : out->children("OutputField")) m.outputs.emplace_back(g_doc->slot(f->get("name")), f->get("feature", "predictedValue"));
   m.model_name = e.get("modelName"); m.function = e.get("functionName");
   if (auto* ms = e.child("MiningSchema"))
     for (auto* f : ms->children("MiningField")) {
@@ -1185,6 +1206,17 @@ static std::unique_ptr<Loaded> load(const char* data, size_t len) {
     if (n.size() > 5 && n.substr(n.size() - 5) == "Model" && n != "MiningModel") throw Unsupported("unsupported model element " + n);
   }
   if (!me) throw Unsupported("no supported model element");
+  {  // Output fields anywhere in the model tree are addressable by later modelChain segments: give them context slots
+    std::function<void(const Xml&)> scan = [&](const Xml& x) {
+      if (x.name == "OutputField" && !L->doc.index.count(x.get("name"))) {
+        DataField df; df.name = x.get("name"); df.op = parse_optype(x.get("optype", "continuous")); df.dt = parse_dtype(x.get("dataType", "double"));
+        L->doc.index[df.name] = (int)L->doc.fields.size(); L->doc.fields.push_back(df);
+      }
+      for (auto& k : x.kids) scan(*k);
+    };
+    scan(*me);
+  }
+  g_doc = &L->doc;
   L->model = load_model(*me, L->doc);
   for (auto& mf : L->model->mining) {
     if (mf.usage == "active") { L->active.push_back(&mf); L->active_slots.push_back(L->doc.slot(mf.name)); L->active_names.push_back(mf.name); }

@@ -114,6 +114,21 @@ def test_rf_average_of_leaf_distributions(engine, oracle, gen):
     assert (r["score"] == lab).mean() > 0.999      # numpy sums the same terms; argmax ties aside they agree
 
 
+@pytest.mark.parametrize("n_classes", [2, 3])
+def test_gbt_classifier_model_chain(engine, oracle, gen, n_classes):
+    # boosted-tree classifier as exporters write it: modelChain(sum of trees per class -> logit / softmax RegressionModel)
+    pm, arr = gen.gbt_classifier_pmml(T=40, depth=6, F=30, n_classes=n_classes, seed=51)
+    m, om = engine.compile(pm), oracle.OracleModel(pm)
+    assert "format=complete" in m.describe and "method=9" in m.describe
+    X, pres, pb = gen.events(20000, 30, 52, 0.1)
+    r, o = engine.score(m, X, pb, n_probs=n_classes), om.predict(X, pb, n_probs=n_classes, nthreads=8)
+    compare(r, o, exact_scores=True)                        # labels bit-exact
+    np.testing.assert_allclose(r["probs"], o["probs"], rtol=RTOL)
+    lab, probs = gen.gbt_classifier_numpy(arr, X, pres)
+    assert np.array_equal(r["score"], lab)
+    np.testing.assert_allclose(r["probs"], probs, rtol=1e-9)
+
+
 def test_c3_multinomial_regression(engine, oracle, gen):
     pm, arr = gen.regression_pmml()
     m, om = engine.compile(pm), oracle.OracleModel(pm)

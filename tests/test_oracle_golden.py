@@ -103,3 +103,13 @@ def test_sklearn_cross_check(oracle, gen):
     r = oracle.OracleModel(pm).predict(X)
     assert (r["status"] == 0).all()
     np.testing.assert_allclose(r["score"], gb.predict(X), rtol=1e-9)
+
+
+@pytest.mark.parametrize("n_classes", [2, 4])
+def test_model_chain_classifier_matches_numpy(oracle, gen, n_classes):
+    pm, arr = gen.gbt_classifier_pmml(T=10, depth=4, F=8, n_classes=n_classes, seed=3)
+    X, pres, pb = gen.events(3000, 8, 4, 0.1)
+    r = oracle.OracleModel(pm).predict(X, pb, n_probs=n_classes)
+    lab, probs = gen.gbt_classifier_numpy(arr, X, pres)
+    assert (r["status"] == 0).all() and np.array_equal(r["score"], lab)
+    np.testing.assert_allclose(r["probs"], probs, rtol=1e-12)
