@@ -65,7 +65,8 @@ static void make_describe(fjp_model* m) {
   else if (d.kind == MK_REGRESSION) s += " tables=" + std::to_string(d.reg.n_tables) + " dense=" + std::to_string(d.reg.dense) + " norm=" + std::to_string(d.reg.norm);
   else if (d.kind == MK_GENERAL_REGRESSION) s += " params=" + std::to_string(d.greg.n_params) + " rows=" + std::to_string(d.greg.n_rows) + " type=" + std::to_string(d.greg.model_type) + " link=" + std::to_string(d.greg.link);
   else if (d.kind == MK_NEURAL) s += " inputs=" + std::to_string(d.nn.n_inputs) + " layers=" + std::to_string(d.nn.n_layers) + " max_width=" + std::to_string(d.nn.max_width);
-  s += " F=" + std::to_string(d.F) + " prep_simple=" + std::to_string(d.prep_simple) + " blob_bytes=" + std::to_string(m->cm.blob.size());
+  if (d.derived.n_derived) s += " derived=" + std::to_string(d.derived.n_derived);
+  s += " F=" + std::to_string(d.F_in) + " prep_simple=" + std::to_string(d.prep_simple) + " blob_bytes=" + std::to_string(m->cm.blob.size());
   m->describe = s;
 }
 
@@ -136,6 +137,7 @@ static int enqueue_chunk(fjp_engine* e, fjp_model* m, Slot& s, const HostBatch& 
   size_t oX = c.take((size_t)n * F * 8), oP = hb.present ? c.take((size_t)n * W * 4) : 0, oR = hb.replace ? c.take((size_t)n * 8) : 0;
   size_t oS = c.take((size_t)n * 8), oT = c.take((size_t)n), oA = hb.aux ? c.take((size_t)n * 4) : 0;
   size_t oN = hb.node_ids ? c.take((size_t)n * hb.node_stride * 4) : 0, oQ = hb.probs ? c.take((size_t)n * hb.prob_stride * 8) : 0;
+  const size_t dsz = derived_scratch_bytes(m->dev, n); size_t oD = dsz ? c.take(dsz) : 0;   // augmented rows of models with derived fields
   if (slot_reserve(s, c.off)) return -1;
   BatchArgs a{};
   a.X = reinterpret_cast<double*>(s.buf + oX); a.n = n; a.present_stride = W;
@@ -149,7 +151,7 @@ static int enqueue_chunk(fjp_engine* e, fjp_model* m, Slot& s, const HostBatch& 
   if (hb.node_ids) CK(cudaMemsetAsync(s.buf + oN, 0xFF, (size_t)n * hb.node_stride * 4, s.s));
   if (hb.probs) CK(cudaMemsetAsync(s.buf + oQ, 0xFF, (size_t)n * hb.prob_stride * 8, s.s));
   int launches = 0;
-  CK(launch_score(m->dev, a, s.s, &launches));
+  CK(launch_score_any(m->dev, a, dsz ? s.buf + oD : nullptr, s.s, &launches));
   e->launches += launches;
   CK(cudaMemcpyAsync(hb.score + lo, s.buf + oS, (size_t)n * 8, cudaMemcpyDeviceToHost, s.s));
   CK(cudaMemcpyAsync(hb.status + lo, s.buf + oT, (size_t)n, cudaMemcpyDeviceToHost, s.s));
@@ -175,7 +177,7 @@ static void count_statuses(fjp_engine* e, const uint8_t* st, long n) {
 static bool host_short_circuit(fjp_model* m, const HostBatch& hb) {
   int st = -1;
   if (!m) st = ST_NOMODEL;
-  else if (hb.vec_size != m->cm.dev.F) st = ST_SIZE;
+  else if (hb.vec_size != m->cm.dev.F_in) st = ST_SIZE;
   if (st < 0) return false;
   uint64_t nanbits = 0x7FF8000000000000ULL; double nanv; memcpy(&nanv, &nanbits, 8);
   for (long i = 0; i < hb.n; i++) { hb.score[i] = nanv; hb.status[i] = (uint8_t)st; if (hb.aux) hb.aux[i] = -1; }
@@ -263,7 +265,7 @@ int fjp_model_replicate(fjp_engine* dst, const fjp_model* src, fjp_model** out, 
   *out = m.release(); return 0;
 }
 
-int fjp_model_num_fields(const fjp_model* m) { return m->cm.dev.F; }
+int fjp_model_num_fields(const fjp_model* m) { return m->cm.dev.F_in; }
 const char* fjp_model_field_name(const fjp_model* m, int i) { return (i >= 0 && i < (int)m->cm.active_names.size()) ? m->cm.active_names[i].c_str() : nullptr; }
 const char* fjp_model_name(const fjp_model* m) { return m->cm.model_name.c_str(); }
 const char* fjp_model_family(const fjp_model* m) { return m->cm.family.c_str(); }
@@ -345,6 +347,7 @@ int fjp_score_sparse(fjp_engine* e, fjp_model* m, const int64_t* row_ptr, const 
     size_t oRp = c.take((size_t)(cn + 1) * 8), oIx = c.take((size_t)std::max<int64_t>(nnz, 1) * 4), oVl = c.take((size_t)std::max<int64_t>(nnz, 1) * 8);
     size_t oX = c.take((size_t)cn * F * 8), oP = c.take((size_t)cn * W * 4), oR = replace ? c.take((size_t)cn * 8) : 0;   // oX, oP: scratch for the expanded rows
     size_t oS = c.take((size_t)cn * 8), oT = c.take((size_t)cn), oA = aux ? c.take((size_t)cn * 4) : 0;
+    const size_t dsz = derived_scratch_bytes(m->dev, cn); size_t oD = dsz ? c.take(dsz) : 0;
     if (slot_reserve(s, c.off)) { rc = -1; break; }
     // row_ptr is re-based on the device side by passing shifted index / value pointers
     rc = [&]() -> int {
@@ -361,7 +364,7 @@ int fjp_score_sparse(fjp_engine* e, fjp_model* m, const int64_t* row_ptr, const 
       BatchArgs a{}; a.X = reinterpret_cast<double*>(s.buf + oX); a.present = reinterpret_cast<uint32_t*>(s.buf + oP); a.present_stride = W;
       a.replace = replace ? reinterpret_cast<double*>(s.buf + oR) : nullptr; a.n = cn;
       a.score = reinterpret_cast<double*>(s.buf + oS); a.status = s.buf + oT; a.aux = aux ? reinterpret_cast<int32_t*>(s.buf + oA) : nullptr;
-      CK(launch_score(m->dev, a, s.s, &launches));
+      CK(launch_score_any(m->dev, a, dsz ? s.buf + oD : nullptr, s.s, &launches));
       e->launches += launches;
       CK(cudaMemcpyAsync(score + lo, s.buf + oS, (size_t)cn * 8, cudaMemcpyDeviceToHost, s.s));
       CK(cudaMemcpyAsync(status + lo, s.buf + oT, (size_t)cn, cudaMemcpyDeviceToHost, s.s));
@@ -388,11 +391,17 @@ int fjp_score_device(fjp_engine* e, fjp_model* m, const double* dX, const uint32
   a.score = dscore; a.status = dstatus; a.aux = daux;
   int launches = 0;
   if (!m) { CK(launch_fill_status(a, ST_NOMODEL, st, &launches)); }
-  else if (vec_size != m->cm.dev.F) { CK(launch_fill_status(a, ST_SIZE, st, &launches)); }
+  else if (vec_size != m->cm.dev.F_in) { CK(launch_fill_status(a, ST_SIZE, st, &launches)); }
   else {
     if (!m->d_blob) return fail("model was compiled without an engine: it cannot score");
     if (m->device != e->device) return fail("model lives on another device; use fjp_model_replicate");
-    CK(launch_score(m->dev, a, st, &launches));
+    const size_t dsz = derived_scratch_bytes(m->dev, n);
+    if (dsz) {   // derived fields need a work area for the augmented rows: stream-ordered allocation on the caller's stream
+      void* scratch = nullptr; CK(cudaMallocAsync(&scratch, dsz, st));
+      cudaError_t ce = launch_score_any(m->dev, a, scratch, st, &launches);
+      cudaFreeAsync(scratch, st);
+      if (ce != cudaSuccess) return fail(std::string("scoring kernel: ") + cudaGetErrorString(ce));
+    } else CK(launch_score(m->dev, a, st, &launches));
   }
   e->launches += launches;
   return 0;
@@ -431,7 +440,8 @@ int fjp_wait(fjp_engine* e, int ticket) {
 namespace fjp {
 const DeviceModel* internal_device_model(const fjp_model* m) { return (m && m->d_blob) ? &m->dev : nullptr; }
 int internal_model_device(const fjp_model* m) { return m ? m->device : -1; }
-int internal_model_fields(const fjp_model* m) { return m ? m->cm.dev.F : -1; }
+int internal_model_fields(const fjp_model* m) { return m ? m->cm.dev.F_in : -1; }
+int internal_model_derived(const fjp_model* m) { return m ? m->cm.dev.derived.n_derived : 0; }
 void internal_count_launches(fjp_engine* e, int launches) { if (e) e->launches += launches; }
 void internal_set_error(const char* msg) { g_last_error = msg; }
 }  // namespace fjp

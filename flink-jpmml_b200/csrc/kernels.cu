@@ -1241,6 +1241,146 @@ cudaError_t launch_expand_sparse(const long long* row_ptr, const int32_t* idx, c
   return cudaGetLastError();
 }
 
+__device__ double norm_cont_dev(const double* __restrict__ pts, int n, int outliers, double x, bool& missing) { return norm_cont(pts, n, outliers, x, missing); }
+
+// ================================================================================================ derived fields
+// Pre-pass for models with a TransformationDictionary / LocalTransformations: one thread per event prepares the F_in raw
+// slots (the same preparation every kernel fuses otherwise), runs the DerivedField programs and writes the augmented row
+// (F = F_in + n_derived values + present bits) into scratch memory; the family kernel then scores the augmented rows with
+// an identity preparation, and fixup_kernel puts the pre-pass failures (preparation 2, evaluation 3) back.
+__device__ bool dx_run(const DerivedDesc& dd, int d, const double* __restrict__ row, const uint32_t* __restrict__ bits, double& out) {
+  double sv[DX_STACK]; bool sp[DX_STACK]; int top = 0;
+  auto field = [&](int slot, double& v) { v = row[slot]; return ((bits[slot >> 5] >> (slot & 31)) & 1u) != 0; };
+  for (int i = dd.prog_off[d]; i < dd.prog_off[d + 1]; i++) {
+    const DxOp o = dd.ops[i]; double v = 0; bool p = false;
+    switch (o.op) {
+      case DX_CONST: v = o.x; p = true; break;
+      case DX_FIELD: p = field(o.a, v); if (!p && (o.flags & 1)) { v = o.x; p = true; } break;
+      case DX_NORMDISC: { double f; p = field(o.a, f); if (p) v = java_eq(f, o.z) ? 1.0 : 0.0; else if (o.flags & 1) { v = o.x; p = true; } break; }
+      case DX_NORMCONT: {
+        double f; p = field(o.a, f);
+        if (p) { bool miss = false; v = norm_cont_dev(dd.pool + o.b, o.c, o.outliers, f, miss); p = !miss; }
+        else if (o.flags & 1) { v = o.x; p = true; }
+        break;
+      }
+      case DX_DISCRETIZE: {
+        double f; p = field(o.a, f);
+        if (!p) { if (o.flags & 1) { v = o.x; p = true; } break; }
+        p = false;
+        for (int k = 0; k < o.c && !p; k++) {
+          const double* bn = dd.pool + o.b + 4 * k; int fl = (int)bn[2];
+          bool lo = !(fl & 1) || ((fl & 4) ? f > bn[0] : f >= bn[0]), hi = !(fl & 2) || ((fl & 8) ? f < bn[1] : f <= bn[1]);
+          if (lo && hi) { v = bn[3]; p = true; }
+        }
+        if (!p && (o.flags & 2)) { v = o.y; p = true; }
+        break;
+      }
+      case DX_MAPVALUES: {
+        double f; p = field(o.a, f);
+        if (!p) { if (o.flags & 1) { v = o.x; p = true; } break; }
+        p = false;
+        for (int k = 0; k < o.c && !p; k++) if (java_eq(f, dd.pool[o.b + 2 * k])) { v = dd.pool[o.b + 2 * k + 1]; p = true; }
+        if (!p && (o.flags & 2)) { v = o.y; p = true; }
+        break;
+      }
+      default: {  // DX_APPLY: pops o.b arguments
+        const int n = o.b; const double* a = sv + top - n; const bool* ap = sp + top - n; top -= n;
+        if (o.a == DF_ISMISSING || o.a == DF_ISNOTMISSING) { v = (ap[0] == (o.a == DF_ISNOTMISSING)) ? 1.0 : 0.0; p = true; break; }
+        if (o.a == DF_IF) {
+          if (!ap[0]) { if (o.flags & 1) { v = o.x; p = true; } break; }
+          if (a[0] != 0.0) { v = a[1]; p = ap[1]; } else if (n > 2) { v = a[2]; p = ap[2]; }
+          if (!p && (o.flags & 2)) { v = o.y; p = true; }
+          break;
+        }
+        bool all = true; for (int k = 0; k < n; k++) all = all && ap[k];
+        if (!all) { if (o.flags & 1) { v = o.x; p = true; } break; }
+        p = true;
+        switch (o.a) {
+          case DF_ADD: v = a[0] + a[1]; break; case DF_SUB: v = a[0] - a[1]; break; case DF_MUL: v = a[0] * a[1]; break; case DF_DIV: v = a[0] / a[1]; break;
+          case DF_MIN: v = a[0]; for (int k = 1; k < n; k++) if (java_cmp(a[k], v) < 0) v = a[k]; break;
+          case DF_MAX: v = a[0]; for (int k = 1; k < n; k++) if (java_cmp(a[k], v) > 0) v = a[k]; break;
+          case DF_SUM: v = 0; for (int k = 0; k < n; k++) v += a[k]; break;
+          case DF_AVG: v = 0; for (int k = 0; k < n; k++) v += a[k]; v /= (double)n; break;
+          case DF_PRODUCT: v = 1; for (int k = 0; k < n; k++) v *= a[k]; break;
+          case DF_POW: v = pow(a[0], a[1]); break; case DF_EXP: v = exp(a[0]); break; case DF_LN: v = log(a[0]); break;
+          case DF_LOG10: v = log10(a[0]); break; case DF_SQRT: v = sqrt(a[0]); break; case DF_ABS: v = fabs(a[0]); break;
+          case DF_FLOOR: v = floor(a[0]); break; case DF_CEIL: v = ceil(a[0]); break; case DF_ROUND: v = floor(a[0] + 0.5); break;
+          case DF_THRESHOLD: v = a[0] > a[1] ? 1.0 : 0.0; break;
+          case DF_EQ: v = java_cmp(a[0], a[1]) == 0; break; case DF_NE: v = java_cmp(a[0], a[1]) != 0; break;
+          case DF_LT: v = java_cmp(a[0], a[1]) < 0; break; case DF_LE: v = java_cmp(a[0], a[1]) <= 0; break;
+          case DF_GT: v = java_cmp(a[0], a[1]) > 0; break; case DF_GE: v = java_cmp(a[0], a[1]) >= 0; break;
+          case DF_AND: v = 1; for (int k = 0; k < n; k++) if (a[k] == 0.0) v = 0; break;
+          case DF_OR: v = 0; for (int k = 0; k < n; k++) if (a[k] != 0.0) v = 1; break;
+          case DF_NOT: v = a[0] == 0.0 ? 1.0 : 0.0; break;
+          default: { bool in = false; for (int k = 1; k < n; k++) if (java_cmp(a[0], a[k]) == 0) in = true; v = (in == (o.a == DF_ISIN)) ? 1.0 : 0.0; }
+        }
+      }
+    }
+    sv[top] = v; sp[top] = p; top++;
+  }
+  out = sv[0];
+  return sp[0];
+}
+
+__global__ void __launch_bounds__(128) derive_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, double* __restrict__ X2,
+                                                    uint32_t* __restrict__ P2, uint8_t* __restrict__ pre_status) {
+  long row = blockIdx.x * (long)blockDim.x + threadIdx.x;
+  if (row >= a.n) return;
+  const int F2 = m.F, W2 = (F2 + 31) / 32;
+  double* xr = X2 + row * (long)F2; uint32_t* pr = P2 + row * (long)W2;
+  for (int w = 0; w < W2; w++) pr[w] = 0u;
+  int status = 0;
+  double rep = 0; bool has_rep = false;
+  if (a.replace) { rep = a.replace[row]; has_rep = rep == rep; }
+  for (int f = 0; f < m.F_in; f++) {
+    double raw = a.X[row * (long)m.F_in + f];
+    bool present = a.present ? ((a.present[row * (long)a.present_stride + (f >> 5)] >> (f & 31)) & 1u) : true;
+    if (!present && has_rep) { raw = rep; present = true; }
+    double v = 0; int st = prep_value(m.prep_in[f], m.prep_in_pool, present, raw, v);
+    if (st == 2) status = ST_PREP;
+    xr[f] = v; if (st == 0) pr[f >> 5] |= 1u << (f & 31);
+  }
+  if (status == 0) {
+    for (int d = 0; d < m.derived.n_derived; d++) {
+      double v; bool p = dx_run(m.derived, d, xr, pr, v); const int slot = m.F_in + d;
+      if (p) {
+        const int dt = m.derived.dtype[d];
+        if (dt == DT_FLOAT) v = (double)(float)v;
+        else if (dt == DT_INTEGER && !(isfinite(v) && v == floor(v))) { status = ST_EVAL; break; }
+        xr[slot] = v; pr[slot >> 5] |= 1u << (slot & 31);
+      } else xr[slot] = 0.0;
+    }
+  }
+  pre_status[row] = (uint8_t)status;
+}
+__global__ void fixup_kernel(BatchArgs a, const uint8_t* __restrict__ pre_status) {
+  long row = blockIdx.x * (long)blockDim.x + threadIdx.x;
+  if (row < a.n && pre_status[row]) write_out(a, row, 0, pre_status[row], -1);
+}
+
+size_t derived_scratch_bytes(const DeviceModel& m, long n) {
+  if (m.derived.n_derived == 0) return 0;
+  size_t x = ((size_t)n * m.F * 8 + 255) & ~size_t(255), p = ((size_t)n * ((m.F + 31) / 32) * 4 + 255) & ~size_t(255);
+  return x + p + (((size_t)n + 255) & ~size_t(255));
+}
+// launch_score for any model: with derived fields, `scratch` must hold derived_scratch_bytes(m, a.n) bytes
+cudaError_t launch_score_any(const DeviceModel& m, const BatchArgs& a, void* scratch, cudaStream_t s, int* launches) {
+  if (m.derived.n_derived == 0) return launch_score(m, a, s, launches);
+  if (a.n <= 0) return cudaSuccess;
+  if (!scratch) return cudaErrorInvalidValue;
+  uint8_t* base = static_cast<uint8_t*>(scratch);
+  size_t x = ((size_t)a.n * m.F * 8 + 255) & ~size_t(255), p = ((size_t)a.n * ((m.F + 31) / 32) * 4 + 255) & ~size_t(255);
+  double* X2 = reinterpret_cast<double*>(base); uint32_t* P2 = reinterpret_cast<uint32_t*>(base + x); uint8_t* pre = base + x + p;
+  if (launches) (*launches)++;
+  derive_kernel<<<(unsigned)((a.n + 127) / 128), 128, 0, s>>>(m, a, X2, P2, pre);
+  cudaError_t e = cudaGetLastError(); if (e != cudaSuccess) return e;
+  BatchArgs b = a; b.X = X2; b.present = P2; b.present_stride = (m.F + 31) / 32; b.replace = nullptr;
+  e = launch_score(m, b, s, launches); if (e != cudaSuccess) return e;
+  if (launches) (*launches)++;
+  fixup_kernel<<<(unsigned)((a.n + 255) / 256), 256, 0, s>>>(a, pre);
+  return cudaGetLastError();
+}
+
 // Fills status for a whole batch without looking at the data: size mismatch (1) and unknown model (5).
 __global__ void fill_status_kernel(BatchArgs a, int status) {
   long row = blockIdx.x * (long)blockDim.x + threadIdx.x;

@@ -33,6 +33,8 @@ bool plan_forest_complete(const DeviceModel& m, ForestLaunch* out);
 cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t s, int* launches);
 cudaError_t launch_expand_sparse(const long long* row_ptr, const int32_t* idx, const double* val, long n, int F,
                                  double* X, uint32_t* present, cudaStream_t s, int* launches);
+size_t derived_scratch_bytes(const DeviceModel& m, long n);
+cudaError_t launch_score_any(const DeviceModel& m, const BatchArgs& a, void* scratch, cudaStream_t s, int* launches);
 cudaError_t launch_fill_status(const BatchArgs& a, int status, cudaStream_t s, int* launches);
 
 }  // namespace fjp

@@ -148,8 +148,33 @@ struct NeuralDesc {
   int out_denorm_off, out_denorm_n;  // regression: NormContinuous of the output to invert (n = 0: none)
 };
 
+// ---- derived fields (TransformationDictionary / LocalTransformations) ---------------------------------------------
+// Every DerivedField is a postfix program over a small value stack (value, present).  A pre-pass kernel prepares the raw
+// slots, runs the programs and writes an augmented row [F_in raw + n_derived] that the family kernel then reads.
+enum : int { DX_CONST = 0, DX_FIELD, DX_NORMDISC, DX_NORMCONT, DX_DISCRETIZE, DX_MAPVALUES, DX_APPLY };
+enum : int { DF_ADD = 0, DF_SUB, DF_MUL, DF_DIV, DF_MIN, DF_MAX, DF_SUM, DF_AVG, DF_PRODUCT, DF_POW, DF_EXP, DF_LN, DF_LOG10, DF_SQRT,
+             DF_ABS, DF_FLOOR, DF_CEIL, DF_ROUND, DF_THRESHOLD, DF_EQ, DF_NE, DF_LT, DF_LE, DF_GT, DF_GE, DF_AND, DF_OR, DF_NOT,
+             DF_ISIN, DF_ISNOTIN, DF_IF, DF_ISMISSING, DF_ISNOTMISSING };
+struct DxOp {
+  int32_t op, a, b, c, flags;   // a: field slot / function id; b, c: pool offset + count, or argument count; flags: 1 mapMissingTo, 2 defaultValue
+  int32_t outliers;             // NORMCONT: 0 asIs, 1 asMissingValues, 2 asExtremeValues
+  double x, y, z;               // x: constant / match / mapMissingTo value, y: defaultValue, z: spare
+};
+static constexpr int DX_STACK = 16;
+struct DerivedDesc {
+  int n_derived;
+  const int32_t* prog_off;   // n_derived + 1
+  const DxOp* ops;
+  const double* pool;        // LinearNorm pairs, Discretize bins (l, r, flags, value), MapValues pairs
+  const uint8_t* dtype;      // n_derived: dataType of the derived field (double / float / integer)
+};
+
 struct DeviceModel {
   int kind, F, prep_simple, n_labels;
+  int F_in;                  // size of the caller's vectors (= F without derived fields; F = F_in + derived.n_derived with them)
+  const PrepField* prep_in; const double* prep_in_pool;   // preparation of the F_in raw slots (used by the pre-pass when deriving)
+  int prep_in_simple;
+  DerivedDesc derived;
   int prep_identity;  // every active field is a plain double: a present value is used as is
   int target_status;  // 0, or ST_EXTRACT when no result can ever be extracted (no named target / non-double target)
   const PrepField* prep; const double* prep_pool;

@@ -66,6 +66,8 @@ extern "C" int fjp_score_sparse_noalloc(fjp_engine* e, fjp_model* m, const int64
   if (device < 0 || device >= kMaxDevices) return noalloc_fail("fjp_score_sparse_noalloc: device ordinal out of range");
   if (vec_size != internal_model_fields(m))
     return noalloc_fail("fjp_score_sparse_noalloc: vec_size differs from the model's number of active fields");
+  if (internal_model_derived(m) > 0)
+    return noalloc_fail("fjp_score_sparse_noalloc: models with derived fields need a larger work area than the built-in one; use fjp_score_sparse");
   const int W = (vec_size + 31) / 32;
   const size_t x_bytes = ((size_t)n * vec_size * 8 + 255) & ~size_t(255), p_bytes = (size_t)n * W * 4;
   if (x_bytes + p_bytes > (size_t)FJP_NOALLOC_SCRATCH_BYTES)

@@ -156,7 +156,6 @@ void read_dictionary(const XNode& root, Builder& b) {
     Field fl{std::string(f.attr("name")), dtype_of(f.attr("dataType")), f.attr("optype") == "continuous", &f};
     b.dict_idx[fl.name] = (int)b.dict.size(); b.dict.push_back(fl);
   });
-  if (const XNode* td = root.child("TransformationDictionary")) if (td->first) unsupported("TransformationDictionary");
 }
 
 void check_nested_schema(const XNode& model) {
@@ -172,7 +171,6 @@ void check_nested_schema(const XNode& model) {
 void read_schema(const XNode& model, Builder& b) {
   const XNode* ms = model.child("MiningSchema");
   if (!ms) malformed("no MiningSchema");
-  if (const XNode* lt = model.child("LocalTransformations")) if (lt->first) unsupported("LocalTransformations");
   std::vector<PrepField> prep; std::vector<double> pool; bool simple = true, identity = true;
   ms->each("MiningField", [&](const XNode& f) {
     sv usage = f.attr("usageType", "active");
@@ -227,7 +225,9 @@ void read_schema(const XNode& model, Builder& b) {
     b.cm.active_names.push_back(name); prep.push_back(p);
   });
   b.cm.dev.F = (int)prep.size(); b.cm.dev.prep_simple = simple ? 1 : 0; b.cm.dev.prep_identity = identity ? 1 : 0;
+  b.cm.dev.F_in = b.cm.dev.F; b.cm.dev.prep_in_simple = simple ? 1 : 0;
   b.put(&b.cm.dev.prep, prep); b.put(&b.cm.dev.prep_pool, pool);
+  b.put(&b.cm.dev.prep_in, prep); b.put(&b.cm.dev.prep_in_pool, pool);
   // <Targets>
   TargetXform tx{1.0, 0.0, 0.0, 0.0, 0, 0, 0};
   if (const XNode* ts = model.child("Targets")) {
@@ -244,6 +244,118 @@ void read_schema(const XNode& model, Builder& b) {
     });
   }
   b.cm.dev.tx = tx;
+}
+
+// ---------------------------------------------------------------------------------------------- derived fields
+struct DerivedCompiler {
+  Builder& b; std::vector<DxOp> ops; std::vector<double> pool;
+  explicit DerivedCompiler(Builder& bb) : b(bb) {}
+  static DxOp mk(int op) { DxOp o{}; o.op = op; return o; }
+  int numeric_slot(sv field) {
+    uint8_t dt = b.dict_field(field).dtype;
+    if (dt == DT_STRING || dt == DT_OTHER) unsupported("transformation of a non-numeric field");
+    int s = b.slot_of(field);
+    if (s < 0) unsupported("transformation of a field that is not an active field");
+    return s;
+  }
+  void opt(const XNode& e, DxOp& o) {
+    if (e.has("mapMissingTo")) { o.flags |= 1; o.x = need_double(e.attr("mapMissingTo"), "mapMissingTo"); }
+    if (e.has("defaultValue")) { o.flags |= 2; o.y = need_double(e.attr("defaultValue"), "defaultValue"); }
+  }
+  void emit(const XNode& e, int depth) {
+    if (depth > DX_STACK - 2) unsupported("transformation nested deeper than 14 levels");
+    if (e.name == "Constant") { DxOp o = mk(DX_CONST); o.x = need_double(e.text, "Constant"); ops.push_back(o); return; }
+    if (e.name == "FieldRef") { DxOp o = mk(DX_FIELD); o.a = numeric_slot(e.attr("field")); opt(e, o); ops.push_back(o); return; }
+    if (e.name == "NormDiscrete") {
+      DxOp o = mk(DX_NORMDISC); o.a = numeric_slot(e.attr("field")); opt(e, o);
+      if (!parse_in_dtype(b.dict_field(e.attr("field")).dtype, e.attr("value"), &o.z)) unsupported("NormDiscrete value does not parse in the field's dataType");
+      ops.push_back(o); return;
+    }
+    if (e.name == "NormContinuous") {
+      DxOp o = mk(DX_NORMCONT); o.a = numeric_slot(e.attr("field")); opt(e, o); o.b = (int32_t)pool.size();
+      sv ol = e.attr("outliers", "asIs"); o.outliers = ol == "asMissingValues" ? 1 : ol == "asExtremeValues" ? 2 : 0;
+      e.each("LinearNorm", [&](const XNode& ln) { pool.push_back(need_double(ln.attr("orig"), "orig")); pool.push_back(need_double(ln.attr("norm"), "norm")); o.c++; });
+      if (o.c < 2) malformed("NormContinuous needs two LinearNorm");
+      ops.push_back(o); return;
+    }
+    if (e.name == "Discretize") {
+      DxOp o = mk(DX_DISCRETIZE); o.a = numeric_slot(e.attr("field")); opt(e, o); o.b = (int32_t)pool.size();
+      e.each("DiscretizeBin", [&](const XNode& bin) {
+        const XNode* iv = bin.child("Interval"); if (!iv) malformed("DiscretizeBin without Interval");
+        sv c = iv->attr("closure"); double flags = 0, lo = 0, hi = 0;
+        if (iv->has("leftMargin")) { flags += 1; lo = need_double(iv->attr("leftMargin"), "leftMargin"); }
+        if (iv->has("rightMargin")) { flags += 2; hi = need_double(iv->attr("rightMargin"), "rightMargin"); }
+        if (c.substr(0, 4) == "open") flags += 4;
+        if (c.size() >= 4 && c.substr(c.size() - 4) == "Open") flags += 8;
+        pool.push_back(lo); pool.push_back(hi); pool.push_back(flags); pool.push_back(need_double(bin.attr("binValue"), "binValue")); o.c++;
+      });
+      ops.push_back(o); return;
+    }
+    if (e.name == "MapValues") {
+      DxOp o = mk(DX_MAPVALUES); opt(e, o); o.b = (int32_t)pool.size();
+      if (e.count("FieldColumnPair") != 1) unsupported("MapValues with several FieldColumnPairs");
+      const XNode& fc = *e.child("FieldColumnPair"); o.a = numeric_slot(fc.attr("field"));
+      sv in_col = fc.attr("column"), out_col = e.attr("outputColumn");
+      const XNode* tbl = e.child("InlineTable"); if (!tbl) unsupported("MapValues without InlineTable");
+      uint8_t dt = b.dict_field(fc.attr("field")).dtype;
+      tbl->each("row", [&](const XNode& row) {
+        const XNode* i = row.child(in_col); const XNode* ot = row.child(out_col);
+        if (!i || !ot) malformed("MapValues row without both columns");
+        double iv; if (!parse_in_dtype(dt == DT_FLOAT ? DT_DOUBLE : dt, i->text, &iv)) unsupported("MapValues input does not parse as a number");
+        pool.push_back(iv); pool.push_back(need_double(ot->text, "MapValues output")); o.c++;
+      });
+      ops.push_back(o); return;
+    }
+    if (e.name == "Apply") {
+      static const char* fn[] = {"+", "-", "*", "/", "min", "max", "sum", "avg", "product", "pow", "exp", "ln", "log10", "sqrt", "abs", "floor", "ceil",
+                                 "round", "threshold", "equal", "notEqual", "lessThan", "lessOrEqual", "greaterThan", "greaterOrEqual", "and", "or", "not",
+                                 "isIn", "isNotIn", "if", "isMissing", "isNotMissing"};
+      sv f = e.attr("function"); int id = -1;
+      for (int i = 0; i < 33; i++) if (f == fn[i]) id = i;
+      if (id < 0) unsupported("Apply function " + std::string(f));
+      int nargs = 0;
+      for (const XNode* k = e.first; k; k = k->next) if (k->name != "Extension") { emit(*k, depth + nargs); nargs++; }
+      static const int arity[] = {2, 2, 2, 2, -1, -1, -1, -1, -1, 2, 1, 1, 1, 1, 1, 1, 1, 1, 2, 2, 2, 2, 2, 2, 2, -1, -1, 1, -2, -2, -3, 1, 1};
+      int ar = arity[id];
+      if ((ar > 0 && nargs != ar) || (ar == -1 && nargs < 1) || (ar == -2 && nargs < 2) || (ar == -3 && (nargs < 2 || nargs > 3)) || depth + nargs > DX_STACK)
+        unsupported("Apply " + std::string(f) + " with " + std::to_string(nargs) + " arguments");
+      DxOp o = mk(DX_APPLY); o.a = id; o.b = nargs; opt(e, o); ops.push_back(o); return;
+    }
+    unsupported("transformation element " + std::string(e.name));
+  }
+};
+
+// TransformationDictionary + the top-level model's LocalTransformations.  Derived field d becomes slot F_in + d of the
+// augmented row; everything compiled after this sees it like any other numeric field.
+void read_derived(const XNode& root, const XNode& model, Builder& b) {
+  std::vector<const XNode*> fields;
+  if (const XNode* td = root.child("TransformationDictionary")) {
+    if (td->child("DefineFunction")) unsupported("DefineFunction");
+    td->each("DerivedField", [&](const XNode& f) { fields.push_back(&f); });
+  }
+  if (const XNode* lt = model.child("LocalTransformations")) lt->each("DerivedField", [&](const XNode& f) { fields.push_back(&f); });
+  DerivedDesc& dd = b.cm.dev.derived; dd.n_derived = (int)fields.size();
+  DerivedCompiler dc(b); std::vector<int32_t> prog_off{0}; std::vector<uint8_t> dtypes;
+  for (const XNode* f : fields) {
+    uint8_t dt = dtype_of(f->attr("dataType", "double"));
+    if (dt != DT_DOUBLE && dt != DT_FLOAT && dt != DT_INTEGER) unsupported("non-numeric DerivedField");
+    const XNode* ex = nullptr;
+    for (const XNode* k = f->first; k && !ex; k = k->next) if (k->name != "Extension" && k->name != "Value") ex = k;
+    if (!ex) malformed("DerivedField without expression");
+    dc.emit(*ex, 0);
+    prog_off.push_back((int32_t)dc.ops.size()); dtypes.push_back(dt);
+    std::string name(f->attr("name"));
+    Field fl{name, dt, f->attr("optype", "continuous") == "continuous", nullptr};
+    b.dict_idx[name] = (int)b.dict.size(); b.dict.push_back(fl);
+    b.active_slot[name] = b.cm.dev.F; b.slot_dtype.push_back(dt); b.cm.dev.F++;
+  }
+  b.put(&dd.prog_off, prog_off); b.put(&dd.ops, dc.ops); b.put(&dd.pool, dc.pool); b.put(&dd.dtype, dtypes);
+  if (dd.n_derived) {   // the family kernel reads already prepared values: identity preparation over the augmented row
+    std::vector<PrepField> ident(b.cm.dev.F); std::vector<double> nopool;
+    for (auto& p : ident) { memset(&p, 0, sizeof(p)); p.dtype = DT_DOUBLE; p.continuous = 1; }
+    b.put(&b.cm.dev.prep, ident); b.put(&b.cm.dev.prep_pool, nopool);
+    b.cm.dev.prep_simple = 1; b.cm.dev.prep_identity = 1;
+  }
 }
 
 // ---------------------------------------------------------------------------------------------- clustering
@@ -937,6 +1049,7 @@ CompiledModel compile_pmml(const char* data, size_t len) {
   if (!me) malformed("no model element");
   b.cm.model_name = std::string(me->attr("modelName"));
   read_schema(*me, b);
+  read_derived(root, *me, b);
   if (me->name == "ClusteringModel") compile_clustering(*me, b);
   else if (me->name == "TreeModel") compile_tree(*me, b);
   else if (me->name == "MiningModel") compile_mining(*me, b);

@@ -297,6 +297,93 @@ static Tri eval_pred(const Predicate& p, const Ctx& cx) {
   return T_UNKNOWN;
 }
 
+// ------------------------------------------------------------------------------------------ derived fields
+// TransformationDictionary / LocalTransformations <DerivedField> expressions over numeric fields (PMML 4.3 Transformations):
+// Constant, FieldRef, NormContinuous, NormDiscrete, Discretize, MapValues (one numeric column), Apply (built-in functions).
+// A value is a double or missing; booleans are 1.0 / 0.0.  Unless a function says otherwise a missing argument gives a
+// missing result (then mapMissingTo applies); a missing result with all arguments present gets defaultValue.
+struct DExpr {
+  enum Kind { CONST, FIELD, NORMCONT, NORMDISC, DISCRETIZE, MAPVALUES, APPLY } kind = CONST;
+  double constant = 0; int slot = -1; std::string function;
+  std::optional<double> map_missing, dflt;
+  std::vector<std::pair<double, double>> pts; int outliers = 0;     // NORMCONT
+  double match = 0;                                                  // NORMDISC
+  struct Bin { bool has_l, has_r, open_l, open_r; double l, r, value; };
+  std::vector<Bin> bins;                                             // DISCRETIZE
+  std::vector<std::pair<double, double>> pairs;                      // MAPVALUES in -> out
+  std::vector<DExpr> args;                                           // APPLY; NORMCONT/NORMDISC/... read `slot`
+
+  bool eval(const Ctx& cx, double* out) const {   // false = missing
+    switch (kind) {
+      case CONST: *out = constant; return true;
+      case FIELD: { const FV& v = cx.v[slot]; if (v.is_missing()) return fill(map_missing, out); if (v.kind != FV::NUM) throw EvalError("non-numeric FieldRef"); *out = v.num; return true; }
+      case NORMDISC: { const FV& v = cx.v[slot]; if (v.is_missing()) return fill(map_missing, out); *out = java_compare(v.num, match) == 0 ? 1.0 : 0.0; return true; }
+      case NORMCONT: {
+        const FV& v = cx.v[slot]; if (v.is_missing()) return fill(map_missing, out);
+        double x = v.num; size_t n = pts.size();
+        auto interp = [&](size_t i) { return pts[i].second + (x - pts[i].first) / (pts[i + 1].first - pts[i].first) * (pts[i + 1].second - pts[i].second); };
+        if (x < pts[0].first) { if (outliers == 1) return false; *out = outliers == 2 ? pts[0].second : interp(0); return true; }
+        if (x > pts[n - 1].first) { if (outliers == 1) return false; *out = outliers == 2 ? pts[n - 1].second : interp(n - 2); return true; }
+        size_t i = 0; while (i + 2 < n && x > pts[i + 1].first) i++;
+        *out = interp(i); return true;
+      }
+      case DISCRETIZE: {
+        const FV& v = cx.v[slot]; if (v.is_missing()) return fill(map_missing, out);
+        for (auto& b : bins) {
+          bool lo = !b.has_l || (b.open_l ? v.num > b.l : v.num >= b.l), hi = !b.has_r || (b.open_r ? v.num < b.r : v.num <= b.r);
+          if (lo && hi) { *out = b.value; return true; }
+        }
+        return fill(dflt, out);
+      }
+      case MAPVALUES: {
+        const FV& v = cx.v[slot]; if (v.is_missing()) return fill(map_missing, out);
+        for (auto& p : pairs) if (java_compare(v.num, p.first) == 0) { *out = p.second; return true; }
+        return fill(dflt, out);
+      }
+      case APPLY: return apply(cx, out);
+    }
+    return false;
+  }
+  static bool fill(const std::optional<double>& v, double* out) { if (v) { *out = *v; return true; } return false; }
+
+  bool apply(const Ctx& cx, double* out) const {
+    const std::string& f = function; size_t n = args.size();
+    if (f == "isMissing" || f == "isNotMissing") { double t; bool present = args.at(0).eval(cx, &t); *out = (present == (f == "isNotMissing")) ? 1.0 : 0.0; return true; }
+    if (f == "if") {
+      double c; if (!args.at(0).eval(cx, &c)) return fill(map_missing, out);
+      if (c != 0.0) { if (args.at(1).eval(cx, out)) return true; return fill(dflt, out); }
+      if (n > 2) { if (args[2].eval(cx, out)) return true; }
+      return fill(dflt, out);
+    }
+    std::vector<double> a(n);
+    for (size_t i = 0; i < n; i++) if (!args[i].eval(cx, &a[i])) return fill(map_missing, out);
+    auto need = [&](size_t k) { if (n != k) throw EvalError("wrong number of arguments for " + f); };
+    double r;
+    if (f == "+") { need(2); r = a[0] + a[1]; } else if (f == "-") { need(2); r = a[0] - a[1]; }
+    else if (f == "*") { need(2); r = a[0] * a[1]; } else if (f == "/") { need(2); r = a[0] / a[1]; }
+    else if (f == "min") { r = a.at(0); for (double v : a) if (java_compare(v, r) < 0) r = v; }
+    else if (f == "max") { r = a.at(0); for (double v : a) if (java_compare(v, r) > 0) r = v; }
+    else if (f == "sum") { r = 0; for (double v : a) r += v; }
+    else if (f == "avg") { r = 0; for (double v : a) r += v; r /= (double)n; }
+    else if (f == "product") { r = 1; for (double v : a) r *= v; }
+    else if (f == "pow") { need(2); r = std::pow(a[0], a[1]); }
+    else if (f == "exp") { need(1); r = std::exp(a[0]); } else if (f == "ln") { need(1); r = std::log(a[0]); }
+    else if (f == "log10") { need(1); r = std::log10(a[0]); } else if (f == "sqrt") { need(1); r = std::sqrt(a[0]); }
+    else if (f == "abs") { need(1); r = std::fabs(a[0]); } else if (f == "floor") { need(1); r = std::floor(a[0]); }
+    else if (f == "ceil") { need(1); r = std::ceil(a[0]); } else if (f == "round") { need(1); r = std::floor(a[0] + 0.5); }
+    else if (f == "threshold") { need(2); r = a[0] > a[1] ? 1.0 : 0.0; }
+    else if (f == "equal") { need(2); r = java_compare(a[0], a[1]) == 0; } else if (f == "notEqual") { need(2); r = java_compare(a[0], a[1]) != 0; }
+    else if (f == "lessThan") { need(2); r = java_compare(a[0], a[1]) < 0; } else if (f == "lessOrEqual") { need(2); r = java_compare(a[0], a[1]) <= 0; }
+    else if (f == "greaterThan") { need(2); r = java_compare(a[0], a[1]) > 0; } else if (f == "greaterOrEqual") { need(2); r = java_compare(a[0], a[1]) >= 0; }
+    else if (f == "and") { r = 1; for (double v : a) if (v == 0.0) r = 0; } else if (f == "or") { r = 0; for (double v : a) if (v != 0.0) r = 1; }
+    else if (f == "not") { need(1); r = a[0] == 0.0 ? 1.0 : 0.0; }
+    else if (f == "isIn" || f == "isNotIn") { bool in = false; for (size_t i = 1; i < n; i++) if (java_compare(a[0], a[i]) == 0) in = true; r = (in == (f == "isIn")) ? 1.0 : 0.0; }
+    else throw EvalError("unsupported Apply function " + f);
+    *out = r; return true;
+  }
+};
+struct DerivedField { int slot; DType dt; DExpr expr; };
+
 // ------------------------------------------------------------------------------------------ model results
 struct Result {
   bool has_value = false;        // regression value or classification label present
@@ -898,8 +985,6 @@ static void load_common(const Xml& e, Model& m) {
       s.cast = t->get("castInteger");
       m.targets.push_back(s);
     }
-  if (e.child("LocalTransformations") && !e.child("LocalTransformations")->kids.empty())
-    throw Unsupported("LocalTransformations are not supported");
 }
 
 static Expr load_expr(const Xml& derived, const Doc& d) {
@@ -917,6 +1002,52 @@ static Expr load_expr(const Xml& derived, const Doc& d) {
     }
   }
   throw Unsupported("unsupported DerivedField expression");
+}
+
+static DExpr load_dexpr(const Xml& e, const Doc& d) {
+  DExpr x;
+  auto opt = [&](const char* k) -> std::optional<double> { if (auto* a = e.attr(k)) return to_d(*a, k); return std::nullopt; };
+  auto numeric_slot = [&](const std::string& f) { int sl = d.slot(f); DType dt = d.fields[sl].dt; if (dt == DT_STRING || dt == DT_OTHER) throw Unsupported("transformation of a non-numeric field"); return sl; };
+  if (e.name == "Constant") { x.kind = DExpr::CONST; x.constant = to_d(trim(e.text), "Constant"); return x; }
+  if (e.name == "FieldRef") { x.kind = DExpr::FIELD; x.slot = numeric_slot(e.get("field")); x.map_missing = opt("mapMissingTo"); return x; }
+  if (e.name == "NormDiscrete") { x.kind = DExpr::NORMDISC; x.slot = numeric_slot(e.get("field")); x.match = to_d(e.get("value"), "NormDiscrete value"); x.map_missing = opt("mapMissingTo"); return x; }
+  if (e.name == "NormContinuous") {
+    x.kind = DExpr::NORMCONT; x.slot = numeric_slot(e.get("field")); x.map_missing = opt("mapMissingTo");
+    std::string o = e.get("outliers", "asIs"); x.outliers = o == "asMissingValues" ? 1 : (o == "asExtremeValues" ? 2 : 0);
+    for (auto* ln : e.children("LinearNorm")) x.pts.emplace_back(to_d(ln->get("orig"), "orig"), to_d(ln->get("norm"), "norm"));
+    if (x.pts.size() < 2) throw Unsupported("NormContinuous needs two LinearNorm");
+    return x;
+  }
+  if (e.name == "Discretize") {
+    x.kind = DExpr::DISCRETIZE; x.slot = numeric_slot(e.get("field")); x.map_missing = opt("mapMissingTo"); x.dflt = opt("defaultValue");
+    for (auto* b : e.children("DiscretizeBin")) {
+      DExpr::Bin bin{false, false, false, false, 0, 0, to_d(b->get("binValue"), "binValue")};
+      const Xml* iv = b->child("Interval"); if (!iv) throw Unsupported("DiscretizeBin without Interval");
+      std::string c = iv->get("closure"); bin.open_l = c.rfind("open", 0) == 0; bin.open_r = c.size() >= 4 && c.substr(c.size() - 4) == "Open";
+      if (auto* a = iv->attr("leftMargin")) { bin.has_l = true; bin.l = to_d(*a, "leftMargin"); }
+      if (auto* a = iv->attr("rightMargin")) { bin.has_r = true; bin.r = to_d(*a, "rightMargin"); }
+      x.bins.push_back(bin);
+    }
+    return x;
+  }
+  if (e.name == "MapValues") {
+    x.kind = DExpr::MAPVALUES; x.map_missing = opt("mapMissingTo"); x.dflt = opt("defaultValue");
+    auto pairs = e.children("FieldColumnPair"); if (pairs.size() != 1) throw Unsupported("MapValues with several FieldColumnPairs");
+    x.slot = numeric_slot(pairs[0]->get("field")); std::string in_col = pairs[0]->get("column"), out_col = e.get("outputColumn");
+    const Xml* tbl = e.child("InlineTable"); if (!tbl) throw Unsupported("MapValues without InlineTable");
+    for (auto* row : tbl->children("row")) {
+      const Xml* i = row->child(in_col.c_str()); const Xml* o = row->child(out_col.c_str());
+      if (!i || !o) throw Unsupported("MapValues row without both columns");
+      x.pairs.emplace_back(to_d(trim(i->text), "MapValues input"), to_d(trim(o->text), "MapValues output"));
+    }
+    return x;
+  }
+  if (e.name == "Apply") {
+    x.kind = DExpr::APPLY; x.function = e.get("function"); x.map_missing = opt("mapMissingTo"); x.dflt = opt("defaultValue");
+    for (auto& k : e.kids) if (k->name != "Extension") x.args.push_back(load_dexpr(*k, d));
+    return x;
+  }
+  throw Unsupported("unsupported transformation element " + e.name);
 }
 
 static std::unique_ptr<Model> load_model(const Xml& e, const Doc& d);
@@ -1090,6 +1221,7 @@ struct Loaded {
   // target extraction (Pipeline.scala:61-98): first *named* target field
   bool has_named_target = false; DType target_dt = DT_DOUBLE;
   int n_segments = 0;
+  std::vector<DerivedField> derived;   // TransformationDictionary then LocalTransformations, document order
 };
 
 enum Status : uint8_t { ST_OK = 0, ST_SIZE = 1, ST_PREP = 2, ST_EVAL = 3, ST_EXTRACT = 4, ST_NOMODEL = 5 };
@@ -1157,7 +1289,16 @@ static void predict_one(const Loaded& L, const double* x, const uint32_t* presen
     }
   } catch (PrepError&) { *status = ST_PREP; return; }
   Result r;
-  try { r = L.model->evaluate(cx, node_ids); }                        // evaluateInput :159-160
+  try {
+    for (auto& df : L.derived) {   // derived fields see the prepared values and the derived fields before them
+      double v;
+      if (!df.expr.eval(cx, &v)) { cx.v[df.slot] = FV::missing(); continue; }
+      if (df.dt == DT_FLOAT) v = (double)(float)v;
+      else if (df.dt == DT_INTEGER && !(std::isfinite(v) && v == std::floor(v))) throw EvalError("derived value is not an integer");
+      cx.v[df.slot] = FV::number(df.dt, v);
+    }
+    r = L.model->evaluate(cx, node_ids);
+  }                        // evaluateInput :159-160
   catch (EvalError&) { *status = ST_EVAL; return; }
   if (probs) { for (auto& p : r.probs) probs->push_back(p.second); }
   if (aux) *aux = r.aux;
@@ -1197,8 +1338,11 @@ static std::unique_ptr<Loaded> load(const char* data, size_t len) {
     }
     L->doc.index[df.name] = (int)L->doc.fields.size(); L->doc.fields.push_back(df);
   }
-  if (root->child("TransformationDictionary") && !root->child("TransformationDictionary")->kids.empty())
-    throw Unsupported("TransformationDictionary is not supported");
+  std::vector<const Xml*> derived_xml;
+  if (auto* td = root->child("TransformationDictionary")) {
+    if (td->child("DefineFunction")) throw Unsupported("DefineFunction is not supported");
+    for (auto* f : td->children("DerivedField")) derived_xml.push_back(f);
+  }
   const Xml* me = nullptr;
   for (auto& k : root->kids) {
     const std::string& n = k->name;
@@ -1206,6 +1350,24 @@ static std::unique_ptr<Loaded> load(const char* data, size_t len) {
     if (n.size() > 5 && n.substr(n.size() - 5) == "Model" && n != "MiningModel") throw Unsupported("unsupported model element " + n);
   }
   if (!me) throw Unsupported("no supported model element");
+  if (auto* lt = me->child("LocalTransformations")) for (auto* f : lt->children("DerivedField")) derived_xml.push_back(f);
+  {  // transformations inside nested models are out of scope
+    std::function<void(const Xml&, int)> scan = [&](const Xml& x, int depth) {
+      if (x.name == "LocalTransformations" && depth > 1 && !x.kids.empty()) throw Unsupported("LocalTransformations in a nested model");
+      for (auto& k : x.kids) scan(*k, depth + 1);
+    };
+    scan(*me, 0);
+  }
+  for (auto* f : derived_xml) {   // each derived field gets a context slot; its expression may use the ones before it
+    DType dt = parse_dtype(f->get("dataType", "double"));
+    if (dt == DT_STRING || dt == DT_OTHER || dt == DT_BOOLEAN) throw Unsupported("non-numeric DerivedField");
+    const Xml* ex = nullptr; for (auto& k : f->kids) if (k->name != "Extension" && k->name != "Value") { ex = k.get(); break; }
+    if (!ex) throw Unsupported("DerivedField without expression");
+    DExpr expr = load_dexpr(*ex, L->doc);
+    DataField df; df.name = f->get("name"); df.op = parse_optype(f->get("optype", "continuous")); df.dt = dt;
+    L->doc.index[df.name] = (int)L->doc.fields.size(); L->doc.fields.push_back(df);
+    L->derived.push_back({(int)L->doc.fields.size() - 1, dt, std::move(expr)});
+  }
   {  // Output fields anywhere in the model tree are addressable by later modelChain segments: give them context slots
     std::function<void(const Xml&)> scan = [&](const Xml& x) {
       if (x.name == "OutputField" && !L->doc.index.count(x.get("name"))) {

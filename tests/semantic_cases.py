@@ -162,6 +162,38 @@ def cases():
     X10, P10 = _rows((2, 1), (2, 0), (-1, 1), (0.25, 0), (None, 0))
     out.append(("greg/multinomial", greg("multinomialLogistic", function="classification", cats=("0", "1", "2"), pcells=pc, target_dtype="string"), X10, P10, None,
                 [(0, 1.0, 1), (0, 0.0, 0), (0, 1.0, 1), (0, 0.0, 0), (3, None, None)]))
+    # ---- derived fields (TransformationDictionary + LocalTransformations) feeding a one-predictor regression y = 1.0 * d
+    fr = lambda f: f'<FieldRef field="{f}"/>'
+    cst = lambda v: f'<Constant dataType="double">{v}</Constant>'
+    td = ('<TransformationDictionary>'
+          '<DerivedField name="d1" optype="continuous" dataType="double"><NormContinuous field="a"><LinearNorm orig="0" norm="0"/><LinearNorm orig="10" norm="1"/></NormContinuous></DerivedField>'
+          f'<DerivedField name="d2" optype="continuous" dataType="double"><Apply function="+">{fr("a")}{cst(2)}</Apply></DerivedField>'
+          f'<DerivedField name="d3" optype="continuous" dataType="double"><Apply function="if"><Apply function="greaterThan">{fr("a")}{cst(1)}</Apply>'
+          f'<Apply function="*">{fr("b")}{cst(3)}</Apply>{cst(-1)}</Apply></DerivedField>'
+          '</TransformationDictionary>')
+    lt = ('<LocalTransformations>'
+          '<DerivedField name="d4" optype="continuous" dataType="double"><Discretize field="b" mapMissingTo="7" defaultValue="99">'
+          '<DiscretizeBin binValue="-5"><Interval closure="openOpen" rightMargin="0"/></DiscretizeBin>'
+          '<DiscretizeBin binValue="5"><Interval closure="closedClosed" leftMargin="0" rightMargin="5"/></DiscretizeBin></Discretize></DerivedField>'
+          '<DerivedField name="d5" optype="continuous" dataType="double"><MapValues outputColumn="o" defaultValue="0"><FieldColumnPair field="a" column="i"/>'
+          '<InlineTable><row><i>1</i><o>100</o></row><row><i>2</i><o>200</o></row></InlineTable></MapValues></DerivedField>'
+          f'<DerivedField name="d6" optype="continuous" dataType="double"><Apply function="max" mapMissingTo="-100">{fr("d2")}{fr("d3")}</Apply></DerivedField>'
+          '</LocalTransformations>')
+    def derived_doc(name):
+        body = (f'<RegressionModel modelName="r" functionName="regression">{schema(["a", "b"])}{lt}'
+                f'<RegressionTable intercept="0"><NumericPredictor name="{name}" coefficient="1"/></RegressionTable></RegressionModel>')
+        d = doc(AB, body).decode()
+        return d.replace("</DataDictionary>", "</DataDictionary>" + td).encode()
+    Xd, Pd = _rows((2, 1), (0.5, 4), (None, 1), (2, None), (20, -3))
+    M = (3, None, None)
+    expect = {"d1": [(0, 0.2, None), (0, 0.05, None), M, (0, 0.2, None), (0, 2.0, None)],
+              "d2": [(0, 4.0, None), (0, 2.5, None), M, (0, 4.0, None), (0, 22.0, None)],
+              "d3": [(0, 3.0, None), (0, -1.0, None), M, M, (0, -9.0, None)],
+              "d4": [(0, 5.0, None), (0, 5.0, None), (0, 5.0, None), (0, 7.0, None), (0, -5.0, None)],
+              "d5": [(0, 200.0, None), (0, 0.0, None), M, (0, 200.0, None), (0, 0.0, None)],
+              "d6": [(0, 4.0, None), (0, 2.5, None), (0, -100.0, None), (0, -100.0, None), (0, 22.0, None)]}
+    for name, exp in expect.items():
+        out.append((f"derived/{name}", derived_doc(name), Xd, Pd, None, exp))
     return out
 
 

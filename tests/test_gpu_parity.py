@@ -221,3 +221,37 @@ def test_model_replicate_peer_copy(gen, oracle):
     with pytest.raises(capi.EngineError, match="another device"):
         e1.score(m0, X, pb)
     e0.close(); e1.close()
+
+
+def test_forest_on_derived_fields_all_entry_points(engine, oracle, gen):
+    """sklearn-pipeline shape: standardised inputs s_i = (x_i - mu_i) / sd_i as LocalTransformations feeding a GBT.
+    Host, sparse and device-pointer entry points all run the derive pre-pass."""
+    import ctypes as C
+    import torch
+    from flink_jpmml_b200 import capi
+    F = 12
+    pm, arr = gen.gbt_pmml(T=24, depth=5, F=F, seed=61)
+    rng = np.random.default_rng(62)
+    mu, sd = rng.normal(size=F), rng.uniform(0.5, 2.0, size=F)
+    lt = "<LocalTransformations>" + "".join(
+        f'<DerivedField name="s{i}" optype="continuous" dataType="double"><Apply function="/"><Apply function="-"><FieldRef field="x{i}"/>'
+        f'<Constant>{float(mu[i])!r}</Constant></Apply><Constant>{float(sd[i])!r}</Constant></Apply></DerivedField>' for i in range(F)) + "</LocalTransformations>"
+    text = pm.decode().replace('<SimplePredicate field="x', '<SimplePredicate field="s')
+    head, tail = text.split("</MiningSchema>", 1)            # the top-level MiningSchema is the first one
+    pm2 = (head + "</MiningSchema>" + lt + tail).encode()
+    m, om = engine.compile(pm2), oracle.OracleModel(pm2)
+    assert "derived=12" in m.describe and m.n_fields == F
+    X, pres, pb = gen.events(20000, F, 63, 0.1)
+    r, o = engine.score(m, X, pb), om.predict(X, pb, nthreads=8)
+    compare(r, o, exact_scores=True)
+    assert np.array_equal(r["score"], gen.gbt_numpy(arr, (X - mu) / sd, pres))
+    rows, cols = np.nonzero(pres)
+    row_ptr = np.concatenate([[0], np.cumsum(pres.sum(1))])
+    sp = engine.score_sparse(m, row_ptr, cols.astype(np.int32), X[rows, cols], F)
+    assert np.array_equal(sp["score"], r["score"])
+    dX, dP = torch.from_numpy(X).cuda(), torch.from_numpy(pb.view(np.int32)).cuda()
+    dS, dT = torch.empty(len(X), dtype=torch.float64, device="cuda"), torch.empty(len(X), dtype=torch.uint8, device="cuda")
+    st = torch.cuda.Stream()
+    rc = capi.lib().fjp_score_device(engine._h, m._h, dX.data_ptr(), dP.data_ptr(), None, len(X), F, dS.data_ptr(), dT.data_ptr(), None, C.c_void_p(st.cuda_stream))
+    st.synchronize()
+    assert rc == 0 and np.array_equal(dS.cpu().numpy(), r["score"])
