@@ -224,7 +224,7 @@ __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.
 // MODE: 0 sum/average, 1 weighted sum/average, 2 majority vote, 3 modelChain (per-channel sums -> RegressionTables).
 // DBG: also write per-tree node ids.
 constexpr int FC_RMAX = 10;  // row-stage elements a thread keeps in flight
-template <int D, int TI, int MODE, bool DBG>
+template <int D, int TI, int MODE, bool DBG, bool SLICE = false>
 __global__ void __launch_bounds__(512, 1)
 forest_complete_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, const ForestLaunch fl) {
   extern __shared__ __align__(128) uint8_t smem[];
@@ -241,6 +241,10 @@ forest_complete_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a,
   uint8_t* row_fail = smem + fl.off_fail;
   const int T = fd.n_trees, NG = (T + G - 1) / G;
   const long ntiles = (a.n + E - 1) / E;
+  // latency path for small batches: gridDim.y CTAs share one tile, each walks a slice of the tree groups and writes the
+  // leaf values to fl.leaf_out[row][tree]; forest_ordered_sum_kernel then adds them in segment order (same result bits)
+  const int g_lo = SLICE ? (int)((long)blockIdx.y * NG / gridDim.y) : 0, g_hi = SLICE ? (int)((long)(blockIdx.y + 1) * NG / gridDim.y) : NG;
+  double* const leaf_out = SLICE ? fl.leaf_out : nullptr;
   const bool rows_alias_ring = fl.off_rows == fl.off_ring;
   const uint32_t inv_f = 0xFFFFFFFFu / (uint32_t)F + 1u;  // i / F == umulhi(i, inv_f) for i < 2^16
 
@@ -257,7 +261,7 @@ forest_complete_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a,
 
   for (long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const long row0 = tile * E;
-    if (!rows_alias_ring && tid == 0) { fence_proxy_async(); issue(0); if (NG > 1) issue(1); }
+    if (!rows_alias_ring && tid == 0) { fence_proxy_async(); issue(g_lo); if (g_lo + 1 < g_hi) issue(g_lo + 1); }
     row_fail[tid] = 0;
     // ---------------- phase A: load, prepare, encode, transpose (32 rows per chunk; lane <-> row when encoding)
     {
@@ -312,7 +316,7 @@ forest_complete_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a,
         __syncthreads();
       }
     }
-    if (rows_alias_ring && tid == 0) { fence_proxy_async(); issue(0); if (NG > 1) issue(1); }
+    if (rows_alias_ring && tid == 0) { fence_proxy_async(); issue(g_lo); if (g_lo + 1 < g_hi) issue(g_lo + 1); }
     // ---------------- phase B: walk all trees
     const uint32_t kbase = smem_u32(keys) + 4u * tid;   // byte address of this event's key column
     const uint32_t E4 = 4u * E;
@@ -321,7 +325,7 @@ forest_complete_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a,
     uint32_t cur_ch = 0;   // modelChain: channel of the running sum
     double* chv = reinterpret_cast<double*>(votes);   // modelChain: finished channel values [channel][event]
     if (MODE == 2) for (int l = 0; l < m.n_labels; l++) { votes[l * E + tid] = 0; votes[(m.n_labels + l) * E + tid] = 0xFFFF; }
-    for (int g = 0; g < NG; g++) {
+    for (int g = g_lo; g < g_hi; g++) {
       uint32_t slot = q_wait & 1u;
       mbar_wait(&bars[slot], (q_wait >> 1) & 1u); q_wait++;
       const uint32_t base = smem_u32(ring + (size_t)slot * G * blob_words);
@@ -355,7 +359,8 @@ forest_complete_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a,
                 uint32_t ch; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(ch) : "r"(bl[k]));
                 if (ch != cur_ch) { chv[cur_ch * E + tid] = channel_value(fd.channels[cur_ch], sum); sum = 0.0; cur_ch = ch; }   // trees arrive channel by channel
                 sum += lv;
-              } else sum += lv;
+              } else if (SLICE) { if (row0 + tid < a.n) leaf_out[(long)(g * G + t + k) * a.n + row0 + tid] = lv; }   // [tree][event]: coalesced
+              else sum += lv;
             } else {
               uint32_t lab;
               asm volatile("ld.shared.u32 %0, [%1];" : "=r"(lab) : "r"(bl[k] + idx[k] * 8u));
@@ -369,11 +374,12 @@ forest_complete_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a,
         }
       }
       __syncthreads();  // everyone is done with this ring slot
-      if (tid == 0 && g + 2 < NG) { fence_proxy_async(); issue(g + 2); }
+      if (tid == 0 && g + 2 < g_hi) { fence_proxy_async(); issue(g + 2); }
     }
     // ---------------- epilogue: combine, Targets, extraction
     long row = row0 + tid;
-    if (row < a.n) {
+    if (SLICE) { if (row < a.n && blockIdx.y == 0) a.status[row] = row_fail[tid] ? ST_PREP : ST_OK; }   // the sum kernel finishes the row
+    else if (row < a.n) {
       if (row_fail[tid]) write_out(a, row, 0, ST_PREP, -1);
       else if (MODE == 3) {
         chv[cur_ch * E + tid] = channel_value(fd.channels[cur_ch], sum);
@@ -393,6 +399,26 @@ forest_complete_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a,
     }
     __syncthreads();  // keys / votes / row_fail / ring (row stage) are reused by the next tile
   }
+}
+
+// Second half of the small-batch latency path: one thread per event adds the T leaf values in segment order (the same
+// sequence of double additions as the one-CTA walk, so the bits are the same), then average / Targets / extraction.
+__global__ void __launch_bounds__(128) forest_ordered_sum_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, const double* __restrict__ leaf) {
+  long row = blockIdx.x * (long)blockDim.x + threadIdx.x;
+  if (row >= a.n) return;
+  if (a.status[row] != ST_OK) { write_out(a, row, 0, ST_PREP, -1); return; }
+  const int T = m.forest.n_trees; const double* lv = leaf + row;   // [tree][event]
+  double sum = 0.0; int t = 0;
+  for (; t + 8 <= T; t += 8) {   // eight loads in flight, added strictly in order
+    double v[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) v[k] = __ldcs(lv + (long)(t + k) * a.n);
+#pragma unroll
+    for (int k = 0; k < 8; k++) sum += v[k];
+  }
+  for (; t < T; t++) sum += __ldcs(lv + (long)t * a.n);
+  if (m.forest.method == FM_AVERAGE) sum = sum / (double)T;
+  write_out(a, row, apply_target(m.tx, sum), m.target_status, -1);
 }
 
 // ================================================================================================ forest, general form
@@ -1039,12 +1065,12 @@ static void query_device() {
   cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
 }
 
-template <int D, int TI, int MODE, bool DBG>
+template <int D, int TI, int MODE, bool DBG, bool SLICE = false>
 static cudaError_t launch_fc(const DeviceModel& m, const BatchArgs& a, const ForestLaunch& fl, int grid, int block, cudaStream_t s) {
-  auto k = forest_complete_kernel<D, TI, MODE, DBG>;
+  auto k = forest_complete_kernel<D, TI, MODE, DBG, SLICE>;
   cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fl.smem_bytes);
   if (e != cudaSuccess) return e;
-  k<<<grid, block, fl.smem_bytes, s>>>(m, a, fl);
+  k<<<dim3(grid, SLICE ? fl.slices : 1), block, fl.smem_bytes, s>>>(m, a, fl);
   return cudaGetLastError();
 }
 
@@ -1092,7 +1118,19 @@ bool plan_forest_complete(const DeviceModel& m, ForestLaunch* out) {
   return false;
 }
 
-cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t s, int* launches) {
+// Work area the small-batch forest path wants for n events (0: path not applicable)
+size_t forest_slice_scratch_bytes(const DeviceModel& m, long n) {
+  query_device();
+  if (m.kind != MK_FOREST || (m.forest.method != FM_SUM && m.forest.method != FM_AVERAGE)) return 0;
+  ForestLaunch fl;
+  if (!plan_forest_complete(m, &fl)) return 0;
+  long ntiles = (n + fl.events_per_cta - 1) / fl.events_per_cta;
+  if (ntiles * 2 > g_num_sms) return 0;                       // enough tiles to fill the chip: the one-kernel walk is the right one
+  size_t bytes = (size_t)n * m.forest.n_trees * 8;
+  return bytes <= (size_t(32) << 20) ? bytes : 0;
+}
+
+cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t s, int* launches, void* slice_scratch) {
   query_device();
   if (a.n <= 0) return cudaSuccess;
   if (launches) (*launches)++;
@@ -1103,6 +1141,19 @@ cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t 
       if (m.forest.method != FM_SINGLE && plan_forest_complete(m, &fl)) {
         long ntiles = (a.n + fl.events_per_cta - 1) / fl.events_per_cta;
         int grid = (int)(ntiles < g_num_sms ? ntiles : g_num_sms);
+        if (slice_scratch && !a.node_ids && forest_slice_scratch_bytes(m, a.n)) {   // small batch: spread the trees over the idle SMs
+          const int NG = (m.forest.n_trees + fl.trees_per_stage - 1) / fl.trees_per_stage;
+          int slices = (int)(g_num_sms / ntiles); if (slices > NG) slices = NG;
+          if (slices > 1) {
+            fl.slices = slices; fl.leaf_out = static_cast<double*>(slice_scratch);
+            cudaError_t e1 = m.forest.depth == 8 ? (fl.trees_interleaved >= 8 ? launch_fc<8, 8, 0, false, true>(m, a, fl, grid, fl.events_per_cta, s) : launch_fc<8, 4, 0, false, true>(m, a, fl, grid, fl.events_per_cta, s))
+                                                  : (fl.trees_interleaved >= 8 ? launch_fc<0, 8, 0, false, true>(m, a, fl, grid, fl.events_per_cta, s) : launch_fc<0, 4, 0, false, true>(m, a, fl, grid, fl.events_per_cta, s));
+            if (e1 != cudaSuccess) return e1;
+            if (launches) (*launches)++;
+            forest_ordered_sum_kernel<<<(unsigned)((a.n + 127) / 128), 128, 0, s>>>(m, a, fl.leaf_out);
+            return cudaGetLastError();
+          }
+        }
         const bool c = m.forest.classify; const int d = m.forest.depth;
 #define FJP_FC2(DD, TT, MM) (a.node_ids ? launch_fc<DD, 4, MM, true>(m, a, fl, grid, fl.events_per_cta, s) : launch_fc<DD, TT, MM, false>(m, a, fl, grid, fl.events_per_cta, s))
 #define FJP_FC1(DD, MM) (fl.trees_interleaved >= 8 ? FJP_FC2(DD, 8, MM) : (fl.trees_interleaved >= 6 ? FJP_FC2(DD, 6, MM) : FJP_FC2(DD, 4, MM)))
@@ -1365,7 +1416,7 @@ size_t derived_scratch_bytes(const DeviceModel& m, long n) {
 }
 // launch_score for any model: with derived fields, `scratch` must hold derived_scratch_bytes(m, a.n) bytes
 cudaError_t launch_score_any(const DeviceModel& m, const BatchArgs& a, void* scratch, cudaStream_t s, int* launches) {
-  if (m.derived.n_derived == 0) return launch_score(m, a, s, launches);
+  if (m.derived.n_derived == 0) return launch_score(m, a, s, launches, scratch);   // scratch (if any) serves the small-batch forest path
   if (a.n <= 0) return cudaSuccess;
   if (!scratch) return cudaErrorInvalidValue;
   uint8_t* base = static_cast<uint8_t*>(scratch);
@@ -1375,7 +1426,7 @@ cudaError_t launch_score_any(const DeviceModel& m, const BatchArgs& a, void* scr
   derive_kernel<<<(unsigned)((a.n + 127) / 128), 128, 0, s>>>(m, a, X2, P2, pre);
   cudaError_t e = cudaGetLastError(); if (e != cudaSuccess) return e;
   BatchArgs b = a; b.X = X2; b.present = P2; b.present_stride = (m.F + 31) / 32; b.replace = nullptr;
-  e = launch_score(m, b, s, launches); if (e != cudaSuccess) return e;
+  e = launch_score(m, b, s, launches, nullptr); if (e != cudaSuccess) return e;
   if (launches) (*launches)++;
   fixup_kernel<<<(unsigned)((a.n + 255) / 256), 256, 0, s>>>(a, pre);
   return cudaGetLastError();

@@ -27,10 +27,12 @@ struct BatchArgs {
 struct ForestLaunch {  // tile geometry of forest_complete_kernel
   int events_per_cta, trees_per_stage, row_stride, trees_interleaved;
   uint32_t off_ring, off_rows, off_votes, off_bars, off_fail, smem_bytes;
+  int slices; double* leaf_out;   // small-batch latency path: tree groups split over gridDim.y, leaf values to scratch
 };
 
 bool plan_forest_complete(const DeviceModel& m, ForestLaunch* out);
-cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t s, int* launches);
+cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t s, int* launches, void* slice_scratch = nullptr);
+size_t forest_slice_scratch_bytes(const DeviceModel& m, long n);
 cudaError_t launch_expand_sparse(const long long* row_ptr, const int32_t* idx, const double* val, long n, int F,
                                  double* X, uint32_t* present, cudaStream_t s, int* launches);
 size_t derived_scratch_bytes(const DeviceModel& m, long n);
