@@ -237,3 +237,42 @@ def test_dynamic_operator_bulk_ingest(engine, gen, oracle, tmp_path):
     assert out == exp
     op.close()
     for n in names: engine.table_del(n, 1)
+
+
+def test_engine_is_usable_from_several_host_threads(engine, gen, oracle):
+    """SURVEY.md §8b Threading: several subtasks (threads) of one TaskManager share an engine.  Four threads score
+    different models concurrently while a fifth keeps adding / deleting table entries; every result must be right."""
+    import threading
+    from flink_jpmml_b200 import capi
+    pms = [gen.gbt_pmml(T=30, depth=6, F=20, seed=300 + k)[0] for k in range(4)]
+    models = [engine.compile(pm) for pm in pms]
+    refs, Xs = [], []
+    for k, pm in enumerate(pms):
+        X, pres, pb = gen.events(30000, 20, 400 + k, 0.1)
+        Xs.append((X, pb)); refs.append(oracle.OracleModel(pm).predict(X[:3000], pb[:3000], nthreads=4)["score"])
+    errors, stop = [], threading.Event()
+
+    def scorer(k):
+        try:
+            for _ in range(15):
+                r = engine.score(models[k], *Xs[k])
+                if not np.array_equal(r["score"][:3000], refs[k]) or (r["status"] != 0).any():
+                    errors.append(f"thread {k}: wrong result")
+        except Exception as e:          # noqa: BLE001
+            errors.append(repr(e))
+
+    def churn():
+        name = str(uuid.UUID(int=900))
+        v = 0
+        while not stop.is_set():
+            v += 1
+            engine.table_add(name, v, models[v % 4]); got = engine.table_get(name, v)
+            if got is None: errors.append("table_get lost an entry")
+            else: got.release()
+            engine.table_del(name, v)
+
+    threads = [threading.Thread(target=scorer, args=(k,)) for k in range(4)]
+    ch = threading.Thread(target=churn); ch.start()
+    [t.start() for t in threads]; [t.join() for t in threads]
+    stop.set(); ch.join()
+    assert not errors, errors[:3]
