@@ -1088,7 +1088,7 @@ bool plan_forest_complete(const DeviceModel& m, ForestLaunch* out) {
   const size_t blob = (size_t)(2u << fd.depth) * 8;
   const int S = m.F | 1;  // odd row stride (in doubles): conflict-free column reads of the row stage
   const size_t rows = (size_t)32 * S * 8;
-  int ti = env_int("FJP_FOREST_TI", 8); ti = ti >= 8 ? 8 : (ti >= 6 ? 6 : 4);
+  int ti = env_int("FJP_FOREST_TI", 8); ti = ti >= 12 ? 12 : (ti >= 8 ? 8 : (ti >= 6 ? 6 : 4));
   const int force_e = env_int("FJP_FOREST_E", 0), force_g = env_int("FJP_FOREST_G", 0);
   const int t_round = ((fd.n_trees + ti - 1) / ti) * ti;
   for (int E = 512; E >= 64; E -= 32) {
@@ -1156,7 +1156,7 @@ cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t 
         }
         const bool c = m.forest.classify; const int d = m.forest.depth;
 #define FJP_FC2(DD, TT, MM) (a.node_ids ? launch_fc<DD, 4, MM, true>(m, a, fl, grid, fl.events_per_cta, s) : launch_fc<DD, TT, MM, false>(m, a, fl, grid, fl.events_per_cta, s))
-#define FJP_FC1(DD, MM) (fl.trees_interleaved >= 8 ? FJP_FC2(DD, 8, MM) : (fl.trees_interleaved >= 6 ? FJP_FC2(DD, 6, MM) : FJP_FC2(DD, 4, MM)))
+#define FJP_FC1(DD, MM) (fl.trees_interleaved >= 12 ? FJP_FC2(DD, 12, MM) : fl.trees_interleaved >= 8 ? FJP_FC2(DD, 8, MM) : (fl.trees_interleaved >= 6 ? FJP_FC2(DD, 6, MM) : FJP_FC2(DD, 4, MM)))
 #define FJP_FC(DD) (c ? FJP_FC1(DD, 2) : (m.forest.method == FM_CHAIN ? FJP_FC1(DD, 3) : ((m.forest.method == FM_WSUM || m.forest.method == FM_WAVERAGE) ? FJP_FC1(DD, 1) : FJP_FC1(DD, 0))))
         if (d == 8) return FJP_FC(8);
         if (d == 6) return FJP_FC(6);

@@ -650,22 +650,26 @@ struct ForestBuilder {
     b.put(&fd.rank_off, rank_off); b.put(&fd.rank_thr, rank_thr);
     auto feat_of = [&](const TNode& n) { return node_slot[&n - nodes.data()]; };
 
-    // complete-tree detection: uniform depth, no sharing, missing goes to one of the two children
+    // Complete-tree form: every tree is laid out as a complete binary tree of ONE depth D (the deepest path of the
+    // ensemble, at most 10).  Shallower branches are padded: a leaf above depth D becomes a subtree of pass-through nodes
+    // whose leaves all repeat it (pruned XGBoost / LightGBM trees, trees of different depths).  Needs: every test sends a
+    // missing value down one of its two branches, and no null prediction is reachable.  Sub-graphs shared by several
+    // parents (compound predicates, equality tests) are simply duplicated while the expansion stays small.
     int depth = -1; bool complete = !roots.empty();
     std::vector<int> dep_memo(nodes.size(), -1);
-    std::function<int(int32_t)> dep = [&](int32_t s) -> int {  // -2: not complete
+    std::function<int(int32_t)> dep = [&](int32_t s) -> int {  // longest path below s; -2: cannot be laid out
       if (s < 0) return s == LEAF_NULL ? -2 : 0;
       if (dep_memo[s] != -1) return dep_memo[s];
       const TNode& n = nodes[s]; int r;
       if (n.on_missing != n.on_true && n.on_missing != n.on_false) r = -2;
-      else { int a = dep(n.on_true), c = dep(n.on_false); r = (a < 0 || c < 0 || a != c) ? -2 : a + 1; }
+      else { int a = dep(n.on_true), c = dep(n.on_false); r = (a < 0 || c < 0) ? -2 : std::max(a, c) + 1; }
       return dep_memo[s] = r;
     };
-    for (int32_t r : roots) { int dd = dep(r); if (dd < 1 || dd > 10 || (depth >= 0 && dd != depth)) { complete = false; break; } depth = dd; }
-    if (complete) {  // every node used exactly once?
-      std::vector<uint8_t> seen(nodes.size(), 0); std::vector<uint8_t> lseen(leaves.size(), 0);
-      std::function<void(int32_t)> mark = [&](int32_t s) { if (s < 0) { if (lseen[~s]++) complete = false; return; } if (seen[s]++) { complete = false; return; } mark(nodes[s].on_true); if (complete) mark(nodes[s].on_false); };
-      for (int32_t r : roots) if (complete) mark(r);
+    for (int32_t r : roots) { int dd = dep(r); if (dd < 0 || dd > 10) { complete = false; break; } depth = std::max(depth, dd); }
+    if (complete && depth < 1) depth = 1;   // a forest of bare leaves still gets one (pass-through) level
+    if (complete) {  // padding must not blow the model up: at most 8x the real node count (always fine up to depth 6)
+      size_t padded = roots.size() << depth;
+      if (depth > 6 && padded > 8 * (nodes.size() + roots.size())) complete = false;
     }
     std::vector<int32_t> leaf_ids;
     if (complete) {
@@ -678,6 +682,10 @@ struct ForestBuilder {
         std::function<void(int32_t, size_t)> place = [&](int32_t s, size_t h) {
           if (s < 0) {
             const TLeaf& lf = leaves[~s];
+            if (h < (size_t(1) << depth)) {   // a leaf above the common depth: pass-through node (every key goes left), repeated below
+              bl[h] = (uint64_t)0u | ((uint64_t)0u << 32);   // feat 0, a = 0, ~ka = 0 => ka = 0xFFFFFFFF: never "right"
+              place(s, 2 * h); place(s, 2 * h + 1); return;
+            }
             if (classify) bl[h] = (uint64_t)(uint32_t)lf.label; else memcpy(&bl[h], &lf.value, 8);
             leaf_ids[(t << depth) + (h - (size_t(1) << depth))] = lf.node_id; return;
           }

@@ -496,3 +496,43 @@ def gbt_classifier_numpy(arrays, X, present=None):
     e = np.exp(dec)
     probs = e / e.sum(axis=1, keepdims=True)
     return probs.argmax(axis=1).astype(np.float64), probs
+
+
+def gbt_pruned_pmml(T=60, max_depth=6, F=20, seed=5, p_leaf=0.25, operator="lessThan", dtype="float"):
+    """XGBoost-export shape: float fields, `x < t` on the left child, <True/> on the right, defaultChild, trees pruned at
+    random (a node below the root becomes a leaf with probability p_leaf), so depths differ within and across trees."""
+    from scipy.stats import norm
+    rng = np.random.default_rng(seed)
+    grid = norm.ppf((np.arange(255) + 1.0) / 256.0).astype(np.float32).astype(np.float64)
+    names = [f"x{i}" for i in range(F)]
+    out = _header()
+    out += _data_dictionary([(n, "continuous", dtype) for n in names], ("y", "continuous", "double", None))
+    out.append(f'<MiningModel modelName="gbt-pruned" functionName="regression">')
+    out += _mining_schema(names, "y")
+    out.append('<Segmentation multipleModelMethod="sum">')
+    for t in range(T):
+        out.append(f'<Segment id="{t + 1}"><True/><TreeModel functionName="regression" missingValueStrategy="defaultChild" '
+                   'noTrueChildStrategy="returnNullPrediction" splitCharacteristic="binarySplit">')
+        out += _mining_schema(names)
+        counter = [0]
+
+        def emit(depth, pred):
+            counter[0] += 1
+            my_id = counter[0]
+            if depth == max_depth or (depth >= 1 and rng.random() < p_leaf):
+                out.append(f'<Node id="{my_id}" score="{_r(rng.normal(0, 0.1))}">{pred}</Node>')
+                return
+            at = len(out)
+            out.append(None)   # patched below once the children's ids are known
+            f, thr = names[int(rng.integers(F))], float(grid[int(rng.integers(255))])
+            left_id = counter[0] + 1
+            emit(depth + 1, f'<SimplePredicate field="{f}" operator="{operator}" value="{_r(thr)}"/>')
+            right_id = counter[0] + 1
+            emit(depth + 1, '<True/>')
+            out[at] = f'<Node id="{my_id}" defaultChild="{left_id if rng.random() < 0.5 else right_id}">{pred}'
+            out.append('</Node>')
+
+        emit(0, '<True/>')
+        out.append('</TreeModel></Segment>')
+    out.append('</Segmentation></MiningModel></PMML>')
+    return "\n".join(out).encode()

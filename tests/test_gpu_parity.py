@@ -255,3 +255,18 @@ def test_forest_on_derived_fields_all_entry_points(engine, oracle, gen):
     rc = capi.lib().fjp_score_device(engine._h, m._h, dX.data_ptr(), dP.data_ptr(), None, len(X), F, dS.data_ptr(), dT.data_ptr(), None, C.c_void_p(st.cuda_stream))
     st.synchronize()
     assert rc == 0 and np.array_equal(dS.cpu().numpy(), r["score"])
+
+
+def test_pruned_trees_are_padded_into_the_on_chip_format(engine, oracle, gen):
+    """XGBoost-style export (float fields, `<`, pruned trees of unequal depth): the compiler pads every tree to the
+    ensemble's depth so the ensemble still runs in the shared-memory kernel; node ids and scores match the oracle."""
+    pm = gen.gbt_pruned_pmml(T=60, max_depth=6, F=20, seed=5)
+    m, om = engine.compile(pm), oracle.OracleModel(pm)
+    assert "format=complete" in m.describe and "depth=6" in m.describe
+    X, pres, pb = gen.events(20000, 20, 6, 0.1)
+    X[::50, 2] = np.nan
+    r, o = engine.score(m, X, pb, node_ids=True), om.predict(X, pb, node_ids=True, nthreads=8)
+    compare(r, o, exact_scores=True)
+    assert np.array_equal(r["node_ids"], o["node_ids"])
+    r2 = engine.score(m, X, pb)                      # the fast instantiation (no node ids)
+    assert np.array_equal(r2["score"], o["score"])
