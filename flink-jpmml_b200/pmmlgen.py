@@ -148,6 +148,9 @@ def _complete_tree_xml(out, feat, thr, dleft, leaf_txt, names, depth, operator="
     emit(0, '<True/>')
 
 
+FLOAT_THRESHOLDS = True   # tests flip this to get thresholds that are NOT float32-representable (rank-encoded keys)
+
+
 def forest_arrays(T, depth, F, seed, n_quantiles=255):
     """Random complete trees: feature ~ U{0..F-1}; thresholds = standard-normal quantiles rounded to float32
     (exactly representable in both float and double); default child uniform; returns level-order arrays."""
@@ -155,7 +158,9 @@ def forest_arrays(T, depth, F, seed, n_quantiles=255):
     rng = np.random.default_rng(seed)
     n_int = (1 << depth) - 1
     feat = rng.integers(0, F, size=(T, n_int))
-    grid = norm.ppf((np.arange(n_quantiles) + 1.0) / (n_quantiles + 1.0)).astype(np.float32).astype(np.float64)
+    grid = norm.ppf((np.arange(n_quantiles) + 1.0) / (n_quantiles + 1.0))
+    if FLOAT_THRESHOLDS:
+        grid = grid.astype(np.float32).astype(np.float64)
     thr = grid[rng.integers(0, n_quantiles, size=(T, n_int))]
     dleft = rng.integers(0, 2, size=(T, n_int)).astype(bool)
     return feat, thr, dleft, rng

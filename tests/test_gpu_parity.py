@@ -270,3 +270,20 @@ def test_pruned_trees_are_padded_into_the_on_chip_format(engine, oracle, gen):
     assert np.array_equal(r["node_ids"], o["node_ids"])
     r2 = engine.score(m, X, pb)                      # the fast instantiation (no node ids)
     assert np.array_equal(r2["score"], o["score"])
+
+
+def test_double_thresholds_use_rank_keys(engine, oracle, gen, monkeypatch):
+    """Thresholds that are not float32 values (scikit-learn style midpoints): keys are ranks among the feature's sorted
+    thresholds (binary search in the kernel), still in the on-chip complete-tree kernel, still bit-exact."""
+    monkeypatch.setattr(gen, "FLOAT_THRESHOLDS", False)
+    pm, arr = gen.gbt_pmml(T=64, depth=6, F=24, seed=71)
+    m, om = engine.compile(pm), oracle.OracleModel(pm)
+    assert "enc=rank" in m.describe and "format=complete" in m.describe
+    X, pres, pb = gen.events(30000, 24, 72, 0.1)
+    X[::7, 0] = arr["thr"][0, 0]                      # values exactly on a threshold
+    X[::11, 1] = np.nextafter(arr["thr"][0, 1], np.inf)
+    X[::13, 2] = np.nan
+    r, o = engine.score(m, X, pb, node_ids=True), om.predict(X, pb, node_ids=True, nthreads=8)
+    compare(r, o, exact_scores=True)
+    assert np.array_equal(r["node_ids"], o["node_ids"])
+    assert np.array_equal(engine.score(m, X, pb)["score"], gen.gbt_numpy(arr, np.nan_to_num(X, nan=np.inf), pres))
