@@ -56,7 +56,7 @@ static void make_describe(fjp_model* m) {
   if (d.kind == MK_FOREST) {
     s += " trees=" + std::to_string(d.forest.n_trees) + " format=" + (d.forest.format == FOREST_COMPLETE ? "complete" : "general") +
          " depth=" + std::to_string(d.forest.depth) + " enc=" + (d.forest.enc == ENC_FLOAT ? "float" : "rank") +
-         " method=" + std::to_string(d.forest.method) + " nodes=" + std::to_string(m->cm.n_nodes);
+         " method=" + std::to_string(d.forest.method) + " nodes=" + std::to_string(m->cm.n_nodes) + " compact=" + std::to_string(d.forest.compact.enabled);
     ForestLaunch fl;
     if (m->d_blob && d.forest.method != FM_SINGLE && plan_forest_complete(d, &fl))
       s += " tile_events=" + std::to_string(fl.events_per_cta) + " trees_per_stage=" + std::to_string(fl.trees_per_stage) + " interleave=" + std::to_string(fl.trees_interleaved) +
@@ -235,6 +235,11 @@ int fjp_engine_create(int device, fjp_engine** out, char* err, size_t errcap) {
   if (device < 0 || device >= count) return fail("device ordinal out of range", err, errcap);
   if (cudaSetDevice(device) != cudaSuccess) return fail("cudaSetDevice failed", err, errcap);
   auto* e = new fjp_engine(); e->device = device;
+  {  // fjp_score_device takes its work areas from the stream-ordered allocator: keep freed blocks in the pool between calls
+    cudaMemPool_t pool; uint64_t keep = UINT64_MAX;
+    if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    cudaGetLastError();
+  }
   for (int i = 0; i < NSLOT; i++) {
     if (cudaStreamCreateWithFlags(&e->slots[i].s, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreateWithFlags(&e->slots[i].done, cudaEventDisableTiming) != cudaSuccess) {
@@ -432,8 +437,9 @@ int fjp_score_device(fjp_engine* e, fjp_model* m, const double* dX, const uint32
   else {
     if (!m->d_blob) return fail("model was compiled without an engine: it cannot score");
     if (m->device != e->device) return fail("model lives on another device; use fjp_model_replicate");
-    const size_t dsz = derived_scratch_bytes(m->dev, n);
-    if (dsz) {   // derived fields need a work area for the augmented rows: stream-ordered allocation on the caller's stream
+    size_t dsz = derived_scratch_bytes(m->dev, n);
+    if (!dsz) dsz = forest_compact_scratch_bytes(m->dev, n);
+    if (dsz) {   // augmented rows (derived fields) / rank-key tiles (large forest batches): stream-ordered allocation on the caller's stream
       void* scratch = nullptr; CK(cudaMallocAsync(&scratch, dsz, st));
       cudaError_t ce = launch_score_any(m->dev, a, scratch, st, &launches);
       cudaFreeAsync(scratch, st);

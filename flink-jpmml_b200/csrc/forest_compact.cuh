@@ -1,0 +1,231 @@
+// forest_compact.cuh -- throughput path for complete forests (included by kernels.cu after the shared device helpers).
+//
+// Two kernels per (sub-)batch, see model.h CompactDesc:
+//   forest_rank_keys_kernel   X[n][F] doubles (+ present bits, replaceNan, input preparation) -> 16-bit rank keys, written as
+//                             ready-made shared-memory images of the walk kernel's key tiles:  tile t = keys[f][e], e < E.
+//   forest_compact_kernel     one CTA = one tile of E events (one per thread): the key tile arrives with one bulk copy, tree
+//                             blobs (4-byte nodes) stream through the same 2-stage ring as forest_complete_kernel, TI trees
+//                             interleaved per thread; per level LDS.32 node, LDS.U16 key, carry-chain index update.
+// Results are bit-identical to forest_complete_kernel: same decisions (rank keys order values exactly like the float images),
+// same leaf values, same order of the double additions.
+#pragma once
+
+struct KeyTiles {
+  uint16_t* keys;        // tiles x (F x E) rank keys
+  uint8_t* fail;         // tiles x E: 1 = input preparation refused the row (returnInvalid); NULL when that cannot happen
+  long row_begin;        // first batch row of tile 0
+  long ntiles;
+  int E;                 // events per tile
+  uint32_t tile_bytes;   // F * E * 2
+};
+
+constexpr int RK_THREADS = 512;
+constexpr int RK_BATCH = 5;      // values a thread has in flight (E = 640: two batches per tile)
+
+// Rank keys of RK_BATCH prepared values of one feature, the chains interleaved by hand: bucket -> first candidate threshold
+// -> three forward steps (a bucket holds about half a threshold on average; the threshold array ends with 0xFFFFFFFF
+// sentinels, so the scan needs no bound checks) -> a loop only for crowded buckets.
+// th_addr / tab_addr: shared-memory byte addresses of the feature's threshold images and bucket table.
+__device__ __forceinline__ void ck_rank_keys(uint32_t th_addr, uint32_t tab_addr, const CkFeat& cf, int mode, const double (&val)[RK_BATCH], uint32_t (&key)[RK_BATCH]) {
+  uint32_t img[RK_BATCH], r[RK_BATCH], t[RK_BATCH];   // r: byte address of the candidate threshold
+  const float top = (float)(cf.nb - 1u);
+  const uint32_t flip = mode == 2 ? 0x80000000u : 0u;  // RD(x) = -RU(-x)
+#pragma unroll
+  for (int k = 0; k < RK_BATCH; k++) {
+    float xf;
+    if (mode == 0) xf = (float)val[k];                  // float field: JPMML's cast (round to nearest); uniform per feature
+    else {
+      const double sx = __hiloint2double(__double2hiint(val[k]) ^ (int)flip, __double2loint(val[k]));
+      xf = __uint_as_float(__float_as_uint(__double2float_ru(sx)) ^ flip);
+    }
+    const uint32_t u = __float_as_uint(xf);
+    img[k] = u ^ ((uint32_t)((int32_t)u >> 31) | 0x80000000u);   // order-preserving image (ordkey); NaN handled below
+    // same bucket as model.h ck_bucket: clamp((x - lo) * scale) to [0, nb - 1], NaN -> 0
+    const uint32_t b = __float2uint_rz(fminf(fmaxf((xf - cf.lo) * cf.scale, 0.0f), top));
+    uint32_t first; asm volatile("ld.shared.u16 %0, [%1];" : "=r"(first) : "r"(tab_addr + 2u * b));   // thresholds in lower buckets are all below x
+    r[k] = th_addr + 4u * (xf != xf ? cf.n_thr : first);         // NaN is the greatest value (Double.compareTo)
+  }
+#pragma unroll
+  for (int k = 0; k < RK_BATCH; k++) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(t[k]) : "r"(r[k]));
+#pragma unroll
+  for (int s = 0; s < 3; s++) {
+#pragma unroll
+    for (int k = 0; k < RK_BATCH; k++) { r[k] += t[k] < img[k] ? 4u : 0u; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(t[k]) : "r"(r[k])); }
+  }
+#pragma unroll
+  for (int k = 0; k < RK_BATCH; k++) {
+    while (t[k] < img[k]) { r[k] += 4u; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(t[k]) : "r"(r[k])); }   // crowded bucket (rare)
+    key[k] = ((r[k] - th_addr) >> 1) + (t[k] == img[k] ? 2u : 1u);   // 2 * rank + 1 (+1 on equality)
+  }
+}
+
+// grid = (x, feature blocks); a CTA keeps the tables of its CK_FB features in shared memory and runs over the tiles
+// x, x + gridDim.x, ...  Element i of a tile is (event, feature) = (i / 8, i % 8): a warp reads four 64-byte runs of X.
+// No lane is ever predicated off: the idle lanes of a short last block redo feature f0 (their staging rows are not written
+// out), rows past the end of the batch redo the last row (the walk kernel never reports them).
+// Shared memory: tables | staging tile u16 [8][OS]
+template <bool SIMPLE>
+__global__ void __launch_bounds__(RK_THREADS, 2) forest_rank_keys_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, const KeyTiles kt) {
+  extern __shared__ __align__(16) uint8_t rk_smem[];
+  const ForestDesc& fd = m.forest; const CompactDesc& cd = fd.compact;
+  const int F = m.F, E = kt.E, tid = threadIdx.x;
+  const int f0 = blockIdx.y * CK_FB, nf = min(CK_FB, F - f0);
+  const int OS = ((E + 63) & ~63) + 8;   // row stride of the staging tile (u16): the 8 feature rows fall into different banks
+  const int total = E * CK_FB;
+  uint16_t* out = reinterpret_cast<uint16_t*>(rk_smem + cd.block_smem);
+  {
+    const uint32_t t0 = cd.block_off[blockIdx.y], tbytes = cd.block_off[blockIdx.y + 1] - t0;
+    const uint4* src = reinterpret_cast<const uint4*>(cd.tables + t0); uint4* dst = reinterpret_cast<uint4*>(rk_smem);
+    for (uint32_t i = tid; i < tbytes / 16; i += RK_THREADS) dst[i] = __ldg(src + i);
+  }
+  const int j = tid & (CK_FB - 1), f = j < nf ? f0 + j : f0;   // this thread's feature never changes (RK_THREADS is a multiple of CK_FB)
+  const CkFeat cf = cd.feat[f]; const int mode = fd.feat_mode[f];
+  const uint32_t th_addr = smem_u32(rk_smem) + cf.thr_off, tab_addr = smem_u32(rk_smem) + cf.tab_off;
+  const uint32_t pbit = 1u << (f & 31); const int pword = f0 >> 5;   // a block's 8 features share one present word
+  uint16_t* const out_row = out + j * OS;
+  __syncthreads();
+  for (long tile = blockIdx.x; tile < kt.ntiles; tile += gridDim.x) {
+    const long row0 = kt.row_begin + tile * E;
+    const int last = (int)min((long)E, a.n - row0) - 1;          // last live row of this tile (>= 0)
+    const double* xt = a.X + row0 * (long)F + f;
+    const uint32_t* pt = a.present ? a.present + row0 * (long)a.present_stride + pword : nullptr;
+    for (int i0 = tid; i0 < total; i0 += RK_THREADS * RK_BATCH) {
+      double val[RK_BATCH]; uint32_t pw[RK_BATCH], key[RK_BATCH]; int st[RK_BATCH], e[RK_BATCH];
+#pragma unroll
+      for (int k = 0; k < RK_BATCH; k++) {
+        e[k] = min(min(i0 + k * RK_THREADS, total - 1) >> 3, last);   // clamped: duplicates recompute a live element
+        val[k] = __ldcs(xt + e[k] * F);
+        pw[k] = pt ? __ldg(pt + e[k] * a.present_stride) : pbit;
+      }
+#pragma unroll
+      for (int k = 0; k < RK_BATCH; k++) {
+        bool present = (pw[k] & pbit) != 0;
+        if (!present && a.replace) { double rep = a.replace[row0 + e[k]]; if (rep == rep) { val[k] = rep; present = true; } }
+        if (SIMPLE) st[k] = present ? 0 : 1;
+        else { double raw = val[k]; val[k] = 0.0; st[k] = prep_value(m.prep[f], m.prep_pool, present, raw, val[k]); }
+      }
+      ck_rank_keys(th_addr, tab_addr, cf, mode, val, key);
+#pragma unroll
+      for (int k = 0; k < RK_BATCH; k++) {
+        const int ee = min(i0 + k * RK_THREADS, total - 1) >> 3;      // the unclamped event slot of the tile
+        if (!SIMPLE && st[k] == 2 && ee <= last) kt.fail[tile * E + ee] = 1;
+        out_row[ee] = (uint16_t)(st[k] == 0 ? key[k] : 0u);
+      }
+    }
+    __syncthreads();
+    uint16_t* dst = kt.keys + (size_t)tile * (kt.tile_bytes / 2) + (size_t)f0 * E;
+    const int q4 = E >> 2;   // 8-byte units per feature row
+    for (int i = tid; i < nf * q4; i += RK_THREADS) {
+      const int jj = i / q4, q = i - jj * q4;
+      *reinterpret_cast<uint2*>(dst + (size_t)jj * E + 4 * q) = *reinterpret_cast<const uint2*>(out + jj * OS + 4 * q);
+    }
+    __syncthreads();   // the staging tile is reused by the next tile
+  }
+}
+
+// MODE: 0 sum / average, 1 weighted sum / average, 2 majority vote.
+template <int D, int TI, int MODE, int MAXT>
+__global__ void __launch_bounds__(MAXT, 1)
+forest_compact_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, const ForestLaunch fl, const KeyTiles kt) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  const ForestDesc& fd = m.forest; const CompactDesc& cd = fd.compact;
+  const int E = blockDim.x, tid = threadIdx.x;
+  const int depth = D ? D : fd.depth;
+  const uint32_t TB = (uint32_t)cd.tree_bytes, nleaf = 1u << depth;
+  const uint32_t off_leaf = 4u * nleaf - 8u * nleaf;   // leaf h (h >= 2^depth) lives at 4*2^depth + 8*(h - 2^depth); wraps, 32-bit address arithmetic
+  const uint32_t off_w = 12u * nleaf;
+  const int G = fl.trees_per_stage;
+  uint16_t* keys = reinterpret_cast<uint16_t*>(smem);
+  uint8_t* ring = smem + fl.off_ring;
+  uint16_t* votes = reinterpret_cast<uint16_t*>(smem + fl.off_votes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + fl.off_bars);
+  const int T = fd.n_trees, NG = (T + G - 1) / G;
+
+  if (tid == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); mbar_init(&bars[2], 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+  __syncthreads();
+
+  uint32_t q_issue = 0, q_wait = 0, tile_parity = 0;
+  auto issue = [&](int g) {  // thread 0: fill ring slot q_issue&1 with tree group g
+    uint32_t slot = q_issue & 1u; int t0 = g * G; int nt = min(G, T - t0); uint32_t bytes = (uint32_t)nt * TB;
+    mbar_expect_tx(&bars[slot], bytes);
+    bulk_g2s(ring + (size_t)slot * G * TB, reinterpret_cast<const uint8_t*>(cd.blobs) + (size_t)t0 * TB, bytes, &bars[slot]);
+    q_issue++;
+  };
+
+  for (long tile = blockIdx.x; tile < kt.ntiles; tile += gridDim.x) {
+    if (tid == 0) {
+      fence_proxy_async();
+      mbar_expect_tx(&bars[2], kt.tile_bytes);
+      const uint8_t* src = reinterpret_cast<const uint8_t*>(kt.keys) + (size_t)tile * kt.tile_bytes;
+      for (uint32_t o = 0; o < kt.tile_bytes; o += 32768u) bulk_g2s(smem + o, src + o, min(32768u, kt.tile_bytes - o), &bars[2]);
+      issue(0); if (NG > 1) issue(1);
+    }
+    const long row = kt.row_begin + tile * E + tid;
+    const bool failed = kt.fail != nullptr && kt.fail[tile * E + tid] != 0;
+    if (MODE == 2) for (int l = 0; l < m.n_labels; l++) { votes[l * E + tid] = 0; votes[(m.n_labels + l) * E + tid] = 0xFFFF; }
+    mbar_wait(&bars[2], tile_parity); tile_parity ^= 1u;
+
+    const uint32_t kbase = smem_u32(keys) + 2u * tid;   // byte address of this event's key column
+    const uint32_t Eb = (uint32_t)E;                     // (node & 0x1FE) * E = feat * 2E bytes
+    double sum = 0.0, wsum = 0.0; uint32_t seen = 0;
+    for (int g = 0; g < NG; g++) {
+      uint32_t slot = q_wait & 1u;
+      mbar_wait(&bars[slot], (q_wait >> 1) & 1u); q_wait++;
+      const uint32_t base = smem_u32(ring + (size_t)slot * G * TB);
+      const int nt = min(G, T - g * G);
+      for (int t = 0; t < nt; t += TI) {
+        uint32_t idx[TI], bl[TI];
+#pragma unroll
+        for (int k = 0; k < TI; k++) { idx[k] = 1; bl[k] = base + (uint32_t)min(t + k, nt - 1) * TB; }
+#pragma unroll
+        for (int d = 0; d < (D ? D : 16); d++) {
+          if (!D && d >= depth) break;
+#pragma unroll
+          for (int k = 0; k < TI; k++) {
+            uint32_t nd, key;
+            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(nd) : "r"(bl[k] + idx[k] * 4u));
+            asm volatile("ld.shared.u16 %0, [%1];" : "=r"(key) : "r"(kbase + (nd & 0x1FEu) * Eb));
+            const uint32_t vv = key - (nd & 1u), ny = (uint32_t)((int32_t)nd >> 16);
+            // ny = ~(K - a): vv + ny carries out exactly when vv > K - a ("go right"); idx = 2*idx + carry
+            asm("{\n\t.reg .u32 t;\n\tadd.cc.u32 t, %2, %3;\n\taddc.u32 %0, %1, %1;\n\t}" : "=r"(idx[k]) : "r"(idx[k]), "r"(ny), "r"(vv));
+          }
+        }
+#pragma unroll
+        for (int k = 0; k < TI; k++) {
+          if (t + k < nt) {
+            if (MODE != 2) {
+              double lv;
+              asm volatile("ld.shared.f64 %0, [%1];" : "=d"(lv) : "r"(bl[k] + off_leaf + idx[k] * 8u));
+              if (MODE == 1) { double w; asm volatile("ld.shared.f64 %0, [%1];" : "=d"(w) : "r"(bl[k] + off_w)); sum += w * lv; wsum += w; }
+              else sum += lv;
+            } else {
+              uint32_t lab;
+              asm volatile("ld.shared.u32 %0, [%1];" : "=r"(lab) : "r"(bl[k] + off_leaf + idx[k] * 8u));
+              uint16_t c = votes[lab * E + tid];
+              if (c == 0) votes[(m.n_labels + lab) * E + tid] = (uint16_t)seen++;
+              votes[lab * E + tid] = c + 1;
+            }
+          }
+        }
+      }
+      __syncthreads();  // everyone is done with this ring slot
+      if (tid == 0 && g + 2 < NG) { fence_proxy_async(); issue(g + 2); }
+    }
+    if (row < a.n) {
+      if (failed) write_out(a, row, 0, ST_PREP, -1);
+      else if (MODE != 2) {
+        double v = sum;
+        if (fd.method == FM_AVERAGE) v = sum / (double)T; else if (fd.method == FM_WAVERAGE) v = sum / wsum;
+        write_out(a, row, apply_target(m.tx, v), m.target_status, -1);
+      } else {
+        int best = -1; uint32_t bc = 0, bo = 0;
+        for (int l = 0; l < m.n_labels; l++) {
+          uint32_t c = votes[l * E + tid], o = votes[(m.n_labels + l) * E + tid];
+          if (c && (best < 0 || c > bc || (c == bc && o < bo))) { best = l; bc = c; bo = o; }  // first maximal in insertion order
+        }
+        write_label(m, a, row, best, best);
+      }
+    }
+    __syncthreads();  // the key tile and the votes are reused by the next tile
+  }
+}

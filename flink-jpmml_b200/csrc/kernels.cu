@@ -1057,6 +1057,8 @@ __global__ void __launch_bounds__(NT_E* NT_WARPS, 1) neural_tile_kernel(const __
 }
 
 // ================================================================================================ launchers
+#include "forest_compact.cuh"
+
 static int g_smem_optin = 0, g_num_sms = 0;
 static void query_device() {
   if (g_num_sms) return;
@@ -1119,8 +1121,10 @@ bool plan_forest_complete(const DeviceModel& m, ForestLaunch* out) {
 }
 
 // Work area the small-batch forest path wants for n events (0: path not applicable)
+size_t forest_compact_scratch_bytes(const DeviceModel& m, long n);
 size_t forest_slice_scratch_bytes(const DeviceModel& m, long n) {
   query_device();
+  if (size_t c = forest_compact_scratch_bytes(m, n)) return c;   // large batch: the work area holds the rank-key tiles instead
   if (m.kind != MK_FOREST || (m.forest.method != FM_SUM && m.forest.method != FM_AVERAGE)) return 0;
   ForestLaunch fl;
   if (!plan_forest_complete(m, &fl)) return 0;
@@ -1130,6 +1134,101 @@ size_t forest_slice_scratch_bytes(const DeviceModel& m, long n) {
   return bytes <= (size_t(32) << 20) ? bytes : 0;
 }
 
+// ---- throughput path (forest_compact.cuh): geometry, work area, launch --------------------------------------
+// FJP_FOREST_COMPACT=0 switches the path off, =2 takes it for every batch size; FJP_FOREST_CE / FJP_FOREST_CG / FJP_FOREST_CTI
+// override the tile geometry (tuning aids, read at every launch).
+static bool plan_forest_compact(const DeviceModel& m, ForestLaunch* out) {
+  query_device();
+  const ForestDesc& fd = m.forest;
+  if (fd.format != FOREST_COMPLETE || !fd.compact.enabled || !env_int("FJP_FOREST_COMPACT", 1)) return false;
+  if (fd.classify ? fd.method != FM_VOTE : (fd.method != FM_SUM && fd.method != FM_AVERAGE && fd.method != FM_WSUM && fd.method != FM_WAVERAGE)) return false;
+  if (fd.classify && m.n_labels > 64) return false;
+  const size_t budget = (size_t)g_smem_optin - 1024, TB = (size_t)fd.compact.tree_bytes;
+  int ti = env_int("FJP_FOREST_CTI", 8); ti = ti >= 8 ? 8 : 4;
+  const int force_e = env_int("FJP_FOREST_CE", 0), force_g = env_int("FJP_FOREST_CG", 0);
+  const int t_round = ((fd.n_trees + ti - 1) / ti) * ti;
+  static const int kE[] = {640, 768, 1024, 512, 384, 256, 128, 64};
+  for (int E : kE) {
+    if (force_e && E != force_e) continue;
+    if (E == 1024) ti = 4;   // 64 registers per thread
+    size_t keys = ((size_t)m.F * E * 2 + 127) & ~size_t(127);
+    size_t votes = fd.classify ? (size_t)2 * m.n_labels * E * 2 : 0;
+    size_t fixed = keys + votes + 64 + 256;
+    if (fixed + 2 * ti * TB > budget) continue;
+    int G = (int)((budget - fixed) / (2 * TB)); G = (G / ti) * ti; if (G > 2 * ti) G = 2 * ti;
+    if (force_g) G = force_g;
+    if (G > t_round) G = t_round;
+    if (G < ti || fixed + 2 * (size_t)G * TB > budget) continue;
+    ForestLaunch fl{}; fl.events_per_cta = E; fl.trees_per_stage = G; fl.trees_interleaved = ti;
+    size_t off = keys; fl.off_ring = (uint32_t)off; off += 2 * (size_t)G * TB;
+    off = (off + 15) & ~size_t(15); fl.off_votes = (uint32_t)off; off += votes; off = (off + 15) & ~size_t(15);
+    fl.off_bars = (uint32_t)off; off += 64;
+    fl.smem_bytes = (uint32_t)((off + 127) & ~size_t(127));
+    *out = fl; return true;
+  }
+  return false;
+}
+// tiles scored per pass over the work area: a multiple of the SM count, at most ~256 MB of keys
+static long compact_tiles_per_pass(const DeviceModel& m, const ForestLaunch& fl, long ntiles) {
+  const size_t tile_bytes = (size_t)m.F * fl.events_per_cta * 2;
+  long cap = (long)((size_t(256) << 20) / tile_bytes); cap = cap / g_num_sms * g_num_sms; if (cap < g_num_sms) cap = g_num_sms;
+  return ntiles < cap ? ntiles : cap;
+}
+size_t forest_compact_scratch_bytes(const DeviceModel& m, long n) {
+  if (m.kind != MK_FOREST) return 0;
+  ForestLaunch fl;
+  if (!plan_forest_compact(m, &fl)) return 0;
+  const long ntiles = (n + fl.events_per_cta - 1) / fl.events_per_cta;
+  if (ntiles < g_num_sms && env_int("FJP_FOREST_COMPACT", 1) != 2) return 0;   // too few tiles to fill the chip: the one-kernel walk / the sliced latency path (2 = always, for tests)
+  const long pass = compact_tiles_per_pass(m, fl, ntiles);
+  return (size_t)pass * m.F * fl.events_per_cta * 2 + (size_t)pass * fl.events_per_cta;
+}
+template <int D, int TI, int MODE, int MAXT>
+static cudaError_t launch_fcc(const DeviceModel& m, const BatchArgs& a, const ForestLaunch& fl, const KeyTiles& kt, int grid, cudaStream_t s) {
+  auto k = forest_compact_kernel<D, TI, MODE, MAXT>;
+  cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fl.smem_bytes);
+  if (e != cudaSuccess) return e;
+  k<<<grid, fl.events_per_cta, fl.smem_bytes, s>>>(m, a, fl, kt);
+  return cudaGetLastError();
+}
+static cudaError_t launch_forest_compact(const DeviceModel& m, const BatchArgs& a, const ForestLaunch& fl, void* scratch, cudaStream_t s, int* launches) {
+  const CompactDesc& cd = m.forest.compact;
+  const int E = fl.events_per_cta; const long ntiles = (a.n + E - 1) / E, pass = compact_tiles_per_pass(m, fl, ntiles);
+  KeyTiles kt{}; kt.keys = static_cast<uint16_t*>(scratch); kt.E = E; kt.tile_bytes = (uint32_t)((size_t)m.F * E * 2);
+  uint8_t* fail = static_cast<uint8_t*>(scratch) + (size_t)pass * kt.tile_bytes;
+  const int OS = ((E + 63) & ~63) + 8; const size_t rk_smem = (size_t)cd.block_smem + (size_t)CK_FB * OS * 2;
+  const int mode = m.forest.classify ? 2 : ((m.forest.method == FM_WSUM || m.forest.method == FM_WAVERAGE) ? 1 : 0);
+  const int d = m.forest.depth;
+  for (long t0 = 0; t0 < ntiles; t0 += pass) {
+    kt.row_begin = t0 * E; kt.ntiles = ntiles - t0 < pass ? ntiles - t0 : pass;
+    kt.fail = m.prep_simple ? nullptr : fail;
+    cudaError_t e;
+    if (kt.fail) { e = cudaMemsetAsync(fail, 0, (size_t)kt.ntiles * E, s); if (e != cudaSuccess) return e; }
+    int gx = 2 * g_num_sms / cd.n_blocks; if (gx < 1) gx = 1; if (gx > kt.ntiles) gx = (int)kt.ntiles;   // one wave: two CTAs per SM
+    if (m.prep_simple) {
+      cudaFuncSetAttribute(forest_rank_keys_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rk_smem);
+      forest_rank_keys_kernel<true><<<dim3(gx, cd.n_blocks), RK_THREADS, rk_smem, s>>>(m, a, kt);
+    } else {
+      cudaFuncSetAttribute(forest_rank_keys_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rk_smem);
+      forest_rank_keys_kernel<false><<<dim3(gx, cd.n_blocks), RK_THREADS, rk_smem, s>>>(m, a, kt);
+    }
+    e = cudaGetLastError(); if (e != cudaSuccess) return e;
+    if (launches) (*launches)++;
+    const int grid = (int)(kt.ntiles < g_num_sms ? kt.ntiles : g_num_sms);
+#define FJP_CC3(DD, TT, MM, XX) launch_fcc<DD, TT, MM, XX>(m, a, fl, kt, grid, s)
+#define FJP_CC2(DD, MM) (E > 768 ? FJP_CC3(DD, 4, MM, 1024) : (E > 640 ? (fl.trees_interleaved >= 8 ? FJP_CC3(DD, 8, MM, 768) : FJP_CC3(DD, 4, MM, 768)) \
+                                                                         : (fl.trees_interleaved >= 8 ? FJP_CC3(DD, 8, MM, 640) : FJP_CC3(DD, 4, MM, 640))))
+#define FJP_CC1(DD) (mode == 2 ? FJP_CC2(DD, 2) : (mode == 1 ? FJP_CC2(DD, 1) : FJP_CC2(DD, 0)))
+    e = d == 8 ? FJP_CC1(8) : FJP_CC1(0);
+#undef FJP_CC1
+#undef FJP_CC2
+#undef FJP_CC3
+    if (e != cudaSuccess) return e;
+    if (launches && t0 + pass < ntiles) (*launches)++;
+  }
+  return cudaSuccess;
+}
+
 cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t s, int* launches, void* slice_scratch) {
   query_device();
   if (a.n <= 0) return cudaSuccess;
@@ -1137,6 +1236,8 @@ cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t 
   switch (m.kind) {
     case MK_FOREST: {
       ForestLaunch fl;
+      if (slice_scratch && !a.node_ids && m.forest.method != FM_SINGLE && forest_compact_scratch_bytes(m, a.n) && plan_forest_compact(m, &fl))
+        return launch_forest_compact(m, a, fl, slice_scratch, s, launches);
       // single trees go through the general path (it reports node ids in aux); ensembles through the on-chip path
       if (m.forest.method != FM_SINGLE && plan_forest_complete(m, &fl)) {
         long ntiles = (a.n + fl.events_per_cta - 1) / fl.events_per_cta;

@@ -32,7 +32,8 @@ struct ForestLaunch {  // tile geometry of forest_complete_kernel
 
 bool plan_forest_complete(const DeviceModel& m, ForestLaunch* out);
 cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t s, int* launches, void* slice_scratch = nullptr);
-size_t forest_slice_scratch_bytes(const DeviceModel& m, long n);
+size_t forest_slice_scratch_bytes(const DeviceModel& m, long n);     // work area of either forest side path (0: none wanted)
+size_t forest_compact_scratch_bytes(const DeviceModel& m, long n);   // throughput path only
 cudaError_t launch_expand_sparse(const long long* row_ptr, const int32_t* idx, const double* val, long n, int F,
                                  double* X, uint32_t* present, cudaStream_t s, int* launches);
 size_t derived_scratch_bytes(const DeviceModel& m, long n);

@@ -62,8 +62,41 @@ struct GNode {
 };
 static constexpr int32_t LEAF_NULL = INT32_MIN;  // successor meaning "null prediction"
 
+#ifdef __CUDACC__
+#define FJP_HD __host__ __device__
+#else
+#define FJP_HD
+#endif
+
+// Compact form of a complete forest for the throughput path (large batches): 16-bit rank keys and 4-byte nodes halve the
+// shared-memory footprint of a key tile (twice the resident warps) and the bank conflicts of the node gather.
+//   key(x[f])   0 = missing, else 2*lo + 1 (+1 when x equals threshold lo), lo = number of distinct thresholds of f below x
+//               (the scheme of ENC_RANK); computed by forest_rank_keys_kernel from the float image of x: a bucket table
+//               over the value range gives the few candidate thresholds, a binary search among them the exact rank.
+//   tree blob   u32 node[2^D] in heap order (node[0] unused), then 2^D leaves (8 B), then the segment weight (double).
+//               node = a | feat << 1 | (~(K - a) & 0xFFFF) << 16;  right iff key - a > K - a, evaluated as the carry of
+//               (key - a) + sign_extend16(node >> 16)  (K < 2^15, or "never"/"only missing": ~(K - a) in {0, 1}).
+constexpr int CK_FB = 8;             // features per block of the key pre-pass
+struct CkFeat { uint32_t thr_off, n_thr, tab_off, nb; float lo, scale; };   // byte offsets inside the feature block's table area
+struct CompactDesc {
+  int enabled, tree_bytes, n_blocks, block_smem;   // block_smem: largest table area of one feature block
+  const uint32_t* blobs;       // n_trees x tree_bytes
+  const CkFeat* feat;          // F
+  const uint8_t* tables;       // per feature block: sorted distinct threshold images (u32, 0xFFFFFFFF-terminated) and bucket tables (u16 x nb)
+  const uint32_t* block_off;   // n_blocks + 1 byte offsets into tables (multiples of 16)
+};
+FJP_HD inline int compact_tree_bytes(int depth) { return (int)(((12u << depth) + 8u + 15u) & ~15u); }
+// bucket of a (finite or infinite, not NaN) float value; monotone non-decreasing in x, the same arithmetic on host and device
+FJP_HD inline uint32_t ck_bucket(float x, float lo, float scale, uint32_t nb) {
+  float t = (x - lo) * scale;
+  if (!(t > 0.0f)) return 0u;
+  if (t >= (float)nb) return nb - 1u;
+  return (uint32_t)t;
+}
+
 struct ForestDesc {
   int n_trees, depth, format, enc, method, classify;
+  CompactDesc compact;
   int n_channels; const ChannelSpec* channels; const int32_t* tree_channel;   // FM_CHAIN only
   // FOREST_COMPLETE: n_trees blobs of 2^(depth+1) 8-byte words: [0] = segment weight (double), [1 .. 2^d-1] = nodes
   // in heap order {lo: feat | a<<31, hi: ~ka}, [2^d .. 2^(d+1)-1] = leaves (double value, or label index as u64);

@@ -602,6 +602,77 @@ struct ForestBuilder {
     return !std::isnan(a) && std::isnan(b);
   }
 
+  // Compact form for the throughput path (model.h CompactDesc): rank keys per feature + bucket tables for the key pre-pass,
+  // 4-byte nodes.  Only when every threshold is a float (so that one float image per value decides every test).
+  template <class FeatOf> void emit_compact(int depth, const std::vector<uint8_t>& used, FeatOf feat_of) {
+    ForestDesc& fd = b.cm.dev.forest; CompactDesc& cd = fd.compact; const int F = b.cm.dev.F;
+    if (F > 256 || depth < 1) return;
+    std::vector<std::vector<uint32_t>> img(F);
+    for (size_t i = 0; i < thr.size(); i++) if (used[i] && thr[i].slot >= 0) img[thr[i].slot].push_back(ordkey((float)thr[i].value));
+    for (auto& v : img) { std::sort(v.begin(), v.end()); v.erase(std::unique(v.begin(), v.end()), v.end()); if (v.size() > 16382) return; }
+    auto unkey = [](uint32_t k) { uint32_t u = (k & 0x80000000u) ? (k & 0x7FFFFFFFu) : ~k; float f; memcpy(&f, &u, 4); return f; };
+    // rank key of every threshold
+    std::vector<uint32_t> K16(thr.size(), 0);
+    for (size_t i = 0; i < thr.size(); i++) {
+      if (!used[i] || thr[i].slot < 0) continue;
+      const auto& v = img[thr[i].slot];
+      uint32_t j = (uint32_t)(std::lower_bound(v.begin(), v.end(), ordkey((float)thr[i].value)) - v.begin());
+      K16[i] = thr[i].strict ? 2u * j + 1u : 2u * j + 2u;
+    }
+    // tables, one area per block of CK_FB features
+    const int nblocks = (F + CK_FB - 1) / CK_FB;
+    std::vector<CkFeat> feats(F); std::vector<uint8_t> tables; std::vector<uint32_t> block_off(nblocks + 1, 0); size_t block_smem = 0;
+    for (int fb = 0; fb < nblocks; fb++) {
+      const size_t start = tables.size(); block_off[fb] = (uint32_t)start;
+      for (int f = fb * CK_FB; f < std::min(F, (fb + 1) * CK_FB); f++) {
+        const auto& v = img[f]; CkFeat& cf = feats[f]; const uint32_t n = (uint32_t)v.size();
+        uint32_t nb = 16; while (nb < 2 * n && nb < 4096) nb *= 2;
+        float lo = n ? unkey(v.front()) : 0.0f, hi = n ? unkey(v.back()) : 0.0f;
+        float scale = (n && hi > lo) ? (float)nb / (hi - lo) : 0.0f;
+        if (!std::isfinite(scale)) scale = 0.0f;
+        cf.n_thr = n; cf.nb = nb; cf.lo = lo; cf.scale = scale;
+        cf.thr_off = (uint32_t)(tables.size() - start);
+        tables.resize(tables.size() + 4 * (size_t)(n + 4), 0xFF);   // four 0xFFFFFFFF sentinels end the array: the scan needs no bounds
+        if (n) memcpy(tables.data() + start + cf.thr_off, v.data(), 4 * (size_t)n);
+        cf.tab_off = (uint32_t)(tables.size() - start);
+        std::vector<uint16_t> tab(nb + 1, 0);   // tab[b] = thresholds whose bucket is below b
+        for (uint32_t j = 0; j < n; j++) tab[ck_bucket(unkey(v[j]), lo, scale, nb) + 1]++;
+        for (uint32_t q = 1; q <= nb; q++) tab[q] = (uint16_t)(tab[q] + tab[q - 1]);
+        tables.resize(tables.size() + 2 * (size_t)nb); memcpy(tables.data() + start + cf.tab_off, tab.data(), 2 * (size_t)nb);   // nb is even: stays 4-byte aligned
+      }
+      tables.resize((tables.size() + 15) & ~size_t(15));
+      block_smem = std::max(block_smem, tables.size() - start);
+    }
+    block_off[nblocks] = (uint32_t)tables.size();
+    if (block_smem > 104 * 1024) return;   // two CTAs of the key pre-pass per SM
+    // trees
+    const size_t TB = (size_t)compact_tree_bytes(depth), first_leaf = size_t(1) << depth;
+    std::vector<uint32_t> blobs(roots.size() * TB / 4, 0); bool ok = true;
+    for (size_t t = 0; t < roots.size() && ok; t++) {
+      uint8_t* bl = reinterpret_cast<uint8_t*>(blobs.data()) + t * TB;
+      uint32_t* nd = reinterpret_cast<uint32_t*>(bl);
+      memcpy(bl + 12 * first_leaf, &weights[t], 8);
+      std::function<void(int32_t, size_t)> place = [&](int32_t s, size_t h) {
+        if (s < 0) {
+          const TLeaf& lf = leaves[~s];
+          if (h < first_leaf) { nd[h] = 0; place(s, 2 * h); place(s, 2 * h + 1); return; }   // pass-through: never "right"
+          uint8_t* dst = bl + 4 * first_leaf + 8 * (h - first_leaf);
+          if (classify) { uint64_t l = (uint64_t)(uint32_t)lf.label; memcpy(dst, &l, 8); } else memcpy(dst, &lf.value, 8);
+          return;
+        }
+        const TNode& n = nodes[s]; uint32_t a = (n.on_missing == n.on_false && n.on_true != n.on_false) ? 1u : 0u;
+        uint32_t kk = n.thr >= 0 ? K16[n.thr] : 0xFFFFFFFFu, y = ~(kk - a), feat = (uint32_t)feat_of(n);
+        if ((uint32_t)(int32_t)(int16_t)(y & 0xFFFFu) != y || feat > 255) ok = false;   // must survive the 16-bit sign extension
+        nd[h] = a | (feat << 1) | ((y & 0xFFFFu) << 16);
+        place(n.on_true, 2 * h); place(n.on_false, 2 * h + 1);
+      };
+      place(roots[t], 1);
+    }
+    if (!ok) return;
+    cd.enabled = 1; cd.tree_bytes = (int)TB; cd.n_blocks = nblocks; cd.block_smem = (int)block_smem;
+    b.put(&cd.blobs, blobs); b.put(&cd.feat, feats); b.put(&cd.tables, tables); b.put(&cd.block_off, block_off);
+  }
+
   void emit(int method) {
     ForestDesc& fd = b.cm.dev.forest; int F = b.cm.dev.F;
     fd.n_trees = (int)roots.size(); fd.method = method; fd.classify = classify ? 1 : 0;
@@ -697,6 +768,7 @@ struct ForestBuilder {
         place(roots[t], 1);
       }
       b.put(&fd.blobs, blobs);
+      if (float_ok && method != FM_CHAIN && method != FM_SINGLE) emit_compact(depth, used, feat_of);
     } else {
       fd.format = FOREST_GENERAL; fd.depth = 0;
       std::vector<uint64_t> blobs; b.put(&fd.blobs, blobs);

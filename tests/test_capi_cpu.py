@@ -72,6 +72,17 @@ def test_compiled_layouts(capi, gen):
     assert "layers=2" in capi.compile_model(pm).describe
 
 
+def test_deep_forests_compile_on_the_host(capi, gen):
+    """Complete-tree blobs of every depth / width the GPU suite and the bench use are built on the host without a device."""
+    for T, depth, F in ((20, 8, 100), (6, 6, 128), (6, 6, 130), (6, 5, 10), (3, 10, 40)):
+        pm, _ = gen.gbt_pmml(T=T, depth=depth, F=F, seed=depth)
+        d = capi.compile_model(pm).describe
+        assert "format=complete" in d and f"depth={depth}" in d and f"trees={T}" in d, d
+        assert f"nodes={T * ((1 << depth) - 1)}" in d, d
+    pm, _ = gen.rf_pmml(T=9, depth=7, F=30, n_labels=3, seed=5)
+    assert "format=complete" in capi.compile_model(pm).describe
+
+
 def test_unsupported_features_are_load_errors_not_wrong_answers(capi, gen):
     pm, _ = gen.gbt_pmml(T=3, depth=2, F=4, seed=1)
     for bad in (pm.replace(b'multipleModelMethod="sum"', b'multipleModelMethod="modelChain"'),

@@ -1,0 +1,131 @@
+"""GPU parity for the forest throughput path (csrc/forest_compact.cuh): rank-key pre-pass + compact walk.
+
+Large batches of an eligible ensemble take this path on their own; here FJP_FOREST_COMPACT=2 forces it for batches small
+enough for the oracle, FJP_FOREST_COMPACT=0 gives the one-kernel walk to compare with.  Bar: statuses, labels and scores
+bit-identical to the oracle and to the other path (sums are added in segment order on both)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def score_both(engine, m, X, pb, monkeypatch, replace=None):
+    monkeypatch.setenv("FJP_FOREST_COMPACT", "0")
+    classic = engine.score(m, X, pb, replace)
+    monkeypatch.setenv("FJP_FOREST_COMPACT", "2")
+    launches = engine.launch_count
+    compact = engine.score(m, X, pb, replace)
+    assert engine.launch_count - launches >= 2          # pre-pass + walk really ran
+    return classic, compact
+
+
+def same(a, b):
+    assert np.array_equal(a["status"], b["status"])
+    assert np.array_equal(a["score"].view(np.int64), b["score"].view(np.int64))
+
+
+@pytest.mark.parametrize("dtype,method,n", [("double", "sum", 20000), ("float", "sum", 7777), ("double", "average", 641)])
+def test_gbt_vs_oracle_and_one_kernel_walk(engine, oracle, gen, monkeypatch, dtype, method, n):
+    pm, arr = gen.gbt_pmml(T=37, depth=5, F=13, seed=11, dtype=dtype, method=method)
+    m, om = engine.compile(pm), oracle.OracleModel(pm)
+    assert "compact=1" in m.describe
+    X, pres, pb = gen.events(n, 13, 12, 0.15)
+    X[::97, 3] = np.nan            # present NaN: greatest in compareTo order
+    X[::89, 5] = np.inf
+    X[::83, 7] = -0.0
+    X[::7, 0] = arr["thr"][0, 0]   # exactly on a threshold, and one float step either side of it
+    X[::11, int(arr["feat"][1, 0])] = np.nextafter(np.float32(arr["thr"][1, 0]), np.float32(np.inf))
+    X[::13, int(arr["feat"][2, 0])] = np.nextafter(arr["thr"][2, 0], -np.inf)
+    classic, compact = score_both(engine, m, X, pb, monkeypatch)
+    o = om.predict(X, pb, nthreads=8)
+    same(compact, o)
+    same(compact, classic)
+
+
+def test_c4_depth8_vs_oracle(engine, oracle, gen, monkeypatch):
+    pm, arr = gen.gbt_pmml()
+    m, om = engine.compile(pm), oracle.OracleModel(pm)
+    X, pres, pb = gen.events(4096, 100, gen.SEED_BASE + 4, 0.10)
+    classic, compact = score_both(engine, m, X, pb, monkeypatch)
+    same(compact, om.predict(X, pb, nthreads=8))
+    same(compact, classic)
+    # at a size where the path is taken unforced: numpy restatement of the same walk
+    monkeypatch.delenv("FJP_FOREST_COMPACT")
+    X, pres, pb = gen.events(148 * 640 + 333, 100, 99, 0.10)
+    launches = engine.launch_count
+    r = engine.score(m, X, pb)
+    assert engine.launch_count - launches >= 2
+    assert (r["status"] == 0).all() and np.array_equal(r["score"], gen.gbt_numpy(arr, X, pres))
+
+
+def test_replace_nan_and_dense_rows(engine, oracle, gen, monkeypatch):
+    pm, arr = gen.gbt_pmml(T=24, depth=6, F=20, seed=3)
+    m, om = engine.compile(pm), oracle.OracleModel(pm)
+    X, pres, pb = gen.events(5000, 20, 4, 0.2)
+    rep = np.full(5000, np.nan); rep[::3] = 0.25; rep[1::3] = -1.5
+    classic, compact = score_both(engine, m, X, pb, monkeypatch, rep)
+    same(compact, om.predict(X, pb, rep, nthreads=8))
+    same(compact, classic)
+    classic, compact = score_both(engine, m, np.nan_to_num(X), None, monkeypatch)      # no present bits at all
+    same(compact, om.predict(np.nan_to_num(X), None, nthreads=8))
+
+
+def test_rf_majority_vote(engine, oracle, gen, monkeypatch):
+    pm, arr = gen.rf_pmml(T=50, depth=6, F=20, n_labels=4, seed=21)
+    m, om = engine.compile(pm), oracle.OracleModel(pm)
+    assert "compact=1" in m.describe
+    X, pres, pb = gen.events(20000, 20, 22, 0.1)
+    classic, compact = score_both(engine, m, X, pb, monkeypatch)
+    same(compact, om.predict(X, pb, nthreads=8))
+    same(compact, classic)
+    assert np.array_equal(compact["score"], gen.rf_numpy(arr, X, pres))
+
+
+def test_pruned_trees_strict_tests_float_fields(engine, oracle, gen, monkeypatch):
+    pm = gen.gbt_pruned_pmml(T=60, max_depth=6, F=20, seed=5)
+    m, om = engine.compile(pm), oracle.OracleModel(pm)
+    assert "compact=1" in m.describe and "depth=6" in m.describe
+    X, pres, pb = gen.events(20000, 20, 6, 0.1)
+    X[::50, 2] = np.nan
+    classic, compact = score_both(engine, m, X, pb, monkeypatch)
+    same(compact, om.predict(X, pb, nthreads=8))
+    same(compact, classic)
+
+
+def test_invalid_values_fail_the_row(engine, oracle, gen, monkeypatch):
+    """An Interval on a DataField makes values outside it invalid; the default invalidValueTreatment (returnInvalid) turns
+    the row into EmptyScore (status 2).  The pre-pass flags those rows for the walk kernel."""
+    pm, arr = gen.gbt_pmml(T=16, depth=4, F=9, seed=8)
+    pm = pm.replace(b'<DataField name="x2" optype="continuous" dataType="double"/>',
+                    b'<DataField name="x2" optype="continuous" dataType="double"><Interval closure="closedClosed" leftMargin="-1" rightMargin="1"/></DataField>')
+    m, om = engine.compile(pm), oracle.OracleModel(pm)
+    assert "prep_simple=0" in m.describe and "compact=1" in m.describe
+    X, pres, pb = gen.events(9000, 9, 9, 0.1)
+    classic, compact = score_both(engine, m, X, pb, monkeypatch)
+    o = om.predict(X, pb, nthreads=8)
+    assert (o["status"] == 2).sum() > 1000 and (o["status"] == 0).sum() > 1000
+    same(compact, o)
+    same(compact, classic)
+
+
+def test_device_entry_point_takes_the_path_for_large_batches(engine, gen):
+    import torch
+    from flink_jpmml_b200 import capi
+    pm, arr = gen.gbt_pmml(T=40, depth=8, F=32, seed=31)
+    m = engine.compile(pm)
+    n = 148 * 1024 + 17
+    X, pres, pb = gen.events(n, 32, 32, 0.1)
+    st = torch.cuda.Stream()
+    with torch.cuda.stream(st):
+        dX = torch.from_numpy(X).cuda(); dP = torch.from_numpy(pb.view(np.int32)).cuda()
+        dS = torch.empty(n, dtype=torch.float64, device="cuda"); dT = torch.empty(n, dtype=torch.uint8, device="cuda")
+        st.synchronize()
+        launches = engine.launch_count
+        for _ in range(2):   # twice: the work area comes back from the stream-ordered pool
+            rc = capi.lib().fjp_score_device(engine._h, m._h, dX.data_ptr(), dP.data_ptr(), None, n, 32, dS.data_ptr(), dT.data_ptr(), None, C.c_void_p(st.cuda_stream))
+            assert rc == 0
+        st.synchronize()
+    assert engine.launch_count - launches == 4
+    assert np.array_equal(dS.cpu().numpy(), gen.gbt_numpy(arr, X, pres)) and int(dT.sum().item()) == 0
