@@ -271,7 +271,9 @@ def main():
         roof = {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": achieved / pk["hbm_gbs"],
                 "traffic": (micro["forest_kernel_dram_bytes_per_event"] * n) if micro.get("forest_kernel_dram_bytes_per_event") else None,
                 "traffic_source": "ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum per event x events per launch (profiles/ncu_forest_r01.txt)", "peak_source": pk["source"],
-                "kernel": "forest_complete_kernel<8,8,0,false>", "algorithmic_bytes_per_event": ALGO_HBM_BYTES,
+                "kernel": ("forest_rank_keys_kernel<true> + forest_compact_kernel<8,8,0,640> (throughput path: %d launches per step, timed together)" % (launches // max(1, args.steps)))
+                          if launches > args.steps else "forest_complete_kernel<8,8,0,false>",
+                "algorithmic_bytes_per_event": ALGO_HBM_BYTES,
                 "note": "the walk is bound by shared-memory gathers / issue, not HBM: see gather",
                 "gather": {"algorithmic_bytes_per_event": ALGO_GATHER_BYTES, "achieved_gbs": gather,
                            "l2_gather_peak_gbs": micro.get("l2_gather_8B_2MB_GBs"), "smem_gather_peak_gbs": micro.get("smem_gather_8B_random_GBs"),

@@ -2,7 +2,10 @@
 //
 // Two kernels per (sub-)batch, see model.h CompactDesc:
 //   forest_rank_keys_kernel   X[n][F] doubles (+ present bits, replaceNan, input preparation) -> 16-bit rank keys, written as
-//                             ready-made shared-memory images of the walk kernel's key tiles:  tile t = keys[f][e], e < E.
+//                             ready-made shared-memory images of the walk kernel's key tiles:  tile t = word[f / 2][e], e < E,
+//                             each 32-bit word holding the keys of features 2p (low half) and 2p + 1 (high half) of one event.
+//                             (Lane e of a warp then always reads bank e whatever feature its node tests; with two EVENTS per
+//                             word, lanes 2i and 2i+1 would collide whenever they test different features.)
 //   forest_compact_kernel     one CTA = one tile of E events (one per thread): the key tile arrives with one bulk copy, tree
 //                             blobs (4-byte nodes) stream through the same 2-stage ring as forest_complete_kernel, TI trees
 //                             interleaved per thread; per level LDS.32 node, LDS.U16 key, carry-chain index update.
@@ -11,12 +14,12 @@
 #pragma once
 
 struct KeyTiles {
-  uint16_t* keys;        // tiles x (F x E) rank keys
+  uint32_t* keys;        // tiles x (ceil(F/2) x E) words of two rank keys
   uint8_t* fail;         // tiles x E: 1 = input preparation refused the row (returnInvalid); NULL when that cannot happen
   long row_begin;        // first batch row of tile 0
   long ntiles;
   int E;                 // events per tile
-  uint32_t tile_bytes;   // F * E * 2
+  uint32_t tile_bytes;   // ceil(F/2) * E * 4
 };
 
 constexpr int RK_THREADS = 512;
@@ -113,11 +116,13 @@ __global__ void __launch_bounds__(RK_THREADS, 2) forest_rank_keys_kernel(const _
       }
     }
     __syncthreads();
-    uint16_t* dst = kt.keys + (size_t)tile * (kt.tile_bytes / 2) + (size_t)f0 * E;
-    const int q4 = E >> 2;   // 8-byte units per feature row
-    for (int i = tid; i < nf * q4; i += RK_THREADS) {
-      const int jj = i / q4, q = i - jj * q4;
-      *reinterpret_cast<uint2*>(dst + (size_t)jj * E + 4 * q) = *reinterpret_cast<const uint2*>(out + jj * OS + 4 * q);
+    uint32_t* dst = kt.keys + (size_t)tile * (kt.tile_bytes / 4) + (size_t)(f0 >> 1) * E;   // f0 is even
+    const int q2 = E >> 1, npairs = (nf + 1) >> 1;   // a thread packs two events of one feature pair per 8-byte store
+    for (int i = tid; i < npairs * q2; i += RK_THREADS) {
+      const int p = i / q2, q = i - p * q2;
+      const uint32_t lo = *reinterpret_cast<const uint32_t*>(out + (2 * p) * OS + 2 * q);                          // feature 2p,   events 2q, 2q+1
+      const uint32_t hi = 2 * p + 1 < nf ? *reinterpret_cast<const uint32_t*>(out + (2 * p + 1) * OS + 2 * q) : 0u;  // feature 2p+1
+      *reinterpret_cast<uint2*>(dst + (size_t)p * E + 2 * q) = make_uint2(__byte_perm(lo, hi, 0x5410), __byte_perm(lo, hi, 0x7632));
     }
     __syncthreads();   // the staging tile is reused by the next tile
   }
@@ -135,7 +140,6 @@ forest_compact_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, 
   const uint32_t off_leaf = 4u * nleaf - 8u * nleaf;   // leaf h (h >= 2^depth) lives at 4*2^depth + 8*(h - 2^depth); wraps, 32-bit address arithmetic
   const uint32_t off_w = 12u * nleaf;
   const int G = fl.trees_per_stage;
-  uint16_t* keys = reinterpret_cast<uint16_t*>(smem);
   uint8_t* ring = smem + fl.off_ring;
   uint16_t* votes = reinterpret_cast<uint16_t*>(smem + fl.off_votes);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + fl.off_bars);
@@ -165,8 +169,8 @@ forest_compact_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, 
     if (MODE == 2) for (int l = 0; l < m.n_labels; l++) { votes[l * E + tid] = 0; votes[(m.n_labels + l) * E + tid] = 0xFFFF; }
     mbar_wait(&bars[2], tile_parity); tile_parity ^= 1u;
 
-    const uint32_t kbase = smem_u32(keys) + 2u * tid;   // byte address of this event's key column
-    const uint32_t Eb = (uint32_t)E;                     // (node & 0x1FE) * E = feat * 2E bytes
+    const uint32_t kbase = smem_u32(smem) + 4u * tid;    // byte address of this event's column of key-pair words
+    const uint32_t Eb = (uint32_t)E;                     // (node & 0x1FC) * E = (feat / 2) * 4E bytes; node & 2 picks the half
     double sum = 0.0, wsum = 0.0; uint32_t seen = 0;
     for (int g = 0; g < NG; g++) {
       uint32_t slot = q_wait & 1u;
@@ -184,7 +188,7 @@ forest_compact_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, 
           for (int k = 0; k < TI; k++) {
             uint32_t nd, key;
             asm volatile("ld.shared.u32 %0, [%1];" : "=r"(nd) : "r"(bl[k] + idx[k] * 4u));
-            asm volatile("ld.shared.u16 %0, [%1];" : "=r"(key) : "r"(kbase + (nd & 0x1FEu) * Eb));
+            asm volatile("ld.shared.u16 %0, [%1];" : "=r"(key) : "r"((kbase + (nd & 0x1FCu) * Eb) | (nd & 2u)));
             const uint32_t vv = key - (nd & 1u), ny = (uint32_t)((int32_t)nd >> 16);
             // ny = ~(K - a): vv + ny carries out exactly when vv > K - a ("go right"); idx = 2*idx + carry
             asm("{\n\t.reg .u32 t;\n\tadd.cc.u32 t, %2, %3;\n\taddc.u32 %0, %1, %1;\n\t}" : "=r"(idx[k]) : "r"(idx[k]), "r"(ny), "r"(vv));

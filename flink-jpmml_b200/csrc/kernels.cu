@@ -1151,7 +1151,7 @@ static bool plan_forest_compact(const DeviceModel& m, ForestLaunch* out) {
   for (int E : kE) {
     if (force_e && E != force_e) continue;
     if (E == 1024) ti = 4;   // 64 registers per thread
-    size_t keys = ((size_t)m.F * E * 2 + 127) & ~size_t(127);
+    size_t keys = ((size_t)((m.F + 1) / 2) * E * 4 + 127) & ~size_t(127);
     size_t votes = fd.classify ? (size_t)2 * m.n_labels * E * 2 : 0;
     size_t fixed = keys + votes + 64 + 256;
     if (fixed + 2 * ti * TB > budget) continue;
@@ -1168,10 +1168,12 @@ static bool plan_forest_compact(const DeviceModel& m, ForestLaunch* out) {
   }
   return false;
 }
-// tiles scored per pass over the work area: a multiple of the SM count, at most ~256 MB of keys
+// tiles scored per pass over the work area: a multiple of the SM count, at most ~64 MB of keys -- written by the pre-pass
+// and read back by the walk kernel while still resident in the 126 MB L2, so they cost no HBM traffic
 static long compact_tiles_per_pass(const DeviceModel& m, const ForestLaunch& fl, long ntiles) {
-  const size_t tile_bytes = (size_t)m.F * fl.events_per_cta * 2;
-  long cap = (long)((size_t(256) << 20) / tile_bytes); cap = cap / g_num_sms * g_num_sms; if (cap < g_num_sms) cap = g_num_sms;
+  const size_t tile_bytes = (size_t)((m.F + 1) / 2) * fl.events_per_cta * 4;
+  long cap = (long)((size_t(64) << 20) / tile_bytes); cap = cap / g_num_sms * g_num_sms; if (cap < g_num_sms) cap = g_num_sms;
+  if (int per_sm = env_int("FJP_FOREST_CPASS", 0)) cap = (long)per_sm * g_num_sms;   // tuning aid: tiles per SM and pass
   return ntiles < cap ? ntiles : cap;
 }
 size_t forest_compact_scratch_bytes(const DeviceModel& m, long n) {
@@ -1181,7 +1183,7 @@ size_t forest_compact_scratch_bytes(const DeviceModel& m, long n) {
   const long ntiles = (n + fl.events_per_cta - 1) / fl.events_per_cta;
   if (ntiles < g_num_sms && env_int("FJP_FOREST_COMPACT", 1) != 2) return 0;   // too few tiles to fill the chip: the one-kernel walk / the sliced latency path (2 = always, for tests)
   const long pass = compact_tiles_per_pass(m, fl, ntiles);
-  return (size_t)pass * m.F * fl.events_per_cta * 2 + (size_t)pass * fl.events_per_cta;
+  return (size_t)pass * ((m.F + 1) / 2) * fl.events_per_cta * 4 + (size_t)pass * fl.events_per_cta;
 }
 template <int D, int TI, int MODE, int MAXT>
 static cudaError_t launch_fcc(const DeviceModel& m, const BatchArgs& a, const ForestLaunch& fl, const KeyTiles& kt, int grid, cudaStream_t s) {
@@ -1194,7 +1196,7 @@ static cudaError_t launch_fcc(const DeviceModel& m, const BatchArgs& a, const Fo
 static cudaError_t launch_forest_compact(const DeviceModel& m, const BatchArgs& a, const ForestLaunch& fl, void* scratch, cudaStream_t s, int* launches) {
   const CompactDesc& cd = m.forest.compact;
   const int E = fl.events_per_cta; const long ntiles = (a.n + E - 1) / E, pass = compact_tiles_per_pass(m, fl, ntiles);
-  KeyTiles kt{}; kt.keys = static_cast<uint16_t*>(scratch); kt.E = E; kt.tile_bytes = (uint32_t)((size_t)m.F * E * 2);
+  KeyTiles kt{}; kt.keys = static_cast<uint32_t*>(scratch); kt.E = E; kt.tile_bytes = (uint32_t)((size_t)((m.F + 1) / 2) * E * 4);
   uint8_t* fail = static_cast<uint8_t*>(scratch) + (size_t)pass * kt.tile_bytes;
   const int OS = ((E + 63) & ~63) + 8; const size_t rk_smem = (size_t)cd.block_smem + (size_t)CK_FB * OS * 2;
   const int mode = m.forest.classify ? 2 : ((m.forest.method == FM_WSUM || m.forest.method == FM_WAVERAGE) ? 1 : 0);

@@ -73,6 +73,7 @@ static constexpr int32_t LEAF_NULL = INT32_MIN;  // successor meaning "null pred
 //   key(x[f])   0 = missing, else 2*lo + 1 (+1 when x equals threshold lo), lo = number of distinct thresholds of f below x
 //               (the scheme of ENC_RANK); computed by forest_rank_keys_kernel from the float image of x: a bucket table
 //               over the value range gives the few candidate thresholds, a binary search among them the exact rank.
+//               A key tile in shared memory is word[f / 2][event]: the keys of features 2p and 2p + 1 share a 32-bit word.
 //   tree blob   u32 node[2^D] in heap order (node[0] unused), then 2^D leaves (8 B), then the segment weight (double).
 //               node = a | feat << 1 | (~(K - a) & 0xFFFF) << 16;  right iff key - a > K - a, evaluated as the carry of
 //               (key - a) + sign_extend16(node >> 16)  (K < 2^15, or "never"/"only missing": ~(K - a) in {0, 1}).

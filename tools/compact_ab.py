@@ -22,7 +22,7 @@ def run(dS, dT):
     assert rc == 0, L.fjp_last_error()
 
 def timed(label, env):
-    for k in ("FJP_FOREST_COMPACT", "FJP_FOREST_CE", "FJP_FOREST_CTI", "FJP_FOREST_CG"): os.environ.pop(k, None)
+    for k in ("FJP_FOREST_COMPACT", "FJP_FOREST_CE", "FJP_FOREST_CTI", "FJP_FOREST_CG", "FJP_FOREST_CPASS"): os.environ.pop(k, None)
     os.environ.update(env)
     dS = torch.full((n,), -1.0, dtype=torch.float64, device="cuda"); dT = torch.full((n,), 9, dtype=torch.uint8, device="cuda")
     for _ in range(3): run(dS, dT)
@@ -40,9 +40,10 @@ ref = g.gbt_numpy(arr, X[:20000], pres[:20000])
 print("classic matches numpy:", np.array_equal(base_S[:20000].cpu().numpy(), ref))
 variants = sys.argv[2:] or ["640,8,0", "768,8,0", "1024,4,0", "640,4,0"]
 for v in variants:
-    ce, cti, cg = v.split(",")
+    ce, cti, cg, *rest = v.split(",")
     env = {"FJP_FOREST_COMPACT": "1", "FJP_FOREST_CE": ce, "FJP_FOREST_CTI": cti}
     if cg != "0": env["FJP_FOREST_CG"] = cg
+    if rest: env["FJP_FOREST_CPASS"] = rest[0]
     S, T = timed(f"compact E={ce} TI={cti} G={cg}", env)
     same = bool(torch.equal(S.view(torch.int64), base_S.view(torch.int64))) and bool(torch.equal(T, base_T))
     print("   bit-identical to classic:", same, flush=True)
