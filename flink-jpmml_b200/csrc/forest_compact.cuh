@@ -8,7 +8,7 @@
 //                             word, lanes 2i and 2i+1 would collide whenever they test different features.)
 //   forest_compact_kernel     one CTA = one tile of E events (one per thread): the key tile arrives with one bulk copy, tree
 //                             blobs (4-byte nodes) stream through the same 2-stage ring as forest_complete_kernel, TI trees
-//                             interleaved per thread; per level LDS.32 node, LDS.U16 key, carry-chain index update.
+//                             interleaved per thread; per level LDS.32 node, LDS.U16 key, two LOP3, carry-chain index update.
 // Results are bit-identical to forest_complete_kernel: same decisions (rank keys order values exactly like the float images),
 // same leaf values, same order of the double additions.
 #pragma once
@@ -112,7 +112,7 @@ __global__ void __launch_bounds__(RK_THREADS, 2) forest_rank_keys_kernel(const _
       for (int k = 0; k < RK_BATCH; k++) {
         const int ee = min(i0 + k * RK_THREADS, total - 1) >> 3;      // the unclamped event slot of the tile
         if (!SIMPLE && st[k] == 2 && ee <= last) kt.fail[tile * E + ee] = 1;
-        out_row[ee] = (uint16_t)(st[k] == 0 ? key[k] : 0u);
+        out_row[ee] = (uint16_t)(st[k] == 0 ? key[k] : 0x8000u);   // 0x8000 = missing
       }
     }
     __syncthreads();
@@ -188,9 +188,12 @@ forest_compact_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, 
           for (int k = 0; k < TI; k++) {
             uint32_t nd, key;
             asm volatile("ld.shared.u32 %0, [%1];" : "=r"(nd) : "r"(bl[k] + idx[k] * 4u));
-            asm volatile("ld.shared.u16 %0, [%1];" : "=r"(key) : "r"((kbase + (nd & 0x1FCu) * Eb) | (nd & 2u)));
-            const uint32_t vv = key - (nd & 1u), ny = (uint32_t)((int32_t)nd >> 16);
-            // ny = ~(K - a): vv + ny carries out exactly when vv > K - a ("go right"); idx = 2*idx + carry
+            uint32_t ka, vv;
+            asm("lop3.b32 %0, %1, %2, 2, 0xF8;" : "=r"(ka) : "r"(kbase + (nd & 0x1FCu) * Eb), "r"(nd));   // | (nd & 2): the half of the word
+            asm volatile("ld.shared.u16 %0, [%1];" : "=r"(key) : "r"(ka));
+            asm("lop3.b32 %0, %1, %2, 0x8000, 0xD0;" : "=r"(vv) : "r"(key), "r"(nd));   // a (node bit 15) keeps the missing bit, else key & 0x7FFF
+            const uint32_t ny = (uint32_t)((int32_t)nd >> 16);
+            // ny = ~K: vv + ny carries out exactly when vv > K ("go right"); idx = 2*idx + carry
             asm("{\n\t.reg .u32 t;\n\tadd.cc.u32 t, %2, %3;\n\taddc.u32 %0, %1, %1;\n\t}" : "=r"(idx[k]) : "r"(idx[k]), "r"(ny), "r"(vv));
           }
         }

@@ -70,13 +70,14 @@ static constexpr int32_t LEAF_NULL = INT32_MIN;  // successor meaning "null pred
 
 // Compact form of a complete forest for the throughput path (large batches): 16-bit rank keys and 4-byte nodes halve the
 // shared-memory footprint of a key tile (twice the resident warps) and the bank conflicts of the node gather.
-//   key(x[f])   0 = missing, else 2*lo + 1 (+1 when x equals threshold lo), lo = number of distinct thresholds of f below x
-//               (the scheme of ENC_RANK); computed by forest_rank_keys_kernel from the float image of x: a bucket table
-//               over the value range gives the few candidate thresholds, a binary search among them the exact rank.
+//   key(x[f])   0x8000 = missing, else 2*lo + 1 (+1 when x equals threshold lo), lo = number of distinct thresholds of f below
+//               x (the scheme of ENC_RANK, < 0x7FFF); computed by forest_rank_keys_kernel from the float image of x: a bucket
+//               table over the value range gives the few candidate thresholds, a short scan among them the exact rank.
 //               A key tile in shared memory is word[f / 2][event]: the keys of features 2p and 2p + 1 share a 32-bit word.
 //   tree blob   u32 node[2^D] in heap order (node[0] unused), then 2^D leaves (8 B), then the segment weight (double).
-//               node = a | feat << 1 | (~(K - a) & 0xFFFF) << 16;  right iff key - a > K - a, evaluated as the carry of
-//               (key - a) + sign_extend16(node >> 16)  (K < 2^15, or "never"/"only missing": ~(K - a) in {0, 1}).
+//               node = feat << 1 | a << 15 | (~K & 0xFFFF) << 16;  right iff (a ? key : key & 0x7FFF) > K, evaluated as the
+//               carry of that value + sign_extend16(node >> 16).  a = 1 sends a missing value right.  Without a threshold:
+//               ~K = 0 (never right) or K = 0x7FFF with a = 1 (right only when missing).
 constexpr int CK_FB = 8;             // features per block of the key pre-pass
 struct CkFeat { uint32_t thr_off, n_thr, tab_off, nb; float lo, scale; };   // byte offsets inside the feature block's table area
 struct CompactDesc {

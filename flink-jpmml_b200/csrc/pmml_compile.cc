@@ -661,9 +661,12 @@ struct ForestBuilder {
           return;
         }
         const TNode& n = nodes[s]; uint32_t a = (n.on_missing == n.on_false && n.on_true != n.on_false) ? 1u : 0u;
-        uint32_t kk = n.thr >= 0 ? K16[n.thr] : 0xFFFFFFFFu, y = ~(kk - a), feat = (uint32_t)feat_of(n);
-        if ((uint32_t)(int32_t)(int16_t)(y & 0xFFFFu) != y || feat > 255) ok = false;   // must survive the 16-bit sign extension
-        nd[h] = a | (feat << 1) | ((y & 0xFFFFu) << 16);
+        // right iff (a ? key : key & 0x7FFF) > K; a missing value has key 0x8000.  No threshold: never right (a = 0, ~K := 0)
+        // or right only when missing (a = 1, K := 0x7FFF)
+        uint32_t feat = (uint32_t)feat_of(n), y;
+        if (n.thr >= 0) { uint32_t kk = K16[n.thr]; if (kk > 0x7FFEu) ok = false; y = ~kk; } else y = a ? ~0x7FFFu : 0u;
+        if (feat > 255) ok = false;
+        nd[h] = (feat << 1) | (a << 15) | ((y & 0xFFFFu) << 16);
         place(n.on_true, 2 * h); place(n.on_false, 2 * h + 1);
       };
       place(roots[t], 1);
