@@ -23,6 +23,7 @@ struct KeyTiles {
 };
 
 constexpr int RK_THREADS = 512;
+constexpr int RK_CTAS = 2;       // resident CTAs per SM the pre-pass is built for (3 spills and is slower)
 constexpr int RK_BATCH = 5;      // values a thread has in flight (E = 640: two batches per tile)
 
 // Rank keys of RK_BATCH prepared values of one feature, the chains interleaved by hand: bucket -> first candidate threshold
@@ -68,7 +69,7 @@ __device__ __forceinline__ void ck_rank_keys(uint32_t th_addr, uint32_t tab_addr
 // out), rows past the end of the batch redo the last row (the walk kernel never reports them).
 // Shared memory: tables | staging tile u16 [8][OS]
 template <bool SIMPLE>
-__global__ void __launch_bounds__(RK_THREADS, 2) forest_rank_keys_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, const KeyTiles kt) {
+__global__ void __launch_bounds__(RK_THREADS, RK_CTAS) forest_rank_keys_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, const KeyTiles kt) {
   extern __shared__ __align__(16) uint8_t rk_smem[];
   const ForestDesc& fd = m.forest; const CompactDesc& cd = fd.compact;
   const int F = m.F, E = kt.E, tid = threadIdx.x;

@@ -1206,7 +1206,7 @@ static cudaError_t launch_forest_compact(const DeviceModel& m, const BatchArgs& 
     kt.fail = m.prep_simple ? nullptr : fail;
     cudaError_t e;
     if (kt.fail) { e = cudaMemsetAsync(fail, 0, (size_t)kt.ntiles * E, s); if (e != cudaSuccess) return e; }
-    int gx = 2 * g_num_sms / cd.n_blocks; if (gx < 1) gx = 1; if (gx > kt.ntiles) gx = (int)kt.ntiles;   // one wave: two CTAs per SM
+    int gx = RK_CTAS * g_num_sms / cd.n_blocks; if (gx < 1) gx = 1; if (gx > kt.ntiles) gx = (int)kt.ntiles;   // one wave of resident CTAs
     if (m.prep_simple) {
       cudaFuncSetAttribute(forest_rank_keys_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rk_smem);
       forest_rank_keys_kernel<true><<<dim3(gx, cd.n_blocks), RK_THREADS, rk_smem, s>>>(m, a, kt);

@@ -167,7 +167,7 @@ def forest_arrays(T, depth, F, seed, n_quantiles=255):
 
 
 def gbt_pmml(T=500, depth=8, F=100, seed=SEED_BASE + 4, dtype="double", method="sum",
-             rescale_constant=0.5, rescale_factor=None, missing_strategy="defaultChild"):
+             rescale_constant=0.5, rescale_factor=None, missing_strategy="defaultChild", segment_weights=False):
     """MiningModel regression, Segmentation sum|average over T complete depth-`depth` TreeModels (config C4)."""
     feat, thr, dleft, rng = forest_arrays(T, depth, F, seed)
     leaf = rng.normal(0.0, 0.1, size=(T, 1 << depth))
@@ -181,8 +181,9 @@ def gbt_pmml(T=500, depth=8, F=100, seed=SEED_BASE + 4, dtype="double", method="
         b = f' rescaleFactor="{_r(rescale_factor)}"' if rescale_factor is not None else ""
         out.append(f'<Targets><Target field="y"{a}{b}/></Targets>')
     out.append(f'<Segmentation multipleModelMethod="{method}">')
+    weights = np.round(rng.uniform(0.5, 1.5, size=T), 3) if segment_weights else None   # weightedSum / weightedAverage
     for t in range(T):
-        out.append(f'<Segment id="{t + 1}"><True/>')
+        out.append(f'<Segment id="{t + 1}"' + (f' weight="{_r(weights[t])}"' if segment_weights else "") + '><True/>')
         out.append(f'<TreeModel functionName="regression" missingValueStrategy="{missing_strategy}" '
                    'noTrueChildStrategy="returnNullPrediction" splitCharacteristic="binarySplit">')
         out += _mining_schema(names)
@@ -192,7 +193,7 @@ def gbt_pmml(T=500, depth=8, F=100, seed=SEED_BASE + 4, dtype="double", method="
     out.append('</Segmentation></MiningModel></PMML>')
     arrays = {"feat": feat, "thr": thr, "dleft": dleft, "leaf": leaf, "depth": depth, "method": method,
               "rescale_constant": rescale_constant or 0.0, "rescale_factor": 1.0 if rescale_factor is None else rescale_factor,
-              "dtype": dtype}
+              "dtype": dtype, "weights": weights}
     return "\n".join(out).encode(), arrays
 
 

@@ -72,6 +72,17 @@ def test_replace_nan_and_dense_rows(engine, oracle, gen, monkeypatch):
     same(compact, om.predict(np.nan_to_num(X), None, nthreads=8))
 
 
+@pytest.mark.parametrize("method", ["weightedAverage", "weightedSum"])
+def test_segment_weights(engine, oracle, gen, monkeypatch, method):
+    pm, arr = gen.gbt_pmml(T=29, depth=7, F=17, seed=14, method=method, segment_weights=True)
+    m, om = engine.compile(pm), oracle.OracleModel(pm)
+    assert "compact=1" in m.describe
+    X, pres, pb = gen.events(6000, 17, 15, 0.1)
+    classic, compact = score_both(engine, m, X, pb, monkeypatch)
+    same(compact, om.predict(X, pb, nthreads=8))
+    same(compact, classic)
+
+
 def test_rf_majority_vote(engine, oracle, gen, monkeypatch):
     pm, arr = gen.rf_pmml(T=50, depth=6, F=20, n_labels=4, seed=21)
     m, om = engine.compile(pm), oracle.OracleModel(pm)
@@ -129,3 +140,24 @@ def test_device_entry_point_takes_the_path_for_large_batches(engine, gen):
         st.synchronize()
     assert engine.launch_count - launches == 4
     assert np.array_equal(dS.cpu().numpy(), gen.gbt_numpy(arr, X, pres)) and int(dT.sum().item()) == 0
+
+
+def test_hand_derived_cases_with_the_path_forced(engine, gen, monkeypatch):
+    """Every hand-derived semantic case (tests/semantic_cases.py) again with FJP_FOREST_COMPACT=2: ensembles that qualify
+    (weighted sums / averages, votes, compound and set predicates, padded trees ...) go through the throughput path,
+    everything else is unaffected; statuses and scores must still be the expected ones."""
+    import semantic_cases
+    monkeypatch.setenv("FJP_FOREST_COMPACT", "2")
+    taken = 0
+    for name, pm, X, P, rep, expected in semantic_cases.cases():
+        m = engine.compile(pm)
+        before = engine.launch_count
+        r = engine.score(m, X, gen.pack_present(P), rep)
+        taken += engine.launch_count - before >= 2 and "compact=1" in m.describe
+        for i, (st, score, aux) in enumerate(expected):
+            assert r["status"][i] == st, (name, i, r["status"])
+            if st == 0 and name in semantic_cases.TOLERANT:
+                assert abs(r["score"][i] - score) <= 1e-9 * abs(score), (name, i)
+            elif st == 0:
+                assert r["score"][i] == score, (name, i, r["score"][i], score)
+    assert taken >= 2, taken
