@@ -63,12 +63,40 @@ __device__ __forceinline__ void ck_rank_keys(uint32_t th_addr, uint32_t tab_addr
   }
 }
 
+// The same for thresholds that are not floats: values are compared as doubles (64-bit images, Double.compareTo order);
+// the bucket still comes from the value rounded to float, which is monotone.
+__device__ __forceinline__ void ck_rank_keys_wide(uint32_t th_addr, uint32_t tab_addr, const CkFeat& cf, const double (&val)[RK_BATCH], uint32_t (&key)[RK_BATCH]) {
+  uint64_t img[RK_BATCH], t[RK_BATCH]; uint32_t r[RK_BATCH];
+  const float top = (float)(cf.nb - 1u);
+#pragma unroll
+  for (int k = 0; k < RK_BATCH; k++) {
+    const uint64_t u = (uint64_t)__double_as_longlong(val[k]);
+    img[k] = u ^ ((uint64_t)((long long)u >> 63) | 0x8000000000000000ull);
+    const float xf = (float)val[k];
+    const uint32_t b = __float2uint_rz(fminf(fmaxf((xf - cf.lo) * cf.scale, 0.0f), top));
+    uint32_t first; asm volatile("ld.shared.u16 %0, [%1];" : "=r"(first) : "r"(tab_addr + 2u * b));
+    r[k] = th_addr + 8u * (val[k] != val[k] ? cf.n_thr : first);
+  }
+#pragma unroll
+  for (int k = 0; k < RK_BATCH; k++) asm volatile("ld.shared.u64 %0, [%1];" : "=l"(t[k]) : "r"(r[k]));
+#pragma unroll
+  for (int s = 0; s < 3; s++) {
+#pragma unroll
+    for (int k = 0; k < RK_BATCH; k++) { r[k] += t[k] < img[k] ? 8u : 0u; asm volatile("ld.shared.u64 %0, [%1];" : "=l"(t[k]) : "r"(r[k])); }
+  }
+#pragma unroll
+  for (int k = 0; k < RK_BATCH; k++) {
+    while (t[k] < img[k]) { r[k] += 8u; asm volatile("ld.shared.u64 %0, [%1];" : "=l"(t[k]) : "r"(r[k])); }
+    key[k] = ((r[k] - th_addr) >> 2) + (t[k] == img[k] ? 2u : 1u);
+  }
+}
+
 // grid = (x, feature blocks); a CTA keeps the tables of its CK_FB features in shared memory and runs over the tiles
 // x, x + gridDim.x, ...  Element i of a tile is (event, feature) = (i / 8, i % 8): a warp reads four 64-byte runs of X.
 // No lane is ever predicated off: the idle lanes of a short last block redo feature f0 (their staging rows are not written
 // out), rows past the end of the batch redo the last row (the walk kernel never reports them).
 // Shared memory: tables | staging tile u16 [8][OS]
-template <bool SIMPLE>
+template <bool SIMPLE, bool WIDE>
 __global__ void __launch_bounds__(RK_THREADS, RK_CTAS) forest_rank_keys_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, const KeyTiles kt) {
   extern __shared__ __align__(16) uint8_t rk_smem[];
   const ForestDesc& fd = m.forest; const CompactDesc& cd = fd.compact;
@@ -83,7 +111,7 @@ __global__ void __launch_bounds__(RK_THREADS, RK_CTAS) forest_rank_keys_kernel(c
     for (uint32_t i = tid; i < tbytes / 16; i += RK_THREADS) dst[i] = __ldg(src + i);
   }
   const int j = tid & (CK_FB - 1), f = j < nf ? f0 + j : f0;   // this thread's feature never changes (RK_THREADS is a multiple of CK_FB)
-  const CkFeat cf = cd.feat[f]; const int mode = fd.feat_mode[f];
+  const CkFeat cf = cd.feat[f]; const int mode = fd.feat_mode[f]; const bool float_field = m.prep[f].dtype == DT_FLOAT;
   const uint32_t th_addr = smem_u32(rk_smem) + cf.thr_off, tab_addr = smem_u32(rk_smem) + cf.tab_off;
   const uint32_t pbit = 1u << (f & 31); const int pword = f0 >> 5;   // a block's 8 features share one present word
   uint16_t* const out_row = out + j * OS;
@@ -105,10 +133,10 @@ __global__ void __launch_bounds__(RK_THREADS, RK_CTAS) forest_rank_keys_kernel(c
       for (int k = 0; k < RK_BATCH; k++) {
         bool present = (pw[k] & pbit) != 0;
         if (!present && a.replace) { double rep = a.replace[row0 + e[k]]; if (rep == rep) { val[k] = rep; present = true; } }
-        if (SIMPLE) st[k] = present ? 0 : 1;
+        if (SIMPLE) { st[k] = present ? 0 : 1; if (WIDE && float_field) val[k] = (double)(float)val[k]; }   // JPMML casts to the field's dataType
         else { double raw = val[k]; val[k] = 0.0; st[k] = prep_value(m.prep[f], m.prep_pool, present, raw, val[k]); }
       }
-      ck_rank_keys(th_addr, tab_addr, cf, mode, val, key);
+      if (WIDE) ck_rank_keys_wide(th_addr, tab_addr, cf, val, key); else ck_rank_keys(th_addr, tab_addr, cf, mode, val, key);
 #pragma unroll
       for (int k = 0; k < RK_BATCH; k++) {
         const int ee = min(i0 + k * RK_THREADS, total - 1) >> 3;      // the unclamped event slot of the tile

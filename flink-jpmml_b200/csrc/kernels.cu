@@ -1207,13 +1207,11 @@ static cudaError_t launch_forest_compact(const DeviceModel& m, const BatchArgs& 
     cudaError_t e;
     if (kt.fail) { e = cudaMemsetAsync(fail, 0, (size_t)kt.ntiles * E, s); if (e != cudaSuccess) return e; }
     int gx = RK_CTAS * g_num_sms / cd.n_blocks; if (gx < 1) gx = 1; if (gx > kt.ntiles) gx = (int)kt.ntiles;   // one wave of resident CTAs
-    if (m.prep_simple) {
-      cudaFuncSetAttribute(forest_rank_keys_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rk_smem);
-      forest_rank_keys_kernel<true><<<dim3(gx, cd.n_blocks), RK_THREADS, rk_smem, s>>>(m, a, kt);
-    } else {
-      cudaFuncSetAttribute(forest_rank_keys_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rk_smem);
-      forest_rank_keys_kernel<false><<<dim3(gx, cd.n_blocks), RK_THREADS, rk_smem, s>>>(m, a, kt);
-    }
+#define FJP_RK(SS, WW) do { cudaFuncSetAttribute(forest_rank_keys_kernel<SS, WW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rk_smem); \
+                            forest_rank_keys_kernel<SS, WW><<<dim3(gx, cd.n_blocks), RK_THREADS, rk_smem, s>>>(m, a, kt); } while (0)
+    if (m.prep_simple) { if (cd.wide) FJP_RK(true, true); else FJP_RK(true, false); }
+    else { if (cd.wide) FJP_RK(false, true); else FJP_RK(false, false); }
+#undef FJP_RK
     e = cudaGetLastError(); if (e != cudaSuccess) return e;
     if (launches) (*launches)++;
     const int grid = (int)(kt.ntiles < g_num_sms ? kt.ntiles : g_num_sms);

@@ -81,10 +81,10 @@ static constexpr int32_t LEAF_NULL = INT32_MIN;  // successor meaning "null pred
 constexpr int CK_FB = 8;             // features per block of the key pre-pass
 struct CkFeat { uint32_t thr_off, n_thr, tab_off, nb; float lo, scale; };   // byte offsets inside the feature block's table area
 struct CompactDesc {
-  int enabled, tree_bytes, n_blocks, block_smem;   // block_smem: largest table area of one feature block
+  int enabled, wide, tree_bytes, n_blocks, block_smem;   // wide: 64-bit threshold images (thresholds that are not floats); block_smem: largest table area of one feature block
   const uint32_t* blobs;       // n_trees x tree_bytes
   const CkFeat* feat;          // F
-  const uint8_t* tables;       // per feature block: sorted distinct threshold images (u32, 0xFFFFFFFF-terminated) and bucket tables (u16 x nb)
+  const uint8_t* tables;       // per feature block: sorted distinct threshold images (u32, or u64 when wide; all-ones-terminated) and bucket tables (u16 x nb)
   const uint32_t* block_off;   // n_blocks + 1 byte offsets into tables (multiples of 16)
 };
 FJP_HD inline int compact_tree_bytes(int depth) { return (int)(((12u << depth) + 8u + 15u) & ~15u); }

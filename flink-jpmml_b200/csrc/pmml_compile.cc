@@ -9,6 +9,7 @@
 // This file is host-only C++; it shares no code with oracle/.
 #include <algorithm>
 #include <charconv>
+#include <cfloat>
 #include <cmath>
 #include <cstring>
 #include <functional>
@@ -603,42 +604,53 @@ struct ForestBuilder {
   }
 
   // Compact form for the throughput path (model.h CompactDesc): rank keys per feature + bucket tables for the key pre-pass,
-  // 4-byte nodes.  Only when every threshold is a float (so that one float image per value decides every test).
-  template <class FeatOf> void emit_compact(int depth, const std::vector<uint8_t>& used, FeatOf feat_of) {
+  // 4-byte nodes.  `wide` = false: every threshold is a float and one float image per value decides every test (ENC_FLOAT's
+  // argument); `wide` = true: thresholds are compared as doubles, the tables hold 64-bit images (ENC_RANK's order).
+  static uint64_t ordkey64(double d) { uint64_t u; memcpy(&u, &d, 8); return (u & 0x8000000000000000ull) ? ~u : (u | 0x8000000000000000ull); }
+  template <class FeatOf> void emit_compact(int depth, const std::vector<uint8_t>& used, FeatOf feat_of, bool wide) {
     ForestDesc& fd = b.cm.dev.forest; CompactDesc& cd = fd.compact; const int F = b.cm.dev.F;
     if (F > 256 || depth < 1) return;
-    std::vector<std::vector<uint32_t>> img(F);
-    for (size_t i = 0; i < thr.size(); i++) if (used[i] && thr[i].slot >= 0) img[thr[i].slot].push_back(ordkey((float)thr[i].value));
+    // per feature: sorted distinct threshold images and the float each one falls on (bucket arithmetic is float)
+    auto image = [&](const Thr& t) -> uint64_t { return wide ? ordkey64(t.value) : (uint64_t)ordkey((float)t.value); };
+    std::vector<std::vector<std::pair<uint64_t, float>>> img(F);
+    for (size_t i = 0; i < thr.size(); i++) if (used[i] && thr[i].slot >= 0) {
+      if (std::isnan(thr[i].value)) return;
+      img[thr[i].slot].push_back({image(thr[i]), (float)thr[i].value});
+    }
     for (auto& v : img) { std::sort(v.begin(), v.end()); v.erase(std::unique(v.begin(), v.end()), v.end()); if (v.size() > 16382) return; }
-    auto unkey = [](uint32_t k) { uint32_t u = (k & 0x80000000u) ? (k & 0x7FFFFFFFu) : ~k; float f; memcpy(&f, &u, 4); return f; };
     // rank key of every threshold
     std::vector<uint32_t> K16(thr.size(), 0);
     for (size_t i = 0; i < thr.size(); i++) {
       if (!used[i] || thr[i].slot < 0) continue;
       const auto& v = img[thr[i].slot];
-      uint32_t j = (uint32_t)(std::lower_bound(v.begin(), v.end(), ordkey((float)thr[i].value)) - v.begin());
+      uint32_t j = (uint32_t)(std::lower_bound(v.begin(), v.end(), std::make_pair(image(thr[i]), -INFINITY)) - v.begin());
       K16[i] = thr[i].strict ? 2u * j + 1u : 2u * j + 2u;
     }
     // tables, one area per block of CK_FB features
-    const int nblocks = (F + CK_FB - 1) / CK_FB;
+    const int nblocks = (F + CK_FB - 1) / CK_FB; const size_t esz = wide ? 8 : 4;
     std::vector<CkFeat> feats(F); std::vector<uint8_t> tables; std::vector<uint32_t> block_off(nblocks + 1, 0); size_t block_smem = 0;
     for (int fb = 0; fb < nblocks; fb++) {
       const size_t start = tables.size(); block_off[fb] = (uint32_t)start;
       for (int f = fb * CK_FB; f < std::min(F, (fb + 1) * CK_FB); f++) {
         const auto& v = img[f]; CkFeat& cf = feats[f]; const uint32_t n = (uint32_t)v.size();
         uint32_t nb = 16; while (nb < 2 * n && nb < 4096) nb *= 2;
-        float lo = n ? unkey(v.front()) : 0.0f, hi = n ? unkey(v.back()) : 0.0f;
+        float lo = n ? v.front().second : 0.0f, hi = n ? v.back().second : 0.0f;
+        if (!std::isfinite(lo)) lo = -FLT_MAX; if (!std::isfinite(hi)) hi = FLT_MAX;
         float scale = (n && hi > lo) ? (float)nb / (hi - lo) : 0.0f;
         if (!std::isfinite(scale)) scale = 0.0f;
         cf.n_thr = n; cf.nb = nb; cf.lo = lo; cf.scale = scale;
+        tables.resize((tables.size() + 7) & ~size_t(7));
         cf.thr_off = (uint32_t)(tables.size() - start);
-        tables.resize(tables.size() + 4 * (size_t)(n + 4), 0xFF);   // four 0xFFFFFFFF sentinels end the array: the scan needs no bounds
-        if (n) memcpy(tables.data() + start + cf.thr_off, v.data(), 4 * (size_t)n);
+        tables.resize(tables.size() + esz * (size_t)(n + 4), 0xFF);   // four all-ones sentinels end the array: the scan needs no bounds
+        for (uint32_t j = 0; j < n; j++) {
+          if (wide) memcpy(tables.data() + start + cf.thr_off + 8 * (size_t)j, &v[j].first, 8);
+          else { uint32_t k = (uint32_t)v[j].first; memcpy(tables.data() + start + cf.thr_off + 4 * (size_t)j, &k, 4); }
+        }
         cf.tab_off = (uint32_t)(tables.size() - start);
         std::vector<uint16_t> tab(nb + 1, 0);   // tab[b] = thresholds whose bucket is below b
-        for (uint32_t j = 0; j < n; j++) tab[ck_bucket(unkey(v[j]), lo, scale, nb) + 1]++;
+        for (uint32_t j = 0; j < n; j++) tab[ck_bucket(v[j].second, lo, scale, nb) + 1]++;
         for (uint32_t q = 1; q <= nb; q++) tab[q] = (uint16_t)(tab[q] + tab[q - 1]);
-        tables.resize(tables.size() + 2 * (size_t)nb); memcpy(tables.data() + start + cf.tab_off, tab.data(), 2 * (size_t)nb);   // nb is even: stays 4-byte aligned
+        tables.resize(tables.size() + 2 * (size_t)nb); memcpy(tables.data() + start + cf.tab_off, tab.data(), 2 * (size_t)nb);
       }
       tables.resize((tables.size() + 15) & ~size_t(15));
       block_smem = std::max(block_smem, tables.size() - start);
@@ -672,7 +684,7 @@ struct ForestBuilder {
       place(roots[t], 1);
     }
     if (!ok) return;
-    cd.enabled = 1; cd.tree_bytes = (int)TB; cd.n_blocks = nblocks; cd.block_smem = (int)block_smem;
+    cd.enabled = 1; cd.wide = wide ? 1 : 0; cd.tree_bytes = (int)TB; cd.n_blocks = nblocks; cd.block_smem = (int)block_smem;
     b.put(&cd.blobs, blobs); b.put(&cd.feat, feats); b.put(&cd.tables, tables); b.put(&cd.block_off, block_off);
   }
 
@@ -771,7 +783,7 @@ struct ForestBuilder {
         place(roots[t], 1);
       }
       b.put(&fd.blobs, blobs);
-      if (float_ok && method != FM_CHAIN && method != FM_SINGLE) emit_compact(depth, used, feat_of);
+      if (method != FM_CHAIN && method != FM_SINGLE) emit_compact(depth, used, feat_of, !float_ok);
     } else {
       fd.format = FOREST_GENERAL; fd.depth = 0;
       std::vector<uint64_t> blobs; b.put(&fd.blobs, blobs);

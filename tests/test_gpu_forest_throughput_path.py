@@ -161,3 +161,23 @@ def test_hand_derived_cases_with_the_path_forced(engine, gen, monkeypatch):
             elif st == 0:
                 assert r["score"][i] == score, (name, i, r["score"][i], score)
     assert taken >= 2, taken
+
+
+@pytest.mark.parametrize("dtype", ["double", "float"])
+def test_thresholds_that_are_not_floats(engine, oracle, gen, monkeypatch, dtype):
+    """scikit-learn / LightGBM style midpoints: thresholds are compared as doubles; the pre-pass tables then hold 64-bit
+    images (compact=2).  float-typed fields parse their thresholds as floats and stay on the 32-bit tables."""
+    monkeypatch.setattr(gen, "FLOAT_THRESHOLDS", False)
+    pm, arr = gen.gbt_pmml(T=64, depth=6, F=24, seed=71, dtype=dtype)
+    m, om = engine.compile(pm), oracle.OracleModel(pm)
+    assert ("compact=2" if dtype == "double" else "compact=1") in m.describe, m.describe
+    X, pres, pb = gen.events(30000, 24, 72, 0.1)
+    X[::7, int(arr["feat"][0, 0])] = arr["thr"][0, 0]                      # exactly on a threshold
+    X[::11, int(arr["feat"][1, 0])] = np.nextafter(arr["thr"][1, 0], np.inf)
+    X[::17, int(arr["feat"][2, 0])] = np.nextafter(arr["thr"][2, 0], -np.inf)
+    X[::13, 2] = np.nan
+    X[::19, 3] = -np.inf
+    X[::23, 4] = 1e300
+    classic, compact = score_both(engine, m, X, pb, monkeypatch)
+    same(compact, om.predict(X, pb, nthreads=8))
+    same(compact, classic)
