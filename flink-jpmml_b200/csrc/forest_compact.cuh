@@ -157,7 +157,7 @@ __global__ void __launch_bounds__(RK_THREADS, RK_CTAS) forest_rank_keys_kernel(c
   }
 }
 
-// MODE: 0 sum / average, 1 weighted sum / average, 2 majority vote.
+// MODE: 0 sum / average, 1 weighted sum / average, 2 majority vote, 3 modelChain (per-channel sums -> RegressionTables).
 template <int D, int TI, int MODE, int MAXT>
 __global__ void __launch_bounds__(MAXT, 1)
 forest_compact_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, const ForestLaunch fl, const KeyTiles kt) {
@@ -201,6 +201,8 @@ forest_compact_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, 
     const uint32_t kbase = smem_u32(smem) + 4u * tid;    // byte address of this event's column of key-pair words
     const uint32_t Eb = (uint32_t)E;                     // (node & 0x1FC) * E = (feat / 2) * 4E bytes; node & 2 picks the half
     double sum = 0.0, wsum = 0.0; uint32_t seen = 0;
+    uint32_t cur_ch = 0;                                  // modelChain: channel of the running sum (node[0] of a tree = its channel)
+    double* chv = reinterpret_cast<double*>(votes);      // modelChain: finished channel values [channel][event]
     for (int g = 0; g < NG; g++) {
       uint32_t slot = q_wait & 1u;
       mbar_wait(&bars[slot], (q_wait >> 1) & 1u); q_wait++;
@@ -233,7 +235,11 @@ forest_compact_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, 
               double lv;
               asm volatile("ld.shared.f64 %0, [%1];" : "=d"(lv) : "r"(bl[k] + off_leaf + idx[k] * 8u));
               if (MODE == 1) { double w; asm volatile("ld.shared.f64 %0, [%1];" : "=d"(w) : "r"(bl[k] + off_w)); sum += w * lv; wsum += w; }
-              else sum += lv;
+              else if (MODE == 3) {
+                uint32_t ch; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(ch) : "r"(bl[k]));
+                if (ch != cur_ch) { chv[cur_ch * E + tid] = channel_value(fd.channels[cur_ch], sum); sum = 0.0; cur_ch = ch; }   // trees arrive channel by channel
+                sum += lv;
+              } else sum += lv;
             } else {
               uint32_t lab;
               asm volatile("ld.shared.u32 %0, [%1];" : "=r"(lab) : "r"(bl[k] + off_leaf + idx[k] * 8u));
@@ -249,7 +255,10 @@ forest_compact_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, 
     }
     if (row < a.n) {
       if (failed) write_out(a, row, 0, ST_PREP, -1);
-      else if (MODE != 2) {
+      else if (MODE == 3) {
+        chv[cur_ch * E + tid] = channel_value(fd.channels[cur_ch], sum);
+        chain_finish(m, a, row, [&](int c) { return chv[c * E + tid]; });
+      } else if (MODE != 2) {
         double v = sum;
         if (fd.method == FM_AVERAGE) v = sum / (double)T; else if (fd.method == FM_WAVERAGE) v = sum / wsum;
         write_out(a, row, apply_target(m.tx, v), m.target_status, -1);

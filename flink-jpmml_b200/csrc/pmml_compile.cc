@@ -664,6 +664,7 @@ struct ForestBuilder {
       uint8_t* bl = reinterpret_cast<uint8_t*>(blobs.data()) + t * TB;
       uint32_t* nd = reinterpret_cast<uint32_t*>(bl);
       memcpy(bl + 12 * first_leaf, &weights[t], 8);
+      if (!chain_channels.empty()) nd[0] = (uint32_t)chain_channels[t];   // modelChain: the unused heap slot 0 carries the channel
       std::function<void(int32_t, size_t)> place = [&](int32_t s, size_t h) {
         if (s < 0) {
           const TLeaf& lf = leaves[~s];
@@ -783,7 +784,7 @@ struct ForestBuilder {
         place(roots[t], 1);
       }
       b.put(&fd.blobs, blobs);
-      if (method != FM_CHAIN && method != FM_SINGLE) emit_compact(depth, used, feat_of, !float_ok);
+      if (method != FM_SINGLE) emit_compact(depth, used, feat_of, !float_ok);
     } else {
       fd.format = FOREST_GENERAL; fd.depth = 0;
       std::vector<uint64_t> blobs; b.put(&fd.blobs, blobs);

@@ -181,3 +181,24 @@ def test_thresholds_that_are_not_floats(engine, oracle, gen, monkeypatch, dtype)
     classic, compact = score_both(engine, m, X, pb, monkeypatch)
     same(compact, om.predict(X, pb, nthreads=8))
     same(compact, classic)
+
+
+@pytest.mark.parametrize("n_classes", [2, 3])
+def test_boosted_classifier_model_chain(engine, oracle, gen, monkeypatch, n_classes):
+    """modelChain (trees per class -> logit / softmax RegressionModel): channel sums close in the walk kernel, the final
+    tables run in its epilogue; labels bit-exact, probabilities identical to the one-kernel walk."""
+    pm, arr = gen.gbt_classifier_pmml(T=40, depth=6, F=30, n_classes=n_classes, seed=51)
+    m, om = engine.compile(pm), oracle.OracleModel(pm)
+    assert "method=9" in m.describe and "compact=1" in m.describe
+    X, pres, pb = gen.events(20000, 30, 52, 0.1)
+    monkeypatch.setenv("FJP_FOREST_COMPACT", "0")
+    classic = engine.score(m, X, pb, n_probs=n_classes)
+    monkeypatch.setenv("FJP_FOREST_COMPACT", "2")
+    before = engine.launch_count
+    compact = engine.score(m, X, pb, n_probs=n_classes)
+    assert engine.launch_count - before >= 2
+    o = om.predict(X, pb, n_probs=n_classes, nthreads=8)
+    same(compact, o)
+    same(compact, classic)
+    assert np.array_equal(compact["probs"].view(np.int64), classic["probs"].view(np.int64))
+    np.testing.assert_allclose(compact["probs"], o["probs"], rtol=1e-6)

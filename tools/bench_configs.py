@@ -54,6 +54,9 @@ configs.append(("C2 kmeans k=64 F=128 5% missing", g.config_c2()[0], 128, 1 << 2
 configs.append(("C3 multinomial logistic 1000x20", g.regression_pmml()[0], 1000, 1 << 20, 0.0, {"dp_instr": 40000, "hbm": 8008}))
 configs.append(("C4 GBT 500x8 F=100 10% missing", g.gbt_pmml()[0], 100, 1 << 22, 0.10, {"gather": 32000, "hbm": 824}))
 configs.append(("C4 GBT float fields (XGBoost style)", g.gbt_pmml(dtype="float")[0], 100, 1 << 22, 0.10, {"gather": 32000, "hbm": 824}))
+g.FLOAT_THRESHOLDS = False
+configs.append(("C4 GBT double thresholds (scikit-learn / LightGBM style)", g.gbt_pmml()[0], 100, 1 << 22, 0.10, {"gather": 32000, "hbm": 824}))
+g.FLOAT_THRESHOLDS = True
 configs.append(("C5 RF 200x8 F=64 majorityVote", g.rf_pmml()[0], 64, 1 << 22, 0.0, {"gather": 12800, "hbm": 528}))
 configs.append(("C5 MLP 64-256-256-8", g.nn_pmml()[0], 64, 1 << 21, 0.0, {"dp_instr": 167936, "hbm": 520}))
 for name, pm, F, n, pmiss, work in configs:
