@@ -274,7 +274,9 @@ def main():
                 "kernel": ("forest_rank_keys_kernel<true> + forest_compact_kernel<8,8,0,640> (throughput path: %d launches per step, timed together)" % (launches // max(1, args.steps)))
                           if launches > args.steps else "forest_complete_kernel<8,8,0,false>",
                 "algorithmic_bytes_per_event": ALGO_HBM_BYTES,
-                "note": "the walk is bound by shared-memory gathers / issue, not HBM: see gather",
+                "note": "the walk is bound by the shared-memory pipe and the issue slots, not HBM: see gather and smem_pipe",
+                "smem_pipe": {"busy_frac": micro.get("forest_walk_smem_pipe_busy"), "issue_slots_busy_frac": micro.get("forest_walk_issue_slots_busy"),
+                              "source": micro.get("forest_walk_note")},
                 "gather": {"algorithmic_bytes_per_event": ALGO_GATHER_BYTES, "achieved_gbs": gather,
                            "l2_gather_peak_gbs": micro.get("l2_gather_8B_2MB_GBs"), "smem_gather_peak_gbs": micro.get("smem_gather_8B_random_GBs"),
                            "frac_of_l2_gather": (gather / micro["l2_gather_8B_2MB_GBs"]) if micro.get("l2_gather_8B_2MB_GBs") else None,
