@@ -565,7 +565,7 @@ __global__ void __launch_bounds__(CL_E* CL_G) cluster_kernel(const __grid_consta
 // 1 + 4 shared loads feed 24 double-precision instructions (sub, mul, add x 8), so the FP64 pipe is the limiter.
 // Sums run over the fields in ClusteringField order in double, unfused: bit-identical to the per-event interpreter.
 constexpr int CK_TC = 8, CK_WARPS = 16;
-struct ClusterPlan { int groups, event_blocks, events, chunk, kp; uint32_t off_x, off_st, off_best, smem_bytes; };
+struct ClusterPlan { int groups, event_blocks, events, chunk, kp, pipelined; uint32_t off_x, off_st, off_best, smem_bytes; };
 template <bool HASMISS>
 __global__ void __launch_bounds__(CK_WARPS * 32, 1) cluster_fast_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, const ClusterPlan pl) {
   extern __shared__ __align__(128) uint8_t smem[];
@@ -582,6 +582,60 @@ __global__ void __launch_bounds__(CK_WARPS * 32, 1) cluster_fast_kernel(const __
   const double INF = __longlong_as_double(0x7FF0000000000000LL);
   for (int i = tid; i < nf * KP; i += blockDim.x) { int f = i / KP, c = i - f * KP; cent[i] = c < K ? cd.centers[(size_t)c * nf + f] : 0.0; }
   const long ntiles = (a.n + E - 1) / E;
+  if (!HASMISS && pl.pipelined) {
+    // Dense rows, all fields in one chunk, one cluster group per warp: the next tile's rows are copied into the second
+    // buffer (cp.async, 8 B each, straight into the transposed position) while this tile's distances are computed.
+    auto fill_async = [&](long tile, int buf) {
+      const long row0 = tile * E; double* xb = xs + (size_t)buf * pl.chunk * EP;
+      const int sh = 31 - __clz(nf); const bool pow2 = (nf & (nf - 1)) == 0;
+      for (int i = tid; i < E * nf; i += blockDim.x) {
+        int r = pow2 ? (i >> sh) : (i / nf), f = i - r * nf; long rr = row0 + r;
+        if (rr < a.n) cp_async8(xb + f * EP + r, a.X + rr * (long)m.F + cd.slot[f]); else xb[f * EP + r] = 0.0;
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    int buf = 0;
+    if ((long)blockIdx.x < ntiles) fill_async(blockIdx.x, 0);
+    for (long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, buf ^= 1) {
+      const long row = tile * E + e;
+      if (tile + gridDim.x < ntiles) { fill_async(tile + gridDim.x, buf ^ 1); asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+      else asm volatile("cp.async.wait_group 0;" ::: "memory");
+      __syncthreads();   // this tile's rows (and, the first time, the centres) are in place
+      double acc[CK_TC];
+#pragma unroll
+      for (int k = 0; k < CK_TC; k++) acc[k] = 0.0;
+      const double* xb = xs + (size_t)buf * pl.chunk * EP; const double* cp = cent + cg0 * CK_TC;
+      for (int f = 0; f < nf; f++, cp += KP) {
+        const double x = xb[f * EP + e];
+        const double2* c2 = reinterpret_cast<const double2*>(cp);
+#pragma unroll
+        for (int k = 0; k < CK_TC / 2; k++) {
+          double2 z = c2[k];
+          double d0 = fabs(x - z.x), d1 = fabs(x - z.y);
+          acc[2 * k] += d0 * d0; acc[2 * k + 1] += d1 * d1;
+        }
+      }
+      int bc = -1; double bd = 0;
+#pragma unroll
+      for (int k = 0; k < CK_TC; k++) {
+        int c = cg0 * CK_TC + k;
+        if (c < K) { double d = cd.measure == CM_EUCLIDEAN ? sqrt(acc[k]) : acc[k]; if (bc < 0 || java_cmp(d, bd) < 0) { bc = c; bd = d; } }
+      }
+      bestd[cg0 * E + e] = bc < 0 ? INF : bd; bestc[cg0 * E + e] = bc;
+      __syncthreads();
+      if (cg0 == 0 && row < a.n) {
+        for (int g = 1; g < warps_per_eb; g++) {
+          int c2 = bestc[g * E + e]; if (c2 < 0) continue; double d2 = bestd[g * E + e];
+          int cmp = bc < 0 ? -1 : java_cmp(d2, bd);
+          if (cmp < 0 || (cmp == 0 && c2 < bc)) { bc = c2; bd = d2; }
+        }
+        write_label(m, a, row, bc, bc + 1);
+        if (a.probs) a.probs[row * (long)a.prob_stride] = bd;
+      }
+      __syncthreads();   // bestd / bestc and this buffer are free for the next rounds
+    }
+    return;
+  }
   for (long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const long row0 = tile * E, row = row0 + e;
     int bc = -1; double bd = 0; bool fail = false;
@@ -1282,7 +1336,11 @@ cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t 
         if (cent + 16384 < (size_t)g_smem_optin) {
           int chunk = (int)(room / ((size_t)(pl.events + 1) * 8 + pl.events + 4)); if (chunk > nf) chunk = nf; if (chunk > 128) chunk = 128;
           if (chunk >= 1) {
-            pl.chunk = chunk; size_t off = cent; pl.off_x = (uint32_t)off; off += (size_t)chunk * (pl.events + 1) * 8;
+            const bool dense = a.present == nullptr && a.replace == nullptr && m.prep_identity;
+            // dense rows whose fields fit one chunk twice over, one cluster group per warp: double-buffered tiles
+            pl.pipelined = dense && chunk >= nf && pl.groups * pl.event_blocks == CK_WARPS && (size_t)2 * nf * (pl.events + 1) * 8 + (size_t)nf * (pl.events + 4) <= room;
+            if (pl.pipelined) chunk = nf;
+            pl.chunk = chunk; size_t off = cent; pl.off_x = (uint32_t)off; off += (size_t)(pl.pipelined ? 2 : 1) * chunk * (pl.events + 1) * 8;
             pl.off_st = (uint32_t)off; off += (size_t)chunk * (pl.events + 4); off = (off + 15) & ~size_t(15);
             pl.off_best = (uint32_t)off; off += (size_t)(CK_WARPS / pl.event_blocks) * pl.events * 12;
             pl.smem_bytes = (uint32_t)((off + 127) & ~size_t(127));
