@@ -761,6 +761,14 @@ __global__ void __launch_bounds__(256, 3) regression_tile_kernel(const __grid_co
       double* wb = wt + (size_t)buf * pl.chunk * KP; double* xb = xs + (size_t)buf * pl.chunk * EP; uint8_t* sb = sts + (size_t)buf * pl.chunk * (E + 4);
       for (int i = tid; i < nfc * KP; i += blockDim.x) cp_async8(wb + i, rd.dense_wt + (size_t)f0 * KP + i);
       const int sh = 31 - __clz(nfc); const bool pow2 = (nfc & (nfc - 1)) == 0;
+      if (!HASMISS && pow2 && nfc <= (int)blockDim.x && (blockDim.x & (nfc - 1)) == 0) {
+        // plain doubles, power-of-two chunk: a thread keeps its field and walks down the rows with pointer increments
+        const int f = tid & (nfc - 1), rstep = blockDim.x >> sh, live = (int)min((long)E, a.n - row0);
+        int r = tid >> sh;
+        const double* src = a.X + (row0 + r) * (long)F + f0 + f; double* dst = xb + f * EP + r; const long sstep = (long)rstep * F;
+        for (; r < live; r += rstep, src += sstep, dst += rstep) cp_async8(dst, src);
+        for (; r < E; r += rstep, dst += rstep) *dst = 0.0;
+      } else
       for (int i = tid; i < E * nfc; i += blockDim.x) {
         int r = pow2 ? (i >> sh) : (i / nfc), f = i - r * nfc; long rr = row0 + r;
         if (HASMISS) { double v = 0; int st = 0; if (rr < a.n) st = load_field(m, a, rr, f0 + f, v); sb[f * (E + 4) + r] = (uint8_t)st; xb[f * EP + r] = v; }
@@ -1378,7 +1386,7 @@ cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t 
           size_t off = ((size_t)2 * chunk * pl.kp * 8 + 127) & ~size_t(127); pl.off_x = (uint32_t)off; off += (size_t)2 * chunk * EP * 8;
           pl.off_st = (uint32_t)off; off += (size_t)2 * chunk * (pl.events + 4); off = (off + 15) & ~size_t(15);
           pl.off_y = (uint32_t)off; off += (size_t)pl.kp * EP * 8; pl.off_flags = (uint32_t)off; off += (size_t)pl.events * 4; pl.smem_bytes = (uint32_t)((off + 127) & ~size_t(127));
-          if (pl.smem_bytes <= 72 * 1024u || chunk == 1) break;   // three CTAs per SM: one loads while the others compute
+          if (pl.smem_bytes <= (unsigned)env_int("FJP_REG_SMEM_KB", 72) * 1024u || chunk == 1) break;   // three CTAs per SM: one loads while the others compute
         }
         pl.chunk = chunk;
         long ntiles = (a.n + pl.events - 1) / pl.events; int grid = (int)(ntiles < 3L * g_num_sms ? ntiles : 3L * g_num_sms);
