@@ -141,7 +141,10 @@ int fjp_score_sparse(fjp_engine* e, fjp_model* m, const int64_t* row_ptr, const 
 int fjp_score_sparse_noalloc(fjp_engine* e, fjp_model* m, const int64_t* d_row_ptr, const int32_t* d_indices,
                              const double* d_values, long n, int vec_size, double* d_score, uint8_t* d_status,
                              void* cuda_stream);
-/* Device-pointer variant: asynchronous on `cuda_stream` (a cudaStream_t, NULL = the engine's stream). */
+/* Device-pointer variant: asynchronous on `cuda_stream` (a cudaStream_t, NULL = the engine's stream).  Models with derived
+ * fields, and tree ensembles scoring a batch large enough for the two-kernel throughput path, take a work area from the
+ * device's stream-ordered allocator (cudaMallocAsync / cudaFreeAsync on that stream; fjp_engine_create raises the default
+ * pool's release threshold so the block is reused from call to call). */
 int fjp_score_device(fjp_engine* e, fjp_model* m, const double* dX, const uint32_t* dpresent, const double* dreplace,
                      long n, int vec_size, double* dscore, uint8_t* dstatus, int32_t* daux, void* cuda_stream);
 /* Double-buffered host variant: submit returns a ticket at once (the buffers must stay valid and should be
