@@ -582,15 +582,23 @@ __global__ void __launch_bounds__(CK_WARPS * 32, 1) cluster_fast_kernel(const __
   const double INF = __longlong_as_double(0x7FF0000000000000LL);
   for (int i = tid; i < nf * KP; i += blockDim.x) { int f = i / KP, c = i - f * KP; cent[i] = c < K ? cd.centers[(size_t)c * nf + f] : 0.0; }
   const long ntiles = (a.n + E - 1) / E;
-  if (!HASMISS && pl.pipelined) {
-    // Dense rows, all fields in one chunk, one cluster group per warp: the next tile's rows are copied into the second
-    // buffer (cp.async, 8 B each, straight into the transposed position) while this tile's distances are computed.
+  if (pl.pipelined) {
+    // Plain double rows (optionally with present bits: HASMISS), all fields in one chunk, one cluster group per warp: the
+    // next tile's rows (and present words) are copied into the second buffer (cp.async, straight into the transposed
+    // position) while this tile's distances are computed.
+    const int W = a.present_stride;                                          // <= 4 words in this path (HASMISS)
+    uint32_t* pbuf = reinterpret_cast<uint32_t*>(sts);                       // 2 x E x 4 present words
     auto fill_async = [&](long tile, int buf) {
       const long row0 = tile * E; double* xb = xs + (size_t)buf * pl.chunk * EP;
       const int sh = 31 - __clz(nf); const bool pow2 = (nf & (nf - 1)) == 0;
       for (int i = tid; i < E * nf; i += blockDim.x) {
         int r = pow2 ? (i >> sh) : (i / nf), f = i - r * nf; long rr = row0 + r;
         if (rr < a.n) cp_async8(xb + f * EP + r, a.X + rr * (long)m.F + cd.slot[f]); else xb[f * EP + r] = 0.0;
+      }
+      if (HASMISS) for (int i = tid; i < E * W; i += blockDim.x) {
+        int r = i / W, w = i - r * W; long rr = row0 + r; uint32_t* dst = pbuf + (buf * E + r) * 4 + w;
+        if (rr < a.n) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst)), "l"(a.present + rr * (long)W + w) : "memory");
+        else *dst = 0u;
       }
       asm volatile("cp.async.commit_group;" ::: "memory");
     };
@@ -605,21 +613,48 @@ __global__ void __launch_bounds__(CK_WARPS * 32, 1) cluster_fast_kernel(const __
 #pragma unroll
       for (int k = 0; k < CK_TC; k++) acc[k] = 0.0;
       const double* xb = xs + (size_t)buf * pl.chunk * EP; const double* cp = cent + cg0 * CK_TC;
-      for (int f = 0; f < nf; f++, cp += KP) {
-        const double x = xb[f * EP + e];
-        const double2* c2 = reinterpret_cast<const double2*>(cp);
+      double adj = 1.0;
+      if (HASMISS) {   // the fields a row supplies, as bits; a missing field is skipped and the sum rescaled (all weights are 1)
+        uint32_t pw[4]; int npresent = 0;
 #pragma unroll
-        for (int k = 0; k < CK_TC / 2; k++) {
-          double2 z = c2[k];
-          double d0 = fabs(x - z.x), d1 = fabs(x - z.y);
-          acc[2 * k] += d0 * d0; acc[2 * k + 1] += d1 * d1;
+        for (int w = 0; w < 4; w++) {
+          pw[w] = w < W ? pbuf[(buf * E + e) * 4 + w] : 0u;
+          const int lim = nf - 32 * w; if (lim < 32) pw[w] &= lim > 0 ? (1u << lim) - 1u : 0u;
+          npresent += __popc(pw[w]);
+        }
+        adj = (double)nf / (double)npresent;
+#pragma unroll
+        for (int w = 0; w < 4; w++) {
+          uint32_t bits = pw[w]; const int fend = min(nf, 32 * (w + 1));
+          for (int f = 32 * w; f < fend; f++, cp += KP, bits >>= 1) {
+            const double x = xb[f * EP + e]; const bool present = bits & 1u;
+            const double2* c2 = reinterpret_cast<const double2*>(cp);
+#pragma unroll
+            for (int k = 0; k < CK_TC / 2; k++) {
+              double2 z = c2[k];
+              double d0 = fabs(x - z.x), d1 = fabs(x - z.y);
+              double t0 = d0 * d0, t1 = d1 * d1;
+              if (present) { acc[2 * k] += t0; acc[2 * k + 1] += t1; }
+            }
+          }
+        }
+      } else {
+        for (int f = 0; f < nf; f++, cp += KP) {
+          const double x = xb[f * EP + e];
+          const double2* c2 = reinterpret_cast<const double2*>(cp);
+#pragma unroll
+          for (int k = 0; k < CK_TC / 2; k++) {
+            double2 z = c2[k];
+            double d0 = fabs(x - z.x), d1 = fabs(x - z.y);
+            acc[2 * k] += d0 * d0; acc[2 * k + 1] += d1 * d1;
+          }
         }
       }
       int bc = -1; double bd = 0;
 #pragma unroll
       for (int k = 0; k < CK_TC; k++) {
         int c = cg0 * CK_TC + k;
-        if (c < K) { double d = cd.measure == CM_EUCLIDEAN ? sqrt(acc[k]) : acc[k]; if (bc < 0 || java_cmp(d, bd) < 0) { bc = c; bd = d; } }
+        if (c < K) { double t = HASMISS ? acc[k] * adj : acc[k], d = cd.measure == CM_EUCLIDEAN ? sqrt(t) : t; if (bc < 0 || java_cmp(d, bd) < 0) { bc = c; bd = d; } }
       }
       bestd[cg0 * E + e] = bc < 0 ? INF : bd; bestc[cg0 * E + e] = bc;
       __syncthreads();
@@ -1209,7 +1244,7 @@ static bool plan_forest_compact(const DeviceModel& m, ForestLaunch* out) {
   int ti = env_int("FJP_FOREST_CTI", 8); ti = ti >= 8 ? 8 : 4;
   const int force_e = env_int("FJP_FOREST_CE", 0), force_g = env_int("FJP_FOREST_CG", 0);
   const int t_round = ((fd.n_trees + ti - 1) / ti) * ti;
-  static const int kE[] = {640, 768, 1024, 512, 384, 256, 128, 64};
+  static const int kE[] = {640, 768, 1024, 576, 512, 448, 384, 320, 256, 192, 128, 64};
   for (int E : kE) {
     if (force_e && E != force_e) continue;
     if (E == 1024) ti = 4;   // 64 registers per thread
@@ -1344,8 +1379,10 @@ cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t 
         if (cent + 16384 < (size_t)g_smem_optin) {
           int chunk = (int)(room / ((size_t)(pl.events + 1) * 8 + pl.events + 4)); if (chunk > nf) chunk = nf; if (chunk > 128) chunk = 128;
           if (chunk >= 1) {
-            const bool dense = a.present == nullptr && a.replace == nullptr && m.prep_identity;
-            // dense rows whose fields fit one chunk twice over, one cluster group per warp: double-buffered tiles
+            // plain double rows (with or without present bits) whose fields fit one chunk twice over, one cluster group per
+            // warp: double-buffered tiles.  With present bits: fields = vector slots, at most 128 of them.
+            const bool dense = a.replace == nullptr && m.prep_identity &&
+                               (a.present == nullptr || (m.cluster.slots_identity && a.present_stride <= 4 && (size_t)nf * (pl.events + 4) >= (size_t)2 * pl.events * 16));   // the status area doubles as the present-word buffers
             pl.pipelined = dense && chunk >= nf && pl.groups * pl.event_blocks == CK_WARPS && (size_t)2 * nf * (pl.events + 1) * 8 + (size_t)nf * (pl.events + 4) <= room;
             if (pl.pipelined) chunk = nf;
             pl.chunk = chunk; size_t off = cent; pl.off_x = (uint32_t)off; off += (size_t)(pl.pipelined ? 2 : 1) * chunk * (pl.events + 1) * 8;

@@ -122,6 +122,7 @@ enum : int { CM_EUCLIDEAN = 0, CM_SQEUCLIDEAN = 1, CM_CHEBYCHEV = 2, CM_CITYBLOC
 enum : int { CF_ABSDIFF = 0, CF_GAUSSSIM = 1, CF_DELTA = 2, CF_EQUAL = 3 };
 struct ClusterDesc {
   int k, nf, measure, fast;  // fast: absDiff everywhere, weights 1, q all 1, (squared)Euclidean
+  int slots_identity;        // ClusteringField i reads vector slot i and there are no other slots
   double p;
   const int32_t* slot;      // nf: active-field index of each ClusteringField
   const double* weight;     // nf

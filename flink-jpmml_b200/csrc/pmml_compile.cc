@@ -401,6 +401,8 @@ void compile_clustering(const XNode& m, Builder& b) {
   bool fast = d.measure == CM_SQEUCLIDEAN || d.measure == CM_EUCLIDEAN;
   for (size_t i = 0; i < nf; i++) fast = fast && cmp[i] == CF_ABSDIFF && w[i] == 1.0 && q[i] == 1.0 && slot[i] >= 0;
   d.fast = fast ? 1 : 0;
+  d.slots_identity = (int)nf == b.cm.dev.F ? 1 : 0;
+  for (size_t i = 0; i < nf; i++) if (slot[i] != (int)i) d.slots_identity = 0;
   b.put(&d.slot, slot); b.put(&d.weight, w); b.put(&d.q, q); b.put(&d.compare, cmp); b.put(&d.sim_scale, scale); b.put(&d.centers, centers);
   b.set_labels(ids, true);
   b.cm.dev.target_status = b.has_target ? ST_OK : ST_EXTRACT;  // no named target field -> nothing to extract
