@@ -732,6 +732,138 @@ __global__ void __launch_bounds__(CK_WARPS * 32, 1) cluster_fast_kernel(const __
   }
 }
 
+// ---- the same register tile with TWO events per thread (plain double rows, with or without present bits) --------------
+// A warp-wide broadcast LDS.128 of centres costs two shared-memory wavefronts; with one event per thread the 4 centre loads
+// + 1 input load of a field (11 wavefronts) nearly fill the 12 cycles its 24 FP64 instructions take.  Two events per thread
+// (lane l owns events l and l + 32 of its warp's 64) halve the centre traffic per distance term.
+// CTA = 16 warps = event blocks x cluster groups (groups <= 16); a tile of 64 x event_blocks events is processed in chunks
+// of fields, and the chunks of this and the next tile are double-buffered with cp.async (8 B each, straight into the
+// transposed position).
+struct ClusterPairPlan { int groups, event_blocks, events, kp, chunk, nchunks; uint32_t off_x, off_p, off_best, smem_bytes; };
+template <bool HASMISS>
+__global__ void __launch_bounds__(512, 1) cluster_pair_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, const ClusterPairPlan pl) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  const ClusterDesc& cd = m.cluster; const int nf = cd.nf, K = cd.k, KP = pl.kp, E = pl.events, EP = E + 1;
+  double* cent = reinterpret_cast<double*>(smem);                       // nf x KP   [f][c]
+  double* xs = reinterpret_cast<double*>(smem + pl.off_x);               // 2 x chunk x EP
+  uint32_t* pbuf = reinterpret_cast<uint32_t*>(smem + pl.off_p);         // 2 x E x 4 present words (by tile parity)
+  double* bestd = reinterpret_cast<double*>(smem + pl.off_best);         // groups x E
+  int* bestc = reinterpret_cast<int*>(bestd + pl.groups * E);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int eb = warp % pl.event_blocks, cg = warp / pl.event_blocks;    // warps = event_blocks x groups exactly
+  const int e0 = eb * 64 + lane;                                          // this thread's events: e0 and e0 + 32
+  const int W = a.present_stride, NC = pl.nchunks;
+  const double INF = __longlong_as_double(0x7FF0000000000000LL);
+  for (int i = tid; i < nf * KP; i += blockDim.x) { int f = i / KP, c = i - f * KP; cent[i] = c < K ? cd.centers[(size_t)c * nf + f] : 0.0; }
+  const long ntiles = (a.n + E - 1) / E;
+  const long my_tiles = (long)blockIdx.x < ntiles ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  const long items = my_tiles * NC;                                       // (tile, chunk) pairs of this CTA, in order
+  auto fill_async = [&](long item) {
+    const long ti = item / NC; const int c = (int)(item - ti * NC), buf = (int)(item & 1);
+    const long row0 = (blockIdx.x + ti * gridDim.x) * E; double* xb = xs + (size_t)buf * pl.chunk * EP;
+    const int f0 = c * pl.chunk, nfc = min(pl.chunk, nf - f0);
+    const int sh = 31 - __clz(nfc); const bool pow2 = (nfc & (nfc - 1)) == 0;
+    for (int i = tid; i < E * nfc; i += blockDim.x) {
+      int r = pow2 ? (i >> sh) : (i / nfc), f = i - r * nfc; long rr = row0 + r;
+      if (rr < a.n) cp_async8(xb + f * EP + r, a.X + rr * (long)m.F + cd.slot[f0 + f]); else xb[f * EP + r] = 0.0;
+    }
+    if (HASMISS && c == 0) for (int i = tid; i < E * W; i += blockDim.x) {
+      int r = i / W, w = i - r * W; long rr = row0 + r; uint32_t* dst = pbuf + ((int)(ti & 1) * E + r) * 4 + w;
+      if (rr < a.n) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst)), "l"(a.present + rr * (long)W + w) : "memory");
+      else *dst = 0u;
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  if (items > 0) fill_async(0);
+  double acc[2][CK_TC]; double adj[2] = {1.0, 1.0}; uint32_t pw[2][4] = {{0u, 0u, 0u, 0u}, {0u, 0u, 0u, 0u}};
+  for (long item = 0; item < items; item++) {
+    const long ti = item / NC; const int c = (int)(item - ti * NC), buf = (int)(item & 1);
+    const long tile = blockIdx.x + ti * gridDim.x;
+    if (item + 1 < items) { fill_async(item + 1); asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+    else asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();   // this chunk's values (and, the first time, the centres) are in place
+    if (c == 0) {
+#pragma unroll
+      for (int k = 0; k < CK_TC; k++) { acc[0][k] = 0.0; acc[1][k] = 0.0; }
+      if (HASMISS) {   // the fields a row supplies, as bits; a missing field is skipped and the sum rescaled (all weights are 1)
+#pragma unroll
+        for (int v = 0; v < 2; v++) {
+          int npresent = 0;
+#pragma unroll
+          for (int w = 0; w < 4; w++) {
+            pw[v][w] = w < W ? pbuf[((int)(ti & 1) * E + e0 + 32 * v) * 4 + w] : 0u;
+            const int lim = nf - 32 * w; if (lim < 32) pw[v][w] &= lim > 0 ? (1u << lim) - 1u : 0u;
+            npresent += __popc(pw[v][w]);
+          }
+          adj[v] = (double)nf / (double)npresent;
+        }
+      }
+    }
+    const int f0 = c * pl.chunk, f1 = min(nf, f0 + pl.chunk);
+    const double* xb = xs + (size_t)buf * pl.chunk * EP + e0; const double* cp = cent + (size_t)f0 * KP + cg * CK_TC;
+    if (HASMISS) {
+#pragma unroll
+      for (int w = 0; w < 4; w++) {
+        const int fa = max(f0, 32 * w), fb = min(f1, 32 * (w + 1));   // the part of present word w inside this chunk (chunks are multiples of 32)
+        uint32_t b0 = pw[0][w] >> (fa & 31), b1 = pw[1][w] >> (fa & 31);
+        for (int f = fa; f < fb; f++, cp += KP, xb += EP, b0 >>= 1, b1 >>= 1) {
+          const double x0 = xb[0], x1 = xb[32]; const bool p0 = b0 & 1u, p1 = b1 & 1u;
+          const double2* c2 = reinterpret_cast<const double2*>(cp);
+#pragma unroll
+          for (int k = 0; k < CK_TC / 2; k++) {
+            double2 z = c2[k];
+            double d00 = fabs(x0 - z.x), d01 = fabs(x0 - z.y), d10 = fabs(x1 - z.x), d11 = fabs(x1 - z.y);
+            double t00 = d00 * d00, t01 = d01 * d01, t10 = d10 * d10, t11 = d11 * d11;
+            if (p0) { acc[0][2 * k] += t00; acc[0][2 * k + 1] += t01; }
+            if (p1) { acc[1][2 * k] += t10; acc[1][2 * k + 1] += t11; }
+          }
+        }
+      }
+    } else {
+      for (int f = f0; f < f1; f++, cp += KP, xb += EP) {
+        const double x0 = xb[0], x1 = xb[32];
+        const double2* c2 = reinterpret_cast<const double2*>(cp);
+#pragma unroll
+        for (int k = 0; k < CK_TC / 2; k++) {
+          double2 z = c2[k];
+          double d00 = fabs(x0 - z.x), d01 = fabs(x0 - z.y), d10 = fabs(x1 - z.x), d11 = fabs(x1 - z.y);
+          acc[0][2 * k] += d00 * d00; acc[0][2 * k + 1] += d01 * d01;
+          acc[1][2 * k] += d10 * d10; acc[1][2 * k + 1] += d11 * d11;
+        }
+      }
+    }
+    if (c == NC - 1) {
+#pragma unroll
+      for (int v = 0; v < 2; v++) {
+        int bc = -1; double bd = 0;
+#pragma unroll
+        for (int k = 0; k < CK_TC; k++) {
+          int cc = cg * CK_TC + k;
+          if (cc < K) { double t = HASMISS ? acc[v][k] * adj[v] : acc[v][k], d = cd.measure == CM_EUCLIDEAN ? sqrt(t) : t; if (bc < 0 || java_cmp(d, bd) < 0) { bc = cc; bd = d; } }
+        }
+        bestd[cg * E + e0 + 32 * v] = bc < 0 ? INF : bd; bestc[cg * E + e0 + 32 * v] = bc;
+      }
+      __syncthreads();
+      if (cg == 0) {
+#pragma unroll
+        for (int v = 0; v < 2; v++) {
+          const int e = e0 + 32 * v; const long row = tile * E + e;
+          if (row >= a.n) continue;
+          int bc = bestc[e]; double bd = bestd[e];
+          for (int g = 1; g < pl.groups; g++) {
+            int c2 = bestc[g * E + e]; if (c2 < 0) continue; double d2 = bestd[g * E + e];
+            int cmp = bc < 0 ? -1 : java_cmp(d2, bd);
+            if (cmp < 0 || (cmp == 0 && c2 < bc)) { bc = c2; bd = d2; }
+          }
+          write_label(m, a, row, bc, bc + 1);
+          if (a.probs) a.probs[row * (long)a.prob_stride] = bd;
+        }
+      }
+    }
+    __syncthreads();   // this buffer (and bestd / bestc) are free for the next rounds
+  }
+}
+
 // ================================================================================================ regression (J4)
 // Generic: thread per event, predictor lists in document order (CSR), values prepared on the fly.
 constexpr int REG_MAXC = 64;
@@ -1378,6 +1510,26 @@ cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t 
         size_t room = (size_t)g_smem_optin - 2048 - cent - (size_t)(CK_WARPS / pl.event_blocks) * pl.events * 12;
         if (cent + 16384 < (size_t)g_smem_optin) {
           int chunk = (int)(room / ((size_t)(pl.events + 1) * 8 + pl.events + 4)); if (chunk > nf) chunk = nf; if (chunk > 128) chunk = 128;
+          {  // two events per thread when the rows are plain doubles and the cluster groups fit 16 warps
+            const bool plain = a.replace == nullptr && m.prep_identity && (a.present == nullptr || (m.cluster.slots_identity && a.present_stride <= 4));
+            if (plain && pl.groups <= 16 && 16 % pl.groups == 0 && env_int("FJP_CLUSTER_PAIR", 1)) {
+              ClusterPairPlan pp{}; pp.groups = pl.groups; pp.kp = pl.kp; pp.event_blocks = 16 / pl.groups; pp.events = 64 * pp.event_blocks;
+              const size_t fixed = cent + (size_t)2 * pp.events * 16 + (size_t)pp.groups * pp.events * 12 + 1024;
+              for (pp.nchunks = 1; pp.nchunks <= 8; pp.nchunks++) {   // fewest chunks (of a multiple of 32 fields) whose two buffers fit
+                pp.chunk = pp.nchunks == 1 ? nf : (((nf + pp.nchunks - 1) / pp.nchunks + 31) / 32) * 32;
+                if (fixed + (size_t)2 * pp.chunk * (pp.events + 1) * 8 <= (size_t)g_smem_optin) break;
+              }
+              if (pp.nchunks <= 8 && (long)pp.chunk * (pp.nchunks - 1) < nf) {
+                size_t off = cent; pp.off_x = (uint32_t)off; off += (size_t)2 * pp.chunk * (pp.events + 1) * 8;
+                pp.off_p = (uint32_t)off; off += (size_t)2 * pp.events * 16;
+                pp.off_best = (uint32_t)off; off += (size_t)pp.groups * pp.events * 12; pp.smem_bytes = (uint32_t)((off + 127) & ~size_t(127));
+                long ntiles = (a.n + pp.events - 1) / pp.events; int grid = (int)(ntiles < g_num_sms ? ntiles : g_num_sms);
+                if (a.present) { cudaFuncSetAttribute(cluster_pair_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pp.smem_bytes); cluster_pair_kernel<true><<<grid, 512, pp.smem_bytes, s>>>(m, a, pp); }
+                else { cudaFuncSetAttribute(cluster_pair_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pp.smem_bytes); cluster_pair_kernel<false><<<grid, 512, pp.smem_bytes, s>>>(m, a, pp); }
+                return cudaGetLastError();
+              }
+            }
+          }
           if (chunk >= 1) {
             // plain double rows (with or without present bits) whose fields fit one chunk twice over, one cluster group per
             // warp: double-buffered tiles.  With present bits: fields = vector slots, at most 128 of them.
