@@ -902,8 +902,11 @@ __global__ void __launch_bounds__(128) regression_kernel(const __grid_constant__
 // warps = event blocks x table groups.  Inputs and the transposed coefficient block [field][table] stream through
 // shared memory in chunks of fields; y[c] accumulates in double, unfused, in field order (= NumericPredictor order).
 struct DensePlan { int groups, event_blocks, events, chunk, kp, warps; uint32_t off_x, off_st, off_y, off_flags, smem_bytes; };
-template <bool HASMISS, int TC>
-__global__ void __launch_bounds__(256, 3) regression_tile_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, const DensePlan pl) {
+// EPT = events per thread (lane l owns events l, l + 32 of its warp's 32 * EPT): a warp-wide broadcast LDS.128 of coefficients
+// costs two shared-memory wavefronts, so with one event per thread the coefficient loads alone (11 wavefronts per field for 10
+// tables) outlast the 10 cycles the field's 20 FP64 instructions take; two events share them.
+template <bool HASMISS, int TC, int EPT>
+__global__ void __launch_bounds__(256, EPT == 1 ? 3 : 2) regression_tile_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, const DensePlan pl) {
   extern __shared__ __align__(128) uint8_t smem[];
   const RegressionDesc& rd = m.reg; const int F = m.F, C = rd.n_tables, KP = pl.kp, E = pl.events, EP = E + 1;
   double* wt = reinterpret_cast<double*>(smem);                          // chunk x KP  [f][c]
@@ -912,14 +915,18 @@ __global__ void __launch_bounds__(256, 3) regression_tile_kernel(const __grid_co
   double* ys = reinterpret_cast<double*>(smem + pl.off_y);               // KP x EP
   int* eflags = reinterpret_cast<int*>(smem + pl.off_flags);             // E: bit0 preparation failure, bit1 missing predictor
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int eb = warp % pl.event_blocks, cg = warp / pl.event_blocks, e = eb * 32 + lane;
-  if (tid < E) eflags[tid] = 0;
+  const int eb = warp % pl.event_blocks, cg = warp / pl.event_blocks, e = eb * 32 * EPT + lane;
+  for (int i = tid; i < E; i += blockDim.x) eflags[i] = 0;
   const long ntiles = (a.n + E - 1) / E;
   for (long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-    const long row0 = tile * E, row = row0 + e;
-    double acc[TC]; int flags = 0;  // bit0 preparation failure, bit1 missing predictor
+    const long row0 = tile * E;
+    double acc[EPT][TC]; int flags[EPT];  // bit0 preparation failure, bit1 missing predictor
 #pragma unroll
-    for (int k = 0; k < TC; k++) { int c = cg * TC + k; acc[k] = c < C ? rd.intercept[c] : 0.0; }
+    for (int v = 0; v < EPT; v++) {
+      flags[v] = 0;
+#pragma unroll
+      for (int k = 0; k < TC; k++) { int c = cg * TC + k; acc[v][k] = c < C ? rd.intercept[c] : 0.0; }
+    }
     // double-buffered chunks: the copies of chunk c+1 (cp.async, 8 B each, written straight into the transposed
     // position) are in flight while chunk c is multiplied
     const int nchunks = (F + pl.chunk - 1) / pl.chunk;
@@ -954,19 +961,33 @@ __global__ void __launch_bounds__(256, 3) regression_tile_kernel(const __grid_co
       const double* wp = wt + (size_t)buf * pl.chunk * KP + cg * TC; const double* xb = xs + (size_t)buf * pl.chunk * EP;
       const uint8_t* sb = sts + (size_t)buf * pl.chunk * (E + 4);
       for (int f = 0; f < nfc; f++, wp += KP) {
-        double x = xb[f * EP + e];
-        if (HASMISS) { int st = sb[f * (E + 4) + e]; flags |= st == 2 ? 1 : (st == 1 ? 2 : 0); }
+        double x[EPT];
+#pragma unroll
+        for (int v = 0; v < EPT; v++) {
+          x[v] = xb[f * EP + e + 32 * v];
+          if (HASMISS) { int st = sb[f * (E + 4) + e + 32 * v]; flags[v] |= st == 2 ? 1 : (st == 1 ? 2 : 0); }
+        }
         const double2* w2 = reinterpret_cast<const double2*>(wp);
 #pragma unroll
-        for (int k = 0; k < TC / 2; k++) { double2 w = w2[k]; acc[2 * k] += w.x * x; acc[2 * k + 1] += w.y * x; }
+        for (int k = 0; k < TC / 2; k++) {
+          double2 w = w2[k];
+#pragma unroll
+          for (int v = 0; v < EPT; v++) { acc[v][2 * k] += w.x * x[v]; acc[v][2 * k + 1] += w.y * x[v]; }
+        }
       }
-      __syncthreads();   // buffer `buf` may be refilled by the next iteration's fill
+      __syncthreads();   // buffer `buf` may be refilled by the next iteration's fill (and, after the last chunk, reused for ys)
     }
 #pragma unroll
-    for (int k = 0; k < TC; k++) ys[(cg * TC + k) * EP + e] = acc[k];
-    if (HASMISS) { if (flags) atomicOr(eflags + e, flags); }
+    for (int v = 0; v < EPT; v++) {
+#pragma unroll
+      for (int k = 0; k < TC; k++) ys[(cg * TC + k) * EP + e + 32 * v] = acc[v][k];
+      if (HASMISS) { if (flags[v]) atomicOr(eflags + e + 32 * v, flags[v]); }
+    }
     __syncthreads();
-    if (cg == 0 && row < a.n) {
+#pragma unroll
+    for (int v = 0; v < EPT; v++) {
+      const int e = eb * 32 * EPT + lane + 32 * v; const long row = row0 + e;
+      if (!(cg == 0 && row < a.n)) continue;
       int fl = HASMISS ? eflags[e] : 0;
       if (fl & 1) write_out(a, row, 0, ST_PREP, -1);
       else if (fl & 2) write_out(a, row, 0, m.target_status ? m.target_status : ST_EVAL, -1);
@@ -979,7 +1000,7 @@ __global__ void __launch_bounds__(256, 3) regression_tile_kernel(const __grid_co
         if (a.probs) for (int i = 0; i < C && i < a.prob_stride; i++) a.probs[row * (long)a.prob_stride + i] = ys[i * EP + e];
       }
     }
-    if (HASMISS) { __syncthreads(); if (tid < E) eflags[tid] = 0; }
+    if (HASMISS) { __syncthreads(); for (int i = tid; i < E; i += blockDim.x) eflags[i] = 0; }
   }
 }
 
@@ -1568,22 +1589,29 @@ cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t 
         int tc = 8, best_pad = 1 << 30;
         for (int cand : {8, 10, 12}) { int pad = (m.reg.n_tables + cand - 1) / cand * cand - m.reg.n_tables; if (pad < best_pad) { best_pad = pad; tc = cand; } }
         DensePlan pl{}; pl.kp = ((m.reg.n_tables + tc - 1) / tc) * tc; pl.groups = pl.kp / tc;
-        pl.event_blocks = pl.groups >= 8 ? 1 : 8 / pl.groups; pl.warps = pl.event_blocks * pl.groups; pl.events = 32 * pl.event_blocks;
+        const bool hasmiss = a.present != nullptr || a.replace != nullptr || !m.prep_identity;
+        // two events per thread once there are enough fields for the coefficient traffic to matter
+        const int ept = env_int("FJP_REG_EPT", m.F >= 64 ? 2 : 1) >= 2 ? 2 : 1, per_sm = ept == 2 ? 2 : 3;
+        pl.event_blocks = pl.groups >= 8 ? 1 : 8 / pl.groups; pl.warps = pl.event_blocks * pl.groups; pl.events = 32 * ept * pl.event_blocks;
         const int EP = pl.events + 1;
         int chunk = 64; while (chunk > m.F && chunk > 1) chunk /= 2;   // power of two: cheap row/column split
+        const unsigned smem_cap = (unsigned)env_int("FJP_REG_SMEM_KB", ept == 2 ? 110 : 72) * 1024u;   // per_sm CTAs per SM: one loads while the others compute
         for (;; chunk /= 2) {
-          size_t off = ((size_t)2 * chunk * pl.kp * 8 + 127) & ~size_t(127); pl.off_x = (uint32_t)off; off += (size_t)2 * chunk * EP * 8;
-          pl.off_st = (uint32_t)off; off += (size_t)2 * chunk * (pl.events + 4); off = (off + 15) & ~size_t(15);
-          pl.off_y = (uint32_t)off; off += (size_t)pl.kp * EP * 8; pl.off_flags = (uint32_t)off; off += (size_t)pl.events * 4; pl.smem_bytes = (uint32_t)((off + 127) & ~size_t(127));
-          if (pl.smem_bytes <= (unsigned)env_int("FJP_REG_SMEM_KB", 72) * 1024u || chunk == 1) break;   // three CTAs per SM: one loads while the others compute
+          size_t off = ((size_t)2 * chunk * pl.kp * 8 + 127) & ~size_t(127); pl.off_x = (uint32_t)off;
+          const size_t xbytes = (size_t)2 * chunk * EP * 8, ybytes = (size_t)pl.kp * EP * 8;
+          pl.off_y = (uint32_t)off; off += xbytes > ybytes ? xbytes : ybytes;   // ys (epilogue only) reuses the input buffers
+          pl.off_st = (uint32_t)off; if (hasmiss) off += (size_t)2 * chunk * (pl.events + 4); off = (off + 15) & ~size_t(15);
+          pl.off_flags = (uint32_t)off; off += (size_t)pl.events * 4; pl.smem_bytes = (uint32_t)((off + 127) & ~size_t(127));
+          if (pl.smem_bytes <= smem_cap || chunk == 1) break;
         }
         pl.chunk = chunk;
-        long ntiles = (a.n + pl.events - 1) / pl.events; int grid = (int)(ntiles < 3L * g_num_sms ? ntiles : 3L * g_num_sms);
-        const bool hasmiss = a.present != nullptr || a.replace != nullptr || !m.prep_identity;
-#define FJP_RT(HM, TCV) do { cudaFuncSetAttribute(regression_tile_kernel<HM, TCV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes); \
-                             regression_tile_kernel<HM, TCV><<<grid, pl.warps * 32, pl.smem_bytes, s>>>(m, a, pl); } while (0)
-        if (hasmiss) { if (tc == 8) FJP_RT(true, 8); else if (tc == 10) FJP_RT(true, 10); else FJP_RT(true, 12); }
-        else { if (tc == 8) FJP_RT(false, 8); else if (tc == 10) FJP_RT(false, 10); else FJP_RT(false, 12); }
+        long ntiles = (a.n + pl.events - 1) / pl.events; int grid = (int)(ntiles < (long)per_sm * g_num_sms ? ntiles : (long)per_sm * g_num_sms);
+#define FJP_RT(HM, TCV, EV) do { cudaFuncSetAttribute(regression_tile_kernel<HM, TCV, EV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes); \
+                                 regression_tile_kernel<HM, TCV, EV><<<grid, pl.warps * 32, pl.smem_bytes, s>>>(m, a, pl); } while (0)
+#define FJP_RT2(HM, TCV) do { if (ept == 2) FJP_RT(HM, TCV, 2); else FJP_RT(HM, TCV, 1); } while (0)
+        if (hasmiss) { if (tc == 8) FJP_RT2(true, 8); else if (tc == 10) FJP_RT2(true, 10); else FJP_RT2(true, 12); }
+        else { if (tc == 8) FJP_RT2(false, 8); else if (tc == 10) FJP_RT2(false, 10); else FJP_RT2(false, 12); }
+#undef FJP_RT2
 #undef FJP_RT
         return cudaGetLastError();
       }
