@@ -1306,6 +1306,158 @@ __global__ void __launch_bounds__(NT_E* NT_WARPS, 1) neural_tile_kernel(const __
   }
 }
 
+// ---- the same streamed-weight scheme with TWO events per thread ------------------------------------------------------
+// With one event per thread a row of the weight matrix costs a warp 8 broadcast LDS.128 (two shared-memory wavefronts each)
+// + 1 activation load for 32 FP64 instructions: 20 wavefronts against 16 FP64 cycles.  Here lane l owns events l and l + 32
+// of a 64-event tile (16 warps x NP_G = 2 groups of 8 output neurons = 256 outputs, as above), so the weight loads are
+// shared by twice the arithmetic (8 warps x 4 groups was slower: too few warps to cover the latencies).  One activation buffer [neuron][64]: a layer's outputs stay in registers until every
+// warp has finished reading its inputs, then overwrite them in place.  Sums run from the bias in connection order, unfused.
+constexpr int NP_E = 64, NP_WARPS = 16, NP_G = 2;
+template <int NG>
+__device__ __forceinline__ void np_rows(double (&z)[NP_G][2][8], const double* __restrict__ xcol, const double* __restrict__ wbase, int rows, int n_out_pad, int warp) {
+  if constexpr (NG <= NP_G)
+#pragma unroll 2
+  for (int r = 0; r < rows; r++) {
+    const double x0 = xcol[r * NP_E], x1 = xcol[r * NP_E + 32];
+    const double2* w2 = reinterpret_cast<const double2*>(wbase + (size_t)r * n_out_pad);
+#pragma unroll
+    for (int g = 0; g < NG; g++) {
+      const int jg = warp + g * NP_WARPS;
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        double2 w = w2[jg * 4 + k];
+        z[g][0][2 * k] += w.x * x0; z[g][0][2 * k + 1] += w.y * x0;
+        z[g][1][2 * k] += w.x * x1; z[g][1][2 * k + 1] += w.y * x1;
+      }
+    }
+  }
+}
+struct NeuralPairPlan { uint32_t off_ring, off_bars, off_flags, smem_bytes; };
+__global__ void __launch_bounds__(32 * NP_WARPS, 1) neural_pair_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, const NeuralPairPlan pl) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  const NeuralDesc& nd = m.nn;
+  double* act = reinterpret_cast<double*>(smem);                         // [neuron][NP_E]
+  double* ring = reinterpret_cast<double*>(smem + pl.off_ring);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + pl.off_bars);
+  int* flags = reinterpret_cast<int*>(smem + pl.off_flags);              // NP_E
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+  __syncthreads();
+  uint32_t q_issue = 0, q_wait = 0; int il = 0, ic = 0;   // producer cursor (thread 0): layer, first row of the next chunk
+  auto rows_per_chunk = [&](const NeuralLayer& L) { int r = NT_RING / (L.n_out_pad * 8); return r < 1 ? 1 : (r > L.n_in ? L.n_in : r); };
+  auto issue_next = [&]() {   // thread 0: next chunk of the per-tile sequence into ring slot q_issue & 1
+    if (il >= nd.n_layers) return;
+    const NeuralLayer& L = nd.layers[il]; int rpc = rows_per_chunk(L); int rows = min(rpc, L.n_in - ic);
+    uint32_t bytes = (uint32_t)rows * L.n_out_pad * 8u, slot = q_issue & 1u;
+    mbar_expect_tx(&bars[slot], bytes);
+    bulk_g2s(ring + (size_t)slot * (NT_RING / 8), nd.weights_t + L.wt_off + (size_t)ic * L.n_out_pad, bytes, &bars[slot]);
+    q_issue++; ic += rows; if (ic >= L.n_in) { ic = 0; il++; }
+  };
+  const long ntiles = (a.n + NP_E - 1) / NP_E;
+  for (long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const long row0 = tile * NP_E;
+    if (tid == 0) { il = 0; ic = 0; fence_proxy_async(); issue_next(); issue_next(); }
+    if (tid < NP_E) flags[tid] = 0;
+    __syncthreads();
+    for (int i = warp; i < nd.n_inputs; i += NP_WARPS) {
+      NeuralInput in = nd.inputs[i];
+#pragma unroll
+      for (int v = 0; v < 2; v++) {
+        const int e = lane + 32 * v; const long row = row0 + e; double out = 0; int fl = 0;
+        if (row < a.n) {
+          if (in.kind == NI_CONSTANT) out = in.value;
+          else {
+            double val; int st = in.slot < 0 ? 1 : load_field(m, a, row, in.slot, val);
+            if (st == 2) fl = 1;
+            else if (st == 1) { if (in.has_map_missing) out = in.map_missing; else fl = 2; }
+            else if (in.kind == NI_FIELDREF) out = val;
+            else if (in.kind == NI_NORMDISC) out = java_eq(val, in.value) ? 1.0 : 0.0;
+            else { bool miss = false; out = norm_cont(nd.pts + 2 * in.pts_off, in.n_pts, in.outliers, val, miss); if (miss) fl = 2; }
+          }
+        }
+        act[i * NP_E + e] = out;
+        if (fl) atomicOr(&flags[e], fl);
+      }
+    }
+    __syncthreads();
+    for (int l = 0; l < nd.n_layers; l++) {
+      const NeuralLayer L = nd.layers[l]; const double* B = nd.biases + L.b_off;
+      const int groups = L.n_out_pad / 8, rpc = rows_per_chunk(L);
+      double z[NP_G][2][8];
+#pragma unroll
+      for (int g = 0; g < NP_G; g++) {
+        int jg = warp + g * NP_WARPS;
+#pragma unroll
+        for (int k = 0; k < 8; k++) { int j = jg * 8 + k; double b = (jg < groups && j < L.n_out) ? B[j] : 0.0; z[g][0][k] = b; z[g][1][k] = b; }
+      }
+      const int ng = groups > warp ? min(NP_G, (groups - warp + NP_WARPS - 1) / NP_WARPS) : 0;   // warp-uniform
+      for (int i0 = 0; i0 < L.n_in; i0 += rpc) {
+        const int rows = min(rpc, L.n_in - i0);
+        uint32_t slot = q_wait & 1u; mbar_wait(&bars[slot], (q_wait >> 1) & 1u); q_wait++;
+        const double* wbase = ring + (size_t)slot * (NT_RING / 8);
+        const double* xcol = act + (size_t)i0 * NP_E + lane;
+        switch (ng) {  // no branches inside the row loop
+          case 4: np_rows<4>(z, xcol, wbase, rows, L.n_out_pad, warp); break;
+          case 3: np_rows<3>(z, xcol, wbase, rows, L.n_out_pad, warp); break;
+          case 2: np_rows<2>(z, xcol, wbase, rows, L.n_out_pad, warp); break;
+          case 1: np_rows<1>(z, xcol, wbase, rows, L.n_out_pad, warp); break;
+          default: break;
+        }
+        __syncthreads();   // ring slot consumed (after the last chunk: every warp is done reading the layer's inputs)
+        if (tid == 0) { fence_proxy_async(); issue_next(); }
+      }
+#pragma unroll
+      for (int g = 0; g < NP_G; g++) {
+        int jg = warp + g * NP_WARPS;
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+          int j = jg * 8 + k;
+          if (jg < groups && j < L.n_out) { act[j * NP_E + lane] = activate(L.act, z[g][0][k], L.threshold); act[j * NP_E + lane + 32] = activate(L.act, z[g][1][k], L.threshold); }
+        }
+      }
+      __syncthreads();
+      if (L.norm != NORM_NONE && warp < 2) {
+        double* col = act + warp * 32 + lane;
+        if (L.norm == NORM_SOFTMAX) {
+          double s = 0; for (int j = 0; j < L.n_out; j++) { double ex = exp(col[j * NP_E]); col[j * NP_E] = ex; s += ex; }
+          for (int j = 0; j < L.n_out; j++) col[j * NP_E] /= s;
+        } else {
+          double s = 0; for (int j = 0; j < L.n_out; j++) s += col[j * NP_E];
+          for (int j = 0; j < L.n_out; j++) col[j * NP_E] /= s;
+        }
+      }
+      __syncthreads();
+    }
+    if (warp < 2) {
+      const int e = warp * 32 + lane; const long row = row0 + e; const double* col = act + e;
+      if (row < a.n) {
+        int fl = flags[e];
+        if (fl & 1) write_out(a, row, 0, ST_PREP, -1);
+        else if (fl & 2) write_out(a, row, 0, m.target_status ? m.target_status : ST_EVAL, -1);
+        else if (!nd.classify) {
+          double y = col[nd.out_neuron[0] * NP_E];
+          if (nd.out_denorm_n) {
+            const double* pts = nd.pts + 2 * nd.out_denorm_off; int n = nd.out_denorm_n, i = 0;
+            while (i + 2 < n && y > pts[2 * (i + 1) + 1]) i++;
+            double a0 = pts[2 * i], b0 = pts[2 * i + 1], a1 = pts[2 * i + 2], b1 = pts[2 * i + 3];
+            y = (y - b0) / (b1 - b0) * (a1 - a0) + a0;
+          }
+          write_out(a, row, apply_target(m.tx, y), m.target_status, -1);
+        } else {
+          int best = -1; double bp = 0;
+          for (int o = 0; o < nd.n_outputs; o++) {
+            double p = col[nd.out_neuron[o] * NP_E];
+            if (a.probs && o < a.prob_stride) a.probs[row * (long)a.prob_stride + o] = p;
+            if (best < 0 || java_cmp(p, bp) > 0) { best = o; bp = p; }
+          }
+          write_label(m, a, row, best, best);
+        }
+      }
+    }
+    __syncthreads();   // activations / flags are reused by the next tile
+  }
+}
+
 // ================================================================================================ launchers
 #include "forest_compact.cuh"
 
@@ -1625,6 +1777,16 @@ cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t 
     case MK_NEURAL: {
       bool tiled = true;   // the streamed path keeps <= 4 groups of 8 outputs per warp: layers up to 256 neurons
       for (int l = 0; l < m.nn.n_layers; l++) tiled = tiled && m.nn.layers[l].n_out_pad <= 8 * NT_G * NT_WARPS && m.nn.layers[l].n_out_pad * 8 <= NT_RING;
+      if (tiled && env_int("FJP_NN_PAIR", 1)) {   // two events per thread, one in-place activation buffer
+        NeuralPairPlan pp{}; size_t act = ((size_t)m.nn.max_width * NP_E * 8 + 127) & ~size_t(127);
+        pp.off_ring = (uint32_t)act; pp.off_bars = pp.off_ring + 2 * NT_RING; pp.off_flags = pp.off_bars + 64; pp.smem_bytes = pp.off_flags + NP_E * 4;
+        if (pp.smem_bytes <= (uint32_t)g_smem_optin) {
+          long ntiles = (a.n + NP_E - 1) / NP_E; int grid = (int)(ntiles < g_num_sms ? ntiles : g_num_sms);
+          cudaFuncSetAttribute(neural_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pp.smem_bytes);
+          neural_pair_kernel<<<grid, 32 * NP_WARPS, pp.smem_bytes, s>>>(m, a, pp);
+          return cudaGetLastError();
+        }
+      }
       if (tiled) {
         NeuralPlan pl{}; pl.width = m.nn.max_width; size_t act = ((size_t)m.nn.max_width * NT_E * 8 + 127) & ~size_t(127);
         pl.off_act1 = (uint32_t)act; pl.off_ring = (uint32_t)(2 * act); pl.off_bars = pl.off_ring + 2 * NT_RING; pl.off_flags = pl.off_bars + 64;
