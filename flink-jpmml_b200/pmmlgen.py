@@ -504,18 +504,21 @@ def gbt_classifier_numpy(arrays, X, present=None):
     return probs.argmax(axis=1).astype(np.float64), probs
 
 
-def gbt_pruned_pmml(T=60, max_depth=6, F=20, seed=5, p_leaf=0.25, operator="lessThan", dtype="float"):
+def gbt_pruned_pmml(T=60, max_depth=6, F=20, seed=5, p_leaf=0.25, operator="lessThan", dtype="float", method="sum",
+                    float_thresholds=True):
     """XGBoost-export shape: float fields, `x < t` on the left child, <True/> on the right, defaultChild, trees pruned at
     random (a node below the root becomes a leaf with probability p_leaf), so depths differ within and across trees."""
     from scipy.stats import norm
     rng = np.random.default_rng(seed)
-    grid = norm.ppf((np.arange(255) + 1.0) / 256.0).astype(np.float32).astype(np.float64)
+    grid = norm.ppf((np.arange(255) + 1.0) / 256.0)
+    if float_thresholds:
+        grid = grid.astype(np.float32).astype(np.float64)
     names = [f"x{i}" for i in range(F)]
     out = _header()
     out += _data_dictionary([(n, "continuous", dtype) for n in names], ("y", "continuous", "double", None))
     out.append(f'<MiningModel modelName="gbt-pruned" functionName="regression">')
     out += _mining_schema(names, "y")
-    out.append('<Segmentation multipleModelMethod="sum">')
+    out.append(f'<Segmentation multipleModelMethod="{method}">')
     for t in range(T):
         out.append(f'<Segment id="{t + 1}"><True/><TreeModel functionName="regression" missingValueStrategy="defaultChild" '
                    'noTrueChildStrategy="returnNullPrediction" splitCharacteristic="binarySplit">')
