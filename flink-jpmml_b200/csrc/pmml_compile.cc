@@ -8,10 +8,12 @@
 //
 // This file is host-only C++; it shares no code with oracle/.
 #include <algorithm>
+#include <atomic>
 #include <charconv>
 #include <cfloat>
 #include <cmath>
 #include <cstring>
+#include <deque>
 #include <functional>
 #include <limits>
 #include <map>
@@ -111,8 +113,10 @@ struct Field { std::string name; uint8_t dtype; bool continuous; const XNode* no
 
 struct Builder {
   CompiledModel cm;
-  std::vector<Field> dict; std::unordered_map<std::string, int> dict_idx;
-  std::unordered_map<std::string, int> active_slot;   // field name -> vector slot
+  std::vector<Field> dict; std::unordered_map<sv, int> dict_idx;   // keys are views of names_ entries (a deque never moves them)
+  std::unordered_map<sv, int> active_slot;   // field name -> vector slot
+  std::deque<std::string> names_;
+  sv keep(sv name) { names_.emplace_back(name); return names_.back(); }
   std::vector<uint8_t> slot_dtype;
   std::string target_name; bool has_target = false; uint8_t target_dtype = DT_DOUBLE;
 
@@ -123,13 +127,13 @@ struct Builder {
     cm.fixups.push_back({off, (size_t)((const char*)field_addr - (const char*)&cm.dev)});
   }
   int slot_of(sv name) const {  // -1: not an active field of the top-level schema -> always missing
-    auto it = active_slot.find(std::string(name));
+    auto it = active_slot.find(name);
     if (it != active_slot.end()) return it->second;
-    if (!dict_idx.count(std::string(name))) malformed("reference to unknown field '" + std::string(name) + "'");
+    if (!dict_idx.count(name)) malformed("reference to unknown field '" + std::string(name) + "'");
     return -1;
   }
   const Field& dict_field(sv name) const {
-    auto it = dict_idx.find(std::string(name));
+    auto it = dict_idx.find(name);
     if (it == dict_idx.end()) malformed("unknown field '" + std::string(name) + "'");
     return dict[it->second];
   }
@@ -155,7 +159,7 @@ void read_dictionary(const XNode& root, Builder& b) {
   if (!dd) malformed("no DataDictionary");
   dd->each("DataField", [&](const XNode& f) {
     Field fl{std::string(f.attr("name")), dtype_of(f.attr("dataType")), f.attr("optype") == "continuous", &f};
-    b.dict_idx[fl.name] = (int)b.dict.size(); b.dict.push_back(fl);
+    b.dict_idx[b.keep(fl.name)] = (int)b.dict.size(); b.dict.push_back(fl);
   });
 }
 
@@ -222,7 +226,7 @@ void read_schema(const XNode& model, Builder& b) {
     bool plain = (df.dtype == DT_DOUBLE || df.dtype == DT_FLOAT) && p.n_intervals == 0 && !p.has_valid_space && p.n_invalid == 0 &&
                  p.n_missing == 0 && p.has_repl == 0 && p.outlier == OT_AS_IS;
     simple = simple && plain; identity = identity && plain && df.dtype == DT_DOUBLE;
-    b.active_slot[name] = (int)prep.size(); b.slot_dtype.push_back(df.dtype);
+    b.active_slot[b.keep(name)] = (int)prep.size(); b.slot_dtype.push_back(df.dtype);
     b.cm.active_names.push_back(name); prep.push_back(p);
   });
   b.cm.dev.F = (int)prep.size(); b.cm.dev.prep_simple = simple ? 1 : 0; b.cm.dev.prep_identity = identity ? 1 : 0;
@@ -347,8 +351,8 @@ void read_derived(const XNode& root, const XNode& model, Builder& b) {
     prog_off.push_back((int32_t)dc.ops.size()); dtypes.push_back(dt);
     std::string name(f->attr("name"));
     Field fl{name, dt, f->attr("optype", "continuous") == "continuous", nullptr};
-    b.dict_idx[name] = (int)b.dict.size(); b.dict.push_back(fl);
-    b.active_slot[name] = b.cm.dev.F; b.slot_dtype.push_back(dt); b.cm.dev.F++;
+    b.dict_idx[b.keep(name)] = (int)b.dict.size(); b.dict.push_back(fl);
+    b.active_slot[b.keep(name)] = b.cm.dev.F; b.slot_dtype.push_back(dt); b.cm.dev.F++;
   }
   b.put(&dd.prog_off, prog_off); b.put(&dd.ops, dc.ops); b.put(&dd.pool, dc.pool); b.put(&dd.dtype, dtypes);
   if (dd.n_derived) {   // the family kernel reads already prepared values: identity preparation over the augmented row
@@ -425,9 +429,20 @@ struct ForestBuilder {
   struct TreeCtx {
     int mvs;  // 0 none, 1 defaultChild, 2 lastPrediction, 3 nullPrediction
     bool last_on_no_true; int counter = 0; TargetXform sub_tx; bool has_sub_tx = false;
-    std::unordered_map<const XNode*, int> number; std::unordered_map<const XNode*, int32_t> entered, leafref;
-    std::map<std::pair<const XNode*, int>, int32_t> chained;
+    uint32_t epoch = 0;   // per-Node memos live in XNode::scratch: [0] node number, [1] entered, [2] leaf, [3] chain from this child on
   };
+  enum : int { M_NUMBER = 0, M_ENTERED = 1, M_LEAF = 2, M_CHAIN = 3 };
+  static uint32_t next_epoch() { static std::atomic<uint32_t> e{0}; return ++e; }   // documents are not shared between threads; the counter is
+  static bool memo_get(const XNode& n, const TreeCtx& cx, int slot, int32_t* v) {
+    if (n.scratch_epoch != cx.epoch || !(n.scratch_set & (1u << slot))) return false;
+    *v = n.scratch[slot]; return true;
+  }
+  static void memo_put(const XNode& n, const TreeCtx& cx, int slot, int32_t v) {
+    if (n.scratch_epoch != cx.epoch) { n.scratch_epoch = cx.epoch; n.scratch_set = 0; }
+    n.scratch[slot] = v; n.scratch_set |= 1u << slot;
+  }
+  static const XNode* next_node(const XNode* k) { for (k = k ? k->next : nullptr; k && k->name != "Node"; k = k->next) {} return k; }
+  static const XNode* first_node(const XNode& p) { const XNode* k = p.first; while (k && k->name != "Node") k = k->next; return k; }
 
   static const XNode* pred_of(const XNode& n) {
     for (const XNode* k = n.first; k; k = k->next)
@@ -436,13 +451,14 @@ struct ForestBuilder {
   }
   void number_nodes(const XNode& n, TreeCtx& cx) {
     cx.counter++; double v; sv id = n.attr("id");
-    cx.number[&n] = (!id.empty() && parse_double(id, &v) && v == std::floor(v) && std::fabs(v) < 2e9) ? (int)v : cx.counter;
-    n.each("Node", [&](const XNode& k) { number_nodes(k, cx); });
+    memo_put(n, cx, M_NUMBER, (!id.empty() && parse_double(id, &v) && v == std::floor(v) && std::fabs(v) < 2e9) ? (int)v : cx.counter);
+    for (const XNode* k = first_node(n); k; k = next_node(k)) number_nodes(*k, cx);
   }
   int32_t leaf_for(const XNode& n, TreeCtx& cx) {  // successor for "the result is node n's score"
     if (!n.has("score")) return LEAF_NULL;
-    auto it = cx.leafref.find(&n); if (it != cx.leafref.end()) return it->second;
-    TLeaf lf{0.0, -1, cx.number[&n], {}};
+    int32_t memo; if (memo_get(n, cx, M_LEAF, &memo)) return memo;
+    int32_t number = 0; memo_get(n, cx, M_NUMBER, &number);
+    TLeaf lf{0.0, -1, number, {}};
     if (classify) {
       lf.label = label_of(n.attr("score"));
       // ScoreDistribution: `probability` if given, else recordCount / sum (JPMML; SURVEY App. A TreeModel)
@@ -465,7 +481,7 @@ struct ForestBuilder {
         lf.value = v;
       }
     }
-    leaves.push_back(lf); int32_t s = ~(int32_t)(leaves.size() - 1); cx.leafref[&n] = s; return s;
+    leaves.push_back(lf); int32_t s = ~(int32_t)(leaves.size() - 1); memo_put(n, cx, M_LEAF, s); return s;
   }
   int32_t add_test(int slot, double value, bool strict, int32_t t, int32_t f, int32_t m) {
     if (slot < 0) return m;  // field is never supplied -> always UNKNOWN
@@ -531,43 +547,38 @@ struct ForestBuilder {
     unsupported(std::string(p.name) + " in a TreeModel");
   }
   int32_t enter(const XNode& n, int32_t last, TreeCtx& cx) {
-    auto it = cx.entered.find(&n); if (it != cx.entered.end()) return it->second;
-    int32_t r;
-    if (!n.child("Node")) r = leaf_for(n, cx);
-    else { int32_t l2 = n.has("score") ? leaf_for(n, cx) : last; r = chain(n, 0, l2, cx); }
-    cx.entered[&n] = r; return r;
+    int32_t r; if (memo_get(n, cx, M_ENTERED, &r)) return r;
+    const XNode* kid = first_node(n);
+    if (!kid) r = leaf_for(n, cx);
+    else { int32_t l2 = n.has("score") ? leaf_for(n, cx) : last; r = chain(n, kid, l2, cx); }
+    memo_put(n, cx, M_ENTERED, r); return r;
   }
-  // successor for "children i.. of parent are still to be tried"
-  int32_t chain(const XNode& parent, int i, int32_t last, TreeCtx& cx) {
-    auto key = std::make_pair(&parent, i);
-    auto it = cx.chained.find(key); if (it != cx.chained.end()) return it->second;
-    std::vector<const XNode*> kids; parent.each("Node", [&](const XNode& k) { kids.push_back(&k); });
-    int32_t r;
-    if (i >= (int)kids.size()) r = cx.last_on_no_true ? last : LEAF_NULL;
+  // successor for "the children of parent from `kid` on are still to be tried" (kid == nullptr: none left)
+  int32_t chain(const XNode& parent, const XNode* kid, int32_t last, TreeCtx& cx) {
+    if (!kid) return cx.last_on_no_true ? last : LEAF_NULL;
+    int32_t r; if (memo_get(*kid, cx, M_CHAIN, &r)) return r;
+    const XNode& p = *pred_of(*kid); const XNode* rest = next_node(kid);
+    if (p.name == "True") r = enter(*kid, last, cx);
+    else if (p.name == "False") r = chain(parent, rest, last, cx);
     else {
-      const XNode& kid = *kids[i]; const XNode& p = *pred_of(kid);
-      if (p.name == "True") r = enter(kid, last, cx);
-      else if (p.name == "False") r = chain(parent, i + 1, last, cx);
-      else {
-        int32_t s_true = enter(kid, last, cx), s_false = chain(parent, i + 1, last, cx), s_miss;
-        switch (cx.mvs) {
-          case 0: s_miss = s_false; break;
-          case 1: { sv dc = parent.attr("defaultChild"); const XNode* d = nullptr;
-                    for (auto* k : kids) if (!dc.empty() && k->attr("id") == dc) d = k;
-                    if (!d) unsupported("missingValueStrategy=defaultChild without a resolvable defaultChild");
-                    s_miss = enter(*d, last, cx); break; }
-          case 2: s_miss = last; break;
-          default: s_miss = LEAF_NULL; break;
-        }
-        r = emit_pred(p, s_true, s_false, s_miss);
+      int32_t s_true = enter(*kid, last, cx), s_false = chain(parent, rest, last, cx), s_miss;
+      switch (cx.mvs) {
+        case 0: s_miss = s_false; break;
+        case 1: { sv dc = parent.attr("defaultChild"); const XNode* d = nullptr;
+                  if (!dc.empty()) for (const XNode* k = first_node(parent); k; k = next_node(k)) if (k->attr("id") == dc) d = k;
+                  if (!d) unsupported("missingValueStrategy=defaultChild without a resolvable defaultChild");
+                  s_miss = enter(*d, last, cx); break; }
+        case 2: s_miss = last; break;
+        default: s_miss = LEAF_NULL; break;
       }
+      r = emit_pred(p, s_true, s_false, s_miss);
     }
-    cx.chained[key] = r; return r;
+    memo_put(*kid, cx, M_CHAIN, r); return r;
   }
 
   void add_tree(const XNode& tm, double weight, bool nested) {
     if (nested) check_nested_schema(tm);
-    TreeCtx cx; sv mvs = tm.attr("missingValueStrategy", "none");
+    TreeCtx cx; cx.epoch = next_epoch(); sv mvs = tm.attr("missingValueStrategy", "none");
     cx.mvs = mvs == "none" ? 0 : mvs == "defaultChild" ? 1 : mvs == "lastPrediction" ? 2 : mvs == "nullPrediction" ? 3 : -1;
     if (cx.mvs < 0) unsupported("missingValueStrategy " + std::string(mvs));
     cx.last_on_no_true = tm.attr("noTrueChildStrategy", "returnNullPrediction") == "returnLastPrediction";

@@ -26,6 +26,9 @@ struct XNode {
   XNode* next = nullptr;                  // next sibling
   std::string_view text;                  // character data (first chunk; later chunks appended in doc.extra)
   const struct XmlDoc* doc = nullptr;
+  // scratch for whoever walks the tree (the PMML compiler memoises per-Node results here instead of in hash maps):
+  // values are valid for the walk whose epoch matches
+  mutable uint32_t scratch_epoch = 0; mutable uint32_t scratch_set = 0; mutable int32_t scratch[4] = {0, 0, 0, 0};
 
   std::string_view attr(std::string_view k, std::string_view dflt = {}) const;
   bool has(std::string_view k) const;
@@ -96,6 +99,10 @@ inline std::string_view strip_prefix(std::string_view n) {
 inline void xml_parse(const char* data, size_t len, XmlDoc& doc) {
   using namespace detail;
   doc.buf.assign(data, len);
+  {  // one attribute per '=' at most: reserve once instead of regrowing (and copying) the array for large ensembles
+    size_t eq = 0; for (size_t i = 0; i < len; i++) eq += data[i] == '=';   // vectorised by the compiler
+    doc.attrs.reserve(eq + 16);
+  }
   doc.buf.push_back('\0');
   char* p = doc.buf.data();
   char* end = p + len;
