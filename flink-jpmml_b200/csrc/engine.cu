@@ -56,7 +56,8 @@ static void make_describe(fjp_model* m) {
   if (d.kind == MK_FOREST) {
     s += " trees=" + std::to_string(d.forest.n_trees) + " format=" + (d.forest.format == FOREST_COMPLETE ? "complete" : "general") +
          " depth=" + std::to_string(d.forest.depth) + " enc=" + (d.forest.enc == ENC_FLOAT ? "float" : "rank") +
-         " method=" + std::to_string(d.forest.method) + " nodes=" + std::to_string(m->cm.n_nodes) + " compact=" + std::to_string(d.forest.compact.enabled + d.forest.compact.wide);   // 1: float thresholds, 2: 64-bit threshold images
+         " method=" + std::to_string(d.forest.method) + " nodes=" + std::to_string(m->cm.n_nodes) + " compact=" + std::to_string(d.forest.compact.enabled + d.forest.compact.wide) +   // 1: float thresholds, 2: 64-bit threshold images
+         (d.forest.compact.sparse ? " sparse=1" : "");
     ForestLaunch fl;
     if (m->d_blob && d.forest.method != FM_SINGLE && plan_forest_complete(d, &fl))
       s += " tile_events=" + std::to_string(fl.events_per_cta) + " trees_per_stage=" + std::to_string(fl.trees_per_stage) + " interleave=" + std::to_string(fl.trees_interleaved) +

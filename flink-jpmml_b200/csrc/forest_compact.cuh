@@ -274,3 +274,115 @@ forest_compact_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, 
     __syncthreads();  // the key tile and the votes are reused by the next tile
   }
 }
+
+// ---- sparse form: trees with explicit children (model.h CompactDesc, "sparse") --------------------------------------------
+// Same tiles, keys and node word as forest_compact_kernel; a node also names its two successors, so trees keep their own
+// shape (leaf-wise grown or heavily pruned trees, DAGs of compound predicates) instead of being padded to a common depth.
+// Groups of up to CK_SG_MAX trees stream through the 2-slot ring; a thread walks TI trees of the group at a time until all
+// of them have reached a leaf.  MODE: 0 sum / average, 1 weighted sum / average, 2 majority vote.
+template <int TI, int MODE, int MAXT>
+__global__ void __launch_bounds__(MAXT, 1)
+forest_sparse_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, const ForestLaunch fl, const KeyTiles kt) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  const ForestDesc& fd = m.forest; const CompactDesc& cd = fd.compact;
+  const int E = blockDim.x, tid = threadIdx.x;
+  uint8_t* ring = smem + fl.off_ring;
+  uint16_t* votes = reinterpret_cast<uint16_t*>(smem + fl.off_votes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + fl.off_bars);
+  const int T = fd.n_trees, NG = cd.n_groups; const uint32_t slot_bytes = (uint32_t)cd.group_max_bytes;
+
+  if (tid == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); mbar_init(&bars[2], 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+  __syncthreads();
+
+  uint32_t q_issue = 0, q_wait = 0, tile_parity = 0;
+  auto issue = [&](int g) {  // thread 0: fill ring slot q_issue&1 with tree group g
+    const uint32_t slot = q_issue & 1u, o0 = cd.group_off[g], bytes = cd.group_off[g + 1] - o0;
+    mbar_expect_tx(&bars[slot], bytes);
+    bulk_g2s(ring + (size_t)slot * slot_bytes, reinterpret_cast<const uint8_t*>(cd.blobs) + o0, bytes, &bars[slot]);
+    q_issue++;
+  };
+
+  for (long tile = blockIdx.x; tile < kt.ntiles; tile += gridDim.x) {
+    if (tid == 0) {
+      fence_proxy_async();
+      mbar_expect_tx(&bars[2], kt.tile_bytes);
+      const uint8_t* src = reinterpret_cast<const uint8_t*>(kt.keys) + (size_t)tile * kt.tile_bytes;
+      for (uint32_t o = 0; o < kt.tile_bytes; o += 32768u) bulk_g2s(smem + o, src + o, min(32768u, kt.tile_bytes - o), &bars[2]);
+      issue(0); if (NG > 1) issue(1);
+    }
+    const long row = kt.row_begin + tile * E + tid;
+    const bool failed = kt.fail != nullptr && kt.fail[tile * E + tid] != 0;
+    if (MODE == 2) for (int l = 0; l < m.n_labels; l++) { votes[l * E + tid] = 0; votes[(m.n_labels + l) * E + tid] = 0xFFFF; }
+    mbar_wait(&bars[2], tile_parity); tile_parity ^= 1u;
+
+    const uint32_t kbase = smem_u32(smem) + 4u * tid, Eb = (uint32_t)E;
+    double sum = 0.0, wsum = 0.0; uint32_t seen = 0;
+    for (int g = 0; g < NG; g++) {
+      const uint32_t slot = q_wait & 1u;
+      mbar_wait(&bars[slot], (q_wait >> 1) & 1u); q_wait++;
+      const uint32_t base = smem_u32(ring + (size_t)slot * slot_bytes);
+      uint32_t nt; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(nt) : "r"(base));
+      for (uint32_t t = 0; t < nt; t += TI) {
+        uint32_t tb[TI], code[TI], nn[TI];
+#pragma unroll
+        for (int k = 0; k < TI; k++) {
+          uint32_t off; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(off) : "r"(base + 8u + 4u * min(t + k, nt - 1)));
+          tb[k] = base + off;
+          asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(nn[k]), "=r"(code[k]) : "r"(tb[k]));
+        }
+        for (;;) {   // one level of every unfinished tree per round
+          bool busy = false;
+#pragma unroll
+          for (int k = 0; k < TI; k++) busy |= code[k] < 0x8000u;
+          if (!busy) break;
+#pragma unroll
+          for (int k = 0; k < TI; k++) {
+            if (code[k] < 0x8000u) {
+              uint32_t nd, ch, ka, key, vv;
+              asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(nd), "=r"(ch) : "r"(tb[k] + 16u + code[k] * 8u));
+              asm("lop3.b32 %0, %1, %2, 2, 0xF8;" : "=r"(ka) : "r"(kbase + (nd & 0x1FCu) * Eb), "r"(nd));
+              asm volatile("ld.shared.u16 %0, [%1];" : "=r"(key) : "r"(ka));
+              asm("lop3.b32 %0, %1, %2, 0x8000, 0xD0;" : "=r"(vv) : "r"(key), "r"(nd));
+              const uint32_t K = ~((uint32_t)((int32_t)nd >> 16));            // node holds ~K
+              code[k] = vv > K ? ch >> 16 : ch & 0xFFFFu;
+            }
+          }
+        }
+#pragma unroll
+        for (int k = 0; k < TI; k++) {
+          if (t + k < nt) {
+            const uint32_t la = tb[k] + 16u + (nn[k] + (code[k] & 0x7FFFu)) * 8u;
+            if (MODE != 2) {
+              double lv; asm volatile("ld.shared.f64 %0, [%1];" : "=d"(lv) : "r"(la));
+              if (MODE == 1) { double w; asm volatile("ld.shared.f64 %0, [%1];" : "=d"(w) : "r"(tb[k] + 8u)); sum += w * lv; wsum += w; }
+              else sum += lv;
+            } else {
+              uint32_t lab; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(lab) : "r"(la));
+              uint16_t c = votes[lab * E + tid];
+              if (c == 0) votes[(m.n_labels + lab) * E + tid] = (uint16_t)seen++;
+              votes[lab * E + tid] = c + 1;
+            }
+          }
+        }
+      }
+      __syncthreads();  // everyone is done with this ring slot
+      if (tid == 0 && g + 2 < NG) { fence_proxy_async(); issue(g + 2); }
+    }
+    if (row < a.n) {
+      if (failed) write_out(a, row, 0, ST_PREP, -1);
+      else if (MODE != 2) {
+        double v = sum;
+        if (fd.method == FM_AVERAGE) v = sum / (double)T; else if (fd.method == FM_WAVERAGE) v = sum / wsum;
+        write_out(a, row, apply_target(m.tx, v), m.target_status, -1);
+      } else {
+        int best = -1; uint32_t bc = 0, bo = 0;
+        for (int l = 0; l < m.n_labels; l++) {
+          uint32_t c = votes[l * E + tid], o = votes[(m.n_labels + l) * E + tid];
+          if (c && (best < 0 || c > bc || (c == bc && o < bo))) { best = l; bc = c; bo = o; }  // first maximal in insertion order
+        }
+        write_label(m, a, row, best, best);
+      }
+    }
+    __syncthreads();  // the key tile and the votes are reused by the next tile
+  }
+}

@@ -1542,11 +1542,28 @@ size_t forest_slice_scratch_bytes(const DeviceModel& m, long n) {
 static bool plan_forest_compact(const DeviceModel& m, ForestLaunch* out) {
   query_device();
   const ForestDesc& fd = m.forest;
-  if (fd.format != FOREST_COMPLETE || !fd.compact.enabled || !env_int("FJP_FOREST_COMPACT", 1)) return false;
-  if (fd.classify ? fd.method != FM_VOTE : (fd.method != FM_SUM && fd.method != FM_AVERAGE && fd.method != FM_WSUM && fd.method != FM_WAVERAGE && fd.method != FM_CHAIN)) return false;
+  const bool sparse = fd.compact.sparse != 0;   // explicit-children trees: one group of trees per ring slot
+  if (!fd.compact.enabled || (fd.format != FOREST_COMPLETE && !sparse) || !env_int("FJP_FOREST_COMPACT", 1)) return false;
+  if (fd.classify ? fd.method != FM_VOTE : (fd.method != FM_SUM && fd.method != FM_AVERAGE && fd.method != FM_WSUM && fd.method != FM_WAVERAGE && (fd.method != FM_CHAIN || sparse))) return false;
   if (fd.classify && m.n_labels > 64) return false;
-  const size_t budget = (size_t)g_smem_optin - 1024, TB = (size_t)fd.compact.tree_bytes;
-  int ti = env_int("FJP_FOREST_CTI", 8); ti = ti >= 8 ? 8 : 4;
+  const size_t budget = (size_t)g_smem_optin - 1024, TB = sparse ? (size_t)fd.compact.group_max_bytes : (size_t)fd.compact.tree_bytes;
+  int ti = env_int("FJP_FOREST_CTI", sparse ? 4 : 8); ti = ti >= 8 ? 8 : 4;
+  if (sparse) {
+    const int force_e = env_int("FJP_FOREST_CE", 0);
+    static const int kEs[] = {640, 768, 1024, 576, 512, 448, 384, 320, 256, 192, 128, 64};
+    for (int E : kEs) {
+      if (force_e && E != force_e) continue;
+      if (E == 1024) ti = 4;
+      size_t keys = ((size_t)((m.F + 1) / 2) * E * 4 + 127) & ~size_t(127);
+      size_t votes = fd.classify ? (size_t)2 * m.n_labels * E * 2 : 0;
+      size_t off = keys + 2 * TB; if (off + votes + 64 + 256 > budget) continue;
+      ForestLaunch fl{}; fl.events_per_cta = E; fl.trees_per_stage = 1; fl.trees_interleaved = ti;
+      fl.off_ring = (uint32_t)keys; off = (off + 15) & ~size_t(15); fl.off_votes = (uint32_t)off; off += votes; off = (off + 15) & ~size_t(15);
+      fl.off_bars = (uint32_t)off; off += 64; fl.smem_bytes = (uint32_t)((off + 127) & ~size_t(127));
+      *out = fl; return true;
+    }
+    return false;
+  }
   const int force_e = env_int("FJP_FOREST_CE", 0), force_g = env_int("FJP_FOREST_CG", 0);
   const int t_round = ((fd.n_trees + ti - 1) / ti) * ti;
   static const int kE[] = {640, 768, 1024, 576, 512, 448, 384, 320, 256, 192, 128, 64};
@@ -1595,6 +1612,14 @@ static cudaError_t launch_fcc(const DeviceModel& m, const BatchArgs& a, const Fo
   k<<<grid, fl.events_per_cta, fl.smem_bytes, s>>>(m, a, fl, kt);
   return cudaGetLastError();
 }
+template <int TI, int MODE, int MAXT>
+static cudaError_t launch_fsp(const DeviceModel& m, const BatchArgs& a, const ForestLaunch& fl, const KeyTiles& kt, int grid, cudaStream_t s) {
+  auto k = forest_sparse_kernel<TI, MODE, MAXT>;
+  cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fl.smem_bytes);
+  if (e != cudaSuccess) return e;
+  k<<<grid, fl.events_per_cta, fl.smem_bytes, s>>>(m, a, fl, kt);
+  return cudaGetLastError();
+}
 static cudaError_t launch_forest_compact(const DeviceModel& m, const BatchArgs& a, const ForestLaunch& fl, void* scratch, cudaStream_t s, int* launches) {
   const CompactDesc& cd = m.forest.compact;
   const int E = fl.events_per_cta; const long ntiles = (a.n + E - 1) / E, pass = compact_tiles_per_pass(m, fl, ntiles);
@@ -1621,6 +1646,13 @@ static cudaError_t launch_forest_compact(const DeviceModel& m, const BatchArgs& 
 #define FJP_CC2(DD, MM) (E > 768 ? FJP_CC3(DD, 4, MM, 1024) : (E > 640 ? (fl.trees_interleaved >= 8 ? FJP_CC3(DD, 8, MM, 768) : FJP_CC3(DD, 4, MM, 768)) \
                                                                          : (fl.trees_interleaved >= 8 ? FJP_CC3(DD, 8, MM, 640) : FJP_CC3(DD, 4, MM, 640))))
 #define FJP_CC1(DD) (mode == 2 ? FJP_CC2(DD, 2) : (mode == 3 ? FJP_CC2(DD, 3) : (mode == 1 ? FJP_CC2(DD, 1) : FJP_CC2(DD, 0))))
+    if (cd.sparse) {
+#define FJP_SP3(TT, MM, XX) launch_fsp<TT, MM, XX>(m, a, fl, kt, grid, s)
+#define FJP_SP2(MM) (E > 768 ? FJP_SP3(4, MM, 1024) : (E > 640 ? FJP_SP3(4, MM, 768) : (fl.trees_interleaved >= 8 ? FJP_SP3(8, MM, 640) : FJP_SP3(4, MM, 640))))
+      e = mode == 2 ? FJP_SP2(2) : (mode == 1 ? FJP_SP2(1) : FJP_SP2(0));
+#undef FJP_SP2
+#undef FJP_SP3
+    } else
     e = d == 8 ? FJP_CC1(8) : FJP_CC1(0);
 #undef FJP_CC1
 #undef FJP_CC2

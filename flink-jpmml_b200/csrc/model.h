@@ -80,9 +80,17 @@ static constexpr int32_t LEAF_NULL = INT32_MIN;  // successor meaning "null pred
 //               ~K = 0 (never right) or K = 0x7FFF with a = 1 (right only when missing).
 constexpr int CK_FB = 8;             // features per block of the key pre-pass
 struct CkFeat { uint32_t thr_off, n_thr, tab_off, nb; float lo, scale; };   // byte offsets inside the feature block's table area
+//   sparse      trees that do not fit one common depth (leaf-wise grown, heavily pruned, DAGs of compound predicates) keep
+//               explicit children: tree = {u32 n_nodes, u32 root, double weight, u64 node[n_nodes], 8-byte leaf[...]},
+//               node = the 32-bit word above | (left | right << 16) << 32; a child / root code >= 0x8000 is leaf (code & 0x7FFF).
+//               Trees are streamed in groups: {u32 n_trees, u32 0, u32 byte offset of tree k [CK_SG_MAX]} followed by the trees.
+constexpr int CK_SG_MAX = 16;        // trees per group of the sparse form
+constexpr int CK_SG_HDR = 8 + 4 * CK_SG_MAX;   // 72 -> trees start at 80
 struct CompactDesc {
   int enabled, wide, tree_bytes, n_blocks, block_smem;   // wide: 64-bit threshold images (thresholds that are not floats); block_smem: largest table area of one feature block
-  const uint32_t* blobs;       // n_trees x tree_bytes
+  int sparse, n_groups, group_max_bytes;                 // sparse form: blobs = the groups back to back
+  const uint32_t* group_off;   // n_groups + 1 byte offsets into blobs (multiples of 16)
+  const uint32_t* blobs;       // n_trees x tree_bytes (complete form) / the groups (sparse form)
   const CkFeat* feat;          // F
   const uint8_t* tables;       // per feature block: sorted distinct threshold images (u32, or u64 when wide; all-ones-terminated) and bucket tables (u16 x nb)
   const uint32_t* block_off;   // n_blocks + 1 byte offsets into tables (multiples of 16)

@@ -620,9 +620,9 @@ struct ForestBuilder {
   // 4-byte nodes.  `wide` = false: every threshold is a float and one float image per value decides every test (ENC_FLOAT's
   // argument); `wide` = true: thresholds are compared as doubles, the tables hold 64-bit images (ENC_RANK's order).
   static uint64_t ordkey64(double d) { uint64_t u; memcpy(&u, &d, 8); return (u & 0x8000000000000000ull) ? ~u : (u | 0x8000000000000000ull); }
-  template <class FeatOf> void emit_compact(int depth, const std::vector<uint8_t>& used, FeatOf feat_of, bool wide) {
+  template <class FeatOf> void emit_compact(int depth, const std::vector<uint8_t>& used, FeatOf feat_of, bool wide, bool sparse) {
     ForestDesc& fd = b.cm.dev.forest; CompactDesc& cd = fd.compact; const int F = b.cm.dev.F;
-    if (F > 256 || depth < 1) return;
+    if (F > 256 || (!sparse && depth < 1)) return;
     // per feature: sorted distinct threshold images and the float each one falls on (bucket arithmetic is float)
     auto image = [&](const Thr& t) -> uint64_t { return wide ? ordkey64(t.value) : (uint64_t)ordkey((float)t.value); };
     std::vector<std::vector<std::pair<uint64_t, float>>> img(F);
@@ -670,9 +670,71 @@ struct ForestBuilder {
     }
     block_off[nblocks] = (uint32_t)tables.size();
     if (block_smem > 104 * 1024) return;   // two CTAs of the key pre-pass per SM
+    // node word shared by both tree forms
+    bool ok = true;
+    auto node_word = [&](const TNode& n) -> uint32_t {
+      // right iff (a ? key : key & 0x7FFF) > K; a missing value has key 0x8000.  No threshold: never right (a = 0, ~K := 0)
+      // or right only when missing (a = 1, K := 0x7FFF)
+      uint32_t a = (n.on_missing == n.on_false && n.on_true != n.on_false) ? 1u : 0u, feat = (uint32_t)feat_of(n), y;
+      if (n.thr >= 0) { uint32_t kk = K16[n.thr]; if (kk > 0x7FFEu) ok = false; y = ~kk; } else y = a ? ~0x7FFFu : 0u;
+      if (feat > 255) ok = false;
+      return (feat << 1) | (a << 15) | ((y & 0xFFFFu) << 16);
+    };
+    if (sparse) {
+      // explicit children: every node sends a missing value down one of its two branches, no null prediction reachable
+      std::vector<uint8_t> out; std::vector<uint32_t> group_off{0}; size_t group_max = 0;
+      std::vector<uint8_t> grp; int in_grp = 0; std::vector<uint32_t> dir;
+      auto close_group = [&]() {
+        if (!in_grp) return;
+        std::vector<uint8_t> g(CK_SG_HDR + 8, 0); uint32_t nt = (uint32_t)in_grp; memcpy(g.data(), &nt, 4);
+        for (int k = 0; k < in_grp; k++) { uint32_t o = dir[k] + (uint32_t)g.size(); memcpy(g.data() + 8 + 4 * k, &o, 4); }
+        g.insert(g.end(), grp.begin(), grp.end()); g.resize((g.size() + 15) & ~size_t(15));
+        group_max = std::max(group_max, g.size()); out.insert(out.end(), g.begin(), g.end()); group_off.push_back((uint32_t)out.size());
+        grp.clear(); dir.clear(); in_grp = 0;
+      };
+      std::vector<int32_t> local(nodes.size(), -1), leaf_local(leaves.size(), -1);
+      for (size_t t = 0; t < roots.size() && ok; t++) {
+        std::vector<int32_t> order, lorder; std::vector<int32_t> stack{roots[t]};
+        while (!stack.empty() && ok) {   // reachable nodes / leaves of this tree, numbered in visiting order
+          int32_t s = stack.back(); stack.pop_back();
+          if (s == LEAF_NULL) { ok = false; break; }
+          if (s < 0) { if (leaf_local[~s] < 0) { leaf_local[~s] = (int32_t)lorder.size(); lorder.push_back(~s); } continue; }
+          if (local[s] >= 0) continue;
+          const TNode& n = nodes[s];
+          if (n.on_missing != n.on_true && n.on_missing != n.on_false) { ok = false; break; }
+          local[s] = (int32_t)order.size(); order.push_back(s); stack.push_back(n.on_false); stack.push_back(n.on_true);
+        }
+        if (order.size() > 32767 || lorder.size() > 32767) ok = false;
+        if (!ok) break;
+        auto code = [&](int32_t s) -> uint32_t { return s < 0 ? 0x8000u | (uint32_t)leaf_local[~s] : (uint32_t)local[s]; };
+        std::vector<uint8_t> tb(16 + 8 * (order.size() + lorder.size()), 0);
+        uint32_t nn = (uint32_t)order.size(), rc = code(roots[t]); memcpy(tb.data(), &nn, 4); memcpy(tb.data() + 4, &rc, 4); memcpy(tb.data() + 8, &weights[t], 8);
+        for (size_t i = 0; i < order.size(); i++) {
+          const TNode& n = nodes[order[i]];
+          uint64_t w = (uint64_t)node_word(n) | ((uint64_t)(code(n.on_true) | (code(n.on_false) << 16)) << 32);
+          memcpy(tb.data() + 16 + 8 * i, &w, 8);
+        }
+        for (size_t i = 0; i < lorder.size(); i++) {
+          const TLeaf& lf = leaves[lorder[i]]; uint8_t* dst = tb.data() + 16 + 8 * (order.size() + i);
+          if (classify) { uint64_t l = (uint64_t)(uint32_t)lf.label; memcpy(dst, &l, 8); } else memcpy(dst, &lf.value, 8);
+        }
+        for (int32_t s : order) local[s] = -1;
+        for (int32_t l : lorder) leaf_local[l] = -1;
+        if (tb.size() > 48 * 1024) { ok = false; break; }                       // one tree must fit a ring slot
+        if (in_grp == CK_SG_MAX || grp.size() + tb.size() > 40 * 1024) close_group();   // a ring slot holds up to 40 KB of trees
+        dir.push_back((uint32_t)grp.size()); grp.insert(grp.end(), tb.begin(), tb.end()); in_grp++;
+      }
+      close_group();
+      if (!ok) return;
+      std::vector<uint32_t> words((out.size() + 3) / 4, 0); memcpy(words.data(), out.data(), out.size());
+      cd.enabled = 1; cd.wide = wide ? 1 : 0; cd.sparse = 1; cd.n_groups = (int)group_off.size() - 1; cd.group_max_bytes = (int)group_max;
+      cd.tree_bytes = 0; cd.n_blocks = nblocks; cd.block_smem = (int)block_smem;
+      b.put(&cd.blobs, words); b.put(&cd.group_off, group_off); b.put(&cd.feat, feats); b.put(&cd.tables, tables); b.put(&cd.block_off, block_off);
+      return;
+    }
     // trees
     const size_t TB = (size_t)compact_tree_bytes(depth), first_leaf = size_t(1) << depth;
-    std::vector<uint32_t> blobs(roots.size() * TB / 4, 0); bool ok = true;
+    std::vector<uint32_t> blobs(roots.size() * TB / 4, 0);
     for (size_t t = 0; t < roots.size() && ok; t++) {
       uint8_t* bl = reinterpret_cast<uint8_t*>(blobs.data()) + t * TB;
       uint32_t* nd = reinterpret_cast<uint32_t*>(bl);
@@ -686,20 +748,16 @@ struct ForestBuilder {
           if (classify) { uint64_t l = (uint64_t)(uint32_t)lf.label; memcpy(dst, &l, 8); } else memcpy(dst, &lf.value, 8);
           return;
         }
-        const TNode& n = nodes[s]; uint32_t a = (n.on_missing == n.on_false && n.on_true != n.on_false) ? 1u : 0u;
-        // right iff (a ? key : key & 0x7FFF) > K; a missing value has key 0x8000.  No threshold: never right (a = 0, ~K := 0)
-        // or right only when missing (a = 1, K := 0x7FFF)
-        uint32_t feat = (uint32_t)feat_of(n), y;
-        if (n.thr >= 0) { uint32_t kk = K16[n.thr]; if (kk > 0x7FFEu) ok = false; y = ~kk; } else y = a ? ~0x7FFFu : 0u;
-        if (feat > 255) ok = false;
-        nd[h] = (feat << 1) | (a << 15) | ((y & 0xFFFFu) << 16);
+        const TNode& n = nodes[s];
+        nd[h] = node_word(n);
         place(n.on_true, 2 * h); place(n.on_false, 2 * h + 1);
       };
       place(roots[t], 1);
     }
     if (!ok) return;
     cd.enabled = 1; cd.wide = wide ? 1 : 0; cd.tree_bytes = (int)TB; cd.n_blocks = nblocks; cd.block_smem = (int)block_smem;
-    b.put(&cd.blobs, blobs); b.put(&cd.feat, feats); b.put(&cd.tables, tables); b.put(&cd.block_off, block_off);
+    std::vector<uint32_t> no_groups{0};
+    b.put(&cd.blobs, blobs); b.put(&cd.group_off, no_groups); b.put(&cd.feat, feats); b.put(&cd.tables, tables); b.put(&cd.block_off, block_off);
   }
 
   void emit(int method) {
@@ -797,10 +855,11 @@ struct ForestBuilder {
         place(roots[t], 1);
       }
       b.put(&fd.blobs, blobs);
-      if (method != FM_SINGLE) emit_compact(depth, used, feat_of, !float_ok);
+      if (method != FM_SINGLE) emit_compact(depth, used, feat_of, !float_ok, false);
     } else {
       fd.format = FOREST_GENERAL; fd.depth = 0;
       std::vector<uint64_t> blobs; b.put(&fd.blobs, blobs);
+      if (method != FM_SINGLE && method != FM_CHAIN && !roots.empty()) emit_compact(0, used, feat_of, !float_ok, true);
     }
     b.put(&fd.leaf_node_id, leaf_ids);
     {  // the general form is always emitted: the engine falls back to it when a tile of keys does not fit on chip

@@ -202,3 +202,43 @@ def test_boosted_classifier_model_chain(engine, oracle, gen, monkeypatch, n_clas
     same(compact, classic)
     assert np.array_equal(compact["probs"].view(np.int64), classic["probs"].view(np.int64))
     np.testing.assert_allclose(compact["probs"], o["probs"], rtol=1e-6)
+
+
+@pytest.mark.parametrize("max_depth,p_leaf,floats,method", [(14, 0.3, True, "sum"), (12, 0.2, False, "average"), (9, 0.4, True, "sum")])
+def test_unbalanced_trees_keep_their_shape(engine, oracle, gen, monkeypatch, max_depth, p_leaf, floats, method):
+    """Leaf-wise / heavily pruned trees do not fit one common depth: the compiler keeps explicit children (sparse=1) and the
+    throughput path walks them as they are; the general kernel (FJP_FOREST_COMPACT=0) is the one to compare with."""
+    pm = gen.gbt_pruned_pmml(T=48, max_depth=max_depth, F=23, seed=max_depth, p_leaf=p_leaf, dtype="double",
+                             operator="lessOrEqual", method=method, float_thresholds=floats)
+    m, om = engine.compile(pm), oracle.OracleModel(pm)
+    assert "format=general" in m.describe and "sparse=1" in m.describe, m.describe
+    X, pres, pb = gen.events(148 * 640 + 1000, 23, 8, 0.1)       # large enough to take the path unforced
+    X[::50, 2] = np.nan
+    classic, compact = score_both(engine, m, X[:20000], pb[:20000], monkeypatch)
+    o = om.predict(X[:20000], pb[:20000], nthreads=8)
+    same(compact, o)
+    same(compact, classic)
+    monkeypatch.delenv("FJP_FOREST_COMPACT")
+    import torch
+    from flink_jpmml_b200 import capi
+    n = len(X); st = torch.cuda.Stream()
+    with torch.cuda.stream(st):
+        dX = torch.from_numpy(X).cuda(); dP = torch.from_numpy(pb.view(np.int32)).cuda()
+        dS = torch.empty(n, dtype=torch.float64, device="cuda"); dT = torch.empty(n, dtype=torch.uint8, device="cuda")
+        st.synchronize()
+        before = engine.launch_count
+        assert capi.lib().fjp_score_device(engine._h, m._h, dX.data_ptr(), dP.data_ptr(), None, n, 23, dS.data_ptr(), dT.data_ptr(), None, C.c_void_p(st.cuda_stream)) == 0
+        st.synchronize()
+    assert engine.launch_count - before >= 2
+    full = om.predict(X, pb, nthreads=8)
+    assert np.array_equal(dS.cpu().numpy().view(np.int64), full["score"].view(np.int64)) and np.array_equal(dT.cpu().numpy(), full["status"])
+
+
+def test_majority_vote_over_trees_deeper_than_the_common_depth_limit(engine, oracle, gen, monkeypatch):
+    pm, arr = gen.rf_pmml(T=7, depth=11, F=16, n_labels=3, seed=77)       # depth 11 > 10: no common-depth layout
+    m, om = engine.compile(pm), oracle.OracleModel(pm)
+    assert "format=general" in m.describe and "sparse=1" in m.describe, m.describe
+    X, pres, pb = gen.events(9000, 16, 78, 0.1)
+    classic, compact = score_both(engine, m, X, pb, monkeypatch)
+    same(compact, om.predict(X, pb, nthreads=8))
+    same(compact, classic)
