@@ -11,7 +11,7 @@ OPERATORS = ["lessThan", "lessOrEqual", "greaterThan", "greaterOrEqual"]
 
 def params(seed):
     rng = np.random.default_rng(1000 + seed)
-    return dict(T=int(rng.integers(1, 48)), max_depth=int(rng.integers(1, 10)), F=int(rng.integers(1, 48)), seed=seed,
+    return dict(T=int(rng.integers(1, 48)), max_depth=int(rng.integers(1, 14)), F=int(rng.integers(1, 48)), seed=seed,
                 p_leaf=float(rng.choice([0.0, 0.15, 0.4])), operator=str(rng.choice(OPERATORS)), dtype=str(rng.choice(["float", "double"])),
                 method=str(rng.choice(["sum", "average"])), float_thresholds=bool(rng.integers(0, 2)))
 
