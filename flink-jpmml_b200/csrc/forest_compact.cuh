@@ -279,7 +279,8 @@ forest_compact_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, 
 // Same tiles, keys and node word as forest_compact_kernel; a node also names its two successors, so trees keep their own
 // shape (leaf-wise grown or heavily pruned trees, DAGs of compound predicates) instead of being padded to a common depth.
 // Groups of up to CK_SG_MAX trees stream through the 2-slot ring; a thread walks TI trees of the group at a time until all
-// of them have reached a leaf.  MODE: 0 sum / average, 1 weighted sum / average, 2 majority vote.
+// of them have reached a leaf.  MODE: 0 sum / average, 1 weighted sum / average, 2 majority vote, 3 modelChain (the tree
+// header's weight slot then holds the channel).
 template <int TI, int MODE, int MAXT>
 __global__ void __launch_bounds__(MAXT, 1)
 forest_sparse_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, const ForestLaunch fl, const KeyTiles kt) {
@@ -317,6 +318,7 @@ forest_sparse_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, c
 
     const uint32_t kbase = smem_u32(smem) + 4u * tid, Eb = (uint32_t)E;
     double sum = 0.0, wsum = 0.0; uint32_t seen = 0;
+    uint32_t cur_ch = 0; double* chv = reinterpret_cast<double*>(votes);   // modelChain: running channel, finished channel values [channel][event]
     for (int g = 0; g < NG; g++) {
       const uint32_t slot = q_wait & 1u;
       mbar_wait(&bars[slot], (q_wait >> 1) & 1u); q_wait++;
@@ -355,7 +357,11 @@ forest_sparse_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, c
             if (MODE != 2) {
               double lv; asm volatile("ld.shared.f64 %0, [%1];" : "=d"(lv) : "r"(la));
               if (MODE == 1) { double w; asm volatile("ld.shared.f64 %0, [%1];" : "=d"(w) : "r"(tb[k] + 8u)); sum += w * lv; wsum += w; }
-              else sum += lv;
+              else if (MODE == 3) {
+                uint32_t ch; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(ch) : "r"(tb[k] + 8u));
+                if (ch != cur_ch) { chv[cur_ch * E + tid] = channel_value(fd.channels[cur_ch], sum); sum = 0.0; cur_ch = ch; }   // trees arrive channel by channel
+                sum += lv;
+              } else sum += lv;
             } else {
               uint32_t lab; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(lab) : "r"(la));
               uint16_t c = votes[lab * E + tid];
@@ -370,7 +376,10 @@ forest_sparse_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, c
     }
     if (row < a.n) {
       if (failed) write_out(a, row, 0, ST_PREP, -1);
-      else if (MODE != 2) {
+      else if (MODE == 3) {
+        chv[cur_ch * E + tid] = channel_value(fd.channels[cur_ch], sum);
+        chain_finish(m, a, row, [&](int c) { return chv[c * E + tid]; });
+      } else if (MODE != 2) {
         double v = sum;
         if (fd.method == FM_AVERAGE) v = sum / (double)T; else if (fd.method == FM_WAVERAGE) v = sum / wsum;
         write_out(a, row, apply_target(m.tx, v), m.target_status, -1);

@@ -709,6 +709,7 @@ struct ForestBuilder {
         auto code = [&](int32_t s) -> uint32_t { return s < 0 ? 0x8000u | (uint32_t)leaf_local[~s] : (uint32_t)local[s]; };
         std::vector<uint8_t> tb(16 + 8 * (order.size() + lorder.size()), 0);
         uint32_t nn = (uint32_t)order.size(), rc = code(roots[t]); memcpy(tb.data(), &nn, 4); memcpy(tb.data() + 4, &rc, 4); memcpy(tb.data() + 8, &weights[t], 8);
+        if (!chain_channels.empty()) { uint64_t ch = (uint64_t)(uint32_t)chain_channels[t]; memcpy(tb.data() + 8, &ch, 8); }   // modelChain: channel instead of weight
         for (size_t i = 0; i < order.size(); i++) {
           const TNode& n = nodes[order[i]];
           uint64_t w = (uint64_t)node_word(n) | ((uint64_t)(code(n.on_true) | (code(n.on_false) << 16)) << 32);
@@ -859,7 +860,7 @@ struct ForestBuilder {
     } else {
       fd.format = FOREST_GENERAL; fd.depth = 0;
       std::vector<uint64_t> blobs; b.put(&fd.blobs, blobs);
-      if (method != FM_SINGLE && method != FM_CHAIN && !roots.empty()) emit_compact(0, used, feat_of, !float_ok, true);
+      if (method != FM_SINGLE && !roots.empty()) emit_compact(0, used, feat_of, !float_ok, true);
     }
     b.put(&fd.leaf_node_id, leaf_ids);
     {  // the general form is always emitted: the engine falls back to it when a tile of keys does not fit on chip

@@ -242,3 +242,21 @@ def test_majority_vote_over_trees_deeper_than_the_common_depth_limit(engine, ora
     classic, compact = score_both(engine, m, X, pb, monkeypatch)
     same(compact, om.predict(X, pb, nthreads=8))
     same(compact, classic)
+
+
+def test_model_chain_over_trees_that_keep_their_shape(engine, oracle, gen, monkeypatch):
+    pm, arr = gen.gbt_classifier_pmml(T=5, depth=11, F=18, n_classes=3, seed=91)     # depth 11: explicit-children form
+    m, om = engine.compile(pm), oracle.OracleModel(pm)
+    assert "method=9" in m.describe and "sparse=1" in m.describe, m.describe
+    X, pres, pb = gen.events(7000, 18, 92, 0.1)
+    monkeypatch.setenv("FJP_FOREST_COMPACT", "0")
+    classic = engine.score(m, X, pb, n_probs=3)
+    monkeypatch.setenv("FJP_FOREST_COMPACT", "2")
+    before = engine.launch_count
+    compact = engine.score(m, X, pb, n_probs=3)
+    assert engine.launch_count - before >= 2
+    o = om.predict(X, pb, n_probs=3, nthreads=8)
+    same(compact, o)
+    same(compact, classic)
+    assert np.array_equal(compact["probs"].view(np.int64), classic["probs"].view(np.int64))
+    np.testing.assert_allclose(compact["probs"], o["probs"], rtol=1e-6)
