@@ -338,16 +338,16 @@ forest_sparse_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, c
           for (int k = 0; k < TI; k++) busy |= code[k] < 0x8000u;
           if (!busy) break;
 #pragma unroll
-          for (int k = 0; k < TI; k++) {
-            if (code[k] < 0x8000u) {
-              uint32_t nd, ch, ka, key, vv;
-              asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(nd), "=r"(ch) : "r"(tb[k] + 16u + code[k] * 8u));
-              asm("lop3.b32 %0, %1, %2, 2, 0xF8;" : "=r"(ka) : "r"(kbase + (nd & 0x1FCu) * Eb), "r"(nd));
-              asm volatile("ld.shared.u16 %0, [%1];" : "=r"(key) : "r"(ka));
-              asm("lop3.b32 %0, %1, %2, 0x8000, 0xD0;" : "=r"(vv) : "r"(key), "r"(nd));
-              const uint32_t K = ~((uint32_t)((int32_t)nd >> 16));            // node holds ~K
-              code[k] = vv > K ? ch >> 16 : ch & 0xFFFFu;
-            }
+          for (int k = 0; k < TI; k++) {   // straight-line: a finished chain re-reads node 0 and keeps its leaf code (no divergent branch)
+            const bool done = code[k] >= 0x8000u;
+            uint32_t nd, ch, ka, key, vv;
+            asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(nd), "=r"(ch) : "r"(tb[k] + 16u + (done ? 0u : code[k]) * 8u));
+            asm("lop3.b32 %0, %1, %2, 2, 0xF8;" : "=r"(ka) : "r"(kbase + (nd & 0x1FCu) * Eb), "r"(nd));
+            asm volatile("ld.shared.u16 %0, [%1];" : "=r"(key) : "r"(ka));
+            asm("lop3.b32 %0, %1, %2, 0x8000, 0xD0;" : "=r"(vv) : "r"(key), "r"(nd));
+            const uint32_t K = ~((uint32_t)((int32_t)nd >> 16));            // node holds ~K
+            const uint32_t next = vv > K ? ch >> 16 : ch & 0xFFFFu;
+            code[k] = done ? code[k] : next;
           }
         }
 #pragma unroll

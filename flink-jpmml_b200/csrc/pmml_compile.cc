@@ -707,8 +707,9 @@ struct ForestBuilder {
         if (order.size() > 32767 || lorder.size() > 32767) ok = false;
         if (!ok) break;
         auto code = [&](int32_t s) -> uint32_t { return s < 0 ? 0x8000u | (uint32_t)leaf_local[~s] : (uint32_t)local[s]; };
-        std::vector<uint8_t> tb(16 + 8 * (order.size() + lorder.size()), 0);
-        uint32_t nn = (uint32_t)order.size(), rc = code(roots[t]); memcpy(tb.data(), &nn, 4); memcpy(tb.data() + 4, &rc, 4); memcpy(tb.data() + 8, &weights[t], 8);
+        const size_t n_slots = std::max<size_t>(order.size(), 1);   // a bare leaf still gets one (all-zero, never visited for real) node:
+        std::vector<uint8_t> tb(16 + 8 * (n_slots + lorder.size()), 0);   // the walk re-reads node 0 for chains that are already done
+        uint32_t nn = (uint32_t)n_slots, rc = code(roots[t]); memcpy(tb.data(), &nn, 4); memcpy(tb.data() + 4, &rc, 4); memcpy(tb.data() + 8, &weights[t], 8);
         if (!chain_channels.empty()) { uint64_t ch = (uint64_t)(uint32_t)chain_channels[t]; memcpy(tb.data() + 8, &ch, 8); }   // modelChain: channel instead of weight
         for (size_t i = 0; i < order.size(); i++) {
           const TNode& n = nodes[order[i]];
@@ -716,7 +717,7 @@ struct ForestBuilder {
           memcpy(tb.data() + 16 + 8 * i, &w, 8);
         }
         for (size_t i = 0; i < lorder.size(); i++) {
-          const TLeaf& lf = leaves[lorder[i]]; uint8_t* dst = tb.data() + 16 + 8 * (order.size() + i);
+          const TLeaf& lf = leaves[lorder[i]]; uint8_t* dst = tb.data() + 16 + 8 * (n_slots + i);
           if (classify) { uint64_t l = (uint64_t)(uint32_t)lf.label; memcpy(dst, &l, 8); } else memcpy(dst, &lf.value, 8);
         }
         for (int32_t s : order) local[s] = -1;
