@@ -157,7 +157,8 @@ __global__ void __launch_bounds__(RK_THREADS, RK_CTAS) forest_rank_keys_kernel(c
   }
 }
 
-// MODE: 0 sum / average, 1 weighted sum / average, 2 majority vote, 3 modelChain (per-channel sums -> RegressionTables).
+// MODE: 0 sum / average, 1 weighted sum / average, 2 majority vote, 3 modelChain (per-channel sums -> RegressionTables),
+// 4 (weighted) average of the leaves' class distributions (scikit-learn style random forests).
 template <int D, int TI, int MODE, int MAXT>
 __global__ void __launch_bounds__(MAXT, 1)
 forest_compact_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, const ForestLaunch fl, const KeyTiles kt) {
@@ -166,8 +167,10 @@ forest_compact_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, 
   const int E = blockDim.x, tid = threadIdx.x;
   const int depth = D ? D : fd.depth;
   const uint32_t TB = (uint32_t)cd.tree_bytes, nleaf = 1u << depth;
-  const uint32_t off_leaf = 4u * nleaf - 8u * nleaf;   // leaf h (h >= 2^depth) lives at 4*2^depth + 8*(h - 2^depth); wraps, 32-bit address arithmetic
-  const uint32_t off_w = 12u * nleaf;
+  const uint32_t LB = MODE == 4 ? (uint32_t)cd.leaf_bytes : 8u;   // bytes per leaf record
+  const uint32_t off_leaf = 4u * nleaf - LB * nleaf;   // leaf h (h >= 2^depth) lives at 4*2^depth + LB*(h - 2^depth); wraps, 32-bit address arithmetic
+  const uint32_t off_w = (4u + LB) * nleaf;
+  double* dvotes = reinterpret_cast<double*>(smem + fl.off_votes);   // MODE 4: summed probabilities [label][event]
   const int G = fl.trees_per_stage;
   uint8_t* ring = smem + fl.off_ring;
   uint16_t* votes = reinterpret_cast<uint16_t*>(smem + fl.off_votes);
@@ -196,6 +199,8 @@ forest_compact_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, 
     const long row = kt.row_begin + tile * E + tid;
     const bool failed = kt.fail != nullptr && kt.fail[tile * E + tid] != 0;
     if (MODE == 2) for (int l = 0; l < m.n_labels; l++) { votes[l * E + tid] = 0; votes[(m.n_labels + l) * E + tid] = 0xFFFF; }
+    if (MODE == 4) for (int l = 0; l < m.n_labels; l++) dvotes[l * E + tid] = 0.0;
+    uint32_t seen_mask = 0, order = 0;   // MODE 4: labels met so far, and the position (nibble) at which each was first met
     mbar_wait(&bars[2], tile_parity); tile_parity ^= 1u;
 
     const uint32_t kbase = smem_u32(smem) + 4u * tid;    // byte address of this event's column of key-pair words
@@ -231,7 +236,16 @@ forest_compact_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, 
 #pragma unroll
         for (int k = 0; k < TI; k++) {
           if (t + k < nt) {
-            if (MODE != 2) {
+            if (MODE == 4) {
+              const uint32_t la = bl[k] + off_leaf + idx[k] * LB; uint32_t nib, cnt; double ww = 1.0;
+              asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(nib), "=r"(cnt) : "r"(la));
+              if (fd.method == FM_WAVG_PROB) asm volatile("ld.shared.f64 %0, [%1];" : "=d"(ww) : "r"(bl[k] + off_w));
+              for (uint32_t i = 0; i < cnt; i++, nib >>= 4) {   // the leaf's distribution in document order
+                const uint32_t lab = nib & 15u; double p; asm volatile("ld.shared.f64 %0, [%1];" : "=d"(p) : "r"(la + 8u + 8u * i));
+                if (!((seen_mask >> lab) & 1u)) { order |= seen << (4u * lab); seen++; seen_mask |= 1u << lab; }
+                dvotes[lab * E + tid] += ww * p;
+              }
+            } else if (MODE != 2) {
               double lv;
               asm volatile("ld.shared.f64 %0, [%1];" : "=d"(lv) : "r"(bl[k] + off_leaf + idx[k] * 8u));
               if (MODE == 1) { double w; asm volatile("ld.shared.f64 %0, [%1];" : "=d"(w) : "r"(bl[k] + off_w)); sum += w * lv; wsum += w; }
@@ -255,7 +269,17 @@ forest_compact_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, 
     }
     if (row < a.n) {
       if (failed) write_out(a, row, 0, ST_PREP, -1);
-      else if (MODE == 3) {
+      else if (MODE == 4) {   // largest summed probability; ties go to the label met first (dividing by the tree count would not move the winner)
+        int best = -1; double bv = 0; uint32_t bo = 0;
+        for (int l = 0; l < m.n_labels; l++) {
+          if (!((seen_mask >> l) & 1u)) continue;
+          const double v = dvotes[l * E + tid]; const uint32_t o = (order >> (4 * l)) & 15u;
+          if (best < 0) { best = l; bv = v; bo = o; continue; }
+          const int c = java_cmp(v, bv);
+          if (c > 0 || (c == 0 && o < bo)) { best = l; bv = v; bo = o; }
+        }
+        write_label(m, a, row, best, best);
+      } else if (MODE == 3) {
         chv[cur_ch * E + tid] = channel_value(fd.channels[cur_ch], sum);
         chain_finish(m, a, row, [&](int c) { return chv[c * E + tid]; });
       } else if (MODE != 2) {

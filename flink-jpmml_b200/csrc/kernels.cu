@@ -1544,7 +1544,8 @@ static bool plan_forest_compact(const DeviceModel& m, ForestLaunch* out) {
   const ForestDesc& fd = m.forest;
   const bool sparse = fd.compact.sparse != 0;   // explicit-children trees: one group of trees per ring slot
   if (!fd.compact.enabled || (fd.format != FOREST_COMPLETE && !sparse) || !env_int("FJP_FOREST_COMPACT", 1)) return false;
-  if (fd.classify ? fd.method != FM_VOTE : (fd.method != FM_SUM && fd.method != FM_AVERAGE && fd.method != FM_WSUM && fd.method != FM_WAVERAGE && fd.method != FM_CHAIN)) return false;
+  const bool avg_prob = fd.classify && (fd.method == FM_AVG_PROB || fd.method == FM_WAVG_PROB) && !sparse && fd.compact.leaf_bytes > 8 && m.n_labels <= 16;
+  if (fd.classify ? (fd.method != FM_VOTE && !avg_prob) : (fd.method != FM_SUM && fd.method != FM_AVERAGE && fd.method != FM_WSUM && fd.method != FM_WAVERAGE && fd.method != FM_CHAIN)) return false;
   if (fd.classify && m.n_labels > 64) return false;
   const size_t budget = (size_t)g_smem_optin - 1024, TB = sparse ? (size_t)fd.compact.group_max_bytes : (size_t)fd.compact.tree_bytes;
   int ti = env_int("FJP_FOREST_CTI", sparse ? 4 : 8); ti = ti >= 8 ? 8 : 4;
@@ -1571,7 +1572,7 @@ static bool plan_forest_compact(const DeviceModel& m, ForestLaunch* out) {
     if (force_e && E != force_e) continue;
     if (E == 1024) ti = 4;   // 64 registers per thread
     size_t keys = ((size_t)((m.F + 1) / 2) * E * 4 + 127) & ~size_t(127);
-    size_t votes = fd.classify ? (size_t)2 * m.n_labels * E * 2 : (fd.method == FM_CHAIN ? (size_t)fd.n_channels * E * 8 : 0);
+    size_t votes = avg_prob ? (size_t)m.n_labels * E * 8 : (fd.classify ? (size_t)2 * m.n_labels * E * 2 : (fd.method == FM_CHAIN ? (size_t)fd.n_channels * E * 8 : 0));
     size_t fixed = keys + votes + 64 + 256;
     if (fixed + 2 * ti * TB > budget) continue;
     int G = (int)((budget - fixed) / (2 * TB)); G = (G / ti) * ti; if (G > 2 * ti) G = 2 * ti;
@@ -1626,7 +1627,7 @@ static cudaError_t launch_forest_compact(const DeviceModel& m, const BatchArgs& 
   KeyTiles kt{}; kt.keys = static_cast<uint32_t*>(scratch); kt.E = E; kt.tile_bytes = (uint32_t)((size_t)((m.F + 1) / 2) * E * 4);
   uint8_t* fail = static_cast<uint8_t*>(scratch) + (size_t)pass * kt.tile_bytes;
   const int OS = ((E + 63) & ~63) + 8; const size_t rk_smem = (size_t)cd.block_smem + (size_t)CK_FB * OS * 2;
-  const int mode = m.forest.classify ? 2 : (m.forest.method == FM_CHAIN ? 3 : ((m.forest.method == FM_WSUM || m.forest.method == FM_WAVERAGE) ? 1 : 0));
+  const int mode = m.forest.classify ? (m.forest.method == FM_VOTE ? 2 : 4) : (m.forest.method == FM_CHAIN ? 3 : ((m.forest.method == FM_WSUM || m.forest.method == FM_WAVERAGE) ? 1 : 0));
   const int d = m.forest.depth;
   for (long t0 = 0; t0 < ntiles; t0 += pass) {
     kt.row_begin = t0 * E; kt.ntiles = ntiles - t0 < pass ? ntiles - t0 : pass;
@@ -1645,7 +1646,7 @@ static cudaError_t launch_forest_compact(const DeviceModel& m, const BatchArgs& 
 #define FJP_CC3(DD, TT, MM, XX) launch_fcc<DD, TT, MM, XX>(m, a, fl, kt, grid, s)
 #define FJP_CC2(DD, MM) (E > 768 ? FJP_CC3(DD, 4, MM, 1024) : (E > 640 ? (fl.trees_interleaved >= 8 ? FJP_CC3(DD, 8, MM, 768) : FJP_CC3(DD, 4, MM, 768)) \
                                                                          : (fl.trees_interleaved >= 8 ? FJP_CC3(DD, 8, MM, 640) : FJP_CC3(DD, 4, MM, 640))))
-#define FJP_CC1(DD) (mode == 2 ? FJP_CC2(DD, 2) : (mode == 3 ? FJP_CC2(DD, 3) : (mode == 1 ? FJP_CC2(DD, 1) : FJP_CC2(DD, 0))))
+#define FJP_CC1(DD) (mode == 2 ? FJP_CC2(DD, 2) : (mode == 4 ? FJP_CC2(DD, 4) : (mode == 3 ? FJP_CC2(DD, 3) : (mode == 1 ? FJP_CC2(DD, 1) : FJP_CC2(DD, 0)))))
     if (cd.sparse) {
 #define FJP_SP3(TT, MM, XX) launch_fsp<TT, MM, XX>(m, a, fl, kt, grid, s)
 #define FJP_SP2(MM) (E > 768 ? FJP_SP3(4, MM, 1024) : (E > 640 ? FJP_SP3(4, MM, 768) : (fl.trees_interleaved >= 8 ? FJP_SP3(8, MM, 640) : FJP_SP3(4, MM, 640))))

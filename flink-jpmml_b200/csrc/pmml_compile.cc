@@ -734,20 +734,31 @@ struct ForestBuilder {
       b.put(&cd.blobs, words); b.put(&cd.group_off, group_off); b.put(&cd.feat, feats); b.put(&cd.tables, tables); b.put(&cd.block_off, block_off);
       return;
     }
-    // trees
-    const size_t TB = (size_t)compact_tree_bytes(depth), first_leaf = size_t(1) << depth;
+    // trees.  Ensembles that average the leaves' class distributions carry them inline (at most 8 entries over at most 16 labels)
+    const bool dist_leaves = classify && (fd.method == FM_AVG_PROB || fd.method == FM_WAVG_PROB);
+    size_t LB = 8;
+    if (dist_leaves) {
+      size_t most = 1; for (auto& lf : leaves) { most = std::max(most, lf.dist.size()); for (auto& d : lf.dist) if (d.first > 15) return; }
+      if (most > 8) return;
+      LB = 8 + 8 * most;
+    }
+    const size_t first_leaf = size_t(1) << depth, TB = (4 * first_leaf + LB * first_leaf + 8 + 15) & ~size_t(15);
     std::vector<uint32_t> blobs(roots.size() * TB / 4, 0);
     for (size_t t = 0; t < roots.size() && ok; t++) {
       uint8_t* bl = reinterpret_cast<uint8_t*>(blobs.data()) + t * TB;
       uint32_t* nd = reinterpret_cast<uint32_t*>(bl);
-      memcpy(bl + 12 * first_leaf, &weights[t], 8);
+      memcpy(bl + (4 + LB) * first_leaf, &weights[t], 8);
       if (!chain_channels.empty()) nd[0] = (uint32_t)chain_channels[t];   // modelChain: the unused heap slot 0 carries the channel
       std::function<void(int32_t, size_t)> place = [&](int32_t s, size_t h) {
         if (s < 0) {
           const TLeaf& lf = leaves[~s];
           if (h < first_leaf) { nd[h] = 0; place(s, 2 * h); place(s, 2 * h + 1); return; }   // pass-through: never "right"
-          uint8_t* dst = bl + 4 * first_leaf + 8 * (h - first_leaf);
-          if (classify) { uint64_t l = (uint64_t)(uint32_t)lf.label; memcpy(dst, &l, 8); } else memcpy(dst, &lf.value, 8);
+          uint8_t* dst = bl + 4 * first_leaf + LB * (h - first_leaf);
+          if (dist_leaves) {
+            uint32_t nib = 0, cnt = (uint32_t)lf.dist.size();
+            for (uint32_t i = 0; i < cnt; i++) { nib |= (uint32_t)lf.dist[i].first << (4 * i); memcpy(dst + 8 + 8 * i, &lf.dist[i].second, 8); }
+            memcpy(dst, &nib, 4); memcpy(dst + 4, &cnt, 4);
+          } else if (classify) { uint64_t l = (uint64_t)(uint32_t)lf.label; memcpy(dst, &l, 8); } else memcpy(dst, &lf.value, 8);
           return;
         }
         const TNode& n = nodes[s];
@@ -757,7 +768,7 @@ struct ForestBuilder {
       place(roots[t], 1);
     }
     if (!ok) return;
-    cd.enabled = 1; cd.wide = wide ? 1 : 0; cd.tree_bytes = (int)TB; cd.n_blocks = nblocks; cd.block_smem = (int)block_smem;
+    cd.enabled = 1; cd.wide = wide ? 1 : 0; cd.tree_bytes = (int)TB; cd.leaf_bytes = (int)LB; cd.n_blocks = nblocks; cd.block_smem = (int)block_smem;
     std::vector<uint32_t> no_groups{0};
     b.put(&cd.blobs, blobs); b.put(&cd.group_off, no_groups); b.put(&cd.feat, feats); b.put(&cd.tables, tables); b.put(&cd.block_off, block_off);
   }

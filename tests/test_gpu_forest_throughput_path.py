@@ -260,3 +260,16 @@ def test_model_chain_over_trees_that_keep_their_shape(engine, oracle, gen, monke
     same(compact, classic)
     assert np.array_equal(compact["probs"].view(np.int64), classic["probs"].view(np.int64))
     np.testing.assert_allclose(compact["probs"], o["probs"], rtol=1e-6)
+
+
+@pytest.mark.parametrize("n_labels,depth", [(3, 5), (4, 8), (7, 6)])
+def test_random_forest_averaging_leaf_distributions(engine, oracle, gen, monkeypatch, n_labels, depth):
+    """scikit-learn style forests: every leaf carries a ScoreDistribution, multipleModelMethod="average".  The compact
+    trees carry the distributions inline; the winner is the largest summed probability, ties to the label met first."""
+    pm, arr = gen.rf_pmml(T=30, depth=depth, F=12, n_labels=n_labels, seed=41 + n_labels, method="average")
+    m, om = engine.compile(pm), oracle.OracleModel(pm)
+    assert "method=7" in m.describe and "compact=1" in m.describe
+    X, pres, pb = gen.events(12000, 12, 42, 0.1)
+    classic, compact = score_both(engine, m, X, pb, monkeypatch)
+    same(compact, om.predict(X, pb, nthreads=8))
+    same(compact, classic)
