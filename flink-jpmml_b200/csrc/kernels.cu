@@ -1539,7 +1539,8 @@ size_t forest_slice_scratch_bytes(const DeviceModel& m, long n) {
 // ---- throughput path (forest_compact.cuh): geometry, work area, launch --------------------------------------
 // FJP_FOREST_COMPACT=0 switches the path off, =2 takes it for every batch size; FJP_FOREST_CE / FJP_FOREST_CG / FJP_FOREST_CTI
 // override the tile geometry (tuning aids, read at every launch).
-static bool plan_forest_compact(const DeviceModel& m, ForestLaunch* out) {
+// pin_e > 0: tile size to use (else FJP_FOREST_CE, else the first that fits)
+static bool plan_forest_compact_e(const DeviceModel& m, ForestLaunch* out, int pin_e) {
   query_device();
   const ForestDesc& fd = m.forest;
   const bool sparse = fd.compact.sparse != 0;   // explicit-children trees: one group of trees per ring slot
@@ -1550,7 +1551,7 @@ static bool plan_forest_compact(const DeviceModel& m, ForestLaunch* out) {
   const size_t budget = (size_t)g_smem_optin - 1024, TB = sparse ? (size_t)fd.compact.group_max_bytes : (size_t)fd.compact.tree_bytes;
   int ti = env_int("FJP_FOREST_CTI", sparse ? 4 : 8); ti = ti >= 8 ? 8 : 4;
   if (sparse) {
-    const int force_e = env_int("FJP_FOREST_CE", 0);
+    const int force_e = pin_e ? pin_e : env_int("FJP_FOREST_CE", 0);
     static const int kEs[] = {640, 768, 1024, 576, 512, 448, 384, 320, 256, 192, 128, 64};
     for (int E : kEs) {
       if (force_e && E != force_e) continue;
@@ -1565,7 +1566,7 @@ static bool plan_forest_compact(const DeviceModel& m, ForestLaunch* out) {
     }
     return false;
   }
-  const int force_e = env_int("FJP_FOREST_CE", 0), force_g = env_int("FJP_FOREST_CG", 0);
+  const int force_e = pin_e ? pin_e : env_int("FJP_FOREST_CE", 0), force_g = env_int("FJP_FOREST_CG", 0);
   const int t_round = ((fd.n_trees + ti - 1) / ti) * ti;
   static const int kE[] = {640, 768, 1024, 576, 512, 448, 384, 320, 256, 192, 128, 64};
   for (int E : kE) {
@@ -1588,6 +1589,17 @@ static bool plan_forest_compact(const DeviceModel& m, ForestLaunch* out) {
   }
   return false;
 }
+// n = batch size.  Ensembles the one-kernel walk cannot take (explicit-children trees, averaged class distributions) pick,
+// for mid-size batches, the largest tile whose tiles still cover the SMs instead of falling back to the global-memory walk.
+static bool plan_forest_compact(const DeviceModel& m, ForestLaunch* out, long n) {
+  query_device();
+  ForestLaunch probe;
+  const bool one_kernel = m.forest.method != FM_SINGLE && plan_forest_complete(m, &probe);
+  if (one_kernel || env_int("FJP_FOREST_CE", 0)) return plan_forest_compact_e(m, out, 0);
+  static const int kFit[] = {640, 512, 384, 320, 256, 192, 128, 64};
+  for (int E : kFit) if (((n + E - 1) / E >= g_num_sms || E == 64) && plan_forest_compact_e(m, out, E)) return true;
+  return false;
+}
 // tiles scored per pass over the work area: a multiple of the SM count, at most ~64 MB of keys -- written by the pre-pass
 // and read back by the walk kernel while still resident in the 126 MB L2, so they cost no HBM traffic
 static long compact_tiles_per_pass(const DeviceModel& m, const ForestLaunch& fl, long ntiles) {
@@ -1599,9 +1611,12 @@ static long compact_tiles_per_pass(const DeviceModel& m, const ForestLaunch& fl,
 size_t forest_compact_scratch_bytes(const DeviceModel& m, long n) {
   if (m.kind != MK_FOREST) return 0;
   ForestLaunch fl;
-  if (!plan_forest_compact(m, &fl)) return 0;
+  if (!plan_forest_compact(m, &fl, n)) return 0;
   const long ntiles = (n + fl.events_per_cta - 1) / fl.events_per_cta;
-  if (ntiles < g_num_sms && env_int("FJP_FOREST_COMPACT", 1) != 2) return 0;   // too few tiles to fill the chip: the one-kernel walk / the sliced latency path (2 = always, for tests)
+  ForestLaunch probe; const bool one_kernel = m.forest.method != FM_SINGLE && plan_forest_complete(m, &probe);
+  // too few tiles to fill the chip: the one-kernel walk / the sliced latency path take it (2 = always, for tests); ensembles
+  // without a one-kernel walk come here from 16 tiles on
+  if (ntiles < (one_kernel ? g_num_sms : 16) && env_int("FJP_FOREST_COMPACT", 1) != 2) return 0;
   const long pass = compact_tiles_per_pass(m, fl, ntiles);
   return (size_t)pass * ((m.F + 1) / 2) * fl.events_per_cta * 4 + (size_t)pass * fl.events_per_cta;
 }
@@ -1671,7 +1686,7 @@ cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t 
   switch (m.kind) {
     case MK_FOREST: {
       ForestLaunch fl;
-      if (slice_scratch && !a.node_ids && m.forest.method != FM_SINGLE && forest_compact_scratch_bytes(m, a.n) && plan_forest_compact(m, &fl))
+      if (slice_scratch && !a.node_ids && m.forest.method != FM_SINGLE && forest_compact_scratch_bytes(m, a.n) && plan_forest_compact(m, &fl, a.n))
         return launch_forest_compact(m, a, fl, slice_scratch, s, launches);
       // single trees go through the general path (it reports node ids in aux); ensembles through the on-chip path
       if (m.forest.method != FM_SINGLE && plan_forest_complete(m, &fl)) {

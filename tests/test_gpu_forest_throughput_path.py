@@ -273,3 +273,18 @@ def test_random_forest_averaging_leaf_distributions(engine, oracle, gen, monkeyp
     classic, compact = score_both(engine, m, X, pb, monkeypatch)
     same(compact, om.predict(X, pb, nthreads=8))
     same(compact, classic)
+
+
+@pytest.mark.parametrize("n", [1100, 3000, 20000, 47000])
+def test_mid_size_batches_of_ensembles_without_a_one_kernel_walk(engine, oracle, gen, n):
+    """Averaged-distribution forests and explicit-children trees have no one-kernel walk; from 16 tiles on their batches take
+    the throughput path unforced, with a tile small enough to spread over the SMs (host entry point, chunked)."""
+    pm, arr = gen.rf_pmml(T=20, depth=6, F=10, n_labels=3, seed=5, method="average")
+    pm2 = gen.gbt_pruned_pmml(T=20, max_depth=12, F=10, seed=6, p_leaf=0.3, dtype="double", operator="lessOrEqual")
+    X, pres, pb = gen.events(n, 10, 43, 0.1)
+    for doc in (pm, pm2):
+        m, om = engine.compile(doc), oracle.OracleModel(doc)
+        before = engine.launch_count
+        r = engine.score(m, X, pb)
+        assert engine.launch_count - before >= 2, m.describe
+        same(r, om.predict(X, pb, nthreads=8))
