@@ -59,6 +59,9 @@ configs.append(("C4 GBT double thresholds (scikit-learn / LightGBM style)", g.gb
 g.FLOAT_THRESHOLDS = True
 configs.append(("C5 RF 200x8 F=64 majorityVote", g.rf_pmml()[0], 64, 1 << 22, 0.0, {"gather": 12800, "hbm": 528}))
 configs.append(("C5 MLP 64-256-256-8", g.nn_pmml()[0], 64, 1 << 21, 0.0, {"dp_instr": 167936, "hbm": 520}))
+# beyond BASELINE.json's configs: the two other common shapes of exported forests
+configs.append(("RF 200x8 F=64 average of leaf distributions (scikit-learn style)", g.rf_pmml(method="average")[0], 64, 1 << 22, 0.0, {"gather": 12800, "hbm": 528}))
+configs.append(("GBT 300 unbalanced trees, max depth 14, F=50 (leaf-wise growth)", g.gbt_pruned_pmml(T=300, max_depth=14, F=50, seed=3, p_leaf=0.3), 50, 1 << 21, 0.10, {"hbm": 416}))
 for name, pm, F, n, pmiss, work in configs:
     if args.only and args.only not in name: continue
     m, rate, ms, ok, X, P = time_model(pm, F, n, pmiss)
