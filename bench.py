@@ -166,6 +166,7 @@ def main():
     from flink_jpmml_b200 import dist as D
     rank, world, local = D.env_rank()
     torch.cuda.set_device(local)
+    numa_node = D.bind_to_gpu_numa_node(local) if world > 1 else None   # pinned buffers next to this rank's GPU
     dev = torch.device("cuda", local)
     dist = D.init("nccl", dev)   # plumbing only: barrier + max-over-ranks of the timings; no collective while scoring
     L = capi.lib()
@@ -286,7 +287,7 @@ def main():
                 "ms_per_step": ms_dev_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
                 "data": "synthetic (torch philox on device, seed 20261110+1000*rank)",
                 "config": {"workload": WORKLOAD, "events_per_gpu_per_step": n, "l2_policy": "inputs (3.4 GB/GPU) larger than L2",
-                           "model": model.describe, "parallelism": f"events sharded over {world} GPU(s), model replicated, no collective"},
+                           "model": model.describe, "parallelism": f"events sharded over {world} GPU(s), model replicated, no collective" + (f"; rank 0 bound to NUMA node {numa_node}" if numa_node is not None else "")},
                 "e2e": {"value": e2e_value, "unit": "events/s", "h2d_bytes_per_step": ne * (F * 8 + W * 4), "d2h_bytes_per_step": ne * 9,
                         "events_per_gpu_per_step": ne, "steps": e2e_steps, "matches_device_path": e2e_match,
                         "api": "fjp_score_batch (pinned host buffers, chunked copy/compute overlap)"},

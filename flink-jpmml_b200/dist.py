@@ -53,3 +53,29 @@ def sum_over_ranks(dist, values: Sequence[float], device=None):
 def whole_job_rate(units_per_rank_per_step: int, world: int, steps: int, max_ms: float) -> float:
     """events/s of the whole job: everything all ranks processed divided by the slowest rank's time."""
     return units_per_rank_per_step * world * steps / (max_ms / 1e3)
+
+
+def bind_to_gpu_numa_node(local_rank: int):
+    """Pins this process to the CPUs of the NUMA node its GPU hangs off, before any pinned buffer is allocated: pinned
+    pages are then local to the GPU's root complex, so N ranks feeding N GPUs do not all pull through one socket
+    (the reference's deployment analogue: one subtask per GPU, S/package.scala:63-65).  Returns the node or None when
+    the topology cannot be read; never raises."""
+    import os
+    try:
+        import torch
+        p = torch.cuda.get_device_properties(local_rank)
+        bdf = f"{p.pci_domain_id:04x}:{p.pci_bus_id:02x}:{p.pci_device_id:02x}.0"
+        node = int(open(f"/sys/bus/pci/devices/{bdf}/numa_node").read())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        allowed = cpus & os.sched_getaffinity(0)
+        if allowed:
+            os.sched_setaffinity(0, allowed)
+            return node
+    except Exception:
+        pass
+    return None
