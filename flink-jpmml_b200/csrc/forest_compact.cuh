@@ -158,7 +158,7 @@ __global__ void __launch_bounds__(RK_THREADS, RK_CTAS) forest_rank_keys_kernel(c
 }
 
 // MODE: 0 sum / average, 1 weighted sum / average, 2 majority vote, 3 modelChain (per-channel sums -> RegressionTables),
-// 4 (weighted) average of the leaves' class distributions (scikit-learn style random forests).
+// 4 (weighted) average of the leaves' class distributions (scikit-learn style random forests) and weighted majority votes.
 template <int D, int TI, int MODE, int MAXT>
 __global__ void __launch_bounds__(MAXT, 1)
 forest_compact_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, const ForestLaunch fl, const KeyTiles kt) {
@@ -239,7 +239,7 @@ forest_compact_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, 
             if (MODE == 4) {
               const uint32_t la = bl[k] + off_leaf + idx[k] * LB; uint32_t nib, cnt; double ww = 1.0;
               asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(nib), "=r"(cnt) : "r"(la));
-              if (fd.method == FM_WAVG_PROB) asm volatile("ld.shared.f64 %0, [%1];" : "=d"(ww) : "r"(bl[k] + off_w));
+              if (fd.method == FM_WAVG_PROB || fd.method == FM_WVOTE) asm volatile("ld.shared.f64 %0, [%1];" : "=d"(ww) : "r"(bl[k] + off_w));
               for (uint32_t i = 0; i < cnt; i++, nib >>= 4) {   // the leaf's distribution in document order
                 const uint32_t lab = nib & 15u; double p; asm volatile("ld.shared.f64 %0, [%1];" : "=d"(p) : "r"(la + 8u + 8u * i));
                 if (!((seen_mask >> lab) & 1u)) { order |= seen << (4u * lab); seen++; seen_mask |= 1u << lab; }

@@ -1545,7 +1545,7 @@ static bool plan_forest_compact_e(const DeviceModel& m, ForestLaunch* out, int p
   const ForestDesc& fd = m.forest;
   const bool sparse = fd.compact.sparse != 0;   // explicit-children trees: one group of trees per ring slot
   if (!fd.compact.enabled || (fd.format != FOREST_COMPLETE && !sparse) || !env_int("FJP_FOREST_COMPACT", 1)) return false;
-  const bool avg_prob = fd.classify && (fd.method == FM_AVG_PROB || fd.method == FM_WAVG_PROB) && !sparse && fd.compact.leaf_bytes > 8 && m.n_labels <= 16;
+  const bool avg_prob = fd.classify && (fd.method == FM_AVG_PROB || fd.method == FM_WAVG_PROB || fd.method == FM_WVOTE) && !sparse && fd.compact.leaf_bytes > 8 && m.n_labels <= 16;
   if (fd.classify ? (fd.method != FM_VOTE && !avg_prob) : (fd.method != FM_SUM && fd.method != FM_AVERAGE && fd.method != FM_WSUM && fd.method != FM_WAVERAGE && fd.method != FM_CHAIN)) return false;
   if (fd.classify && m.n_labels > 64) return false;
   const size_t budget = (size_t)g_smem_optin - 1024, TB = sparse ? (size_t)fd.compact.group_max_bytes : (size_t)fd.compact.tree_bytes;

@@ -735,10 +735,14 @@ struct ForestBuilder {
       return;
     }
     // trees.  Ensembles that average the leaves' class distributions carry them inline (at most 8 entries over at most 16 labels)
-    const bool dist_leaves = classify && (fd.method == FM_AVG_PROB || fd.method == FM_WAVG_PROB);
+    // (a weighted majority vote is the same sum with one-entry distributions: the leaf's label with probability 1)
+    const bool wvote = classify && fd.method == FM_WVOTE;
+    const bool dist_leaves = classify && (fd.method == FM_AVG_PROB || fd.method == FM_WAVG_PROB || wvote);
     size_t LB = 8;
     if (dist_leaves) {
-      size_t most = 1; for (auto& lf : leaves) { most = std::max(most, lf.dist.size()); for (auto& d : lf.dist) if (d.first > 15) return; }
+      size_t most = 1;
+      if (wvote) { for (auto& lf : leaves) if (lf.label > 15) return; }
+      else for (auto& lf : leaves) { most = std::max(most, lf.dist.size()); for (auto& d : lf.dist) if (d.first > 15) return; }
       if (most > 8) return;
       LB = 8 + 8 * most;
     }
@@ -754,7 +758,8 @@ struct ForestBuilder {
           const TLeaf& lf = leaves[~s];
           if (h < first_leaf) { nd[h] = 0; place(s, 2 * h); place(s, 2 * h + 1); return; }   // pass-through: never "right"
           uint8_t* dst = bl + 4 * first_leaf + LB * (h - first_leaf);
-          if (dist_leaves) {
+          if (wvote) { uint32_t nib = (uint32_t)lf.label, cnt = 1; double one = 1.0; memcpy(dst, &nib, 4); memcpy(dst + 4, &cnt, 4); memcpy(dst + 8, &one, 8); }
+          else if (dist_leaves) {
             uint32_t nib = 0, cnt = (uint32_t)lf.dist.size();
             for (uint32_t i = 0; i < cnt; i++) { nib |= (uint32_t)lf.dist[i].first << (4 * i); memcpy(dst + 8 + 8 * i, &lf.dist[i].second, 8); }
             memcpy(dst, &nib, 4); memcpy(dst + 4, &cnt, 4);

@@ -197,15 +197,17 @@ def gbt_pmml(T=500, depth=8, F=100, seed=SEED_BASE + 4, dtype="double", method="
     return "\n".join(out).encode(), arrays
 
 
-def rf_pmml(T=200, depth=8, F=64, n_labels=4, seed=SEED_BASE + 5, target_dtype="string", method="majorityVote"):
+def rf_pmml(T=200, depth=8, F=64, n_labels=4, seed=SEED_BASE + 5, target_dtype="string", method="majorityVote",
+            segment_weights=False):
     """MiningModel classification over T complete TreeModels whose leaves carry labels "0".."L-1".
     method="majorityVote" (labels only) or "average" (scikit-learn style: every leaf has a ScoreDistribution of record
     counts and the ensemble averages the leaf probabilities)."""
     feat, thr, dleft, rng = forest_arrays(T, depth, F, seed)
     leaf = rng.integers(0, n_labels, size=(T, 1 << depth))
-    counts = rng.integers(0, 20, size=(T, 1 << depth, n_labels)) if method != "majorityVote" else None
+    counts = rng.integers(0, 20, size=(T, 1 << depth, n_labels)) if method in ("average", "weightedAverage") else None
     if counts is not None:
         counts[np.arange(T)[:, None], np.arange(1 << depth)[None, :], leaf] += 21      # the leaf's label has the most records
+    weights = np.round(rng.uniform(0.5, 1.5, size=T), 3) if segment_weights else None   # drawn last: earlier draws keep their values
     names = [f"x{i}" for i in range(F)]
     labels = [str(i) for i in range(n_labels)]
     out = _header()
@@ -214,7 +216,7 @@ def rf_pmml(T=200, depth=8, F=64, n_labels=4, seed=SEED_BASE + 5, target_dtype="
     out += _mining_schema(names, "y")
     out.append(f'<Segmentation multipleModelMethod="{method}">')
     for t in range(T):
-        out.append(f'<Segment id="{t + 1}"><True/>')
+        out.append(f'<Segment id="{t + 1}"' + (f' weight="{_r(weights[t])}"' if segment_weights else "") + '><True/>')
         out.append('<TreeModel functionName="classification" missingValueStrategy="defaultChild" '
                    'noTrueChildStrategy="returnNullPrediction" splitCharacteristic="binarySplit">')
         out += _mining_schema(names)

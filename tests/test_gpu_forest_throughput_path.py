@@ -288,3 +288,14 @@ def test_mid_size_batches_of_ensembles_without_a_one_kernel_walk(engine, oracle,
         r = engine.score(m, X, pb)
         assert engine.launch_count - before >= 2, m.describe
         same(r, om.predict(X, pb, nthreads=8))
+
+
+@pytest.mark.parametrize("method", ["weightedMajorityVote", "weightedAverage"])
+def test_weighted_classification_ensembles(engine, oracle, gen, monkeypatch, method):
+    pm, arr = gen.rf_pmml(T=25, depth=6, F=14, n_labels=4, seed=61, method=method, segment_weights=True)
+    m, om = engine.compile(pm), oracle.OracleModel(pm)
+    assert "compact=1" in m.describe
+    X, pres, pb = gen.events(9000, 14, 62, 0.1)
+    classic, compact = score_both(engine, m, X, pb, monkeypatch)
+    same(compact, om.predict(X, pb, nthreads=8))
+    same(compact, classic)
