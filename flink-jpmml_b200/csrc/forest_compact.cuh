@@ -304,7 +304,7 @@ forest_compact_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, 
 // shape (leaf-wise grown or heavily pruned trees, DAGs of compound predicates) instead of being padded to a common depth.
 // Groups of up to CK_SG_MAX trees stream through the 2-slot ring; a thread walks TI trees of the group at a time until all
 // of them have reached a leaf.  MODE: 0 sum / average, 1 weighted sum / average, 2 majority vote, 3 modelChain (the tree
-// header's weight slot then holds the channel).
+// header's weight slot then holds the channel), 4 (weighted) sums of leaf class distributions.
 template <int TI, int MODE, int MAXT>
 __global__ void __launch_bounds__(MAXT, 1)
 forest_sparse_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, const ForestLaunch fl, const KeyTiles kt) {
@@ -315,6 +315,8 @@ forest_sparse_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, c
   uint16_t* votes = reinterpret_cast<uint16_t*>(smem + fl.off_votes);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + fl.off_bars);
   const int T = fd.n_trees, NG = cd.n_groups; const uint32_t slot_bytes = (uint32_t)cd.group_max_bytes;
+  const uint32_t LB = MODE == 4 ? (uint32_t)cd.leaf_bytes : 8u;   // bytes per leaf record
+  double* dvotes = reinterpret_cast<double*>(smem + fl.off_votes);   // MODE 4: summed probabilities [label][event]
 
   if (tid == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); mbar_init(&bars[2], 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
   __syncthreads();
@@ -338,6 +340,8 @@ forest_sparse_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, c
     const long row = kt.row_begin + tile * E + tid;
     const bool failed = kt.fail != nullptr && kt.fail[tile * E + tid] != 0;
     if (MODE == 2) for (int l = 0; l < m.n_labels; l++) { votes[l * E + tid] = 0; votes[(m.n_labels + l) * E + tid] = 0xFFFF; }
+    if (MODE == 4) for (int l = 0; l < m.n_labels; l++) dvotes[l * E + tid] = 0.0;
+    uint32_t seen_mask = 0, order = 0;   // MODE 4: labels met so far, and the position (nibble) at which each was first met
     mbar_wait(&bars[2], tile_parity); tile_parity ^= 1u;
 
     const uint32_t kbase = smem_u32(smem) + 4u * tid, Eb = (uint32_t)E;
@@ -377,8 +381,17 @@ forest_sparse_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, c
 #pragma unroll
         for (int k = 0; k < TI; k++) {
           if (t + k < nt) {
-            const uint32_t la = tb[k] + 16u + (nn[k] + (code[k] & 0x7FFFu)) * 8u;
-            if (MODE != 2) {
+            const uint32_t la = tb[k] + 16u + nn[k] * 8u + (code[k] & 0x7FFFu) * LB;
+            if (MODE == 4) {
+              uint32_t nib, cnt; double ww = 1.0;
+              asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(nib), "=r"(cnt) : "r"(la));
+              if (fd.method == FM_WAVG_PROB || fd.method == FM_WVOTE) asm volatile("ld.shared.f64 %0, [%1];" : "=d"(ww) : "r"(tb[k] + 8u));
+              for (uint32_t i = 0; i < cnt; i++, nib >>= 4) {   // the leaf's distribution in document order
+                const uint32_t lab = nib & 15u; double p; asm volatile("ld.shared.f64 %0, [%1];" : "=d"(p) : "r"(la + 8u + 8u * i));
+                if (!((seen_mask >> lab) & 1u)) { order |= seen << (4u * lab); seen++; seen_mask |= 1u << lab; }
+                dvotes[lab * E + tid] += ww * p;
+              }
+            } else if (MODE != 2) {
               double lv; asm volatile("ld.shared.f64 %0, [%1];" : "=d"(lv) : "r"(la));
               if (MODE == 1) { double w; asm volatile("ld.shared.f64 %0, [%1];" : "=d"(w) : "r"(tb[k] + 8u)); sum += w * lv; wsum += w; }
               else if (MODE == 3) {
@@ -400,7 +413,17 @@ forest_sparse_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, c
     }
     if (row < a.n) {
       if (failed) write_out(a, row, 0, ST_PREP, -1);
-      else if (MODE == 3) {
+      else if (MODE == 4) {
+        int best = -1; double bv = 0; uint32_t bo = 0;
+        for (int l = 0; l < m.n_labels; l++) {
+          if (!((seen_mask >> l) & 1u)) continue;
+          const double v = dvotes[l * E + tid]; const uint32_t o = (order >> (4 * l)) & 15u;
+          if (best < 0) { best = l; bv = v; bo = o; continue; }
+          const int c = java_cmp(v, bv);
+          if (c > 0 || (c == 0 && o < bo)) { best = l; bv = v; bo = o; }
+        }
+        write_label(m, a, row, best, best);
+      } else if (MODE == 3) {
         chv[cur_ch * E + tid] = channel_value(fd.channels[cur_ch], sum);
         chain_finish(m, a, row, [&](int c) { return chv[c * E + tid]; });
       } else if (MODE != 2) {

@@ -1545,7 +1545,7 @@ static bool plan_forest_compact_e(const DeviceModel& m, ForestLaunch* out, int p
   const ForestDesc& fd = m.forest;
   const bool sparse = fd.compact.sparse != 0;   // explicit-children trees: one group of trees per ring slot
   if (!fd.compact.enabled || (fd.format != FOREST_COMPLETE && !sparse) || !env_int("FJP_FOREST_COMPACT", 1)) return false;
-  const bool avg_prob = fd.classify && (fd.method == FM_AVG_PROB || fd.method == FM_WAVG_PROB || fd.method == FM_WVOTE) && !sparse && fd.compact.leaf_bytes > 8 && m.n_labels <= 16;
+  const bool avg_prob = fd.classify && (fd.method == FM_AVG_PROB || fd.method == FM_WAVG_PROB || fd.method == FM_WVOTE) && fd.compact.leaf_bytes > 8 && m.n_labels <= 16;
   if (fd.classify ? (fd.method != FM_VOTE && !avg_prob) : (fd.method != FM_SUM && fd.method != FM_AVERAGE && fd.method != FM_WSUM && fd.method != FM_WAVERAGE && fd.method != FM_CHAIN)) return false;
   if (fd.classify && m.n_labels > 64) return false;
   const size_t budget = (size_t)g_smem_optin - 1024, TB = sparse ? (size_t)fd.compact.group_max_bytes : (size_t)fd.compact.tree_bytes;
@@ -1557,7 +1557,7 @@ static bool plan_forest_compact_e(const DeviceModel& m, ForestLaunch* out, int p
       if (force_e && E != force_e) continue;
       if (E == 1024) ti = 4;
       size_t keys = ((size_t)((m.F + 1) / 2) * E * 4 + 127) & ~size_t(127);
-      size_t votes = fd.classify ? (size_t)2 * m.n_labels * E * 2 : (fd.method == FM_CHAIN ? (size_t)fd.n_channels * E * 8 : 0);
+      size_t votes = avg_prob ? (size_t)m.n_labels * E * 8 : (fd.classify ? (size_t)2 * m.n_labels * E * 2 : (fd.method == FM_CHAIN ? (size_t)fd.n_channels * E * 8 : 0));
       size_t off = keys + 2 * TB; if (off + votes + 64 + 256 > budget) continue;
       ForestLaunch fl{}; fl.events_per_cta = E; fl.trees_per_stage = 1; fl.trees_interleaved = ti;
       fl.off_ring = (uint32_t)keys; off = (off + 15) & ~size_t(15); fl.off_votes = (uint32_t)off; off += votes; off = (off + 15) & ~size_t(15);
@@ -1665,7 +1665,7 @@ static cudaError_t launch_forest_compact(const DeviceModel& m, const BatchArgs& 
     if (cd.sparse) {
 #define FJP_SP3(TT, MM, XX) launch_fsp<TT, MM, XX>(m, a, fl, kt, grid, s)
 #define FJP_SP2(MM) (E > 768 ? FJP_SP3(4, MM, 1024) : (E > 640 ? FJP_SP3(4, MM, 768) : (fl.trees_interleaved >= 8 ? FJP_SP3(8, MM, 640) : FJP_SP3(4, MM, 640))))
-      e = mode == 2 ? FJP_SP2(2) : (mode == 3 ? FJP_SP2(3) : (mode == 1 ? FJP_SP2(1) : FJP_SP2(0)));
+      e = mode == 2 ? FJP_SP2(2) : (mode == 4 ? FJP_SP2(4) : (mode == 3 ? FJP_SP2(3) : (mode == 1 ? FJP_SP2(1) : FJP_SP2(0))));
 #undef FJP_SP2
 #undef FJP_SP3
     } else

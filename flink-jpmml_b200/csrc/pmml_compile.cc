@@ -680,6 +680,26 @@ struct ForestBuilder {
       if (feat > 255) ok = false;
       return (feat << 1) | (a << 15) | ((y & 0xFFFFu) << 16);
     };
+    // Ensembles that average the leaves' class distributions carry them inline (at most 8 entries over at most 16 labels)
+    // (a weighted majority vote is the same sum with one-entry distributions: the leaf's label with probability 1)
+    const bool wvote = classify && fd.method == FM_WVOTE;
+    const bool dist_leaves = classify && (fd.method == FM_AVG_PROB || fd.method == FM_WAVG_PROB || wvote);
+    size_t LB = 8;
+    if (dist_leaves) {
+      size_t most = 1;
+      if (wvote) { for (auto& lf : leaves) if (lf.label > 15) return; }
+      else for (auto& lf : leaves) { most = std::max(most, lf.dist.size()); for (auto& d : lf.dist) if (d.first > 15) return; }
+      if (most > 8) return;
+      LB = 8 + 8 * most;
+    }
+    auto put_leaf = [&](uint8_t* dst, const TLeaf& lf) {
+      if (wvote) { uint32_t nib = (uint32_t)lf.label, cnt = 1; double one = 1.0; memcpy(dst, &nib, 4); memcpy(dst + 4, &cnt, 4); memcpy(dst + 8, &one, 8); }
+      else if (dist_leaves) {
+        uint32_t nib = 0, cnt = (uint32_t)lf.dist.size();
+        for (uint32_t i = 0; i < cnt; i++) { nib |= (uint32_t)lf.dist[i].first << (4 * i); memcpy(dst + 8 + 8 * i, &lf.dist[i].second, 8); }
+        memcpy(dst, &nib, 4); memcpy(dst + 4, &cnt, 4);
+      } else if (classify) { uint64_t l = (uint64_t)(uint32_t)lf.label; memcpy(dst, &l, 8); } else memcpy(dst, &lf.value, 8);
+    };
     if (sparse) {
       // explicit children: every node sends a missing value down one of its two branches, no null prediction reachable
       std::vector<uint8_t> out; std::vector<uint32_t> group_off{0}; size_t group_max = 0;
@@ -708,7 +728,7 @@ struct ForestBuilder {
         if (!ok) break;
         auto code = [&](int32_t s) -> uint32_t { return s < 0 ? 0x8000u | (uint32_t)leaf_local[~s] : (uint32_t)local[s]; };
         const size_t n_slots = std::max<size_t>(order.size(), 1);   // a bare leaf still gets one (all-zero, never visited for real) node:
-        std::vector<uint8_t> tb(16 + 8 * (n_slots + lorder.size()), 0);   // the walk re-reads node 0 for chains that are already done
+        std::vector<uint8_t> tb(16 + 8 * n_slots + LB * lorder.size(), 0);   // the walk re-reads node 0 for chains that are already done
         uint32_t nn = (uint32_t)n_slots, rc = code(roots[t]); memcpy(tb.data(), &nn, 4); memcpy(tb.data() + 4, &rc, 4); memcpy(tb.data() + 8, &weights[t], 8);
         if (!chain_channels.empty()) { uint64_t ch = (uint64_t)(uint32_t)chain_channels[t]; memcpy(tb.data() + 8, &ch, 8); }   // modelChain: channel instead of weight
         for (size_t i = 0; i < order.size(); i++) {
@@ -717,12 +737,11 @@ struct ForestBuilder {
           memcpy(tb.data() + 16 + 8 * i, &w, 8);
         }
         for (size_t i = 0; i < lorder.size(); i++) {
-          const TLeaf& lf = leaves[lorder[i]]; uint8_t* dst = tb.data() + 16 + 8 * (n_slots + i);
-          if (classify) { uint64_t l = (uint64_t)(uint32_t)lf.label; memcpy(dst, &l, 8); } else memcpy(dst, &lf.value, 8);
+          put_leaf(tb.data() + 16 + 8 * n_slots + LB * i, leaves[lorder[i]]);
         }
         for (int32_t s : order) local[s] = -1;
         for (int32_t l : lorder) leaf_local[l] = -1;
-        if (tb.size() > 48 * 1024) { ok = false; break; }                       // one tree must fit a ring slot
+        if (tb.size() > 100 * 1024) { ok = false; break; }                      // one tree must fit a ring slot (the launch plan checks the rest)
         if (in_grp == CK_SG_MAX || grp.size() + tb.size() > 40 * 1024) close_group();   // a ring slot holds up to 40 KB of trees
         dir.push_back((uint32_t)grp.size()); grp.insert(grp.end(), tb.begin(), tb.end()); in_grp++;
       }
@@ -730,22 +749,11 @@ struct ForestBuilder {
       if (!ok) return;
       std::vector<uint32_t> words((out.size() + 3) / 4, 0); memcpy(words.data(), out.data(), out.size());
       cd.enabled = 1; cd.wide = wide ? 1 : 0; cd.sparse = 1; cd.n_groups = (int)group_off.size() - 1; cd.group_max_bytes = (int)group_max;
-      cd.tree_bytes = 0; cd.n_blocks = nblocks; cd.block_smem = (int)block_smem;
+      cd.tree_bytes = 0; cd.leaf_bytes = (int)LB; cd.n_blocks = nblocks; cd.block_smem = (int)block_smem;
       b.put(&cd.blobs, words); b.put(&cd.group_off, group_off); b.put(&cd.feat, feats); b.put(&cd.tables, tables); b.put(&cd.block_off, block_off);
       return;
     }
-    // trees.  Ensembles that average the leaves' class distributions carry them inline (at most 8 entries over at most 16 labels)
-    // (a weighted majority vote is the same sum with one-entry distributions: the leaf's label with probability 1)
-    const bool wvote = classify && fd.method == FM_WVOTE;
-    const bool dist_leaves = classify && (fd.method == FM_AVG_PROB || fd.method == FM_WAVG_PROB || wvote);
-    size_t LB = 8;
-    if (dist_leaves) {
-      size_t most = 1;
-      if (wvote) { for (auto& lf : leaves) if (lf.label > 15) return; }
-      else for (auto& lf : leaves) { most = std::max(most, lf.dist.size()); for (auto& d : lf.dist) if (d.first > 15) return; }
-      if (most > 8) return;
-      LB = 8 + 8 * most;
-    }
+    // trees
     const size_t first_leaf = size_t(1) << depth, TB = (4 * first_leaf + LB * first_leaf + 8 + 15) & ~size_t(15);
     std::vector<uint32_t> blobs(roots.size() * TB / 4, 0);
     for (size_t t = 0; t < roots.size() && ok; t++) {
@@ -758,12 +766,7 @@ struct ForestBuilder {
           const TLeaf& lf = leaves[~s];
           if (h < first_leaf) { nd[h] = 0; place(s, 2 * h); place(s, 2 * h + 1); return; }   // pass-through: never "right"
           uint8_t* dst = bl + 4 * first_leaf + LB * (h - first_leaf);
-          if (wvote) { uint32_t nib = (uint32_t)lf.label, cnt = 1; double one = 1.0; memcpy(dst, &nib, 4); memcpy(dst + 4, &cnt, 4); memcpy(dst + 8, &one, 8); }
-          else if (dist_leaves) {
-            uint32_t nib = 0, cnt = (uint32_t)lf.dist.size();
-            for (uint32_t i = 0; i < cnt; i++) { nib |= (uint32_t)lf.dist[i].first << (4 * i); memcpy(dst + 8 + 8 * i, &lf.dist[i].second, 8); }
-            memcpy(dst, &nib, 4); memcpy(dst + 4, &cnt, 4);
-          } else if (classify) { uint64_t l = (uint64_t)(uint32_t)lf.label; memcpy(dst, &l, 8); } else memcpy(dst, &lf.value, 8);
+          put_leaf(dst, lf);
           return;
         }
         const TNode& n = nodes[s];

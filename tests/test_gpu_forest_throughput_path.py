@@ -299,3 +299,14 @@ def test_weighted_classification_ensembles(engine, oracle, gen, monkeypatch, met
     classic, compact = score_both(engine, m, X, pb, monkeypatch)
     same(compact, om.predict(X, pb, nthreads=8))
     same(compact, classic)
+
+
+@pytest.mark.parametrize("method,weights", [("average", False), ("weightedMajorityVote", True)])
+def test_distribution_sums_over_trees_that_keep_their_shape(engine, oracle, gen, monkeypatch, method, weights):
+    pm, arr = gen.rf_pmml(T=6, depth=11, F=12, n_labels=3, seed=83, method=method, segment_weights=weights)   # depth 11: explicit children
+    m, om = engine.compile(pm), oracle.OracleModel(pm)
+    assert "format=general" in m.describe and "sparse=1" in m.describe, m.describe
+    X, pres, pb = gen.events(8000, 12, 84, 0.1)
+    classic, compact = score_both(engine, m, X, pb, monkeypatch)
+    same(compact, om.predict(X, pb, nthreads=8))
+    same(compact, classic)
