@@ -200,7 +200,7 @@ forest_compact_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, 
     const bool failed = kt.fail != nullptr && kt.fail[tile * E + tid] != 0;
     if (MODE == 2) for (int l = 0; l < m.n_labels; l++) { votes[l * E + tid] = 0; votes[(m.n_labels + l) * E + tid] = 0xFFFF; }
     if (MODE == 4) for (int l = 0; l < m.n_labels; l++) dvotes[l * E + tid] = 0.0;
-    uint32_t seen_mask = 0, order = 0;   // MODE 4: labels met so far, and the position (nibble) at which each was first met
+    uint32_t seen_mask = 0; uint64_t order = 0;   // MODE 4: labels met so far, and the position (nibble) at which each was first met
     mbar_wait(&bars[2], tile_parity); tile_parity ^= 1u;
 
     const uint32_t kbase = smem_u32(smem) + 4u * tid;    // byte address of this event's column of key-pair words
@@ -237,12 +237,13 @@ forest_compact_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, 
         for (int k = 0; k < TI; k++) {
           if (t + k < nt) {
             if (MODE == 4) {
-              const uint32_t la = bl[k] + off_leaf + idx[k] * LB; uint32_t nib, cnt; double ww = 1.0;
-              asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(nib), "=r"(cnt) : "r"(la));
+              const uint32_t la = bl[k] + off_leaf + idx[k] * LB; uint32_t hlo, hhi; double ww = 1.0;
+              asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(hlo), "=r"(hhi) : "r"(la));
+              uint64_t nib = ((uint64_t)hhi << 32) | hlo; const uint32_t cnt = hhi >> 28;
               if (fd.method == FM_WAVG_PROB || fd.method == FM_WVOTE) asm volatile("ld.shared.f64 %0, [%1];" : "=d"(ww) : "r"(bl[k] + off_w));
               for (uint32_t i = 0; i < cnt; i++, nib >>= 4) {   // the leaf's distribution in document order
-                const uint32_t lab = nib & 15u; double p; asm volatile("ld.shared.f64 %0, [%1];" : "=d"(p) : "r"(la + 8u + 8u * i));
-                if (!((seen_mask >> lab) & 1u)) { order |= seen << (4u * lab); seen++; seen_mask |= 1u << lab; }
+                const uint32_t lab = (uint32_t)nib & 15u; double p; asm volatile("ld.shared.f64 %0, [%1];" : "=d"(p) : "r"(la + 8u + 8u * i));
+                if (!((seen_mask >> lab) & 1u)) { order |= (uint64_t)seen << (4u * lab); seen++; seen_mask |= 1u << lab; }
                 dvotes[lab * E + tid] += ww * p;
               }
             } else if (MODE != 2) {
@@ -273,7 +274,7 @@ forest_compact_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, 
         int best = -1; double bv = 0; uint32_t bo = 0;
         for (int l = 0; l < m.n_labels; l++) {
           if (!((seen_mask >> l) & 1u)) continue;
-          const double v = dvotes[l * E + tid]; const uint32_t o = (order >> (4 * l)) & 15u;
+          const double v = dvotes[l * E + tid]; const uint32_t o = (uint32_t)(order >> (4 * l)) & 15u;
           if (best < 0) { best = l; bv = v; bo = o; continue; }
           const int c = java_cmp(v, bv);
           if (c > 0 || (c == 0 && o < bo)) { best = l; bv = v; bo = o; }
@@ -341,7 +342,7 @@ forest_sparse_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, c
     const bool failed = kt.fail != nullptr && kt.fail[tile * E + tid] != 0;
     if (MODE == 2) for (int l = 0; l < m.n_labels; l++) { votes[l * E + tid] = 0; votes[(m.n_labels + l) * E + tid] = 0xFFFF; }
     if (MODE == 4) for (int l = 0; l < m.n_labels; l++) dvotes[l * E + tid] = 0.0;
-    uint32_t seen_mask = 0, order = 0;   // MODE 4: labels met so far, and the position (nibble) at which each was first met
+    uint32_t seen_mask = 0; uint64_t order = 0;   // MODE 4: labels met so far, and the position (nibble) at which each was first met
     mbar_wait(&bars[2], tile_parity); tile_parity ^= 1u;
 
     const uint32_t kbase = smem_u32(smem) + 4u * tid, Eb = (uint32_t)E;
@@ -383,12 +384,13 @@ forest_sparse_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, c
           if (t + k < nt) {
             const uint32_t la = tb[k] + 16u + nn[k] * 8u + (code[k] & 0x7FFFu) * LB;
             if (MODE == 4) {
-              uint32_t nib, cnt; double ww = 1.0;
-              asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(nib), "=r"(cnt) : "r"(la));
+              uint32_t hlo, hhi; double ww = 1.0;
+              asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(hlo), "=r"(hhi) : "r"(la));
+              uint64_t nib = ((uint64_t)hhi << 32) | hlo; const uint32_t cnt = hhi >> 28;
               if (fd.method == FM_WAVG_PROB || fd.method == FM_WVOTE) asm volatile("ld.shared.f64 %0, [%1];" : "=d"(ww) : "r"(tb[k] + 8u));
               for (uint32_t i = 0; i < cnt; i++, nib >>= 4) {   // the leaf's distribution in document order
-                const uint32_t lab = nib & 15u; double p; asm volatile("ld.shared.f64 %0, [%1];" : "=d"(p) : "r"(la + 8u + 8u * i));
-                if (!((seen_mask >> lab) & 1u)) { order |= seen << (4u * lab); seen++; seen_mask |= 1u << lab; }
+                const uint32_t lab = (uint32_t)nib & 15u; double p; asm volatile("ld.shared.f64 %0, [%1];" : "=d"(p) : "r"(la + 8u + 8u * i));
+                if (!((seen_mask >> lab) & 1u)) { order |= (uint64_t)seen << (4u * lab); seen++; seen_mask |= 1u << lab; }
                 dvotes[lab * E + tid] += ww * p;
               }
             } else if (MODE != 2) {
@@ -417,7 +419,7 @@ forest_sparse_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, c
         int best = -1; double bv = 0; uint32_t bo = 0;
         for (int l = 0; l < m.n_labels; l++) {
           if (!((seen_mask >> l) & 1u)) continue;
-          const double v = dvotes[l * E + tid]; const uint32_t o = (order >> (4 * l)) & 15u;
+          const double v = dvotes[l * E + tid]; const uint32_t o = (uint32_t)(order >> (4 * l)) & 15u;
           if (best < 0) { best = l; bv = v; bo = o; continue; }
           const int c = java_cmp(v, bv);
           if (c > 0 || (c == 0 && o < bo)) { best = l; bv = v; bo = o; }

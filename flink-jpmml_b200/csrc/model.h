@@ -90,7 +90,7 @@ struct CompactDesc {
   int enabled, wide, tree_bytes, n_blocks, block_smem;   // wide: 64-bit threshold images (thresholds that are not floats); block_smem: largest table area of one feature block
   int sparse, n_groups, group_max_bytes;                 // sparse form: blobs = the groups back to back
   int leaf_bytes;              // complete form: 8, or 8 + 8 * (most entries of a leaf's class distribution) for ensembles that average them:
-                               // {u32 label nibbles in document order, u32 count, double probability[...]}
+                               // {u64: label nibbles in document order, entry count in the top nibble; double probability[...]}
   const uint32_t* group_off;   // n_groups + 1 byte offsets into blobs (multiples of 16)
   const uint32_t* blobs;       // n_trees x tree_bytes (complete form) / the groups (sparse form)
   const CkFeat* feat;          // F

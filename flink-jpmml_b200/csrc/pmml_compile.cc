@@ -680,7 +680,7 @@ struct ForestBuilder {
       if (feat > 255) ok = false;
       return (feat << 1) | (a << 15) | ((y & 0xFFFFu) << 16);
     };
-    // Ensembles that average the leaves' class distributions carry them inline (at most 8 entries over at most 16 labels)
+    // Ensembles that average the leaves' class distributions carry them inline (at most 15 entries over at most 16 labels)
     // (a weighted majority vote is the same sum with one-entry distributions: the leaf's label with probability 1)
     const bool wvote = classify && fd.method == FM_WVOTE;
     const bool dist_leaves = classify && (fd.method == FM_AVG_PROB || fd.method == FM_WAVG_PROB || wvote);
@@ -689,15 +689,16 @@ struct ForestBuilder {
       size_t most = 1;
       if (wvote) { for (auto& lf : leaves) if (lf.label > 15) return; }
       else for (auto& lf : leaves) { most = std::max(most, lf.dist.size()); for (auto& d : lf.dist) if (d.first > 15) return; }
-      if (most > 8) return;
+      if (most > 15) return;
       LB = 8 + 8 * most;
     }
     auto put_leaf = [&](uint8_t* dst, const TLeaf& lf) {
-      if (wvote) { uint32_t nib = (uint32_t)lf.label, cnt = 1; double one = 1.0; memcpy(dst, &nib, 4); memcpy(dst + 4, &cnt, 4); memcpy(dst + 8, &one, 8); }
+      // header: label nibbles in document order (up to 15), the entry count in the top nibble
+      if (wvote) { uint64_t hdr = (uint64_t)(uint32_t)lf.label | (1ull << 60); double one = 1.0; memcpy(dst, &hdr, 8); memcpy(dst + 8, &one, 8); }
       else if (dist_leaves) {
-        uint32_t nib = 0, cnt = (uint32_t)lf.dist.size();
-        for (uint32_t i = 0; i < cnt; i++) { nib |= (uint32_t)lf.dist[i].first << (4 * i); memcpy(dst + 8 + 8 * i, &lf.dist[i].second, 8); }
-        memcpy(dst, &nib, 4); memcpy(dst + 4, &cnt, 4);
+        uint64_t hdr = (uint64_t)lf.dist.size() << 60;
+        for (size_t i = 0; i < lf.dist.size(); i++) { hdr |= (uint64_t)(uint32_t)lf.dist[i].first << (4 * i); memcpy(dst + 8 + 8 * i, &lf.dist[i].second, 8); }
+        memcpy(dst, &hdr, 8);
       } else if (classify) { uint64_t l = (uint64_t)(uint32_t)lf.label; memcpy(dst, &l, 8); } else memcpy(dst, &lf.value, 8);
     };
     if (sparse) {

@@ -262,7 +262,7 @@ def test_model_chain_over_trees_that_keep_their_shape(engine, oracle, gen, monke
     np.testing.assert_allclose(compact["probs"], o["probs"], rtol=1e-6)
 
 
-@pytest.mark.parametrize("n_labels,depth", [(3, 5), (4, 8), (7, 6)])
+@pytest.mark.parametrize("n_labels,depth", [(3, 5), (4, 8), (7, 6), (13, 5)])
 def test_random_forest_averaging_leaf_distributions(engine, oracle, gen, monkeypatch, n_labels, depth):
     """scikit-learn style forests: every leaf carries a ScoreDistribution, multipleModelMethod="average".  The compact
     trees carry the distributions inline; the winner is the largest summed probability, ties to the label met first."""
