@@ -93,34 +93,35 @@ __device__ __forceinline__ void ck_rank_keys_wide(uint32_t th_addr, uint32_t tab
 
 // grid = (x, feature blocks); a CTA keeps the tables of its CK_FB features in shared memory and runs over the tiles
 // x, x + gridDim.x, ...  Element i of a tile is (event, feature) = (i / 8, i % 8): a warp reads four 64-byte runs of X.
-// No lane is ever predicated off: the idle lanes of a short last block redo feature f0 (their staging rows are not written
-// out), rows past the end of the batch redo the last row (the walk kernel never reports them).
-// Shared memory: tables | staging tile u16 [8][OS]
+// Loads are never predicated off: the idle lanes of a short last block redo feature f0 (and store nothing), rows past the end
+// of the batch redo the last row (the walk kernel never reports them).  Keys go straight to their place in the tile image,
+// word[f / 2][event] half f & 1, as 2-byte stores that the L2 merges (a shared-memory staging tile with coalesced write-out
+// cost two barriers per tile and was 15 % slower).
+// Shared memory: the feature block's tables.
 template <bool SIMPLE, bool WIDE>
 __global__ void __launch_bounds__(RK_THREADS, RK_CTAS) forest_rank_keys_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, const KeyTiles kt) {
   extern __shared__ __align__(16) uint8_t rk_smem[];
   const ForestDesc& fd = m.forest; const CompactDesc& cd = fd.compact;
   const int F = m.F, E = kt.E, tid = threadIdx.x;
   const int f0 = blockIdx.y * CK_FB, nf = min(CK_FB, F - f0);
-  const int OS = ((E + 63) & ~63) + 8;   // row stride of the staging tile (u16): the 8 feature rows fall into different banks
   const int total = E * CK_FB;
-  uint16_t* out = reinterpret_cast<uint16_t*>(rk_smem + cd.block_smem);
   {
     const uint32_t t0 = cd.block_off[blockIdx.y], tbytes = cd.block_off[blockIdx.y + 1] - t0;
     const uint4* src = reinterpret_cast<const uint4*>(cd.tables + t0); uint4* dst = reinterpret_cast<uint4*>(rk_smem);
     for (uint32_t i = tid; i < tbytes / 16; i += RK_THREADS) dst[i] = __ldg(src + i);
   }
   const int j = tid & (CK_FB - 1), f = j < nf ? f0 + j : f0;   // this thread's feature never changes (RK_THREADS is a multiple of CK_FB)
+  const bool owner = j < nf;
   const CkFeat cf = cd.feat[f]; const int mode = fd.feat_mode[f]; const bool float_field = m.prep[f].dtype == DT_FLOAT;
   const uint32_t th_addr = smem_u32(rk_smem) + cf.thr_off, tab_addr = smem_u32(rk_smem) + cf.tab_off;
   const uint32_t pbit = 1u << (f & 31); const int pword = f0 >> 5;   // a block's 8 features share one present word
-  uint16_t* const out_row = out + j * OS;
   __syncthreads();
   for (long tile = blockIdx.x; tile < kt.ntiles; tile += gridDim.x) {
     const long row0 = kt.row_begin + tile * E;
     const int last = (int)min((long)E, a.n - row0) - 1;          // last live row of this tile (>= 0)
     const double* xt = a.X + row0 * (long)F + f;
     const uint32_t* pt = a.present ? a.present + row0 * (long)a.present_stride + pword : nullptr;
+    uint16_t* const gout = reinterpret_cast<uint16_t*>(kt.keys + (size_t)tile * (kt.tile_bytes / 4) + (size_t)(f >> 1) * E) + (f & 1);
     for (int i0 = tid; i0 < total; i0 += RK_THREADS * RK_BATCH) {
       double val[RK_BATCH]; uint32_t pw[RK_BATCH], key[RK_BATCH]; int st[RK_BATCH], e[RK_BATCH];
 #pragma unroll
@@ -141,19 +142,9 @@ __global__ void __launch_bounds__(RK_THREADS, RK_CTAS) forest_rank_keys_kernel(c
       for (int k = 0; k < RK_BATCH; k++) {
         const int ee = min(i0 + k * RK_THREADS, total - 1) >> 3;      // the unclamped event slot of the tile
         if (!SIMPLE && st[k] == 2 && ee <= last) kt.fail[tile * E + ee] = 1;
-        out_row[ee] = (uint16_t)(st[k] == 0 ? key[k] : 0x8000u);   // 0x8000 = missing
+        if (owner) gout[2 * ee] = (uint16_t)(st[k] == 0 ? key[k] : 0x8000u);   // 0x8000 = missing
       }
     }
-    __syncthreads();
-    uint32_t* dst = kt.keys + (size_t)tile * (kt.tile_bytes / 4) + (size_t)(f0 >> 1) * E;   // f0 is even
-    const int q2 = E >> 1, npairs = (nf + 1) >> 1;   // a thread packs two events of one feature pair per 8-byte store
-    for (int i = tid; i < npairs * q2; i += RK_THREADS) {
-      const int p = i / q2, q = i - p * q2;
-      const uint32_t lo = *reinterpret_cast<const uint32_t*>(out + (2 * p) * OS + 2 * q);                          // feature 2p,   events 2q, 2q+1
-      const uint32_t hi = 2 * p + 1 < nf ? *reinterpret_cast<const uint32_t*>(out + (2 * p + 1) * OS + 2 * q) : 0u;  // feature 2p+1
-      *reinterpret_cast<uint2*>(dst + (size_t)p * E + 2 * q) = make_uint2(__byte_perm(lo, hi, 0x5410), __byte_perm(lo, hi, 0x7632));
-    }
-    __syncthreads();   // the staging tile is reused by the next tile
   }
 }
 

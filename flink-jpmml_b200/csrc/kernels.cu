@@ -1641,7 +1641,7 @@ static cudaError_t launch_forest_compact(const DeviceModel& m, const BatchArgs& 
   const int E = fl.events_per_cta; const long ntiles = (a.n + E - 1) / E, pass = compact_tiles_per_pass(m, fl, ntiles);
   KeyTiles kt{}; kt.keys = static_cast<uint32_t*>(scratch); kt.E = E; kt.tile_bytes = (uint32_t)((size_t)((m.F + 1) / 2) * E * 4);
   uint8_t* fail = static_cast<uint8_t*>(scratch) + (size_t)pass * kt.tile_bytes;
-  const int OS = ((E + 63) & ~63) + 8; const size_t rk_smem = (size_t)cd.block_smem + (size_t)CK_FB * OS * 2;
+  const size_t rk_smem = (size_t)cd.block_smem;   // the feature block's tables
   const int mode = m.forest.classify ? (m.forest.method == FM_VOTE ? 2 : 4) : (m.forest.method == FM_CHAIN ? 3 : ((m.forest.method == FM_WSUM || m.forest.method == FM_WAVERAGE) ? 1 : 0));
   const int d = m.forest.depth;
   for (long t0 = 0; t0 < ntiles; t0 += pass) {
