@@ -1733,8 +1733,11 @@ cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t 
           int chunk = (int)(room / ((size_t)(pl.events + 1) * 8 + pl.events + 4)); if (chunk > nf) chunk = nf; if (chunk > 128) chunk = 128;
           {  // two events per thread when the rows are plain doubles and the cluster groups fit 16 warps
             const bool plain = a.replace == nullptr && m.prep_identity && (a.present == nullptr || (m.cluster.slots_identity && a.present_stride <= 4));
-            if (plain && pl.groups <= 16 && 16 % pl.groups == 0 && env_int("FJP_CLUSTER_PAIR", 1)) {
-              ClusterPairPlan pp{}; pp.groups = pl.groups; pp.kp = pl.kp; pp.event_blocks = 16 / pl.groups; pp.events = 64 * pp.event_blocks;
+            if (plain && pl.groups <= 16 && env_int("FJP_CLUSTER_PAIR", 1)) {
+              // the group count is rounded up to a divisor of 16 (padding clusters never win): 3 groups run as 4, 5..7 as 8
+              ClusterPairPlan pp{}; pp.groups = 1; while (pp.groups < pl.groups) pp.groups *= 2;
+              pp.kp = pp.groups * CK_TC; pp.event_blocks = 16 / pp.groups; pp.events = 64 * pp.event_blocks;
+              const size_t cent = ((size_t)nf * pp.kp * 8 + 127) & ~size_t(127);   // shadows the one-event geometry's figure
               const size_t fixed = cent + (size_t)2 * pp.events * 16 + (size_t)pp.groups * pp.events * 12 + 1024;
               for (pp.nchunks = 1; pp.nchunks <= 8; pp.nchunks++) {   // fewest chunks (of a multiple of 32 fields) whose two buffers fit
                 pp.chunk = pp.nchunks == 1 ? nf : (((nf + pp.nchunks - 1) / pp.nchunks + 31) / 32) * 32;

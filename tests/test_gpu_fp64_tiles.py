@@ -16,7 +16,7 @@ def check(r, o, probs=False):
         np.testing.assert_allclose(r["probs"][ok], o["probs"][ok], rtol=1e-6)
 
 
-@pytest.mark.parametrize("k,F", [(32, 150), (16, 40), (64, 128), (8, 70), (24, 33)])
+@pytest.mark.parametrize("k,F", [(32, 150), (16, 40), (64, 128), (8, 70), (24, 33), (44, 64), (3, 9), (100, 20)])
 def test_kmeans_shapes_dense_missing_and_replace(engine, oracle, gen, k, F):
     rng = np.random.default_rng(k * 1000 + F)
     pm = gen.kmeans_pmml(rng.standard_normal((k, F)))
