@@ -272,7 +272,7 @@ def main():
         roof = {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": achieved / pk["hbm_gbs"],
                 "traffic": (micro["forest_kernel_dram_bytes_per_event"] * n) if micro.get("forest_kernel_dram_bytes_per_event") else None,
                 "traffic_source": "ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum of the pre-pass and walk launches per event x events per step (profiles/ncu_forest_r01.txt; ncu flushes L2 between the two launches, so the 205 B/event of key tiles count as DRAM traffic there and stay in L2 in a real run)", "peak_source": pk["source"],
-                "kernel": ("forest_rank_keys_kernel<true> + forest_compact_kernel<8,8,0,640> (throughput path: %d launches per step, timed together)" % (launches // max(1, args.steps)))
+                "kernel": ("forest_rank_keys_kernel<true,false> + forest_compact_kernel<8,8,0,640> (throughput path: %d launches per step, timed together)" % (launches // max(1, args.steps)))
                           if launches > args.steps else "forest_complete_kernel<8,8,0,false>",
                 "algorithmic_bytes_per_event": ALGO_HBM_BYTES,
                 "note": "the walk is bound by the shared-memory pipe and the issue slots, not HBM: see gather and smem_pipe",
