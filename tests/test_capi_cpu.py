@@ -83,6 +83,27 @@ def test_deep_forests_compile_on_the_host(capi, gen):
     assert "format=complete" in capi.compile_model(pm).describe
 
 
+def test_throughput_path_forms_compile_on_the_host(capi, gen, monkeypatch):
+    """Every variant of the compact forest forms is built by host code only: complete / explicit-children trees, float and
+    64-bit threshold tables, inline leaf distributions, modelChain channels."""
+    d = capi.compile_model(gen.gbt_pmml(T=9, depth=8, F=100, seed=2)[0]).describe
+    assert "format=complete" in d and "compact=1" in d and "sparse" not in d
+    d = capi.compile_model(gen.gbt_pruned_pmml(T=12, max_depth=13, F=20, seed=3, p_leaf=0.3)).describe
+    assert "format=general" in d and "compact=1 sparse=1" in d, d
+    d = capi.compile_model(gen.gbt_pruned_pmml(T=12, max_depth=13, F=20, seed=3, p_leaf=0.3, dtype="double", float_thresholds=False)).describe
+    assert "compact=2 sparse=1" in d, d
+    for method in ("average", "weightedMajorityVote"):
+        d = capi.compile_model(gen.rf_pmml(T=5, depth=6, F=9, n_labels=5, seed=4, method=method, segment_weights=method != "average")[0]).describe
+        assert "compact=1" in d, d
+    d = capi.compile_model(gen.rf_pmml(T=3, depth=11, F=9, n_labels=3, seed=4, method="average")[0]).describe
+    assert "sparse=1" in d, d
+    d = capi.compile_model(gen.gbt_classifier_pmml(T=4, depth=11, F=9, n_classes=3, seed=5)[0]).describe
+    assert "method=9" in d and "sparse=1" in d, d
+    monkeypatch.setattr(gen, "FLOAT_THRESHOLDS", False)
+    d = capi.compile_model(gen.gbt_pmml(T=9, depth=6, F=12, seed=2)[0]).describe
+    assert "enc=rank" in d and "compact=2" in d, d
+
+
 def test_unsupported_features_are_load_errors_not_wrong_answers(capi, gen):
     pm, _ = gen.gbt_pmml(T=3, depth=2, F=4, seed=1)
     for bad in (pm.replace(b'multipleModelMethod="sum"', b'multipleModelMethod="modelChain"'),
