@@ -168,7 +168,8 @@ forest_compact_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, 
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + fl.off_bars);
   const int T = fd.n_trees, NG = (T + G - 1) / G;
 
-  if (tid == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); mbar_init(&bars[2], 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+  // bars: [0],[1] ring slot filled (bulk-copy bytes), [2] key tile filled, [3],[4] ring slot drained (one arrival per warp)
+  if (tid == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); mbar_init(&bars[2], 1); mbar_init(&bars[3], E >> 5); mbar_init(&bars[4], E >> 5); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
   __syncthreads();
 
   uint32_t q_issue = 0, q_wait = 0, tile_parity = 0;
@@ -256,8 +257,10 @@ forest_compact_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, 
           }
         }
       }
-      __syncthreads();  // everyone is done with this ring slot
-      if (tid == 0 && g + 2 < NG) { fence_proxy_async(); issue(g + 2); }
+      // this warp is done with the slot; only the producer waits for the other warps before refilling it
+      __syncwarp();
+      if ((tid & 31) == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&bars[3 + slot])) : "memory");
+      if (tid == 0 && g + 2 < NG) { mbar_wait(&bars[3 + slot], ((q_wait - 1) >> 1) & 1u); fence_proxy_async(); issue(g + 2); }
     }
     if (row < a.n) {
       if (failed) write_out(a, row, 0, ST_PREP, -1);
