@@ -313,7 +313,7 @@ forest_sparse_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, c
   const uint32_t LB = MODE == 4 ? (uint32_t)cd.leaf_bytes : 8u;   // bytes per leaf record
   double* dvotes = reinterpret_cast<double*>(smem + fl.off_votes);   // MODE 4: summed probabilities [label][event]
 
-  if (tid == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); mbar_init(&bars[2], 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+  if (tid == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); mbar_init(&bars[2], 1); mbar_init(&bars[3], E >> 5); mbar_init(&bars[4], E >> 5); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }   // as in forest_compact_kernel
   __syncthreads();
 
   uint32_t q_issue = 0, q_wait = 0, tile_parity = 0;
@@ -404,8 +404,9 @@ forest_sparse_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, c
           }
         }
       }
-      __syncthreads();  // everyone is done with this ring slot
-      if (tid == 0 && g + 2 < NG) { fence_proxy_async(); issue(g + 2); }
+      __syncwarp();     // this warp is done with the slot; only the producer waits for the others before refilling it
+      if ((tid & 31) == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&bars[3 + slot])) : "memory");
+      if (tid == 0 && g + 2 < NG) { mbar_wait(&bars[3 + slot], ((q_wait - 1) >> 1) & 1u); fence_proxy_async(); issue(g + 2); }
     }
     if (row < a.n) {
       if (failed) write_out(a, row, 0, ST_PREP, -1);

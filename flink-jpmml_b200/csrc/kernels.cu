@@ -248,7 +248,8 @@ forest_complete_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a,
   const bool rows_alias_ring = fl.off_rows == fl.off_ring;
   const uint32_t inv_f = 0xFFFFFFFFu / (uint32_t)F + 1u;  // i / F == umulhi(i, inv_f) for i < 2^16
 
-  if (tid == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+  // bars: [0],[1] ring slot filled (bulk-copy bytes), [2],[3] ring slot drained (one arrival per warp)
+  if (tid == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); mbar_init(&bars[2], nwarps); mbar_init(&bars[3], nwarps); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
   __syncthreads();
 
   uint32_t q_issue = 0, q_wait = 0;  // running stage counters (producer: thread 0 only)
@@ -373,8 +374,9 @@ forest_complete_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a,
           }
         }
       }
-      __syncthreads();  // everyone is done with this ring slot
-      if (tid == 0 && g + 2 < g_hi) { fence_proxy_async(); issue(g + 2); }
+      __syncwarp();     // this warp is done with the slot; only the producer waits for the others before refilling it
+      if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&bars[2 + slot])) : "memory");
+      if (tid == 0 && g + 2 < g_hi) { mbar_wait(&bars[2 + slot], ((q_wait - 1) >> 1) & 1u); fence_proxy_async(); issue(g + 2); }
     }
     // ---------------- epilogue: combine, Targets, extraction
     long row = row0 + tid;
