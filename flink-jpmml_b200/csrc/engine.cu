@@ -79,7 +79,8 @@ struct Table {
   ~Table() { for (auto& kv : models) fjp_model_release(kv.second); }
 };
 
-static constexpr int NSLOT = 4;
+static constexpr int NSLOT = 8;        // stream slots shared by every host thread that uses the engine
+static constexpr int MAX_INFLIGHT = 3; // open tickets one caller may hold (fjp_max_inflight)
 struct Slot {
   cudaStream_t s = nullptr; cudaEvent_t done = nullptr;
   uint8_t* buf = nullptr; size_t cap = 0;   // one device arena per slot, carved per call
@@ -226,7 +227,7 @@ extern "C" {
 
 const char* fjp_version(void) { return "flink-jpmml-b200 0.1 (sm_100a)"; }
 const char* fjp_last_error(void) { return g_last_error.c_str(); }
-int fjp_max_inflight(void) { return NSLOT - 1; }
+int fjp_max_inflight(void) { return MAX_INFLIGHT; }
 
 int fjp_engine_create(int device, fjp_engine** out, char* err, size_t errcap) {
   int count = 0;
@@ -454,15 +455,23 @@ int fjp_score_device(fjp_engine* e, fjp_model* m, const double* dX, const uint32
 int fjp_submit(fjp_engine* e, fjp_model* m, const double* X, const uint32_t* present, const double* replace,
                long n, int vec_size, double* score, uint8_t* status, int32_t* aux, int* ticket) {
   HostBatch hb{X, present, replace, n, vec_size, score, status, aux, nullptr, 0, nullptr, 0};
+  *ticket = -1;
   CK(cudaSetDevice(e->device));
-  int si = acquire_slot(e); Slot& s = e->slots[si];
-  *ticket = si; s.pending_status = status; s.pending_n = n > 0 ? n : 0;
-  if (n <= 0 || host_short_circuit(m, hb)) return 0;
-  if (!m->d_blob || m->device != e->device) { release_slot(e, si); return fail("model is not resident on this engine's device"); }
+  // never blocks: slots are shared by all host threads, so a thread that waited here while holding tickets of its own
+  // could wait for ever on a thread doing the same.  FJP_BUSY tells the caller to fjp_wait its oldest ticket and retry.
+  const int si = try_acquire_slot(e);
+  if (si < 0) return FJP_BUSY;
+  Slot& s = e->slots[si];
+  auto give_up = [&](int rc) { if (s.held) { fjp_model_release(s.held); s.held = nullptr; } s.pending_status = nullptr; s.pending_n = 0; release_slot(e, si); return rc; };
+  s.pending_status = status; s.pending_n = n > 0 ? n : 0;
+  if (n <= 0 || host_short_circuit(m, hb)) { *ticket = si; return 0; }
+  if (!m->d_blob || m->device != e->device) return give_up(fail("model is not resident on this engine's device"));
   fjp_model_retain(m); s.held = m;  // the batch keeps its model alive across a concurrent fjp_table_del
   int zc = try_zero_copy(e, m, s, hb);
-  if (zc < 0 || (zc == 0 && enqueue_chunk(e, m, s, hb, 0, n))) { fjp_model_release(m); s.held = nullptr; release_slot(e, si); return -1; }
-  CK(cudaEventRecord(s.done, s.s));
+  if (zc < 0 || (zc == 0 && enqueue_chunk(e, m, s, hb, 0, n))) { cudaStreamSynchronize(s.s); return give_up(-1); }
+  cudaError_t ce = cudaEventRecord(s.done, s.s);
+  if (ce != cudaSuccess) { cudaStreamSynchronize(s.s); return give_up(fail(std::string("cudaEventRecord: ") + cudaGetErrorString(ce))); }
+  *ticket = si;
   return 0;
 }
 

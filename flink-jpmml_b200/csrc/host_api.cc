@@ -5,6 +5,7 @@
 #include <fstream>
 #include <limits>
 #include <sstream>
+#include <thread>
 
 #include "../../include/fjpmml_host.h"
 #include "host/flinkjpmml.hpp"
@@ -119,6 +120,18 @@ int MicroBatch::append_dense(const double* x) {
 int MicroBatch::submit(fjp_engine* e, fjp_model* m, int* ticket) {
   return fjp_submit(e, m, X_, any_sparse_ ? present_ : nullptr, any_replace_ ? replace_ : nullptr, n_, F_, score_, status_, nullptr, ticket);
 }
+// fjp_submit never blocks; FJP_BUSY = every stream slot of the engine is taken (other subtasks share it).  The caller gives
+// back its own oldest ticket through `wait_oldest` (returns false when it holds none: then only other threads can free a
+// slot, and they always can, so yielding is enough).
+template <class WaitOldest>
+static void submit_or_throw(MicroBatch& mb, fjp_engine* e, fjp_model* m, int* ticket, WaitOldest&& wait_oldest) {
+  for (;;) {
+    int rc = mb.submit(e, m, ticket);
+    if (rc == 0) return;
+    if (rc != FJP_BUSY) throw std::runtime_error(fjp_last_error());
+    if (!wait_oldest()) std::this_thread::yield();
+  }
+}
 int MicroBatch::score(fjp_engine* e, fjp_model* m) {
   if (n_ == 0) return 0;
   return fjp_score_batch(e, m, X_, any_sparse_ ? present_ : nullptr, any_replace_ ? replace_ : nullptr, n_, F_, score_, status_, nullptr);
@@ -154,7 +167,12 @@ void EvaluationFunction::collect(int b) {
 }
 void EvaluationFunction::submit_current() {
   const int b = cur_;
-  if (batch_[b]->size() > 0 && batch_[b]->submit(engine_, model_.handle(), &ticket_[b]) != 0) throw std::runtime_error(fjp_last_error());
+  if (batch_[b]->size() > 0)
+    submit_or_throw(*batch_[b], engine_, model_.handle(), &ticket_[b], [&] {   // the older batch is the only other ticket this operator can hold
+      if (ticket_[b ^ 1] < 0) return false;
+      if (fjp_wait(engine_, ticket_[b ^ 1]) != 0) throw std::runtime_error(fjp_last_error());
+      ticket_[b ^ 1] = -1; return true;
+    });
   collect(b ^ 1);      // the older batch: its results come first, and its buffer becomes the one being packed
   cur_ = b ^ 1;
 }
@@ -275,7 +293,11 @@ void EvaluationCoFunction::flush() {
     if (!b.batch->size()) continue;
     if ((int)(tickets.size() - waited) >= maxfly) { if (fjp_wait(engine_, tickets[waited++]) != 0) throw std::runtime_error(fjp_last_error()); }
     int t = -1;
-    if (b.batch->submit(engine_, b.model.handle(), &t) != 0) throw std::runtime_error(fjp_last_error());
+    submit_or_throw(*b.batch, engine_, b.model.handle(), &t, [&] {
+      if (waited >= tickets.size()) return false;
+      if (fjp_wait(engine_, tickets[waited++]) != 0) throw std::runtime_error(fjp_last_error());
+      return true;
+    });
     tickets.push_back(t);
   }
   for (; waited < tickets.size(); waited++) if (fjp_wait(engine_, tickets[waited]) != 0) throw std::runtime_error(fjp_last_error());
@@ -293,8 +315,9 @@ void EvaluationCoFunction::flush() {
 // ============================================================================================ C wrappers
 using namespace flinkjpmml;
 
-struct fjh_eval_function { std::unique_ptr<EvaluationFunction> op; };
-struct fjh_cofunction { std::unique_ptr<EvaluationCoFunction> op; };
+// `backlog`: predictions already drained from the operator that did not fit the caller's last poll buffer
+struct fjh_eval_function { std::unique_ptr<EvaluationFunction> op; std::vector<Prediction> backlog; };
+struct fjh_cofunction { std::unique_ptr<EvaluationCoFunction> op; std::vector<Prediction> backlog; };
 
 static void set_err(char* err, size_t cap, const char* msg) { if (err && cap) { strncpy(err, msg, cap - 1); err[cap - 1] = 0; } }
 static Vector make_vector(const double* values, int size, const int* indices, int nnz) {
@@ -348,8 +371,7 @@ int fjh_eval_function_process_dense(fjh_eval_function* h, const double* X, long 
 }
 int fjh_eval_function_flush(fjh_eval_function* h) { return guarded(nullptr, 0, [&] { h->op->flush(); }); }
 long fjh_eval_function_poll(fjh_eval_function* h, double* scores, uint8_t* status, long cap) {
-  static std::unordered_map<fjh_eval_function*, std::vector<Prediction>> bufs;
-  return poll_out(bufs[h], h->op->drain(), scores, status, cap);
+  return poll_out(h->backlog, h->op->drain(), scores, status, cap);
 }
 void fjh_eval_function_close(fjh_eval_function* h) { if (h) { try { h->op->close(); } catch (...) {} delete h; } }
 
@@ -369,8 +391,7 @@ int fjh_cofunction_process_control(fjh_cofunction* h, int is_add, const char* na
 }
 int fjh_cofunction_flush(fjh_cofunction* h, char* err, size_t errcap) { return guarded(err, errcap, [&] { h->op->flush(); }); }
 long fjh_cofunction_poll(fjh_cofunction* h, double* scores, uint8_t* status, long cap) {
-  static std::unordered_map<fjh_cofunction*, std::vector<Prediction>> bufs;
-  return poll_out(bufs[h], h->op->drain(), scores, status, cap);
+  return poll_out(h->backlog, h->op->drain(), scores, status, cap);
 }
 // snapshot format: one "name_version<TAB>path<LF>" line per entry (the checkpointed HashMap[ModelId, ModelInfo])
 long fjh_cofunction_snapshot(fjh_cofunction* h, char* buf, long cap) {

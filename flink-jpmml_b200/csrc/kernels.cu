@@ -10,8 +10,10 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <atomic>
 #include <cstdint>
 #include <cstdlib>
+#include <mutex>
 
 #include "kernels.h"
 
@@ -102,7 +104,7 @@ __device__ __forceinline__ double apply_target(const TargetXform& t, double v) {
   if (t.has_min && v < t.mn) v = t.mn;
   if (t.has_max && v > t.mx) v = t.mx;
   v = v * t.factor + t.constant;
-  if (t.cast == 1) v = (double)llround(v); else if (t.cast == 2) v = ceil(v); else if (t.cast == 3) v = floor(v);
+  if (t.cast == 1) v = floor(v + 0.5); /* Math.round: half goes up, also below zero */ else if (t.cast == 2) v = ceil(v); else if (t.cast == 3) v = floor(v);
   return v;
 }
 
@@ -1463,12 +1465,24 @@ __global__ void __launch_bounds__(32 * NP_WARPS, 1) neural_pair_kernel(const __g
 // ================================================================================================ launchers
 #include "forest_compact.cuh"
 
-static int g_smem_optin = 0, g_num_sms = 0;
+// Device facts the launch plans depend on.  One process may drive several GPUs from several host threads (one subtask per
+// GPU, fjp_model_replicate), so the cache is per device ordinal and the values a call works with are thread-local copies
+// refreshed from it at every entry point.
+static thread_local int g_smem_optin = 0, g_num_sms = 0;
 static void query_device() {
-  if (g_num_sms) return;
+  struct Facts { std::atomic<int> ready{0}; int smem_optin = 0, num_sms = 0; };
+  static Facts facts[64];
   int dev = 0; cudaGetDevice(&dev);
-  cudaDeviceGetAttribute(&g_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
-  cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+  Facts& f = facts[dev & 63];
+  if (!f.ready.load(std::memory_order_acquire)) {
+    static std::mutex mu; std::lock_guard<std::mutex> lk(mu);
+    if (!f.ready.load(std::memory_order_relaxed)) {
+      cudaDeviceGetAttribute(&f.smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+      cudaDeviceGetAttribute(&f.num_sms, cudaDevAttrMultiProcessorCount, dev);
+      f.ready.store(1, std::memory_order_release);
+    }
+  }
+  g_smem_optin = f.smem_optin; g_num_sms = f.num_sms;
 }
 
 template <int D, int TI, int MODE, bool DBG, bool SLICE = false>

@@ -69,7 +69,7 @@ extern "C" int fjp_score_sparse_noalloc(fjp_engine* e, fjp_model* m, const int64
   if (internal_model_derived(m) > 0)
     return noalloc_fail("fjp_score_sparse_noalloc: models with derived fields need a larger work area than the built-in one; use fjp_score_sparse");
   const int W = (vec_size + 31) / 32;
-  const size_t x_bytes = ((size_t)n * vec_size * 8 + 255) & ~size_t(255), p_bytes = (size_t)n * W * 4;
+  const size_t x_bytes = (size_t)n * vec_size * 8, p_bytes = (size_t)n * W * 4;   // rows are 8-byte, present words 4-byte aligned: no padding, the documented bound is exact
   if (x_bytes + p_bytes > (size_t)FJP_NOALLOC_SCRATCH_BYTES)
     return noalloc_fail("fjp_score_sparse_noalloc: batch needs " + std::to_string(x_bytes + p_bytes) + " bytes of scratch, the built-in area holds " +
                         std::to_string((size_t)FJP_NOALLOC_SCRATCH_BYTES) + "; split the batch (rows * (vec_size*8 + ceil(vec_size/32)*4) must fit)");

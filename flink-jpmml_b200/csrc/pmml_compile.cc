@@ -477,7 +477,7 @@ struct ForestBuilder {
       if (cx.has_sub_tx) {  // a segment model's own <Targets> act on its result before aggregation
         const TargetXform& t = cx.sub_tx; double v = lf.value;
         if (t.has_min && v < t.mn) v = t.mn; if (t.has_max && v > t.mx) v = t.mx; v = v * t.factor + t.constant;
-        if (t.cast == 1) v = (double)std::llround(v); else if (t.cast == 2) v = std::ceil(v); else if (t.cast == 3) v = std::floor(v);
+        if (t.cast == 1) v = std::floor(v + 0.5); else if (t.cast == 2) v = std::ceil(v); else if (t.cast == 3) v = std::floor(v);
         lf.value = v;
       }
     }
@@ -503,7 +503,11 @@ struct ForestBuilder {
       // thr = -1: "passes whenever present"; the missing successor is the failing branch
       if (op == "isMissing") { if (slot < 0) return sT; int32_t r = add_test(slot, 0, false, sF, sT, sT); nodes[r].thr = -1; return r; }
       if (op == "isNotMissing") { if (slot < 0) return sF; int32_t r = add_test(slot, 0, false, sT, sF, sF); nodes[r].thr = -1; return r; }
-      if (dt == DT_STRING || dt == DT_OTHER) unsupported("SimplePredicate on a non-numeric field");
+      // A string-typed field can never hold a value here: vectors carry doubles, and a Double offered to a string field
+      // fails input preparation for the whole event before any model code runs (status 2 / EmptyScore, as the reference
+      // does for its k-means string fixture, T/api/PmmlModelSpec.scala:131-136).  What reaches the walk is only the
+      // absent slot, so the test is always UNKNOWN -- the model loads and keeps the job alive, like in the reference.
+      if (dt == DT_STRING || dt == DT_OTHER) return sU;
       double v; if (!parse_in_dtype(dt, p.attr("value"), &v)) unsupported("SimplePredicate value '" + std::string(p.attr("value")) + "' does not parse in the field's dataType");
       if (op == "lessOrEqual") return add_test(slot, v, false, sT, sF, sU);
       if (op == "lessThan") return add_test(slot, v, true, sT, sF, sU);
@@ -515,9 +519,8 @@ struct ForestBuilder {
     }
     if (p.name == "SimpleSetPredicate") {
       sv fname = p.attr("field"); int slot = b.slot_of(fname); uint8_t dt = b.dict_field(fname).dtype;
-      if (dt == DT_STRING || dt == DT_OTHER) unsupported("SimpleSetPredicate on a non-numeric field");
       sv bop = p.attr("booleanOperator"); bool in = bop == "isIn"; if (!in && bop != "isNotIn") malformed("bad booleanOperator " + std::string(bop));
-      if (slot < 0) return sU;
+      if (slot < 0 || dt == DT_STRING || dt == DT_OTHER) return sU;   // string field: see SimplePredicate above
       const XNode* arr = p.child("Array"); std::vector<double> vals;
       if (arr) for (auto& t : split_array(*arr)) { double v; if (!parse_in_dtype(dt, t, &v)) unsupported("set member does not parse in the field's dataType"); vals.push_back(v); }
       int32_t hit = in ? sT : sF, miss = in ? sF : sT, next = miss;

@@ -134,8 +134,9 @@ int fjp_score_sparse(fjp_engine* e, fjp_model* m, const int64_t* row_ptr, const 
  *     n * (vec_size*8 + ceil(vec_size/32)*4) exceeds it, when vec_size is not the model's field count, or without a model;
  *   - the area is shared by all calls and keeps the previous call's contents (nothing needs clearing: each call rewrites
  *     what it reads).  Calls whose GPU work overlaps -- two streams, two threads -- corrupt each other: serialise them;
- *   - the first call on a device also looks up the area's device address (once per device): make it at start-up, before
- *     any stream capture on that device;
+ *   - the first call on a device also looks up the area's device address (once per device), and the first call with a
+ *     model of a new family loads that family's kernels (the CUDA runtime loads code lazily, which takes device memory):
+ *     make one warm-up call per model at start-up, before any stream capture on that device;
  *   - asynchronous on `cuda_stream` (a cudaStream_t; NULL = the default stream). */
 #define FJP_NOALLOC_SCRATCH_BYTES (8u << 20)
 int fjp_score_sparse_noalloc(fjp_engine* e, fjp_model* m, const int64_t* d_row_ptr, const int32_t* d_indices,
@@ -148,7 +149,11 @@ int fjp_score_sparse_noalloc(fjp_engine* e, fjp_model* m, const int64_t* d_row_p
 int fjp_score_device(fjp_engine* e, fjp_model* m, const double* dX, const uint32_t* dpresent, const double* dreplace,
                      long n, int vec_size, double* dscore, uint8_t* dstatus, int32_t* daux, void* cuda_stream);
 /* Double-buffered host variant: submit returns a ticket at once (the buffers must stay valid and should be
- * pinned); wait blocks until that batch's results are in `score`/`status`/`aux`.  Up to fjp_max_inflight() tickets. */
+ * pinned); wait blocks until that batch's results are in `score`/`status`/`aux`.  A caller may keep up to
+ * fjp_max_inflight() tickets open.  fjp_submit never blocks: the engine's stream slots are shared by all host threads,
+ * and when none is free it returns FJP_BUSY with *ticket = -1 -- fjp_wait your oldest open ticket (or, holding none,
+ * yield) and submit again.  On every failure *ticket is -1 and nothing is left to wait for. */
+#define FJP_BUSY 1
 int fjp_submit(fjp_engine* e, fjp_model* m, const double* X, const uint32_t* present, const double* replace,
                long n, int vec_size, double* score, uint8_t* status, int32_t* aux, int* ticket);
 int fjp_wait(fjp_engine* e, int ticket);

@@ -424,7 +424,7 @@ static double apply_target(const Model& m, double v) {
     if (t.mn && v < *t.mn) v = *t.mn;
     if (t.mx && v > *t.mx) v = *t.mx;
     v = v * t.factor + t.constant;
-    if (t.cast == "round") v = (double)std::llround(v);  // Math.round semantics differ at .5 negatives; fine for tests
+    if (t.cast == "round") v = std::floor(v + 0.5);  // java.lang.Math.round: floor(x + 1/2), so -2.5 -> -2
     else if (t.cast == "ceiling") v = std::ceil(v);
     else if (t.cast == "floor") v = std::floor(v);
     break;

@@ -78,6 +78,22 @@ def cases():
                 [(4, None, 2), (4, None, 3)]))
     out.append(("tree/float-regression-target", doc(AB, tree_model(["a", "b"], SMALL_TREE, strategy="defaultChild"), target=("y", "continuous", "float", ())),
                 X[:3], P[:3], None, [(4, None, 2), (4, None, 4), (4, None, 5)]))
+    # Math.round: half goes up also below zero (-2 * 1.25 = -2.5 -> -2; C's round() would give -3)
+    tr = '<Targets><Target field="y" rescaleFactor="1.25" castInteger="round"/></Targets>'
+    out.append(("tree/targets-round-negative-half", t(strategy="defaultChild", extra=tr), X[:3], P[:3], None, [(0, 2.0, 2), (0, -2.0, 4), (0, 9.0, 5)]))
+    # a tree over a string-typed field loads; a Double offered for that field fails preparation (status 2, as for the
+    # reference's k-means string fixture), an absent slot makes the test UNKNOWN
+    sfields = [("a", "categorical", "string"), ("b", "continuous", "double")]
+    stree = ('<Node id="1" score="0" defaultChild="3"><True/><Node id="2" score="1"><SimplePredicate field="a" operator="equal" value="x"/></Node>'
+             '<Node id="3" score="2"><SimpleSetPredicate field="a" booleanOperator="isIn"><Array n="2" type="string">x y</Array></SimpleSetPredicate></Node>'
+             '<Node id="4" score="3"><SimplePredicate field="b" operator="lessThan" value="0"/></Node></Node>')
+    Xs, Ps = _rows((1, 0), (None, -1), (None, 1), (None, None))
+    out.append(("tree/string-field-none", doc(sfields, tree_model(["a", "b"], stree, strategy="none")), Xs, Ps, None,
+                [(2, None, None), (0, 3.0, 4), (3, None, None), (3, None, None)]))
+    out.append(("tree/string-field-defaultChild", doc(sfields, tree_model(["a", "b"], stree, strategy="defaultChild")), Xs, Ps, None,
+                [(2, None, None), (0, 2.0, 3), (0, 2.0, 3), (0, 2.0, 3)]))
+    out.append(("tree/string-field-last", doc(sfields, tree_model(["a", "b"], stree, strategy="none", no_true="returnLastPrediction")), Xs, Ps, None,
+                [(2, None, None), (0, 3.0, 4), (0, 0.0, 1), (0, 0.0, 1)]))
     # ---- input preparation (JPMML FieldValueUtil.prepareInputValue)
     iv = '<Interval closure="closedOpen" leftMargin="0" rightMargin="10"/>'
     fields = [("a", "continuous", "double", iv), ("b", "continuous", "double")]

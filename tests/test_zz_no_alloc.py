@@ -42,9 +42,6 @@ def _noalloc(lib, engine, model, row_ptr, indices, values, F):
 def test_noalloc_sparse_matches_allocating_entry_point(engine, gen):
     from flink_jpmml_b200 import capi
     lib = capi.lib()
-    vp = C.c_void_p
-    lib.fjp_score_sparse_noalloc.restype = C.c_int
-    lib.fjp_score_sparse_noalloc.argtypes = [vp, vp, vp, vp, vp, C.c_long, C.c_int, vp, vp, vp]
     F = 100
     pm, _ = gen.gbt_pmml(T=48, depth=8, F=F, seed=77)
     model = engine.compile(pm)
@@ -57,8 +54,24 @@ def test_noalloc_sparse_matches_allocating_entry_point(engine, gen):
         assert np.array_equal(status, ref["status"])
         assert np.array_equal(score, ref["score"]), "no-alloc path differs from fjp_score_sparse"
         assert (status == 0).all()
-    # a batch that does not fit the built-in area is refused with a message, not truncated
+    # the point of the entry point: once a model's kernels are loaded (the warm-up calls above), a call takes nothing from
+    # the device -- the free-memory figure and the default pool's reservation are the same before and after
+    import torch
+    row_ptr, indices, values = _csr(gen, 4000, F, 9, 0.5)
+    d_rp, d_ix, d_v = (torch.from_numpy(a).cuda() for a in (row_ptr, indices, values))
+    d_score = torch.empty(4000, dtype=torch.float64, device="cuda"); d_status = torch.empty(4000, dtype=torch.uint8, device="cuda")
+    torch.cuda.synchronize()
+    free0 = torch.cuda.mem_get_info()[0]
+    for _ in range(2):
+        assert lib.fjp_score_sparse_noalloc(engine._h, model._h, d_rp.data_ptr(), d_ix.data_ptr(), d_v.data_ptr(), 4000, F,
+                                            d_score.data_ptr(), d_status.data_ptr(), None) == 0
+    torch.cuda.synchronize()
+    assert torch.cuda.mem_get_info()[0] == free0, "the no-alloc entry point changed the device's free memory"
+    # a batch that does not fit the built-in area is refused with a message, not truncated; the documented bound is exact
     limit_rows = (8 << 20) // (F * 8 + 4 * 4)
+    row_ptr, indices, values = _csr(gen, limit_rows, F, 4, 0.9)
+    rc, score, status = _noalloc(lib, engine, model, row_ptr, indices, values, F)
+    assert rc == 0 and (status == 0).all(), "a batch of exactly the documented size must fit"
     row_ptr, indices, values = _csr(gen, limit_rows + 500, F, 3, 0.9)
     rc, score, status = _noalloc(lib, engine, model, row_ptr, indices, values, F)
     assert rc < 0 and b"scratch" in lib.fjp_last_error()
