@@ -21,7 +21,7 @@ class WrongModelIdFormat(Exception):
 ModelLoadingException = capi.ModelLoadingException
 
 
-# ---- prediction ADT (models/prediction/Target.scala:40-84, Prediction.scala:57) ----------------------------------------
+# ---- prediction ADT (models/prediction/Target.scala:44-84, Prediction.scala:72) ----------------------------------------
 @dataclass(frozen=True)
 class Score:
     value: float
@@ -216,7 +216,7 @@ def _poll(fn, handle):
 
 # ---- operators ---------------------------------------------------------------------------------------------------------
 class EvaluationFunction:
-    """stream.evaluate(reader) / quickEvaluate(reader) with micro-batching (package.scala:44-50, 73-80)."""
+    """stream.evaluate(reader) / quickEvaluate(reader) with micro-batching (package.scala:76-82, 138-142)."""
 
     def __init__(self, engine: capi.Engine, path: str, max_batch: int = 1024):
         err = C.create_string_buffer(512)
@@ -249,7 +249,7 @@ class EvaluationFunction:
 
 
 class EvaluationCoFunction:
-    """events.withSupportStream(ctrl).evaluate(...) with micro-batching (package.scala:57-69, EvaluationCoFunction.scala)."""
+    """events.withSupportStream(ctrl).evaluate(...) with micro-batching (package.scala:63-65, 107-119, EvaluationCoFunction.scala:55-133)."""
 
     def __init__(self, engine: Optional[capi.Engine], max_batch: int = 1024):
         self._h = _lib().fjh_cofunction_create(engine._h if engine else None, max_batch)

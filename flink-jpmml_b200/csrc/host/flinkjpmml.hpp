@@ -4,15 +4,15 @@
 // the reference's.  S/ = flink-jpmml-scala/src/main/scala/io/radicalbit/flink/pmml/scala/
 //
 //   Vector / DenseVector / SparseVector      org.apache.flink.ml.math (input type of S/api/PmmlModel.scala:109)
-//   Target / Score / EmptyScore / Prediction S/models/prediction/Target.scala:40-84, Prediction.scala:29-57
+//   Target / Score / EmptyScore / Prediction S/models/prediction/Target.scala:44-84, Prediction.scala:30-72
 //   exceptions                               S/api/exceptions/package.scala:27-53
-//   ModelId / ModelInfo                      S/models/core/ModelId.scala:26-48, ModelInfo.scala:26
-//   AddMessage / DelMessage                  S/models/control/ServingMessage.scala:24-44
-//   MetadataManager / ModelsManager          S/api/managers/MetadataManager.scala:34-61, ModelsManager.scala:34-47
+//   ModelId / ModelInfo                      S/models/core/ModelId.scala:32-64, ModelInfo.scala:26
+//   AddMessage / DelMessage                  S/models/control/ServingMessage.scala:27-60
+//   MetadataManager / ModelsManager          S/api/managers/MetadataManager.scala:39-88, ModelsManager.scala:39-59
 //   ModelReader                              S/api/reader/ModelReader.scala:27, FsReader.scala:41-49 (local files only)
-//   PmmlModel                                S/api/PmmlModel.scala:24-157
-//   EvaluationFunction                       S/api/functions/EvaluationFunction.scala:31-42 + S/package.scala:44-50, 73-80
-//   EvaluationCoFunction                     S/api/functions/EvaluationCoFunction.scala:42-120 + S/package.scala:57-69
+//   PmmlModel                                S/api/PmmlModel.scala:43-176
+//   EvaluationFunction                       S/api/functions/EvaluationFunction.scala:39-50 + S/package.scala:76-82, 138-142
+//   EvaluationCoFunction                     S/api/functions/EvaluationCoFunction.scala:55-133 + S/package.scala:63-65, 107-119
 //
 // What is different on purpose: the operators buffer events into pinned-host micro-batches and emit predictions in
 // arrival order when the batch is flushed (size reached, flush(), snapshotState(), close()).  Every buffered event
@@ -58,8 +58,8 @@ struct Vector {
 struct Target {
   bool empty = true; double value = 0;
   static Target score(double v) { Target t; t.empty = false; t.value = v; return t; }
-  double get() const { if (empty) throw std::out_of_range("EmptyScore.nan"); return value; }   // Target.scala:45-47
-  double getOrElse(double dflt) const { return empty ? dflt : value; }                           // Target.scala:31-35
+  double get() const { if (empty) throw std::out_of_range("EmptyScore.nan"); return value; }   // Target.scala:83
+  double getOrElse(double dflt) const { return empty ? dflt : value; }                           // Target.scala:51-55
   bool operator==(const Target& o) const { return empty == o.empty && (empty || value == o.value); }
 };
 struct Prediction {
@@ -71,9 +71,9 @@ struct Prediction {
 struct ModelId {
   std::string name; int64_t version = 0;
   static constexpr const char* separatorSymbol = "_";
-  static ModelId fromIdentifier(const std::string& id);   // throws WrongModelIdFormat (ModelId.scala:36-40)
+  static ModelId fromIdentifier(const std::string& id);   // throws WrongModelIdFormat (ModelId.scala:36-40, 47-51)
   std::string identifier() const { return name + separatorSymbol + std::to_string(version); }
-  int32_t hashCode() const;                               // (name + "_" + version).hashCode (ModelId.scala:46)
+  int32_t hashCode() const;                               // (name + "_" + version).hashCode (ModelId.scala:62)
   bool operator<(const ModelId& o) const { return name != o.name ? name < o.name : version < o.version; }
   bool operator==(const ModelId& o) const { return name == o.name && version == o.version; }
 };
@@ -89,7 +89,7 @@ inline ServingMessage AddMessage(std::string name, int64_t version, std::string 
 inline ServingMessage DelMessage(std::string name, int64_t version, int64_t occurredOn) { return {ServingMessage::Del, std::move(name), version, "", occurredOn}; }
 
 using Metadata = std::map<ModelId, ModelInfo>;   // immutable.Map[ModelId, ModelInfo] / CheckpointType.scala:29-32
-struct MetadataManager {  // Add on an existing id is ignored; Del removes (MetadataManager.scala:41-59)
+struct MetadataManager {  // Add on an existing id is ignored; Del removes (MetadataManager.scala:59-69, 80-86)
   static Metadata apply(const ServingMessage& m, const Metadata& md);
 };
 
@@ -144,7 +144,7 @@ class MicroBatch {
 };
 
 // ---------------------------------------------------------------------------------------- fixed-model operator
-// stream.evaluate(reader)(f) / quickEvaluate(reader): S/package.scala:44-50, 73-80.
+// stream.evaluate(reader)(f) / quickEvaluate(reader): S/package.scala:76-82, 138-142.
 class EvaluationFunction {
  public:
   EvaluationFunction(fjp_engine* e, ModelReader reader, int maxBatch) : engine_(e), reader_(std::move(reader)), max_batch_(maxBatch) {}
@@ -166,21 +166,21 @@ class EvaluationFunction {
 };
 
 // ---------------------------------------------------------------------------------------- dynamic operator
-// events.withSupportStream(ctrl).evaluate(f): S/package.scala:57-69, S/api/functions/EvaluationCoFunction.scala:42-120.
+// events.withSupportStream(ctrl).evaluate(f): S/package.scala:63-65, 107-119, S/api/functions/EvaluationCoFunction.scala:55-133.
 class EvaluationCoFunction {
  public:
   EvaluationCoFunction(fjp_engine* e, int maxBatch) : engine_(e), max_batch_(maxBatch) {}
-  void initializeState(const std::vector<Metadata>& restored);   // union of the restored maps (:68-83)
-  Metadata snapshotState();                                      // flushes, then returns the metadata (:63-66)
+  void initializeState(const std::vector<Metadata>& restored);   // union of the restored maps (:81-96)
+  Metadata snapshotState();                                      // flushes, then returns the metadata (:76-79)
   void processElement1(const std::string& modelId, const Vector& v, std::optional<double> replaceNan = std::nullopt);
   void processDense1(const std::string& modelId, const double* x, int size);
   // n dense events in arrival order, event i addressed to ids[id_index[i]]; ids are resolved once per call and flush
   void processDenseBatch(const char* const* ids, const int32_t* id_index, const double* X, long n, int size);
-  void processElement2(const ServingMessage& control);           // manageModels then manageMetadata (:56-61)
+  void processElement2(const ServingMessage& control);           // manageModels then manageMetadata (:69-74)
   void flush();
   std::vector<Prediction> drain() { std::vector<Prediction> r; r.swap(out_); return r; }
-  PmmlModel fromMetadata(const std::string& modelId);            // (:93-97)
-  PmmlModel loadModel(const std::string& path);                  // (:85-91)
+  PmmlModel fromMetadata(const std::string& modelId);            // (:106-117)
+  PmmlModel loadModel(const std::string& path);                  // (:98-104)
   const Metadata& servingMetadata() const { return metadata_; }
   int servingModels() const { return engine_ ? fjp_table_size(engine_) : 0; }
  private:

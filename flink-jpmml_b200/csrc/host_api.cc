@@ -20,7 +20,7 @@ int32_t javaStringHashCode(const std::string& s) {
 }
 int32_t ModelId::hashCode() const { return javaStringHashCode(identifier()); }
 
-// RegexParsers semantics of S/models/core/ModelId.scala:30-40: whitespace is skipped before every token; the name is
+// RegexParsers semantics of S/models/core/ModelId.scala:32-51: whitespace is skipped before every token; the name is
 // a lowercase-hex UUID; the version token must be all digits up to the end of the input.
 ModelId ModelId::fromIdentifier(const std::string& id) {
   size_t p = 0;
@@ -97,10 +97,10 @@ MicroBatch::~MicroBatch() { fjp_host_free(X_); fjp_host_free(present_); fjp_host
 int MicroBatch::append(const Vector& v, std::optional<double> replaceNan) {
   int r = n_++;
   double* x = X_ + (size_t)r * F_; uint32_t* p = present_ + (size_t)r * W_;
-  if (!v.sparse) {  // DenseVector: every slot present (VectorConverter.scala:49-54)
+  if (!v.sparse) {  // DenseVector: every slot present (VectorConverter.scala:68-73)
     memcpy(x, v.data.data(), (size_t)F_ * 8);
     for (int w = 0; w < W_; w++) p[w] = 0xFFFFFFFFu;
-  } else {          // SparseVector: only listed indices are present (VectorConverter.scala:61-67, 81-84)
+  } else {          // SparseVector: only listed indices are present (VectorConverter.scala:80-86, 100-103)
     any_sparse_ = true;
     memset(x, 0, (size_t)F_ * 8); memset(p, 0, (size_t)W_ * 4);
     for (size_t k = 0; k < v.indices.size(); k++) { int i = v.indices[k]; if (i >= 0 && i < F_) { x[i] = v.data[k]; p[i >> 5] |= 1u << (i & 31); } }
@@ -145,7 +145,7 @@ static Prediction make_prediction(uint8_t status, double score) {
 
 // ---------------------------------------------------------------------------------------- EvaluationFunction
 void EvaluationFunction::open() {
-  model_ = PmmlModel::fromReader(engine_, reader_);   // ModelLoadingException propagates: the job fails (EvaluationFunction.scala:37-40)
+  model_ = PmmlModel::fromReader(engine_, reader_);   // ModelLoadingException propagates: the job fails (EvaluationFunction.scala:45-48)
   for (auto& b : batch_) b = std::make_unique<MicroBatch>(model_.activeFields(), max_batch_);
 }
 void EvaluationFunction::processElement(const Vector& v, std::optional<double> replaceNan) {
@@ -242,7 +242,7 @@ void EvaluationCoFunction::enqueue(const PmmlModel& model, const Vector* v, cons
 }
 
 void EvaluationCoFunction::processElement1(const std::string& modelId, const Vector& v, std::optional<double> replaceNan) {
-  // servingModels.getOrElse(event.modelId.hashCode, fromMetadata(event.modelId))   (S/package.scala:62)
+  // servingModels.getOrElse(event.modelId.hashCode, fromMetadata(event.modelId))   (S/package.scala:112)
   enqueue(resolve(modelId), &v, nullptr, v.size, replaceNan);
 }
 void EvaluationCoFunction::processDense1(const std::string& modelId, const double* x, int size) {
@@ -272,7 +272,7 @@ void EvaluationCoFunction::processDenseBatch(const char* const* ids, const int32
 }
 
 void EvaluationCoFunction::processElement2(const ServingMessage& control) {
-  // manageModels first, then manageMetadata (EvaluationCoFunction.scala:56-61, Appendix B of SURVEY.md)
+  // manageModels first, then manageMetadata (EvaluationCoFunction.scala:69-74, Appendix B of SURVEY.md)
   if (control.kind == ServingMessage::Del && engine_) fjp_table_del(engine_, control.name.c_str(), control.version);
   const bool known = metadata_.count(control.modelId()) != 0;
   metadata_ = MetadataManager::apply(control, metadata_);

@@ -1879,7 +1879,7 @@ cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t 
 // ================================================================================================ sparse ingest
 // SparseVector rows arrive as CSR (row_ptr, indices, values) and are expanded ON THE DEVICE into the dense row +
 // present-bit form every scoring kernel reads (absent index = cleared bit = missing value; an explicit 0.0 is present:
-// api/converter/VectorConverter.scala:61-67, 81-84).  One warp per row; the expanded rows live in scratch memory that
+// api/converter/VectorConverter.scala:80-86, 100-103).  One warp per row; the expanded rows live in scratch memory that
 // the caller provides (n x F doubles + n x ceil(F/32) words).  Indices outside [0, F) match no slot and are dropped, as
 // in the reference's `(0 until size).map(indices.contains)`.
 __global__ void __launch_bounds__(256) expand_sparse_kernel(const long long* __restrict__ row_ptr, const int32_t* __restrict__ idx,

@@ -118,7 +118,7 @@ int fjp_score_batch_ex(fjp_engine* e, fjp_model* m, const double* X, const uint3
                        long n, int vec_size, double* score, uint8_t* status, int32_t* aux,
                        int32_t* node_ids, int node_stride, double* probs, int prob_stride);
 /* SparseVector rows in CSR form: row i holds indices[row_ptr[i] .. row_ptr[i+1]) with their values; every index that is
- * not listed is a missing value, an explicit 0.0 is present (S/api/converter/VectorConverter.scala:61-67, 81-84).  The rows
+ * not listed is a missing value, an explicit 0.0 is present (S/api/converter/VectorConverter.scala:80-86, 100-103).  The rows
  * are expanded on the device (O(nnz), where the reference's toDenseData is O(size * nnz), :100-103); only the non-zeros
  * cross PCIe.  Indices outside [0, vec_size) are ignored, as in the reference.  Host pointers, synchronous. */
 int fjp_score_sparse(fjp_engine* e, fjp_model* m, const int64_t* row_ptr, const int32_t* indices, const double* values,

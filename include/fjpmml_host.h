@@ -24,7 +24,7 @@ extern "C" {
 typedef struct fjh_eval_function fjh_eval_function;
 typedef struct fjh_cofunction fjh_cofunction;
 
-/* ModelId.fromIdentifier / ModelId.hashCode  (S/models/core/ModelId.scala:36-40, 46). */
+/* ModelId.fromIdentifier / ModelId.hashCode  (S/models/core/ModelId.scala:36-40, 47-51, 62). */
 int fjh_model_id_parse(const char* id, char* name_out, size_t name_cap, int64_t* version_out);
 int32_t fjh_model_id_hash(const char* name, int64_t version);
 
@@ -33,9 +33,9 @@ int32_t fjh_model_id_hash(const char* name, int64_t version);
 int fjh_predict(fjp_engine* e, fjp_model* m, const double* values, int size, const int* indices, int nnz, double replace_nan,
                 double* score, uint8_t* status);
 
-/* ---- fixed-model operator: stream.evaluate(reader)(f) / quickEvaluate(reader)   (S/package.scala:44-50, 73-80,
- * S/api/functions/EvaluationFunction.scala:31-42).  open() loads the model: NULL + message = ModelLoadingException
- * (the job fails, T/RichDataStreamSpec.scala:82-105).  Events are buffered into a pinned micro-batch of `max_batch`
+/* ---- fixed-model operator: stream.evaluate(reader)(f) / quickEvaluate(reader)   (S/package.scala:76-82, 138-142,
+ * S/api/functions/EvaluationFunction.scala:39-50).  open() loads the model: NULL + message = ModelLoadingException
+ * (the job fails, T/RichDataStreamSpec.scala:82-89).  Events are buffered into a pinned micro-batch of `max_batch`
  * rows; predictions are emitted in arrival order when the batch fills or on flush/close. */
 fjh_eval_function* fjh_eval_function_open(fjp_engine* e, const char* path, int max_batch, char* err, size_t errcap);
 const char* fjh_eval_function_model_name(fjh_eval_function* op);
@@ -46,15 +46,16 @@ int fjh_eval_function_flush(fjh_eval_function* op);
 long fjh_eval_function_poll(fjh_eval_function* op, double* scores, uint8_t* status, long cap);
 void fjh_eval_function_close(fjh_eval_function* op);
 
-/* ---- dynamic operator: events.withSupportStream(ctrl).evaluate(f)   (S/package.scala:57-69,
- * S/api/functions/EvaluationCoFunction.scala:42-120).
+/* ---- dynamic operator: events.withSupportStream(ctrl).evaluate(f)   (S/package.scala:63-65, 107-119,
+ * S/api/functions/EvaluationCoFunction.scala:55-133).
  * process_event  = processElement1: binds the event to the model its id names at this moment (cache, else metadata
  *                  -> lazy load, else the empty model), buffers it.  FJH_WRONG_MODEL_ID_FORMAT / FJH_MODEL_LOADING are
  *                  the job-fatal outcomes (T/api/functions/EvaluationCoFunctionSpec.scala:132-144,
  *                  T/RichConnectedStreamSpec.scala:288-300).
- * process_control = processElement2: Del evicts the cached model, then the metadata map is updated
- *                  (Add on a known id is ignored).
- * snapshot / restore = snapshotState / initializeState: the metadata map only; models reload lazily. */
+ * process_control = processElement2 (:69-74): Del evicts the cached model, then the metadata map is updated
+ *                  (Add on a known id is ignored, S/api/managers/MetadataManager.scala:59-69).
+ * snapshot / restore = snapshotState (:76-79) / initializeState (:81-96): the metadata map only; models reload lazily
+ *                  (loadModel :98-104, fromMetadata :106-117). */
 fjh_cofunction* fjh_cofunction_create(fjp_engine* e, int max_batch);
 int fjh_cofunction_process_event(fjh_cofunction* op, const char* model_id, const double* values, int size, const int* indices, int nnz,
                                  double replace_nan, char* err, size_t errcap);

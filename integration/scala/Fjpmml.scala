@@ -30,7 +30,8 @@ object Fjpmml {
   @native def hostAlloc(bytes: Long): ByteBuffer
   @native def hostFree(buffer: ByteBuffer): Unit
 
-  /** fjp_submit: returns the ticket; buffers must stay untouched until `await(ticket)`. */
+  /** fjp_submit: returns the ticket; buffers must stay untouched until `await(ticket)`.  -1 = FJP_BUSY: the engine's stream
+    * slots are all taken (they are shared by the subtasks of this JVM) -- `await` an own ticket, or yield, and submit again. */
   @native def submit(engine: Long,
                      model: Long,
                      x: ByteBuffer,

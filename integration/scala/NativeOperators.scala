@@ -1,8 +1,8 @@
 /*
  * SOURCE ONLY (no JVM in the build image).  Batching versions of the two operators of
- *   flink-jpmml-scala/src/main/scala/io/radicalbit/flink/pmml/scala/api/functions/EvaluationFunction.scala:31-42
- *   flink-jpmml-scala/src/main/scala/io/radicalbit/flink/pmml/scala/api/functions/EvaluationCoFunction.scala:42-120
- * on top of Fjpmml.  Public names and the user-facing DSL (package.scala:38-80) stay as they are; the compiled and
+ *   flink-jpmml-scala/src/main/scala/io/radicalbit/flink/pmml/scala/api/functions/EvaluationFunction.scala:39-50
+ *   flink-jpmml-scala/src/main/scala/io/radicalbit/flink/pmml/scala/api/functions/EvaluationCoFunction.scala:55-133
+ * on top of Fjpmml.  Public names and the user-facing DSL (package.scala:58-143) stay as they are; the compiled and
  * tested statement of this logic is flink-jpmml_b200/csrc/host/flinkjpmml.hpp + tests/test_gpu_operators.py.
  */
 package io.radicalbit.flink.pmml.scala.native
@@ -14,6 +14,8 @@ import io.radicalbit.flink.pmml.scala.models.core.{ModelId, ModelInfo}
 import io.radicalbit.flink.pmml.scala.models.input.BaseEvent
 import io.radicalbit.flink.pmml.scala.models.prediction.{EmptyScore, Prediction, Score}
 import org.apache.flink.api.common.functions.RichFlatMapFunction
+import org.apache.flink.api.common.state.{ListState, ListStateDescriptor}
+import org.apache.flink.api.common.typeinfo.{TypeHint, TypeInformation}
 import org.apache.flink.configuration.Configuration
 import org.apache.flink.ml.math.Vector
 import org.apache.flink.runtime.state.{FunctionInitializationContext, FunctionSnapshotContext}
@@ -21,6 +23,7 @@ import org.apache.flink.streaming.api.checkpoint.CheckpointedFunction
 import org.apache.flink.streaming.api.functions.co.CoProcessFunction
 import org.apache.flink.util.Collector
 
+import scala.collection.JavaConverters._
 import scala.collection.mutable
 import scala.concurrent.{Await, ExecutionContext, Future}
 import scala.concurrent.duration.Duration
@@ -58,6 +61,7 @@ abstract class BatchedEvaluationFunction[IN, OUT](reader: ModelReader, maxBatch:
   @transient private var events: Array[mutable.ArrayBuffer[(IN, Int)]] = _ // (event, row or -1 for a size mismatch)
   @transient private var tickets: Array[Int] = _
   @transient private var current: Int = 0
+  @transient private var lastOut: Collector[OUT] = _ // the operator's collector: the same object for every flatMap call
 
   override def open(parameters: Configuration): Unit = {
     engine = Fjpmml.engineCreate(getRuntimeContext.getIndexOfThisSubtask % gpusPerHost)
@@ -70,6 +74,7 @@ abstract class BatchedEvaluationFunction[IN, OUT](reader: ModelReader, maxBatch:
   protected def gpusPerHost: Int = 8
 
   override def flatMap(value: IN, out: Collector[OUT]): Unit = {
+    lastOut = out
     val v = vectorOf(value)
     val row = if (v.size != model.fields) -1 else batches(current).append(v, None)
     events(current) += ((value, row))
@@ -78,9 +83,15 @@ abstract class BatchedEvaluationFunction[IN, OUT](reader: ModelReader, maxBatch:
 
   private def handOver(out: Collector[OUT]): Unit = {
     val b = current
-    if (batches(b).rows > 0)
-      tickets(b) = Fjpmml.submit(engine, model.handle, batches(b).x, batches(b).present, batches(b).replace,
-                                 batches(b).rows, model.fields, batches(b).score, batches(b).status)
+    if (batches(b).rows > 0) {
+      def trySubmit(): Int = Fjpmml.submit(engine, model.handle, batches(b).x, batches(b).present, batches(b).replace,
+                                           batches(b).rows, model.fields, batches(b).score, batches(b).status)
+      tickets(b) = trySubmit()
+      while (tickets(b) < 0) { // FJP_BUSY: give back the older batch's slot (results stay in its buffers), else yield
+        if (tickets(1 - b) >= 0) { Fjpmml.await(engine, tickets(1 - b)); tickets(1 - b) = -1 } else Thread.`yield`()
+        tickets(b) = trySubmit()
+      }
+    }
     collect(1 - b, out) // the older batch first: keeps arrival order
     current = 1 - b
   }
@@ -96,13 +107,24 @@ abstract class BatchedEvaluationFunction[IN, OUT](reader: ModelReader, maxBatch:
     events(b).clear(); batches(b).clear()
   }
 
-  // a checkpoint barrier must not overtake buffered events: Flink calls snapshotState on the task thread; the pending
-  // batches are drained through the collector captured at the last flatMap (or a ProcessFunction timer in practice)
-  override def snapshotState(context: FunctionSnapshotContext): Unit = ()
+  /** A checkpoint barrier must not overtake buffered events: everything that arrived before the barrier is scored and
+    * emitted before the snapshot is taken, so the operator holds no in-flight events at the barrier and needs no state
+    * of its own (the reference's contract: state is consistent at snapshotState,
+    * S/api/functions/EvaluationCoFunction.scala:76-79).  Flink calls snapshotState on the task thread, between two
+    * flatMap calls, so emitting through the operator's collector here is the same as emitting from flatMap. */
+  override def snapshotState(context: FunctionSnapshotContext): Unit = drain()
+
+  /** Scores and emits both micro-batches, oldest first (arrival order). */
+  private def drain(): Unit =
+    if (lastOut != null) {
+      if (events(current).nonEmpty) handOver(lastOut) // submits the batch being packed, collects the older one
+      collect(1 - current, lastOut)                   // ... and the one just submitted
+    }
+
   override def initializeState(context: FunctionInitializationContext): Unit = ()
 
   override def close(): Unit = {
-    if (batches != null) batches.foreach(_.release())
+    if (batches != null) { drain(); batches.foreach(_.release()) }
     if (model != null && !model.isEmpty) Fjpmml.modelRelease(model.handle)
     if (engine != 0L) Fjpmml.engineDestroy(engine)
   }
@@ -111,7 +133,8 @@ abstract class BatchedEvaluationFunction[IN, OUT](reader: ModelReader, maxBatch:
 /** Dynamic models: metadata map + device model table.  An event is bound, on arrival, to the model its id names at that
   * moment, and buffered in that model's bucket; control messages therefore act between events without a flush. */
 abstract class BatchedEvaluationCoFunction[EVENT <: BaseEvent, CTRL <: ServingMessage, OUT](maxBatch: Int = 16384)
-    extends CoProcessFunction[EVENT, CTRL, OUT] {
+    extends CoProcessFunction[EVENT, CTRL, OUT]
+    with CheckpointedFunction {
 
   protected def vectorOf(event: EVENT): Vector
   protected def emit(event: EVENT, prediction: Prediction): OUT
@@ -121,6 +144,24 @@ abstract class BatchedEvaluationCoFunction[EVENT <: BaseEvent, CTRL <: ServingMe
   @transient private var loading: mutable.Map[ModelId, Future[NativeModel]] = _
   @transient private var buckets: mutable.LinkedHashMap[Long, MicroBatch] = _
   @transient private var pending: mutable.ArrayBuffer[(EVENT, Long, Int)] = _ // (event, model handle or 0, row / -1)
+  @transient private var lastOut: Collector[OUT] = _
+  @transient private var snapshotMetadata: ListState[java.util.HashMap[ModelId, ModelInfo]] = _
+
+  /** Buffered events are scored and emitted before the metadata map is written, exactly where the reference writes it
+    * (S/api/functions/EvaluationCoFunction.scala:76-79): no event is in flight at a checkpoint barrier. */
+  override def snapshotState(context: FunctionSnapshotContext): Unit = {
+    if (lastOut != null && pending.nonEmpty) flush(lastOut)
+    snapshotMetadata.clear()
+    snapshotMetadata.add(new java.util.HashMap[ModelId, ModelInfo](servingMetadata.asJava))
+  }
+
+  /** Union list state, as in the reference (:81-96); models are re-loaded lazily on the first event for their id. */
+  override def initializeState(context: FunctionInitializationContext): Unit = {
+    servingMetadata = Map.empty
+    snapshotMetadata = context.getOperatorStateStore.getUnionListState(
+      new ListStateDescriptor("metadata-snapshot", TypeInformation.of(new TypeHint[java.util.HashMap[ModelId, ModelInfo]]() {})))
+    if (context.isRestored) snapshotMetadata.get().asScala.foreach(m => servingMetadata ++= m.asScala)
+  }
 
   override def open(parameters: Configuration): Unit = {
     engine = Fjpmml.engineCreate(getRuntimeContext.getIndexOfThisSubtask % 8)
@@ -128,6 +169,7 @@ abstract class BatchedEvaluationCoFunction[EVENT <: BaseEvent, CTRL <: ServingMe
   }
 
   override def processElement1(event: EVENT, ctx: CoProcessFunction[EVENT, CTRL, OUT]#Context, out: Collector[OUT]): Unit = {
+    lastOut = out
     val id = ModelId.fromIdentifier(event.modelId) // WrongModelIdFormat is fatal, as in the reference
     var handle = Fjpmml.tableGet(engine, id.name, id.version)
     if (handle == 0L && servingMetadata.contains(id)) {
@@ -155,7 +197,7 @@ abstract class BatchedEvaluationCoFunction[EVENT <: BaseEvent, CTRL <: ServingMe
         if (!servingMetadata.contains(add.modelId)) {
           servingMetadata += add.modelId -> add.modelInfo
           loading(add.modelId) = Future(NativeModel.load(engine, ModelReader(add.path)))(ExecutionContext.global)
-        } // Add on a known id is ignored (MetadataManager.scala:45-48)
+        } // Add on a known id is ignored (MetadataManager.scala:59-69)
       case del: DelMessage =>
         Fjpmml.tableDel(engine, del.name, del.version) // buffered events keep their reference; HBM is freed when they drain
         loading.remove(del.modelId)
@@ -163,10 +205,18 @@ abstract class BatchedEvaluationCoFunction[EVENT <: BaseEvent, CTRL <: ServingMe
     }
 
   protected def flush(out: Collector[OUT]): Unit = {
-    val tickets = buckets.toSeq.filter(_._2.rows > 0).map {
-      case (handle, b) => Fjpmml.submit(engine, handle, b.x, b.present, b.replace, b.rows, b.fields, b.score, b.status)
+    val open = mutable.Queue.empty[Int] // own tickets, oldest first
+    buckets.foreach {
+      case (handle, b) if b.rows > 0 =>
+        var t = Fjpmml.submit(engine, handle, b.x, b.present, b.replace, b.rows, b.fields, b.score, b.status)
+        while (t < 0) { // FJP_BUSY
+          if (open.nonEmpty) Fjpmml.await(engine, open.dequeue()) else Thread.`yield`()
+          t = Fjpmml.submit(engine, handle, b.x, b.present, b.replace, b.rows, b.fields, b.score, b.status)
+        }
+        open.enqueue(t)
+      case _ =>
     }
-    tickets.foreach(Fjpmml.await(engine, _))
+    open.foreach(Fjpmml.await(engine, _))
     pending.foreach {
       case (event, handle, row) =>
         val p = if (row < 0) Prediction(EmptyScore)
