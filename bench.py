@@ -44,11 +44,17 @@ def peaks():
         p = {"hbm_gbs": float(m["hbm_gbs"]), "source": "measured (MEASURED_PEAKS.json)"}
     except Exception:
         pass
+    p["micro"] = {}
+    for name in ("microbench_r01.json", "microbench_r02.json"):     # later rounds override / extend earlier figures
+        try:
+            with open(os.path.join(ROOT, "profiles", name)) as f:
+                p["micro"].update(json.load(f))
+        except Exception:
+            pass
     try:
-        with open(os.path.join(ROOT, "profiles", "microbench_r01.json")) as f:
-            p["micro"] = json.load(f)
+        p["bf16_tflops_sustained"] = float(m["bf16_tflops_sustained"]); p["bf16_tflops"] = float(m["bf16_tflops"])
     except Exception:
-        p["micro"] = {}
+        p["bf16_tflops_sustained"], p["bf16_tflops"] = 1400.0, 1590.0
     return p
 
 
@@ -112,6 +118,89 @@ def device_events(torch, n, seed, device):
     return X, P
 
 
+# ---------------------------------------------------------------------------------------------------------------------
+# The other named shapes of BASELINE.json: device-resident events/s, the roofline that binds each
+# per section 8(d), and parity of a sample against the oracle.  C4 is the headline above; these ride in `configs`.
+def other_configs():
+    """name -> (PMML bytes factory, F, events per GPU, p_missing, algorithmic work per event)"""
+    from flink_jpmml_b200 import pmmlgen as g
+    iris = lambda: open(os.path.join(ROOT, "tests", "golden", "iris_kmeans43.pmml"), "rb").read()
+    return [
+        ("C1", "Iris k-means k=4 F=4 (A/kmeans.xml)", iris, 4, 1 << 22, 0.0, {"flop": 48, "hbm": 40, "bound": "latency"}),
+        ("C2", "k-means k=64 F=128, dense", lambda: g.config_c2()[0], 128, 1 << 22, 0.0, {"flop": 24576, "hbm": 1032, "bound": "fp64"}),
+        ("C2_missing5", "k-means k=64 F=128, 5% missing", lambda: g.config_c2()[0], 128, 1 << 22, 0.05, {"flop": 24576, "hbm": 1032, "bound": "fp64"}),
+        ("C3", "multinomial logistic 1000 features x 20 classes", lambda: g.regression_pmml()[0], 1000, 1 << 20, 0.0, {"flop": 40000, "hbm": 8008, "bound": "hbm"}),
+        ("C5_RF", "random forest 200 trees depth 8 F=64 majorityVote", lambda: g.rf_pmml()[0], 64, 1 << 22, 0.0, {"gather": 12800, "hbm": 528, "bound": "gather"}),
+        ("C5_MLP", "NeuralNetwork 64-256-256-8 rectifier + softmax", lambda: g.nn_pmml()[0], 64, 1 << 21, 0.0, {"flop": 167936, "hbm": 520, "bound": "tensor"}),
+    ]
+
+
+def measure_config(torch, np, eng, L, stream, dev, spec, seed, reps, want_parity):
+    from flink_jpmml_b200 import pmmlgen as g
+    key, desc, make, F_, n, pmiss, work = spec
+    pm = make()
+    m = eng.compile(pm)
+    gen = torch.Generator(device=dev); gen.manual_seed(seed)
+    if key == "C1":   # Iris-shaped events: U[0.2, 6.0] floored to one decimal (E/sources/IrisSource.scala:32-43)
+        X = (torch.floor((torch.rand(n, F_, generator=gen, device=dev, dtype=torch.float64) * 5.8 + 0.2) * 10.0) / 10.0).contiguous()
+    else:
+        X = torch.randn(n, F_, generator=gen, device=dev, dtype=torch.float64)
+    P = None
+    if pmiss > 0:
+        _, _, pb = g.events(1 << 16, F_, seed, pmiss)       # present pattern tiled from a 65k-row sample
+        P = torch.from_numpy(pb.view(np.int32)).to(dev).repeat((n + (1 << 16) - 1) // (1 << 16), 1)[:n].contiguous()
+    S = torch.empty(n, dtype=torch.float64, device=dev); T = torch.empty(n, dtype=torch.uint8, device=dev)
+
+    def run():
+        rc = L.fjp_score_device(eng._h, m._h, X.data_ptr(), P.data_ptr() if P is not None else None, None, n, F_, S.data_ptr(), T.data_ptr(), None, C.c_void_p(stream.cuda_stream))
+        if rc != 0:
+            raise RuntimeError(L.fjp_last_error().decode())
+    for _ in range(3):
+        run()
+    torch.cuda.synchronize(dev)
+    l0 = eng.launch_count
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with torch.cuda.stream(stream):
+        e0.record(stream)
+        for _ in range(reps):
+            run()
+        e1.record(stream)
+    torch.cuda.synchronize(dev)
+    ms = e0.elapsed_time(e1) / reps
+    out = {"workload": desc, "events_per_gpu_per_step": n, "ms_per_step": ms, "rows_scored_ok": int((T == 0).sum().item()),
+           "gpu_launches_per_step": (eng.launch_count - l0) // reps, "model": m.describe, "work": work}
+    if want_parity:
+        from oracle import oracle   # checker only: a 2048-event sample of this very batch against the CPU restatement
+        ns = 2048
+        xs = X[:ns].cpu().numpy(); ps = P[:ns].cpu().numpy().view(np.uint32) if P is not None else None
+        o = oracle.OracleModel(pm).predict(xs, ps, nthreads=os.cpu_count() or 1)
+        same = np.array_equal(o["status"], T[:ns].cpu().numpy()) and np.array_equal(o["score"], S[:ns].cpu().numpy(), equal_nan=True)
+        out["parity_on_sample"] = "bit-exact (2048 events: status + score)" if same else "MISMATCH"
+    del X, P, S, T
+    torch.cuda.empty_cache()
+    m.release()
+    return out
+
+
+def config_rooflines(rate, work, pk):
+    """Fractions of the resource SURVEY.md section 8(d) names as binding for the shape (per GPU rate)."""
+    micro = pk.get("micro", {}); r = {"hbm_frac": rate * work["hbm"] / 1e9 / pk["hbm_gbs"]}
+    if "gather" in work:
+        gbs = rate * work["gather"] / 1e9
+        r.update({"gather_gbs": gbs, "frac_of_l2_gather_peak": gbs / micro["l2_gather_8B_2MB_GBs"] if micro.get("l2_gather_8B_2MB_GBs") else None,
+                  "frac_of_smem_gather_peak": gbs / micro["smem_gather_8B_random_GBs"] if micro.get("smem_gather_8B_random_GBs") else None})
+    if "flop" in work:
+        tf = rate * work["flop"] / 1e12
+        r.update({"algorithmic_tflops": tf, "frac_of_fp64_fma_peak": tf / micro["fp64_fma_TFLOPs"] if micro.get("fp64_fma_TFLOPs") else None})
+        if work["bound"] == "tensor":
+            r["frac_of_bf16_tensor_sustained"] = tf / pk["bf16_tflops_sustained"]
+    b = work["bound"]
+    r["binding"] = b
+    r["frac"] = {"hbm": r["hbm_frac"], "fp64": r.get("frac_of_fp64_fma_peak"), "gather": r.get("frac_of_l2_gather_peak"),
+                 "tensor": r.get("frac_of_bf16_tensor_sustained"), "latency": None}[b]
+    return r
+
+
 def run_reference(args):
     """--impl reference: the reference's CPU path.  JPMML/Flink cannot run here (no JVM on the box), so this is the
     oracle port (oracle/oracle.cc: literal per-event interpreter) on all host cores, same metric / config."""
@@ -154,6 +243,7 @@ def main():
     ap.add_argument("--events", type=int, default=EVENTS_PER_GPU, help="events per GPU per step (default 2^22)")
     ap.add_argument("--no-latency", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the other BASELINE.json shapes (C1, C2, C3, C5)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
@@ -229,8 +319,22 @@ def main():
     clocks = sampler.stop()
     e2e_match = bool(torch.equal(hS[:4096], score[:4096].cpu()))
 
+    # ------------------------------------------------------------------ the other named shapes (all at N = 1; C5 halves at N > 1)
+    cfg_out = {}
+    if not args.no_configs:
+        del X, P
+        torch.cuda.empty_cache()
+        for spec in other_configs():
+            if world > 1 and spec[0] not in ("C5_RF", "C5_MLP"):
+                continue
+            cfg_out[spec[0]] = measure_config(torch, np, eng, L, stream, dev, spec, SEED + 17 + 1000 * rank, 5, rank == 0 and world == 1 and not args.no_cpu)
+    cfg_keys = sorted(cfg_out)
+
     # ------------------------------------------------------------------ max over ranks
-    ms_dev_max, ms_e2e_max = D.max_over_ranks(dist, [ms_dev, t_e2e * 1e3], dev)
+    maxed = D.max_over_ranks(dist, [ms_dev, t_e2e * 1e3] + [cfg_out[k]["ms_per_step"] for k in cfg_keys], dev)
+    ms_dev_max, ms_e2e_max = maxed[0], maxed[1]
+    for k, v in zip(cfg_keys, maxed[2:]):
+        cfg_out[k]["ms_per_step"] = v
 
     # ------------------------------------------------------------------ latency sweep + CPU baseline: rank 0 only
     latency, cpu = None, None
@@ -269,19 +373,33 @@ def main():
         achieved = n * ALGO_HBM_BYTES / per_launch_s / 1e9
         micro = pk.get("micro", {})
         gather = n * ALGO_GATHER_BYTES / per_launch_s / 1e9
-        roof = {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": achieved / pk["hbm_gbs"],
+        # What binds the walk is the shared-memory pipe (one wavefront per cycle and SM): `frac` is the share of those cycles the
+        # timed region used, from the wavefronts per event ncu counted for these kernels (profiles/) and the SM clock sampled
+        # during the run.  The HBM roofline of SURVEY.md section 8(d) (824 algorithmic B/event) and its L2-gather figure follow as
+        # secondary keys: neither binds (the node records are gathered from shared memory, not from L2).
+        wf_event = micro.get("forest_step_smem_wavefronts_per_event")
+        sm_mhz = clocks.get("sm_mhz") or pk.get("sm_max_mhz") or 1965.0
+        wf_peak = 148 * sm_mhz * 1e6 / 1e9                      # G wavefronts/s the chip can issue
+        wf_rate = (n * wf_event / per_launch_s / 1e9) if wf_event else None
+        roof = {"bound": "smem_pipe", "achieved": wf_rate, "peak": wf_peak, "unit": "Gwavefronts/s", "frac": (wf_rate / wf_peak) if wf_rate else None,
+                "wavefronts_per_event": wf_event, "wavefronts_source": micro.get("forest_step_smem_wavefronts_note"),
+                "peak_note": "148 SMs x SM clock sampled during the timed region (%.0f MHz): one shared-memory wavefront per SM and cycle" % sm_mhz,
                 "traffic": (micro["forest_kernel_dram_bytes_per_event"] * n) if micro.get("forest_kernel_dram_bytes_per_event") else None,
-                "traffic_source": "ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum of the pre-pass and walk launches per event x events per step (profiles/ncu_forest_r01.txt; ncu flushes L2 between the two launches, so the 205 B/event of key tiles count as DRAM traffic there and stay in L2 in a real run)", "peak_source": pk["source"],
-                "kernel": ("forest_rank_keys_kernel<true,false> + forest_compact_kernel<8,8,0,640> (throughput path: %d launches per step, timed together)" % (launches // max(1, args.steps)))
+                "traffic_source": micro.get("forest_kernel_dram_note"),
+                "kernel": ("forest_rank_keys_kernel + forest_compact_kernel<8,8,0,640> (throughput path: %d launches per step, timed together)" % (launches // max(1, args.steps)))
                           if launches > args.steps else "forest_complete_kernel<8,8,0,false>",
-                "algorithmic_bytes_per_event": ALGO_HBM_BYTES,
-                "note": "the walk is bound by the shared-memory pipe and the issue slots, not HBM: see gather and smem_pipe",
-                "smem_pipe": {"busy_frac": micro.get("forest_walk_smem_pipe_busy"), "issue_slots_busy_frac": micro.get("forest_walk_issue_slots_busy"),
+                "hbm": {"algorithmic_bytes_per_event": ALGO_HBM_BYTES, "achieved_gbs": achieved, "peak_gbs": pk["hbm_gbs"], "frac": achieved / pk["hbm_gbs"], "peak_source": pk["source"]},
+                "smem_pipe": {"walk_kernel_busy_frac_ncu": micro.get("forest_walk_smem_pipe_busy"), "walk_kernel_issue_slots_busy_frac_ncu": micro.get("forest_walk_issue_slots_busy"),
                               "source": micro.get("forest_walk_note")},
                 "gather": {"algorithmic_bytes_per_event": ALGO_GATHER_BYTES, "achieved_gbs": gather,
                            "l2_gather_peak_gbs": micro.get("l2_gather_8B_2MB_GBs"), "smem_gather_peak_gbs": micro.get("smem_gather_8B_random_GBs"),
                            "frac_of_l2_gather": (gather / micro["l2_gather_8B_2MB_GBs"]) if micro.get("l2_gather_8B_2MB_GBs") else None,
                            "frac_of_smem_gather": (gather / micro["smem_gather_8B_random_GBs"]) if micro.get("smem_gather_8B_random_GBs") else None}}
+        configs = {}
+        for k in cfg_keys:
+            c = cfg_out[k]; per_gpu = c["events_per_gpu_per_step"] / (c["ms_per_step"] / 1e3)
+            c["events_per_s"] = per_gpu * world; c["roofline"] = config_rooflines(per_gpu, c.pop("work"), pk)
+            configs[k] = c
         e2e_value = D.whole_job_rate(ne, world, e2e_steps, ms_e2e_max)
         line = {"metric": "scored events/sec", "value": value, "unit": "events/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_dev_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
@@ -291,7 +409,7 @@ def main():
                 "e2e": {"value": e2e_value, "unit": "events/s", "h2d_bytes_per_step": ne * (F * 8 + W * 4), "d2h_bytes_per_step": ne * 9,
                         "events_per_gpu_per_step": ne, "steps": e2e_steps, "matches_device_path": e2e_match,
                         "api": "fjp_score_batch (pinned host buffers, chunked copy/compute overlap)"},
-                "gpu_launches": launches, "rows_scored_ok": ok_rows, "roofline": roof, "cpu_baseline": cpu, "clocks": clocks,
+                "gpu_launches": launches, "rows_scored_ok": ok_rows, "roofline": roof, "cpu_baseline": cpu, "clocks": clocks, "configs": configs,
                 "latency_ms": latency}
         print(json.dumps(line), flush=True)
     if dist:

@@ -214,6 +214,18 @@ def _poll(fn, handle):
             return out
 
 
+def _poll_arrays(fn, handle):
+    """Same drain as _poll, as (scores, status) arrays: what a throughput test or benchmark wants."""
+    scs, sts = [], []
+    sc = np.empty(1 << 16, dtype=np.float64)
+    st = np.empty(1 << 16, dtype=np.uint8)
+    while True:
+        n = fn(handle, capi._ptr(sc), capi._ptr(st), 1 << 16)
+        scs.append(sc[:n].copy()); sts.append(st[:n].copy())
+        if n < (1 << 16):
+            return np.concatenate(scs), np.concatenate(sts)
+
+
 # ---- operators ---------------------------------------------------------------------------------------------------------
 class EvaluationFunction:
     """stream.evaluate(reader) / quickEvaluate(reader) with micro-batching (package.scala:76-82, 138-142)."""
@@ -241,6 +253,9 @@ class EvaluationFunction:
 
     def collect(self):
         return _poll(_lib().fjh_eval_function_poll, self._h)
+
+    def collect_arrays(self):
+        return _poll_arrays(_lib().fjh_eval_function_poll, self._h)
 
     def close(self):
         if self._h:
@@ -281,6 +296,9 @@ class EvaluationCoFunction:
 
     def collect(self):
         return _poll(_lib().fjh_cofunction_poll, self._h)
+
+    def collect_arrays(self):
+        return _poll_arrays(_lib().fjh_cofunction_poll, self._h)
 
     def snapshotState(self) -> bytes:
         buf = C.create_string_buffer(1 << 16)

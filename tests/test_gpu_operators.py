@@ -276,3 +276,45 @@ def test_engine_is_usable_from_several_host_threads(engine, gen, oracle):
     [t.start() for t in threads]; [t.join() for t in threads]
     stop.set(); ch.join()
     assert not errors, errors[:3]
+
+
+def test_operators_of_several_threads_share_one_engine_without_deadlock(engine, gen, oracle, tmp_path):
+    """Four dynamic operators (four task threads of one TaskManager) on ONE engine, each with five model buckets per flush:
+    together they want more stream slots than the engine has.  fjp_submit never blocks (it answers FJP_BUSY and the operator
+    gives back its own oldest ticket), so every thread finishes and every prediction is the oracle's."""
+    import threading
+    pms = [gen.gbt_pmml(T=12, depth=4, F=10, seed=800 + k)[0] for k in range(5)]
+    paths = []
+    for k, pm in enumerate(pms):
+        p = tmp_path / f"s{k}.pmml"; p.write_bytes(pm); paths.append(str(p))
+    rng = np.random.default_rng(3)
+    X = rng.standard_normal((6000, 10)); idx = rng.integers(0, 5, 6000).astype(np.int32)
+    oms = [oracle.OracleModel(pm) for pm in pms]
+    exp = np.empty(6000)
+    for k in range(5):
+        exp[idx == k] = oms[k].predict(X[idx == k])["score"]
+    errors = []
+
+    def task(t):
+        try:
+            names = [str(uuid.UUID(int=8000 + 10 * t + k)) for k in range(5)]
+            op = api.EvaluationCoFunction(engine, max_batch=300)
+            for k in range(5):
+                op.processElement2(api.AddMessage(names[k], 1, paths[k]))
+            for _ in range(4):
+                op.processDense1([f"{n}_1" for n in names], idx, X)
+            op.flush()
+            score, status = op.collect_arrays()
+            op.close()
+            if len(score) != 4 * 6000 or (status != 0).any() or not np.array_equal(score, np.tile(exp, 4)):
+                errors.append(f"thread {t}: wrong predictions")
+            for n in names:
+                engine.table_del(n, 1)
+        except Exception as e:          # noqa: BLE001
+            errors.append(repr(e))
+
+    threads = [threading.Thread(target=task, args=(t,), daemon=True) for t in range(4)]
+    [t.start() for t in threads]
+    [t.join(timeout=120) for t in threads]
+    assert not any(t.is_alive() for t in threads), "an operator thread is stuck in fjp_submit / fjp_wait"
+    assert not errors, errors[:3]

@@ -105,6 +105,20 @@ def test_sklearn_cross_check(oracle, gen):
     np.testing.assert_allclose(r["score"], gb.predict(X), rtol=1e-9)
 
 
+def test_sklearn_classifiers_cross_check(oracle):
+    """Oracle vs scikit-learn's own predict_proba: random forest (averaged leaf distributions), multinomial logistic
+    regression, MLPs with relu / tanh / logistic hidden layers (tests/hand_pmml.py exports them)."""
+    pytest.importorskip("sklearn")
+    import hand_pmml
+    for name, pm, X, proba in hand_pmml.sklearn_suite():
+        r = oracle.OracleModel(pm).predict(X, n_probs=proba.shape[1], nthreads=4)
+        if name.startswith("rf"):   # the oracle lists a forest's probabilities in first-met label order: compare the winner's
+            hand_pmml.check_against_sklearn(name, r, proba, False)
+            np.testing.assert_allclose(np.nanmax(r["probs"], axis=1), proba.max(axis=1), rtol=1e-9)
+        else:
+            hand_pmml.check_against_sklearn(name, r, proba, True)
+
+
 @pytest.mark.parametrize("n_classes", [2, 4])
 def test_model_chain_classifier_matches_numpy(oracle, gen, n_classes):
     pm, arr = gen.gbt_classifier_pmml(T=10, depth=4, F=8, n_classes=n_classes, seed=3)
