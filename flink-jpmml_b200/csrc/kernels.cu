@@ -100,6 +100,15 @@ __device__ __forceinline__ int load_field(const DeviceModel& m, const BatchArgs&
   return prep_value(m.prep[f], m.prep_pool, present, raw, out);
 }
 
+// The reference prepares EVERY active field before it evaluates the model (S/api/PmmlModel.scala:143-152: activeFields.map
+// { EvaluatorUtil.prepare }), so an invalid value fails the event even in a field the model never looks at.  Kernels that
+// only load the fields their model references ask this first.  Models whose fields cannot fail (prep_simple) skip it.
+__device__ __noinline__ bool row_fails_preparation(const DeviceModel& m, const BatchArgs& a, long row) {
+  if (m.prep_simple) return false;
+  for (int f = 0; f < m.F; f++) { double v; if (load_field(m, a, row, f, v) == 2) return true; }
+  return false;
+}
+
 __device__ __forceinline__ double apply_target(const TargetXform& t, double v) {
   if (t.has_min && v < t.mn) v = t.mn;
   if (t.has_max && v > t.mx) v = t.mx;
@@ -433,7 +442,7 @@ __global__ void __launch_bounds__(256) forest_general_kernel(const __grid_consta
   long row = blockIdx.x * (long)blockDim.x + threadIdx.x;
   if (row >= a.n) return;
   const int T = fd.n_trees; const bool classify = fd.classify;
-  double sum = 0, wsum = 0; bool fail = false, null_result = false;
+  double sum = 0, wsum = 0; bool fail = row_fails_preparation(m, a, row), null_result = false;
   constexpr int MAXL = 64;
   double votes[MAXL]; int order[MAXL]; int seen = 0;
   if (classify) for (int l = 0; l < m.n_labels && l < MAXL; l++) { votes[l] = 0; order[l] = -1; }
@@ -515,7 +524,7 @@ __global__ void __launch_bounds__(CL_E* CL_G) cluster_kernel(const __grid_consta
   }
   __syncthreads();
   const long row = row0 + e;
-  bool fail = false; double adj = 1.0;
+  bool fail = row < a.n && !cd.slots_identity && row_fails_preparation(m, a, row); double adj = 1.0;   // active fields that are not clustering fields
   {
     double sum_q = 0, sum_nm = 0;
     for (int f = 0; f < nf; f++) { int st = st_s[f * CL_SS + e]; if (st == 2) fail = true; double q = cd.q[f]; sum_q += q; sum_nm += st == 0 ? q : 0.0; }
@@ -875,7 +884,7 @@ __global__ void __launch_bounds__(128) regression_kernel(const __grid_constant__
   const RegressionDesc& rd = m.reg;
   long row = blockIdx.x * (long)blockDim.x + threadIdx.x;
   if (row >= a.n) return;
-  double y[REG_MAXC]; bool fail = false, null_result = false;
+  double y[REG_MAXC]; bool fail = row_fails_preparation(m, a, row), null_result = false;
   for (int t = 0; t < rd.n_tables && !fail; t++) {
     double acc = rd.intercept[t];
     for (int i = rd.term_off[t]; i < rd.term_off[t + 1]; i++) {
@@ -1029,7 +1038,7 @@ __global__ void __launch_bounds__(128) general_regression_kernel(const __grid_co
   const GeneralRegDesc& gd = m.greg;
   long row = blockIdx.x * (long)blockDim.x + threadIdx.x;
   if (row >= a.n) return;
-  double x[GR_MAX_PARAMS]; bool fail = false, null_result = false;
+  double x[GR_MAX_PARAMS]; bool fail = row_fails_preparation(m, a, row), null_result = false;
   for (int p = 0; p < gd.n_params; p++) {
     double v = 1.0;
     for (int i = gd.cell_off[p]; i < gd.cell_off[p + 1]; i++) {
@@ -1149,6 +1158,7 @@ __global__ void __launch_bounds__(NN_E* NN_WARPS) neural_kernel(const __grid_con
   }
   if (warp != 0 || row >= a.n) return;
   int fl = flags[lane];
+  if (row_fails_preparation(m, a, row)) fl |= 1;
   if (fl & 1) { write_out(a, row, 0, ST_PREP, -1); return; }
   if (fl & 2) { write_out(a, row, 0, m.target_status ? m.target_status : ST_EVAL, -1); return; }
   if (!nd.classify) {
@@ -1285,6 +1295,7 @@ __global__ void __launch_bounds__(NT_E* NT_WARPS, 1) neural_tile_kernel(const __
     }
     if (warp == 0 && row < a.n) {
       int fl = flags[lane];
+      if (row_fails_preparation(m, a, row)) fl |= 1;
       if (fl & 1) write_out(a, row, 0, ST_PREP, -1);
       else if (fl & 2) write_out(a, row, 0, m.target_status ? m.target_status : ST_EVAL, -1);
       else if (!nd.classify) {
@@ -1436,6 +1447,7 @@ __global__ void __launch_bounds__(32 * NP_WARPS, 1) neural_pair_kernel(const __g
       const int e = warp * 32 + lane; const long row = row0 + e; const double* col = act + e;
       if (row < a.n) {
         int fl = flags[e];
+        if (row_fails_preparation(m, a, row)) fl |= 1;
         if (fl & 1) write_out(a, row, 0, ST_PREP, -1);
         else if (fl & 2) write_out(a, row, 0, m.target_status ? m.target_status : ST_EVAL, -1);
         else if (!nd.classify) {

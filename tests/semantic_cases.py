@@ -94,6 +94,16 @@ def cases():
                 [(2, None, None), (0, 2.0, 3), (0, 2.0, 3), (0, 2.0, 3)]))
     out.append(("tree/string-field-last", doc(sfields, tree_model(["a", "b"], stree, strategy="none", no_true="returnLastPrediction")), Xs, Ps, None,
                 [(2, None, None), (0, 3.0, 4), (0, 0.0, 1), (0, 0.0, 1)]))
+    # every ACTIVE field is prepared before the model runs (S/api/PmmlModel.scala:143-152): an invalid value fails the event
+    # even when the model never reads that field
+    ivu = '<Interval closure="closedOpen" leftMargin="0" rightMargin="10"/>'
+    ufields = [("a", "continuous", "double", ivu), ("b", "continuous", "double")]
+    only_b = ('<Node id="1"><True/><Node id="2" score="1"><SimplePredicate field="b" operator="lessThan" value="0"/></Node><Node id="3" score="2"><True/></Node></Node>')
+    Xu, Pu = _rows((5, -1), (20, -1), (None, 1), (-3, 1))
+    out.append(("prep/unused-field-tree", doc(ufields, tree_model(["a", "b"], only_b)), Xu, Pu, None, [(0, 1.0, 2), (2, None, None), (0, 2.0, 3), (2, None, None)]))
+    ureg = (f'<RegressionModel modelName="r" functionName="regression">{schema(["a", "b"])}'
+            '<RegressionTable intercept="1"><NumericPredictor name="b" coefficient="2"/></RegressionTable></RegressionModel>')
+    out.append(("prep/unused-field-regression", doc(ufields, ureg), Xu, Pu, None, [(0, -1.0, None), (2, None, None), (0, 3.0, None), (2, None, None)]))
     # ---- input preparation (JPMML FieldValueUtil.prepareInputValue)
     iv = '<Interval closure="closedOpen" leftMargin="0" rightMargin="10"/>'
     fields = [("a", "continuous", "double", iv), ("b", "continuous", "double")]
