@@ -95,6 +95,7 @@ struct fjp_engine {
   std::mutex table_mu; std::shared_ptr<const Table> table{std::make_shared<Table>()};
   std::atomic<long> launches{0};
   std::atomic<uint64_t> status_counts[6];   // per-batch aggregation of the outcomes the reference logs one WARN line for
+  unsigned long long* d_stats = nullptr;    // device counters of the tensor-core path (BatchArgs::stats)
   fjp_engine() { for (auto& c : status_counts) c = 0; }
 };
 
@@ -123,7 +124,7 @@ static int slot_reserve(Slot& s, size_t bytes) {
   return 0;
 }
 
-static size_t score_scratch_bytes(const fjp_model* m, long n);
+static size_t score_scratch_bytes(const fjp_model* m, long n, bool verification_outputs = false);
 
 struct Carve {  // sub-allocation inside a slot arena
   size_t off = 0;
@@ -141,9 +142,9 @@ static int enqueue_chunk(fjp_engine* e, fjp_model* m, Slot& s, const HostBatch& 
   size_t oX = c.take((size_t)n * F * 8), oP = hb.present ? c.take((size_t)n * W * 4) : 0, oR = hb.replace ? c.take((size_t)n * 8) : 0;
   size_t oS = c.take((size_t)n * 8), oT = c.take((size_t)n), oA = hb.aux ? c.take((size_t)n * 4) : 0;
   size_t oN = hb.node_ids ? c.take((size_t)n * hb.node_stride * 4) : 0, oQ = hb.probs ? c.take((size_t)n * hb.prob_stride * 8) : 0;
-  const size_t dsz = score_scratch_bytes(m, n); size_t oD = dsz ? c.take(dsz) : 0;   // augmented rows (derived fields) / leaf values (small-batch forest path)
+  const size_t dsz = score_scratch_bytes(m, n, hb.node_ids || hb.probs); size_t oD = dsz ? c.take(dsz) : 0;   // augmented rows (derived fields) / leaf values (small-batch forest path) / digit planes
   if (slot_reserve(s, c.off)) return -1;
-  BatchArgs a{};
+  BatchArgs a{}; a.stats = e->d_stats;
   a.X = reinterpret_cast<double*>(s.buf + oX); a.n = n; a.present_stride = W;
   CK(cudaMemcpyAsync(s.buf + oX, hb.X + lo * (long)F, (size_t)n * F * 8, cudaMemcpyHostToDevice, s.s));
   if (hb.present) { a.present = reinterpret_cast<uint32_t*>(s.buf + oP); CK(cudaMemcpyAsync(s.buf + oP, hb.present + lo * (long)W, (size_t)n * W * 4, cudaMemcpyHostToDevice, s.s)); }
@@ -167,9 +168,14 @@ static int enqueue_chunk(fjp_engine* e, fjp_model* m, Slot& s, const HostBatch& 
 
 // work area a batch of n events wants besides its inputs and outputs: augmented rows (derived fields) or the per-tree leaf
 // values of the small-batch forest path
-static size_t score_scratch_bytes(const fjp_model* m, long n) {
+static size_t score_scratch_bytes(const fjp_model* m, long n, bool verification_outputs) {
   size_t d = derived_scratch_bytes(m->dev, n);
-  return d ? d : forest_slice_scratch_bytes(m->dev, n);
+  if (d) return d;
+  if (!verification_outputs) {   // digit planes of the tensor-core path (dense layers; not when probabilities / node ids are asked for)
+    BatchArgs t{}; t.n = n;
+    if (size_t sl = sliced_scratch_bytes(m->dev, t)) return sl;
+  }
+  return forest_slice_scratch_bytes(m->dev, n);
 }
 
 // status histogram of a finished batch (host side; rows are mostly 0, so whole zero words are skipped)
@@ -242,6 +248,7 @@ int fjp_engine_create(int device, fjp_engine** out, char* err, size_t errcap) {
     if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
     cudaGetLastError();
   }
+  if (cudaMalloc(&e->d_stats, 64) != cudaSuccess || cudaMemset(e->d_stats, 0, 64) != cudaSuccess) { delete e; return fail("engine counters: cudaMalloc failed", err, errcap); }
   for (int i = 0; i < NSLOT; i++) {
     if (cudaStreamCreateWithFlags(&e->slots[i].s, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreateWithFlags(&e->slots[i].done, cudaEventDisableTiming) != cudaSuccess) {
@@ -256,12 +263,19 @@ void fjp_engine_destroy(fjp_engine* e) {
   cudaSetDevice(e->device);
   for (auto& s : e->slots) { if (s.s) cudaStreamSynchronize(s.s); if (s.held) fjp_model_release(s.held); if (s.buf) cudaFree(s.buf); if (s.done) cudaEventDestroy(s.done); if (s.s) cudaStreamDestroy(s.s); }
   { std::lock_guard<std::mutex> lk(e->table_mu); e->table.reset(); }
+  if (e->d_stats) cudaFree(e->d_stats);
   delete e;
 }
 int fjp_engine_device(const fjp_engine* e) { return e->device; }
 int fjp_engine_sync(fjp_engine* e) { CK(cudaSetDevice(e->device)); for (auto& s : e->slots) CK(cudaStreamSynchronize(s.s)); return 0; }
 long fjp_engine_launch_count(const fjp_engine* e) { return e->launches.load(); }
 void fjp_engine_status_counts(const fjp_engine* e, uint64_t out[6]) { for (int k = 0; k < 6; k++) out[k] = e->status_counts[k].load(); }
+int fjp_engine_tensor_path_counts(fjp_engine* e, uint64_t out[2]) {
+  if (fjp_engine_sync(e) != 0) return -1;
+  unsigned long long h[2] = {0, 0};
+  CK(cudaMemcpy(h, e->d_stats, sizeof h, cudaMemcpyDeviceToHost));
+  out[0] = h[0]; out[1] = h[1]; return 0;
+}
 
 int fjp_model_compile(fjp_engine* e, const char* pmml, size_t len, fjp_model** out, char* err, size_t errcap) {
   std::unique_ptr<fjp_model> m(new fjp_model());
@@ -405,7 +419,7 @@ int fjp_score_sparse(fjp_engine* e, fjp_model* m, const int64_t* row_ptr, const 
       CK(launch_expand_sparse(reinterpret_cast<const long long*>(s.buf + oRp), reinterpret_cast<const int32_t*>(s.buf + oIx) - nz0,
                               reinterpret_cast<const double*>(s.buf + oVl) - nz0, cn, F, reinterpret_cast<double*>(s.buf + oX),
                               reinterpret_cast<uint32_t*>(s.buf + oP), s.s, &launches));
-      BatchArgs a{}; a.X = reinterpret_cast<double*>(s.buf + oX); a.present = reinterpret_cast<uint32_t*>(s.buf + oP); a.present_stride = W;
+      BatchArgs a{}; a.stats = e->d_stats; a.X = reinterpret_cast<double*>(s.buf + oX); a.present = reinterpret_cast<uint32_t*>(s.buf + oP); a.present_stride = W;
       a.replace = replace ? reinterpret_cast<double*>(s.buf + oR) : nullptr; a.n = cn;
       a.score = reinterpret_cast<double*>(s.buf + oS); a.status = s.buf + oT; a.aux = aux ? reinterpret_cast<int32_t*>(s.buf + oA) : nullptr;
       CK(launch_score_any(m->dev, a, dsz ? s.buf + oD : nullptr, s.s, &launches));
@@ -431,7 +445,7 @@ int fjp_score_device(fjp_engine* e, fjp_model* m, const double* dX, const uint32
   if (n <= 0) return 0;
   CK(cudaSetDevice(e->device));
   cudaStream_t st = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : e->slots[0].s;
-  BatchArgs a{}; a.X = dX; a.present = dpresent; a.replace = dreplace; a.n = n; a.present_stride = (vec_size + 31) / 32;
+  BatchArgs a{}; a.stats = e->d_stats; a.X = dX; a.present = dpresent; a.replace = dreplace; a.n = n; a.present_stride = (vec_size + 31) / 32;
   a.score = dscore; a.status = dstatus; a.aux = daux;
   int launches = 0;
   if (!m) { CK(launch_fill_status(a, ST_NOMODEL, st, &launches)); }
@@ -440,6 +454,7 @@ int fjp_score_device(fjp_engine* e, fjp_model* m, const double* dX, const uint32
     if (!m->d_blob) return fail("model was compiled without an engine: it cannot score");
     if (m->device != e->device) return fail("model lives on another device; use fjp_model_replicate");
     size_t dsz = derived_scratch_bytes(m->dev, n);
+    if (!dsz) dsz = sliced_scratch_bytes(m->dev, a);
     if (!dsz) dsz = forest_compact_scratch_bytes(m->dev, n);
     if (dsz) {   // augmented rows (derived fields) / rank-key tiles (large forest batches): stream-ordered allocation on the caller's stream
       void* scratch = nullptr; CK(cudaMallocAsync(&scratch, dsz, st));

@@ -22,6 +22,11 @@ struct BatchArgs {
   int node_stride;
   double* probs;             // n x prob_stride optional: class probabilities (regression, NN) / winning distance
   int prob_stride;
+  // re-scoring of selected rows (the exact FP64 kernels behind the tensor-core path): when set, work item i is row row_map[i]
+  // and the number of work items is *n_dev (both in device memory, written by an earlier kernel on the same stream)
+  const int32_t* row_map;
+  const int32_t* n_dev;
+  unsigned long long* stats; // optional device counters: [0] events that took the tensor-core path, [1] of those re-scored in FP64
 };
 
 struct ForestLaunch {  // tile geometry of forest_complete_kernel
@@ -37,6 +42,7 @@ size_t forest_compact_scratch_bytes(const DeviceModel& m, long n);   // throughp
 cudaError_t launch_expand_sparse(const long long* row_ptr, const int32_t* idx, const double* val, long n, int F,
                                  double* X, uint32_t* present, cudaStream_t s, int* launches);
 size_t derived_scratch_bytes(const DeviceModel& m, long n);
+size_t sliced_scratch_bytes(const DeviceModel& m, const BatchArgs& a);   // tensor-core path of dense layers (0: not taken for this batch)
 cudaError_t launch_score_any(const DeviceModel& m, const BatchArgs& a, void* scratch, cudaStream_t s, int* launches);
 cudaError_t launch_fill_status(const BatchArgs& a, int status, cudaStream_t s, int* launches);
 

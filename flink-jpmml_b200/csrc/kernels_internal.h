@@ -1,0 +1,13 @@
+// kernels_internal.h -- what the kernel translation units (kernels.cu, sliced_gemm.cu) share on the host side.
+#pragma once
+#include <cuda_runtime.h>
+
+#include "kernels.h"
+
+namespace fjp {
+void device_facts(int* num_sms, int* smem_optin);    // of the current device (cached per device ordinal)
+int env_int(const char* name, int dflt);
+cudaError_t launch_neural_pair(const DeviceModel& m, const BatchArgs& a, cudaStream_t s);   // FP64 MLP tiles; honours a.row_map / a.n_dev
+// tensor-core path of dense layers: false = not taken for this model / batch (nothing launched); true = launched, *err says how it went
+bool launch_sliced(const DeviceModel& m, const BatchArgs& a, void* scratch, cudaStream_t s, int* launches, cudaError_t* err);
+}  // namespace fjp

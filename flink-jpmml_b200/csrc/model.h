@@ -182,6 +182,33 @@ struct NeuralInput {  // DerivedField of a NeuralInput
 };
 struct NeuralLayer { int32_t n_in, n_out, act, norm; double threshold; int64_t w_off, b_off; int64_t wt_off; int32_t n_out_pad, pad; };
 static constexpr int MAX_LAYERS = 8;
+
+// ---- tensor-core form of a dense layer (tcgen05.mma kind::i8; sliced_gemm.cuh) -----------------------------------------
+// y_j = b_j + sum_i w_ji a_i is evaluated in EXACT integer arithmetic on fixed-point images of the operands:
+//   a_i = sigma * qa_i * 2^-34, sigma = a power of two >= max_i |a_i| of the event's row   (|qa_i| <= 2^34)
+//   w_ji = tau_j * qw_ji * 2^-34, tau_j = a power of two >= max_i |w_ji| of the neuron
+//   q = sum_{k=1..S} d_k 128^(S-k), balanced base-128 digits d_k in [-65, 65]: S = 5 int8 "slices" per operand.
+// Level c = k + l of the digit products accumulates in its own int32 TMEM accumulator (|.| < 2^24 for K <= 512); the pairs
+// with k + l <= S + 1 are kept (15 MMAs per K step), the epilogue recombines the 5 levels in double.  What is lost is bounded
+// per element by SG_CS * sigma * tau_j (digit truncation of both operands + the dropped pairs), so every value carries a
+// rigorous error bound; labels whose top-2 margin is inside it are re-scored by the FP64 kernels in JPMML's order.
+constexpr int SG_S = 5;             // slices per operand
+constexpr int SG_M = 128;           // events per tile (UMMA M)
+constexpr int SG_NC = 32;           // output neurons per accumulator set (UMMA N)
+constexpr int SG_KC = 64;           // input neurons per pipeline stage (two K = 32 MMA steps)
+constexpr int SG_QBITS = 34;        // |q| <= 2^34
+constexpr double SG_CS = 6.3 * 2.9103830456733704e-11;   // (1 + 1 + 4.2 + slack) * 2^-35: see DESIGN.md
+struct SgLayer {
+  int32_t K, Kp, N, Np, act, last;     // Kp = K rounded up to SG_KC (zero digits), Np = N rounded up to SG_NC
+  int64_t w_off;       // bytes into SgDesc::weights: [Np/32][Kp/64][S][4][32][16] int8 -- one (nc, kc) stage = S * 2048 contiguous bytes
+  int64_t tau_off;     // index into SgDesc::tau_exp (Np entries: exponent of tau_j)
+  int64_t b_off;       // index into NeuralDesc::biases (N entries) / RegressionDesc::intercept
+  double amax, bmax;   // max_j sum_i |w_ji| (rounded up), max_j |b_j|
+  int32_t tau_max_exp, norm;
+};
+struct SgDesc { int enabled, n_layers; SgLayer layers[MAX_LAYERS]; const int8_t* weights; const int32_t* tau_exp; };
+struct SgRow { double err; float amax; int32_t sexp; };   // per event between layers: error bound so far (inf = not on this path), max |a_i|, exponent of sigma
+
 struct NeuralDesc {
   int n_inputs, n_layers, classify, n_outputs, max_width;
   NeuralLayer layers[MAX_LAYERS];
@@ -192,6 +219,7 @@ struct NeuralDesc {
   const double* biases;
   const int32_t* out_neuron;  // n_outputs: index into the last layer
   int out_denorm_off, out_denorm_n;  // regression: NormContinuous of the output to invert (n = 0: none)
+  SgDesc sg;                  // tensor-core form (classification MLPs with 1-Lipschitz activations, layers up to 256 inputs)
 };
 
 // ---- derived fields (TransformationDictionary / LocalTransformations) ---------------------------------------------

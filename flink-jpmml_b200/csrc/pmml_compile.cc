@@ -1137,6 +1137,40 @@ void compile_general_regression(const XNode& m, Builder& b) {
   b.set_labels(cats, false); finish_target(b, classify);
 }
 
+// ---------------------------------------------------------------------------------------------- tensor-core form of dense layers
+// model.h "tensor-core form": fixed-point images of a weight matrix, cut into SG_S balanced base-128 digits per weight.
+void sg_digits(long long q, int8_t* d /* d[0] = most significant */) {
+  for (int k = SG_S - 1; k > 0; k--) { long long t = q + 64; d[k] = (int8_t)((t & 127) - 64); q = t >> 7; }
+  d[0] = (int8_t)q;
+}
+// W: N x K row-major.  Appends the layer's slices / tau exponents and fills its SgLayer; false when a weight is not finite.
+bool sg_add_layer(const double* W, const double* bias, int N, int K, SgLayer& ly, std::vector<int8_t>& SW, std::vector<int32_t>& TAU) {
+  ly.K = K; ly.N = N; ly.Kp = (K + SG_KC - 1) / SG_KC * SG_KC; ly.Np = (N + SG_NC - 1) / SG_NC * SG_NC;
+  ly.w_off = (int64_t)SW.size(); ly.tau_off = (int64_t)TAU.size();
+  const int n_nc = ly.Np / SG_NC, n_kc = ly.Kp / SG_KC;
+  SW.resize(SW.size() + (size_t)n_nc * n_kc * SG_S * 2048, 0); TAU.resize(TAU.size() + ly.Np, 0);
+  int8_t* base = SW.data() + ly.w_off; double amax = 0, bmax = 0; int tmax = -10000;
+  for (int j = 0; j < N; j++) {
+    double rowmax = 0, rowsum = 0;
+    for (int i = 0; i < K; i++) { double w = W[(size_t)j * K + i]; if (!std::isfinite(w)) return false; rowmax = std::max(rowmax, std::fabs(w)); rowsum += std::fabs(w); }
+    if (!std::isfinite(bias[j])) return false;
+    int e = 0; if (rowmax > 0) std::frexp(rowmax, &e);          // rowmax = f * 2^e, f in [0.5, 1): tau = 2^e >= rowmax
+    if (e < -400 || e > 400) return false;
+    TAU[ly.tau_off + j] = e; tmax = std::max(tmax, e);
+    amax = std::max(amax, rowsum * (1.0 + 1e-12)); bmax = std::max(bmax, std::fabs(bias[j]));
+    const int nc = j / SG_NC, jn = j % SG_NC;
+    for (int i = 0; i < K; i++) {
+      long long q = std::llrint(std::ldexp(W[(size_t)j * K + i], SG_QBITS - e));   // exact scaling, one rounding: |w / tau - q 2^-34| <= 2^-35
+      int8_t d[SG_S]; sg_digits(q, d);
+      const int kc = i / SG_KC, kb = i % SG_KC;
+      int8_t* stage = base + ((size_t)nc * n_kc + kc) * SG_S * 2048;
+      for (int sl = 0; sl < SG_S; sl++) stage[(size_t)sl * 2048 + (kb / 16) * (SG_NC * 16) + jn * 16 + (kb % 16)] = d[sl];
+    }
+  }
+  ly.amax = amax; ly.bmax = bmax; ly.tau_max_exp = tmax == -10000 ? 0 : tmax;
+  return true;
+}
+
 // ---------------------------------------------------------------------------------------------- neural network
 int act_of(sv s) {
   static const char* names[] = {"threshold", "logistic", "tanh", "identity", "exponential", "reciprocal", "square", "Gauss", "sine", "cosine", "Elliott", "arctan", "rectifier"};
@@ -1219,7 +1253,27 @@ void compile_neural(const XNode& m, Builder& b) {
     WT.resize(WT.size() + (size_t)ly.n_in * ly.n_out_pad, 0.0);
     for (int j = 0; j < ly.n_out; j++) for (int i = 0; i < ly.n_in; i++) WT[(size_t)ly.wt_off + (size_t)i * ly.n_out_pad + j] = W[(size_t)ly.w_off + (size_t)j * ly.n_in + i];
   }
+  // tensor-core form: classification, layers of at most 256 inputs, activations with Lipschitz constant <= 1 (an input error is
+  // not amplified), identity + softmax / no normalisation on the last layer, at most 16 output neurons
+  std::vector<int8_t> SW; std::vector<int32_t> TAU; SgDesc& sg = d.sg; sg = SgDesc{};
+  {
+    bool ok = classify && d.n_inputs <= 256 && nl <= MAX_LAYERS;
+    for (int l = 0; l < nl && ok; l++) {
+      const NeuralLayer& ly = d.layers[l]; const bool last = l == nl - 1;
+      ok = ly.n_in <= 256 && ly.n_out <= 256;   // also what neural_pair_kernel (the re-scoring kernel) takes
+      if (!last) ok = ok && ly.norm == NORM_NONE && (ly.act == ACT_RECTIFIER || ly.act == ACT_IDENTITY || ly.act == ACT_TANH || ly.act == ACT_LOGISTIC);
+      else ok = ok && ly.act == ACT_IDENTITY && (ly.norm == NORM_SOFTMAX || ly.norm == NORM_NONE) && ly.n_out <= 16;
+    }
+    for (int l = 0; l < nl && ok; l++) {
+      const NeuralLayer& ly = d.layers[l]; SgLayer& sl = sg.layers[l];
+      ok = sg_add_layer(W.data() + ly.w_off, B.data() + ly.b_off, ly.n_out, ly.n_in, sl, SW, TAU);
+      sl.act = ly.act; sl.last = l == nl - 1; sl.norm = ly.norm; sl.b_off = ly.b_off;
+    }
+    sg.enabled = ok ? 1 : 0; sg.n_layers = ok ? nl : 0;
+    if (!ok) { SW.clear(); TAU.clear(); }
+  }
   b.put(&d.inputs, inputs); b.put(&d.pts, pts); b.put(&d.weights, W); b.put(&d.weights_t, WT); b.put(&d.biases, B); b.put(&d.out_neuron, out_neuron);
+  b.put(&d.sg.weights, SW); b.put(&d.sg.tau_exp, TAU);
   b.set_labels(labels, false); finish_target(b, classify);
 }
 

@@ -1,0 +1,370 @@
+// sliced_gemm.cuh -- dense layers (NeuralNetwork, J6) on the 5th-generation tensor cores: tcgen05.mma kind::i8 with the
+// accumulators in tensor memory.  Compiled as sliced_gemm.cu (device helpers from device_common.cuh).  Replaces, for large batches, the FP64
+// CUDA-core tiles of neural_pair_kernel on the path the reference hands to JPMML's NeuralNetworkEvaluator
+// (flink-jpmml-scala/src/main/scala/io/radicalbit/flink/pmml/scala/api/PmmlModel.scala:159-160).
+//
+// Arithmetic (model.h "tensor-core form"): both operands of a layer are fixed-point images cut into SG_S = 5 balanced
+// base-128 digits; digit products of level c = k + l are summed EXACTLY in int32 accumulators (one 32-column TMEM
+// accumulator per level), and the epilogue recombines the levels in double:  z_j = b_j + sigma tau_j 2^-40 (sum_c 128^(6-c) L_c).
+// Nothing in the tensor pipe rounds, so the only errors are the digit truncation of the operands and the dropped pairs
+// (k + l > 6), bounded per layer and event by  K sigma tau_max SG_CS;  the bound is carried from layer to layer
+// (1-Lipschitz activations, |W| row sums) and the last layer's epilogue accepts a label only when the winner's margin
+// exceeds twice the bound.  Every other event -- and every event with a missing / invalid / non-finite input -- goes on a
+// list that neural_pair_kernel re-scores in FP64 in JPMML's order: labels are bit-exact by construction.
+//
+// Kernels per pass of <= 8 tiles per SM (activations of a pass stay in L2 / HBM between the layer launches):
+//   sg_slice_inputs_kernel  NeuralInputs (same FP64 code as the exact kernels) -> row scale sigma -> 5 digit planes
+//   sg_layer_kernel<LAST>   one launch per layer; CTA = 128 events (UMMA M) x all output neurons in chunks of 32 (UMMA N):
+//       warp 0    producer: the tile's input digit planes (K-chunks of 64, 40 KB each) and the layer's weight digit planes
+//                 (10 KB per (neuron chunk, K chunk)) arrive with cp.async.bulk (TMA unit) on mbarriers; both are stored in
+//                 global memory in exactly the shared-memory image the MMA reads (K-major, no swizzle: 8 x 16 B core matrices)
+//       warp 1    one lane issues 30 tcgen05.mma (M128 N32 K32, 15 digit pairs x 2 K steps) per stage; tcgen05.commit
+//                 hands smem stages back to the producer and full accumulator sets (double-buffered in TMEM) to the epilogue
+//       warps 2-9 epilogue: tcgen05.ld 5 levels x 16 columns, recombination, bias, activation, re-slicing into the next
+//                 layer's digit planes (coalesced 16-byte stores) or, for the last layer, arg-max + margin test
+#pragma once
+
+namespace fjp {
+namespace sg {
+
+constexpr int THREADS = 320;                 // producer warp, MMA warp, 8 epilogue warps
+constexpr int EPI_WARPS = 8;
+constexpr int NSTAGE = 4;                    // weight stages in flight
+constexpr uint32_t A_CHUNK = SG_S * SG_M * SG_KC;      // 40960 B: one K chunk of a tile, all digit planes
+constexpr uint32_t A_PLANE = SG_M * SG_KC;             // 8192 B
+constexpr uint32_t B_STAGE = SG_S * SG_NC * SG_KC;     // 10240 B
+constexpr uint32_t B_PLANE = SG_NC * SG_KC;            // 2048 B
+constexpr int TMEM_COLS = 512;               // two accumulator sets of SG_S x 32 columns (320 used)
+constexpr int MAX_KC = 4;                    // K <= 256
+constexpr long PASS_TILES_PER_SM = 8;
+
+struct Pass {
+  const int8_t* a_in;    // [tile][Kp / 64][S][4][128][16]
+  int8_t* a_out;         // next layer's input planes (NULL on the last layer)
+  const SgRow* rows_in;  // row state of the pass's events as the previous kernel left it
+  SgRow* rows_out;       // ... as this kernel leaves it (another array: the two column halves of an event read rows_in at their own pace)
+  long row_begin, n_rows;
+  int layer;
+  int32_t* fb_count; int32_t* fb_rows;
+};
+
+__device__ __forceinline__ void digits(long long q, int (&d)[SG_S]) {   // d[0] most significant; q = sum d[k] 128^(S-1-k)
+  long long t = q + 64; d[4] = (int)(t & 127) - 64; int r = (int)(t >> 7);
+  int u = r + 64; d[3] = (u & 127) - 64; r = u >> 7;
+  u = r + 64; d[2] = (u & 127) - 64; r = u >> 7;
+  u = r + 64; d[1] = (u & 127) - 64; r = u >> 7;
+  d[0] = r;
+}
+__device__ __forceinline__ double pow2(int e) { return __longlong_as_double((long long)(e + 1023) << 52); }   // -1022 <= e <= 1023
+// smallest power-of-two exponent e with 2^e > v (v >= 0, finite); v == 0 -> 0
+__device__ __forceinline__ int exp_above(double v) {
+  if (!(v > 0.0)) return 0;
+  const int be = (int)((__double_as_longlong(v) >> 52) & 0x7FF);
+  return be == 0 ? -1021 : be - 1022;
+}
+
+// ---------------------------------------------------------------------------------------------- NeuralInputs -> digit planes
+__device__ double input_value(const DeviceModel& m, const BatchArgs& a, long row, int i, int& fl) {
+  const NeuralDesc& nd = m.nn;
+  if (i >= nd.n_inputs) return 0.0;
+  const NeuralInput in = nd.inputs[i];
+  if (in.kind == NI_CONSTANT) return in.value;
+  double v; const int st = in.slot < 0 ? 1 : load_field(m, a, row, in.slot, v);
+  if (st == 2) { fl |= 1; return 0.0; }
+  if (st == 1) { if (in.has_map_missing) return in.map_missing; fl |= 2; return 0.0; }
+  if (in.kind == NI_FIELDREF) return v;
+  if (in.kind == NI_NORMDISC) return java_eq(v, in.value) ? 1.0 : 0.0;
+  bool miss = false; const double out = norm_cont(nd.pts + 2 * in.pts_off, in.n_pts, in.outliers, v, miss);
+  if (miss) fl |= 2;
+  return out;
+}
+
+// 4 lanes per event; lane q takes the 16-input groups q, q + 4, ...  Two sweeps over the inputs: row maximum, then digits.
+__global__ void __launch_bounds__(256) sg_slice_inputs_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, const Pass ps) {
+  const SgLayer& L0 = m.nn.sg.layers[0];
+  const int groups = L0.Kp / 16, n_kc = L0.Kp / SG_KC;
+  const long t = blockIdx.x * (long)blockDim.x + threadIdx.x;
+  const long r_pass = t >> 2; const int q4 = (int)(t & 3);
+  const bool live = r_pass < ps.n_rows;
+  const long row = ps.row_begin + (live ? r_pass : 0);
+  int fl = 0; double amax = 0.0;
+  for (int g = q4; g < groups; g += 4)
+    for (int k = 0; k < 16; k++) { const double v = input_value(m, a, row, g * 16 + k, fl); amax = fmax(amax, fabs(v)); if (!(fabs(v) <= 1e300)) fl |= 4; }
+  amax = fmax(amax, __shfl_xor_sync(0xffffffffu, amax, 1)); amax = fmax(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+  fl |= __shfl_xor_sync(0xffffffffu, fl, 1); fl |= __shfl_xor_sync(0xffffffffu, fl, 2);
+  if (q4 == 0 && live && !fl && row_fails_preparation(m, a, row)) fl |= 1;
+  fl = __shfl_sync(0xffffffffu, fl, (threadIdx.x & 31) & ~3);
+  int sexp = exp_above(amax);
+  if (sexp < -400 || sexp > 400) { fl |= 4; sexp = 0; }
+  if (!live) return;
+  const long tile = r_pass / SG_M; const int r = (int)(r_pass % SG_M);
+  int8_t* tbase = ps.a_out + (size_t)tile * n_kc * A_CHUNK;
+  for (int g = q4; g < groups; g += 4) {
+    uint32_t w[SG_S][4];
+#pragma unroll
+    for (int s = 0; s < SG_S; s++) { w[s][0] = 0; w[s][1] = 0; w[s][2] = 0; w[s][3] = 0; }
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+      int dummy = 0; const double v = fl ? 0.0 : input_value(m, a, row, g * 16 + k, dummy);
+      const long long qv = __double2ll_rn(scalbn(v, SG_QBITS - sexp));
+      int d[SG_S]; digits(qv, d);
+#pragma unroll
+      for (int s = 0; s < SG_S; s++) w[s][k >> 2] |= (uint32_t)(d[s] & 0xFF) << (8 * (k & 3));
+    }
+    int8_t* dst = tbase + (size_t)(g >> 2) * A_CHUNK + (size_t)(g & 3) * (SG_M * 16) + (size_t)r * 16;
+#pragma unroll
+    for (int s = 0; s < SG_S; s++) *reinterpret_cast<uint4*>(dst + (size_t)s * A_PLANE) = make_uint4(w[s][0], w[s][1], w[s][2], w[s][3]);
+  }
+  if (q4 == 0) {
+    SgRow rs; rs.amax = (float)amax; rs.sexp = sexp;
+    // the planes hold x to within sigma 2^-35 per input; anything irregular sends the event to the FP64 kernels
+    rs.err = fl ? __longlong_as_double(0x7FF0000000000000LL) : pow2(sexp - 35);
+    if ((double)rs.amax < amax) rs.amax = __float_as_uint(rs.amax) == 0x7f7fffffu ? rs.amax : __uint_as_float(__float_as_uint(rs.amax) + 1u);   // round up
+    ps.rows_out[r_pass] = rs;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- the layer kernel
+__device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo_bytes) {
+  // K-major, no swizzle: 8-row groups 128 B apart (SBO), the two 16-byte K halves of one MMA lbo_bytes apart (LBO); version 1
+  return (uint64_t)((addr >> 4) & 0x3FFFu) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16) | ((uint64_t)(128u >> 4) << 32) | ((uint64_t)1 << 46);
+}
+__device__ __forceinline__ void mma_i8(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+  const uint32_t z = 0;
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+               "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %6, %7, %8}, p;\n\t}"
+               ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate), "r"(z), "r"(z), "r"(z), "r"(z) : "memory");
+}
+__device__ __forceinline__ void mma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                 "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]) : "r"(taddr));
+}
+
+struct Smem { uint32_t off_b, off_bias, off_tau, off_hmax, off_bars, off_tmem, bytes; };
+__host__ __device__ inline Smem smem_plan(int n_kc, int Np) {
+  Smem p; uint32_t o = (uint32_t)n_kc * A_CHUNK;
+  p.off_b = o; o += NSTAGE * B_STAGE;
+  p.off_bias = o; o += (uint32_t)Np * 8;
+  p.off_tau = o; o += (uint32_t)Np * 4; o = (o + 15u) & ~15u;
+  p.off_hmax = o; o += 2u * SG_M * 8u;
+  p.off_bars = o; o += 8u * (2 * MAX_KC + 2 * NSTAGE + 4);
+  p.off_tmem = o; o += 16;
+  p.bytes = o;
+  return p;
+}
+
+template <bool LAST>
+__global__ void __launch_bounds__(THREADS, 1) sg_layer_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, const Pass ps) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const NeuralDesc& nd = m.nn; const SgLayer& L = nd.sg.layers[ps.layer];
+  const int n_kc = L.Kp / SG_KC, n_nc = L.Np / SG_NC;
+  const Smem sp = smem_plan(n_kc, L.Np);
+  uint8_t* sA = smem; uint8_t* sB = smem + sp.off_b;
+  double* s_bias = reinterpret_cast<double*>(smem + sp.off_bias); int* s_tau = reinterpret_cast<int*>(smem + sp.off_tau);
+  double* s_hmax = reinterpret_cast<double*>(smem + sp.off_hmax);     // [2 column halves][128 events]: largest |h| of the tile (inf = digit overflow)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + sp.off_bars);
+  uint64_t* a_full = bars; uint64_t* a_empty = bars + MAX_KC; uint64_t* b_full = bars + 2 * MAX_KC; uint64_t* b_empty = b_full + NSTAGE;
+  uint64_t* t_full = b_empty + NSTAGE; uint64_t* t_empty = t_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + sp.off_tmem);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const long ntiles = (ps.n_rows + SG_M - 1) / SG_M;
+
+  for (int j = tid; j < L.Np; j += THREADS) { s_bias[j] = j < L.N ? nd.biases[L.b_off + j] : 0.0; s_tau[j] = j < L.N ? nd.sg.tau_exp[L.tau_off + j] : 0; }
+  if (tid == 0) {
+    for (int i = 0; i < MAX_KC; i++) { mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1); }
+    for (int i = 0; i < NSTAGE; i++) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], 1); }
+    for (int i = 0; i < 2; i++) { mbar_init(&t_full[i], 1); mbar_init(&t_empty[i], EPI_WARPS); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(TMEM_COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================================================================== producer
+    if (lane == 0) {
+      const int8_t* wsl = nd.sg.weights + L.w_off;
+      uint32_t it_b = 0, it_t = 0;
+      for (long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it_t++) {
+        const int8_t* asrc = ps.a_in + (size_t)tile * n_kc * A_CHUNK;
+        for (int nc = 0; nc < n_nc; nc++)
+          for (int kc = 0; kc < n_kc; kc++, it_b++) {
+            const uint32_t st = it_b % NSTAGE;
+            mbar_wait(&b_empty[st], ((it_b / NSTAGE) & 1u) ^ 1u);
+            mbar_expect_tx(&b_full[st], B_STAGE);
+            bulk_g2s(sB + (size_t)st * B_STAGE, wsl + ((size_t)nc * n_kc + kc) * B_STAGE, B_STAGE, &b_full[st]);
+            if (nc == 0) {   // the tile's own K chunk follows its first weight stage: the slot frees up later than the weight ring does
+              mbar_wait(&a_empty[kc], (it_t & 1u) ^ 1u);
+              mbar_expect_tx(&a_full[kc], A_CHUNK);
+#pragma unroll
+              for (int s = 0; s < SG_S; s++) bulk_g2s(sA + (size_t)kc * A_CHUNK + (size_t)s * A_PLANE, asrc + (size_t)kc * A_CHUNK + (size_t)s * A_PLANE, A_PLANE, &a_full[kc]);
+            }
+          }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================================================== MMA issuer (one lane)
+    if (lane == 0) {
+      const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(SG_NC >> 3) << 17) | ((uint32_t)(SG_M >> 4) << 24);   // S32 += S8 x S8, K-major A and B, M128 N32
+      const uint64_t da0 = smem_desc(smem_u32(sA), SG_M * 16), db0 = smem_desc(smem_u32(sB), SG_NC * 16);
+      uint32_t it_b = 0, it_t = 0, it_acc = 0;
+      for (long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it_t++) {
+        for (int nc = 0; nc < n_nc; nc++, it_acc++) {
+          const uint32_t buf = it_acc & 1u;
+          mbar_wait(&t_empty[buf], ((it_acc >> 1) & 1u) ^ 1u);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint32_t d0 = tmem + buf * (SG_S * SG_NC);
+          for (int kc = 0; kc < n_kc; kc++, it_b++) {
+            const uint32_t st = it_b % NSTAGE;
+            if (nc == 0) mbar_wait(&a_full[kc], it_t & 1u);
+            mbar_wait(&b_full[st], (it_b / NSTAGE) & 1u);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll
+            for (int ks = 0; ks < 2; ks++) {
+#pragma unroll
+              for (int k = 0; k < SG_S; k++) {
+#pragma unroll
+                for (int l = 0; l + k < SG_S; l++) {
+                  const uint64_t da = da0 + (uint64_t)(((uint32_t)kc * A_CHUNK + (uint32_t)k * A_PLANE + (uint32_t)ks * 2u * (SG_M * 16)) >> 4);
+                  const uint64_t db = db0 + (uint64_t)((st * B_STAGE + (uint32_t)l * B_PLANE + (uint32_t)ks * 2u * (SG_NC * 16)) >> 4);
+                  mma_i8(d0 + (uint32_t)(k + l) * SG_NC, da, db, idesc, (kc == 0 && ks == 0 && k == 0) ? 0u : 1u);
+                }
+              }
+            }
+            mma_commit(&b_empty[st]);                       // the weight stage can be refilled once these MMAs have read it
+            if (nc == n_nc - 1) mma_commit(&a_empty[kc]);   // last use of this K chunk of the tile
+          }
+          mma_commit(&t_full[buf]);
+        }
+      }
+    }
+  } else {
+    // ===================================================================== epilogue: 8 warps, lane <-> event, 16 columns per thread
+    const int ew = warp - 2, quarter = warp & 3, half = ew >> 2;       // TMEM lanes 32 * (warp % 4) .. + 31 are this warp's
+    const int r = quarter * 32 + lane;
+    uint32_t it_acc = 0;
+    const int next_kc = LAST ? 0 : nd.sg.layers[ps.layer + 1].Kp / SG_KC;
+    const bool bounded_act = L.act == ACT_TANH || L.act == ACT_LOGISTIC;
+    for (long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      const long r_pass = tile * SG_M + r; const bool live = r_pass < ps.n_rows;
+      const SgRow rs = ps.rows_in[live ? r_pass : 0];
+      const double sigma_in = pow2(rs.sexp);
+      // scale of this layer's outputs, known before any of them: |h_j| <= |b_j| + sum_i |w_ji| |a_i| <= bmax + amax_W * max|a|
+      const double out_bound = bounded_act ? 1.0 : L.bmax + L.amax * (double)rs.amax;
+      int sexp_out = exp_above(out_bound * (1.0 + 1e-9));
+      double hmax = 0.0; bool overflow = !(out_bound < 1e280) || sexp_out < -400 || sexp_out > 400;
+      if (overflow) sexp_out = 0;
+      double zl[16];
+      for (int nc = 0; nc < n_nc; nc++, it_acc++) {
+        const uint32_t buf = it_acc & 1u;
+        mbar_wait(&t_full[buf], (it_acc >> 1) & 1u);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        uint32_t lv[SG_S][16];
+        const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + buf * (SG_S * SG_NC) + (uint32_t)half * 16u;
+#pragma unroll
+        for (int c = 0; c < SG_S; c++) tmem_ld16(taddr + (uint32_t)c * SG_NC, lv[c]);
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&t_empty[buf]);          // the accumulator set is in registers: the next chunk may overwrite it
+        const int j0 = nc * SG_NC + half * 16;
+        uint32_t w[SG_S][4];
+#pragma unroll
+        for (int s = 0; s < SG_S; s++) { w[s][0] = 0; w[s][1] = 0; w[s][2] = 0; w[s][3] = 0; }
+#pragma unroll
+        for (int c = 0; c < 16; c++) {
+          const int hi = (int)lv[0][c] * 128 + (int)lv[1][c], mid = (int)lv[2][c] * 128 + (int)lv[3][c], lo = (int)lv[4][c];
+          const double V = fma((double)hi, 2097152.0, fma((double)mid, 128.0, (double)lo));      // exact: |V| < 2^53
+          const double z = fma(V, pow2(rs.sexp + s_tau[j0 + c] - 40), s_bias[j0 + c]);
+          if (LAST) zl[c] = z;
+          else {
+            const double h = (j0 + c < L.N) ? activate(L.act, z, 0.0) : 0.0;
+            hmax = fmax(hmax, fabs(h));
+            const long long qv = __double2ll_rn(scalbn(h, SG_QBITS - sexp_out));
+            if (qv > (1LL << SG_QBITS) || qv < -(1LL << SG_QBITS)) overflow = true;
+            int d[SG_S]; digits(qv, d);
+#pragma unroll
+            for (int s = 0; s < SG_S; s++) w[s][c >> 2] |= (uint32_t)(d[s] & 0xFF) << (8 * (c & 3));
+          }
+        }
+        if (!LAST) {
+          // output neuron j is input k = j of the next layer: plane s, K chunk j / 64, 16-byte column (j % 64) / 16, row r
+          int8_t* dst = ps.a_out + (size_t)tile * next_kc * A_CHUNK + (size_t)(j0 >> 6) * A_CHUNK + (size_t)((j0 & 63) >> 4) * (SG_M * 16) + (size_t)r * 16;
+          if (j0 < next_kc * SG_KC) {
+#pragma unroll
+            for (int s = 0; s < SG_S; s++) *reinterpret_cast<uint4*>(dst + (size_t)s * A_PLANE) = make_uint4(w[s][0], w[s][1], w[s][2], w[s][3]);
+          }
+        }
+      }
+      // error bound of this layer's outputs for the event (model.h): propagated input error + slicing / dropped pairs + FP64 rounding
+      // of both this evaluation and the reference's sequential sum
+      const double mag = L.bmax + L.amax * (double)rs.amax;
+      const double e_out = L.amax * rs.err + (double)L.K * sigma_in * pow2(L.tau_max_exp) * SG_CS + (double)(L.K + 8) * 2.220446049250313e-16 * mag;
+      if (!LAST) {
+        // pad columns of the next layer's planes (Np of this layer < Kp of the next) are zero digits
+        if (half == 0) {
+          for (int j = L.Np; j < next_kc * SG_KC; j += 16) {
+            int8_t* dst = ps.a_out + (size_t)tile * next_kc * A_CHUNK + (size_t)(j >> 6) * A_CHUNK + (size_t)((j & 63) >> 4) * (SG_M * 16) + (size_t)r * 16;
+#pragma unroll
+            for (int s = 0; s < SG_S; s++) *reinterpret_cast<uint4*>(dst + (size_t)s * A_PLANE) = make_uint4(0, 0, 0, 0);
+          }
+        }
+        // the two column halves of an event exchange their largest |h|: the next layer scales ITS outputs from the actual
+        // maximum of its inputs, so the a-priori bounds do not compound from layer to layer
+        s_hmax[half * SG_M + r] = overflow ? __longlong_as_double(0x7FF0000000000000LL) : hmax;
+        asm volatile("bar.sync 1, %0;" ::"r"(EPI_WARPS * 32) : "memory");
+        if (half == 0 && live) {
+          const double hm = fmax(s_hmax[r], s_hmax[SG_M + r]);
+          SgRow o; o.sexp = sexp_out;
+          o.amax = (float)fmin((hm + pow2(sexp_out - 34)) * (1.0 + 1e-6), 3.0e38);     // what the planes hold: h to within sigma_out 2^-35
+          // an activation is evaluated on z instead of the exact z*: at most e_out away (Lipschitz constant <= 1) plus its own
+          // rounding; the planes then hold it to within sigma_out 2^-35
+          o.err = !(hm <= out_bound * (1.0 + 1e-9)) ? __longlong_as_double(0x7FF0000000000000LL)
+                                                   : e_out + 4.0 * 2.220446049250313e-16 * fmax(1.0, out_bound) + pow2(sexp_out - 35);
+          ps.rows_out[r_pass] = o;
+        }
+        asm volatile("bar.sync 1, %0;" ::"r"(EPI_WARPS * 32) : "memory");   // s_hmax is rewritten by the next tile
+      } else if (half == 0) {
+        // first maximal NeuralOutput, accepted when it wins by more than twice the error bound (softmax is monotone; |z| < 600
+        // keeps exp() finite and non-zero so the order of the probabilities is the order of the z)
+        bool ok = live && rs.err < 1e300 && e_out < 1e300;
+        int best = -1; double zb = 0, z2 = -1e308, zabs = 0;
+        for (int o = 0; o < nd.n_outputs; o++) {
+          const double z = zl[nd.out_neuron[o]]; zabs = fmax(zabs, fabs(z));
+          if (best < 0) { best = o; zb = z; }
+          else if (z > zb) { z2 = zb; zb = z; best = o; }
+          else z2 = fmax(z2, z);
+        }
+        ok = ok && zabs < 600.0 && (nd.n_outputs == 1 || zb - z2 > 2.0 * e_out + 1e-12 * fmax(1.0, zabs));
+        const long row = ps.row_begin + r_pass;
+        if (ok) write_label(m, a, row, best, best);
+        const unsigned need = __ballot_sync(0xffffffffu, live && !ok), alive = __ballot_sync(0xffffffffu, live);
+        if (a.stats && lane == 0) { atomicAdd(a.stats, (unsigned long long)__popc(alive)); if (need) atomicAdd(a.stats + 1, (unsigned long long)__popc(need)); }
+        if (need) {
+          int base = 0;
+          if (lane == 0) base = atomicAdd(ps.fb_count, __popc(need));
+          base = __shfl_sync(0xffffffffu, base, 0);
+          if (live && !ok) ps.fb_rows[base + __popc(need & ((1u << lane) - 1u))] = (int32_t)row;
+        }
+      }
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TMEM_COLS) : "memory");
+}
+
+}  // namespace sg
+}  // namespace fjp
