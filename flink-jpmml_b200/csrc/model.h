@@ -185,28 +185,36 @@ static constexpr int MAX_LAYERS = 8;
 
 // ---- tensor-core form of a dense layer (tcgen05.mma kind::i8; sliced_gemm.cuh) -----------------------------------------
 // y_j = b_j + sum_i w_ji a_i is evaluated in EXACT integer arithmetic on fixed-point images of the operands:
-//   a_i = sigma * qa_i * 2^-34, sigma = a power of two >= max_i |a_i| of the event's row   (|qa_i| <= 2^34)
-//   w_ji = tau_j * qw_ji * 2^-34, tau_j = a power of two >= max_i |w_ji| of the neuron
-//   q = sum_{k=1..S} d_k 128^(S-k), balanced base-128 digits d_k in [-65, 65]: S = 5 int8 "slices" per operand.
-// Level c = k + l of the digit products accumulates in its own int32 TMEM accumulator (|.| < 2^24 for K <= 512); the pairs
-// with k + l <= S + 1 are kept (15 MMAs per K step), the epilogue recombines the 5 levels in double.  What is lost is bounded
-// per element by SG_CS * sigma * tau_j (digit truncation of both operands + the dropped pairs), so every value carries a
-// rigorous error bound; labels whose top-2 margin is inside it are re-scored by the FP64 kernels in JPMML's order.
-constexpr int SG_S = 5;             // slices per operand
+//   a_i = sigma * qa_i * 2^-Q, sigma = a power of two > max_i |a_i| of the event's row      (|qa_i| <= 2^Q, Q = 8 S - 2)
+//   w_ji = tau * qw_ji * 2^-Q,  tau = a power of two > max_ji |w_ji| of the layer
+//   q = sum_{k<S} d_k 256^k with balanced digits d_k in [-128, 127] (the top one in [-65, 65]): S int8 "slices" per operand --
+//   the bytes of q + 0x808080, the low S - 1 of them XOR 0x80.
+// The digit products of level c = k + l accumulate in their own int32 TMEM accumulator (|.| < 2^25 for K <= 256); the pairs of
+// the S most significant levels are kept (S (S + 1) / 2 MMAs per K step) and the epilogue recombines them.  What is lost is
+// bounded per element by SG_CS * sigma * tau (digit truncation of both operands: 2 x 2^-(Q+1); dropped pairs: 2 (S - 1) x
+// 2^-(Q+1)), so every value carries a rigorous error bound; labels whose top-2 margin is inside it are re-scored by the FP64
+// kernels in JPMML's order.  S = 4 (30-bit operands, 10 MMAs per K step) keeps the re-scored share of the C5 MLP near 1e-3;
+// S = 5 brings it to 1e-5 for 50 % more tensor work and 25 % more plane traffic.
+constexpr int SG_S = 4;             // slices (base-256 digits) per operand: 4 or 5
 constexpr int SG_M = 128;           // events per tile (UMMA M)
 constexpr int SG_NC = 32;           // output neurons per accumulator set (UMMA N)
 constexpr int SG_KC = 64;           // input neurons per pipeline stage (two K = 32 MMA steps)
-constexpr int SG_QBITS = 34;        // |q| <= 2^34
-constexpr double SG_CS = 6.3 * 2.9103830456733704e-11;   // (1 + 1 + 4.2 + slack) * 2^-35: see DESIGN.md
+constexpr int SG_QBITS = 8 * SG_S - 2;        // |q| <= 2^Q
+constexpr double SG_CS = (2.0 * SG_S + 0.5) / (double)(1ULL << (8 * SG_S - 1));   // (2 + 2 (S - 1) + slack) * 2^-(Q+1): see DESIGN.md
 struct SgLayer {
   int32_t K, Kp, N, Np, act, last;     // Kp = K rounded up to SG_KC (zero digits), Np = N rounded up to SG_NC
   int64_t w_off;       // bytes into SgDesc::weights: [Np/32][Kp/64][S][4][32][16] int8 -- one (nc, kc) stage = S * 2048 contiguous bytes
-  int64_t tau_off;     // index into SgDesc::tau_exp (Np entries: exponent of tau_j)
+  int64_t tau_off;     // index into SgDesc::tau_exp (Np entries, all equal to tau_max_exp: one scale per layer)
   int64_t b_off;       // index into NeuralDesc::biases (N entries) / RegressionDesc::intercept
   double amax, bmax;   // max_j sum_i |w_ji| (rounded up), max_j |b_j|
   int32_t tau_max_exp, norm;
 };
-struct SgDesc { int enabled, n_layers; SgLayer layers[MAX_LAYERS]; const int8_t* weights; const int32_t* tau_exp; };
+struct SgDesc {
+  int enabled, n_layers;
+  int inputs_identity;    // NeuralInput i is a plain FieldRef to vector slot i (no mapMissingTo): rows can be read straight from X
+  int pad;
+  SgLayer layers[MAX_LAYERS]; const int8_t* weights; const int32_t* tau_exp;
+};
 struct SgRow { double err; float amax; int32_t sexp; };   // per event between layers: error bound so far (inf = not on this path), max |a_i|, exponent of sigma
 
 struct NeuralDesc {

@@ -1140,8 +1140,10 @@ void compile_general_regression(const XNode& m, Builder& b) {
 // ---------------------------------------------------------------------------------------------- tensor-core form of dense layers
 // model.h "tensor-core form": fixed-point images of a weight matrix, cut into SG_S balanced base-128 digits per weight.
 void sg_digits(long long q, int8_t* d /* d[0] = most significant */) {
-  for (int k = SG_S - 1; k > 0; k--) { long long t = q + 64; d[k] = (int8_t)((t & 127) - 64); q = t >> 7; }
-  d[0] = (int8_t)q;
+  long long bias = 0; for (int k = 0; k < SG_S - 1; k++) bias |= 0x80LL << (8 * k);
+  const long long t = q + bias;                          // bytes 0 .. S-2 of t are d_k + 128, the rest is the top digit
+  for (int k = 0; k < SG_S - 1; k++) d[SG_S - 1 - k] = (int8_t)(int)(((t >> (8 * k)) & 255) - 128);
+  d[0] = (int8_t)(t >> (8 * (SG_S - 1)));
 }
 // W: N x K row-major.  Appends the layer's slices / tau exponents and fills its SgLayer; false when a weight is not finite.
 bool sg_add_layer(const double* W, const double* bias, int N, int K, SgLayer& ly, std::vector<int8_t>& SW, std::vector<int32_t>& TAU) {
@@ -1149,25 +1151,27 @@ bool sg_add_layer(const double* W, const double* bias, int N, int K, SgLayer& ly
   ly.w_off = (int64_t)SW.size(); ly.tau_off = (int64_t)TAU.size();
   const int n_nc = ly.Np / SG_NC, n_kc = ly.Kp / SG_KC;
   SW.resize(SW.size() + (size_t)n_nc * n_kc * SG_S * 2048, 0); TAU.resize(TAU.size() + ly.Np, 0);
-  int8_t* base = SW.data() + ly.w_off; double amax = 0, bmax = 0; int tmax = -10000;
+  int8_t* base = SW.data() + ly.w_off; double amax = 0, bmax = 0, wmax = 0;
   for (int j = 0; j < N; j++) {
-    double rowmax = 0, rowsum = 0;
-    for (int i = 0; i < K; i++) { double w = W[(size_t)j * K + i]; if (!std::isfinite(w)) return false; rowmax = std::max(rowmax, std::fabs(w)); rowsum += std::fabs(w); }
+    double rowsum = 0;
+    for (int i = 0; i < K; i++) { double w = W[(size_t)j * K + i]; if (!std::isfinite(w)) return false; wmax = std::max(wmax, std::fabs(w)); rowsum += std::fabs(w); }
     if (!std::isfinite(bias[j])) return false;
-    int e = 0; if (rowmax > 0) std::frexp(rowmax, &e);          // rowmax = f * 2^e, f in [0.5, 1): tau = 2^e >= rowmax
-    if (e < -400 || e > 400) return false;
-    TAU[ly.tau_off + j] = e; tmax = std::max(tmax, e);
     amax = std::max(amax, rowsum * (1.0 + 1e-12)); bmax = std::max(bmax, std::fabs(bias[j]));
+  }
+  int e = 0; if (wmax > 0) std::frexp(wmax, &e);          // wmax = f * 2^e, f in [0.5, 1): tau = 2^e > wmax
+  if (e < -400 || e > 400) return false;
+  for (int j = 0; j < ly.Np; j++) TAU[ly.tau_off + j] = e;
+  for (int j = 0; j < N; j++) {
     const int nc = j / SG_NC, jn = j % SG_NC;
     for (int i = 0; i < K; i++) {
-      long long q = std::llrint(std::ldexp(W[(size_t)j * K + i], SG_QBITS - e));   // exact scaling, one rounding: |w / tau - q 2^-34| <= 2^-35
+      long long q = std::llrint(std::ldexp(W[(size_t)j * K + i], SG_QBITS - e));   // exact scaling, one rounding: |w / tau - q 2^-Q| <= 2^-(Q+1)
       int8_t d[SG_S]; sg_digits(q, d);
       const int kc = i / SG_KC, kb = i % SG_KC;
       int8_t* stage = base + ((size_t)nc * n_kc + kc) * SG_S * 2048;
       for (int sl = 0; sl < SG_S; sl++) stage[(size_t)sl * 2048 + (kb / 16) * (SG_NC * 16) + jn * 16 + (kb % 16)] = d[sl];
     }
   }
-  ly.amax = amax; ly.bmax = bmax; ly.tau_max_exp = tmax == -10000 ? 0 : tmax;
+  ly.amax = amax; ly.bmax = bmax; ly.tau_max_exp = e;
   return true;
 }
 
@@ -1270,6 +1274,8 @@ void compile_neural(const XNode& m, Builder& b) {
       sl.act = ly.act; sl.last = l == nl - 1; sl.norm = ly.norm; sl.b_off = ly.b_off;
     }
     sg.enabled = ok ? 1 : 0; sg.n_layers = ok ? nl : 0;
+    sg.inputs_identity = 1;
+    for (size_t i = 0; i < inputs.size(); i++) if (inputs[i].kind != NI_FIELDREF || inputs[i].slot != (int)i || inputs[i].has_map_missing) sg.inputs_identity = 0;
     if (!ok) { SW.clear(); TAU.clear(); }
   }
   b.put(&d.inputs, inputs); b.put(&d.pts, pts); b.put(&d.weights, W); b.put(&d.weights_t, WT); b.put(&d.biases, B); b.put(&d.out_neuron, out_neuron);

@@ -37,14 +37,17 @@ static cudaError_t launch_sliced_plan(const DeviceModel& m, const BatchArgs& a, 
   uint8_t* base = static_cast<uint8_t*>(scratch); const SgDesc& sg = m.nn.sg;
   int32_t* fb_count = reinterpret_cast<int32_t*>(base); int32_t* fb_rows = reinterpret_cast<int32_t*>(base + p.off_fb_rows);
   cudaError_t e = cudaMemsetAsync(fb_count, 0, 4, s); if (e != cudaSuccess) return e;
-  cudaFuncSetAttribute(sg::sg_layer_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_smem_optin);
-  cudaFuncSetAttribute(sg::sg_layer_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_smem_optin);
+#define FJP_SG_ATTR(MM) cudaFuncSetAttribute(sg::sg_layer_kernel<sg::MM>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_smem_optin)
+  FJP_SG_ATTR(M_RELU); FJP_SG_ATTR(M_IDENT); FJP_SG_ATTR(M_TANH); FJP_SG_ATTR(M_LOGISTIC); FJP_SG_ATTR(M_LAST);
+#undef FJP_SG_ATTR
   int nl = 0;
   for (long r0 = 0; r0 < a.n; r0 += p.pass_rows) {
     sg::Pass ps{}; ps.row_begin = r0; ps.n_rows = a.n - r0 < p.pass_rows ? a.n - r0 : p.pass_rows; ps.fb_count = fb_count; ps.fb_rows = fb_rows;
     const long tiles = (ps.n_rows + SG_M - 1) / SG_M;
     ps.a_out = reinterpret_cast<int8_t*>(base + p.off_a[0]); ps.rows_out = reinterpret_cast<SgRow*>(base + p.off_rows[0]);
-    sg::sg_slice_inputs_kernel<<<(unsigned)((ps.n_rows * 4 + 255) / 256), 256, 0, s>>>(m, a, ps);
+    const bool plain = sg.inputs_identity && m.prep_identity && a.present == nullptr && a.replace == nullptr;
+    if (plain) sg::sg_slice_inputs_kernel<true><<<(unsigned)((ps.n_rows * 4 + 255) / 256), 256, 0, s>>>(m, a, ps);
+    else sg::sg_slice_inputs_kernel<false><<<(unsigned)((ps.n_rows * 4 + 255) / 256), 256, 0, s>>>(m, a, ps);
     e = cudaGetLastError(); if (e != cudaSuccess) return e;
     nl++;
     for (int l = 0; l < sg.n_layers; l++) {
@@ -53,7 +56,12 @@ static cudaError_t launch_sliced_plan(const DeviceModel& m, const BatchArgs& a, 
       ps.rows_in = reinterpret_cast<const SgRow*>(base + p.off_rows[l & 1]); ps.rows_out = reinterpret_cast<SgRow*>(base + p.off_rows[(l & 1) ^ 1]);
       const uint32_t smem = sg::smem_plan(sg.layers[l].Kp / SG_KC, sg.layers[l].Np).bytes;
       const int grid = (int)(tiles < g_num_sms ? tiles : g_num_sms);
-      if (last) sg::sg_layer_kernel<true><<<grid, sg::THREADS, smem, s>>>(m, a, ps); else sg::sg_layer_kernel<false><<<grid, sg::THREADS, smem, s>>>(m, a, ps);
+      const int act = sg.layers[l].act;
+      if (last) sg::sg_layer_kernel<sg::M_LAST><<<grid, sg::THREADS, smem, s>>>(m, a, ps);
+      else if (act == ACT_RECTIFIER) sg::sg_layer_kernel<sg::M_RELU><<<grid, sg::THREADS, smem, s>>>(m, a, ps);
+      else if (act == ACT_IDENTITY) sg::sg_layer_kernel<sg::M_IDENT><<<grid, sg::THREADS, smem, s>>>(m, a, ps);
+      else if (act == ACT_TANH) sg::sg_layer_kernel<sg::M_TANH><<<grid, sg::THREADS, smem, s>>>(m, a, ps);
+      else sg::sg_layer_kernel<sg::M_LOGISTIC><<<grid, sg::THREADS, smem, s>>>(m, a, ps);
       e = cudaGetLastError(); if (e != cudaSuccess) return e;
       nl++;
     }

@@ -14,27 +14,28 @@
 //
 // Kernels per pass of <= 8 tiles per SM (activations of a pass stay in L2 / HBM between the layer launches):
 //   sg_slice_inputs_kernel  NeuralInputs (same FP64 code as the exact kernels) -> row scale sigma -> 5 digit planes
-//   sg_layer_kernel<LAST>   one launch per layer; CTA = 128 events (UMMA M) x all output neurons in chunks of 32 (UMMA N):
+//   sg_layer_kernel<MODE>   one launch per layer; CTA = 128 events (UMMA M) x all output neurons in chunks of 32 (UMMA N):
 //       warp 0    producer: the tile's input digit planes (K-chunks of 64, 40 KB each) and the layer's weight digit planes
 //                 (10 KB per (neuron chunk, K chunk)) arrive with cp.async.bulk (TMA unit) on mbarriers; both are stored in
 //                 global memory in exactly the shared-memory image the MMA reads (K-major, no swizzle: 8 x 16 B core matrices)
 //       warp 1    one lane issues 30 tcgen05.mma (M128 N32 K32, 15 digit pairs x 2 K steps) per stage; tcgen05.commit
 //                 hands smem stages back to the producer and full accumulator sets (double-buffered in TMEM) to the epilogue
-//       warps 2-9 epilogue: tcgen05.ld 5 levels x 16 columns, recombination, bias, activation, re-slicing into the next
+//       warps 2-17 epilogue (two groups of 8, one per accumulator set): tcgen05.ld 5 levels x 8 columns at a time, recombination,
+//                 bias, activation (integer-only for rectifier / identity), re-slicing into the next
 //                 layer's digit planes (coalesced 16-byte stores) or, for the last layer, arg-max + margin test
 #pragma once
 
 namespace fjp {
 namespace sg {
 
-constexpr int THREADS = 320;                 // producer warp, MMA warp, 8 epilogue warps
-constexpr int EPI_WARPS = 8;
+constexpr int THREADS = 576;                 // producer warp, MMA warp, 16 epilogue warps
+constexpr int EPI_WARPS = 16;
 constexpr int NSTAGE = 4;                    // weight stages in flight
 constexpr uint32_t A_CHUNK = SG_S * SG_M * SG_KC;      // 40960 B: one K chunk of a tile, all digit planes
 constexpr uint32_t A_PLANE = SG_M * SG_KC;             // 8192 B
 constexpr uint32_t B_STAGE = SG_S * SG_NC * SG_KC;     // 10240 B
 constexpr uint32_t B_PLANE = SG_NC * SG_KC;            // 2048 B
-constexpr int TMEM_COLS = 512;               // two accumulator sets of SG_S x 32 columns (320 used)
+constexpr int TMEM_COLS = SG_S * SG_NC * 2 <= 256 ? 256 : 512;   // two accumulator sets of SG_S x 32 columns
 constexpr int MAX_KC = 4;                    // K <= 256
 constexpr long PASS_TILES_PER_SM = 8;
 
@@ -48,12 +49,26 @@ struct Pass {
   int32_t* fb_count; int32_t* fb_rows;
 };
 
-__device__ __forceinline__ void digits(long long q, int (&d)[SG_S]) {   // d[0] most significant; q = sum d[k] 128^(S-1-k)
-  long long t = q + 64; d[4] = (int)(t & 127) - 64; int r = (int)(t >> 7);
-  int u = r + 64; d[3] = (u & 127) - 64; r = u >> 7;
-  u = r + 64; d[2] = (u & 127) - 64; r = u >> 7;
-  u = r + 64; d[1] = (u & 127) - 64; r = u >> 7;
-  d[0] = r;
+// Balanced base-256 digits of four fixed-point values at once, written as byte lanes of the S plane words:
+// q + 0x808080 has the bytes d_k + 128 (k < S - 1) and the top digit above them; XOR 0x80 turns a byte into the int8 digit.  The
+// 4 x 4 byte transpose (value-major -> plane-major) is 8 PRMTs (S = 5: 3 more for the fifth digit).  w[0] = most significant plane.
+__device__ __forceinline__ void pack4(long long q0, long long q1, long long q2, long long q3, uint32_t (&w)[SG_S][4], int wi) {
+  if constexpr (SG_S == 5) {
+    const long long B = 0x80808080LL;
+    const long long p0 = q0 + B, p1 = q1 + B, p2 = q2 + B, p3 = q3 + B;
+    const uint32_t l0 = (uint32_t)p0 ^ 0x80808080u, l1 = (uint32_t)p1 ^ 0x80808080u, l2 = (uint32_t)p2 ^ 0x80808080u, l3 = (uint32_t)p3 ^ 0x80808080u;
+    const uint32_t t0 = __byte_perm(l0, l1, 0x5140), t1 = __byte_perm(l2, l3, 0x5140), t2 = __byte_perm(l0, l1, 0x7362), t3 = __byte_perm(l2, l3, 0x7362);
+    w[4][wi] = __byte_perm(t0, t1, 0x5410); w[3][wi] = __byte_perm(t0, t1, 0x7632);
+    w[2][wi] = __byte_perm(t2, t3, 0x5410); w[1][wi] = __byte_perm(t2, t3, 0x7632);
+    const uint32_t u0 = __byte_perm((uint32_t)(p0 >> 32), (uint32_t)(p1 >> 32), 0x0040), u1 = __byte_perm((uint32_t)(p2 >> 32), (uint32_t)(p3 >> 32), 0x0040);
+    w[0][wi] = __byte_perm(u0, u1, 0x5410);
+  } else {   // S = 4: |q| <= 2^30, everything fits 32 bits; byte 3 of q + 0x808080 IS the (signed) top digit
+    const uint32_t l0 = ((uint32_t)q0 + 0x00808080u) ^ 0x00808080u, l1 = ((uint32_t)q1 + 0x00808080u) ^ 0x00808080u;
+    const uint32_t l2 = ((uint32_t)q2 + 0x00808080u) ^ 0x00808080u, l3 = ((uint32_t)q3 + 0x00808080u) ^ 0x00808080u;
+    const uint32_t t0 = __byte_perm(l0, l1, 0x5140), t1 = __byte_perm(l2, l3, 0x5140), t2 = __byte_perm(l0, l1, 0x7362), t3 = __byte_perm(l2, l3, 0x7362);
+    w[SG_S - 1][wi] = __byte_perm(t0, t1, 0x5410); w[SG_S - 2][wi] = __byte_perm(t0, t1, 0x7632);
+    w[SG_S - 3][wi] = __byte_perm(t2, t3, 0x5410); w[0][wi] = __byte_perm(t2, t3, 0x7632);
+  }
 }
 __device__ __forceinline__ double pow2(int e) { return __longlong_as_double((long long)(e + 1023) << 52); }   // -1022 <= e <= 1023
 // smallest power-of-two exponent e with 2^e > v (v >= 0, finite); v == 0 -> 0
@@ -79,46 +94,68 @@ __device__ double input_value(const DeviceModel& m, const BatchArgs& a, long row
   return out;
 }
 
-// 4 lanes per event; lane q takes the 16-input groups q, q + 4, ...  Two sweeps over the inputs: row maximum, then digits.
+// 4 lanes per event: lane q takes inputs 16 g + 4 q .. + 3 of every 16-input group g, so a quad reads 128 contiguous bytes
+// of the row and writes one 16-byte unit of every plane (a warp: 8 rows = 128 contiguous bytes per plane and group).  Two
+// sweeps over the inputs: row maximum, then digits.
+// PLAIN: every NeuralInput is a FieldRef to the vector slot of the same index, the fields are plain doubles and the batch is
+// dense (no present bits, no replaceNan) -- the rows are read straight from X with 16-byte loads.
+template <bool PLAIN>
 __global__ void __launch_bounds__(256) sg_slice_inputs_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, const Pass ps) {
   const SgLayer& L0 = m.nn.sg.layers[0];
-  const int groups = L0.Kp / 16, n_kc = L0.Kp / SG_KC;
+  const int groups = L0.Kp / 16, n_kc = L0.Kp / SG_KC, n_in = m.nn.n_inputs;
   const long t = blockIdx.x * (long)blockDim.x + threadIdx.x;
   const long r_pass = t >> 2; const int q4 = (int)(t & 3);
   const bool live = r_pass < ps.n_rows;
   const long row = ps.row_begin + (live ? r_pass : 0);
+  const double* xrow = a.X + row * (long)m.F;
+  const bool vec_ok = PLAIN && (m.F & 1) == 0;     // rows start 16-byte aligned
+  auto load4 = [&](int g, double (&v)[4], int& fl) {
+    const int i0 = g * 16 + q4 * 4;
+    if (PLAIN) {
+      if (vec_ok && i0 + 3 < n_in) {
+        const double2 a0 = __ldg(reinterpret_cast<const double2*>(xrow + i0)), a1 = __ldg(reinterpret_cast<const double2*>(xrow + i0 + 2));
+        v[0] = a0.x; v[1] = a0.y; v[2] = a1.x; v[3] = a1.y;
+      } else {
+#pragma unroll
+        for (int k = 0; k < 4; k++) v[k] = i0 + k < n_in ? __ldg(xrow + i0 + k) : 0.0;
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < 4; k++) v[k] = input_value(m, a, row, i0 + k, fl);
+    }
+  };
   int fl = 0; double amax = 0.0;
-  for (int g = q4; g < groups; g += 4)
-    for (int k = 0; k < 16; k++) { const double v = input_value(m, a, row, g * 16 + k, fl); amax = fmax(amax, fabs(v)); if (!(fabs(v) <= 1e300)) fl |= 4; }
+  for (int g = 0; g < groups; g++) {
+    double v[4]; load4(g, v, fl);
+#pragma unroll
+    for (int k = 0; k < 4; k++) { amax = fmax(amax, fabs(v[k])); if (!(fabs(v[k]) <= 1e300)) fl |= 4; }
+  }
   amax = fmax(amax, __shfl_xor_sync(0xffffffffu, amax, 1)); amax = fmax(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
   fl |= __shfl_xor_sync(0xffffffffu, fl, 1); fl |= __shfl_xor_sync(0xffffffffu, fl, 2);
-  if (q4 == 0 && live && !fl && row_fails_preparation(m, a, row)) fl |= 1;
-  fl = __shfl_sync(0xffffffffu, fl, (threadIdx.x & 31) & ~3);
+  if (!PLAIN) {
+    if (q4 == 0 && live && !fl && row_fails_preparation(m, a, row)) fl |= 1;
+    fl = __shfl_sync(0xffffffffu, fl, (threadIdx.x & 31) & ~3);
+  }
   int sexp = exp_above(amax);
   if (sexp < -400 || sexp > 400) { fl |= 4; sexp = 0; }
   if (!live) return;
+  const double qscale = pow2(SG_QBITS - sexp);
   const long tile = r_pass / SG_M; const int r = (int)(r_pass % SG_M);
-  int8_t* tbase = ps.a_out + (size_t)tile * n_kc * A_CHUNK;
-  for (int g = q4; g < groups; g += 4) {
-    uint32_t w[SG_S][4];
+  int8_t* tbase = ps.a_out + (size_t)tile * n_kc * A_CHUNK + (size_t)r * 16 + (size_t)q4 * 4;
+  for (int g = 0; g < groups; g++) {
+    double v[4]; int dummy = 0; load4(g, v, dummy);
+    long long qv[4];
 #pragma unroll
-    for (int s = 0; s < SG_S; s++) { w[s][0] = 0; w[s][1] = 0; w[s][2] = 0; w[s][3] = 0; }
+    for (int k = 0; k < 4; k++) qv[k] = fl ? 0 : __double2ll_rn(v[k] * qscale);      // |v| < sigma: |q| <= 2^Q, off by at most 1/2
+    uint32_t w[SG_S][4]; pack4(qv[0], qv[1], qv[2], qv[3], w, 0);
+    int8_t* dst = tbase + (size_t)(g >> 2) * A_CHUNK + (size_t)(g & 3) * (SG_M * 16);
 #pragma unroll
-    for (int k = 0; k < 16; k++) {
-      int dummy = 0; const double v = fl ? 0.0 : input_value(m, a, row, g * 16 + k, dummy);
-      const long long qv = __double2ll_rn(scalbn(v, SG_QBITS - sexp));
-      int d[SG_S]; digits(qv, d);
-#pragma unroll
-      for (int s = 0; s < SG_S; s++) w[s][k >> 2] |= (uint32_t)(d[s] & 0xFF) << (8 * (k & 3));
-    }
-    int8_t* dst = tbase + (size_t)(g >> 2) * A_CHUNK + (size_t)(g & 3) * (SG_M * 16) + (size_t)r * 16;
-#pragma unroll
-    for (int s = 0; s < SG_S; s++) *reinterpret_cast<uint4*>(dst + (size_t)s * A_PLANE) = make_uint4(w[s][0], w[s][1], w[s][2], w[s][3]);
+    for (int s = 0; s < SG_S; s++) *reinterpret_cast<uint32_t*>(dst + (size_t)s * A_PLANE) = w[s][0];
   }
   if (q4 == 0) {
     SgRow rs; rs.amax = (float)amax; rs.sexp = sexp;
-    // the planes hold x to within sigma 2^-35 per input; anything irregular sends the event to the FP64 kernels
-    rs.err = fl ? __longlong_as_double(0x7FF0000000000000LL) : pow2(sexp - 35);
+    // the planes hold x to within sigma 2^-(Q+1) per input; anything irregular sends the event to the FP64 kernels
+    rs.err = fl ? __longlong_as_double(0x7FF0000000000000LL) : pow2(sexp - SG_QBITS - 1);
     if ((double)rs.amax < amax) rs.amax = __float_as_uint(rs.amax) == 0x7f7fffffu ? rs.amax : __uint_as_float(__float_as_uint(rs.amax) + 1u);   // round up
     ps.rows_out[r_pass] = rs;
   }
@@ -135,6 +172,11 @@ __device__ __forceinline__ void mma_i8(uint32_t tmem_d, uint64_t da, uint64_t db
                "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %6, %7, %8}, p;\n\t}"
                ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate), "r"(z), "r"(z), "r"(z), "r"(z) : "memory");
 }
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void mma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
@@ -147,20 +189,28 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
                  "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]) : "r"(taddr));
 }
 
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&v)[8]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]) : "r"(taddr));
+}
+
 struct Smem { uint32_t off_b, off_bias, off_tau, off_hmax, off_bars, off_tmem, bytes; };
 __host__ __device__ inline Smem smem_plan(int n_kc, int Np) {
   Smem p; uint32_t o = (uint32_t)n_kc * A_CHUNK;
   p.off_b = o; o += NSTAGE * B_STAGE;
   p.off_bias = o; o += (uint32_t)Np * 8;
   p.off_tau = o; o += (uint32_t)Np * 4; o = (o + 15u) & ~15u;
-  p.off_hmax = o; o += 2u * SG_M * 8u;
+  p.off_hmax = o; o += 4u * SG_M * 8u;
   p.off_bars = o; o += 8u * (2 * MAX_KC + 2 * NSTAGE + 4);
   p.off_tmem = o; o += 16;
   p.bytes = o;
   return p;
 }
 
-template <bool LAST>
+// MODE: what the epilogue does with z.  Rectifier / identity layers re-slice in integer arithmetic; tanh / logistic go through
+// double; the last layer keeps z for the arg-max.
+enum : int { M_RELU = 0, M_IDENT = 1, M_TANH = 2, M_LOGISTIC = 3, M_LAST = 4 };
+template <int MODE>
 __global__ void __launch_bounds__(THREADS, 1) sg_layer_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, const Pass ps) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const NeuralDesc& nd = m.nn; const SgLayer& L = nd.sg.layers[ps.layer];
@@ -168,7 +218,7 @@ __global__ void __launch_bounds__(THREADS, 1) sg_layer_kernel(const __grid_const
   const Smem sp = smem_plan(n_kc, L.Np);
   uint8_t* sA = smem; uint8_t* sB = smem + sp.off_b;
   double* s_bias = reinterpret_cast<double*>(smem + sp.off_bias); int* s_tau = reinterpret_cast<int*>(smem + sp.off_tau);
-  double* s_hmax = reinterpret_cast<double*>(smem + sp.off_hmax);     // [2 column halves][128 events]: largest |h| of the tile (inf = digit overflow)
+  double* s_hmax = reinterpret_cast<double*>(smem + sp.off_hmax);     // [2 groups x 2 column halves][128 events]: largest |h| of the tile (inf = digit overflow)
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + sp.off_bars);
   uint64_t* a_full = bars; uint64_t* a_empty = bars + MAX_KC; uint64_t* b_full = bars + 2 * MAX_KC; uint64_t* b_empty = b_full + NSTAGE;
   uint64_t* t_full = b_empty + NSTAGE; uint64_t* t_empty = t_full + 2;
@@ -180,7 +230,7 @@ __global__ void __launch_bounds__(THREADS, 1) sg_layer_kernel(const __grid_const
   if (tid == 0) {
     for (int i = 0; i < MAX_KC; i++) { mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1); }
     for (int i = 0; i < NSTAGE; i++) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], 1); }
-    for (int i = 0; i < 2; i++) { mbar_init(&t_full[i], 1); mbar_init(&t_empty[i], EPI_WARPS); }
+    for (int i = 0; i < 2; i++) { mbar_init(&t_full[i], 1); mbar_init(&t_empty[i], EPI_WARPS / 2); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -215,128 +265,158 @@ __global__ void __launch_bounds__(THREADS, 1) sg_layer_kernel(const __grid_const
       }
     }
   } else if (warp == 1) {
-    // ===================================================================== MMA issuer (one lane)
-    if (lane == 0) {
-      const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(SG_NC >> 3) << 17) | ((uint32_t)(SG_M >> 4) << 24);   // S32 += S8 x S8, K-major A and B, M128 N32
-      const uint64_t da0 = smem_desc(smem_u32(sA), SG_M * 16), db0 = smem_desc(smem_u32(sB), SG_NC * 16);
-      uint32_t it_b = 0, it_t = 0, it_acc = 0;
-      for (long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it_t++) {
-        for (int nc = 0; nc < n_nc; nc++, it_acc++) {
-          const uint32_t buf = it_acc & 1u;
-          mbar_wait(&t_empty[buf], ((it_acc >> 1) & 1u) ^ 1u);
+    // ===================================================================== MMA issuer
+    // The whole warp walks the loops (so every address below is warp-uniform and lives in uniform registers); one elected lane
+    // issues the tcgen05 instructions.
+    const bool leader = elect_one();
+    const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(SG_NC >> 3) << 17) | ((uint32_t)(SG_M >> 4) << 24);   // S32 += S8 x S8, K-major A and B, M128 N32
+    const uint64_t da0 = smem_desc(smem_u32(sA), SG_M * 16), db0 = smem_desc(smem_u32(sB), SG_NC * 16);
+    uint32_t it_b = 0, it_t = 0, it_acc = 0;
+    for (long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it_t++) {
+      for (int nc = 0; nc < n_nc; nc++, it_acc++) {
+        const uint32_t buf = it_acc & 1u;
+        mbar_wait(&t_empty[buf], ((it_acc >> 1) & 1u) ^ 1u);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t d0 = tmem + buf * (SG_S * SG_NC);
+        for (int kc = 0; kc < n_kc; kc++, it_b++) {
+          const uint32_t st = it_b % NSTAGE;
+          if (nc == 0) mbar_wait(&a_full[kc], it_t & 1u);
+          mbar_wait(&b_full[st], (it_b / NSTAGE) & 1u);
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-          const uint32_t d0 = tmem + buf * (SG_S * SG_NC);
-          for (int kc = 0; kc < n_kc; kc++, it_b++) {
-            const uint32_t st = it_b % NSTAGE;
-            if (nc == 0) mbar_wait(&a_full[kc], it_t & 1u);
-            mbar_wait(&b_full[st], (it_b / NSTAGE) & 1u);
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint64_t da_st = da0 + (uint64_t)(((uint32_t)kc * A_CHUNK) >> 4), db_st = db0 + (uint64_t)((st * B_STAGE) >> 4);
+          const uint32_t first = kc == 0 ? 0u : 1u;
+          if (leader) {
 #pragma unroll
             for (int ks = 0; ks < 2; ks++) {
 #pragma unroll
               for (int k = 0; k < SG_S; k++) {
 #pragma unroll
-                for (int l = 0; l + k < SG_S; l++) {
-                  const uint64_t da = da0 + (uint64_t)(((uint32_t)kc * A_CHUNK + (uint32_t)k * A_PLANE + (uint32_t)ks * 2u * (SG_M * 16)) >> 4);
-                  const uint64_t db = db0 + (uint64_t)((st * B_STAGE + (uint32_t)l * B_PLANE + (uint32_t)ks * 2u * (SG_NC * 16)) >> 4);
-                  mma_i8(d0 + (uint32_t)(k + l) * SG_NC, da, db, idesc, (kc == 0 && ks == 0 && k == 0) ? 0u : 1u);
-                }
+                for (int l = 0; l + k < SG_S; l++)
+                  mma_i8(d0 + (uint32_t)(k + l) * SG_NC, da_st + (uint64_t)(((uint32_t)k * A_PLANE + (uint32_t)ks * 2u * (SG_M * 16)) >> 4),
+                         db_st + (uint64_t)(((uint32_t)l * B_PLANE + (uint32_t)ks * 2u * (SG_NC * 16)) >> 4), idesc, (ks == 0 && k == 0) ? first : 1u);
               }
             }
             mma_commit(&b_empty[st]);                       // the weight stage can be refilled once these MMAs have read it
             if (nc == n_nc - 1) mma_commit(&a_empty[kc]);   // last use of this K chunk of the tile
           }
-          mma_commit(&t_full[buf]);
+          __syncwarp();
         }
+        if (leader) mma_commit(&t_full[buf]);
+        __syncwarp();
       }
     }
   } else {
-    // ===================================================================== epilogue: 8 warps, lane <-> event, 16 columns per thread
-    const int ew = warp - 2, quarter = warp & 3, half = ew >> 2;       // TMEM lanes 32 * (warp % 4) .. + 31 are this warp's
+    // ===================================================================== epilogue: 16 warps, lane <-> event
+    // Two groups of 8 warps, one per accumulator set (group g drains the neuron chunks that land in TMEM buffer g); inside a
+    // group a thread owns one event (TMEM lane) and 16 of the chunk's 32 columns, taken in two rounds of 8.
+    const int ew = warp - 2, quarter = warp & 3, group = (ew >> 2) & 1, half = ew >> 3;   // TMEM lanes 32 * (warp % 4) .. + 31 are this warp's
     const int r = quarter * 32 + lane;
     uint32_t it_acc = 0;
-    const int next_kc = LAST ? 0 : nd.sg.layers[ps.layer + 1].Kp / SG_KC;
-    const bool bounded_act = L.act == ACT_TANH || L.act == ACT_LOGISTIC;
+    const int next_kc = MODE == M_LAST ? 0 : nd.sg.layers[ps.layer + 1].Kp / SG_KC;
+    constexpr bool INT_PATH = MODE == M_RELU || MODE == M_IDENT;
+    constexpr int ACT = MODE == M_TANH ? ACT_TANH : ACT_LOGISTIC;
     for (long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
       const long r_pass = tile * SG_M + r; const bool live = r_pass < ps.n_rows;
       const SgRow rs = ps.rows_in[live ? r_pass : 0];
       const double sigma_in = pow2(rs.sexp);
       // scale of this layer's outputs, known before any of them: |h_j| <= |b_j| + sum_i |w_ji| |a_i| <= bmax + amax_W * max|a|
-      const double out_bound = bounded_act ? 1.0 : L.bmax + L.amax * (double)rs.amax;
+      const double out_bound = INT_PATH || MODE == M_LAST ? L.bmax + L.amax * (double)rs.amax : 1.0;
       int sexp_out = exp_above(out_bound * (1.0 + 1e-9));
-      double hmax = 0.0; bool overflow = !(out_bound < 1e280) || sexp_out < -400 || sexp_out > 400;
+      bool overflow = !(out_bound < 1e280) || sexp_out < -400 || sexp_out > 400;
       if (overflow) sexp_out = 0;
+      const double qscale = pow2(SG_QBITS - sexp_out);          // value -> fixed point of the next layer's planes
+      const double zscale = pow2(rs.sexp + L.tau_max_exp - 2 * SG_QBITS + 8 * (SG_S - 1));  // z - b = V sigma tau 2^-(2Q) 256^(S-1): the kept levels start at 256^(S-1)
+      // V sigma tau 2^-(2Q) 256^(S-1) * 2^(Q - sexp_out) = V >> sh, the same shift for every neuron of the row
+      int sh = sexp_out + (SG_QBITS - 8 * (SG_S - 1)) - rs.sexp - L.tau_max_exp;
+      if (INT_PATH && (sh < 1 || sh > 62)) { overflow = true; sh = 1; }
+      const long long rnd = 1LL << (sh - 1);
+      long long qmax = 0;                                        // largest |q| this thread produced (|h| = q sigma_out 2^-34)
       double zl[16];
       for (int nc = 0; nc < n_nc; nc++, it_acc++) {
         const uint32_t buf = it_acc & 1u;
+        if (buf != (uint32_t)group) continue;                    // the other group's chunk
         mbar_wait(&t_full[buf], (it_acc >> 1) & 1u);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        uint32_t lv[SG_S][16];
-        const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + buf * (SG_S * SG_NC) + (uint32_t)half * 16u;
-#pragma unroll
-        for (int c = 0; c < SG_S; c++) tmem_ld16(taddr + (uint32_t)c * SG_NC, lv[c]);
-        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&t_empty[buf]);          // the accumulator set is in registers: the next chunk may overwrite it
         const int j0 = nc * SG_NC + half * 16;
         uint32_t w[SG_S][4];
 #pragma unroll
-        for (int s = 0; s < SG_S; s++) { w[s][0] = 0; w[s][1] = 0; w[s][2] = 0; w[s][3] = 0; }
+        for (int round = 0; round < 2; round++) {
+          uint32_t lv[SG_S][8];
+          const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + buf * (SG_S * SG_NC) + (uint32_t)half * 16u + (uint32_t)round * 8u;
 #pragma unroll
-        for (int c = 0; c < 16; c++) {
-          const int hi = (int)lv[0][c] * 128 + (int)lv[1][c], mid = (int)lv[2][c] * 128 + (int)lv[3][c], lo = (int)lv[4][c];
-          const double V = fma((double)hi, 2097152.0, fma((double)mid, 128.0, (double)lo));      // exact: |V| < 2^53
-          const double z = fma(V, pow2(rs.sexp + s_tau[j0 + c] - 40), s_bias[j0 + c]);
-          if (LAST) zl[c] = z;
-          else {
-            const double h = (j0 + c < L.N) ? activate(L.act, z, 0.0) : 0.0;
-            hmax = fmax(hmax, fabs(h));
-            const long long qv = __double2ll_rn(scalbn(h, SG_QBITS - sexp_out));
-            if (qv > (1LL << SG_QBITS) || qv < -(1LL << SG_QBITS)) overflow = true;
-            int d[SG_S]; digits(qv, d);
-#pragma unroll
-            for (int s = 0; s < SG_S; s++) w[s][c >> 2] |= (uint32_t)(d[s] & 0xFF) << (8 * (c & 3));
+          for (int c = 0; c < SG_S; c++) tmem_ld8(taddr + (uint32_t)c * SG_NC, lv[c]);
+          asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+          if (round == 1) {
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&t_empty[buf]);          // the accumulator set is in registers: the next chunk may overwrite it
           }
+          long long qv[8];
+#pragma unroll
+          for (int c = 0; c < 8; c++) {
+            const int cc = round * 8 + c, j = j0 + cc;
+            // V = sum_c 256^(S-1-c) L_c   (|V| < 2^(8 S + 16))
+            const int hi = (int)lv[0][c] * 256 + (int)lv[1][c];
+            if (INT_PATH) {
+              // all-integer: V is brought to the next planes' fixed point with one rounding shift (the same for the whole row), the
+              // bias with one rounding conversion: the planes hold h to within sigma_out 2^-Q
+              long long V = hi;
+#pragma unroll
+              for (int lc = 2; lc < SG_S; lc++) V = (V << 8) + (long long)(int)lv[lc][c];
+              long long q = ((V + rnd) >> sh) + __double2ll_rn(s_bias[j] * qscale);
+              if (MODE == M_RELU) q = q < 0 ? 0 : q;
+              qv[c] = q;
+            } else {
+              double V = (double)hi;
+#pragma unroll
+              for (int lc = 2; lc < SG_S; lc++) V = fma(V, 256.0, (double)(int)lv[lc][c]);
+              const double z = fma(V, zscale, s_bias[j]);
+              if (MODE == M_LAST) { zl[cc] = z; qv[c] = 0; }
+              else qv[c] = __double2ll_rn(((j < L.N) ? activate(ACT, z, 0.0) : 0.0) * qscale);
+            }
+            if (MODE != M_LAST) { const long long qa = qv[c] < 0 ? -qv[c] : qv[c]; qmax = qa > qmax ? qa : qmax; }
+          }
+          if (MODE != M_LAST) { pack4(qv[0], qv[1], qv[2], qv[3], w, round * 2); pack4(qv[4], qv[5], qv[6], qv[7], w, round * 2 + 1); }
         }
-        if (!LAST) {
+        if (MODE != M_LAST) {
           // output neuron j is input k = j of the next layer: plane s, K chunk j / 64, 16-byte column (j % 64) / 16, row r
           int8_t* dst = ps.a_out + (size_t)tile * next_kc * A_CHUNK + (size_t)(j0 >> 6) * A_CHUNK + (size_t)((j0 & 63) >> 4) * (SG_M * 16) + (size_t)r * 16;
-          if (j0 < next_kc * SG_KC) {
 #pragma unroll
-            for (int s = 0; s < SG_S; s++) *reinterpret_cast<uint4*>(dst + (size_t)s * A_PLANE) = make_uint4(w[s][0], w[s][1], w[s][2], w[s][3]);
-          }
+          for (int s = 0; s < SG_S; s++) *reinterpret_cast<uint4*>(dst + (size_t)s * A_PLANE) = make_uint4(w[s][0], w[s][1], w[s][2], w[s][3]);
         }
       }
       // error bound of this layer's outputs for the event (model.h): propagated input error + slicing / dropped pairs + FP64 rounding
       // of both this evaluation and the reference's sequential sum
       const double mag = L.bmax + L.amax * (double)rs.amax;
       const double e_out = L.amax * rs.err + (double)L.K * sigma_in * pow2(L.tau_max_exp) * SG_CS + (double)(L.K + 8) * 2.220446049250313e-16 * mag;
-      if (!LAST) {
+      if (MODE != M_LAST) {
         // pad columns of the next layer's planes (Np of this layer < Kp of the next) are zero digits
-        if (half == 0) {
+        if (half == 0 && group == 0) {
           for (int j = L.Np; j < next_kc * SG_KC; j += 16) {
             int8_t* dst = ps.a_out + (size_t)tile * next_kc * A_CHUNK + (size_t)(j >> 6) * A_CHUNK + (size_t)((j & 63) >> 4) * (SG_M * 16) + (size_t)r * 16;
 #pragma unroll
             for (int s = 0; s < SG_S; s++) *reinterpret_cast<uint4*>(dst + (size_t)s * A_PLANE) = make_uint4(0, 0, 0, 0);
           }
         }
-        // the two column halves of an event exchange their largest |h|: the next layer scales ITS outputs from the actual
-        // maximum of its inputs, so the a-priori bounds do not compound from layer to layer
-        s_hmax[half * SG_M + r] = overflow ? __longlong_as_double(0x7FF0000000000000LL) : hmax;
+        // the four threads of an event (2 groups x 2 column halves) exchange their largest |h|: the next layer scales ITS outputs
+        // from the actual maximum of its inputs, so the a-priori bounds do not compound from layer to layer
+        if (qmax > (1LL << SG_QBITS)) overflow = true;
+        s_hmax[(group * 2 + half) * SG_M + r] = overflow ? __longlong_as_double(0x7FF0000000000000LL) : (double)qmax * pow2(sexp_out - SG_QBITS);
         asm volatile("bar.sync 1, %0;" ::"r"(EPI_WARPS * 32) : "memory");
-        if (half == 0 && live) {
-          const double hm = fmax(s_hmax[r], s_hmax[SG_M + r]);
+        if (half == 0 && group == 0 && live) {
+          const double hm = fmax(fmax(s_hmax[r], s_hmax[SG_M + r]), fmax(s_hmax[2 * SG_M + r], s_hmax[3 * SG_M + r]));
           SgRow o; o.sexp = sexp_out;
-          o.amax = (float)fmin((hm + pow2(sexp_out - 34)) * (1.0 + 1e-6), 3.0e38);     // what the planes hold: h to within sigma_out 2^-35
+          o.amax = (float)fmin(hm * (1.0 + 1e-6), 3.0e38);      // largest |a_i| the planes hold
           // an activation is evaluated on z instead of the exact z*: at most e_out away (Lipschitz constant <= 1) plus its own
-          // rounding; the planes then hold it to within sigma_out 2^-35
-          o.err = !(hm <= out_bound * (1.0 + 1e-9)) ? __longlong_as_double(0x7FF0000000000000LL)
-                                                   : e_out + 4.0 * 2.220446049250313e-16 * fmax(1.0, out_bound) + pow2(sexp_out - 35);
+          // rounding; the planes then hold it to within sigma_out 2^-Q
+          o.err = !(hm <= out_bound * (1.0 + 1e-9) + pow2(sexp_out - SG_QBITS + 1)) ? __longlong_as_double(0x7FF0000000000000LL)
+                                                                         : e_out + 4.0 * 2.220446049250313e-16 * fmax(1.0, out_bound) + pow2(sexp_out - SG_QBITS);
           ps.rows_out[r_pass] = o;
         }
         asm volatile("bar.sync 1, %0;" ::"r"(EPI_WARPS * 32) : "memory");   // s_hmax is rewritten by the next tile
-      } else if (half == 0) {
+      }
+      // the last layer has one neuron chunk per tile: the group whose accumulator set it landed in finishes the event
+      if (MODE == M_LAST && half == 0 && group == (int)((it_acc - 1) & 1u)) {
         // first maximal NeuralOutput, accepted when it wins by more than twice the error bound (softmax is monotone; |z| < 600
         // keeps exp() finite and non-zero so the order of the probabilities is the order of the z)
         bool ok = live && rs.err < 1e300 && e_out < 1e300;
