@@ -197,13 +197,14 @@ static constexpr int MAX_LAYERS = 8;
 // S = 5 brings it to 1e-5 for 50 % more tensor work and 25 % more plane traffic.
 constexpr int SG_S = 4;             // slices (base-256 digits) per operand: 4 or 5
 constexpr int SG_M = 128;           // events per tile (UMMA M)
-constexpr int SG_NC = 32;           // output neurons per accumulator set (UMMA N)
+constexpr int SG_NC = SG_S == 4 ? 64 : 32;   // output neurons per accumulator set (UMMA N): two sets of S x N columns fill the 512 TMEM columns.
+                                    // (N = 32 leaves the MMA bound by the shared-memory reads of its 128 x 32 A operand: 40 cycles for 16 of math)
 constexpr int SG_KC = 64;           // input neurons per pipeline stage (two K = 32 MMA steps)
 constexpr int SG_QBITS = 8 * SG_S - 2;        // |q| <= 2^Q
 constexpr double SG_CS = (2.0 * SG_S + 0.5) / (double)(1ULL << (8 * SG_S - 1));   // (2 + 2 (S - 1) + slack) * 2^-(Q+1): see DESIGN.md
 struct SgLayer {
   int32_t K, Kp, N, Np, act, last;     // Kp = K rounded up to SG_KC (zero digits), Np = N rounded up to SG_NC
-  int64_t w_off;       // bytes into SgDesc::weights: [Np/32][Kp/64][S][4][32][16] int8 -- one (nc, kc) stage = S * 2048 contiguous bytes
+  int64_t w_off;       // bytes into SgDesc::weights: [Np/NC][Kp/64][S][4][NC][16] int8 -- one (nc, kc) stage = S * NC * 64 contiguous bytes
   int64_t tau_off;     // index into SgDesc::tau_exp (Np entries, all equal to tau_max_exp: one scale per layer)
   int64_t b_off;       // index into NeuralDesc::biases (N entries) / RegressionDesc::intercept
   double amax, bmax;   // max_j sum_i |w_ji| (rounded up), max_j |b_j|

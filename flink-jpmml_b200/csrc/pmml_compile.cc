@@ -1150,7 +1150,7 @@ bool sg_add_layer(const double* W, const double* bias, int N, int K, SgLayer& ly
   ly.K = K; ly.N = N; ly.Kp = (K + SG_KC - 1) / SG_KC * SG_KC; ly.Np = (N + SG_NC - 1) / SG_NC * SG_NC;
   ly.w_off = (int64_t)SW.size(); ly.tau_off = (int64_t)TAU.size();
   const int n_nc = ly.Np / SG_NC, n_kc = ly.Kp / SG_KC;
-  SW.resize(SW.size() + (size_t)n_nc * n_kc * SG_S * 2048, 0); TAU.resize(TAU.size() + ly.Np, 0);
+  SW.resize(SW.size() + (size_t)n_nc * n_kc * SG_S * (SG_NC * SG_KC), 0); TAU.resize(TAU.size() + ly.Np, 0);
   int8_t* base = SW.data() + ly.w_off; double amax = 0, bmax = 0, wmax = 0;
   for (int j = 0; j < N; j++) {
     double rowsum = 0;
@@ -1167,8 +1167,8 @@ bool sg_add_layer(const double* W, const double* bias, int N, int K, SgLayer& ly
       long long q = std::llrint(std::ldexp(W[(size_t)j * K + i], SG_QBITS - e));   // exact scaling, one rounding: |w / tau - q 2^-Q| <= 2^-(Q+1)
       int8_t d[SG_S]; sg_digits(q, d);
       const int kc = i / SG_KC, kb = i % SG_KC;
-      int8_t* stage = base + ((size_t)nc * n_kc + kc) * SG_S * 2048;
-      for (int sl = 0; sl < SG_S; sl++) stage[(size_t)sl * 2048 + (kb / 16) * (SG_NC * 16) + jn * 16 + (kb % 16)] = d[sl];
+      int8_t* stage = base + ((size_t)nc * n_kc + kc) * SG_S * (SG_NC * SG_KC);
+      for (int sl = 0; sl < SG_S; sl++) stage[(size_t)sl * (SG_NC * SG_KC) + (kb / 16) * (SG_NC * 16) + jn * 16 + (kb % 16)] = d[sl];
     }
   }
   ly.amax = amax; ly.bmax = bmax; ly.tau_max_exp = e;

@@ -24,13 +24,16 @@
 //                 bias, activation (integer-only for rectifier / identity), re-slicing into the next
 //                 layer's digit planes (coalesced 16-byte stores) or, for the last layer, arg-max + margin test
 #pragma once
+#include <type_traits>
 
 namespace fjp {
 namespace sg {
 
 constexpr int THREADS = 576;                 // producer warp, MMA warp, 16 epilogue warps
 constexpr int EPI_WARPS = 16;
-constexpr int NSTAGE = 4;                    // weight stages in flight
+constexpr int NSTAGE = 5;                    // weight stages in flight
+constexpr int COLQ = SG_NC / 16;             // 16-column shares of a neuron chunk
+constexpr int GROUPS = 16 / (4 * COLQ);      // epilogue warp groups: N = 32 -> one group of 8 warps per accumulator set; N = 64 -> all 16 warps on every chunk
 constexpr uint32_t A_CHUNK = SG_S * SG_M * SG_KC;      // 40960 B: one K chunk of a tile, all digit planes
 constexpr uint32_t A_PLANE = SG_M * SG_KC;             // 8192 B
 constexpr uint32_t B_STAGE = SG_S * SG_NC * SG_KC;     // 10240 B
@@ -52,10 +55,11 @@ struct Pass {
 // Balanced base-256 digits of four fixed-point values at once, written as byte lanes of the S plane words:
 // q + 0x808080 has the bytes d_k + 128 (k < S - 1) and the top digit above them; XOR 0x80 turns a byte into the int8 digit.  The
 // 4 x 4 byte transpose (value-major -> plane-major) is 8 PRMTs (S = 5: 3 more for the fifth digit).  w[0] = most significant plane.
-__device__ __forceinline__ void pack4(long long q0, long long q1, long long q2, long long q3, uint32_t (&w)[SG_S][4], int wi) {
+using qint = std::conditional<SG_S == 5, long long, int>::type;   // a fixed-point value: 30 bits + sign for S = 4, 38 for S = 5
+__device__ __forceinline__ void pack4(qint q0, qint q1, qint q2, qint q3, uint32_t (&w)[SG_S][4], int wi) {
   if constexpr (SG_S == 5) {
     const long long B = 0x80808080LL;
-    const long long p0 = q0 + B, p1 = q1 + B, p2 = q2 + B, p3 = q3 + B;
+    const long long p0 = (long long)q0 + B, p1 = q1 + B, p2 = q2 + B, p3 = q3 + B;
     const uint32_t l0 = (uint32_t)p0 ^ 0x80808080u, l1 = (uint32_t)p1 ^ 0x80808080u, l2 = (uint32_t)p2 ^ 0x80808080u, l3 = (uint32_t)p3 ^ 0x80808080u;
     const uint32_t t0 = __byte_perm(l0, l1, 0x5140), t1 = __byte_perm(l2, l3, 0x5140), t2 = __byte_perm(l0, l1, 0x7362), t3 = __byte_perm(l2, l3, 0x7362);
     w[4][wi] = __byte_perm(t0, t1, 0x5410); w[3][wi] = __byte_perm(t0, t1, 0x7632);
@@ -144,9 +148,9 @@ __global__ void __launch_bounds__(256) sg_slice_inputs_kernel(const __grid_const
   int8_t* tbase = ps.a_out + (size_t)tile * n_kc * A_CHUNK + (size_t)r * 16 + (size_t)q4 * 4;
   for (int g = 0; g < groups; g++) {
     double v[4]; int dummy = 0; load4(g, v, dummy);
-    long long qv[4];
+    qint qv[4];
 #pragma unroll
-    for (int k = 0; k < 4; k++) qv[k] = fl ? 0 : __double2ll_rn(v[k] * qscale);      // |v| < sigma: |q| <= 2^Q, off by at most 1/2
+    for (int k = 0; k < 4; k++) qv[k] = fl ? 0 : (qint)__double2ll_rn(v[k] * qscale);      // |v| < sigma: |q| <= 2^Q, off by at most 1/2
     uint32_t w[SG_S][4]; pack4(qv[0], qv[1], qv[2], qv[3], w, 0);
     int8_t* dst = tbase + (size_t)(g >> 2) * A_CHUNK + (size_t)(g & 3) * (SG_M * 16);
 #pragma unroll
@@ -217,7 +221,7 @@ __global__ void __launch_bounds__(THREADS, 1) sg_layer_kernel(const __grid_const
   const int n_kc = L.Kp / SG_KC, n_nc = L.Np / SG_NC;
   const Smem sp = smem_plan(n_kc, L.Np);
   uint8_t* sA = smem; uint8_t* sB = smem + sp.off_b;
-  double* s_bias = reinterpret_cast<double*>(smem + sp.off_bias); int* s_tau = reinterpret_cast<int*>(smem + sp.off_tau);
+  double* s_bias = reinterpret_cast<double*>(smem + sp.off_bias); int* s_tau = reinterpret_cast<int*>(smem + sp.off_tau);   // (the fixed-point biases)
   double* s_hmax = reinterpret_cast<double*>(smem + sp.off_hmax);     // [2 groups x 2 column halves][128 events]: largest |h| of the tile (inf = digit overflow)
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + sp.off_bars);
   uint64_t* a_full = bars; uint64_t* a_empty = bars + MAX_KC; uint64_t* b_full = bars + 2 * MAX_KC; uint64_t* b_empty = b_full + NSTAGE;
@@ -226,11 +230,17 @@ __global__ void __launch_bounds__(THREADS, 1) sg_layer_kernel(const __grid_const
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const long ntiles = (ps.n_rows + SG_M - 1) / SG_M;
 
-  for (int j = tid; j < L.Np; j += THREADS) { s_bias[j] = j < L.N ? nd.biases[L.b_off + j] : 0.0; s_tau[j] = j < L.N ? nd.sg.tau_exp[L.tau_off + j] : 0; }
+  // biases twice: as doubles (double-precision epilogues) and as 31-bit fixed point b_j 2^(30 - E_b), 2^E_b > max_j |b_j| (the
+  // integer epilogue shifts them to each event's output scale)
+  const int e_b = exp_above(L.bmax);
+  for (int j = tid; j < L.Np; j += THREADS) {
+    const double b = j < L.N ? nd.biases[L.b_off + j] : 0.0;
+    s_bias[j] = b; s_tau[j] = __double2int_rn(b * pow2(30 - e_b));
+  }
   if (tid == 0) {
     for (int i = 0; i < MAX_KC; i++) { mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1); }
     for (int i = 0; i < NSTAGE; i++) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], 1); }
-    for (int i = 0; i < 2; i++) { mbar_init(&t_full[i], 1); mbar_init(&t_empty[i], EPI_WARPS / 2); }
+    for (int i = 0; i < 2; i++) { mbar_init(&t_full[i], 1); mbar_init(&t_empty[i], EPI_WARPS / GROUPS); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -307,9 +317,10 @@ __global__ void __launch_bounds__(THREADS, 1) sg_layer_kernel(const __grid_const
     }
   } else {
     // ===================================================================== epilogue: 16 warps, lane <-> event
-    // Two groups of 8 warps, one per accumulator set (group g drains the neuron chunks that land in TMEM buffer g); inside a
-    // group a thread owns one event (TMEM lane) and 16 of the chunk's 32 columns, taken in two rounds of 8.
-    const int ew = warp - 2, quarter = warp & 3, group = (ew >> 2) & 1, half = ew >> 3;   // TMEM lanes 32 * (warp % 4) .. + 31 are this warp's
+    // A thread owns one event (TMEM lane) and 16 columns of a neuron chunk, taken in two rounds of 8.  N = 64: all 16 warps drain
+    // every chunk (4 lane quarters x 4 column shares).  N = 32: two groups of 8 warps, one per accumulator set.
+    const int ew = warp - 2, quarter = warp & 3;                                  // TMEM lanes 32 * (warp % 4) .. + 31 are this warp's
+    const int group = GROUPS == 2 ? (ew >> 2) & 1 : 0, half = GROUPS == 2 ? ew >> 3 : ew >> 2;   // half: which 16 columns of the chunk
     const int r = quarter * 32 + lane;
     uint32_t it_acc = 0;
     const int next_kc = MODE == M_LAST ? 0 : nd.sg.layers[ps.layer + 1].Kp / SG_KC;
@@ -330,11 +341,15 @@ __global__ void __launch_bounds__(THREADS, 1) sg_layer_kernel(const __grid_const
       int sh = sexp_out + (SG_QBITS - 8 * (SG_S - 1)) - rs.sexp - L.tau_max_exp;
       if (INT_PATH && (sh < 1 || sh > 62)) { overflow = true; sh = 1; }
       const long long rnd = 1LL << (sh - 1);
+      int shb = sexp_out - e_b + 30 - SG_QBITS;                 // b_j 2^(30 - E_b) -> b_j 2^(Q - sexp_out)
+      if (INT_PATH && (shb < 0 || shb > 31)) { if (shb < 0) overflow = true; shb = shb < 0 ? 0 : 31; }
+      const int rndb = shb > 0 ? (1 << (shb - 1)) : 0;
+      uint32_t ovf = 0; int qmax32 = 0;
       long long qmax = 0;                                        // largest |q| this thread produced (|h| = q sigma_out 2^-34)
       double zl[16];
       for (int nc = 0; nc < n_nc; nc++, it_acc++) {
         const uint32_t buf = it_acc & 1u;
-        if (buf != (uint32_t)group) continue;                    // the other group's chunk
+        if (GROUPS == 2 && buf != (uint32_t)group) continue;     // the other group's chunk
         mbar_wait(&t_full[buf], (it_acc >> 1) & 1u);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const int j0 = nc * SG_NC + half * 16;
@@ -351,7 +366,7 @@ __global__ void __launch_bounds__(THREADS, 1) sg_layer_kernel(const __grid_const
             __syncwarp();
             if (lane == 0) mbar_arrive(&t_empty[buf]);          // the accumulator set is in registers: the next chunk may overwrite it
           }
-          long long qv[8];
+          qint qv[8];
 #pragma unroll
           for (int c = 0; c < 8; c++) {
             const int cc = round * 8 + c, j = j0 + cc;
@@ -359,22 +374,37 @@ __global__ void __launch_bounds__(THREADS, 1) sg_layer_kernel(const __grid_const
             const int hi = (int)lv[0][c] * 256 + (int)lv[1][c];
             if (INT_PATH) {
               // all-integer: V is brought to the next planes' fixed point with one rounding shift (the same for the whole row), the
-              // bias with one rounding conversion: the planes hold h to within sigma_out 2^-Q
-              long long V = hi;
-#pragma unroll
-              for (int lc = 2; lc < SG_S; lc++) V = (V << 8) + (long long)(int)lv[lc][c];
-              long long q = ((V + rnd) >> sh) + __double2ll_rn(s_bias[j] * qscale);
-              if (MODE == M_RELU) q = q < 0 ? 0 : q;
-              qv[c] = q;
+              // bias with another: the planes hold h to within 1.5 sigma_out 2^-Q
+              long long V;
+              if constexpr (SG_S == 4) V = (long long)hi * 65536 + ((long long)(int)lv[2][c] * 256 + (long long)(int)lv[3][c] + rnd);
+              else { V = hi; for (int lc = 2; lc < SG_S; lc++) V = (V << 8) + (long long)(int)lv[lc][c]; V += rnd; }
+              const long long vs = V >> sh;
+              const int bq = (s_tau[j] + rndb) >> shb;
+              if constexpr (SG_S == 4) {
+                const int lo = (int)vs;
+                ovf |= (uint32_t)(vs >> 32) ^ (uint32_t)(lo >> 31);          // non-zero: the value left 32 bits (a violated bound)
+                int q = lo + bq;
+                if (MODE == M_RELU) q = max(q, 0);
+                qmax32 = max(qmax32, MODE == M_RELU ? q : abs(q));
+                qv[c] = q;
+              } else {
+                long long q = vs + bq;
+                if (MODE == M_RELU) q = q < 0 ? 0 : q;
+                const long long qa = q < 0 ? -q : q; qmax = qa > qmax ? qa : qmax;
+                qv[c] = (qint)q;
+              }
             } else {
               double V = (double)hi;
 #pragma unroll
               for (int lc = 2; lc < SG_S; lc++) V = fma(V, 256.0, (double)(int)lv[lc][c]);
               const double z = fma(V, zscale, s_bias[j]);
               if (MODE == M_LAST) { zl[cc] = z; qv[c] = 0; }
-              else qv[c] = __double2ll_rn(((j < L.N) ? activate(ACT, z, 0.0) : 0.0) * qscale);
+              else {
+                const long long q = __double2ll_rn(((j < L.N) ? activate(ACT, z, 0.0) : 0.0) * qscale);
+                const long long qa = q < 0 ? -q : q; qmax = qa > qmax ? qa : qmax;
+                qv[c] = (qint)q;
+              }
             }
-            if (MODE != M_LAST) { const long long qa = qv[c] < 0 ? -qv[c] : qv[c]; qmax = qa > qmax ? qa : qmax; }
           }
           if (MODE != M_LAST) { pack4(qv[0], qv[1], qv[2], qv[3], w, round * 2); pack4(qv[4], qv[5], qv[6], qv[7], w, round * 2 + 1); }
         }
@@ -400,23 +430,25 @@ __global__ void __launch_bounds__(THREADS, 1) sg_layer_kernel(const __grid_const
         }
         // the four threads of an event (2 groups x 2 column halves) exchange their largest |h|: the next layer scales ITS outputs
         // from the actual maximum of its inputs, so the a-priori bounds do not compound from layer to layer
+        if (ovf) overflow = true;
+        if ((long long)qmax32 > qmax) qmax = qmax32;
         if (qmax > (1LL << SG_QBITS)) overflow = true;
-        s_hmax[(group * 2 + half) * SG_M + r] = overflow ? __longlong_as_double(0x7FF0000000000000LL) : (double)qmax * pow2(sexp_out - SG_QBITS);
+        s_hmax[(group * COLQ + half) * SG_M + r] = overflow ? __longlong_as_double(0x7FF0000000000000LL) : (double)qmax * pow2(sexp_out - SG_QBITS);
         asm volatile("bar.sync 1, %0;" ::"r"(EPI_WARPS * 32) : "memory");
         if (half == 0 && group == 0 && live) {
           const double hm = fmax(fmax(s_hmax[r], s_hmax[SG_M + r]), fmax(s_hmax[2 * SG_M + r], s_hmax[3 * SG_M + r]));
           SgRow o; o.sexp = sexp_out;
           o.amax = (float)fmin(hm * (1.0 + 1e-6), 3.0e38);      // largest |a_i| the planes hold
           // an activation is evaluated on z instead of the exact z*: at most e_out away (Lipschitz constant <= 1) plus its own
-          // rounding; the planes then hold it to within sigma_out 2^-Q
+          // rounding; the planes then hold it to within 1.5 sigma_out 2^-Q
           o.err = !(hm <= out_bound * (1.0 + 1e-9) + pow2(sexp_out - SG_QBITS + 1)) ? __longlong_as_double(0x7FF0000000000000LL)
-                                                                         : e_out + 4.0 * 2.220446049250313e-16 * fmax(1.0, out_bound) + pow2(sexp_out - SG_QBITS);
+                                                                         : e_out + 4.0 * 2.220446049250313e-16 * fmax(1.0, out_bound) + 1.5 * pow2(sexp_out - SG_QBITS);
           ps.rows_out[r_pass] = o;
         }
         asm volatile("bar.sync 1, %0;" ::"r"(EPI_WARPS * 32) : "memory");   // s_hmax is rewritten by the next tile
       }
       // the last layer has one neuron chunk per tile: the group whose accumulator set it landed in finishes the event
-      if (MODE == M_LAST && half == 0 && group == (int)((it_acc - 1) & 1u)) {
+      if (MODE == M_LAST && half == 0 && group == (GROUPS == 2 ? (int)((it_acc - 1) & 1u) : 0)) {
         // first maximal NeuralOutput, accepted when it wins by more than twice the error bound (softmax is monotone; |z| < 600
         // keeps exp() finite and non-zero so the order of the probabilities is the order of the z)
         bool ok = live && rs.err < 1e300 && e_out < 1e300;
