@@ -159,6 +159,7 @@ def measure_config(torch, np, eng, L, stream, dev, spec, seed, reps, want_parity
         run()
     torch.cuda.synchronize(dev)
     l0 = eng.launch_count
+    t0 = eng.fast_path_counts
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with torch.cuda.stream(stream):
         e0.record(stream)
@@ -167,8 +168,17 @@ def measure_config(torch, np, eng, L, stream, dev, spec, seed, reps, want_parity
         e1.record(stream)
     torch.cuda.synchronize(dev)
     ms = e0.elapsed_time(e1) / reps
+    t1 = eng.fast_path_counts
     out = {"workload": desc, "events_per_gpu_per_step": n, "ms_per_step": ms, "rows_scored_ok": int((T == 0).sum().item()),
            "gpu_launches_per_step": (eng.launch_count - l0) // reps, "model": m.describe, "work": work}
+    if t1[0] > t0[0]:   # the tensor-core path took the batch: how many events its margin test handed back to the FP64 kernels
+        out["tensor_path"] = {"events": (t1[0] - t0[0]) // reps, "rescored_fp64": (t1[1] - t0[1]) // reps,
+                              "rescored_fraction": (t1[1] - t0[1]) / max(1, t1[0] - t0[0]),
+                              "arithmetic": "tcgen05.mma kind::i8 on 4 base-256 digit planes per operand, exact int32 accumulation in TMEM; labels decided only outside the proven error bound"}
+    if t1[2] > t0[2]:   # the fused-multiply-add path of the dense tile kernel took the batch
+        out["fma_path"] = {"events": (t1[2] - t0[2]) // reps, "rescored_unfused": (t1[3] - t0[3]) // reps,
+                           "rescored_fraction": (t1[3] - t0[3]) / max(1, t1[2] - t0[2]),
+                           "arithmetic": "FP64 fused multiply-add; labels decided only outside the rounding bound between the two evaluation orders, the rest re-scored unfused in JPMML's order"}
     if want_parity:
         from oracle import oracle   # checker only: a 2048-event sample of this very batch against the CPU restatement
         ns = 2048
@@ -193,11 +203,17 @@ def config_rooflines(rate, work, pk):
         tf = rate * work["flop"] / 1e12
         r.update({"algorithmic_tflops": tf, "frac_of_fp64_fma_peak": tf / micro["fp64_fma_TFLOPs"] if micro.get("fp64_fma_TFLOPs") else None})
         if work["bound"] == "tensor":
+            # the path computes in int8 (dense int8 rate = 2 x the bf16 rate on this chip; MEASURED_PEAKS.json holds the bf16 figure).
+            # Two readings: the algorithmic FP64-equivalent work against the bf16 peak, and the int8 operations the tensor pipe
+            # really executes (10 digit-pair products per multiply-add at S = 4) against 2 x that peak.
             r["frac_of_bf16_tensor_sustained"] = tf / pk["bf16_tflops_sustained"]
+            r["int8_tensor_tops_executed"] = tf * 10.0
+            r["frac_of_int8_tensor_peak"] = tf * 10.0 / (2.0 * pk["bf16_tflops_sustained"])
+            r["int8_peak_note"] = "2 x bf16_tflops_sustained of MEASURED_PEAKS.json (nominal dense int8 = 2 x bf16 on B200)"
     b = work["bound"]
     r["binding"] = b
     r["frac"] = {"hbm": r["hbm_frac"], "fp64": r.get("frac_of_fp64_fma_peak"), "gather": r.get("frac_of_l2_gather_peak"),
-                 "tensor": r.get("frac_of_bf16_tensor_sustained"), "latency": None}[b]
+                 "tensor": r.get("frac_of_int8_tensor_peak"), "latency": None}[b]
     return r
 
 

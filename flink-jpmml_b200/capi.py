@@ -50,7 +50,7 @@ def lib():
         "fjp_engine_sync": (i32, [vp]),
         "fjp_engine_launch_count": (lng, [vp]),
         "fjp_engine_status_counts": (None, [vp, C.POINTER(C.c_uint64)]),
-        "fjp_engine_tensor_path_counts": (i32, [vp, C.POINTER(C.c_uint64)]),
+        "fjp_engine_fast_path_counts": (i32, [vp, C.POINTER(C.c_uint64)]),
         "fjp_model_compile": (i32, [vp, cp, sz, C.POINTER(vp), cp, sz]),
         "fjp_model_retain": (None, [vp]),
         "fjp_model_release": (None, [vp]),
@@ -87,7 +87,7 @@ def lib():
 
 
 EXPORTS = ["fjp_version", "fjp_last_error", "fjp_max_inflight", "fjp_engine_create", "fjp_engine_destroy", "fjp_engine_device",
-           "fjp_engine_sync", "fjp_engine_launch_count", "fjp_engine_status_counts", "fjp_engine_tensor_path_counts", "fjp_model_compile", "fjp_model_retain", "fjp_model_release",
+           "fjp_engine_sync", "fjp_engine_launch_count", "fjp_engine_status_counts", "fjp_engine_fast_path_counts", "fjp_model_compile", "fjp_model_retain", "fjp_model_release",
            "fjp_model_replicate", "fjp_model_num_fields", "fjp_model_field_name", "fjp_model_name", "fjp_model_family",
            "fjp_model_num_labels", "fjp_model_label", "fjp_model_num_segments", "fjp_model_describe", "fjp_model_device_bytes",
            "fjp_table_add", "fjp_table_del", "fjp_table_get", "fjp_table_size", "fjp_table_epoch", "fjp_host_alloc",
@@ -206,9 +206,14 @@ class Engine:
     @property
     def tensor_path_counts(self):
         """(events scored by the tensor-core path so far, events of those re-scored by the FP64 kernels)"""
-        out = (C.c_uint64 * 2)()
-        _check(lib().fjp_engine_tensor_path_counts(self._h, out))
-        return int(out[0]), int(out[1])
+        return self.fast_path_counts[:2]
+
+    @property
+    def fast_path_counts(self):
+        """(tensor path: events, handed back; FMA dense path: events, handed back)"""
+        out = (C.c_uint64 * 4)()
+        _check(lib().fjp_engine_fast_path_counts(self._h, out))
+        return tuple(int(v) for v in out)
 
     def sync(self):
         _check(lib().fjp_engine_sync(self._h))

@@ -124,7 +124,7 @@ static int slot_reserve(Slot& s, size_t bytes) {
   return 0;
 }
 
-static size_t score_scratch_bytes(const fjp_model* m, long n, bool verification_outputs = false);
+static size_t score_scratch_bytes(const fjp_model* m, long n, bool want_probs = false, bool want_node_ids = false);
 
 struct Carve {  // sub-allocation inside a slot arena
   size_t off = 0;
@@ -142,7 +142,7 @@ static int enqueue_chunk(fjp_engine* e, fjp_model* m, Slot& s, const HostBatch& 
   size_t oX = c.take((size_t)n * F * 8), oP = hb.present ? c.take((size_t)n * W * 4) : 0, oR = hb.replace ? c.take((size_t)n * 8) : 0;
   size_t oS = c.take((size_t)n * 8), oT = c.take((size_t)n), oA = hb.aux ? c.take((size_t)n * 4) : 0;
   size_t oN = hb.node_ids ? c.take((size_t)n * hb.node_stride * 4) : 0, oQ = hb.probs ? c.take((size_t)n * hb.prob_stride * 8) : 0;
-  const size_t dsz = score_scratch_bytes(m, n, hb.node_ids || hb.probs); size_t oD = dsz ? c.take(dsz) : 0;   // augmented rows (derived fields) / leaf values (small-batch forest path) / digit planes
+  const size_t dsz = score_scratch_bytes(m, n, hb.probs != nullptr, hb.node_ids != nullptr); size_t oD = dsz ? c.take(dsz) : 0;   // augmented rows (derived fields) / leaf values (small-batch forest path) / digit planes
   if (slot_reserve(s, c.off)) return -1;
   BatchArgs a{}; a.stats = e->d_stats;
   a.X = reinterpret_cast<double*>(s.buf + oX); a.n = n; a.present_stride = W;
@@ -168,13 +168,13 @@ static int enqueue_chunk(fjp_engine* e, fjp_model* m, Slot& s, const HostBatch& 
 
 // work area a batch of n events wants besides its inputs and outputs: augmented rows (derived fields) or the per-tree leaf
 // values of the small-batch forest path
-static size_t score_scratch_bytes(const fjp_model* m, long n, bool verification_outputs) {
+static size_t score_scratch_bytes(const fjp_model* m, long n, bool want_probs, bool want_node_ids) {
   size_t d = derived_scratch_bytes(m->dev, n);
   if (d) return d;
-  if (!verification_outputs) {   // digit planes of the tensor-core path (dense layers; not when probabilities / node ids are asked for)
-    BatchArgs t{}; t.n = n;
-    if (size_t sl = sliced_scratch_bytes(m->dev, t)) return sl;
-  }
+  // the fast paths look at the same fields of the batch the launcher will see (probabilities / node ids asked for or not)
+  BatchArgs t{}; t.n = n; t.probs = want_probs ? reinterpret_cast<double*>(8) : nullptr; t.node_ids = want_node_ids ? reinterpret_cast<int32_t*>(8) : nullptr;
+  if (size_t sl = sliced_scratch_bytes(m->dev, t)) return sl;       // digit planes of the tensor-core path (dense layers)
+  if (size_t df = dense_fma_scratch_bytes(m->dev, t)) return df;    // re-scoring list of the FMA paths (dense tile kernel)
   return forest_slice_scratch_bytes(m->dev, n);
 }
 
@@ -270,11 +270,12 @@ int fjp_engine_device(const fjp_engine* e) { return e->device; }
 int fjp_engine_sync(fjp_engine* e) { CK(cudaSetDevice(e->device)); for (auto& s : e->slots) CK(cudaStreamSynchronize(s.s)); return 0; }
 long fjp_engine_launch_count(const fjp_engine* e) { return e->launches.load(); }
 void fjp_engine_status_counts(const fjp_engine* e, uint64_t out[6]) { for (int k = 0; k < 6; k++) out[k] = e->status_counts[k].load(); }
-int fjp_engine_tensor_path_counts(fjp_engine* e, uint64_t out[2]) {
+int fjp_engine_fast_path_counts(fjp_engine* e, uint64_t out[4]) {
   if (fjp_engine_sync(e) != 0) return -1;
-  unsigned long long h[2] = {0, 0};
+  unsigned long long h[4] = {0, 0, 0, 0};
   CK(cudaMemcpy(h, e->d_stats, sizeof h, cudaMemcpyDeviceToHost));
-  out[0] = h[0]; out[1] = h[1]; return 0;
+  for (int k = 0; k < 4; k++) out[k] = h[k];
+  return 0;
 }
 
 int fjp_model_compile(fjp_engine* e, const char* pmml, size_t len, fjp_model** out, char* err, size_t errcap) {
@@ -455,6 +456,7 @@ int fjp_score_device(fjp_engine* e, fjp_model* m, const double* dX, const uint32
     if (m->device != e->device) return fail("model lives on another device; use fjp_model_replicate");
     size_t dsz = derived_scratch_bytes(m->dev, n);
     if (!dsz) dsz = sliced_scratch_bytes(m->dev, a);
+    if (!dsz) dsz = dense_fma_scratch_bytes(m->dev, a);
     if (!dsz) dsz = forest_compact_scratch_bytes(m->dev, n);
     if (dsz) {   // augmented rows (derived fields) / rank-key tiles (large forest batches): stream-ordered allocation on the caller's stream
       void* scratch = nullptr; CK(cudaMallocAsync(&scratch, dsz, st));

@@ -313,17 +313,21 @@ __global__ void __launch_bounds__(CL_E* CL_G) cluster_kernel(const __grid_consta
   double* bd = reinterpret_cast<double*>(st_s + (((size_t)nf * CL_SS + 15) & ~size_t(15)));  // CL_G x CL_E
   int* bc = reinterpret_cast<int*>(bd + CL_G * CL_E);
   const int tid = threadIdx.x, e = tid & (CL_E - 1), g = tid / CL_E;
-  const long row0 = blockIdx.x * (long)CL_E;
+  // re-scoring mode (a.row_map): work item i is row row_map[i], *n_dev of them (the events the FMA path handed back)
+  const long n_items = a.n_dev ? min((long)*a.n_dev, a.n) : a.n;
+  auto row_of = [&](long item) { return a.row_map ? (long)a.row_map[item] : item; };
+  for (long row0 = blockIdx.x * (long)CL_E; row0 < n_items; row0 += gridDim.x * (long)CL_E) {
+  __syncthreads();   // the previous tile's reductions are done with the buffers
   // load + prepare: consecutive threads take consecutive clustering fields of one row
   for (int i = tid; i < nf * CL_E; i += blockDim.x) {
-    int r = i / nf, f = i - r * nf; long row = row0 + r;
+    int r = i / nf, f = i - r * nf; long item = row0 + r;
     double v = 0; int st = 1;
-    if (row < a.n) { int slot = cd.slot[f]; if (slot >= 0) st = load_field(m, a, row, slot, v); }
+    if (item < n_items) { int slot = cd.slot[f]; if (slot >= 0) st = load_field(m, a, row_of(item), slot, v); }
     xs[f * CL_XS + r] = v; st_s[f * CL_SS + r] = (uint8_t)st;
   }
   __syncthreads();
-  const long row = row0 + e;
-  bool fail = row < a.n && !cd.slots_identity && row_fails_preparation(m, a, row); double adj = 1.0;   // active fields that are not clustering fields
+  const bool live = row0 + e < n_items; const long row = live ? row_of(row0 + e) : 0;
+  bool fail = live && !cd.slots_identity && row_fails_preparation(m, a, row); double adj = 1.0;   // active fields that are not clustering fields
   {
     double sum_q = 0, sum_nm = 0;
     for (int f = 0; f < nf; f++) { int st = st_s[f * CL_SS + e]; if (st == 2) fail = true; double q = cd.q[f]; sum_q += q; sum_nm += st == 0 ? q : 0.0; }
@@ -357,7 +361,7 @@ __global__ void __launch_bounds__(CL_E* CL_G) cluster_kernel(const __grid_consta
   }
   bd[g * CL_E + e] = bestd; bc[g * CL_E + e] = best;
   __syncthreads();
-  if (g == 0 && row < a.n) {
+  if (g == 0 && live) {
     for (int gg = 1; gg < CL_G; gg++) {
       int c2 = bc[gg * CL_E + e]; if (c2 < 0) continue; double d2 = bd[gg * CL_E + e];
       int cmp = best < 0 ? -1 : java_cmp(d2, bestd);
@@ -366,6 +370,7 @@ __global__ void __launch_bounds__(CL_E* CL_G) cluster_kernel(const __grid_consta
     if (fail) write_out(a, row, 0, ST_PREP, -1);
     else write_label(m, a, row, best, best + 1);
     if (a.probs) a.probs[row * (long)a.prob_stride] = bestd;
+  }
   }
 }
 
@@ -714,13 +719,24 @@ __global__ void __launch_bounds__(128) regression_kernel(const __grid_constant__
 // warps = event blocks x table groups.  Inputs and the transposed coefficient block [field][table] stream through
 // shared memory in chunks of fields; y[c] accumulates in double, unfused, in field order (= NumericPredictor order).
 struct DensePlan { int groups, event_blocks, events, chunk, kp, warps; uint32_t off_x, off_st, off_y, off_flags, smem_bytes; };
+// What the tile kernel multiplies: y_t = icpt_t + sum_f wt[f][t] x_f for C tables.  RegressionModel: the RegressionTables.
+// ClusteringModel (FAST = 2): wt = -2 c_t, icpt = |c_t|^2, so that y_t = |x - c_t|^2 - |x|^2 and the nearest centre is the smallest y.
+struct DenseView {
+  const double* wt; const double* icpt; int C;
+  double amax, bmax;      // max_t sum_f |wt[f][t]|, max_t |icpt_t|   (FAST = 1)  /  max |c|, unused (FAST = 2)
+  int32_t* fb_count; int32_t* fb_rows;   // events the margin test hands to the FAST = 0 kernel
+};
 // EPT = events per thread (lane l owns events l, l + 32 of its warp's 32 * EPT): a warp-wide broadcast LDS.128 of coefficients
 // costs two shared-memory wavefronts, so with one event per thread the coefficient loads alone (11 wavefronts per field for 10
 // tables) outlast the 10 cycles the field's 20 FP64 instructions take; two events share them.
-template <bool HASMISS, int TC, int EPT>
-__global__ void __launch_bounds__(256, EPT == 1 ? 3 : 2) regression_tile_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, const DensePlan pl) {
+// FAST = 0: the reference's arithmetic -- unfused multiply and add in predictor order (JPMML on the JVM).
+// FAST = 1 / 2: fused multiply-add (twice the FP64 rate) for softmax classification / nearest centre.  y then differs from the
+//   reference's by at most eps = (2 F + 8) 2^-53 (|icpt| + sum |w| |x|), bounded per event from the largest |x|; a label is written
+//   only when the winner's margin exceeds 2 eps, every other event goes on the list the FAST = 0 kernel re-scores (a.row_map).
+template <bool HASMISS, int TC, int EPT, int FAST>
+__global__ void __launch_bounds__(256, EPT == 1 ? 3 : 2) regression_tile_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, const DensePlan pl, const DenseView dv) {
   extern __shared__ __align__(128) uint8_t smem[];
-  const RegressionDesc& rd = m.reg; const int F = m.F, C = rd.n_tables, KP = pl.kp, E = pl.events, EP = E + 1;
+  const RegressionDesc& rd = m.reg; const int F = m.F, C = dv.C, KP = pl.kp, E = pl.events, EP = E + 1;
   double* wt = reinterpret_cast<double*>(smem);                          // chunk x KP  [f][c]
   double* xs = reinterpret_cast<double*>(smem + pl.off_x);               // chunk x EP
   uint8_t* sts = smem + pl.off_st;                                       // chunk x (E + 4)
@@ -729,15 +745,19 @@ __global__ void __launch_bounds__(256, EPT == 1 ? 3 : 2) regression_tile_kernel(
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int eb = warp % pl.event_blocks, cg = warp / pl.event_blocks, e = eb * 32 * EPT + lane;
   for (int i = tid; i < E; i += blockDim.x) eflags[i] = 0;
-  const long ntiles = (a.n + E - 1) / E;
+  // re-scoring mode (a.row_map): work item i is row row_map[i], *n_dev of them
+  const long n_items = a.n_dev ? min((long)*a.n_dev, a.n) : a.n;
+  auto row_of = [&](long item) { return a.row_map ? (long)a.row_map[item] : item; };
+  const long ntiles = (n_items + E - 1) / E;
   for (long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const long row0 = tile * E;
     double acc[EPT][TC]; int flags[EPT];  // bit0 preparation failure, bit1 missing predictor
+    int xm[EPT];                           // FAST: high word of the largest |x| of the event
 #pragma unroll
     for (int v = 0; v < EPT; v++) {
-      flags[v] = 0;
+      flags[v] = 0; xm[v] = 0;
 #pragma unroll
-      for (int k = 0; k < TC; k++) { int c = cg * TC + k; acc[v][k] = c < C ? rd.intercept[c] : 0.0; }
+      for (int k = 0; k < TC; k++) { int c = cg * TC + k; acc[v][k] = c < C ? dv.icpt[c] : 0.0; }
     }
     // double-buffered chunks: the copies of chunk c+1 (cp.async, 8 B each, written straight into the transposed
     // position) are in flight while chunk c is multiplied
@@ -745,20 +765,20 @@ __global__ void __launch_bounds__(256, EPT == 1 ? 3 : 2) regression_tile_kernel(
     auto fill = [&](int buf, int f0) {
       const int nfc = min(pl.chunk, F - f0);
       double* wb = wt + (size_t)buf * pl.chunk * KP; double* xb = xs + (size_t)buf * pl.chunk * EP; uint8_t* sb = sts + (size_t)buf * pl.chunk * (E + 4);
-      for (int i = tid; i < nfc * KP; i += blockDim.x) cp_async8(wb + i, rd.dense_wt + (size_t)f0 * KP + i);
+      for (int i = tid; i < nfc * KP; i += blockDim.x) cp_async8(wb + i, dv.wt + (size_t)f0 * KP + i);
       const int sh = 31 - __clz(nfc); const bool pow2 = (nfc & (nfc - 1)) == 0;
       if (!HASMISS && pow2 && nfc <= (int)blockDim.x && (blockDim.x & (nfc - 1)) == 0) {
         // plain doubles, power-of-two chunk: a thread keeps its field and walks down the rows with pointer increments
-        const int f = tid & (nfc - 1), rstep = blockDim.x >> sh, live = (int)min((long)E, a.n - row0);
+        const int f = tid & (nfc - 1), rstep = blockDim.x >> sh, live = (int)min((long)E, n_items - row0);
         int r = tid >> sh;
         const double* src = a.X + (row0 + r) * (long)F + f0 + f; double* dst = xb + f * EP + r; const long sstep = (long)rstep * F;
         for (; r < live; r += rstep, src += sstep, dst += rstep) cp_async8(dst, src);
         for (; r < E; r += rstep, dst += rstep) *dst = 0.0;
       } else
       for (int i = tid; i < E * nfc; i += blockDim.x) {
-        int r = pow2 ? (i >> sh) : (i / nfc), f = i - r * nfc; long rr = row0 + r;
-        if (HASMISS) { double v = 0; int st = 0; if (rr < a.n) st = load_field(m, a, rr, f0 + f, v); sb[f * (E + 4) + r] = (uint8_t)st; xb[f * EP + r] = v; }
-        else if (rr < a.n) cp_async8(xb + f * EP + r, a.X + rr * (long)F + f0 + f);   // plain doubles, all present
+        int r = pow2 ? (i >> sh) : (i / nfc), f = i - r * nfc; long it = row0 + r;
+        if (HASMISS) { double v = 0; int st = 0; if (it < n_items) st = load_field(m, a, row_of(it), f0 + f, v); sb[f * (E + 4) + r] = (uint8_t)st; xb[f * EP + r] = v; }
+        else if (it < n_items) cp_async8(xb + f * EP + r, a.X + it * (long)F + f0 + f);   // plain doubles, all present
         else xb[f * EP + r] = 0.0;
       }
       asm volatile("cp.async.commit_group;" ::: "memory");
@@ -778,13 +798,17 @@ __global__ void __launch_bounds__(256, EPT == 1 ? 3 : 2) regression_tile_kernel(
         for (int v = 0; v < EPT; v++) {
           x[v] = xb[f * EP + e + 32 * v];
           if (HASMISS) { int st = sb[f * (E + 4) + e + 32 * v]; flags[v] |= st == 2 ? 1 : (st == 1 ? 2 : 0); }
+          if (FAST) xm[v] = max(xm[v], __double2hiint(x[v]) & 0x7fffffff);
         }
         const double2* w2 = reinterpret_cast<const double2*>(wp);
 #pragma unroll
         for (int k = 0; k < TC / 2; k++) {
           double2 w = w2[k];
 #pragma unroll
-          for (int v = 0; v < EPT; v++) { acc[v][2 * k] += w.x * x[v]; acc[v][2 * k + 1] += w.y * x[v]; }
+          for (int v = 0; v < EPT; v++) {
+            if (FAST) { acc[v][2 * k] = fma(w.x, x[v], acc[v][2 * k]); acc[v][2 * k + 1] = fma(w.y, x[v], acc[v][2 * k + 1]); }
+            else { acc[v][2 * k] += w.x * x[v]; acc[v][2 * k + 1] += w.y * x[v]; }
+          }
         }
       }
       __syncthreads();   // buffer `buf` may be refilled by the next iteration's fill (and, after the last chunk, reused for ys)
@@ -798,18 +822,50 @@ __global__ void __launch_bounds__(256, EPT == 1 ? 3 : 2) regression_tile_kernel(
     __syncthreads();
 #pragma unroll
     for (int v = 0; v < EPT; v++) {
-      const int e = eb * 32 * EPT + lane + 32 * v; const long row = row0 + e;
-      if (!(cg == 0 && row < a.n)) continue;
-      int fl = HASMISS ? eflags[e] : 0;
-      if (fl & 1) write_out(a, row, 0, ST_PREP, -1);
-      else if (fl & 2) write_out(a, row, 0, m.target_status ? m.target_status : ST_EVAL, -1);
-      else if (!rd.classify) write_out(a, row, apply_target(m.tx, link_fn(rd.norm, ys[e])), m.target_status, -1);
-      else {
-        normalize_classes(rd.norm, C, [&](int i) { return ys[i * EP + e]; }, [&](int i, double v) { ys[i * EP + e] = v; });
-        int best = 0; double bp = ys[e];
-        for (int i = 1; i < C; i++) { double p = ys[i * EP + e]; if (java_cmp(p, bp) > 0) { best = i; bp = p; } }
-        write_label(m, a, row, best, best);
-        if (a.probs) for (int i = 0; i < C && i < a.prob_stride; i++) a.probs[row * (long)a.prob_stride + i] = ys[i * EP + e];
+      const int e = eb * 32 * EPT + lane + 32 * v; const long item = row0 + e;
+      bool rescore = false; long row = 0;
+      if (cg == 0 && item < n_items) {
+        row = row_of(item);
+        int fl = HASMISS ? eflags[e] : 0;
+        if (fl & 1) write_out(a, row, 0, ST_PREP, -1);
+        else if (fl & 2) write_out(a, row, 0, m.target_status ? m.target_status : ST_EVAL, -1);
+        else if (FAST == 2) {
+          // nearest centre: smallest y, the first one on ties -- decided here only when the runner-up is farther than the bound
+          const double xmax = __hiloint2double(xm[v] + 1, 0), s = xmax + dv.amax;
+          const double eps = (double)(2 * F + 8) * 2.220446049250313e-16 * (double)F * s * s;
+          int best = 0; double yb = ys[e], y2 = __longlong_as_double(0x7FF0000000000000LL);
+          for (int i = 1; i < C; i++) { const double y = ys[i * EP + e]; if (y < yb) { y2 = yb; yb = y; best = i; } else y2 = fmin(y2, y); }
+          if (C == 1 || (y2 - yb > 2.0 * eps && s < 1e150)) write_label(m, a, row, best, best + 1); else rescore = true;
+        }
+        else if (!rd.classify) write_out(a, row, apply_target(m.tx, link_fn(rd.norm, ys[e])), m.target_status, -1);
+        else {
+          bool decided = true;
+          if (FAST == 1) {
+            const double xmax = __hiloint2double(xm[v] + 1, 0);
+            const double eps = (double)(2 * F + 8) * 1.1102230246251565e-16 * (dv.bmax + dv.amax * xmax);
+            double yb = ys[e], y2 = -__longlong_as_double(0x7FF0000000000000LL), ya = fabs(yb);
+            for (int i = 1; i < C; i++) { const double y = ys[i * EP + e]; ya = fmax(ya, fabs(y)); if (y > yb) { y2 = yb; yb = y; } else y2 = fmax(y2, y); }
+            decided = C == 1 || (yb - y2 > 2.0 * eps && ya < 600.0);      // |y| < 600: exp() stays finite and non-zero, so the order of p is the order of y
+          }
+          if (!decided) rescore = true;
+          else {
+            normalize_classes(rd.norm, C, [&](int i) { return ys[i * EP + e]; }, [&](int i, double v) { ys[i * EP + e] = v; });
+            int best = 0; double bp = ys[e];
+            for (int i = 1; i < C; i++) { double p = ys[i * EP + e]; if (java_cmp(p, bp) > 0) { best = i; bp = p; } }
+            write_label(m, a, row, best, best);
+            if (a.probs) for (int i = 0; i < C && i < a.prob_stride; i++) a.probs[row * (long)a.prob_stride + i] = ys[i * EP + e];
+          }
+        }
+      }
+      if (FAST) {   // (cg == 0 warps only have candidates; the ballot is over the whole warp)
+        const unsigned need = __ballot_sync(0xffffffffu, rescore), alive = __ballot_sync(0xffffffffu, cg == 0 && item < n_items);
+        if (a.stats && lane == 0 && alive) { atomicAdd(a.stats + 2, (unsigned long long)__popc(alive)); if (need) atomicAdd(a.stats + 3, (unsigned long long)__popc(need)); }
+        if (need) {
+          int base = 0;
+          if (lane == 0) base = atomicAdd(dv.fb_count, __popc(need));
+          base = __shfl_sync(0xffffffffu, base, 0);
+          if (rescore) dv.fb_rows[base + __popc(need & ((1u << lane) - 1u))] = (int32_t)row;
+        }
       }
     }
     if (HASMISS) { __syncthreads(); for (int i = tid; i < E; i += blockDim.x) eflags[i] = 0; }
@@ -1332,6 +1388,7 @@ bool plan_forest_complete(const DeviceModel& m, ForestLaunch* out) {
 
 // Work area the small-batch forest path wants for n events (0: path not applicable)
 size_t forest_compact_scratch_bytes(const DeviceModel& m, long n);
+size_t dense_fma_scratch_bytes(const DeviceModel& m, const BatchArgs& a);
 size_t forest_slice_scratch_bytes(const DeviceModel& m, long n) {
   query_device();
   if (size_t c = forest_compact_scratch_bytes(m, n)) return c;   // large batch: the work area holds the rank-key tiles instead
@@ -1487,6 +1544,55 @@ static cudaError_t launch_forest_compact(const DeviceModel& m, const BatchArgs& 
   return cudaSuccess;
 }
 
+// ---- dense tile kernel (RegressionModel tables / k-means centres): geometry + dispatch ----------------------------------
+// fast: 0 = the reference's unfused arithmetic, 1 = FMA + margin (softmax classification), 2 = FMA + margin (nearest centre)
+static cudaError_t launch_dense_tile(const DeviceModel& m, const BatchArgs& a, const DenseView& dv, bool hasmiss, int fast, cudaStream_t s) {
+  // tables per thread: 8, 10 or 12, whichever pads the table count least (20 tables -> 2 groups of 10); the same rule lays out wt
+  int tc = 8, best_pad = 1 << 30;
+  for (int cand : {8, 10, 12}) { int pad = (dv.C + cand - 1) / cand * cand - dv.C; if (pad < best_pad) { best_pad = pad; tc = cand; } }
+  DensePlan pl{}; pl.kp = ((dv.C + tc - 1) / tc) * tc; pl.groups = pl.kp / tc;
+  // two events per thread once there are enough fields for the coefficient traffic to matter
+  const int ept = fast ? 2 : (env_int("FJP_REG_EPT", m.F >= 64 ? 2 : 1) >= 2 ? 2 : 1), per_sm = ept == 2 ? 2 : 3;
+  pl.event_blocks = pl.groups >= 8 ? 1 : 8 / pl.groups; pl.warps = pl.event_blocks * pl.groups; pl.events = 32 * ept * pl.event_blocks;
+  const int EP = pl.events + 1;
+  int chunk = 64; while (chunk > m.F && chunk > 1) chunk /= 2;   // power of two: cheap row/column split
+  const unsigned smem_cap = (unsigned)env_int("FJP_REG_SMEM_KB", ept == 2 ? 110 : 72) * 1024u;   // per_sm CTAs per SM: one loads while the others compute
+  for (;; chunk /= 2) {
+    size_t off = ((size_t)2 * chunk * pl.kp * 8 + 127) & ~size_t(127); pl.off_x = (uint32_t)off;
+    const size_t xbytes = (size_t)2 * chunk * EP * 8, ybytes = (size_t)pl.kp * EP * 8;
+    pl.off_y = (uint32_t)off; off += xbytes > ybytes ? xbytes : ybytes;   // ys (epilogue only) reuses the input buffers
+    pl.off_st = (uint32_t)off; if (hasmiss) off += (size_t)2 * chunk * (pl.events + 4); off = (off + 15) & ~size_t(15);
+    pl.off_flags = (uint32_t)off; off += (size_t)pl.events * 4; pl.smem_bytes = (uint32_t)((off + 127) & ~size_t(127));
+    if (pl.smem_bytes <= smem_cap || chunk == 1) break;
+  }
+  pl.chunk = chunk;
+  if (pl.smem_bytes > (uint32_t)g_smem_optin || pl.warps * 32 > 256) return cudaErrorInvalidConfiguration;
+  long ntiles = (a.n + pl.events - 1) / pl.events; int grid = (int)(ntiles < (long)per_sm * g_num_sms ? ntiles : (long)per_sm * g_num_sms);
+#define FJP_RT(HM, TCV, EV, FV) do { cudaFuncSetAttribute(regression_tile_kernel<HM, TCV, EV, FV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes); \
+                                     regression_tile_kernel<HM, TCV, EV, FV><<<grid, pl.warps * 32, pl.smem_bytes, s>>>(m, a, pl, dv); } while (0)
+#define FJP_RT2(HM, TCV) do { if (ept == 2) FJP_RT(HM, TCV, 2, 0); else FJP_RT(HM, TCV, 1, 0); } while (0)
+  if (fast == 1) { if (tc == 8) FJP_RT(false, 8, 2, 1); else if (tc == 10) FJP_RT(false, 10, 2, 1); else FJP_RT(false, 12, 2, 1); }
+  else if (fast == 2) { if (tc == 8) FJP_RT(false, 8, 2, 2); else if (tc == 10) FJP_RT(false, 10, 2, 2); else FJP_RT(false, 12, 2, 2); }
+  else if (hasmiss) { if (tc == 8) FJP_RT2(true, 8); else if (tc == 10) FJP_RT2(true, 10); else FJP_RT2(true, 12); }
+  else { if (tc == 8) FJP_RT2(false, 8); else if (tc == 10) FJP_RT2(false, 10); else FJP_RT2(false, 12); }
+#undef FJP_RT2
+#undef FJP_RT
+  return cudaGetLastError();
+}
+// FMA paths of the dense tile kernel: softmax classification (RegressionModel) and nearest centre (ClusteringModel) over plain
+// dense rows, batches that fill the chip.  Work area: the re-scoring counter + one row index per event.  FJP_DENSE_FMA=0 switches
+// them off, =2 takes them for every batch size.
+size_t dense_fma_scratch_bytes(const DeviceModel& m, const BatchArgs& a) {
+  const int mode = env_int("FJP_DENSE_FMA", 1);
+  if (!mode || a.present || a.replace || !m.prep_identity || a.row_map || a.node_ids) return 0;
+  query_device();
+  if (mode != 2 && a.n < 64L * g_num_sms) return 0;
+  if (m.kind == MK_REGRESSION) { if (!(m.reg.dense && m.reg.classify && m.reg.norm == NORM_SOFTMAX && m.reg.n_tables <= REG_MAXC)) return 0; }
+  else if (m.kind == MK_CLUSTERING) { if (!(m.cluster.fast && m.cluster.slots_identity && m.cluster.fast_wt && m.cluster.k <= REG_MAXC && !a.probs)) return 0; }
+  else return 0;
+  return 256 + (((size_t)a.n * 4 + 255) & ~size_t(255));
+}
+
 cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t s, int* launches, void* slice_scratch) {
   query_device();
   if (a.n <= 0) return cudaSuccess;
@@ -1530,6 +1636,22 @@ cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t 
     }
     case MK_CLUSTERING: {
       const int nf = m.cluster.nf;
+      if (slice_scratch && dense_fma_scratch_bytes(m, a)) {
+        // |x - c|^2 = |x|^2 + (|c|^2 - 2 x.c): one fused multiply-add per term instead of sub, mul, add; the nearest centre is decided
+        // here when the runner-up is farther than the rounding bound, the other events go to the exact kernel below
+        DenseView dv{}; dv.wt = m.cluster.fast_wt; dv.icpt = m.cluster.fast_icpt; dv.C = m.cluster.k; dv.amax = m.cluster.cmax;
+        dv.fb_count = static_cast<int32_t*>(slice_scratch); dv.fb_rows = dv.fb_count + 64;
+        cudaError_t e = cudaMemsetAsync(dv.fb_count, 0, 4, s); if (e != cudaSuccess) return e;
+        e = launch_dense_tile(m, a, dv, false, 2, s); if (e != cudaSuccess) return e;
+        if (launches) (*launches)++;
+        BatchArgs fb = a; fb.row_map = dv.fb_rows; fb.n_dev = dv.fb_count;
+        size_t sm = (size_t)nf * CL_XS * 8 + (((size_t)nf * CL_SS + 15) & ~size_t(15)) + CL_G * CL_E * 12;
+        if (sm > (size_t)g_smem_optin) return cudaErrorInvalidValue;
+        unsigned grid = (unsigned)std::min<long>((a.n + CL_E - 1) / CL_E, 4L * g_num_sms);
+        cudaFuncSetAttribute(cluster_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+        cluster_kernel<true><<<grid, CL_E * CL_G, sm, s>>>(m, fb);
+        return cudaGetLastError();
+      }
       if (m.cluster.fast && (m.cluster.measure == CM_SQEUCLIDEAN || m.cluster.measure == CM_EUCLIDEAN)) {
         ClusterPlan pl{}; pl.kp = ((m.cluster.k + CK_TC - 1) / CK_TC) * CK_TC; pl.groups = pl.kp / CK_TC;
         pl.event_blocks = pl.groups >= CK_WARPS ? 1 : CK_WARPS / pl.groups;
@@ -1596,35 +1718,18 @@ cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t 
     case MK_REGRESSION: {
       if (m.reg.n_tables > REG_MAXC) return cudaErrorInvalidValue;
       if (m.reg.dense) {
-        // tables per thread: 8, 10 or 12, whichever pads the table count least (20 tables -> 2 groups of 10)
-        int tc = 8, best_pad = 1 << 30;
-        for (int cand : {8, 10, 12}) { int pad = (m.reg.n_tables + cand - 1) / cand * cand - m.reg.n_tables; if (pad < best_pad) { best_pad = pad; tc = cand; } }
-        DensePlan pl{}; pl.kp = ((m.reg.n_tables + tc - 1) / tc) * tc; pl.groups = pl.kp / tc;
+        DenseView dv{}; dv.wt = m.reg.dense_wt; dv.icpt = m.reg.intercept; dv.C = m.reg.n_tables; dv.amax = m.reg.dense_amax; dv.bmax = m.reg.dense_bmax;
         const bool hasmiss = a.present != nullptr || a.replace != nullptr || !m.prep_identity;
-        // two events per thread once there are enough fields for the coefficient traffic to matter
-        const int ept = env_int("FJP_REG_EPT", m.F >= 64 ? 2 : 1) >= 2 ? 2 : 1, per_sm = ept == 2 ? 2 : 3;
-        pl.event_blocks = pl.groups >= 8 ? 1 : 8 / pl.groups; pl.warps = pl.event_blocks * pl.groups; pl.events = 32 * ept * pl.event_blocks;
-        const int EP = pl.events + 1;
-        int chunk = 64; while (chunk > m.F && chunk > 1) chunk /= 2;   // power of two: cheap row/column split
-        const unsigned smem_cap = (unsigned)env_int("FJP_REG_SMEM_KB", ept == 2 ? 110 : 72) * 1024u;   // per_sm CTAs per SM: one loads while the others compute
-        for (;; chunk /= 2) {
-          size_t off = ((size_t)2 * chunk * pl.kp * 8 + 127) & ~size_t(127); pl.off_x = (uint32_t)off;
-          const size_t xbytes = (size_t)2 * chunk * EP * 8, ybytes = (size_t)pl.kp * EP * 8;
-          pl.off_y = (uint32_t)off; off += xbytes > ybytes ? xbytes : ybytes;   // ys (epilogue only) reuses the input buffers
-          pl.off_st = (uint32_t)off; if (hasmiss) off += (size_t)2 * chunk * (pl.events + 4); off = (off + 15) & ~size_t(15);
-          pl.off_flags = (uint32_t)off; off += (size_t)pl.events * 4; pl.smem_bytes = (uint32_t)((off + 127) & ~size_t(127));
-          if (pl.smem_bytes <= smem_cap || chunk == 1) break;
+        // softmax classification over plain dense rows: fused multiply-add + margin test, the undecided events re-scored below
+        if (slice_scratch && dense_fma_scratch_bytes(m, a)) {
+          dv.fb_count = static_cast<int32_t*>(slice_scratch); dv.fb_rows = dv.fb_count + 64;
+          cudaError_t e = cudaMemsetAsync(dv.fb_count, 0, 4, s); if (e != cudaSuccess) return e;
+          e = launch_dense_tile(m, a, dv, false, 1, s); if (e != cudaSuccess) return e;
+          if (launches) (*launches)++;
+          BatchArgs fb = a; fb.row_map = dv.fb_rows; fb.n_dev = dv.fb_count;
+          return launch_dense_tile(m, fb, dv, true, 0, s);
         }
-        pl.chunk = chunk;
-        long ntiles = (a.n + pl.events - 1) / pl.events; int grid = (int)(ntiles < (long)per_sm * g_num_sms ? ntiles : (long)per_sm * g_num_sms);
-#define FJP_RT(HM, TCV, EV) do { cudaFuncSetAttribute(regression_tile_kernel<HM, TCV, EV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes); \
-                                 regression_tile_kernel<HM, TCV, EV><<<grid, pl.warps * 32, pl.smem_bytes, s>>>(m, a, pl); } while (0)
-#define FJP_RT2(HM, TCV) do { if (ept == 2) FJP_RT(HM, TCV, 2); else FJP_RT(HM, TCV, 1); } while (0)
-        if (hasmiss) { if (tc == 8) FJP_RT2(true, 8); else if (tc == 10) FJP_RT2(true, 10); else FJP_RT2(true, 12); }
-        else { if (tc == 8) FJP_RT2(false, 8); else if (tc == 10) FJP_RT2(false, 10); else FJP_RT2(false, 12); }
-#undef FJP_RT2
-#undef FJP_RT
-        return cudaGetLastError();
+        return launch_dense_tile(m, a, dv, hasmiss || a.row_map != nullptr, 0, s);
       }
       regression_kernel<<<(unsigned)((a.n + 127) / 128), 128, 0, s>>>(m, a);
       return cudaGetLastError();

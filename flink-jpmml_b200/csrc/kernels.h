@@ -42,7 +42,8 @@ size_t forest_compact_scratch_bytes(const DeviceModel& m, long n);   // throughp
 cudaError_t launch_expand_sparse(const long long* row_ptr, const int32_t* idx, const double* val, long n, int F,
                                  double* X, uint32_t* present, cudaStream_t s, int* launches);
 size_t derived_scratch_bytes(const DeviceModel& m, long n);
-size_t sliced_scratch_bytes(const DeviceModel& m, const BatchArgs& a);   // tensor-core path of dense layers (0: not taken for this batch)
+size_t sliced_scratch_bytes(const DeviceModel& m, const BatchArgs& a);
+size_t dense_fma_scratch_bytes(const DeviceModel& m, const BatchArgs& a);  // FMA paths of the dense tile kernel (0: not taken for this batch)   // tensor-core path of dense layers (0: not taken for this batch)
 cudaError_t launch_score_any(const DeviceModel& m, const BatchArgs& a, void* scratch, cudaStream_t s, int* launches);
 cudaError_t launch_fill_status(const BatchArgs& a, int status, cudaStream_t s, int* launches);
 

@@ -140,6 +140,9 @@ struct ClusterDesc {
   const int32_t* compare;   // nf
   const double* sim_scale;  // nf
   const double* centers;    // k x nf
+  // FMA form (fast models): |x - c_t|^2 - |x|^2 = fast_icpt[t] + sum_f fast_wt[f][t] x_f, fast_wt = -2 c transposed [nf][KP] (KP as for
+  // the regression tables: k rounded up to 8 / 10 / 12 per thread), fast_icpt = |c_t|^2; cmax = largest |centre coordinate|
+  const double* fast_wt; const double* fast_icpt; double cmax;
 };
 
 // ---- regression / neural network ---------------------------------------------------------------------
@@ -155,6 +158,7 @@ struct RegressionDesc {
   const int32_t* cat_off;     // n_tables+1
   const RegCat* cats;
   const double* dense_wt;     // dense only: F x KP transposed, KP = n_tables rounded up to a multiple of 8, 10 or 12 (least padding), zero padded
+  double dense_amax, dense_bmax;   // dense only: max_t sum_f |coef|, max_t |intercept| (error bound of the FMA path)
 };
 
 // ---- GeneralRegressionModel (PPMatrix x ParamMatrix) -------------------------------------------------------

@@ -408,6 +408,21 @@ void compile_clustering(const XNode& m, Builder& b) {
   d.slots_identity = (int)nf == b.cm.dev.F ? 1 : 0;
   for (size_t i = 0; i < nf; i++) if (slot[i] != (int)i) d.slots_identity = 0;
   b.put(&d.slot, slot); b.put(&d.weight, w); b.put(&d.q, q); b.put(&d.compare, cmp); b.put(&d.sim_scale, scale); b.put(&d.centers, centers);
+  {  // FMA form for the dense tile kernel (model.h): -2 c transposed, |c|^2
+    std::vector<double> fw, fi; d.cmax = 0; bool finite = true;
+    if (fast && d.slots_identity && d.k <= 64) {
+      size_t tcs = 8, bestpad = ~size_t(0); for (size_t cand : {size_t(8), size_t(10), size_t(12)}) { size_t pad = ((size_t)d.k + cand - 1) / cand * cand - (size_t)d.k; if (pad < bestpad) { bestpad = pad; tcs = cand; } }
+      const size_t KP = ((size_t)d.k + tcs - 1) / tcs * tcs; fw.assign(KP * nf, 0.0); fi.assign(KP, 0.0);
+      for (int t = 0; t < d.k; t++) {
+        double s2 = 0;
+        for (size_t f = 0; f < nf; f++) { const double c = centers[(size_t)t * nf + f]; finite = finite && std::isfinite(c); fw[f * KP + t] = -2.0 * c; s2 += c * c; d.cmax = std::max(d.cmax, std::fabs(c)); }
+        fi[t] = s2;
+      }
+      if (!finite || !(d.cmax < 1e150)) { fw.clear(); fi.clear(); }
+    }
+    if (fw.empty()) { d.fast_wt = nullptr; d.fast_icpt = nullptr; }
+    else { b.put(&d.fast_wt, fw); b.put(&d.fast_icpt, fi); }
+  }
   b.set_labels(ids, true);
   b.cm.dev.target_status = b.has_target ? ST_OK : ST_EXTRACT;  // no named target field -> nothing to extract
 }
@@ -1062,7 +1077,16 @@ bool compile_regression_tables(const XNode& m, Builder& b, const std::unordered_
   std::vector<double> w;
   // same choice as the launcher: 8, 10 or 12 tables per thread, least padding
   size_t tcs = 8, bestpad = ~size_t(0); for (size_t cand : {size_t(8), size_t(10), size_t(12)}) { size_t pad = (icpt.size() + cand - 1) / cand * cand - icpt.size(); if (pad < bestpad) { bestpad = pad; tcs = cand; } }
-  if (dense) { size_t KP = (icpt.size() + tcs - 1) / tcs * tcs; w.assign(KP * (size_t)F, 0.0); for (size_t t = 0; t < icpt.size(); t++) for (int i = 0; i < F; i++) w[(size_t)i * KP + t] = terms[toff[t] + i].coef; }
+  d.dense_amax = 0; d.dense_bmax = 0;
+  if (dense) {
+    size_t KP = (icpt.size() + tcs - 1) / tcs * tcs; w.assign(KP * (size_t)F, 0.0);
+    for (size_t t = 0; t < icpt.size(); t++) {
+      double rowsum = 0;
+      for (int i = 0; i < F; i++) { w[(size_t)i * KP + t] = terms[toff[t] + i].coef; rowsum += std::fabs(terms[toff[t] + i].coef); }
+      d.dense_amax = std::max(d.dense_amax, rowsum * (1.0 + 1e-12)); d.dense_bmax = std::max(d.dense_bmax, std::fabs(icpt[t]));
+    }
+    if (!std::isfinite(d.dense_amax) || !std::isfinite(d.dense_bmax)) d.dense_amax = d.dense_bmax = std::numeric_limits<double>::infinity();   // the FMA path then decides nothing
+  }
   b.put(&d.intercept, icpt); b.put(&d.term_off, toff); b.put(&d.terms, terms); b.put(&d.cat_off, coff); b.put(&d.cats, cats); b.put(&d.dense_wt, w);
   if (classify) b.set_labels(labels, false); else b.set_labels({}, false);
   finish_target(b, classify);

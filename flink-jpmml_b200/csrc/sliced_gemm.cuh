@@ -1,28 +1,32 @@
 // sliced_gemm.cuh -- dense layers (NeuralNetwork, J6) on the 5th-generation tensor cores: tcgen05.mma kind::i8 with the
-// accumulators in tensor memory.  Compiled as sliced_gemm.cu (device helpers from device_common.cuh).  Replaces, for large batches, the FP64
-// CUDA-core tiles of neural_pair_kernel on the path the reference hands to JPMML's NeuralNetworkEvaluator
+// accumulators in tensor memory.  Compiled as sliced_gemm.cu (device helpers from device_common.cuh).  Replaces, for large
+// batches, the FP64 CUDA-core tiles of neural_pair_kernel on the path the reference hands to JPMML's NeuralNetworkEvaluator
 // (flink-jpmml-scala/src/main/scala/io/radicalbit/flink/pmml/scala/api/PmmlModel.scala:159-160).
 //
-// Arithmetic (model.h "tensor-core form"): both operands of a layer are fixed-point images cut into SG_S = 5 balanced
-// base-128 digits; digit products of level c = k + l are summed EXACTLY in int32 accumulators (one 32-column TMEM
-// accumulator per level), and the epilogue recombines the levels in double:  z_j = b_j + sigma tau_j 2^-40 (sum_c 128^(6-c) L_c).
-// Nothing in the tensor pipe rounds, so the only errors are the digit truncation of the operands and the dropped pairs
-// (k + l > 6), bounded per layer and event by  K sigma tau_max SG_CS;  the bound is carried from layer to layer
-// (1-Lipschitz activations, |W| row sums) and the last layer's epilogue accepts a label only when the winner's margin
-// exceeds twice the bound.  Every other event -- and every event with a missing / invalid / non-finite input -- goes on a
-// list that neural_pair_kernel re-scores in FP64 in JPMML's order: labels are bit-exact by construction.
+// Arithmetic (model.h "tensor-core form"): both operands of a layer are fixed-point images cut into S balanced base-256
+// digits (S = 4: 30-bit operands); the digit products of level c = k + l are summed EXACTLY in int32 accumulators (one TMEM
+// accumulator of N columns per level), and the epilogue recombines the S kept levels:
+//     z_j = b_j + sigma tau 2^-(2Q) 256^(S-1) (sum_c 256^(S-1-c) L_c).
+// Nothing in the tensor pipe rounds, so the only errors are the digit truncation of the operands and the dropped low-order
+// pairs, bounded per layer and event by  K sigma tau SG_CS;  the bound is carried from layer to layer (activations with
+// Lipschitz constant <= 1, |W| row sums) and the last layer's epilogue accepts a label only when the winner's margin exceeds
+// twice the bound.  Every other event -- and every event with a missing / invalid / non-finite input -- goes on a list that
+// neural_pair_kernel re-scores in FP64 in JPMML's order: labels are bit-exact by construction.
 //
-// Kernels per pass of <= 8 tiles per SM (activations of a pass stay in L2 / HBM between the layer launches):
-//   sg_slice_inputs_kernel  NeuralInputs (same FP64 code as the exact kernels) -> row scale sigma -> 5 digit planes
-//   sg_layer_kernel<MODE>   one launch per layer; CTA = 128 events (UMMA M) x all output neurons in chunks of 32 (UMMA N):
-//       warp 0    producer: the tile's input digit planes (K-chunks of 64, 40 KB each) and the layer's weight digit planes
-//                 (10 KB per (neuron chunk, K chunk)) arrive with cp.async.bulk (TMA unit) on mbarriers; both are stored in
-//                 global memory in exactly the shared-memory image the MMA reads (K-major, no swizzle: 8 x 16 B core matrices)
-//       warp 1    one lane issues 30 tcgen05.mma (M128 N32 K32, 15 digit pairs x 2 K steps) per stage; tcgen05.commit
-//                 hands smem stages back to the producer and full accumulator sets (double-buffered in TMEM) to the epilogue
-//       warps 2-17 epilogue (two groups of 8, one per accumulator set): tcgen05.ld 5 levels x 8 columns at a time, recombination,
-//                 bias, activation (integer-only for rectifier / identity), re-slicing into the next
-//                 layer's digit planes (coalesced 16-byte stores) or, for the last layer, arg-max + margin test
+// Kernels per pass of <= 8 tiles per SM (a pass's digit planes go through L2 / HBM between the launches):
+//   sg_slice_inputs_kernel  NeuralInputs (same FP64 code as the exact kernels) -> row scale sigma -> S digit planes
+//   sg_layer_kernel<MODE>   one launch per layer; CTA = 128 events (UMMA M) x all output neurons in chunks of SG_NC (UMMA N):
+//       warp 0    producer: the tile's input digit planes (K chunks of 64 inputs) and the layer's weight digit planes (one stage
+//                 per (neuron chunk, K chunk)) arrive with cp.async.bulk (TMA unit) on mbarriers; both live in global memory in
+//                 exactly the shared-memory image the MMA reads (K-major, no swizzle: 8 x 16 B core matrices)
+//       warp 1    issues S (S + 1) / 2 digit pairs x 2 K steps of tcgen05.mma (M128 N<=64 K32) per stage from one elected lane;
+//                 tcgen05.commit hands smem stages back to the producer and full accumulator sets (double-buffered in the 512
+//                 TMEM columns) to the epilogue
+//       warps 2-17 epilogue: tcgen05.ld S levels x 8 columns at a time, recombination, bias, activation (integer-only for
+//                 rectifier / identity: one rounding shift per value), the byte transpose into the next layer's digit planes
+//                 (coalesced 16-byte stores) or, for the last layer, arg-max + margin test
+// Measured on the B200 (C5 MLP 64-256-256-8, profiles/): the 32-wide MMA was bound by the shared-memory reads of its 128 x 32 A
+// operand (40 cycles for 16 of math), hence 64-neuron chunks; the epilogue is paced by tensor-memory reads (S x 4 B per output).
 #pragma once
 #include <type_traits>
 
@@ -34,10 +38,10 @@ constexpr int EPI_WARPS = 16;
 constexpr int NSTAGE = 5;                    // weight stages in flight
 constexpr int COLQ = SG_NC / 16;             // 16-column shares of a neuron chunk
 constexpr int GROUPS = 16 / (4 * COLQ);      // epilogue warp groups: N = 32 -> one group of 8 warps per accumulator set; N = 64 -> all 16 warps on every chunk
-constexpr uint32_t A_CHUNK = SG_S * SG_M * SG_KC;      // 40960 B: one K chunk of a tile, all digit planes
-constexpr uint32_t A_PLANE = SG_M * SG_KC;             // 8192 B
-constexpr uint32_t B_STAGE = SG_S * SG_NC * SG_KC;     // 10240 B
-constexpr uint32_t B_PLANE = SG_NC * SG_KC;            // 2048 B
+constexpr uint32_t A_CHUNK = SG_S * SG_M * SG_KC;      // one K chunk of a tile, all digit planes (32 KB for S = 4)
+constexpr uint32_t A_PLANE = SG_M * SG_KC;             // 8 KB
+constexpr uint32_t B_STAGE = SG_S * SG_NC * SG_KC;     // 16 KB for S = 4, N = 64
+constexpr uint32_t B_PLANE = SG_NC * SG_KC;            // 4 KB
 constexpr int TMEM_COLS = SG_S * SG_NC * 2 <= 256 ? 256 : 512;   // two accumulator sets of SG_S x 32 columns
 constexpr int MAX_KC = 4;                    // K <= 256
 constexpr long PASS_TILES_PER_SM = 8;
@@ -279,7 +283,7 @@ __global__ void __launch_bounds__(THREADS, 1) sg_layer_kernel(const __grid_const
     // The whole warp walks the loops (so every address below is warp-uniform and lives in uniform registers); one elected lane
     // issues the tcgen05 instructions.
     const bool leader = elect_one();
-    const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(SG_NC >> 3) << 17) | ((uint32_t)(SG_M >> 4) << 24);   // S32 += S8 x S8, K-major A and B, M128 N32
+    const uint32_t idesc0 = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(SG_M >> 4) << 24);   // S32 += S8 x S8, K-major A and B, M = 128; N is set per chunk
     const uint64_t da0 = smem_desc(smem_u32(sA), SG_M * 16), db0 = smem_desc(smem_u32(sB), SG_NC * 16);
     uint32_t it_b = 0, it_t = 0, it_acc = 0;
     for (long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it_t++) {
@@ -288,6 +292,10 @@ __global__ void __launch_bounds__(THREADS, 1) sg_layer_kernel(const __grid_const
         mbar_wait(&t_empty[buf], ((it_acc >> 1) & 1u) ^ 1u);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const uint32_t d0 = tmem + buf * (SG_S * SG_NC);
+        // a narrow last chunk (or a narrow layer) is multiplied at its own width: N = the chunk's neurons rounded up to 16
+        const int n_left = L.N - nc * SG_NC;
+        const uint32_t n_mma = n_left >= SG_NC ? (uint32_t)SG_NC : (uint32_t)((n_left + 15) & ~15);
+        const uint32_t idesc = idesc0 | ((n_mma >> 3) << 17);
         for (int kc = 0; kc < n_kc; kc++, it_b++) {
           const uint32_t st = it_b % NSTAGE;
           if (nc == 0) mbar_wait(&a_full[kc], it_t & 1u);
@@ -353,6 +361,7 @@ __global__ void __launch_bounds__(THREADS, 1) sg_layer_kernel(const __grid_const
         mbar_wait(&t_full[buf], (it_acc >> 1) & 1u);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const int j0 = nc * SG_NC + half * 16;
+        const bool partial = j0 + 16 > L.N;                    // warp-uniform: this share reaches past the layer's last neuron
         uint32_t w[SG_S][4];
 #pragma unroll
         for (int round = 0; round < 2; round++) {
@@ -382,14 +391,16 @@ __global__ void __launch_bounds__(THREADS, 1) sg_layer_kernel(const __grid_const
               const int bq = (s_tau[j] + rndb) >> shb;
               if constexpr (SG_S == 4) {
                 const int lo = (int)vs;
-                ovf |= (uint32_t)(vs >> 32) ^ (uint32_t)(lo >> 31);          // non-zero: the value left 32 bits (a violated bound)
+                if (!(partial && j >= L.N)) ovf |= (uint32_t)(vs >> 32) ^ (uint32_t)(lo >> 31);   // non-zero: the value left 32 bits (a violated bound)
                 int q = lo + bq;
                 if (MODE == M_RELU) q = max(q, 0);
+                if (partial && j >= L.N) q = 0;                                 // columns the narrow MMA did not write
                 qmax32 = max(qmax32, MODE == M_RELU ? q : abs(q));
                 qv[c] = q;
               } else {
                 long long q = vs + bq;
                 if (MODE == M_RELU) q = q < 0 ? 0 : q;
+                if (partial && j >= L.N) q = 0;
                 const long long qa = q < 0 ? -q : q; qmax = qa > qmax ? qa : qmax;
                 qv[c] = (qint)q;
               }
@@ -400,7 +411,7 @@ __global__ void __launch_bounds__(THREADS, 1) sg_layer_kernel(const __grid_const
               const double z = fma(V, zscale, s_bias[j]);
               if (MODE == M_LAST) { zl[cc] = z; qv[c] = 0; }
               else {
-                const long long q = __double2ll_rn(((j < L.N) ? activate(ACT, z, 0.0) : 0.0) * qscale);
+                const long long q = (j < L.N) ? __double2ll_rn(activate(ACT, z, 0.0) * qscale) : 0;
                 const long long qa = q < 0 ? -q : q; qmax = qa > qmax ? qa : qmax;
                 qv[c] = (qint)q;
               }

@@ -54,11 +54,12 @@ long fjp_engine_launch_count(const fjp_engine* e);
  * per failed prediction of S/models/prediction/Prediction.scala:47-62 with per-batch counters an operator can export
  * as Flink metrics. */
 void fjp_engine_status_counts(const fjp_engine* e, uint64_t out[6]);
-/* Diagnostics of the tensor-core path of dense layers (NeuralNetwork models, large batches): out[0] = events that took it so
- * far, out[1] = how many of those its margin test handed back to the FP64 kernels (the events whose class could not be
- * decided inside the path's error bound; their answers are the FP64 kernels').  Waits for the engine's streams.  The path
- * stands in for JPMML's NeuralNetworkEvaluator behind S/api/PmmlModel.scala:159-160. */
-int fjp_engine_tensor_path_counts(fjp_engine* e, uint64_t out[2]);
+/* Diagnostics of the two fast paths that decide a class label only outside a proven error bound and hand every other event
+ * to the kernels that follow JPMML's arithmetic order:
+ *   out[0], out[1]  tensor-core path of dense layers (NeuralNetwork models, large batches): events taken / handed back
+ *   out[2], out[3]  fused-multiply-add path of the dense tile kernel (softmax RegressionModel, k-means ClusteringModel)
+ * Waits for the engine's streams.  The paths stand in for JPMML's evaluators behind S/api/PmmlModel.scala:159-160. */
+int fjp_engine_fast_path_counts(fjp_engine* e, uint64_t out[4]);
 
 /* ---- model load: PMML bytes in, device-resident flattened model out -----------------------------------------
  * Replaces PmmlModel.fromReader (S/api/PmmlModel.scala:53-61): JAXB unmarshal + ModelEvaluatorFactory.  The bytes
