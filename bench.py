@@ -323,17 +323,39 @@ def main():
         if rc != 0:
             raise RuntimeError(L.fjp_last_error().decode())
 
-    for _ in range(2):
-        step_e2e()
-    barrier()
+    def time_e2e(step):
+        for _ in range(2):
+            step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            step()
+        torch.cuda.synchronize(dev)
+        return time.perf_counter() - t0
+
     e2e_steps = max(3, min(args.steps, 10))
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        step_e2e()
-    torch.cuda.synchronize(dev)
-    t_e2e = time.perf_counter() - t0
-    clocks = sampler.stop()
+    t_e2e_f64 = time_e2e(step_e2e)
     e2e_match = bool(torch.equal(hS[:4096], score[:4096].cpu()))
+    # float rows: the model's tests see every feature through ONE float (fjp_model_float_row_modes), so the binding can ship
+    # 4-byte values rounded the way the model prescribes -- half the PCIe bytes, bit-identical scores
+    modes = eng.float_row_modes(model)
+    t_e2e, e2e_rows, e2e_f32_match = t_e2e_f64, "double", None
+    if modes is not None:
+        md = torch.from_numpy(modes.astype(np.int64)).to(dev)[None, :]
+        Xd = X[:ne]; f = Xd.to(torch.float32); back = f.to(torch.float64)
+        f = torch.where((back < Xd) & (md == 1), torch.nextafter(f, torch.full_like(f, float("inf"))), f)
+        f = torch.where((back > Xd) & (md == 2), torch.nextafter(f, torch.full_like(f, float("-inf"))), f)
+        hXf = torch.empty(ne, F, dtype=torch.float32).pin_memory(); hXf.copy_(f)
+        del f, back, Xd
+        hS2 = torch.empty(ne, dtype=torch.float64).pin_memory()
+
+        def step_e2e_f32():
+            rc = L.fjp_score_batch_f32(eng._h, model._h, hXf.data_ptr(), hP.data_ptr(), ne, F, hS2.data_ptr(), hT.data_ptr(), None)
+            if rc != 0:
+                raise RuntimeError(L.fjp_last_error().decode())
+        t_e2e = time_e2e(step_e2e_f32); e2e_rows = "float"
+        e2e_f32_match = bool(torch.equal(hS2, hS))          # every score of the float rows against the double rows
+    clocks = sampler.stop()
 
     # ------------------------------------------------------------------ the other named shapes (all at N = 1; C5 halves at N > 1)
     cfg_out = {}
@@ -347,9 +369,9 @@ def main():
     cfg_keys = sorted(cfg_out)
 
     # ------------------------------------------------------------------ max over ranks
-    maxed = D.max_over_ranks(dist, [ms_dev, t_e2e * 1e3] + [cfg_out[k]["ms_per_step"] for k in cfg_keys], dev)
-    ms_dev_max, ms_e2e_max = maxed[0], maxed[1]
-    for k, v in zip(cfg_keys, maxed[2:]):
+    maxed = D.max_over_ranks(dist, [ms_dev, t_e2e * 1e3, t_e2e_f64 * 1e3] + [cfg_out[k]["ms_per_step"] for k in cfg_keys], dev)
+    ms_dev_max, ms_e2e_max, ms_e2e_f64_max = maxed[0], maxed[1], maxed[2]
+    for k, v in zip(cfg_keys, maxed[3:]):
         cfg_out[k]["ms_per_step"] = v
 
     # ------------------------------------------------------------------ latency sweep + CPU baseline: rank 0 only
@@ -422,9 +444,13 @@ def main():
                 "data": "synthetic (torch philox on device, seed 20261110+1000*rank)",
                 "config": {"workload": WORKLOAD, "events_per_gpu_per_step": n, "l2_policy": "inputs (3.4 GB/GPU) larger than L2",
                            "model": model.describe, "parallelism": f"events sharded over {world} GPU(s), model replicated, no collective" + (f"; rank 0 bound to NUMA node {numa_node}" if numa_node is not None else "")},
-                "e2e": {"value": e2e_value, "unit": "events/s", "h2d_bytes_per_step": ne * (F * 8 + W * 4), "d2h_bytes_per_step": ne * 9,
-                        "events_per_gpu_per_step": ne, "steps": e2e_steps, "matches_device_path": e2e_match,
-                        "api": "fjp_score_batch (pinned host buffers, chunked copy/compute overlap)"},
+                "e2e": {"value": e2e_value, "unit": "events/s", "h2d_bytes_per_step": ne * (F * (4 if e2e_rows == "float" else 8) + W * 4), "d2h_bytes_per_step": ne * 9,
+                        "events_per_gpu_per_step": ne, "steps": e2e_steps, "matches_device_path": e2e_match, "rows": e2e_rows,
+                        "api": ("fjp_score_batch_f32: float rows rounded per fjp_model_float_row_modes (the ensemble's tests see one float per value), "
+                                "pinned host buffers, chunked copy/compute overlap" if e2e_rows == "float" else "fjp_score_batch (pinned host buffers, chunked copy/compute overlap)"),
+                        "float_rows_match_double_rows": e2e_f32_match,
+                        "double_rows": {"value": D.whole_job_rate(ne, world, e2e_steps, ms_e2e_f64_max), "h2d_bytes_per_step": ne * (F * 8 + W * 4), "api": "fjp_score_batch"},
+                        "frac_of_h2d_copy_peak": (e2e_value / world * (F * (4 if e2e_rows == "float" else 8) + W * 4) / 1e9 / micro["h2d_pinned_GBs"]) if micro.get("h2d_pinned_GBs") else None},
                 "gpu_launches": launches, "rows_scored_ok": ok_rows, "roofline": roof, "cpu_baseline": cpu, "clocks": clocks, "configs": configs,
                 "latency_ms": latency}
         print(json.dumps(line), flush=True)

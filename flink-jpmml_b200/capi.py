@@ -74,6 +74,8 @@ def lib():
         "fjp_score_batch": (i32, [vp, vp, vp, vp, vp, lng, i32, vp, vp, vp]),
         "fjp_score_batch_ex": (i32, [vp, vp, vp, vp, vp, lng, i32, vp, vp, vp, vp, i32, vp, i32]),
         "fjp_score_sparse": (i32, [vp, vp, vp, vp, vp, vp, lng, i32, vp, vp, vp]),
+        "fjp_model_float_row_modes": (i32, [vp, vp, i32]),
+        "fjp_score_batch_f32": (i32, [vp, vp, vp, vp, lng, i32, vp, vp, vp]),
         "fjp_score_device": (i32, [vp, vp, vp, vp, vp, lng, i32, vp, vp, vp, vp]),
         "fjp_score_sparse_noalloc": (i32, [vp, vp, vp, vp, vp, lng, i32, vp, vp, vp]),
         "fjp_submit": (i32, [vp, vp, vp, vp, vp, lng, i32, vp, vp, vp, C.POINTER(i32)]),
@@ -91,7 +93,7 @@ EXPORTS = ["fjp_version", "fjp_last_error", "fjp_max_inflight", "fjp_engine_crea
            "fjp_model_replicate", "fjp_model_num_fields", "fjp_model_field_name", "fjp_model_name", "fjp_model_family",
            "fjp_model_num_labels", "fjp_model_label", "fjp_model_num_segments", "fjp_model_describe", "fjp_model_device_bytes",
            "fjp_table_add", "fjp_table_del", "fjp_table_get", "fjp_table_size", "fjp_table_epoch", "fjp_host_alloc",
-           "fjp_host_free", "fjp_score_batch", "fjp_score_batch_ex", "fjp_score_sparse", "fjp_score_sparse_noalloc", "fjp_score_device", "fjp_submit", "fjp_wait"]
+           "fjp_host_free", "fjp_score_batch", "fjp_score_batch_ex", "fjp_score_sparse", "fjp_model_float_row_modes", "fjp_score_batch_f32", "fjp_score_sparse_noalloc", "fjp_score_device", "fjp_submit", "fjp_wait"]
 
 
 def _ptr(a):
@@ -226,6 +228,36 @@ class Engine:
         score = np.empty(n, dtype=np.float64); status = np.empty(n, dtype=np.uint8); aux = np.empty(n, dtype=np.int32)
         _check(lib().fjp_score_sparse(self._h, model._h if model else None, _ptr(row_ptr), _ptr(indices), _ptr(values), _ptr(rp), n, vec_size,
                                       _ptr(score), _ptr(status), _ptr(aux)))
+        return {"score": score, "status": status, "aux": aux}
+
+    def float_row_modes(self, model):
+        """Per vector slot: 0 cast, 1 round up, 2 round down -- or None when the model needs double rows."""
+        F = lib().fjp_model_float_row_modes(model._h, None, 0)
+        if F == 0:
+            return None
+        modes = np.zeros(F, dtype=np.uint8)
+        lib().fjp_model_float_row_modes(model._h, _ptr(modes), F)
+        return modes
+
+    @staticmethod
+    def narrow_rows(X, modes):
+        """What a binding does when it packs a micro-batch of float rows: every double becomes the float the model's tests see."""
+        X = np.asarray(X, dtype=np.float64)
+        with np.errstate(over="ignore"):
+            f = X.astype(np.float32)
+        back = f.astype(np.float64)
+        up = (back < X) & (modes[None, :] == 1)          # rounded down by the cast but must round up
+        dn = (back > X) & (modes[None, :] == 2)
+        f = np.where(up, np.nextafter(f, np.float32(np.inf)), f)
+        f = np.where(dn, np.nextafter(f, np.float32(-np.inf)), f)
+        return np.ascontiguousarray(f, dtype=np.float32)
+
+    def score_f32(self, model, Xf, present_bits=None):
+        Xf = np.ascontiguousarray(Xf, dtype=np.float32)
+        n, F = Xf.shape
+        pb = None if present_bits is None else np.ascontiguousarray(present_bits, dtype=np.uint32)
+        score = np.empty(n, dtype=np.float64); status = np.empty(n, dtype=np.uint8); aux = np.empty(n, dtype=np.int32)
+        _check(lib().fjp_score_batch_f32(self._h, model._h if model else None, _ptr(Xf), _ptr(pb), n, F, _ptr(score), _ptr(status), _ptr(aux)))
         return {"score": score, "status": status, "aux": aux}
 
     # ---- scoring (host buffers)

@@ -9,6 +9,7 @@
 
 #include <atomic>
 #include <condition_variable>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <memory>
@@ -133,6 +134,7 @@ struct Carve {  // sub-allocation inside a slot arena
 struct HostBatch {
   const double* X; const uint32_t* present; const double* replace; long n; int vec_size;
   double* score; uint8_t* status; int32_t* aux; int32_t* node_ids; int node_stride; double* probs; int prob_stride;
+  const float* Xf;   // float rows (fjp_score_batch_f32): X is NULL then
 };
 
 // enqueue H2D + kernel + D2H for rows [lo, hi) of hb on slot s
@@ -140,13 +142,18 @@ static int enqueue_chunk(fjp_engine* e, fjp_model* m, Slot& s, const HostBatch& 
   const long n = hi - lo; const int F = hb.vec_size, W = (F + 31) / 32;
   Carve c;
   size_t oX = c.take((size_t)n * F * 8), oP = hb.present ? c.take((size_t)n * W * 4) : 0, oR = hb.replace ? c.take((size_t)n * 8) : 0;
+  size_t oF = hb.Xf ? c.take((size_t)n * F * 4) : 0;
   size_t oS = c.take((size_t)n * 8), oT = c.take((size_t)n), oA = hb.aux ? c.take((size_t)n * 4) : 0;
   size_t oN = hb.node_ids ? c.take((size_t)n * hb.node_stride * 4) : 0, oQ = hb.probs ? c.take((size_t)n * hb.prob_stride * 8) : 0;
   const size_t dsz = score_scratch_bytes(m, n, hb.probs != nullptr, hb.node_ids != nullptr); size_t oD = dsz ? c.take(dsz) : 0;   // augmented rows (derived fields) / leaf values (small-batch forest path) / digit planes
   if (slot_reserve(s, c.off)) return -1;
   BatchArgs a{}; a.stats = e->d_stats;
   a.X = reinterpret_cast<double*>(s.buf + oX); a.n = n; a.present_stride = W;
-  CK(cudaMemcpyAsync(s.buf + oX, hb.X + lo * (long)F, (size_t)n * F * 8, cudaMemcpyHostToDevice, s.s));
+  int launches = 0;
+  if (hb.Xf) {   // half the bytes over PCIe; widened on the device (exact)
+    CK(cudaMemcpyAsync(s.buf + oF, hb.Xf + lo * (long)F, (size_t)n * F * 4, cudaMemcpyHostToDevice, s.s));
+    CK(launch_widen_f32(reinterpret_cast<const float*>(s.buf + oF), reinterpret_cast<double*>(s.buf + oX), n * (long)F, s.s, &launches));
+  } else CK(cudaMemcpyAsync(s.buf + oX, hb.X + lo * (long)F, (size_t)n * F * 8, cudaMemcpyHostToDevice, s.s));
   if (hb.present) { a.present = reinterpret_cast<uint32_t*>(s.buf + oP); CK(cudaMemcpyAsync(s.buf + oP, hb.present + lo * (long)W, (size_t)n * W * 4, cudaMemcpyHostToDevice, s.s)); }
   if (hb.replace) { a.replace = reinterpret_cast<double*>(s.buf + oR); CK(cudaMemcpyAsync(s.buf + oR, hb.replace + lo, (size_t)n * 8, cudaMemcpyHostToDevice, s.s)); }
   a.score = reinterpret_cast<double*>(s.buf + oS); a.status = s.buf + oT;
@@ -155,7 +162,6 @@ static int enqueue_chunk(fjp_engine* e, fjp_model* m, Slot& s, const HostBatch& 
   a.probs = hb.probs ? reinterpret_cast<double*>(s.buf + oQ) : nullptr; a.prob_stride = hb.prob_stride;
   if (hb.node_ids) CK(cudaMemsetAsync(s.buf + oN, 0xFF, (size_t)n * hb.node_stride * 4, s.s));
   if (hb.probs) CK(cudaMemsetAsync(s.buf + oQ, 0xFF, (size_t)n * hb.prob_stride * 8, s.s));
-  int launches = 0;
   CK(launch_score_any(m->dev, a, dsz ? s.buf + oD : nullptr, s.s, &launches));
   e->launches += launches;
   CK(cudaMemcpyAsync(hb.score + lo, s.buf + oS, (size_t)n * 8, cudaMemcpyDeviceToHost, s.s));
@@ -367,30 +373,53 @@ uint64_t fjp_table_epoch(const fjp_engine* e) { return std::atomic_load(&e->tabl
 void* fjp_host_alloc(size_t bytes) { void* p = nullptr; if (cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) return nullptr; return p; }
 void fjp_host_free(void* p) { if (p) cudaFreeHost(p); }
 
-int fjp_score_batch_ex(fjp_engine* e, fjp_model* m, const double* X, const uint32_t* present, const double* replace,
-                       long n, int vec_size, double* score, uint8_t* status, int32_t* aux,
-                       int32_t* node_ids, int node_stride, double* probs, int prob_stride) {
+static int score_host_batch(fjp_engine* e, fjp_model* m, const HostBatch& hb) {
+  const long n = hb.n; const int vec_size = hb.vec_size;
   if (n <= 0) return 0;
-  HostBatch hb{X, present, replace, n, vec_size, score, status, aux, node_ids, node_stride, probs, prob_stride};
-  if (host_short_circuit(m, hb)) { count_statuses(e, status, n); return 0; }
+  if (host_short_circuit(m, hb)) { count_statuses(e, hb.status, n); return 0; }
   if (!m->d_blob) return fail("model was compiled without an engine: it cannot score");
   CK(cudaSetDevice(e->device));
   if (m->device != e->device) return fail("model lives on another device; use fjp_model_replicate");
   // chunked 2-slot pipeline: copy-in of chunk i+1 overlaps the kernel and copy-out of chunk i
-  long rows = (long)((size_t(24) << 20) / ((size_t)vec_size * 8 + 16));
+  long rows = (long)((size_t(24) << 20) / ((size_t)vec_size * (hb.Xf ? 4 : 8) + 16));
   if (rows < 4096) rows = 4096; if (rows > (1 << 18)) rows = 1 << 18;
+  // large batches: eight chunks (up to 2^18 rows each) -- a chunk then fills the chip on the throughput kernels, and the
+  // un-overlapped first copy / last kernel stay an eighth of the batch (measured on C4: tools/e2e_chunks.py)
+  if (n / 8 > rows) rows = std::min<long>(n / 8, 1 << 18);
+  if (const char* v = getenv("FJP_CHUNK_ROWS")) { long r = atol(v); if (r >= 256) rows = r; }   // tuning aid
   int s0 = acquire_slot(e), s1 = n > rows ? try_acquire_slot(e) : -1;
   int used[2] = {s0, s1}; int ns = s1 >= 0 ? 2 : 1; int rc = 0; long k = 0;
   for (long lo = 0; lo < n && rc == 0; lo += rows, k++) rc = enqueue_chunk(e, m, e->slots[used[k % ns]], hb, lo, std::min(n, lo + rows));
   for (int i = 0; i < ns; i++) { cudaError_t ce = cudaStreamSynchronize(e->slots[used[i]].s); if (ce != cudaSuccess && rc == 0) rc = fail(std::string("scoring failed: ") + cudaGetErrorString(ce)); release_slot(e, used[i]); }
-  if (rc == 0) count_statuses(e, status, n);
+  if (rc == 0) count_statuses(e, hb.status, n);
   return rc;
+}
+
+int fjp_score_batch_ex(fjp_engine* e, fjp_model* m, const double* X, const uint32_t* present, const double* replace,
+                       long n, int vec_size, double* score, uint8_t* status, int32_t* aux,
+                       int32_t* node_ids, int node_stride, double* probs, int prob_stride) {
+  HostBatch hb{X, present, replace, n, vec_size, score, status, aux, node_ids, node_stride, probs, prob_stride, nullptr};
+  return score_host_batch(e, m, hb);
+}
+
+int fjp_model_float_row_modes(const fjp_model* m, uint8_t* modes, int cap) {
+  if (!m || m->cm.float_row_modes.empty()) return 0;
+  const int F = (int)m->cm.float_row_modes.size();
+  if (modes) for (int i = 0; i < F && i < cap; i++) modes[i] = m->cm.float_row_modes[i];
+  return F;
+}
+
+int fjp_score_batch_f32(fjp_engine* e, fjp_model* m, const float* X, const uint32_t* present, long n, int vec_size,
+                        double* score, uint8_t* status, int32_t* aux) {
+  if (m && m->cm.float_row_modes.empty()) return fail("fjp_score_batch_f32: this model's tests need the double values (fjp_model_float_row_modes says 0); use fjp_score_batch");
+  HostBatch hb{nullptr, present, nullptr, n, vec_size, score, status, aux, nullptr, 0, nullptr, 0, X};
+  return score_host_batch(e, m, hb);
 }
 
 int fjp_score_sparse(fjp_engine* e, fjp_model* m, const int64_t* row_ptr, const int32_t* indices, const double* values,
                      const double* replace, long n, int vec_size, double* score, uint8_t* status, int32_t* aux) {
   if (n <= 0) return 0;
-  HostBatch hb{nullptr, nullptr, replace, n, vec_size, score, status, aux, nullptr, 0, nullptr, 0};
+  HostBatch hb{nullptr, nullptr, replace, n, vec_size, score, status, aux, nullptr, 0, nullptr, 0, nullptr};
   if (host_short_circuit(m, hb)) { count_statuses(e, status, n); return 0; }
   if (!m->d_blob) return fail("model was compiled without an engine: it cannot score");
   CK(cudaSetDevice(e->device));
@@ -471,7 +500,7 @@ int fjp_score_device(fjp_engine* e, fjp_model* m, const double* dX, const uint32
 
 int fjp_submit(fjp_engine* e, fjp_model* m, const double* X, const uint32_t* present, const double* replace,
                long n, int vec_size, double* score, uint8_t* status, int32_t* aux, int* ticket) {
-  HostBatch hb{X, present, replace, n, vec_size, score, status, aux, nullptr, 0, nullptr, 0};
+  HostBatch hb{X, present, replace, n, vec_size, score, status, aux, nullptr, 0, nullptr, 0, nullptr};
   *ticket = -1;
   CK(cudaSetDevice(e->device));
   // never blocks: slots are shared by all host threads, so a thread that waited here while holding tickets of its own

@@ -1810,6 +1810,21 @@ cudaError_t launch_expand_sparse(const long long* row_ptr, const int32_t* idx, c
 
 __device__ double norm_cont_dev(const double* __restrict__ pts, int n, int outliers, double x, bool& missing) { return norm_cont(pts, n, outliers, x, missing); }
 
+// float rows (fjp_score_batch_f32): widened on the device into the double rows every kernel reads (exact)
+__global__ void __launch_bounds__(256) widen_f32_kernel(const float* __restrict__ src, double* __restrict__ dst, long count) {
+  const long i = (blockIdx.x * (long)blockDim.x + threadIdx.x) * 4;
+  if (i + 3 < count) {
+    const float4 v = __ldcs(reinterpret_cast<const float4*>(src + i));
+    reinterpret_cast<double2*>(dst + i)[0] = make_double2((double)v.x, (double)v.y); reinterpret_cast<double2*>(dst + i)[1] = make_double2((double)v.z, (double)v.w);
+  } else for (long k = i; k < count; k++) dst[k] = (double)src[k];
+}
+cudaError_t launch_widen_f32(const float* src, double* dst, long count, cudaStream_t s, int* launches) {
+  if (count <= 0) return cudaSuccess;
+  if (launches) (*launches)++;
+  widen_f32_kernel<<<(unsigned)((count / 4 + 256) / 256), 256, 0, s>>>(src, dst, count);
+  return cudaGetLastError();
+}
+
 // ================================================================================================ derived fields
 // Pre-pass for models with a TransformationDictionary / LocalTransformations: one thread per event prepares the F_in raw
 // slots (the same preparation every kernel fuses otherwise), runs the DerivedField programs and writes the augmented row

@@ -41,6 +41,7 @@ size_t forest_slice_scratch_bytes(const DeviceModel& m, long n);     // work are
 size_t forest_compact_scratch_bytes(const DeviceModel& m, long n);   // throughput path only
 cudaError_t launch_expand_sparse(const long long* row_ptr, const int32_t* idx, const double* val, long n, int F,
                                  double* X, uint32_t* present, cudaStream_t s, int* launches);
+cudaError_t launch_widen_f32(const float* src, double* dst, long count, cudaStream_t s, int* launches);   // src, dst 16-byte aligned
 size_t derived_scratch_bytes(const DeviceModel& m, long n);
 size_t sliced_scratch_bytes(const DeviceModel& m, const BatchArgs& a);
 size_t dense_fma_scratch_bytes(const DeviceModel& m, const BatchArgs& a);  // FMA paths of the dense tile kernel (0: not taken for this batch)   // tensor-core path of dense layers (0: not taken for this batch)

@@ -284,6 +284,9 @@ struct CompiledModel {
   struct Fixup { size_t off; size_t field_off; };  // field_off: byte offset of the pointer inside DeviceModel
   std::vector<Fixup> fixups;
   size_t n_nodes = 0;           // statistics
+  // per vector slot, when the model can be scored bit-identically from FLOAT rows (fjp_score_batch_f32): 0 = the field is a float
+  // field (plain cast), 1 = round the double up to float, 2 = round it down.  Empty: double rows only.
+  std::vector<uint8_t> float_row_modes;
 };
 
 CompiledModel compile_pmml(const char* data, size_t len);

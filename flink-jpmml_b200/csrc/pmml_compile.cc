@@ -825,6 +825,12 @@ struct ForestBuilder {
     }
     fd.enc = float_ok ? ENC_FLOAT : ENC_RANK;
     b.put(&fd.feat_mode, feat_mode);
+    // every test of the ensemble sees a feature only through that one float: float rows rounded the same way score identically
+    // (fields whose preparation could tell the double from its float image -- intervals, value lists, integers -- keep double rows)
+    if (float_ok && b.cm.dev.prep_simple && b.cm.dev.derived.n_derived == 0) {
+      bool plain = true; for (int f = 0; f < F; f++) plain = plain && (b.slot_dtype[f] == DT_FLOAT || b.slot_dtype[f] == DT_DOUBLE);
+      if (plain) b.cm.float_row_modes.assign(feat_mode.begin(), feat_mode.begin() + F);
+    }
     std::vector<uint32_t> K(thr.size());
     std::vector<int32_t> rank_off(F + 1, 0); std::vector<double> rank_thr;
     if (float_ok) {

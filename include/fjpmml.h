@@ -123,6 +123,17 @@ int fjp_score_batch(fjp_engine* e, fjp_model* m, const double* X, const uint32_t
 int fjp_score_batch_ex(fjp_engine* e, fjp_model* m, const double* X, const uint32_t* present, const double* replace,
                        long n, int vec_size, double* score, uint8_t* status, int32_t* aux,
                        int32_t* node_ids, int node_stride, double* probs, int prob_stride);
+/* Float rows: half the bytes over PCIe for models whose tests never need more than one float per value.
+ * A tree ensemble compiled with the float key encoding looks at a double feature only through RU(x) (all its tests on that
+ * field are `x <= t`) or RD(x) (`x < t`) with float thresholds t, and at a float-typed field through (float)x, which is what
+ * JPMML's cast to the field's dataType does as well.  fjp_model_float_row_modes fills, per vector slot, how the binding must
+ * turn the Vector's double into the float it ships: 0 = plain cast (float field), 1 = round up, 2 = round down; it returns
+ * vec_size, or 0 when the model needs the doubles (modes may be NULL to just ask).  Rows prepared that way score bit-identically
+ * to the double rows through fjp_score_batch (S/api/converter/VectorConverter.scala:68-86 is where the reference copies the
+ * Vector's values; here the copy narrows them).  Same conventions as fjp_score_batch otherwise; no replaceNan. */
+int fjp_model_float_row_modes(const fjp_model* m, uint8_t* modes, int cap);
+int fjp_score_batch_f32(fjp_engine* e, fjp_model* m, const float* X, const uint32_t* present, long n, int vec_size,
+                        double* score, uint8_t* status, int32_t* aux);
 /* SparseVector rows in CSR form: row i holds indices[row_ptr[i] .. row_ptr[i+1]) with their values; every index that is
  * not listed is a missing value, an explicit 0.0 is present (S/api/converter/VectorConverter.scala:80-86, 100-103).  The rows
  * are expanded on the device (O(nnz), where the reference's toDenseData is O(size * nnz), :100-103); only the non-zeros

@@ -287,3 +287,31 @@ def test_double_thresholds_use_rank_keys(engine, oracle, gen, monkeypatch):
     compare(r, o, exact_scores=True)
     assert np.array_equal(r["node_ids"], o["node_ids"])
     assert np.array_equal(engine.score(m, X, pb)["score"], gen.gbt_numpy(arr, np.nan_to_num(X, nan=np.inf), pres))
+
+
+@pytest.mark.parametrize("dtype,operator", [("double", "lessOrEqual"), ("float", "lessOrEqual"), ("double", "lessThan")])
+def test_float_rows_score_identically(engine, gen, oracle, dtype, operator):
+    """fjp_score_batch_f32: rows narrowed to float the way fjp_model_float_row_modes prescribes (round up for `<=` tests, down
+    for `<`, plain cast for float fields) give the double rows' scores bit for bit -- including values that sit exactly on, one
+    ulp above and one ulp below a threshold, huge values, infinities and NaN."""
+    if operator == "lessThan":
+        pm = gen.gbt_pruned_pmml(T=40, max_depth=6, F=20, seed=9, operator="lessThan", dtype=dtype)
+        F = 20
+    else:
+        pm, _ = gen.gbt_pmml(T=64, depth=8, F=100, seed=11, dtype=dtype)
+        F = 100
+    m = engine.compile(pm)
+    modes = engine.float_row_modes(m)
+    assert modes is not None and len(modes) == F and set(modes.tolist()) <= ({0} if dtype == "float" else {1, 2})
+    X, pres, pb = gen.events(148 * 640 + 777, F, 12, 0.1)
+    thr = np.float32(X[:2000, :].astype(np.float32)).astype(np.float64)        # plant values on / next to float grid points
+    X[:2000] = thr; X[2000:4000] = np.nextafter(X[2000:4000].astype(np.float32).astype(np.float64), np.inf)
+    X[4000:6000] = np.nextafter(X[4000:6000].astype(np.float32).astype(np.float64), -np.inf)
+    X[6000, :5] = [1e300, -1e300, np.inf, -np.inf, np.nan]
+    ref = engine.score(m, X, pb)
+    r = engine.score_f32(m, engine.narrow_rows(X, modes), pb)
+    assert np.array_equal(r["status"], ref["status"]) and np.array_equal(r["score"], ref["score"], equal_nan=True)
+    o = oracle.OracleModel(pm).predict(X[:8000], pb[:8000], nthreads=4)
+    assert np.array_equal(r["score"][:8000], o["score"], equal_nan=True) and np.array_equal(r["status"][:8000], o["status"])
+    # a model whose tests need the doubles says so
+    assert engine.float_row_modes(engine.compile(gen.config_c2(k=4, F=8)[0])) is None
