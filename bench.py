@@ -375,7 +375,25 @@ def main():
         cfg_out[k]["ms_per_step"] = v
 
     # ------------------------------------------------------------------ latency sweep + CPU baseline: rank 0 only
-    latency, cpu = None, None
+    latency, cpu, replicate = None, None, None
+    # ------------------------------------------------------------------ model replication by peer copy (N >= 2, rank 0, after the timed regions)
+    # The control stream reaches every subtask (S/package.scala:63-65); here a compiled model is copied GPU -> GPU over NVLink
+    # (cudaMemcpyPeerAsync, no kernel reads a peer's memory) instead of being parsed and compiled once per GPU.
+    if rank == 0 and world > 1 and torch.cuda.device_count() > 1:
+        try:
+            peer = (local + 1) % torch.cuda.device_count()
+            eng2 = capi.Engine(peer)
+            t1 = time.perf_counter(); m2 = eng2.replicate(model); t_rep = time.perf_counter() - t1
+            t1 = time.perf_counter(); m3 = eng2.compile(pm); t_cmp = time.perf_counter() - t1
+            nr = 1 << 16
+            xs = hX[:nr].numpy(); ps = hP[:nr].numpy().view(np.uint32)
+            ra = eng.score(model, xs, ps); rb = eng2.score(m2, xs, ps)
+            replicate = {"bytes": model.device_bytes, "ms": t_rep * 1e3, "compile_instead_ms": t_cmp * 1e3, "from_gpu": local, "to_gpu": peer, "events_checked": nr,
+                         "bit_identical": bool(np.array_equal(ra["score"], rb["score"]) and np.array_equal(ra["status"], rb["status"]))}
+            m2.release(); m3.release(); eng2.close()
+            torch.cuda.set_device(local)
+        except Exception as ex:          # noqa: BLE001
+            replicate = {"error": repr(ex)}
     if rank == 0 and not args.no_latency:
         latency = {}
         ticket = C.c_int()
@@ -451,7 +469,7 @@ def main():
                         "float_rows_match_double_rows": e2e_f32_match,
                         "double_rows": {"value": D.whole_job_rate(ne, world, e2e_steps, ms_e2e_f64_max), "h2d_bytes_per_step": ne * (F * 8 + W * 4), "api": "fjp_score_batch"},
                         "frac_of_h2d_copy_peak": (e2e_value / world * (F * (4 if e2e_rows == "float" else 8) + W * 4) / 1e9 / micro["h2d_pinned_GBs"]) if micro.get("h2d_pinned_GBs") else None},
-                "gpu_launches": launches, "rows_scored_ok": ok_rows, "roofline": roof, "cpu_baseline": cpu, "clocks": clocks, "configs": configs,
+                "gpu_launches": launches, "rows_scored_ok": ok_rows, "roofline": roof, "cpu_baseline": cpu, "clocks": clocks, "configs": configs, "replicate": replicate,
                 "latency_ms": latency}
         print(json.dumps(line), flush=True)
     if dist:
