@@ -1583,6 +1583,7 @@ static cudaError_t launch_dense_tile(const DeviceModel& m, const BatchArgs& a, c
 // dense rows, batches that fill the chip.  Work area: the re-scoring counter + one row index per event.  FJP_DENSE_FMA=0 switches
 // them off, =2 takes them for every batch size.
 size_t dense_fma_scratch_bytes(const DeviceModel& m, const BatchArgs& a) {
+  if (sliced_dense_takes(m, a)) return 256 + (((size_t)a.n * 4 + 255) & ~size_t(255));   // the fused tensor-core layer keeps the same re-scoring list
   const int mode = env_int("FJP_DENSE_FMA", 1);
   if (!mode || a.present || a.replace || !m.prep_identity || a.row_map || a.node_ids) return 0;
   query_device();
@@ -1720,6 +1721,15 @@ cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t 
       if (m.reg.dense) {
         DenseView dv{}; dv.wt = m.reg.dense_wt; dv.icpt = m.reg.intercept; dv.C = m.reg.n_tables; dv.amax = m.reg.dense_amax; dv.bmax = m.reg.dense_bmax;
         const bool hasmiss = a.present != nullptr || a.replace != nullptr || !m.prep_identity;
+        // wide softmax models, labels only: the fused tensor-core layer (sliced_gemm.cuh); what it cannot decide is re-scored below
+        if (slice_scratch && dense_fma_scratch_bytes(m, a) && sliced_dense_takes(m, a)) {
+          dv.fb_count = static_cast<int32_t*>(slice_scratch); dv.fb_rows = dv.fb_count + 64;
+          cudaError_t e = cudaMemsetAsync(dv.fb_count, 0, 4, s); if (e != cudaSuccess) return e;
+          e = launch_sliced_dense(m, a, dv.fb_count, dv.fb_rows, s); if (e != cudaSuccess) return e;
+          if (launches) (*launches)++;
+          BatchArgs fb = a; fb.row_map = dv.fb_rows; fb.n_dev = dv.fb_count;
+          return launch_dense_tile(m, fb, dv, true, 0, s);
+        }
         // softmax classification over plain dense rows: fused multiply-add + margin test, the undecided events re-scored below
         if (slice_scratch && dense_fma_scratch_bytes(m, a)) {
           dv.fb_count = static_cast<int32_t*>(slice_scratch); dv.fb_rows = dv.fb_count + 64;

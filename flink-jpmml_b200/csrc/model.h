@@ -145,48 +145,7 @@ struct ClusterDesc {
   const double* fast_wt; const double* fast_icpt; double cmax;
 };
 
-// ---- regression / neural network ---------------------------------------------------------------------
-enum : int { NORM_NONE = 0, NORM_SIMPLEMAX = 1, NORM_SOFTMAX = 2, NORM_LOGIT = 3, NORM_PROBIT = 4, NORM_CLOGLOG = 5,
-             NORM_EXP = 6, NORM_LOGLOG = 7, NORM_CAUCHIT = 8 };
-struct RegTerm { int32_t slot; int32_t exponent; double coef; };           // NumericPredictor
-struct RegCat { int32_t slot; int32_t pad; double value; double coef; };   // CategoricalPredictor on a numeric field
-struct RegressionDesc {
-  int n_tables, classify, norm, dense;  // dense: every table lists all F active fields in slot order, exponent 1
-  const double* intercept;    // n_tables
-  const int32_t* term_off;    // n_tables+1
-  const RegTerm* terms;
-  const int32_t* cat_off;     // n_tables+1
-  const RegCat* cats;
-  const double* dense_wt;     // dense only: F x KP transposed, KP = n_tables rounded up to a multiple of 8, 10 or 12 (least padding), zero padded
-  double dense_amax, dense_bmax;   // dense only: max_t sum_f |coef|, max_t |intercept| (error bound of the FMA path)
-};
-
-// ---- GeneralRegressionModel (PPMatrix x ParamMatrix) -------------------------------------------------------
-enum : int { GR_REGRESSION = 0, GR_GENERAL_LINEAR = 1, GR_MULTINOMIAL = 2 };
-enum : int { GL_IDENTITY = 0, GL_LOG, GL_LOGIT, GL_PROBIT, GL_CLOGLOG, GL_LOGLOG, GL_LOGC, GL_CAUCHIT, GL_POWER, GL_NEGBIN };
-struct GCell { int32_t slot; int32_t is_factor; double value; };  // factor: indicator [x == value]; covariate: x ^ value
-static constexpr int GR_MAX_PARAMS = 64, GR_MAX_CATS = 32;
-struct GeneralRegDesc {
-  int n_params, n_rows, n_cats, classify, model_type, link;
-  double link_param, offset;
-  const int32_t* cell_off;    // n_params + 1
-  const GCell* cells;
-  const int32_t* beta_off;    // n_rows + 1
-  const int32_t* beta_param;  // parameter index per PCell
-  const double* beta;
-  const int32_t* row_cat;     // n_rows: index of the row's targetCategory among the labels (-1: regression)
-};
-
-enum : int { ACT_THRESHOLD = 0, ACT_LOGISTIC, ACT_TANH, ACT_IDENTITY, ACT_EXPONENTIAL, ACT_RECIPROCAL, ACT_SQUARE,
-             ACT_GAUSS, ACT_SINE, ACT_COSINE, ACT_ELLIOTT, ACT_ARCTAN, ACT_RECTIFIER };
-enum : int { NI_FIELDREF = 0, NI_NORMCONT = 1, NI_NORMDISC = 2, NI_CONSTANT = 3 };
-struct NeuralInput {  // DerivedField of a NeuralInput
-  int32_t kind, slot, pts_off, n_pts, outliers, has_map_missing;  // outliers: 0 asIs, 1 asMissingValues, 2 asExtremeValues
-  double value, map_missing;
-};
-struct NeuralLayer { int32_t n_in, n_out, act, norm; double threshold; int64_t w_off, b_off; int64_t wt_off; int32_t n_out_pad, pad; };
 static constexpr int MAX_LAYERS = 8;
-
 // ---- tensor-core form of a dense layer (tcgen05.mma kind::i8; sliced_gemm.cuh) -----------------------------------------
 // y_j = b_j + sum_i w_ji a_i is evaluated in EXACT integer arithmetic on fixed-point images of the operands:
 //   a_i = sigma * qa_i * 2^-Q, sigma = a power of two > max_i |a_i| of the event's row      (|qa_i| <= 2^Q, Q = 8 S - 2)
@@ -221,6 +180,48 @@ struct SgDesc {
   SgLayer layers[MAX_LAYERS]; const int8_t* weights; const int32_t* tau_exp;
 };
 struct SgRow { double err; float amax; int32_t sexp; };   // per event between layers: error bound so far (inf = not on this path), max |a_i|, exponent of sigma
+
+// ---- regression / neural network ---------------------------------------------------------------------
+enum : int { NORM_NONE = 0, NORM_SIMPLEMAX = 1, NORM_SOFTMAX = 2, NORM_LOGIT = 3, NORM_PROBIT = 4, NORM_CLOGLOG = 5,
+             NORM_EXP = 6, NORM_LOGLOG = 7, NORM_CAUCHIT = 8 };
+struct RegTerm { int32_t slot; int32_t exponent; double coef; };           // NumericPredictor
+struct RegCat { int32_t slot; int32_t pad; double value; double coef; };   // CategoricalPredictor on a numeric field
+struct RegressionDesc {
+  int n_tables, classify, norm, dense;  // dense: every table lists all F active fields in slot order, exponent 1
+  const double* intercept;    // n_tables
+  const int32_t* term_off;    // n_tables+1
+  const RegTerm* terms;
+  const int32_t* cat_off;     // n_tables+1
+  const RegCat* cats;
+  const double* dense_wt;     // dense only: F x KP transposed, KP = n_tables rounded up to a multiple of 8, 10 or 12 (least padding), zero padded
+  double dense_amax, dense_bmax;   // dense only: max_t sum_f |coef|, max_t |intercept| (error bound of the FMA path)
+  SgDesc sg;                       // dense softmax classification with <= 24 tables: weight digit planes of the fused tensor-core layer
+};
+
+// ---- GeneralRegressionModel (PPMatrix x ParamMatrix) -------------------------------------------------------
+enum : int { GR_REGRESSION = 0, GR_GENERAL_LINEAR = 1, GR_MULTINOMIAL = 2 };
+enum : int { GL_IDENTITY = 0, GL_LOG, GL_LOGIT, GL_PROBIT, GL_CLOGLOG, GL_LOGLOG, GL_LOGC, GL_CAUCHIT, GL_POWER, GL_NEGBIN };
+struct GCell { int32_t slot; int32_t is_factor; double value; };  // factor: indicator [x == value]; covariate: x ^ value
+static constexpr int GR_MAX_PARAMS = 64, GR_MAX_CATS = 32;
+struct GeneralRegDesc {
+  int n_params, n_rows, n_cats, classify, model_type, link;
+  double link_param, offset;
+  const int32_t* cell_off;    // n_params + 1
+  const GCell* cells;
+  const int32_t* beta_off;    // n_rows + 1
+  const int32_t* beta_param;  // parameter index per PCell
+  const double* beta;
+  const int32_t* row_cat;     // n_rows: index of the row's targetCategory among the labels (-1: regression)
+};
+
+enum : int { ACT_THRESHOLD = 0, ACT_LOGISTIC, ACT_TANH, ACT_IDENTITY, ACT_EXPONENTIAL, ACT_RECIPROCAL, ACT_SQUARE,
+             ACT_GAUSS, ACT_SINE, ACT_COSINE, ACT_ELLIOTT, ACT_ARCTAN, ACT_RECTIFIER };
+enum : int { NI_FIELDREF = 0, NI_NORMCONT = 1, NI_NORMDISC = 2, NI_CONSTANT = 3 };
+struct NeuralInput {  // DerivedField of a NeuralInput
+  int32_t kind, slot, pts_off, n_pts, outliers, has_map_missing;  // outliers: 0 asIs, 1 asMissingValues, 2 asExtremeValues
+  double value, map_missing;
+};
+struct NeuralLayer { int32_t n_in, n_out, act, norm; double threshold; int64_t w_off, b_off; int64_t wt_off; int32_t n_out_pad, pad; };
 
 struct NeuralDesc {
   int n_inputs, n_layers, classify, n_outputs, max_width;

@@ -110,6 +110,7 @@ std::vector<std::string> split_array(const XNode& arr) {
 }
 
 struct Field { std::string name; uint8_t dtype; bool continuous; const XNode* node; };
+bool sg_add_layer(const double* W, const double* bias, int N, int K, SgLayer& ly, std::vector<int8_t>& SW, std::vector<int32_t>& TAU);
 
 struct Builder {
   CompiledModel cm;
@@ -1094,6 +1095,17 @@ bool compile_regression_tables(const XNode& m, Builder& b, const std::unordered_
     if (!std::isfinite(d.dense_amax) || !std::isfinite(d.dense_bmax)) d.dense_amax = d.dense_bmax = std::numeric_limits<double>::infinity();   // the FMA path then decides nothing
   }
   b.put(&d.intercept, icpt); b.put(&d.term_off, toff); b.put(&d.terms, terms); b.put(&d.cat_off, coff); b.put(&d.cats, cats); b.put(&d.dense_wt, w);
+  {  // weight digit planes of the fused tensor-core layer (model.h): softmax classification, <= 24 tables, wide rows
+    std::vector<int8_t> SW; std::vector<int32_t> TAU; d.sg = SgDesc{};
+    if (dense && classify && d.norm == NORM_SOFTMAX && icpt.size() <= 24 && F >= 128 && F <= 8192) {
+      std::vector<double> Wm(icpt.size() * (size_t)F);
+      for (size_t t = 0; t < icpt.size(); t++) for (int i = 0; i < F; i++) Wm[t * (size_t)F + i] = terms[toff[t] + i].coef;
+      SgLayer& sl = d.sg.layers[0];
+      if (sg_add_layer(Wm.data(), icpt.data(), (int)icpt.size(), F, sl, SW, TAU)) { sl.act = ACT_IDENTITY; sl.last = 1; sl.norm = NORM_SOFTMAX; sl.b_off = 0; d.sg.enabled = 1; d.sg.n_layers = 1; }
+      else { SW.clear(); TAU.clear(); }
+    }
+    b.put(&d.sg.weights, SW); b.put(&d.sg.tau_exp, TAU);
+  }
   if (classify) b.set_labels(labels, false); else b.set_labels({}, false);
   finish_target(b, classify);
   return classify;

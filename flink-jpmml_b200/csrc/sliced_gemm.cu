@@ -73,6 +73,24 @@ static cudaError_t launch_sliced_plan(const DeviceModel& m, const BatchArgs& a, 
   return cudaSuccess;
 }
 
+// fused single dense layer (softmax RegressionModel over plain dense rows, sliced_gemm.cuh namespace dense)
+bool sliced_dense_takes(const DeviceModel& m, const BatchArgs& a) {
+  if (m.kind != MK_REGRESSION || !m.reg.sg.enabled || a.probs || a.node_ids || a.row_map || a.present || a.replace || !m.prep_identity || (m.F & 1)) return false;
+  const int mode = env_int("FJP_SLICED", 1);
+  if (!mode) return false;
+  device_facts(&g_num_sms, &g_smem_optin);
+  if (mode != 2 && a.n < (long)SG_M * g_num_sms / 2) return false;
+  return sg::dense::smem_plan().bytes <= (uint32_t)g_smem_optin;
+}
+cudaError_t launch_sliced_dense(const DeviceModel& m, const BatchArgs& a, int32_t* fb_count, int32_t* fb_rows, cudaStream_t s) {
+  device_facts(&g_num_sms, &g_smem_optin);
+  const uint32_t smem = sg::dense::smem_plan().bytes;
+  cudaFuncSetAttribute(sg::dense::sg_dense_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  const long tiles = (a.n + SG_M - 1) / SG_M; const int grid = (int)(tiles < g_num_sms ? tiles : g_num_sms);
+  sg::dense::sg_dense_kernel<<<grid, sg::dense::THREADS, smem, s>>>(m, a, fb_count, fb_rows);
+  return cudaGetLastError();
+}
+
 bool launch_sliced(const DeviceModel& m, const BatchArgs& a, void* scratch, cudaStream_t s, int* launches, cudaError_t* err) {
   SlicedPlan p;
   if (!plan_sliced(m, a, &p)) return false;

@@ -489,5 +489,230 @@ __global__ void __launch_bounds__(THREADS, 1) sg_layer_kernel(const __grid_const
   if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TMEM_COLS) : "memory");
 }
 
+// ---------------------------------------------------------------------------------------------- fused single dense layer (C3)
+// RegressionModel with softmax over plain dense rows: y_t = b_t + sum_f w_tf x_f for F up to thousands of fields, a handful
+// of tables.  The contraction is tiny for the tensor cores; what has to be fast is getting 8 F bytes per event from HBM into
+// int8 digit planes, so the slicing is fused into the kernel and the rows are read ONCE:
+//   warps 0-15  producers: a quad per event reads 64 fields (one K chunk, 512 contiguous bytes) with 16-byte streaming loads,
+//               software-pipelined one chunk ahead; every (event, chunk) gets its OWN power-of-two scale (largest |x| of those
+//               64 values), so no pass over the whole row is needed; the four digit planes go to shared memory in the MMA's
+//               layout (conflict-free 4-byte stores), then fence.proxy.async + one mbarrier arrive per warp;
+//   warp 16     TMA: the weight digit planes of the chunk (cp.async.bulk);
+//   warp 17     MMA issuer: S (S + 1) / 2 pairs x 2 K steps of tcgen05.mma.kind::i8 per chunk into a FRESH accumulator set (the chunks
+//               have different scales, so they are not accumulated in tensor memory);
+//   warps 18-21 epilogue: per chunk tcgen05.ld of the S levels, recombination to one int64 per table, scaled by the event's
+//               chunk scale and added into double registers; after the last chunk: intercepts, arg-max, margin test.
+// Error bound per event: sum over chunks of 64 sigma_c tau SG_CS (+ the FP64 rounding of both orders); labels inside it go to the
+// FP64 tile kernel through the re-scoring list, like everywhere else.
+namespace dense {
+constexpr int PROD_WARPS = 16, TMA_WARP = 16, MMA_WARP = 17, EPI_WARP0 = 18, EPI_WARPS = 4;
+constexpr int THREADS = 32 * (PROD_WARPS + 2 + EPI_WARPS);
+constexpr int A_SLOTS = 3, B_SLOTS = 4, SEXP_SLOTS = 8;
+constexpr int MAXT = 32;                    // MMA width (N = 32)
+constexpr int MAXZ = 24;                    // tables the epilogue keeps running sums for
+struct Smem { uint32_t off_b, off_sexp, off_bars, off_tmem, bytes; };
+__host__ __device__ inline Smem smem_plan() {
+  Smem p; uint32_t o = A_SLOTS * A_CHUNK;
+  p.off_b = o; o += B_SLOTS * B_STAGE;
+  p.off_sexp = o; o += SEXP_SLOTS * SG_M * 4;
+  p.off_bars = o; o += 8u * (2 * A_SLOTS + 2 * B_SLOTS + 4);
+  p.off_tmem = o; o += 16; p.bytes = o;
+  return p;
+}
+
+__global__ void __launch_bounds__(THREADS, 1) sg_dense_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, int32_t* fb_count, int32_t* fb_rows) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const RegressionDesc& rd = m.reg; const SgLayer& L = rd.sg.layers[0];
+  const int F = m.F, n_kc = L.Kp / SG_KC, C = rd.n_tables;
+  const Smem sp = smem_plan();
+  uint8_t* sA = smem; uint8_t* sB = smem + sp.off_b;
+  int* s_sexp = reinterpret_cast<int*>(smem + sp.off_sexp);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + sp.off_bars);
+  uint64_t* a_full = bars; uint64_t* a_empty = bars + A_SLOTS; uint64_t* b_full = bars + 2 * A_SLOTS; uint64_t* b_empty = b_full + B_SLOTS;
+  uint64_t* t_full = b_empty + B_SLOTS; uint64_t* t_empty = t_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + sp.off_tmem);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const long ntiles = (a.n + SG_M - 1) / SG_M;
+  if (tid == 0) {
+    for (int i = 0; i < A_SLOTS; i++) { mbar_init(&a_full[i], PROD_WARPS); mbar_init(&a_empty[i], 1); }
+    for (int i = 0; i < B_SLOTS; i++) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], 1); }
+    for (int i = 0; i < 2; i++) { mbar_init(&t_full[i], 1); mbar_init(&t_empty[i], EPI_WARPS); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == MMA_WARP) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(256) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = *tmem_slot;
+  constexpr uint32_t ACC_COLS = SG_S * MAXT;          // columns of one accumulator set
+
+  if (warp < PROD_WARPS) {
+    // ===================================================================== producers
+    const int q4 = lane & 3, r = warp * 8 + (lane >> 2);
+    uint32_t it = 0;                                   // chunks produced so far (all tiles)
+    for (long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      const long row = tile * SG_M + r; const bool live = row < a.n;
+      const double* xrow = a.X + (live ? row : 0) * (long)F + q4 * 4;
+      double cur[16], nxt[16];
+      auto load = [&](int kc, double (&v)[16]) {
+#pragma unroll
+        for (int g = 0; g < 4; g++) {
+          const int i0 = kc * SG_KC + g * 16 + q4 * 4;
+          if (live && i0 + 3 < F) {
+            const double2 u0 = __ldcs(reinterpret_cast<const double2*>(xrow + kc * SG_KC + g * 16)), u1 = __ldcs(reinterpret_cast<const double2*>(xrow + kc * SG_KC + g * 16 + 2));
+            v[4 * g] = u0.x; v[4 * g + 1] = u0.y; v[4 * g + 2] = u1.x; v[4 * g + 3] = u1.y;
+          } else {
+#pragma unroll
+            for (int k = 0; k < 4; k++) v[4 * g + k] = (live && i0 + k < F) ? __ldcs(xrow + kc * SG_KC + g * 16 + k) : 0.0;
+          }
+        }
+      };
+      load(0, cur);
+      for (int kc = 0; kc < n_kc; kc++, it++) {
+        if (kc + 1 < n_kc) load(kc + 1, nxt);
+        // the chunk's scale for this event: largest |x| of its 64 values (high words compare like the doubles)
+        int hm = 0;
+#pragma unroll
+        for (int k = 0; k < 16; k++) hm = max(hm, __double2hiint(cur[k]) & 0x7fffffff);
+        hm = max(hm, __shfl_xor_sync(0xffffffffu, hm, 1)); hm = max(hm, __shfl_xor_sync(0xffffffffu, hm, 2));
+        int sexp = (hm >> 20) - 1022;                  // 2^sexp > |x| (zero / denormal chunk: far below, harmless)
+        const bool wild = hm >= 0x7ff00000 || sexp > 400;   // NaN / Inf / huge: the event is re-scored
+        if (sexp < -400) sexp = -400;
+        if (wild) sexp = 0;
+        const double qscale = pow2(SG_QBITS - sexp);
+        const uint32_t slot = it % A_SLOTS;
+        mbar_wait(&a_empty[slot], ((it / A_SLOTS) & 1u) ^ 1u);
+        uint8_t* dst = sA + (size_t)slot * A_CHUNK + (size_t)r * 16 + (size_t)q4 * 4;
+#pragma unroll
+        for (int g = 0; g < 4; g++) {
+          qint qv[4];
+#pragma unroll
+          for (int k = 0; k < 4; k++) qv[k] = wild ? 0 : (qint)__double2ll_rn(cur[4 * g + k] * qscale);
+          uint32_t w[SG_S][4]; pack4(qv[0], qv[1], qv[2], qv[3], w, 0);
+#pragma unroll
+          for (int s = 0; s < SG_S; s++) *reinterpret_cast<uint32_t*>(dst + (size_t)s * A_PLANE + (size_t)g * (SG_M * 16)) = w[s][0];
+        }
+        if (q4 == 0) s_sexp[(it % SEXP_SLOTS) * SG_M + r] = wild ? 0x7fffffff : sexp;
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // generic-proxy stores -> the tensor core's async-proxy reads
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&a_full[slot]);
+#pragma unroll
+        for (int k = 0; k < 16; k++) cur[k] = nxt[k];
+      }
+    }
+  } else if (warp == TMA_WARP) {
+    // ===================================================================== weight planes
+    if (lane == 0) {
+      const int8_t* wsl = rd.sg.weights + L.w_off;
+      uint32_t it = 0;
+      for (long tile = blockIdx.x; tile < ntiles; tile += gridDim.x)
+        for (int kc = 0; kc < n_kc; kc++, it++) {
+          const uint32_t st = it % B_SLOTS;
+          mbar_wait(&b_empty[st], ((it / B_SLOTS) & 1u) ^ 1u);
+          mbar_expect_tx(&b_full[st], B_STAGE);
+          bulk_g2s(sB + (size_t)st * B_STAGE, wsl + (size_t)kc * B_STAGE, B_STAGE, &b_full[st]);
+        }
+    }
+  } else if (warp == MMA_WARP) {
+    // ===================================================================== MMA issuer
+    const bool leader = elect_one();
+    const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(MAXT >> 3) << 17) | ((uint32_t)(SG_M >> 4) << 24);
+    const uint64_t da0 = smem_desc(smem_u32(sA), SG_M * 16), db0 = smem_desc(smem_u32(sB), SG_NC * 16);
+    uint32_t it = 0;
+    for (long tile = blockIdx.x; tile < ntiles; tile += gridDim.x)
+      for (int kc = 0; kc < n_kc; kc++, it++) {
+        const uint32_t sa = it % A_SLOTS, sb = it % B_SLOTS, buf = it & 1u;
+        mbar_wait(&t_empty[buf], ((it >> 1) & 1u) ^ 1u);
+        mbar_wait(&a_full[sa], (it / A_SLOTS) & 1u);
+        mbar_wait(&b_full[sb], (it / B_SLOTS) & 1u);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint64_t da_st = da0 + (uint64_t)((sa * A_CHUNK) >> 4), db_st = db0 + (uint64_t)((sb * B_STAGE) >> 4);
+        const uint32_t d0 = tmem + buf * ACC_COLS;
+        if (leader) {
+#pragma unroll
+          for (int ks = 0; ks < 2; ks++) {
+#pragma unroll
+            for (int k = 0; k < SG_S; k++) {
+#pragma unroll
+              for (int l = 0; l + k < SG_S; l++)
+                mma_i8(d0 + (uint32_t)(k + l) * MAXT, da_st + (uint64_t)(((uint32_t)k * A_PLANE + (uint32_t)ks * 2u * (SG_M * 16)) >> 4),
+                       db_st + (uint64_t)(((uint32_t)l * B_PLANE + (uint32_t)ks * 2u * (SG_NC * 16)) >> 4), idesc, (ks == 0 && k == 0) ? 0u : 1u);
+            }
+          }
+          mma_commit(&a_empty[sa]); mma_commit(&b_empty[sb]); mma_commit(&t_full[buf]);
+        }
+        __syncwarp();
+      }
+  } else {
+    // ===================================================================== epilogue: 4 warps, lane <-> event
+    const int quarter = warp & 3, r = quarter * 32 + lane;
+    uint32_t it = 0;
+    for (long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      const long row = tile * SG_M + r; const bool live = row < a.n;
+      double z[MAXZ];
+#pragma unroll
+      for (int j = 0; j < MAXZ; j++) z[j] = 0.0;
+      double sig_sum = 0.0, sig_max = 0.0; bool wild = false;
+      for (int kc = 0; kc < n_kc; kc++, it++) {
+        const uint32_t buf = it & 1u;
+        mbar_wait(&t_full[buf], (it >> 1) & 1u);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const int se = s_sexp[(it % SEXP_SLOTS) * SG_M + r];
+        if (se == 0x7fffffff) wild = true;
+        const double sigma = pow2(se == 0x7fffffff ? 0 : se);
+        const double scale = sigma * pow2(L.tau_max_exp - 2 * SG_QBITS + 8 * (SG_S - 1));
+        sig_sum += sigma; sig_max = fmax(sig_max, sigma);
+#pragma unroll
+        for (int round = 0; round < MAXZ / 8; round++) {
+          uint32_t lv[SG_S][8];
+          const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + buf * ACC_COLS + (uint32_t)round * 8u;
+#pragma unroll
+          for (int c = 0; c < SG_S; c++) tmem_ld8(taddr + (uint32_t)c * MAXT, lv[c]);
+          asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+          if (round == MAXZ / 8 - 1) {
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&t_empty[buf]);
+          }
+#pragma unroll
+          for (int c = 0; c < 8; c++) {
+            long long V = (long long)((int)lv[0][c] * 256 + (int)lv[1][c]);
+#pragma unroll
+            for (int lc = 2; lc < SG_S; lc++) V = (V << 8) + (long long)(int)lv[lc][c];
+            z[round * 8 + c] = fma((double)V, scale, z[round * 8 + c]);      // exact product, one rounding per chunk
+          }
+        }
+      }
+      // intercepts, first maximal table, margin against the bound
+      const double e = (double)SG_KC * sig_sum * pow2(L.tau_max_exp) * SG_CS + (double)(F + 64) * 2.220446049250313e-16 * (L.bmax + L.amax * sig_max);
+      int best = 0; double zb = 0, z2 = -1e308, zabs = 0;
+#pragma unroll
+      for (int j = 0; j < MAXZ; j++) {
+        if (j < C) {
+          const double zz = z[j] + rd.intercept[j]; zabs = fmax(zabs, fabs(zz));
+          if (j == 0) { zb = zz; } else if (zz > zb) { z2 = zb; zb = zz; best = j; } else z2 = fmax(z2, zz);
+        }
+      }
+      const bool ok = live && !wild && zabs < 600.0 && (C == 1 || zb - z2 > 2.0 * e + 1e-12 * fmax(1.0, zabs));
+      if (ok) write_label(m, a, row, best, best);
+      const unsigned need = __ballot_sync(0xffffffffu, live && !ok), alive = __ballot_sync(0xffffffffu, live);
+      if (a.stats && lane == 0) { atomicAdd(a.stats, (unsigned long long)__popc(alive)); if (need) atomicAdd(a.stats + 1, (unsigned long long)__popc(need)); }
+      if (need) {
+        int base = 0;
+        if (lane == 0) base = atomicAdd(fb_count, __popc(need));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (live && !ok) fb_rows[base + __popc(need & ((1u << lane) - 1u))] = (int32_t)row;
+      }
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == MMA_WARP) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(256) : "memory");
+}
+}  // namespace dense
+
 }  // namespace sg
 }  // namespace fjp

@@ -86,3 +86,51 @@ def test_near_ties_go_to_the_fp64_kernel(engine, gen, oracle, monkeypatch):
     winners_01 = np.isin(o["aux"], (0, 1)).sum()
     assert f1 - f0 >= winners_01 > 0, "tied events were decided by the tensor path"
     assert (o["aux"] != 1).all()          # the first of two equal outputs wins
+
+
+# ---- the fused single-layer variant: softmax RegressionModels over wide plain dense rows (config 3) ---------------------------
+def _check_reg(engine, oracle, pm, X, expect_taken=True):
+    m = engine.compile(pm)
+    t0, f0 = engine.tensor_path_counts
+    r = engine.score(m, X)
+    t1, f1 = engine.tensor_path_counts
+    o = oracle.OracleModel(pm).predict(X, nthreads=os.cpu_count() or 4)
+    assert np.array_equal(r["status"], o["status"]) and (o["status"] == 0).all()
+    assert np.array_equal(r["score"], o["score"]), f"{(r['score'] != o['score']).sum()} labels differ from the oracle"
+    assert np.array_equal(r["aux"], o["aux"])
+    if expect_taken:
+        assert t1 - t0 == len(X), "the fused tensor-core layer did not take this batch"
+    return t1 - t0, f1 - f0
+
+
+def test_c3_multinomial_labels_bit_exact_on_the_fused_tensor_layer(engine, gen, oracle, monkeypatch):
+    """BASELINE.json config 3 (1000 fields x 20 classes, softmax): rows are read once, sliced per (event, 64-field chunk) with
+    their own scales, multiplied on the tensor cores; labels must be the oracle's for every event."""
+    monkeypatch.setenv("FJP_SLICED", "2")
+    pm, _ = gen.regression_pmml()
+    X, _, _ = gen.events(148 * 128 + 55, 1000, 41, 0.0)
+    took, back = _check_reg(engine, oracle, pm, X)
+    assert back < 0.01 * took, (took, back)
+    print(f"fused tensor layer: {took} events, {back} re-scored in FP64")
+
+
+@pytest.mark.parametrize("F,C,n", [(128, 2, 1), (130, 24, 777), (256, 3, 4096), (1000, 20, 129), (2050, 7, 300)])
+def test_fused_layer_shapes(engine, gen, oracle, monkeypatch, F, C, n):
+    monkeypatch.setenv("FJP_SLICED", "2")
+    pm, _ = gen.regression_pmml(F=F, C=C, seed=80 + C)
+    X, _, _ = gen.events(n, F, 42, 0.0)
+    _check_reg(engine, oracle, pm, X)
+
+
+def test_fused_layer_wild_values_and_scales(engine, gen, oracle, monkeypatch):
+    """Chunks with very different magnitudes inside one row, zeros, denormals, NaN / Inf (those events are re-scored)."""
+    monkeypatch.setenv("FJP_SLICED", "2")
+    pm, _ = gen.regression_pmml(F=512, C=6, seed=90)
+    X, _, _ = gen.events(5000, 512, 43, 0.0)
+    X[:, 64:128] *= 1e-9; X[:, 128:192] *= 1e6; X[:, 192:256] = 0.0; X[100:200, 256:320] *= 1e-300
+    X[7, 3] = np.nan; X[8, 500] = np.inf; X[9, :] = 0.0; X[10, 70] = 1e250
+    _check_reg(engine, oracle, pm, X)
+    # an odd field count keeps the model on the FP64 tiles (rows are not 16-byte aligned): still the oracle's answers
+    pm2, _ = gen.regression_pmml(F=257, C=4, seed=91)
+    X2, _, _ = gen.events(2000, 257, 44, 0.0)
+    _check_reg(engine, oracle, pm2, X2, expect_taken=False)
