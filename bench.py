@@ -422,6 +422,37 @@ def main():
                "single_thread_value": 2048 / dt1,
                "parity_on_sample": "bit-exact" if (np.array_equal(o["score"], hS[:ns].numpy()) and np.array_equal(o["status"], hT[:ns].numpy())) else "MISMATCH"}
 
+    # ------------------------------------------------------------------ through the operator (what a Flink job sees): rank 0, N = 1
+    operator = None
+    if rank == 0 and world == 1 and not args.no_latency:
+        try:
+            import tempfile
+            from flink_jpmml_b200 import api
+            d = tempfile.mkdtemp(); path = os.path.join(d, "c4.pmml")
+            with open(path, "wb") as f:
+                f.write(pm)
+            xs = hX[: 1 << 20].numpy()
+
+            def drive(n_threads):
+                fns = [api.EvaluationFunction(eng, path, max_batch=16384) for _ in range(n_threads)]
+                for fn in fns:
+                    fn.processDense(xs[:16384]); fn.flush(); fn.collect_arrays()
+                emitted = [0] * n_threads
+
+                def task(k):
+                    fns[k].processDense(xs); fns[k].flush(); emitted[k] = len(fns[k].collect_arrays()[0])
+                ths = [threading.Thread(target=task, args=(k,)) for k in range(n_threads)]
+                t1 = time.perf_counter(); [t.start() for t in ths]; [t.join() for t in ths]; dt = time.perf_counter() - t1
+                for fn in fns:
+                    fn.close()
+                return sum(emitted) / dt, sum(emitted)
+            r1, e1 = drive(1); r4, e4 = drive(4)
+            operator = {"fixed_model_C4_1_task_thread": {"events_per_s": r1, "emitted": e1}, "fixed_model_C4_4_task_threads_one_engine": {"events_per_s": r4, "emitted": e4},
+                        "max_batch": 16384, "api": "fjh_eval_function_process_dense -> pinned micro-batches -> fjp_submit / fjp_wait (EvaluationFunction mirror, S/api/functions/EvaluationFunction.scala:39-50)",
+                        "note": "one task thread copies every 800-byte event into a pinned micro-batch: the rate is the host core's copy bandwidth, not the GPU's"}
+        except Exception as ex:          # noqa: BLE001
+            operator = {"error": repr(ex)}
+
     if rank == 0:
         pk = peaks()
         value = D.whole_job_rate(n, world, args.steps, ms_dev_max)
@@ -469,7 +500,7 @@ def main():
                         "float_rows_match_double_rows": e2e_f32_match,
                         "double_rows": {"value": D.whole_job_rate(ne, world, e2e_steps, ms_e2e_f64_max), "h2d_bytes_per_step": ne * (F * 8 + W * 4), "api": "fjp_score_batch"},
                         "frac_of_h2d_copy_peak": (e2e_value / world * (F * (4 if e2e_rows == "float" else 8) + W * 4) / 1e9 / micro["h2d_pinned_GBs"]) if micro.get("h2d_pinned_GBs") else None},
-                "gpu_launches": launches, "rows_scored_ok": ok_rows, "roofline": roof, "cpu_baseline": cpu, "clocks": clocks, "configs": configs, "replicate": replicate,
+                "gpu_launches": launches, "rows_scored_ok": ok_rows, "roofline": roof, "cpu_baseline": cpu, "clocks": clocks, "configs": configs, "replicate": replicate, "operator": operator,
                 "latency_ms": latency}
         print(json.dumps(line), flush=True)
     if dist:

@@ -120,6 +120,19 @@ class PmmlModel {
   std::shared_ptr<fjp_model> model_;
 };
 
+// Predictions waiting to be emitted, in arrival order: two flat arrays and a read cursor (an operator emits hundreds of millions
+// of them; one heap object or one vector shuffle per event would cost more than scoring it).
+class PredictionQueue {
+ public:
+  void push(uint8_t status, double score) { status_.push_back(status); score_.push_back(score); }
+  size_t size() const { return status_.size() - head_; }
+  // copies up to `cap` predictions out (score NaN for an empty one); returns how many
+  long pop(double* scores, uint8_t* status, long cap);
+  std::vector<Prediction> drain();
+ private:
+  std::vector<double> score_; std::vector<uint8_t> status_; size_t head_ = 0;
+};
+
 // ---------------------------------------------------------------------------------------- micro-batch buffer
 // Rows of one model packed for fjp_score_batch / fjp_submit: pinned X (dense slots), present bits, replace values.
 class MicroBatch {
@@ -133,12 +146,17 @@ class MicroBatch {
   int size() const { return n_; }
   int append(const Vector& v, std::optional<double> replaceNan);   // returns the row index
   int append_dense(const double* x);                                // DenseVector payload, no replaceNan
+  int append_dense_block(const double* X, int rows);                // `rows` DenseVector payloads, contiguous: one copy; returns the first row index
   void clear() { n_ = 0; any_sparse_ = false; any_replace_ = false; }
+  int room() const { return cap_ - n_; }
   int score(fjp_engine* e, fjp_model* m);                         // fills score()/status()
   int submit(fjp_engine* e, fjp_model* m, int* ticket);           // asynchronous: fjp_submit; results valid after fjp_wait(ticket)
   const double* scores() const { return score_; }
   const uint8_t* statuses() const { return status_; }
  private:
+  // present words / replace values are written lazily: dense rows leave them alone until the first sparse row (or replaceNan)
+  // of the batch makes the kernels look at them, at which point the rows before it are back-filled
+  void need_present(); void need_replace();
   int F_, W_, cap_, n_ = 0; bool any_sparse_ = false, any_replace_ = false;
   double* X_; uint32_t* present_; double* replace_; double* score_; uint8_t* status_;
 };
@@ -154,12 +172,14 @@ class EvaluationFunction {
   void processElement(const Vector& v, std::optional<double> replaceNan = std::nullopt);
   void processDense(const double* x, int size);           // same for a DenseVector payload given in place
   void flush();
-  std::vector<Prediction> drain() { std::vector<Prediction> r; r.swap(out_); return r; }
+  std::vector<Prediction> drain() { return out_.drain(); }
+  long poll(double* scores, uint8_t* status, long cap) { return out_.pop(scores, status, cap); }
+  void processDenseBlock(const double* X, long n, int size);   // n DenseVector payloads in arrival order
   void close() { flush(); }
  private:
   // two pinned micro-batches: while the GPU scores one, the task thread packs the other (fjp_submit / fjp_wait)
   fjp_engine* engine_; ModelReader reader_; int max_batch_; PmmlModel model_;
-  std::unique_ptr<MicroBatch> batch_[2]; int cur_ = 0; int ticket_[2] = {-1, -1}; std::vector<Prediction> out_;
+  std::unique_ptr<MicroBatch> batch_[2]; int cur_ = 0; int ticket_[2] = {-1, -1}; PredictionQueue out_;
   std::vector<int> pending_[2];   // per buffered event: row in its batch, or -1 = size mismatch (EmptyScore)
   void submit_current();          // hand the current batch to the GPU, then collect the older one
   void collect(int b);            // wait for batch b and emit its predictions in arrival order
@@ -178,7 +198,8 @@ class EvaluationCoFunction {
   void processDenseBatch(const char* const* ids, const int32_t* id_index, const double* X, long n, int size);
   void processElement2(const ServingMessage& control);           // manageModels then manageMetadata (:69-74)
   void flush();
-  std::vector<Prediction> drain() { std::vector<Prediction> r; r.swap(out_); return r; }
+  std::vector<Prediction> drain() { return out_.drain(); }
+  long poll(double* scores, uint8_t* status, long cap) { return out_.pop(scores, status, cap); }
   PmmlModel fromMetadata(const std::string& modelId);            // (:106-117)
   PmmlModel loadModel(const std::string& path);                  // (:98-104)
   const Metadata& servingMetadata() const { return metadata_; }
@@ -187,7 +208,7 @@ class EvaluationCoFunction {
   struct Pending { int bucket; int row; };
   struct Bucket { PmmlModel model; std::unique_ptr<MicroBatch> batch; };
   fjp_engine* engine_; int max_batch_; Metadata metadata_;
-  std::vector<Bucket> buckets_; std::vector<Pending> pending_; std::vector<Prediction> out_; uint64_t flushes_ = 0;
+  std::vector<Bucket> buckets_; std::vector<Pending> pending_; PredictionQueue out_; uint64_t flushes_ = 0;
   // id string -> model bound to it right now; dropped on every control message and whenever the table changes
   std::unordered_map<std::string, PmmlModel> resolved_; uint64_t resolved_epoch_ = ~0ull;
   std::vector<std::unique_ptr<MicroBatch>> pool_;   // pinned micro-batches are recycled: cudaHostAlloc is far too slow for the event path

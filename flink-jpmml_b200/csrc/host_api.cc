@@ -94,27 +94,49 @@ MicroBatch::MicroBatch(int n_fields, int capacity) : F_(n_fields), W_((n_fields 
 }
 MicroBatch::~MicroBatch() { fjp_host_free(X_); fjp_host_free(present_); fjp_host_free(replace_); fjp_host_free(score_); fjp_host_free(status_); }
 
+void MicroBatch::need_present() {   // first sparse row of the batch: the dense rows before it become "all present"
+  if (any_sparse_) return;
+  any_sparse_ = true; memset(present_, 0xFF, (size_t)n_ * W_ * 4);
+}
+void MicroBatch::need_replace() {
+  if (any_replace_) return;
+  any_replace_ = true; for (int r = 0; r < n_; r++) replace_[r] = std::numeric_limits<double>::quiet_NaN();
+}
 int MicroBatch::append(const Vector& v, std::optional<double> replaceNan) {
+  if (v.sparse) need_present();
+  if (replaceNan) need_replace();
   int r = n_++;
   double* x = X_ + (size_t)r * F_; uint32_t* p = present_ + (size_t)r * W_;
   if (!v.sparse) {  // DenseVector: every slot present (VectorConverter.scala:68-73)
     memcpy(x, v.data.data(), (size_t)F_ * 8);
-    for (int w = 0; w < W_; w++) p[w] = 0xFFFFFFFFu;
+    if (any_sparse_) for (int w = 0; w < W_; w++) p[w] = 0xFFFFFFFFu;
   } else {          // SparseVector: only listed indices are present (VectorConverter.scala:80-86, 100-103)
-    any_sparse_ = true;
     memset(x, 0, (size_t)F_ * 8); memset(p, 0, (size_t)W_ * 4);
     for (size_t k = 0; k < v.indices.size(); k++) { int i = v.indices[k]; if (i >= 0 && i < F_) { x[i] = v.data[k]; p[i >> 5] |= 1u << (i & 31); } }
   }
-  replace_[r] = replaceNan ? *replaceNan : std::numeric_limits<double>::quiet_NaN();
-  if (replaceNan) any_replace_ = true;
+  if (any_replace_) replace_[r] = replaceNan ? *replaceNan : std::numeric_limits<double>::quiet_NaN();
   return r;
 }
-int MicroBatch::append_dense(const double* x) {
-  int r = n_++;
-  memcpy(X_ + (size_t)r * F_, x, (size_t)F_ * 8);
-  uint32_t* p = present_ + (size_t)r * W_;
-  for (int w = 0; w < W_; w++) p[w] = 0xFFFFFFFFu;
-  replace_[r] = std::numeric_limits<double>::quiet_NaN();
+int MicroBatch::append_dense(const double* x) { return append_dense_block(x, 1); }
+int MicroBatch::append_dense_block(const double* X, int rows) {
+  const int r = n_; n_ += rows;
+  memcpy(X_ + (size_t)r * F_, X, (size_t)rows * F_ * 8);
+  if (any_sparse_) memset(present_ + (size_t)r * W_, 0xFF, (size_t)rows * W_ * 4);
+  if (any_replace_) for (int k = 0; k < rows; k++) replace_[r + k] = std::numeric_limits<double>::quiet_NaN();
+  return r;
+}
+
+long PredictionQueue::pop(double* scores, uint8_t* status, long cap) {
+  const long n = std::min<long>(cap, (long)size());
+  for (long i = 0; i < n; i++) { const uint8_t st = status_[head_ + i]; status[i] = st; scores[i] = st == FJP_ST_SCORE ? score_[head_ + i] : std::numeric_limits<double>::quiet_NaN(); }
+  head_ += n;
+  if (head_ == status_.size()) { status_.clear(); score_.clear(); head_ = 0; }
+  return n;
+}
+std::vector<Prediction> PredictionQueue::drain() {
+  std::vector<Prediction> r; r.reserve(size());
+  for (size_t i = head_; i < status_.size(); i++) { Prediction p; p.status = status_[i]; if (p.status == FJP_ST_SCORE) p.value = Target::score(score_[i]); r.push_back(p); }
+  status_.clear(); score_.clear(); head_ = 0;
   return r;
 }
 int MicroBatch::submit(fjp_engine* e, fjp_model* m, int* ticket) {
@@ -137,12 +159,6 @@ int MicroBatch::score(fjp_engine* e, fjp_model* m) {
   return fjp_score_batch(e, m, X_, any_sparse_ ? present_ : nullptr, any_replace_ ? replace_ : nullptr, n_, F_, score_, status_, nullptr);
 }
 
-static Prediction make_prediction(uint8_t status, double score) {
-  Prediction p; p.status = status;
-  if (status == FJP_ST_SCORE) p.value = Target::score(score);
-  return p;
-}
-
 // ---------------------------------------------------------------------------------------- EvaluationFunction
 void EvaluationFunction::open() {
   model_ = PmmlModel::fromReader(engine_, reader_);   // ModelLoadingException propagates: the job fails (EvaluationFunction.scala:45-48)
@@ -160,9 +176,22 @@ void EvaluationFunction::processDense(const double* x, int size) {
   else pending_[cur_].push_back(batch_[cur_]->append_dense(x));
   if (batch_[cur_]->full() || (int)pending_[cur_].size() >= max_batch_) submit_current();
 }
+void EvaluationFunction::processDenseBlock(const double* X, long n, int size) {
+  if (model_.isEmpty()) open();
+  if (size != model_.activeFields()) { for (long i = 0; i < n; i++) processDense(X + i * (long)size, size); return; }
+  for (long i = 0; i < n;) {   // whole runs of rows go into the pinned batch with one copy
+    const int take = (int)std::min<long>(n - i, std::min(batch_[cur_]->room(), max_batch_ - (int)pending_[cur_].size()));
+    const int r0 = batch_[cur_]->append_dense_block(X + i * (long)size, take);
+    const size_t p0 = pending_[cur_].size(); pending_[cur_].resize(p0 + take);
+    for (int k = 0; k < take; k++) pending_[cur_][p0 + k] = r0 + k;
+    i += take;
+    if (batch_[cur_]->full() || (int)pending_[cur_].size() >= max_batch_) submit_current();
+  }
+}
 void EvaluationFunction::collect(int b) {
   if (ticket_[b] >= 0) { if (fjp_wait(engine_, ticket_[b]) != 0) throw std::runtime_error(fjp_last_error()); ticket_[b] = -1; }
-  for (int r : pending_[b]) out_.push_back(r < 0 ? make_prediction(FJP_ST_SIZE, 0) : make_prediction(batch_[b]->statuses()[r], batch_[b]->scores()[r]));
+  const double* sc = batch_[b]->scores(); const uint8_t* st = batch_[b]->statuses();
+  for (int r : pending_[b]) { if (r < 0) out_.push(FJP_ST_SIZE, 0); else out_.push(st[r], sc[r]); }
   pending_[b].clear(); batch_[b]->clear();
 }
 void EvaluationFunction::submit_current() {
@@ -302,8 +331,8 @@ void EvaluationCoFunction::flush() {
   }
   for (; waited < tickets.size(); waited++) if (fjp_wait(engine_, tickets[waited]) != 0) throw std::runtime_error(fjp_last_error());
   for (auto& p : pending_) {
-    if (p.bucket < 0) out_.push_back(make_prediction((uint8_t)p.row, 0));
-    else out_.push_back(make_prediction(buckets_[p.bucket].batch->statuses()[p.row], buckets_[p.bucket].batch->scores()[p.row]));
+    if (p.bucket < 0) out_.push((uint8_t)p.row, 0);
+    else out_.push(buckets_[p.bucket].batch->statuses()[p.row], buckets_[p.bucket].batch->scores()[p.row]);
   }
   pending_.clear(); flushes_++;
   for (auto& b : buckets_) { b.batch->clear(); if (pool_.size() < 64) pool_.push_back(std::move(b.batch)); }
@@ -315,9 +344,8 @@ void EvaluationCoFunction::flush() {
 // ============================================================================================ C wrappers
 using namespace flinkjpmml;
 
-// `backlog`: predictions already drained from the operator that did not fit the caller's last poll buffer
-struct fjh_eval_function { std::unique_ptr<EvaluationFunction> op; std::vector<Prediction> backlog; };
-struct fjh_cofunction { std::unique_ptr<EvaluationCoFunction> op; std::vector<Prediction> backlog; };
+struct fjh_eval_function { std::unique_ptr<EvaluationFunction> op; };
+struct fjh_cofunction { std::unique_ptr<EvaluationCoFunction> op; };
 
 static void set_err(char* err, size_t cap, const char* msg) { if (err && cap) { strncpy(err, msg, cap - 1); err[cap - 1] = 0; } }
 static Vector make_vector(const double* values, int size, const int* indices, int nnz) {
@@ -325,13 +353,6 @@ static Vector make_vector(const double* values, int size, const int* indices, in
   return Vector::sparseOf(size, std::vector<int>(indices, indices + nnz), std::vector<double>(values, values + nnz));
 }
 static std::optional<double> opt(double r) { return std::isnan(r) ? std::nullopt : std::optional<double>(r); }
-static long poll_out(std::vector<Prediction>& buf, std::vector<Prediction> fresh, double* scores, uint8_t* status, long cap) {
-  buf.insert(buf.end(), fresh.begin(), fresh.end());
-  long n = std::min<long>(cap, (long)buf.size());
-  for (long i = 0; i < n; i++) { scores[i] = buf[i].value.empty ? std::numeric_limits<double>::quiet_NaN() : buf[i].value.value; status[i] = buf[i].status; }
-  buf.erase(buf.begin(), buf.begin() + n);
-  return n;
-}
 template <class F> static int guarded(char* err, size_t cap, F&& f) {
   try { f(); return FJH_OK; }
   catch (WrongModelIdFormat& e) { set_err(err, cap, e.what()); return FJH_WRONG_MODEL_ID_FORMAT; }
@@ -367,11 +388,11 @@ int fjh_eval_function_process(fjh_eval_function* h, const double* values, int si
   return guarded(nullptr, 0, [&] { h->op->processElement(make_vector(values, size, indices, nnz), opt(replace_nan)); });
 }
 int fjh_eval_function_process_dense(fjh_eval_function* h, const double* X, long n, int size) {
-  return guarded(nullptr, 0, [&] { for (long i = 0; i < n; i++) h->op->processDense(X + i * (long)size, size); });
+  return guarded(nullptr, 0, [&] { h->op->processDenseBlock(X, n, size); });
 }
 int fjh_eval_function_flush(fjh_eval_function* h) { return guarded(nullptr, 0, [&] { h->op->flush(); }); }
 long fjh_eval_function_poll(fjh_eval_function* h, double* scores, uint8_t* status, long cap) {
-  return poll_out(h->backlog, h->op->drain(), scores, status, cap);
+  return h->op->poll(scores, status, cap);
 }
 void fjh_eval_function_close(fjh_eval_function* h) { if (h) { try { h->op->close(); } catch (...) {} delete h; } }
 
@@ -391,7 +412,7 @@ int fjh_cofunction_process_control(fjh_cofunction* h, int is_add, const char* na
 }
 int fjh_cofunction_flush(fjh_cofunction* h, char* err, size_t errcap) { return guarded(err, errcap, [&] { h->op->flush(); }); }
 long fjh_cofunction_poll(fjh_cofunction* h, double* scores, uint8_t* status, long cap) {
-  return poll_out(h->backlog, h->op->drain(), scores, status, cap);
+  return h->op->poll(scores, status, cap);
 }
 // snapshot format: one "name_version<TAB>path<LF>" line per entry (the checkpointed HashMap[ModelId, ModelInfo])
 long fjh_cofunction_snapshot(fjh_cofunction* h, char* buf, long cap) {
