@@ -60,6 +60,7 @@ struct Pass {
 // q + 0x808080 has the bytes d_k + 128 (k < S - 1) and the top digit above them; XOR 0x80 turns a byte into the int8 digit.  The
 // 4 x 4 byte transpose (value-major -> plane-major) is 8 PRMTs (S = 5: 3 more for the fifth digit).  w[0] = most significant plane.
 using qint = std::conditional<SG_S == 5, long long, int>::type;   // a fixed-point value: 30 bits + sign for S = 4, 38 for S = 5
+__device__ __forceinline__ qint to_q(double v) { if constexpr (SG_S == 5) return __double2ll_rn(v); else return __double2int_rn(v); }   // |v| <= 2^Q
 __device__ __forceinline__ void pack4(qint q0, qint q1, qint q2, qint q3, uint32_t (&w)[SG_S][4], int wi) {
   if constexpr (SG_S == 5) {
     const long long B = 0x80808080LL;
@@ -154,7 +155,7 @@ __global__ void __launch_bounds__(256) sg_slice_inputs_kernel(const __grid_const
     double v[4]; int dummy = 0; load4(g, v, dummy);
     qint qv[4];
 #pragma unroll
-    for (int k = 0; k < 4; k++) qv[k] = fl ? 0 : (qint)__double2ll_rn(v[k] * qscale);      // |v| < sigma: |q| <= 2^Q, off by at most 1/2
+    for (int k = 0; k < 4; k++) qv[k] = fl ? 0 : to_q(v[k] * qscale);      // |v| < sigma: |q| <= 2^Q, off by at most 1/2
     uint32_t w[SG_S][4]; pack4(qv[0], qv[1], qv[2], qv[3], w, 0);
     int8_t* dst = tbase + (size_t)(g >> 2) * A_CHUNK + (size_t)(g & 3) * (SG_M * 16);
 #pragma unroll
@@ -590,7 +591,7 @@ __global__ void __launch_bounds__(THREADS, 1) sg_dense_kernel(const __grid_const
         for (int g = 0; g < 4; g++) {
           qint qv[4];
 #pragma unroll
-          for (int k = 0; k < 4; k++) qv[k] = wild ? 0 : (qint)__double2ll_rn(cur[4 * g + k] * qscale);
+          for (int k = 0; k < 4; k++) qv[k] = wild ? 0 : to_q(cur[4 * g + k] * qscale);
           uint32_t w[SG_S][4]; pack4(qv[0], qv[1], qv[2], qv[3], w, 0);
 #pragma unroll
           for (int s = 0; s < SG_S; s++) *reinterpret_cast<uint32_t*>(dst + (size_t)s * A_PLANE + (size_t)g * (SG_M * 16)) = w[s][0];
