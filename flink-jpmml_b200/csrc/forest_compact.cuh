@@ -63,6 +63,40 @@ __device__ __forceinline__ void ck_rank_keys(uint32_t th_addr, uint32_t tab_addr
   }
 }
 
+// Direct table (model.h CkFeat): ONE 8-byte shared-memory load per value -- the bucket's first threshold image, how many thresholds lie
+// in lower buckets, how many in this one.  A bucket with more than one threshold (rare at ~4 buckets per threshold) scans on.
+__device__ __forceinline__ void ck_rank_keys_direct(uint32_t th_addr, uint32_t ent_addr, const CkFeat& cf, int mode, const double (&val)[RK_BATCH], uint32_t (&key)[RK_BATCH]) {
+  uint32_t img[RK_BATCH]; uint2 en[RK_BATCH]; bool nan[RK_BATCH];
+  const float top = (float)(cf.nb_e - 1u);
+  const uint32_t flip = mode == 2 ? 0x80000000u : 0u;  // RD(x) = -RU(-x)
+#pragma unroll
+  for (int k = 0; k < RK_BATCH; k++) {
+    float xf;
+    if (mode == 0) xf = (float)val[k];
+    else {
+      const double sx = __hiloint2double(__double2hiint(val[k]) ^ (int)flip, __double2loint(val[k]));
+      xf = __uint_as_float(__float_as_uint(__double2float_ru(sx)) ^ flip);
+    }
+    const uint32_t u = __float_as_uint(xf);
+    img[k] = u ^ ((uint32_t)((int32_t)u >> 31) | 0x80000000u);
+    nan[k] = xf != xf;
+    const uint32_t b = __float2uint_rz(fminf(fmaxf((xf - cf.lo) * cf.scale_e, 0.0f), top));     // model.h ck_bucket
+    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(en[k].x), "=r"(en[k].y) : "r"(ent_addr + 8u * b));
+  }
+#pragma unroll
+  for (int k = 0; k < RK_BATCH; k++) {
+    const uint32_t first = en[k].y & 0xFFFFu, cnt = en[k].y >> 16;
+    uint32_t kk = 2u * first + 1u + (img[k] > en[k].x ? 2u : (img[k] == en[k].x ? 1u : 0u));
+    if (cnt > 1u && img[k] > en[k].x) {        // crowded bucket: scan the threshold array from the second one on (sentinels end it)
+      uint32_t r = th_addr + 4u * (first + 1u), t;
+      asm volatile("ld.shared.u32 %0, [%1];" : "=r"(t) : "r"(r));
+      while (t < img[k]) { r += 4u; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(t) : "r"(r)); }
+      kk = ((r - th_addr) >> 1) + (t == img[k] ? 2u : 1u);
+    }
+    key[k] = nan[k] ? 2u * cf.n_thr + 1u : kk;      // NaN is the greatest value (Double.compareTo)
+  }
+}
+
 // The same for thresholds that are not floats: values are compared as doubles (64-bit images, Double.compareTo order);
 // the bucket still comes from the value rounded to float, which is monotone.
 __device__ __forceinline__ void ck_rank_keys_wide(uint32_t th_addr, uint32_t tab_addr, const CkFeat& cf, const double (&val)[RK_BATCH], uint32_t (&key)[RK_BATCH]) {
@@ -113,7 +147,7 @@ __global__ void __launch_bounds__(RK_THREADS, RK_CTAS) forest_rank_keys_kernel(c
   const int j = tid & (CK_FB - 1), f = j < nf ? f0 + j : f0;   // this thread's feature never changes (RK_THREADS is a multiple of CK_FB)
   const bool owner = j < nf;
   const CkFeat cf = cd.feat[f]; const int mode = fd.feat_mode[f]; const bool float_field = m.prep[f].dtype == DT_FLOAT;
-  const uint32_t th_addr = smem_u32(rk_smem) + cf.thr_off, tab_addr = smem_u32(rk_smem) + cf.tab_off;
+  const uint32_t th_addr = smem_u32(rk_smem) + cf.thr_off, tab_addr = smem_u32(rk_smem) + cf.tab_off, ent_addr = smem_u32(rk_smem) + cf.ent_off;
   const uint32_t pbit = 1u << (f & 31); const int pword = f0 >> 5;   // a block's 8 features share one present word
   __syncthreads();
   for (long tile = blockIdx.x; tile < kt.ntiles; tile += gridDim.x) {
@@ -137,7 +171,9 @@ __global__ void __launch_bounds__(RK_THREADS, RK_CTAS) forest_rank_keys_kernel(c
         if (SIMPLE) { st[k] = present ? 0 : 1; if (WIDE && float_field) val[k] = (double)(float)val[k]; }   // JPMML casts to the field's dataType
         else { double raw = val[k]; val[k] = 0.0; st[k] = prep_value(m.prep[f], m.prep_pool, present, raw, val[k]); }
       }
-      if (WIDE) ck_rank_keys_wide(th_addr, tab_addr, cf, val, key); else ck_rank_keys(th_addr, tab_addr, cf, mode, val, key);
+      if (WIDE) ck_rank_keys_wide(th_addr, tab_addr, cf, val, key);
+      else if (cf.nb_e) ck_rank_keys_direct(th_addr, ent_addr, cf, mode, val, key);
+      else ck_rank_keys(th_addr, tab_addr, cf, mode, val, key);
 #pragma unroll
       for (int k = 0; k < RK_BATCH; k++) {
         const int ee = min(i0 + k * RK_THREADS, total - 1) >> 3;      // the unclamped event slot of the tile

@@ -79,7 +79,12 @@ static constexpr int32_t LEAF_NULL = INT32_MIN;  // successor meaning "null pred
 //               carry of that value + sign_extend16(node >> 16).  a = 1 sends a missing value right.  Without a threshold:
 //               ~K = 0 (never right) or K = 0x7FFF with a = 1 (right only when missing).
 constexpr int CK_FB = 8;             // features per block of the key pre-pass
-struct CkFeat { uint32_t thr_off, n_thr, tab_off, nb; float lo, scale; };   // byte offsets inside the feature block's table area
+struct CkFeat {   // byte offsets inside the feature block's table area
+  uint32_t thr_off, n_thr, tab_off, nb; float lo, scale;
+  // direct table (float thresholds only): nb_e entries {u32 image of the bucket's first threshold or all-ones, u16 thresholds in lower
+  // buckets, u16 thresholds in this bucket}; with about four buckets per threshold one 8-byte load decides almost every value
+  uint32_t ent_off, nb_e; float scale_e; uint32_t pad;
+};
 //   sparse      trees that do not fit one common depth (leaf-wise grown, heavily pruned, DAGs of compound predicates) keep
 //               explicit children: tree = {u32 n_nodes, u32 root, double weight, u64 node[n_nodes], 8-byte leaf[...]},
 //               node = the 32-bit word above | (left | right << 16) << 32; a child / root code >= 0x8000 is leaf (code & 0x7FFF).

@@ -18,6 +18,7 @@
 #include <limits>
 #include <map>
 #include <stdexcept>
+#include <tuple>
 #include <unordered_map>
 
 #include "model.h"
@@ -683,6 +684,34 @@ struct ForestBuilder {
         for (uint32_t j = 0; j < n; j++) tab[ck_bucket(v[j].second, lo, scale, nb) + 1]++;
         for (uint32_t q = 1; q <= nb; q++) tab[q] = (uint16_t)(tab[q] + tab[q - 1]);
         tables.resize(tables.size() + 2 * (size_t)nb); memcpy(tables.data() + start + cf.tab_off, tab.data(), 2 * (size_t)nb);
+        cf.ent_off = 0; cf.nb_e = 0; cf.scale_e = 0.0f; cf.pad = 0;
+      }
+      // direct tables of the block's features (float thresholds only): ~4 buckets per threshold, at most 1024; dropped for the block
+      // when they would push its table area past the 104 KB two resident CTAs can have
+      if (!wide) {
+        std::vector<uint8_t> ent; std::vector<std::tuple<int, uint32_t, uint32_t, float>> placed;   // feature, offset in ent, nb_e, scale_e
+        for (int f = fb * CK_FB; f < std::min(F, (fb + 1) * CK_FB); f++) {
+          const auto& v = img[f]; const uint32_t n = (uint32_t)v.size(); const CkFeat& cf = feats[f];
+          uint32_t nbe = 16; while (nbe < 4 * n && nbe < 1024) nbe *= 2;
+          float hi = n ? v.back().second : 0.0f; if (!std::isfinite(hi)) hi = FLT_MAX;
+          float se = (n && hi > cf.lo) ? (float)nbe / (hi - cf.lo) : 0.0f; if (!std::isfinite(se)) se = 0.0f;
+          std::vector<uint32_t> cnt(nbe, 0), firstj(nbe, 0);
+          for (uint32_t j = n; j-- > 0;) { uint32_t bq = ck_bucket(v[j].second, cf.lo, se, nbe); cnt[bq]++; firstj[bq] = j; }
+          const uint32_t off = (uint32_t)ent.size(); ent.resize(ent.size() + 8 * (size_t)nbe);
+          uint32_t below = 0;
+          for (uint32_t bq = 0; bq < nbe; bq++) {
+            const uint32_t tf = cnt[bq] ? (uint32_t)v[firstj[bq]].first : 0xFFFFFFFFu, meta = below | (std::min<uint32_t>(cnt[bq], 0xFFFF) << 16);
+            memcpy(ent.data() + off + 8 * (size_t)bq, &tf, 4); memcpy(ent.data() + off + 8 * (size_t)bq + 4, &meta, 4);
+            below += cnt[bq];
+          }
+          placed.emplace_back(f, off, nbe, se);
+        }
+        tables.resize((tables.size() + 7) & ~size_t(7));
+        if (tables.size() - start + ent.size() + 16 <= 104 * 1024) {
+          const uint32_t base = (uint32_t)(tables.size() - start);
+          tables.insert(tables.end(), ent.begin(), ent.end());
+          for (auto& pl : placed) { CkFeat& cf = feats[std::get<0>(pl)]; cf.ent_off = base + std::get<1>(pl); cf.nb_e = std::get<2>(pl); cf.scale_e = std::get<3>(pl); }
+        }
       }
       tables.resize((tables.size() + 15) & ~size_t(15));
       block_smem = std::max(block_smem, tables.size() - start);
