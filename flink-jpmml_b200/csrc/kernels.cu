@@ -243,9 +243,10 @@ __global__ void __launch_bounds__(256) forest_general_kernel(const __grid_consta
   const int T = fd.n_trees; const bool classify = fd.classify;
   double sum = 0, wsum = 0; bool fail = row_fails_preparation(m, a, row), null_result = false;
   constexpr int MAXL = 64;
-  double votes[MAXL]; int order[MAXL]; int seen = 0;
+  static_assert(MAX_MEDIAN_SEGMENTS <= MAXL, "median values share the vote array");
+  double votes[MAXL]; int order[MAXL]; int seen = 0;   // regression median / max: votes[] holds the active segments' values
   if (classify) for (int l = 0; l < m.n_labels && l < MAXL; l++) { votes[l] = 0; order[l] = -1; }
-  int last_node_id = -1;
+  int last_node_id = -1, n_active = 0, first_label = -1;
   double chv[MAX_CHANNELS]; int cur_ch = 0;   // modelChain: finished channel values
   for (int t = 0; t < T && !fail; t++) {
     int32_t s = fd.troot[t];
@@ -257,14 +258,29 @@ __global__ void __launch_bounds__(256) forest_general_kernel(const __grid_consta
       else s = encode_key(fd, (int)nd.feat, v) <= nd.k ? nd.on_true : nd.on_false;
     }
     if (fail) break;
+    if (s == LEAF_SKIP) { if (a.node_ids) a.node_ids[row * (long)a.node_stride + t] = -1; continue; }   // Segment predicate not TRUE
+    n_active++;
     if (a.node_ids) a.node_ids[row * (long)a.node_stride + t] = s == LEAF_NULL ? 0 : fd.gleaf_node_id[~s];
-    if (s == LEAF_NULL) { null_result = true; continue; }
+    if (s == LEAF_NULL) {
+      null_result = true;
+      if (fd.method == FM_SELECT_FIRST) { if (a.node_ids) for (int u = t + 1; u < T; u++) a.node_ids[row * (long)a.node_stride + u] = -1; break; }
+      continue;
+    }
     int leaf = ~s; last_node_id = fd.gleaf_node_id[leaf];
     double w = fd.tweight[t];
+    if (fd.method == FM_SELECT_FIRST) {   // the first segment whose predicate holds decides alone; later segments are not evaluated
+      if (classify) first_label = fd.gleaf_label[leaf]; else sum = fd.gleaf_value[leaf];
+      if (a.node_ids) for (int u = t + 1; u < T; u++) a.node_ids[row * (long)a.node_stride + u] = -1;
+      break;
+    }
     if (!classify) {
       double v = fd.gleaf_value[leaf];
       if (fd.method == FM_CHAIN) { int ch = fd.tree_channel[t]; if (ch != cur_ch) { chv[cur_ch] = channel_value(fd.channels[cur_ch], sum); sum = 0.0; cur_ch = ch; } sum += v; }
-      else if (fd.method == FM_WSUM || fd.method == FM_WAVERAGE) { sum += w * v; wsum += w; } else sum += v;
+      else if (fd.method == FM_WSUM || fd.method == FM_WAVERAGE) { sum += w * v; wsum += w; }
+      else if (fd.method == FM_MEDIAN || fd.method == FM_MAX) {   // insertion into the sorted prefix
+        int k = n_active - 1; while (k > 0 && votes[k - 1] > v) { votes[k] = votes[k - 1]; k--; } votes[k] = v;
+      }
+      else sum += v;
     } else {
       if (fd.method == FM_AVG_PROB || fd.method == FM_WAVG_PROB) {   // sum of (weighted) leaf distributions; /sum(w) does not move the winner
         const double ww = fd.method == FM_WAVG_PROB ? w : 1.0;
@@ -282,12 +298,23 @@ __global__ void __launch_bounds__(256) forest_general_kernel(const __grid_consta
     }
   }
   if (fail) { write_out(a, row, 0, ST_PREP, -1); return; }
-  if (null_result) { write_out(a, row, 0, m.target_status ? m.target_status : ST_EVAL, -1); return; }  // null prediction / failed aggregation
+  const bool alone = fd.method == FM_SINGLE || fd.method == FM_SELECT_FIRST;   // the result is one tree's own
+  // a null prediction of the deciding tree (or no active segment at all) is "no target value"; a null prediction inside an
+  // aggregation fails the evaluation itself, before target extraction is looked at
+  if (null_result) { write_out(a, row, 0, (alone || fd.method == FM_CHAIN) && m.target_status ? m.target_status : ST_EVAL, -1); return; }
+  if (n_active == 0) { write_out(a, row, 0, m.target_status ? m.target_status : ST_EVAL, -1); return; }
   if (fd.method == FM_CHAIN) { chv[cur_ch] = channel_value(fd.channels[cur_ch], sum); chain_finish(m, a, row, [&](int c) { return chv[c]; }); return; }
   if (!classify) {
     double v = sum;
-    if (fd.method == FM_AVERAGE) v = sum / (double)T; else if (fd.method == FM_WAVERAGE) v = sum / wsum;
-    write_out(a, row, apply_target(m.tx, v), m.target_status, fd.method == FM_SINGLE ? last_node_id : -1);
+    if (fd.method == FM_AVERAGE) v = sum / (double)n_active; else if (fd.method == FM_WAVERAGE) v = sum / wsum;
+    else if (fd.method == FM_MAX) v = votes[n_active - 1];
+    else if (fd.method == FM_MEDIAN) {   // 50th percentile as commons-math's Percentile (LEGACY estimate) computes it: position (n + 1) / 2
+      const int h = n_active / 2;
+      if (n_active & 1) v = votes[h]; else { double lo = votes[h - 1], hi = votes[h]; v = lo + 0.5 * (hi - lo); }
+    }
+    write_out(a, row, apply_target(m.tx, v), m.target_status, alone ? last_node_id : -1);
+  } else if (fd.method == FM_SELECT_FIRST) {
+    write_label(m, a, row, first_label, last_node_id);
   } else {
     int best = -1;
     for (int l = 0; l < m.n_labels; l++) {

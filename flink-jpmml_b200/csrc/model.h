@@ -49,18 +49,22 @@ enum : int { FOREST_COMPLETE = 0, FOREST_GENERAL = 1 };
 enum : int { ENC_FLOAT = 0, ENC_RANK = 1 };
 enum : int { FM_SINGLE = 0, FM_SUM = 1, FM_AVERAGE = 2, FM_WSUM = 3, FM_WAVERAGE = 4, FM_VOTE = 5, FM_WVOTE = 6,
              FM_AVG_PROB = 7, FM_WAVG_PROB = 8,
-             FM_CHAIN = 9 };  // modelChain: per-channel tree sums feed RegressionTables (DeviceModel::reg, slot = channel)
+             FM_CHAIN = 9,    // modelChain: per-channel tree sums feed RegressionTables (DeviceModel::reg, slot = channel)
+             FM_SELECT_FIRST = 10, FM_MEDIAN = 11, FM_MAX = 12 };  // general form only (forest_general_kernel)
+static constexpr int MAX_MEDIAN_SEGMENTS = 64;
 static constexpr int MAX_CHANNELS = 16;
 struct ChannelSpec { TargetXform tx; int32_t n_trees; int32_t average; };  // one regression segment of a modelChain  // classification average / weightedAverage of the leaves' distributions
 
 // General decision node: key = key(x[feat]); key == 0 (missing) -> on_missing, key <= k -> on_true, else on_false.
-// Successors >= 0 are node indices, < 0 are ~leaf index, LEAF_NULL is "null prediction".
+// Successors >= 0 are node indices, < 0 are ~leaf index, LEAF_NULL is "null prediction", LEAF_SKIP is "the Segment's
+// predicate is not TRUE: the segment takes no part in the aggregation" (general form only).
 struct GNode {
   uint32_t feat;
   uint32_t k;
   int32_t on_true, on_false, on_missing;
 };
 static constexpr int32_t LEAF_NULL = INT32_MIN;  // successor meaning "null prediction"
+static constexpr int32_t LEAF_SKIP = INT32_MIN + 1;
 
 #ifdef __CUDACC__
 #define FJP_HD __host__ __device__

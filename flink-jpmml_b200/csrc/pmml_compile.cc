@@ -439,6 +439,16 @@ struct ForestBuilder {
   std::vector<Thr> thr; std::vector<TNode> nodes; std::vector<int> node_slot; std::vector<TLeaf> leaves; std::vector<int32_t> roots;
   std::vector<double> weights; std::vector<std::string> labels; std::unordered_map<std::string, int> label_idx;
   std::vector<int32_t> chain_channels;   // modelChain: channel of every tree (empty otherwise)
+  // Segment predicates: a segment whose predicate is not TRUE leaves the aggregation (LEAF_SKIP).  For sum / weightedSum
+  // with at least one always-active segment, "leaves" is the same as "adds +0.0" bit for bit (the running sum starts at
+  // +0.0 and x + (+-0.0) == x for every x it can hold), so the skip becomes one shared zero leaf with node id -1 and the
+  // ensemble keeps its on-chip forms.
+  bool skip_as_zero = false; int32_t zero_skip_leaf = 0;
+  int32_t skip_successor() {
+    if (!skip_as_zero) return LEAF_SKIP;
+    if (zero_skip_leaf == 0) { leaves.push_back(TLeaf{0.0, -1, -1, {}}); zero_skip_leaf = ~(int32_t)(leaves.size() - 1); }
+    return zero_skip_leaf;
+  }
   explicit ForestBuilder(Builder& bb, bool c) : b(bb), classify(c) {}
 
   int label_of(sv s) { std::string k(s); auto it = label_idx.find(k); if (it != label_idx.end()) return it->second; int i = (int)labels.size(); labels.push_back(k); label_idx[k] = i; return i; }
@@ -500,9 +510,24 @@ struct ForestBuilder {
     }
     leaves.push_back(lf); int32_t s = ~(int32_t)(leaves.size() - 1); memo_put(n, cx, M_LEAF, s); return s;
   }
-  int32_t add_test(int slot, double value, bool strict, int32_t t, int32_t f, int32_t m) {
+  // One decision node.  presence_only: "passes whenever the value is there" (thr = -1; the false branch is never taken).
+  // Nodes are hash-consed, and a test all of whose outcomes lead to the same place is not emitted at all: compound
+  // predicates then collapse to graphs in which a missing value follows one of the two branches wherever the logic
+  // allows it, which is what the on-chip tree forms need.
+  struct NodeKey { uint64_t vb; int32_t slot, kind, t, f, m; bool operator==(const NodeKey& o) const { return vb == o.vb && slot == o.slot && kind == o.kind && t == o.t && f == o.f && m == o.m; } };
+  struct NodeKeyHash { size_t operator()(const NodeKey& k) const {
+    uint64_t h = k.vb * 0x9E3779B97F4A7C15ull; for (uint32_t v : {(uint32_t)k.slot, (uint32_t)k.kind, (uint32_t)k.t, (uint32_t)k.f, (uint32_t)k.m}) h = (h ^ v) * 0x100000001B3ull + (h >> 29);
+    return (size_t)h; } };
+  std::unordered_map<NodeKey, int32_t, NodeKeyHash> node_memo; int cons = 0;   // consing is on inside compound / Segment / root predicates only
+  int32_t add_test(int slot, double value, bool strict, int32_t t, int32_t f, int32_t m, bool presence_only = false) {
     if (slot < 0) return m;  // field is never supplied -> always UNKNOWN
-    thr.push_back({slot, value, strict}); nodes.push_back({(int)thr.size() - 1, t, f, m}); node_slot.push_back(slot); return (int32_t)nodes.size() - 1;
+    if (presence_only ? t == m : (t == f && f == m)) return t;
+    uint64_t vb; memcpy(&vb, &value, 8);
+    NodeKey key{presence_only ? uint64_t(0) : vb, slot, presence_only ? 2 : (int)strict, t, f, m};
+    if (cons) { auto it = node_memo.find(key); if (it != node_memo.end()) return it->second; }
+    thr.push_back({slot, value, strict}); nodes.push_back({presence_only ? -1 : (int)thr.size() - 1, t, f, m}); node_slot.push_back(slot);
+    if (cons) node_memo[key] = (int32_t)nodes.size() - 1;
+    return (int32_t)nodes.size() - 1;
   }
   // x == v on slot:  (x <= v) and not (x < v)
   int32_t emit_eq(int slot, double v, int32_t sT, int32_t sF, int32_t sU) {
@@ -518,8 +543,8 @@ struct ForestBuilder {
       sv op = p.attr("operator"); sv fname = p.attr("field"); int slot = b.slot_of(fname);
       uint8_t dt = b.dict_field(fname).dtype;
       // thr = -1: "passes whenever present"; the missing successor is the failing branch
-      if (op == "isMissing") { if (slot < 0) return sT; int32_t r = add_test(slot, 0, false, sF, sT, sT); nodes[r].thr = -1; return r; }
-      if (op == "isNotMissing") { if (slot < 0) return sF; int32_t r = add_test(slot, 0, false, sT, sF, sF); nodes[r].thr = -1; return r; }
+      if (op == "isMissing") { if (slot < 0) return sT; return add_test(slot, 0, false, sF, sT, sT, true); }
+      if (op == "isNotMissing") { if (slot < 0) return sF; return add_test(slot, 0, false, sT, sF, sF, true); }
       // A string-typed field can never hold a value here: vectors carry doubles, and a Double offered to a string field
       // fails input preparation for the whole event before any model code runs (status 2 / EmptyScore, as the reference
       // does for its k-means string fixture, T/api/PmmlModelSpec.scala:131-136).  What reaches the walk is only the
@@ -541,7 +566,7 @@ struct ForestBuilder {
       const XNode* arr = p.child("Array"); std::vector<double> vals;
       if (arr) for (auto& t : split_array(*arr)) { double v; if (!parse_in_dtype(dt, t, &v)) unsupported("set member does not parse in the field's dataType"); vals.push_back(v); }
       int32_t hit = in ? sT : sF, miss = in ? sF : sT, next = miss;
-      if (vals.empty()) { int32_t r = add_test(slot, 0, false, miss, miss, sU); nodes[r].thr = -1; return r; }
+      if (vals.empty()) return add_test(slot, 0, false, miss, miss, sU, true);
       for (size_t k = vals.size(); k-- > 0;) next = emit_eq(slot, vals[k], hit, next, sU);   // membership: a chain of equalities
       return next;
     }
@@ -550,6 +575,7 @@ struct ForestBuilder {
       for (const XNode* k = p.first; k; k = k->next) if (k->name != "Extension") ops.push_back(k);
       if (ops.size() < 2) malformed("CompoundPredicate needs two operands");
       sv bop = p.attr("booleanOperator"); const int n = (int)ops.size();
+      cons++; struct Leave { int& c; ~Leave() { c--; } } leave{cons};
       std::map<std::pair<int, int>, int32_t> memo;   // (operand index, state) -> successor
       std::function<int32_t(int, int)> go = [&](int i, int state) -> int32_t {
         auto key = std::make_pair(i, state); auto it = memo.find(key); if (it != memo.end()) return it->second;
@@ -596,7 +622,7 @@ struct ForestBuilder {
     memo_put(*kid, cx, M_CHAIN, r); return r;
   }
 
-  void add_tree(const XNode& tm, double weight, bool nested) {
+  void add_tree(const XNode& tm, double weight, bool nested, const XNode* seg_pred = nullptr) {
     if (nested) check_nested_schema(tm);
     TreeCtx cx; cx.epoch = next_epoch(); sv mvs = tm.attr("missingValueStrategy", "none");
     cx.mvs = mvs == "none" ? 0 : mvs == "defaultChild" ? 1 : mvs == "lastPrediction" ? 2 : mvs == "nullPrediction" ? 3 : -1;
@@ -617,9 +643,9 @@ struct ForestBuilder {
     number_nodes(*root, cx);
     const XNode& rp = *pred_of(*root);
     int32_t r;
-    if (rp.name == "True") r = enter(*root, LEAF_NULL, cx);
-    else if (rp.name == "False") r = LEAF_NULL;
-    else unsupported("root Node predicate other than True/False");
+    if (rp.name == "False") r = LEAF_NULL;
+    else { int32_t body = enter(*root, LEAF_NULL, cx); cons++; r = emit_pred(rp, body, LEAF_NULL, LEAF_NULL); cons--; }   // a root test that is not TRUE: null prediction
+    if (seg_pred && seg_pred->name != "True") { int32_t skip = skip_successor(); cons++; r = emit_pred(*seg_pred, r, skip, skip); cons--; }
     roots.push_back(r); weights.push_back(weight);
   }
 
@@ -766,7 +792,7 @@ struct ForestBuilder {
         std::vector<int32_t> order, lorder; std::vector<int32_t> stack{roots[t]};
         while (!stack.empty() && ok) {   // reachable nodes / leaves of this tree, numbered in visiting order
           int32_t s = stack.back(); stack.pop_back();
-          if (s == LEAF_NULL) { ok = false; break; }
+          if (s == LEAF_NULL || s == LEAF_SKIP) { ok = false; break; }
           if (s < 0) { if (leaf_local[~s] < 0) { leaf_local[~s] = (int32_t)lorder.size(); lorder.push_back(~s); } continue; }
           if (local[s] >= 0) continue;
           const TNode& n = nodes[s];
@@ -889,10 +915,11 @@ struct ForestBuilder {
     // whose leaves all repeat it (pruned XGBoost / LightGBM trees, trees of different depths).  Needs: every test sends a
     // missing value down one of its two branches, and no null prediction is reachable.  Sub-graphs shared by several
     // parents (compound predicates, equality tests) are simply duplicated while the expansion stays small.
-    int depth = -1; bool complete = !roots.empty();
+    const bool general_only = method == FM_SELECT_FIRST || method == FM_MEDIAN || method == FM_MAX;
+    int depth = -1; bool complete = !roots.empty() && !general_only;
     std::vector<int> dep_memo(nodes.size(), -1);
     std::function<int(int32_t)> dep = [&](int32_t s) -> int {  // longest path below s; -2: cannot be laid out
-      if (s < 0) return s == LEAF_NULL ? -2 : 0;
+      if (s < 0) return (s == LEAF_NULL || s == LEAF_SKIP) ? -2 : 0;
       if (dep_memo[s] != -1) return dep_memo[s];
       const TNode& n = nodes[s]; int r;
       if (n.on_missing != n.on_true && n.on_missing != n.on_false) r = -2;
@@ -935,7 +962,7 @@ struct ForestBuilder {
     } else {
       fd.format = FOREST_GENERAL; fd.depth = 0;
       std::vector<uint64_t> blobs; b.put(&fd.blobs, blobs);
-      if (method != FM_SINGLE && !roots.empty()) emit_compact(0, used, feat_of, !float_ok, true);
+      if (method != FM_SINGLE && !general_only && !roots.empty()) emit_compact(0, used, feat_of, !float_ok, true);
     }
     b.put(&fd.leaf_node_id, leaf_ids);
     {  // the general form is always emitted: the engine falls back to it when a tile of keys does not fit on chip
@@ -1047,19 +1074,24 @@ void compile_mining(const XNode& m, Builder& b) {
   bool classify = m.attr("functionName") == "classification"; sv mm = sg->attr("multipleModelMethod");
   if (mm == "modelChain") { compile_model_chain(m, *sg, b); return; }
   int method = -1;
-  if (!classify) method = mm == "sum" ? FM_SUM : mm == "average" ? FM_AVERAGE : mm == "weightedSum" ? FM_WSUM : mm == "weightedAverage" ? FM_WAVERAGE : -1;
+  if (!classify) method = mm == "sum" ? FM_SUM : mm == "average" ? FM_AVERAGE : mm == "weightedSum" ? FM_WSUM : mm == "weightedAverage" ? FM_WAVERAGE
+                        : mm == "median" ? FM_MEDIAN : mm == "max" ? FM_MAX : -1;
   else method = mm == "majorityVote" ? FM_VOTE : mm == "weightedMajorityVote" ? FM_WVOTE : mm == "average" ? FM_AVG_PROB : mm == "weightedAverage" ? FM_WAVG_PROB : -1;
+  if (mm == "selectFirst") method = FM_SELECT_FIRST;
   if (method < 0) unsupported("multipleModelMethod " + std::string(mm) + " for " + (classify ? "classification" : "regression"));
   ForestBuilder fb(b, classify);
+  bool always_active = false;
+  sg->each("Segment", [&](const XNode& s) { if (ForestBuilder::pred_of(s)->name == "True") always_active = true; });
+  fb.skip_as_zero = (method == FM_SUM || method == FM_WSUM) && always_active;
   sg->each("Segment", [&](const XNode& s) {
     const XNode& p = *ForestBuilder::pred_of(s);
-    if (p.name == "False") return;
-    if (p.name != "True") unsupported("Segment predicate other than True/False");
+    if (p.name == "False") return;   // never takes part
     const XNode* tm = s.child("TreeModel");
     if (!tm) unsupported("Segment model other than TreeModel");
-    fb.add_tree(*tm, need_double(s.attr("weight", "1"), "weight"), true);
+    fb.add_tree(*tm, need_double(s.attr("weight", "1"), "weight"), true, &p);
   });
   if (fb.roots.empty()) unsupported("Segmentation without active segments");
+  if (method == FM_MEDIAN && (int)fb.roots.size() > MAX_MEDIAN_SEGMENTS) unsupported("median over more than 64 segments");
   fb.emit(method); b.set_labels(fb.labels, false); finish_target(b, classify);
 }
 

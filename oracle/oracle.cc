@@ -869,7 +869,11 @@ struct MiningModel : Model {
       } else if (method == "median" || method == "max") {
         std::vector<double> v; for (auto& p : res) v.push_back(apply_target(*p.first->model, p.second.value));
         std::sort(v.begin(), v.end());
-        out = method == "max" ? v.back() : (v.size() % 2 ? v[v.size() / 2] : 0.5 * (v[v.size() / 2 - 1] + v[v.size() / 2]));
+        // median = JPMML's DoubleVector.median(): the 50th percentile of commons-math3's Percentile in its default
+        // (LEGACY) estimation: position p = (n + 1) / 2 in the sorted values, lower + frac(p) * (upper - lower)
+        if (method == "max") out = v.back();
+        else if (v.size() % 2) out = v[v.size() / 2];
+        else { double lo = v[v.size() / 2 - 1], hi = v[v.size() / 2]; out = lo + 0.5 * (hi - lo); }
       } else throw EvalError("unsupported multipleModelMethod " + method);
       r.has_value = true; r.value = out;
       return r;

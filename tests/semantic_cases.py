@@ -150,6 +150,47 @@ def cases():
     tie = lambda: doc(AB, f'<MiningModel functionName="classification">{schema(["a", "b"])}<Segmentation multipleModelMethod="majorityVote">'
                       f'{cseg(1, 1, "1", "0")}{cseg(2, 1, "0", "1")}</Segmentation></MiningModel>', target=("y", "categorical", "string", ("0", "1")))
     out.append(("mining/vote-tie-first-seen", tie(), X7, P7, None, [(0, 1.0, None), (0, 0.0, None)]))
+    # ---- Segment predicates: only segments whose predicate is TRUE take part (UNKNOWN counts as not TRUE)
+    gt = lambda f, v: f'<SimplePredicate field="{f}" operator="greaterThan" value="{v}"/>'
+    miss_b = '<SimplePredicate field="b" operator="isMissing"/>'
+    const = lambda v: f'<Node id="1" score="{v}"><True/></Node>'
+    pseg = lambda i, w, pred, nodes: f'<Segment id="{i}" weight="{w}">{pred}{tree_model(["a", "b"], nodes, strategy="defaultChild", target=None)}</Segment>'
+    pm_ = lambda method, *segs: doc(AB, f'<MiningModel functionName="regression">{schema(["a", "b"])}<Segmentation multipleModelMethod="{method}">'
+                                        + "".join(segs) + '</Segmentation></MiningModel>')
+    s_all, s_agt1, s_bmiss = pseg(1, 1, "<True/>", SMALL_TREE), pseg(2, 3, gt("a", 1), t2), pseg(3, 1, miss_b, const(1000))
+    Xp, Pp = _rows((0, 5), (2, -1), (None, None), (2, None))
+    #   S1 (always): 1.5, -2, -2, -2.   S2 (a > 1): -, 100, - (UNKNOWN), 100.   S3 (b missing): -, -, 1000, 1000
+    out.append(("mining/segment-predicates-sum", pm_("sum", s_all, s_agt1, s_bmiss), Xp, Pp, None,
+                [(0, 1.5, None), (0, 98.0, None), (0, 998.0, None), (0, 1098.0, None)]))
+    out.append(("mining/segment-predicates-average", pm_("average", s_all, s_agt1, s_bmiss), Xp, Pp, None,
+                [(0, 1.5, None), (0, 49.0, None), (0, 499.0, None), (0, 366.0, None)]))
+    out.append(("mining/segment-predicates-weightedAverage", pm_("weightedAverage", s_all, s_agt1, s_bmiss), Xp, Pp, None,
+                [(0, 1.5, None), (0, 74.5, None), (0, 499.0, None), (0, (-2.0 + 300.0 + 1000.0) / 5.0, None)]))
+    # no always-active segment: an event none of the predicates accepts has no result at all
+    out.append(("mining/no-active-segment", pm_("sum", s_agt1, s_bmiss), Xp, Pp, None,
+                [(3, None, None), (0, 100.0, None), (0, 1000.0, None), (0, 1100.0, None)]))
+    # selectFirst: the first segment whose predicate holds decides alone (aux = that tree's node id)
+    out.append(("mining/selectFirst", pm_("selectFirst", s_agt1, s_bmiss, s_all), Xp, Pp, None,
+                [(0, 1.5, 2), (0, 100.0, 2), (0, 1000.0, 1), (0, 100.0, 2)]))
+    out.append(("mining/selectFirst-none", pm_("selectFirst", s_agt1, s_bmiss), Xp, Pp, None,
+                [(3, None, None), (0, 100.0, 2), (0, 1000.0, 1), (0, 100.0, 2)]))
+    pcseg = lambda i, pred, lab_l, lab_r: cseg(i, 1, lab_l, lab_r).replace("<True/>", pred, 1)
+    sfc = doc(AB, f'<MiningModel functionName="classification">{schema(["a", "b"])}<Segmentation multipleModelMethod="selectFirst">'
+                  f'{pcseg(1, gt("b", 0), "1", "0")}{pcseg(2, "<True/>", "2", "0")}</Segmentation></MiningModel>', target=("y", "categorical", "string", ("0", "1", "2")))
+    Xf, Pf = _rows((-1, 1), (-1, 0), (1, None), (1, 3))
+    out.append(("mining/selectFirst-classification", sfc, Xf, Pf, None, [(0, 1.0, 2), (0, 2.0, 2), (0, 0.0, 3), (0, 0.0, 3)]))
+    # median (odd count: the middle value; even count: lower + (upper - lower) / 2) and max over the active segments
+    s_c3 = pseg(4, 1, "<True/>", const(3))
+    s_c1000_agt1 = pseg(3, 1, gt("a", 1), const(1000))
+    plain_t2 = pseg(2, 1, "<True/>", t2)
+    #   (0,5): 1.5, 200, -, 3 -> sorted 1.5 3 200;   (2,-1): -2, 100, 1000, 3 -> sorted -2 3 100 1000
+    out.append(("mining/median", pm_("median", s_all, plain_t2, s_c1000_agt1, s_c3), Xp[:2], Pp[:2], None, [(0, 3.0, None), (0, 51.5, None)]))
+    out.append(("mining/max", pm_("max", s_all, plain_t2, s_c1000_agt1, s_c3), Xp[:2], Pp[:2], None, [(0, 200.0, None), (0, 1000.0, None)]))
+    # a root Node whose own predicate is not TRUE: null prediction, whatever the strategies say
+    rooted = (f'<Node id="1" score="9">{gt("a", 0)}<Node id="2" score="1"><SimplePredicate field="b" operator="lessThan" value="0"/></Node></Node>')
+    Xr, Pr = _rows((1, -1), (-1, -1), (None, -1), (1, 1))
+    out.append(("tree/root-predicate", doc(AB, tree_model(["a", "b"], rooted, strategy="lastPrediction", no_true="returnLastPrediction")), Xr, Pr, None,
+                [(0, 1.0, 2), (3, None, None), (3, None, None), (0, 9.0, 1)]))
     # ---- clustering variants: 1-D centres 0 and 10 plus a second field; cluster ids "5" and "x"
     def clu(measure, compare="absDiff", extra="", ids=("5", "x"), weights=""):
         body = (f'<ClusteringModel modelName="c" functionName="clustering" modelClass="centerBased" numberOfClusters="2">'

@@ -107,7 +107,7 @@ def test_throughput_path_forms_compile_on_the_host(capi, gen, monkeypatch):
 def test_unsupported_features_are_load_errors_not_wrong_answers(capi, gen):
     pm, _ = gen.gbt_pmml(T=3, depth=2, F=4, seed=1)
     for bad in (pm.replace(b'multipleModelMethod="sum"', b'multipleModelMethod="modelChain"'),
-                pm.replace(b'multipleModelMethod="sum"', b'multipleModelMethod="median"'),
+                pm.replace(b'multipleModelMethod="sum"', b'multipleModelMethod="selectAll"'),
                 pm.replace(b'missingValueStrategy="defaultChild"', b'missingValueStrategy="weightedConfidence"')):
         with pytest.raises(capi.ModelLoadingException, match="unsupported"):
             capi.compile_model(bad)
