@@ -988,6 +988,13 @@ __global__ void __launch_bounds__(NN_E* NN_WARPS) neural_kernel(const __grid_con
   for (int l = 0; l < nd.n_layers; l++) {
     const NeuralLayer L = nd.layers[l];
     const double* Wm = nd.weights + L.w_off; const double* B = nd.biases + L.b_off;
+    if (L.act == ACT_RADIAL) {   // radial basis layer: squared distance to the weight vector instead of a weighted sum; no bias
+      for (int j = warp; j < L.n_out; j += NN_WARPS) {
+        double z = 0;
+        for (int i = 0; i < L.n_in; i++) { const double dlt = cur[i * NN_E + lane] - __ldg(Wm + (size_t)j * L.n_in + i); z += dlt * dlt; }
+        nxt[j * NN_E + lane] = exp(B[2 * L.n_out + j] - z / B[L.n_out + j]);
+      }
+    } else
     for (int j0 = warp * NN_J; j0 < L.n_out; j0 += NN_WARPS * NN_J) {
       double z[NN_J];
 #pragma unroll
@@ -1778,7 +1785,8 @@ cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t 
     case MK_NEURAL: {
       { cudaError_t e; if (slice_scratch && launch_sliced(m, a, slice_scratch, s, launches, &e)) return e; }
       bool tiled = true;   // the streamed path keeps <= 4 groups of 8 outputs per warp: layers up to 256 neurons
-      for (int l = 0; l < m.nn.n_layers; l++) tiled = tiled && m.nn.layers[l].n_out_pad <= 8 * NT_G * NT_WARPS && m.nn.layers[l].n_out_pad * 8 <= NT_RING;
+      for (int l = 0; l < m.nn.n_layers; l++) tiled = tiled && m.nn.layers[l].n_out_pad <= 8 * NT_G * NT_WARPS && m.nn.layers[l].n_out_pad * 8 <= NT_RING
+                                                           && m.nn.layers[l].act != ACT_RADIAL;   // radial basis layers: the general kernel only
       if (tiled && env_int("FJP_NN_PAIR", 1)) {   // two events per thread, one in-place activation buffer
         cudaError_t e = launch_neural_pair(m, a, s);
         if (e != cudaErrorInvalidConfiguration) return e;
@@ -1908,6 +1916,15 @@ __device__ bool dx_run(const DerivedDesc& dd, int d, const double* __restrict__ 
         if (o.a == DF_IF) {
           if (!ap[0]) { if (o.flags & 1) { v = o.x; p = true; } break; }
           if (a[0] != 0.0) { v = a[1]; p = ap[1]; } else if (n > 2) { v = a[2]; p = ap[2]; }
+          if (!p && (o.flags & 2)) { v = o.y; p = true; }
+          break;
+        }
+        if (o.a == DF_COALESCE) { v = a[0]; p = ap[0]; if (!p) { v = o.x; p = true; } break; }
+        if (o.a == DF_USERCALL) {   // a[0..n-2]: the arguments (present only when mapMissingTo looks at them), a[n-1]: the body's value
+          bool args_ok = true; for (int k = 0; k + 1 < n; k++) args_ok = args_ok && ap[k];
+          if (!args_ok) { v = o.x; p = true; break; }
+          v = a[n - 1]; p = ap[n - 1];
+          if (p && o.outliers) v = (double)(float)v;
           if (!p && (o.flags & 2)) { v = o.y; p = true; }
           break;
         }

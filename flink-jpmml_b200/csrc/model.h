@@ -224,7 +224,8 @@ struct GeneralRegDesc {
 };
 
 enum : int { ACT_THRESHOLD = 0, ACT_LOGISTIC, ACT_TANH, ACT_IDENTITY, ACT_EXPONENTIAL, ACT_RECIPROCAL, ACT_SQUARE,
-             ACT_GAUSS, ACT_SINE, ACT_COSINE, ACT_ELLIOTT, ACT_ARCTAN, ACT_RECTIFIER };
+             ACT_GAUSS, ACT_SINE, ACT_COSINE, ACT_ELLIOTT, ACT_ARCTAN, ACT_RECTIFIER,
+             ACT_RADIAL };   // radialBasis: exp(fanIn ln(altitude) - sum (x - w)^2 / (2 width^2)); biases hold [bias | 2 width^2 | fanIn ln(altitude)] x n_out
 enum : int { NI_FIELDREF = 0, NI_NORMCONT = 1, NI_NORMDISC = 2, NI_CONSTANT = 3 };
 struct NeuralInput {  // DerivedField of a NeuralInput
   int32_t kind, slot, pts_off, n_pts, outliers, has_map_missing;  // outliers: 0 asIs, 1 asMissingValues, 2 asExtremeValues
@@ -251,7 +252,9 @@ struct NeuralDesc {
 enum : int { DX_CONST = 0, DX_FIELD, DX_NORMDISC, DX_NORMCONT, DX_DISCRETIZE, DX_MAPVALUES, DX_APPLY };
 enum : int { DF_ADD = 0, DF_SUB, DF_MUL, DF_DIV, DF_MIN, DF_MAX, DF_SUM, DF_AVG, DF_PRODUCT, DF_POW, DF_EXP, DF_LN, DF_LOG10, DF_SQRT,
              DF_ABS, DF_FLOOR, DF_CEIL, DF_ROUND, DF_THRESHOLD, DF_EQ, DF_NE, DF_LT, DF_LE, DF_GT, DF_GE, DF_AND, DF_OR, DF_NOT,
-             DF_ISIN, DF_ISNOTIN, DF_IF, DF_ISMISSING, DF_ISNOTMISSING };
+             DF_ISIN, DF_ISNOTIN, DF_IF, DF_ISMISSING, DF_ISNOTMISSING,
+             DF_COALESCE,    // FieldRef to a DefineFunction parameter carrying mapMissingTo: the argument's value, or x when it is missing
+             DF_USERCALL };  // DefineFunction call: [arguments when mapMissingTo needs them] body; outliers = 1: float result
 struct DxOp {
   int32_t op, a, b, c, flags;   // a: field slot / function id; b, c: pool offset + count, or argument count; flags: 1 mapMissingTo, 2 defaultValue
   int32_t outliers;             // NORMCONT: 0 asIs, 1 asMissingValues, 2 asExtremeValues

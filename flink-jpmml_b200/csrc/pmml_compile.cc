@@ -256,6 +256,10 @@ void read_schema(const XNode& model, Builder& b) {
 // ---------------------------------------------------------------------------------------------- derived fields
 struct DerivedCompiler {
   Builder& b; std::vector<DxOp> ops; std::vector<double> pool;
+  // DefineFunction: calls are expanded in place.  Inside a body only the ParameterFields are visible; a FieldRef to one
+  // re-emits the argument's expression in the caller's scope (expressions are pure), then applies its own mapMissingTo.
+  struct Scope { std::map<std::string, const XNode*> params; const Scope* caller; int depth; };
+  std::map<std::string, const XNode*> fns;
   explicit DerivedCompiler(Builder& bb) : b(bb) {}
   static DxOp mk(int op) { DxOp o{}; o.op = op; return o; }
   int numeric_slot(sv field) {
@@ -269,8 +273,18 @@ struct DerivedCompiler {
     if (e.has("mapMissingTo")) { o.flags |= 1; o.x = need_double(e.attr("mapMissingTo"), "mapMissingTo"); }
     if (e.has("defaultValue")) { o.flags |= 2; o.y = need_double(e.attr("defaultValue"), "defaultValue"); }
   }
-  void emit(const XNode& e, int depth) {
+  void emit(const XNode& e, int depth, const Scope* sc = nullptr) {
     if (depth > DX_STACK - 2) unsupported("transformation nested deeper than 14 levels");
+    if (sc) {
+      if (e.name == "FieldRef") {
+        auto it = sc->params.find(std::string(e.attr("field")));
+        if (it == sc->params.end()) unsupported("DefineFunction body refers to a field that is not a ParameterField");
+        emit(*it->second, depth, sc->caller);
+        if (e.has("mapMissingTo")) { DxOp o = mk(DX_APPLY); o.a = DF_COALESCE; o.b = 1; opt(e, o); ops.push_back(o); }
+        return;
+      }
+      if (e.name != "Constant" && e.name != "Apply") unsupported("DefineFunction body element " + std::string(e.name));
+    }
     if (e.name == "Constant") { DxOp o = mk(DX_CONST); o.x = need_double(e.text, "Constant"); ops.push_back(o); return; }
     if (e.name == "FieldRef") { DxOp o = mk(DX_FIELD); o.a = numeric_slot(e.attr("field")); opt(e, o); ops.push_back(o); return; }
     if (e.name == "NormDiscrete") {
@@ -318,10 +332,33 @@ struct DerivedCompiler {
                                  "round", "threshold", "equal", "notEqual", "lessThan", "lessOrEqual", "greaterThan", "greaterOrEqual", "and", "or", "not",
                                  "isIn", "isNotIn", "if", "isMissing", "isNotMissing"};
       sv f = e.attr("function"); int id = -1;
+      auto uf = fns.find(std::string(f));
+      if (uf != fns.end()) {   // user function: [arguments (only when the Apply's mapMissingTo has to look at them)] body -> DF_USERCALL
+        const XNode& df = *uf->second; const int level = sc ? sc->depth + 1 : 1;
+        if (level > 8) unsupported("DefineFunction calls nested deeper than 8");
+        uint8_t fdt = dtype_of(df.attr("dataType", "double"));
+        if (fdt != DT_DOUBLE && fdt != DT_FLOAT) unsupported("DefineFunction dataType other than double / float");
+        std::vector<const XNode*> args; for (const XNode* k = e.first; k; k = k->next) if (k->name != "Extension") args.push_back(k);
+        Scope inner{{}, sc, level}; size_t i = 0; const XNode* body = nullptr;
+        for (const XNode* k = df.first; k; k = k->next) {
+          if (k->name == "Extension") continue;
+          if (k->name == "ParameterField") {
+            if (k->has("dataType") && k->attr("dataType") != "double") unsupported("ParameterField dataType other than double");
+            if (i >= args.size()) unsupported("too few arguments for " + std::string(f));
+            inner.params[std::string(k->attr("name"))] = args[i++];
+          } else body = k;
+        }
+        if (i != args.size() || !body) unsupported("wrong number of arguments for " + std::string(f));
+        int pushed = 0;
+        if (e.has("mapMissingTo")) for (const XNode* a : args) { emit(*a, depth + pushed, sc); pushed++; }
+        emit(*body, depth + pushed, &inner); pushed++;
+        if (depth + pushed > DX_STACK) unsupported("Apply " + std::string(f) + " with " + std::to_string(args.size()) + " arguments");
+        DxOp o = mk(DX_APPLY); o.a = DF_USERCALL; o.b = pushed; o.outliers = fdt == DT_FLOAT ? 1 : 0; opt(e, o); ops.push_back(o); return;
+      }
       for (int i = 0; i < 33; i++) if (f == fn[i]) id = i;
       if (id < 0) unsupported("Apply function " + std::string(f));
       int nargs = 0;
-      for (const XNode* k = e.first; k; k = k->next) if (k->name != "Extension") { emit(*k, depth + nargs); nargs++; }
+      for (const XNode* k = e.first; k; k = k->next) if (k->name != "Extension") { emit(*k, depth + nargs, sc); nargs++; }
       static const int arity[] = {2, 2, 2, 2, -1, -1, -1, -1, -1, 2, 1, 1, 1, 1, 1, 1, 1, 1, 2, 2, 2, 2, 2, 2, 2, -1, -1, 1, -2, -2, -3, 1, 1};
       int ar = arity[id];
       if ((ar > 0 && nargs != ar) || (ar == -1 && nargs < 1) || (ar == -2 && nargs < 2) || (ar == -3 && (nargs < 2 || nargs > 3)) || depth + nargs > DX_STACK)
@@ -337,12 +374,12 @@ struct DerivedCompiler {
 void read_derived(const XNode& root, const XNode& model, Builder& b) {
   std::vector<const XNode*> fields;
   if (const XNode* td = root.child("TransformationDictionary")) {
-    if (td->child("DefineFunction")) unsupported("DefineFunction");
     td->each("DerivedField", [&](const XNode& f) { fields.push_back(&f); });
   }
   if (const XNode* lt = model.child("LocalTransformations")) lt->each("DerivedField", [&](const XNode& f) { fields.push_back(&f); });
   DerivedDesc& dd = b.cm.dev.derived; dd.n_derived = (int)fields.size();
   DerivedCompiler dc(b); std::vector<int32_t> prog_off{0}; std::vector<uint8_t> dtypes;
+  if (const XNode* td = root.child("TransformationDictionary")) td->each("DefineFunction", [&](const XNode& f) { dc.fns[std::string(f.attr("name"))] = &f; });
   for (const XNode* f : fields) {
     uint8_t dt = dtype_of(f->attr("dataType", "double"));
     if (dt != DT_DOUBLE && dt != DT_FLOAT && dt != DT_INTEGER) unsupported("non-numeric DerivedField");
@@ -1282,6 +1319,7 @@ bool sg_add_layer(const double* W, const double* bias, int N, int K, SgLayer& ly
 int act_of(sv s) {
   static const char* names[] = {"threshold", "logistic", "tanh", "identity", "exponential", "reciprocal", "square", "Gauss", "sine", "cosine", "Elliott", "arctan", "rectifier"};
   for (int i = 0; i < 13; i++) if (s == names[i]) return i;
+  if (s == "radialBasis") return ACT_RADIAL;
   unsupported("activationFunction " + std::string(s));
 }
 
@@ -1324,9 +1362,16 @@ void compile_neural(const XNode& m, Builder& b) {
     if (nm != "none" && ly.norm == NORM_NONE) unsupported("layer normalizationMethod " + std::string(nm));
     ly.threshold = L.has("threshold") ? need_double(L.attr("threshold"), "threshold") : dflt_thr;
     ly.w_off = (int64_t)W.size(); ly.b_off = (int64_t)B.size();
-    std::vector<std::string> ids;
+    std::vector<std::string> ids; std::vector<double> rbf_den, rbf_alt;
     L.each("Neuron", [&](const XNode& n) {
       ids.push_back(std::string(n.attr("id"))); B.push_back(need_double(n.attr("bias", "0"), "bias"));
+      if (ly.act == ACT_RADIAL) {   // width / altitude: the Neuron's, else the layer's, else the network's
+        const XNode* src[3] = {&n, &L, &m}; double width = 0, alt = 1; bool has_w = false;
+        for (const XNode* x : src) if (!has_w && x->has("width")) { width = need_double(x->attr("width"), "width"); has_w = true; }
+        for (const XNode* x : src) if (x->has("altitude")) { alt = need_double(x->attr("altitude"), "altitude"); break; }
+        if (!has_w) unsupported("radialBasis neuron without width");
+        rbf_den.push_back(2.0 * width * width); rbf_alt.push_back((double)prev_ids.size() * std::log(alt));
+      }
       size_t i = 0;
       n.each("Con", [&](const XNode& c) {
         // the accumulation order is the Con order; only "every neuron of the previous layer, in order" is flattened
@@ -1336,6 +1381,7 @@ void compile_neural(const XNode& m, Builder& b) {
       if (i != prev_ids.size()) unsupported("NeuralNetwork that is not layer-wise fully connected in neuron order");
     });
     ly.n_out = (int)ids.size(); if (!ly.n_out) malformed("empty NeuralLayer");
+    B.insert(B.end(), rbf_den.begin(), rbf_den.end()); B.insert(B.end(), rbf_alt.begin(), rbf_alt.end());
     d.max_width = std::max(d.max_width, ly.n_out); prev_ids = ids; nl++;
   });
   if (!nl) malformed("no NeuralLayer");

@@ -303,7 +303,8 @@ static Tri eval_pred(const Predicate& p, const Ctx& cx) {
 // A value is a double or missing; booleans are 1.0 / 0.0.  Unless a function says otherwise a missing argument gives a
 // missing result (then mapMissingTo applies); a missing result with all arguments present gets defaultValue.
 struct DExpr {
-  enum Kind { CONST, FIELD, NORMCONT, NORMDISC, DISCRETIZE, MAPVALUES, APPLY } kind = CONST;
+  enum Kind { CONST, FIELD, NORMCONT, NORMDISC, DISCRETIZE, MAPVALUES, APPLY, PARAM, USERCALL } kind = CONST;
+  bool to_float = false;                                             // USERCALL: the DefineFunction's dataType is float
   double constant = 0; int slot = -1; std::string function;
   std::optional<double> map_missing, dflt;
   std::vector<std::pair<double, double>> pts; int outliers = 0;     // NORMCONT
@@ -341,6 +342,19 @@ struct DExpr {
         return fill(dflt, out);
       }
       case APPLY: return apply(cx, out);
+      // DefineFunction (JPMML FunctionUtil.evaluate(DefineFunction ...)): the body runs in a context that holds only the
+      // ParameterFields, bound to the argument values (a missing argument is a missing parameter).  Loaded by substitution:
+      // PARAM = a FieldRef to a parameter (args[0] is the argument's expression; the FieldRef's own mapMissingTo applies),
+      // USERCALL = the Apply (args = the arguments, then the body): Apply@mapMissingTo if any argument is missing, else the
+      // body's value in the function's dataType, Apply@defaultValue if that is missing.
+      case PARAM: if (args[0].eval(cx, out)) return true; return fill(map_missing, out);
+      case USERCALL: {
+        double t;
+        if (map_missing) for (size_t i = 0; i + 1 < args.size(); i++) if (!args[i].eval(cx, &t)) return fill(map_missing, out);
+        if (!args.back().eval(cx, out)) return fill(dflt, out);
+        if (to_float) *out = (double)(float)*out;
+        return true;
+      }
     }
     return false;
   }
@@ -770,7 +784,7 @@ static double activate(const std::string& f, double z, double threshold) {
 struct NeuralNetwork : Model {
   std::string activation = "logistic", normalization = "none"; double threshold = 0;
   struct Input { std::string id; Expr expr; };
-  struct Neuron { std::string id; double bias = 0; std::vector<std::pair<int, double>> con; };  // (index in id table, weight)
+  struct Neuron { std::string id; double bias = 0, width = 0, altitude = 1; std::vector<std::pair<int, double>> con; };  // (index in id table, weight)
   struct Layer { std::string activation, normalization; double threshold; std::vector<Neuron> neurons; };
   struct Output { int neuron; Expr expr; };
   std::vector<Input> inputs; std::vector<Layer> layers; std::vector<Output> outputs;
@@ -784,6 +798,14 @@ struct NeuralNetwork : Model {
     for (auto& L : layers) {
       size_t first = k;
       for (auto& n : L.neurons) {
+        if (L.activation == "radialBasis") {
+          // PMML 4.3 NeuralNetwork, radial basis function: Z = sum_i (x_i - w_i)^2 / (2 width^2),
+          // activation = exp(fanIn * ln(altitude) - Z); the bias takes no part (JPMML NeuralNetworkEvaluator, RADIAL_BASIS)
+          double z = 0;
+          for (auto& c : n.con) { double dlt = a[c.first] - c.second; z += dlt * dlt; }
+          a[k++] = std::exp((double)n.con.size() * std::log(n.altitude) - z / (2.0 * n.width * n.width));
+          continue;
+        }
         double z = n.bias;
         for (auto& c : n.con) z += c.second * a[c.first];
         a[k++] = activate(L.activation, z, L.threshold);
@@ -1008,8 +1030,18 @@ static Expr load_expr(const Xml& derived, const Doc& d) {
   throw Unsupported("unsupported DerivedField expression");
 }
 
-static DExpr load_dexpr(const Xml& e, const Doc& d) {
+// user functions of the TransformationDictionary + the parameter bindings of the call being expanded
+struct FnEnv { std::map<std::string, const Xml*> fns; const std::map<std::string, DExpr>* params = nullptr; int depth = 0; };
+
+static DExpr load_dexpr(const Xml& e, const Doc& d, const FnEnv* env = nullptr) {
   DExpr x;
+  if (env && env->params) {   // inside a DefineFunction body only the ParameterFields are visible
+    if (e.name == "FieldRef") {
+      auto it = env->params->find(e.get("field")); if (it == env->params->end()) throw Unsupported("DefineFunction body refers to a field that is not a ParameterField");
+      x.kind = DExpr::PARAM; x.args.push_back(it->second); if (auto* a = e.attr("mapMissingTo")) x.map_missing = to_d(*a, "mapMissingTo"); return x;
+    }
+    if (e.name != "Constant" && e.name != "Apply") throw Unsupported("DefineFunction body element " + e.name);
+  }
   auto opt = [&](const char* k) -> std::optional<double> { if (auto* a = e.attr(k)) return to_d(*a, k); return std::nullopt; };
   auto numeric_slot = [&](const std::string& f) { int sl = d.slot(f); DType dt = d.fields[sl].dt; if (dt == DT_STRING || dt == DT_OTHER) throw Unsupported("transformation of a non-numeric field"); return sl; };
   if (e.name == "Constant") { x.kind = DExpr::CONST; x.constant = to_d(trim(e.text), "Constant"); return x; }
@@ -1048,7 +1080,26 @@ static DExpr load_dexpr(const Xml& e, const Doc& d) {
   }
   if (e.name == "Apply") {
     x.kind = DExpr::APPLY; x.function = e.get("function"); x.map_missing = opt("mapMissingTo"); x.dflt = opt("defaultValue");
-    for (auto& k : e.kids) if (k->name != "Extension") x.args.push_back(load_dexpr(*k, d));
+    for (auto& k : e.kids) if (k->name != "Extension") x.args.push_back(load_dexpr(*k, d, env));
+    auto fn = env ? env->fns.find(x.function) : std::map<std::string, const Xml*>::const_iterator();
+    if (env && fn != env->fns.end()) {
+      const Xml& df = *fn->second;
+      if (env->depth > 8) throw Unsupported("DefineFunction calls nested deeper than 8");
+      DType fdt = parse_dtype(df.get("dataType", "double"));
+      if (fdt != DT_DOUBLE && fdt != DT_FLOAT) throw Unsupported("DefineFunction dataType other than double / float");
+      std::map<std::string, DExpr> bind; size_t i = 0; const Xml* body = nullptr;
+      for (auto& k : df.kids) {
+        if (k->name == "Extension") continue;
+        if (k->name == "ParameterField") {
+          if (k->attr("dataType") && k->get("dataType") != "double") throw Unsupported("ParameterField dataType other than double");
+          if (i >= x.args.size()) throw Unsupported("too few arguments for " + x.function);
+          bind[k->get("name")] = x.args[i++];
+        } else body = k.get();
+      }
+      if (i != x.args.size() || !body) throw Unsupported("wrong number of arguments for " + x.function);
+      FnEnv inner; inner.fns = env->fns; inner.params = &bind; inner.depth = env->depth + 1;
+      x.kind = DExpr::USERCALL; x.to_float = fdt == DT_FLOAT; x.args.push_back(load_dexpr(*body, d, &inner));
+    }
     return x;
   }
   throw Unsupported("unsupported transformation element " + e.name);
@@ -1179,6 +1230,12 @@ static std::unique_ptr<Model> load_model(const Xml& e, const Doc& d) {
       layer.threshold = L->attr("threshold") ? to_d(L->get("threshold"), "threshold") : m->threshold;
       for (auto* n : L->children("Neuron")) {
         NeuralNetwork::Neuron nn; nn.id = n->get("id"); nn.bias = to_d(n->get("bias", "0"), "bias");
+        if (layer.activation == "radialBasis") {   // width / altitude: the Neuron's, else the layer's, else the network's
+          const Xml* src[3] = {n, L, &e}; bool has_w = false;
+          for (auto* x : src) if (!has_w && x->attr("width")) { nn.width = to_d(x->get("width"), "width"); has_w = true; }
+          for (auto* x : src) if (x->attr("altitude")) { nn.altitude = to_d(x->get("altitude"), "altitude"); break; }
+          if (!has_w) throw Unsupported("radialBasis neuron without width");
+        }
         for (auto* c : n->children("Con")) { auto it = ids.find(c->get("from")); if (it == ids.end()) throw Unsupported("Con from unknown neuron"); nn.con.emplace_back(it->second, to_d(c->get("weight"), "weight")); }
         layer.neurons.push_back(nn);
       }
@@ -1342,9 +1399,9 @@ static std::unique_ptr<Loaded> load(const char* data, size_t len) {
     }
     L->doc.index[df.name] = (int)L->doc.fields.size(); L->doc.fields.push_back(df);
   }
-  std::vector<const Xml*> derived_xml;
+  std::vector<const Xml*> derived_xml; FnEnv fn_env;
   if (auto* td = root->child("TransformationDictionary")) {
-    if (td->child("DefineFunction")) throw Unsupported("DefineFunction is not supported");
+    for (auto* f : td->children("DefineFunction")) fn_env.fns[f->get("name")] = f;
     for (auto* f : td->children("DerivedField")) derived_xml.push_back(f);
   }
   const Xml* me = nullptr;
@@ -1367,7 +1424,7 @@ static std::unique_ptr<Loaded> load(const char* data, size_t len) {
     if (dt == DT_STRING || dt == DT_OTHER || dt == DT_BOOLEAN) throw Unsupported("non-numeric DerivedField");
     const Xml* ex = nullptr; for (auto& k : f->kids) if (k->name != "Extension" && k->name != "Value") { ex = k.get(); break; }
     if (!ex) throw Unsupported("DerivedField without expression");
-    DExpr expr = load_dexpr(*ex, L->doc);
+    DExpr expr = load_dexpr(*ex, L->doc, &fn_env);
     DataField df; df.name = f->get("name"); df.op = parse_optype(f->get("optype", "continuous")); df.dt = dt;
     L->doc.index[df.name] = (int)L->doc.fields.size(); L->doc.fields.push_back(df);
     L->derived.push_back({(int)L->doc.fields.size() - 1, dt, std::move(expr)});

@@ -232,11 +232,19 @@ def cases():
     # ---- derived fields (TransformationDictionary + LocalTransformations) feeding a one-predictor regression y = 1.0 * d
     fr = lambda f: f'<FieldRef field="{f}"/>'
     cst = lambda v: f'<Constant dataType="double">{v}</Constant>'
-    td = ('<TransformationDictionary>'
+    # DefineFunction: scale(x, k) = x * (k + 1) with k's own mapMissingTo inside the body; f32(v) = scale(v, 0.1) as a float
+    fns = ('<DefineFunction name="scale" optype="continuous" dataType="double"><ParameterField name="x"/><ParameterField name="k" dataType="double"/>'
+           f'<Apply function="*">{fr("x")}<Apply function="+"><FieldRef field="k" mapMissingTo="10"/>{cst(1)}</Apply></Apply></DefineFunction>'
+           '<DefineFunction name="f32" optype="continuous" dataType="float"><ParameterField name="v"/>'
+           f'<Apply function="scale">{fr("v")}{cst(0.1)}</Apply></DefineFunction>')
+    td = ('<TransformationDictionary>' + fns +
           '<DerivedField name="d1" optype="continuous" dataType="double"><NormContinuous field="a"><LinearNorm orig="0" norm="0"/><LinearNorm orig="10" norm="1"/></NormContinuous></DerivedField>'
           f'<DerivedField name="d2" optype="continuous" dataType="double"><Apply function="+">{fr("a")}{cst(2)}</Apply></DerivedField>'
           f'<DerivedField name="d3" optype="continuous" dataType="double"><Apply function="if"><Apply function="greaterThan">{fr("a")}{cst(1)}</Apply>'
           f'<Apply function="*">{fr("b")}{cst(3)}</Apply>{cst(-1)}</Apply></DerivedField>'
+          f'<DerivedField name="d7" optype="continuous" dataType="double"><Apply function="scale">{fr("a")}{fr("b")}</Apply></DerivedField>'
+          f'<DerivedField name="d8" optype="continuous" dataType="double"><Apply function="scale" mapMissingTo="-7">{fr("a")}{fr("b")}</Apply></DerivedField>'
+          f'<DerivedField name="d9" optype="continuous" dataType="double"><Apply function="f32" defaultValue="5">{fr("a")}</Apply></DerivedField>'
           '</TransformationDictionary>')
     lt = ('<LocalTransformations>'
           '<DerivedField name="d4" optype="continuous" dataType="double"><Discretize field="b" mapMissingTo="7" defaultValue="99">'
@@ -246,6 +254,7 @@ def cases():
           '<InlineTable><row><i>1</i><o>100</o></row><row><i>2</i><o>200</o></row></InlineTable></MapValues></DerivedField>'
           f'<DerivedField name="d6" optype="continuous" dataType="double"><Apply function="max" mapMissingTo="-100">{fr("d2")}{fr("d3")}</Apply></DerivedField>'
           '</LocalTransformations>')
+    f32 = lambda v: float(np.float32(v))
     def derived_doc(name):
         body = (f'<RegressionModel modelName="r" functionName="regression">{schema(["a", "b"])}{lt}'
                 f'<RegressionTable intercept="0"><NumericPredictor name="{name}" coefficient="1"/></RegressionTable></RegressionModel>')
@@ -258,11 +267,29 @@ def cases():
               "d3": [(0, 3.0, None), (0, -1.0, None), M, M, (0, -9.0, None)],
               "d4": [(0, 5.0, None), (0, 5.0, None), (0, 5.0, None), (0, 7.0, None), (0, -5.0, None)],
               "d5": [(0, 200.0, None), (0, 0.0, None), M, (0, 200.0, None), (0, 0.0, None)],
-              "d6": [(0, 4.0, None), (0, 2.5, None), (0, -100.0, None), (0, -100.0, None), (0, 22.0, None)]}
+              "d6": [(0, 4.0, None), (0, 2.5, None), (0, -100.0, None), (0, -100.0, None), (0, 22.0, None)],
+              "d7": [(0, 4.0, None), (0, 2.5, None), M, (0, 22.0, None), (0, -40.0, None)],
+              "d8": [(0, 4.0, None), (0, 2.5, None), (0, -7.0, None), (0, -7.0, None), (0, -40.0, None)],
+              "d9": [(0, f32(2 * (0.1 + 1)), None), (0, f32(0.5 * (0.1 + 1)), None), (0, 5.0, None), (0, f32(2 * (0.1 + 1)), None), (0, f32(20 * (0.1 + 1)), None)]}
     for name, exp in expect.items():
         out.append((f"derived/{name}", derived_doc(name), Xd, Pd, None, exp))
+    # ---- NeuralNetwork with a radial basis layer: h = exp(fanIn ln(altitude) - sum (x - w)^2 / (2 width^2)), no bias;
+    #      h1: centre (0,0), width 1 (network), altitude 1;  h2: centre (1,1), width 2 (neuron), altitude 2 (layer);  y = 0.5 + h1 + 2 h2
+    inp = lambda i, f: f'<NeuralInput id="i{i}"><DerivedField optype="continuous" dataType="double"><FieldRef field="{f}"/></DerivedField></NeuralInput>'
+    rbf = (f'<NeuralNetwork modelName="rbf" functionName="regression" activationFunction="radialBasis" width="1">{schema(["a", "b"])}'
+           f'<NeuralInputs numberOfInputs="2">{inp(0, "a")}{inp(1, "b")}</NeuralInputs>'
+           '<NeuralLayer numberOfNeurons="2" altitude="2">'
+           '<Neuron id="h1" bias="99" altitude="1"><Con from="i0" weight="0"/><Con from="i1" weight="0"/></Neuron>'
+           '<Neuron id="h2" width="2"><Con from="i0" weight="1"/><Con from="i1" weight="1"/></Neuron></NeuralLayer>'
+           '<NeuralLayer numberOfNeurons="1" activationFunction="identity"><Neuron id="o" bias="0.5"><Con from="h1" weight="1"/><Con from="h2" weight="2"/></Neuron></NeuralLayer>'
+           '<NeuralOutputs numberOfOutputs="1"><NeuralOutput outputNeuron="o"><DerivedField optype="continuous" dataType="double"><FieldRef field="y"/></DerivedField></NeuralOutput></NeuralOutputs>'
+           '</NeuralNetwork>')
+    Xn_, Pn_ = _rows((0, 0), (1, 1), (2, 0), (None, 1))
+    out.append(("neural/radialBasis", doc(AB, rbf), Xn_, Pn_, None,
+                [(0, 0.5 + 1.0 + 8.0 * math.exp(-0.25), None), (0, 0.5 + math.exp(-1.0) + 8.0, None),
+                 (0, 0.5 + math.exp(-2.0) + 8.0 * math.exp(-0.25), None), (3, None, None)]))
     return out
 
 
 # cases whose expected scores go through exp(): compared with a relative tolerance instead of bit-exactly
-TOLERANT = {"greg/link-log": 1e-12, "greg/link-logit-offset": 1e-12}
+TOLERANT = {"greg/link-log": 1e-12, "greg/link-logit-offset": 1e-12, "neural/radialBasis": 1e-12}

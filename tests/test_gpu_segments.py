@@ -94,3 +94,18 @@ def test_classification_segments_with_predicates(engine, oracle, gen, method):
     same(r, o, method, aux=method == "selectFirst")          # aggregated votes: aux is the winner's index, not compared here
     assert np.array_equal(r["node_ids"], o["node_ids"]), method
     assert len(np.unique(o["score"][o["status"] == 0])) >= 3
+
+
+def test_radial_basis_layer(engine, oracle, gen):
+    """NeuralNetwork with a radialBasis hidden layer (width / altitude at network level) against the oracle: labels
+    bit-exact, probabilities within 1e-6 relative (the tolerance north_star states for floating point)."""
+    pm, _ = gen.nn_pmml(n_in=16, hidden=(32,), n_out=4, seed=911, activation="radialBasis")
+    pm = pm.replace(b'activationFunction="radialBasis">', b'activationFunction="radialBasis" width="3.0" altitude="1.01">', 1)
+    m, om = engine.compile(pm), oracle.OracleModel(pm)
+    X, pres, pb = gen.events(20000, 16, 912, 0.01)
+    o = om.predict(X, pb, n_probs=4, nthreads=8); r = engine.score(m, X, pb, n_probs=4)
+    assert np.array_equal(r["status"], o["status"]) and (o["status"] == 0).sum() > 15000 and (o["status"] == 3).sum() > 100
+    ok = o["status"] == 0
+    assert np.array_equal(r["score"][ok], o["score"][ok])
+    np.testing.assert_allclose(r["probs"][ok], o["probs"][ok], rtol=1e-6)
+    assert len(np.unique(o["score"][ok])) >= 2
