@@ -447,9 +447,20 @@ def main():
                     fn.close()
                 return sum(emitted) / dt, sum(emitted)
             r1, e1 = drive(1); r4, e4 = drive(4)
-            operator = {"fixed_model_C4_1_task_thread": {"events_per_s": r1, "emitted": e1}, "fixed_model_C4_4_task_threads_one_engine": {"events_per_s": r4, "emitted": e4},
-                        "max_batch": 16384, "api": "fjh_eval_function_process_dense -> pinned micro-batches -> fjp_submit / fjp_wait (EvaluationFunction mirror, S/api/functions/EvaluationFunction.scala:39-50)",
-                        "note": "one task thread copies every 800-byte event into a pinned micro-batch: the rate is the host core's copy bandwidth, not the GPU's"}
+            import importlib.util
+            spec = importlib.util.spec_from_file_location("bench_operators", os.path.join(os.path.dirname(os.path.abspath(__file__)), "tools", "bench_operators.py"))
+            bo = importlib.util.module_from_spec(spec); spec.loader.exec_module(bo)
+            core = bo.one_core_copy(F=F)
+            names5, files5 = bo.c5_models(d)
+            dyn_swaps = bo.c5_dynamic(eng, names5, files5, 0.050, passes=2)
+            dyn_quiet = bo.c5_dynamic(eng, names5, files5, 1e9, passes=2)
+            operator = {"fixed_model_C4_1_task_thread": {"events_per_s": r1, "emitted": e1, "frac_of_one_core_copy": r1 / core["events_per_s"]},
+                        "fixed_model_C4_4_task_threads_one_engine": {"events_per_s": r4, "emitted": e4},
+                        "one_core_copy_into_pinned": core,
+                        "dynamic_C5_32_ids_hot_swap_every_50ms": dyn_swaps, "dynamic_C5_32_ids_no_control_traffic": dyn_quiet,
+                        "max_batch": 16384, "api": "fjh_eval_function_process_dense / fjh_cofunction_process_dense -> pinned micro-batches -> fjp_submit / fjp_wait (EvaluationFunction / EvaluationCoFunction mirrors, S/api/functions/EvaluationFunction.scala:39-50, EvaluationCoFunction.scala:55-133)",
+                        "note": "one task thread copies every 800-byte event into a pinned micro-batch: the rate is the host core's copy bandwidth (one_core_copy_into_pinned), not the GPU's; "
+                                "events for a model whose background load is still running are parked and scored when it finishes, the other models' events keep flowing"}
         except Exception as ex:          # noqa: BLE001
             operator = {"error": repr(ex)}
 

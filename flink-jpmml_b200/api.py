@@ -95,6 +95,8 @@ def _lib():
         "fjh_eval_function_model_name": (cp, [vp]),
         "fjh_eval_function_process": (i32, [vp, vp, i32, vp, i32, dbl]),
         "fjh_eval_function_process_dense": (i32, [vp, vp, lng, i32]),
+        "fjh_eval_function_reserve": (vp, [vp, i32, i32, C.POINTER(i32)]),
+        "fjh_eval_function_commit": (i32, [vp, i32]),
         "fjh_eval_function_flush": (i32, [vp]),
         "fjh_eval_function_poll": (lng, [vp, vp, vp, lng]),
         "fjh_eval_function_close": (None, [vp]),
@@ -108,6 +110,7 @@ def _lib():
         "fjh_cofunction_restore": (i32, [vp, C.POINTER(cp), i32]),
         "fjh_cofunction_metadata_size": (i32, [vp]),
         "fjh_cofunction_cached_models": (i32, [vp]),
+        "fjh_cofunction_parked_events": (lng, [vp]),
         "fjh_cofunction_destroy": (None, [vp]),
     }
     for name, (res, args) in sig.items():
@@ -118,10 +121,10 @@ def _lib():
 
 
 HOST_EXPORTS = ["fjh_model_id_parse", "fjh_model_id_hash", "fjh_predict", "fjh_eval_function_open", "fjh_eval_function_model_name",
-                "fjh_eval_function_process", "fjh_eval_function_process_dense", "fjh_eval_function_flush", "fjh_eval_function_poll", "fjh_eval_function_close",
+                "fjh_eval_function_process", "fjh_eval_function_process_dense", "fjh_eval_function_reserve", "fjh_eval_function_commit", "fjh_eval_function_flush", "fjh_eval_function_poll", "fjh_eval_function_close",
                 "fjh_cofunction_create", "fjh_cofunction_process_event", "fjh_cofunction_process_dense", "fjh_cofunction_process_control", "fjh_cofunction_flush",
                 "fjh_cofunction_poll", "fjh_cofunction_snapshot", "fjh_cofunction_restore", "fjh_cofunction_metadata_size",
-                "fjh_cofunction_cached_models", "fjh_cofunction_destroy"]
+                "fjh_cofunction_cached_models", "fjh_cofunction_parked_events", "fjh_cofunction_destroy"]
 
 
 def _raise(rc, err=b""):
@@ -248,6 +251,18 @@ class EvaluationFunction:
         X = np.ascontiguousarray(X, dtype=np.float64)
         _raise(_lib().fjh_eval_function_process_dense(self._h, capi._ptr(X), X.shape[0], X.shape[1]))
 
+    def reserve(self, size: int, want_rows: int):
+        """Rows of the pinned micro-batch the producer may fill itself: a writable (granted, size) array, or None when `size`
+        is not the model's field count.  commit(rows) declares how many were written."""
+        granted = C.c_int(0)
+        p = _lib().fjh_eval_function_reserve(self._h, size, want_rows, C.byref(granted))
+        if not p or granted.value <= 0:
+            return None
+        return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_double)), shape=(granted.value, size))
+
+    def commit(self, rows: int):
+        _raise(_lib().fjh_eval_function_commit(self._h, rows))
+
     def flush(self):
         _raise(_lib().fjh_eval_function_flush(self._h))
 
@@ -318,6 +333,11 @@ class EvaluationCoFunction:
     @property
     def servingModels(self) -> int:
         return _lib().fjh_cofunction_cached_models(self._h)
+
+    @property
+    def parkedEvents(self) -> int:
+        """Events the bulk path parked behind a model load that was still running (they keep their output position)."""
+        return _lib().fjh_cofunction_parked_events(self._h)
 
     def close(self):
         if self._h:

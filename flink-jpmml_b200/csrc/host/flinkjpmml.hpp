@@ -124,13 +124,18 @@ class PmmlModel {
 // of them; one heap object or one vector shuffle per event would cost more than scoring it).
 class PredictionQueue {
  public:
+  static constexpr uint8_t kOpen = 0xFF;   // placeholder: the prediction is still being computed; nothing behind it is handed out
   void push(uint8_t status, double score) { status_.push_back(status); score_.push_back(score); }
-  size_t size() const { return status_.size() - head_; }
+  size_t reserve() { status_.push_back(kOpen); score_.push_back(0); open_++; return status_.size() - 1; }   // stays valid until filled
+  void fill(size_t slot, uint8_t status, double score) { status_[slot] = status; score_[slot] = score; open_--; }
+  // predictions that can be emitted now: everything up to the first placeholder
+  size_t size() const { return ready_end() - head_; }
   // copies up to `cap` predictions out (score NaN for an empty one); returns how many
   long pop(double* scores, uint8_t* status, long cap);
   std::vector<Prediction> drain();
  private:
-  std::vector<double> score_; std::vector<uint8_t> status_; size_t head_ = 0;
+  size_t ready_end() const;
+  std::vector<double> score_; std::vector<uint8_t> status_; size_t head_ = 0, open_ = 0;
 };
 
 // ---------------------------------------------------------------------------------------- micro-batch buffer
@@ -147,6 +152,8 @@ class MicroBatch {
   int append(const Vector& v, std::optional<double> replaceNan);   // returns the row index
   int append_dense(const double* x);                                // DenseVector payload, no replaceNan
   int append_dense_block(const double* X, int rows);                // `rows` DenseVector payloads, contiguous: one copy; returns the first row index
+  double* tail() { return X_ + (size_t)n_ * F_; }                   // where the next row goes: a producer may write room() rows there itself ...
+  int commit_rows(int rows);                                        // ... and then declare them (dense, no replaceNan); returns the first row index
   void clear() { n_ = 0; any_sparse_ = false; any_replace_ = false; }
   int room() const { return cap_ - n_; }
   int score(fjp_engine* e, fjp_model* m);                         // fills score()/status()
@@ -175,6 +182,10 @@ class EvaluationFunction {
   std::vector<Prediction> drain() { return out_.drain(); }
   long poll(double* scores, uint8_t* status, long cap) { return out_.pop(scores, status, cap); }
   void processDenseBlock(const double* X, long n, int size);   // n DenseVector payloads in arrival order
+  // The same without the operator's copy: the producer (a JNI shim holding a Java double[]) writes up to *granted DenseVector
+  // payloads straight into the pinned micro-batch and commits them; nothing else may be called on the operator in between.
+  double* reserve(int size, int want_rows, int* granted);      // nullptr: `size` is not the model's field count (use processDense)
+  void commit(int rows);
   void close() { flush(); }
  private:
   // two pinned micro-batches: while the GPU scores one, the task thread packs the other (fjp_submit / fjp_wait)
@@ -197,14 +208,16 @@ class EvaluationCoFunction {
   // n dense events in arrival order, event i addressed to ids[id_index[i]]; ids are resolved once per call and flush
   void processDenseBatch(const char* const* ids, const int32_t* id_index, const double* X, long n, int size);
   void processElement2(const ServingMessage& control);           // manageModels then manageMetadata (:69-74)
-  void flush();
+  void flush();                                                   // every buffered event scored and ready to poll (waits for parked ones)
   std::vector<Prediction> drain() { return out_.drain(); }
   long poll(double* scores, uint8_t* status, long cap) { return out_.pop(scores, status, cap); }
   PmmlModel fromMetadata(const std::string& modelId);            // (:106-117)
   PmmlModel loadModel(const std::string& path);                  // (:98-104)
   const Metadata& servingMetadata() const { return metadata_; }
   int servingModels() const { return engine_ ? fjp_table_size(engine_) : 0; }
+  long parkedEvents() const { return parked_events_; }
  private:
+  long parked_events_ = 0;
   struct Pending { int bucket; int row; };
   struct Bucket { PmmlModel model; std::unique_ptr<MicroBatch> batch; };
   fjp_engine* engine_; int max_batch_; Metadata metadata_;
@@ -215,6 +228,21 @@ class EvaluationCoFunction {
   // Add starts the model load in the background; its outcome (model or ModelLoadingException) is consumed by the first
   // event for that id, which is where the reference loads -- and fails -- too (T/RichConnectedStreamSpec.scala:288-300)
   std::map<ModelId, std::shared_future<PmmlModel>> loading_;
+  // Bulk ingest (processDenseBatch) does not stop the stream for a model that is still loading: its events are PARKED -- rows in
+  // pinned micro-batches of their own, a placeholder keeping their place in the output order -- and scored as soon as the load
+  // has finished, while events of the other models keep flowing.  The single-event calls keep the reference's behaviour to the
+  // letter (the first event waits for the load and is where a ModelLoadingException surfaces); for parked events the exception
+  // surfaces from the next call that settles them (a later processDenseBatch, flush or snapshotState): job-fatal either way.
+  struct Parked {
+    ModelId id; std::shared_future<PmmlModel> fut; int size; bool detached = false;   // detached: the id was deleted meanwhile -- score, but do not cache
+    std::vector<std::unique_ptr<MicroBatch>> batches; std::vector<size_t> slots;       // slots[i]: output position of the i-th parked row
+  };
+  std::vector<std::unique_ptr<Parked>> parked_;
+  static constexpr int kMaxParkedBatches = 8;
+  int park_index(const std::string& modelId, int size);   // >= 0: the events of this id are parked there right now
+  void settle(Parked& p);                                 // load finished: score the parked rows, fill their placeholders
+  void flush_buckets(bool wait_for_parked);
+  std::unique_ptr<MicroBatch> take_batch(int fields);
   int bucket_for(const PmmlModel& m);
   PmmlModel resolve(const std::string& modelId);   // servingModels.getOrElse(id.hashCode, fromMetadata(id))
   void enqueue(const PmmlModel& model, const Vector* v, const double* dense, int size, std::optional<double> replaceNan);

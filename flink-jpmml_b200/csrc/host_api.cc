@@ -1,6 +1,7 @@
 // host_api.cc -- implementation of host/flinkjpmml.hpp and the extern "C" operator-emulator entry points declared in
 // include/fjpmml_host.h (what pytest drives in place of a Flink mini-cluster; T/utils/FlinkTestKits.scala:32-67).
 #include <algorithm>
+#include <chrono>
 #include <cstring>
 #include <fstream>
 #include <limits>
@@ -126,6 +127,18 @@ int MicroBatch::append_dense_block(const double* X, int rows) {
   return r;
 }
 
+int MicroBatch::commit_rows(int rows) {
+  const int r = n_; n_ += rows;
+  if (any_sparse_) memset(present_ + (size_t)r * W_, 0xFF, (size_t)rows * W_ * 4);
+  if (any_replace_) for (int k = 0; k < rows; k++) replace_[r + k] = std::numeric_limits<double>::quiet_NaN();
+  return r;
+}
+
+size_t PredictionQueue::ready_end() const {
+  if (!open_) return status_.size();
+  const void* f = memchr(status_.data() + head_, kOpen, status_.size() - head_);
+  return f ? (size_t)(static_cast<const uint8_t*>(f) - status_.data()) : status_.size();
+}
 long PredictionQueue::pop(double* scores, uint8_t* status, long cap) {
   const long n = std::min<long>(cap, (long)size());
   for (long i = 0; i < n; i++) { const uint8_t st = status_[head_ + i]; status[i] = st; scores[i] = st == FJP_ST_SCORE ? score_[head_ + i] : std::numeric_limits<double>::quiet_NaN(); }
@@ -134,9 +147,11 @@ long PredictionQueue::pop(double* scores, uint8_t* status, long cap) {
   return n;
 }
 std::vector<Prediction> PredictionQueue::drain() {
-  std::vector<Prediction> r; r.reserve(size());
-  for (size_t i = head_; i < status_.size(); i++) { Prediction p; p.status = status_[i]; if (p.status == FJP_ST_SCORE) p.value = Target::score(score_[i]); r.push_back(p); }
-  status_.clear(); score_.clear(); head_ = 0;
+  const size_t end = ready_end();
+  std::vector<Prediction> r; r.reserve(end - head_);
+  for (size_t i = head_; i < end; i++) { Prediction p; p.status = status_[i]; if (p.status == FJP_ST_SCORE) p.value = Target::score(score_[i]); r.push_back(p); }
+  head_ = end;
+  if (head_ == status_.size()) { status_.clear(); score_.clear(); head_ = 0; }
   return r;
 }
 int MicroBatch::submit(fjp_engine* e, fjp_model* m, int* ticket) {
@@ -188,6 +203,20 @@ void EvaluationFunction::processDenseBlock(const double* X, long n, int size) {
     if (batch_[cur_]->full() || (int)pending_[cur_].size() >= max_batch_) submit_current();
   }
 }
+double* EvaluationFunction::reserve(int size, int want_rows, int* granted) {
+  if (model_.isEmpty()) open();
+  *granted = 0;
+  if (size != model_.activeFields() || want_rows <= 0) return nullptr;
+  *granted = std::min(want_rows, std::min(batch_[cur_]->room(), max_batch_ - (int)pending_[cur_].size()));
+  return batch_[cur_]->tail();
+}
+void EvaluationFunction::commit(int rows) {
+  if (rows <= 0) return;
+  const int r0 = batch_[cur_]->commit_rows(rows);
+  const size_t p0 = pending_[cur_].size(); pending_[cur_].resize(p0 + rows);
+  for (int k = 0; k < rows; k++) pending_[cur_][p0 + k] = r0 + k;
+  if (batch_[cur_]->full() || (int)pending_[cur_].size() >= max_batch_) submit_current();
+}
 void EvaluationFunction::collect(int b) {
   if (ticket_[b] >= 0) { if (fjp_wait(engine_, ticket_[b]) != 0) throw std::runtime_error(fjp_last_error()); ticket_[b] = -1; }
   const double* sc = batch_[b]->scores(); const uint8_t* st = batch_[b]->statuses();
@@ -224,6 +253,11 @@ PmmlModel EvaluationCoFunction::fromMetadata(const std::string& modelId) {
   ModelId id = ModelId::fromIdentifier(modelId);                       // WrongModelIdFormat is not caught: job-fatal
   auto it = metadata_.find(id);
   if (it == metadata_.end()) return PmmlModel::empty();
+  for (auto& p : parked_) if (!p->detached && p->id == id) {   // the bulk path parked events on this load: settle them, the model is cached then
+    flush_buckets(true);
+    if (fjp_model* cached = fjp_table_get(engine_, id.name.c_str(), id.version)) return PmmlModel(engine_, cached);
+    break;
+  }
   PmmlModel loaded;
   auto lf = loading_.find(id);
   if (lf != loading_.end()) { auto fut = lf->second; loading_.erase(lf); loaded = fut.get(); }   // background load started by the Add (rethrows its failure)
@@ -232,14 +266,51 @@ PmmlModel EvaluationCoFunction::fromMetadata(const std::string& modelId) {
   return loaded;
 }
 
+std::unique_ptr<MicroBatch> EvaluationCoFunction::take_batch(int fields) {
+  for (size_t i = 0; i < pool_.size(); i++)
+    if (pool_[i]->fields() == fields && pool_[i]->capacity() == max_batch_) { auto mb = std::move(pool_[i]); pool_.erase(pool_.begin() + i); return mb; }
+  return std::make_unique<MicroBatch>(fields, max_batch_);
+}
 int EvaluationCoFunction::bucket_for(const PmmlModel& m) {
   for (size_t i = 0; i < buckets_.size(); i++) if (buckets_[i].model.handle() == m.handle()) return (int)i;
-  std::unique_ptr<MicroBatch> mb;
-  for (size_t i = 0; i < pool_.size(); i++)
-    if (pool_[i]->fields() == m.activeFields() && pool_[i]->capacity() == max_batch_) { mb = std::move(pool_[i]); pool_.erase(pool_.begin() + i); break; }
-  if (!mb) mb = std::make_unique<MicroBatch>(m.activeFields(), max_batch_);
-  buckets_.push_back(Bucket{m, std::move(mb)});
+  buckets_.push_back(Bucket{m, take_batch(m.activeFields())});
   return (int)buckets_.size() - 1;
+}
+
+// Where the events of `modelId` go while its model is still loading in the background (bulk path only): the index of its Parked
+// record, created on the first such event; -1 = not parked (bound already, unknown id, load finished, or no background load).
+int EvaluationCoFunction::park_index(const std::string& modelId, int size) {
+  if (parked_.empty() && loading_.empty()) return -1;
+  if (fjp_table_epoch(engine_) == resolved_epoch_ && resolved_.count(modelId)) return -1;
+  const ModelId id = ModelId::fromIdentifier(modelId);
+  auto ready = [](const std::shared_future<PmmlModel>& f) { return f.wait_for(std::chrono::seconds(0)) == std::future_status::ready; };
+  for (size_t i = 0; i < parked_.size(); i++) {
+    Parked& p = *parked_[i];
+    if (p.detached || !(p.id == id)) continue;
+    const bool over = (int)p.batches.size() >= kMaxParkedBatches && p.batches.back()->full();
+    if (ready(p.fut) || p.size != size || over) { flush_buckets(p.size != size || over); return -1; }   // settles it (waiting only when it has to)
+    return (int)i;
+  }
+  auto lf = loading_.find(id);
+  if (lf == loading_.end() || !metadata_.count(id) || ready(lf->second)) return -1;   // ready: the usual path picks it up without waiting
+  auto p = std::make_unique<Parked>(); p->id = id; p->fut = lf->second; p->size = size;
+  loading_.erase(lf);
+  parked_.push_back(std::move(p));
+  return (int)parked_.size() - 1;
+}
+
+void EvaluationCoFunction::settle(Parked& p) {
+  PmmlModel loaded = p.fut.get();   // rethrows the load's ModelLoadingException: job-fatal, as on the first event in the reference
+  if (!p.detached && metadata_.count(p.id)) { fjp_table_add(engine_, p.id.name.c_str(), p.id.version, loaded.handle()); }
+  const bool size_ok = p.size == loaded.activeFields();
+  size_t s = 0;
+  for (auto& mb : p.batches) {
+    if (size_ok && mb->score(engine_, loaded.handle()) != 0) throw std::runtime_error(fjp_last_error());
+    const int n = mb->size();
+    for (int r = 0; r < n; r++, s++) { if (size_ok) out_.fill(p.slots[s], mb->statuses()[r], mb->scores()[r]); else out_.fill(p.slots[s], FJP_ST_SIZE, 0); }
+    mb->clear(); if (pool_.size() < 64) pool_.push_back(std::move(mb));
+  }
+  p.batches.clear(); p.slots.clear();
 }
 
 PmmlModel EvaluationCoFunction::resolve(const std::string& modelId) {
@@ -265,9 +336,9 @@ void EvaluationCoFunction::enqueue(const PmmlModel& model, const Vector* v, cons
     int b = bucket_for(model);
     int row = v ? buckets_[b].batch->append(*v, replaceNan) : buckets_[b].batch->append_dense(dense);
     pending_.push_back({b, row});
-    if (buckets_[b].batch->full()) flush();
+    if (buckets_[b].batch->full()) flush_buckets(false);
   }
-  if ((int)pending_.size() >= max_batch_) flush();
+  if ((int)pending_.size() >= max_batch_) flush_buckets(false);
 }
 
 void EvaluationCoFunction::processElement1(const std::string& modelId, const Vector& v, std::optional<double> replaceNan) {
@@ -287,16 +358,31 @@ void EvaluationCoFunction::processDenseBatch(const char* const* ids, const int32
     if (seen_flush != flushes_) { std::fill(where.begin(), where.end(), -3); seen_flush = flushes_; }   // a flush dropped the buckets
     int w = where[k];
     if (w == -3) {
-      PmmlModel model = resolve(ids[k]);
-      w = model.isEmpty() ? -1 : (size != model.activeFields() ? -2 : bucket_for(model));
+      const uint64_t before = flushes_;
+      const int parked = park_index(ids[k], size);
+      if (before != flushes_) { std::fill(where.begin(), where.end(), -3); seen_flush = flushes_; }   // park_index settled a finished load
+      if (parked >= 0) w = -4 - parked;
+      else {
+        PmmlModel model = resolve(ids[k]);
+        w = model.isEmpty() ? -1 : (size != model.activeFields() ? -2 : bucket_for(model));
+      }
       where[k] = w;
     }
-    if (w < 0) pending_.push_back({-1, w == -1 ? FJP_ST_NOMODEL : FJP_ST_SIZE});
+    if (w <= -4) {   // the model is still loading: park the row, keep its place in the output order
+      Parked& p = *parked_[-4 - w];
+      if (p.batches.empty() || p.batches.back()->full()) {
+        if ((int)p.batches.size() >= kMaxParkedBatches) { where[k] = -3; i--; continue; }   // too much parked: look again (park_index waits for the load)
+        p.batches.push_back(take_batch(size));
+      }
+      p.batches.back()->append_dense(X + i * (long)size); parked_events_++;
+      pending_.push_back({-2 - (-4 - w), 0});
+    }
+    else if (w < 0) pending_.push_back({-1, w == -1 ? FJP_ST_NOMODEL : FJP_ST_SIZE});
     else {
       pending_.push_back({w, buckets_[w].batch->append_dense(X + i * (long)size)});
-      if (buckets_[w].batch->full()) flush();
+      if (buckets_[w].batch->full()) flush_buckets(false);
     }
-    if ((int)pending_.size() >= max_batch_) flush();
+    if ((int)pending_.size() >= max_batch_) flush_buckets(false);
   }
 }
 
@@ -306,7 +392,10 @@ void EvaluationCoFunction::processElement2(const ServingMessage& control) {
   const bool known = metadata_.count(control.modelId()) != 0;
   metadata_ = MetadataManager::apply(control, metadata_);
   resolved_.clear();   // bindings are looked up again after any control message
-  if (control.kind == ServingMessage::Del) loading_.erase(control.modelId());
+  if (control.kind == ServingMessage::Del) {
+    loading_.erase(control.modelId());
+    for (auto& p : parked_) if (p->id == control.modelId()) p->detached = true;   // its parked events are still scored; the model is not cached
+  }
   else if (!known && engine_) {   // a new id: parse + compile + upload off the task thread
     fjp_engine* eng = engine_; std::string path = control.path;
     loading_[control.modelId()] = std::async(std::launch::async, [eng, path] { return PmmlModel::fromReader(eng, ModelReader(path)); }).share();
@@ -314,8 +403,18 @@ void EvaluationCoFunction::processElement2(const ServingMessage& control) {
   // buffered events keep the model they were bound to (each bucket holds a reference), so nothing is flushed here
 }
 
-void EvaluationCoFunction::flush() {
-  if (pending_.empty()) return;
+void EvaluationCoFunction::flush() { flush_buckets(true); }
+
+void EvaluationCoFunction::flush_buckets(bool wait_for_parked) {
+  auto settle_parked = [&] {
+    for (size_t i = 0; i < parked_.size();) {
+      Parked& p = *parked_[i];
+      if (!wait_for_parked && p.fut.wait_for(std::chrono::seconds(0)) != std::future_status::ready) { i++; continue; }
+      std::unique_ptr<Parked> done = std::move(parked_[i]); parked_.erase(parked_.begin() + i);   // out of the list first: settle may throw
+      settle(*done);
+    }
+  };
+  if (pending_.empty()) { if (!parked_.empty()) { settle_parked(); flushes_++; } return; }
   // every model's bucket is its own submission; up to fjp_max_inflight() of them overlap on the GPU
   std::vector<int> tickets; const int maxfly = fjp_max_inflight(); size_t waited = 0;
   for (auto& b : buckets_) {
@@ -331,10 +430,12 @@ void EvaluationCoFunction::flush() {
   }
   for (; waited < tickets.size(); waited++) if (fjp_wait(engine_, tickets[waited]) != 0) throw std::runtime_error(fjp_last_error());
   for (auto& p : pending_) {
-    if (p.bucket < 0) out_.push((uint8_t)p.row, 0);
+    if (p.bucket <= -2) parked_[-2 - p.bucket]->slots.push_back(out_.reserve());
+    else if (p.bucket < 0) out_.push((uint8_t)p.row, 0);
     else out_.push(buckets_[p.bucket].batch->statuses()[p.row], buckets_[p.bucket].batch->scores()[p.row]);
   }
   pending_.clear(); flushes_++;
+  settle_parked();   // nothing refers to parked_ by index any more
   for (auto& b : buckets_) { b.batch->clear(); if (pool_.size() < 64) pool_.push_back(std::move(b.batch)); }
   buckets_.clear();   // dropping the buckets releases models deleted in the meantime
 }
@@ -390,6 +491,13 @@ int fjh_eval_function_process(fjh_eval_function* h, const double* values, int si
 int fjh_eval_function_process_dense(fjh_eval_function* h, const double* X, long n, int size) {
   return guarded(nullptr, 0, [&] { h->op->processDenseBlock(X, n, size); });
 }
+double* fjh_eval_function_reserve(fjh_eval_function* h, int size, int want_rows, int* granted_rows) {
+  double* p = nullptr; int g = 0;
+  if (guarded(nullptr, 0, [&] { p = h->op->reserve(size, want_rows, &g); }) != FJH_OK) { p = nullptr; g = 0; }
+  if (granted_rows) *granted_rows = g;
+  return p;
+}
+int fjh_eval_function_commit(fjh_eval_function* h, int rows) { return guarded(nullptr, 0, [&] { h->op->commit(rows); }); }
 int fjh_eval_function_flush(fjh_eval_function* h) { return guarded(nullptr, 0, [&] { h->op->flush(); }); }
 long fjh_eval_function_poll(fjh_eval_function* h, double* scores, uint8_t* status, long cap) {
   return h->op->poll(scores, status, cap);
@@ -435,6 +543,7 @@ int fjh_cofunction_restore(fjh_cofunction* h, const char* const* snapshots, int 
 }
 int fjh_cofunction_metadata_size(fjh_cofunction* h) { return (int)h->op->servingMetadata().size(); }
 int fjh_cofunction_cached_models(fjh_cofunction* h) { return h->op->servingModels(); }
+long fjh_cofunction_parked_events(fjh_cofunction* h) { return h->op->parkedEvents(); }
 void fjh_cofunction_destroy(fjh_cofunction* h) { delete h; }
 
 }  // extern "C"

@@ -42,6 +42,13 @@ const char* fjh_eval_function_model_name(fjh_eval_function* op);
 int fjh_eval_function_process(fjh_eval_function* op, const double* values, int size, const int* indices, int nnz, double replace_nan);
 /* n DenseVector events of `size` values each, in arrival order (the task thread's inner loop without per-event FFI). */
 int fjh_eval_function_process_dense(fjh_eval_function* op, const double* X, long n, int size);
+/* The same without the operator's copy (one host core moves about 12 GB/s, which is what bounds process_dense): the caller
+ * -- a JNI shim holding the event's double[] -- writes up to *granted_rows DenseVector payloads of `size` doubles each
+ * straight into the pinned micro-batch at the returned address (GetDoubleArrayRegion into it) and commits how many it
+ * wrote.  NULL (granted 0): `size` is not the model's field count, fall back to fjh_eval_function_process (EmptyScore,
+ * S/api/PmmlModel.scala:136-141).  No other call on the operator between reserve and commit. */
+double* fjh_eval_function_reserve(fjh_eval_function* op, int size, int want_rows, int* granted_rows);
+int fjh_eval_function_commit(fjh_eval_function* op, int rows);
 int fjh_eval_function_flush(fjh_eval_function* op);
 long fjh_eval_function_poll(fjh_eval_function* op, double* scores, uint8_t* status, long cap);
 void fjh_eval_function_close(fjh_eval_function* op);
@@ -59,7 +66,12 @@ void fjh_eval_function_close(fjh_eval_function* op);
 fjh_cofunction* fjh_cofunction_create(fjp_engine* e, int max_batch);
 int fjh_cofunction_process_event(fjh_cofunction* op, const char* model_id, const double* values, int size, const int* indices, int nnz,
                                  double replace_nan, char* err, size_t errcap);
-/* n DenseVector events in arrival order; event i carries the model id string ids[id_index[i]]. */
+/* n DenseVector events in arrival order; event i carries the model id string ids[id_index[i]].
+ * Unlike process_event, this call does not stop the stream for a model whose background load (started by the Add) has not
+ * finished: such events are parked, keep their place in the output order (poll hands out predictions only up to the first
+ * of them) and are scored when the load completes; a failed load surfaces as FJH_MODEL_LOADING from the call that settles
+ * them (a later process_dense, flush or snapshot) -- job-fatal like the reference's first-event failure
+ * (T/RichConnectedStreamSpec.scala:288-300). */
 int fjh_cofunction_process_dense(fjh_cofunction* op, const char* const* ids, const int32_t* id_index, const double* X, long n, int size,
                                  char* err, size_t errcap);
 int fjh_cofunction_process_control(fjh_cofunction* op, int is_add, const char* name, int64_t version, const char* path, int64_t occurred_on);
@@ -69,6 +81,7 @@ long fjh_cofunction_snapshot(fjh_cofunction* op, char* buf, long cap);
 int fjh_cofunction_restore(fjh_cofunction* op, const char* const* snapshots, int n_snapshots);
 int fjh_cofunction_metadata_size(fjh_cofunction* op);
 int fjh_cofunction_cached_models(fjh_cofunction* op);
+long fjh_cofunction_parked_events(fjh_cofunction* op);   /* events that were parked behind a model load so far (statistic) */
 void fjh_cofunction_destroy(fjh_cofunction* op);
 
 #ifdef __cplusplus

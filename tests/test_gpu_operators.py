@@ -239,6 +239,79 @@ def test_dynamic_operator_bulk_ingest(engine, gen, oracle, tmp_path):
     for n in names: engine.table_del(n, 1)
 
 
+def test_producer_writes_rows_into_the_pinned_batch_itself(engine, gen, oracle, tmp_path):
+    """reserve / commit: the producer fills the micro-batch in place (no operator-side copy); mixed with ordinary events and a
+    wrong-size event the output order and values are those of processElement."""
+    pm = gen.gbt_pmml(T=20, depth=4, F=12, seed=70)[0]
+    p = tmp_path / "g.pmml"; p.write_bytes(pm)
+    om = oracle.OracleModel(pm)
+    rng = np.random.default_rng(3); X = rng.standard_normal((3000, 12))
+    fn = api.EvaluationFunction(engine, str(p), max_batch=256)
+    assert fn.reserve(5, 10) is None                                  # not the model's field count
+    def produce(lo, hi):                                              # grants stop at the batch boundary
+        while lo < hi:
+            rows = fn.reserve(12, hi - lo)
+            assert rows is not None and 0 < rows.shape[0] <= 256
+            rows[:] = X[lo:lo + rows.shape[0]]; fn.commit(rows.shape[0]); lo += rows.shape[0]
+    produce(0, 1000)
+    fn.processElement(api.DenseVector(X[1000]))
+    fn.processElement(api.DenseVector([1.0, 2.0]))                    # wrong size: EmptyScore, in place
+    produce(1001, 1101)
+    fn.processDense(X[1101:])
+    fn.flush()
+    out = fn.collect(); fn.close()
+    r = om.predict(X)
+    exp = [api.Prediction.of(r["score"][i], r["status"][i]) for i in range(3000)]
+    assert out == exp[:1001] + [EMPTY] + exp[1001:]
+
+
+def test_bulk_ingest_parks_events_behind_a_running_model_load(engine, gen, oracle, tmp_path):
+    """Hot swap without stopping the stream: Add starts the load in the background; bulk events for that id that arrive
+    before it has finished are parked (they keep their output position), the other models' events are scored meanwhile.
+    Order and values must be what a blocking load would have produced; a Del while parked does not resurrect the model."""
+    small = gen.rf_pmml(T=10, depth=4, F=64, n_labels=3, seed=60)[0]
+    big = gen.rf_pmml(seed=61)[0]                                  # 200 trees x depth 8: tens of ms to parse and compile
+    ps, pb_ = tmp_path / "small.pmml", tmp_path / "big.pmml"; ps.write_bytes(small); pb_.write_bytes(big)
+    ns, nb = str(uuid.UUID(int=600)), str(uuid.UUID(int=601))
+    oms, omb = oracle.OracleModel(small), oracle.OracleModel(big)
+    rng = np.random.default_rng(2)
+    n = 40000; X = rng.standard_normal((n, 64)); idx = rng.integers(0, 2, n).astype(np.int32)
+    exp_s, exp_b = oms.predict(X, nthreads=8), omb.predict(X, nthreads=8)
+    expect = lambda second: [api.Prediction.of((exp_s if k == 0 else second)["score"][i], (exp_s if k == 0 else second)["status"][i]) for i, k in enumerate(idx)]
+    op = api.EvaluationCoFunction(engine, max_batch=4096)
+    base = op.servingModels                                        # the engine's table is shared with the other tests' leftovers
+    op.processElement2(api.AddMessage(ns, 1, str(ps)))
+    op.processDense1([f"{ns}_1"], np.zeros(16, np.int32), X[:16]); op.flush(); op.collect()     # the small model is loaded and cached
+    op.processElement2(api.AddMessage(nb, 1, str(pb_)))            # background load starts ...
+    op.processDense1([f"{ns}_1", f"{nb}_1"], idx, X)               # ... and the events do not wait for it
+    parked = op.parkedEvents
+    early = op.collect()                                           # whatever is ready: a prefix of the expected output
+    op.flush()
+    out = early + op.collect()
+    assert parked > 0, "the load finished before the first event: nothing was parked (make the model bigger)"
+    assert len(early) < n and out == expect(exp_b)
+    assert op.servingModels == base + 2
+    # Del while events are parked: they are still scored with the model they were bound to; the model is not cached afterwards
+    op.processElement2(api.DelMessage(nb, 1))
+    op.processElement2(api.AddMessage(nb, 2, str(pb_)))
+    op.processDense1([f"{ns}_1", f"{nb}_2"], idx, X)
+    parked2 = op.parkedEvents - parked
+    op.processElement2(api.DelMessage(nb, 2))
+    op.processDense1([f"{ns}_1", f"{nb}_2"], idx[:100], X[:100])   # after the Del: EmptyScore for that id
+    op.flush()
+    out2 = op.collect()
+    assert parked2 > 0 and out2[:n] == expect(exp_b)
+    assert out2[n:] == [EMPTY if k == 1 else api.Prediction.of(exp_s["score"][i], exp_s["status"][i]) for i, k in enumerate(idx[:100])]
+    assert op.servingModels == base + 1
+    # a load that fails is fatal for the job from the call that settles the parked events
+    op.processElement2(api.AddMessage(nb, 3, MISSING))
+    with pytest.raises(api.ModelLoadingException):
+        op.processDense1([f"{nb}_3"], np.zeros(8, np.int32), X[:8])
+        op.flush()
+    op.close()
+    engine.table_del(ns, 1)
+
+
 def test_engine_is_usable_from_several_host_threads(engine, gen, oracle):
     """SURVEY.md §8b Threading: several subtasks (threads) of one TaskManager share an engine.  Four threads score
     different models concurrently while a fifth keeps adding / deleting table entries; every result must be right."""
