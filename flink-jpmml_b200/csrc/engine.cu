@@ -84,6 +84,7 @@ static constexpr int NSLOT = 8;        // stream slots shared by every host thre
 static constexpr int MAX_INFLIGHT = 3; // open tickets one caller may hold (fjp_max_inflight)
 struct Slot {
   cudaStream_t s = nullptr; cudaEvent_t done = nullptr;
+  cudaEvent_t copied = nullptr;   // the copy-in of the chunk this slot carries has finished (the next chunk's copy-in waits for it)
   uint8_t* buf = nullptr; size_t cap = 0;   // one device arena per slot, carved per call
   bool busy = false; fjp_model* held = nullptr;
   const uint8_t* pending_status = nullptr; long pending_n = 0;   // submitted batch whose outcomes are counted at fjp_wait
@@ -126,6 +127,7 @@ static int slot_reserve(Slot& s, size_t bytes) {
 }
 
 static size_t score_scratch_bytes(const fjp_model* m, long n, bool want_probs = false, bool want_node_ids = false);
+static bool env_flag(const char* name) { const char* v = getenv(name); return v && *v && *v != '0'; }
 
 struct Carve {  // sub-allocation inside a slot arena
   size_t off = 0;
@@ -137,8 +139,20 @@ struct HostBatch {
   const float* Xf;   // float rows (fjp_score_batch_f32): X is NULL then
 };
 
+// FJP_TRACE_CHUNKS=1 (dev aid): device timeline of the chunk pipeline of one host-buffer call, printed to stderr
+struct ChunkTrace { std::vector<cudaEvent_t> ev; bool on = false; };
+static thread_local ChunkTrace g_trace;
+static void trace_mark(cudaStream_t st) {
+  if (!g_trace.on) return;
+  cudaEvent_t ev; if (cudaEventCreate(&ev) != cudaSuccess) return;
+  cudaEventRecord(ev, st); g_trace.ev.push_back(ev);
+}
+
 // enqueue H2D + kernel + D2H for rows [lo, hi) of hb on slot s
-static int enqueue_chunk(fjp_engine* e, fjp_model* m, Slot& s, const HostBatch& hb, long lo, long hi) {
+// copy_after: the previous chunk's `copied` event.  Two copy-ins issued on two streams would otherwise run side by side at half
+// the PCIe rate each, finish together, and leave the link idle while both chunks' kernels run; chained, every copy-in has the
+// link to itself and the kernels of chunk i run under the copy-in of chunk i + 1.
+static int enqueue_chunk(fjp_engine* e, fjp_model* m, Slot& s, const HostBatch& hb, long lo, long hi, cudaEvent_t copy_after = nullptr) {
   const long n = hi - lo; const int F = hb.vec_size, W = (F + 31) / 32;
   Carve c;
   size_t oX = c.take((size_t)n * F * 8), oP = hb.present ? c.take((size_t)n * W * 4) : 0, oR = hb.replace ? c.take((size_t)n * 8) : 0;
@@ -150,25 +164,30 @@ static int enqueue_chunk(fjp_engine* e, fjp_model* m, Slot& s, const HostBatch& 
   BatchArgs a{}; a.stats = e->d_stats;
   a.X = reinterpret_cast<double*>(s.buf + oX); a.n = n; a.present_stride = W;
   int launches = 0;
-  if (hb.Xf) {   // half the bytes over PCIe; widened on the device (exact)
-    CK(cudaMemcpyAsync(s.buf + oF, hb.Xf + lo * (long)F, (size_t)n * F * 4, cudaMemcpyHostToDevice, s.s));
-    CK(launch_widen_f32(reinterpret_cast<const float*>(s.buf + oF), reinterpret_cast<double*>(s.buf + oX), n * (long)F, s.s, &launches));
-  } else CK(cudaMemcpyAsync(s.buf + oX, hb.X + lo * (long)F, (size_t)n * F * 8, cudaMemcpyHostToDevice, s.s));
+  if (copy_after) CK(cudaStreamWaitEvent(s.s, copy_after, 0));
+  trace_mark(s.s);
+  if (hb.Xf) CK(cudaMemcpyAsync(s.buf + oF, hb.Xf + lo * (long)F, (size_t)n * F * 4, cudaMemcpyHostToDevice, s.s));   // half the bytes over PCIe
+  else CK(cudaMemcpyAsync(s.buf + oX, hb.X + lo * (long)F, (size_t)n * F * 8, cudaMemcpyHostToDevice, s.s));
   if (hb.present) { a.present = reinterpret_cast<uint32_t*>(s.buf + oP); CK(cudaMemcpyAsync(s.buf + oP, hb.present + lo * (long)W, (size_t)n * W * 4, cudaMemcpyHostToDevice, s.s)); }
   if (hb.replace) { a.replace = reinterpret_cast<double*>(s.buf + oR); CK(cudaMemcpyAsync(s.buf + oR, hb.replace + lo, (size_t)n * 8, cudaMemcpyHostToDevice, s.s)); }
+  CK(cudaEventRecord(s.copied, s.s));
+  if (hb.Xf) CK(launch_widen_f32(reinterpret_cast<const float*>(s.buf + oF), reinterpret_cast<double*>(s.buf + oX), n * (long)F, s.s, &launches));   // widened on the device (exact)
   a.score = reinterpret_cast<double*>(s.buf + oS); a.status = s.buf + oT;
   a.aux = hb.aux ? reinterpret_cast<int32_t*>(s.buf + oA) : nullptr;
   a.node_ids = hb.node_ids ? reinterpret_cast<int32_t*>(s.buf + oN) : nullptr; a.node_stride = hb.node_stride;
   a.probs = hb.probs ? reinterpret_cast<double*>(s.buf + oQ) : nullptr; a.prob_stride = hb.prob_stride;
   if (hb.node_ids) CK(cudaMemsetAsync(s.buf + oN, 0xFF, (size_t)n * hb.node_stride * 4, s.s));
   if (hb.probs) CK(cudaMemsetAsync(s.buf + oQ, 0xFF, (size_t)n * hb.prob_stride * 8, s.s));
+  trace_mark(s.s);
   CK(launch_score_any(m->dev, a, dsz ? s.buf + oD : nullptr, s.s, &launches));
+  trace_mark(s.s);
   e->launches += launches;
   CK(cudaMemcpyAsync(hb.score + lo, s.buf + oS, (size_t)n * 8, cudaMemcpyDeviceToHost, s.s));
   CK(cudaMemcpyAsync(hb.status + lo, s.buf + oT, (size_t)n, cudaMemcpyDeviceToHost, s.s));
   if (hb.aux) CK(cudaMemcpyAsync(hb.aux + lo, s.buf + oA, (size_t)n * 4, cudaMemcpyDeviceToHost, s.s));
   if (hb.node_ids) CK(cudaMemcpyAsync(hb.node_ids + lo * (long)hb.node_stride, s.buf + oN, (size_t)n * hb.node_stride * 4, cudaMemcpyDeviceToHost, s.s));
   if (hb.probs) CK(cudaMemcpyAsync(hb.probs + lo * (long)hb.prob_stride, s.buf + oQ, (size_t)n * hb.prob_stride * 8, cudaMemcpyDeviceToHost, s.s));
+  trace_mark(s.s);
   return 0;
 }
 
@@ -257,7 +276,8 @@ int fjp_engine_create(int device, fjp_engine** out, char* err, size_t errcap) {
   if (cudaMalloc(&e->d_stats, 64) != cudaSuccess || cudaMemset(e->d_stats, 0, 64) != cudaSuccess) { delete e; return fail("engine counters: cudaMalloc failed", err, errcap); }
   for (int i = 0; i < NSLOT; i++) {
     if (cudaStreamCreateWithFlags(&e->slots[i].s, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaEventCreateWithFlags(&e->slots[i].done, cudaEventDisableTiming) != cudaSuccess) {
+        cudaEventCreateWithFlags(&e->slots[i].done, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&e->slots[i].copied, cudaEventDisableTiming) != cudaSuccess) {
       delete e; return fail("stream/event creation failed", err, errcap);
     }
   }
@@ -267,7 +287,7 @@ int fjp_engine_create(int device, fjp_engine** out, char* err, size_t errcap) {
 void fjp_engine_destroy(fjp_engine* e) {
   if (!e) return;
   cudaSetDevice(e->device);
-  for (auto& s : e->slots) { if (s.s) cudaStreamSynchronize(s.s); if (s.held) fjp_model_release(s.held); if (s.buf) cudaFree(s.buf); if (s.done) cudaEventDestroy(s.done); if (s.s) cudaStreamDestroy(s.s); }
+  for (auto& s : e->slots) { if (s.s) cudaStreamSynchronize(s.s); if (s.held) fjp_model_release(s.held); if (s.buf) cudaFree(s.buf); if (s.done) cudaEventDestroy(s.done); if (s.copied) cudaEventDestroy(s.copied); if (s.s) cudaStreamDestroy(s.s); }
   { std::lock_guard<std::mutex> lk(e->table_mu); e->table.reset(); }
   if (e->d_stats) cudaFree(e->d_stats);
   delete e;
@@ -389,8 +409,23 @@ static int score_host_batch(fjp_engine* e, fjp_model* m, const HostBatch& hb) {
   if (const char* v = getenv("FJP_CHUNK_ROWS")) { long r = atol(v); if (r >= 256) rows = r; }   // tuning aid
   int s0 = acquire_slot(e), s1 = n > rows ? try_acquire_slot(e) : -1;
   int used[2] = {s0, s1}; int ns = s1 >= 0 ? 2 : 1; int rc = 0; long k = 0;
-  for (long lo = 0; lo < n && rc == 0; lo += rows, k++) rc = enqueue_chunk(e, m, e->slots[used[k % ns]], hb, lo, std::min(n, lo + rows));
+  g_trace.on = env_flag("FJP_TRACE_CHUNKS");
+  // the last chunk's kernels and copy-out run under no copy-in: taper the end (half, quarter, quarter of a chunk)
+  for (long lo = 0; lo < n && rc == 0; k++) {
+    long take = std::min(rows, n - lo);
+    if (ns > 1 && n - lo <= rows && n - lo > 65536) take = (n - lo + 1) / 2;
+    rc = enqueue_chunk(e, m, e->slots[used[k % ns]], hb, lo, lo + take, (k > 0 && ns > 1) ? e->slots[used[(k - 1) % ns]].copied : nullptr);
+    lo += take;
+  }
   for (int i = 0; i < ns; i++) { cudaError_t ce = cudaStreamSynchronize(e->slots[used[i]].s); if (ce != cudaSuccess && rc == 0) rc = fail(std::string("scoring failed: ") + cudaGetErrorString(ce)); release_slot(e, used[i]); }
+  if (g_trace.on) {   // per chunk: copy-in start, copy-in end = kernels start, kernels end, copy-out end (ms from the first mark)
+    for (size_t i = 0; i + 3 < g_trace.ev.size(); i += 4) {
+      float t[4]; for (int q = 0; q < 4; q++) cudaEventElapsedTime(&t[q], g_trace.ev[0], g_trace.ev[i + q]);
+      fprintf(stderr, "[fjp trace] chunk %zu: h2d %.3f..%.3f  kernels ..%.3f  d2h ..%.3f ms\n", i / 4, t[0], t[1], t[2], t[3]);
+    }
+    for (cudaEvent_t ev : g_trace.ev) cudaEventDestroy(ev);
+    g_trace.ev.clear(); g_trace.on = false;
+  }
   if (rc == 0) count_statuses(e, hb.status, n);
   return rc;
 }
