@@ -83,18 +83,25 @@ __device__ __forceinline__ void ck_rank_keys_direct(uint32_t th_addr, uint32_t e
     const uint32_t b = __float2uint_rz(fminf(fmaxf((xf - cf.lo) * cf.scale_e, 0.0f), top));     // model.h ck_bucket
     asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(en[k].x), "=r"(en[k].y) : "r"(ent_addr + 8u * b));
   }
+  bool crowded[RK_BATCH], any_crowded = false;
 #pragma unroll
   for (int k = 0; k < RK_BATCH; k++) {
-    const uint32_t first = en[k].y & 0xFFFFu, cnt = en[k].y >> 16;
-    uint32_t kk = 2u * first + 1u + (img[k] > en[k].x ? 2u : (img[k] == en[k].x ? 1u : 0u));
-    if (cnt > 1u && img[k] > en[k].x) {        // crowded bucket: scan the threshold array from the second one on (sentinels end it)
-      uint32_t r = th_addr + 4u * (first + 1u), t;
+    const uint32_t first = en[k].y & 0xFFFFu;
+    key[k] = 2u * first + 1u + (img[k] > en[k].x ? 2u : (img[k] == en[k].x ? 1u : 0u));
+    crowded[k] = en[k].y > 0x1FFFFu && img[k] > en[k].x;   // more than one threshold in the bucket and the first one is below the value
+    any_crowded = any_crowded || crowded[k];
+  }
+  if (any_crowded) {   // rare (about four buckets per threshold): one branch for the whole batch
+#pragma unroll
+    for (int k = 0; k < RK_BATCH; k++) if (crowded[k]) {   // scan the threshold array from the bucket's second one on (sentinels end it)
+      uint32_t r = th_addr + 4u * ((en[k].y & 0xFFFFu) + 1u), t;
       asm volatile("ld.shared.u32 %0, [%1];" : "=r"(t) : "r"(r));
       while (t < img[k]) { r += 4u; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(t) : "r"(r)); }
-      kk = ((r - th_addr) >> 1) + (t == img[k] ? 2u : 1u);
+      key[k] = ((r - th_addr) >> 1) + (t == img[k] ? 2u : 1u);
     }
-    key[k] = nan[k] ? 2u * cf.n_thr + 1u : kk;      // NaN is the greatest value (Double.compareTo)
   }
+#pragma unroll
+  for (int k = 0; k < RK_BATCH; k++) key[k] = nan[k] ? 2u * cf.n_thr + 1u : key[k];      // NaN is the greatest value (Double.compareTo)
 }
 
 // The same for thresholds that are not floats: values are compared as doubles (64-bit images, Double.compareTo order);
@@ -156,31 +163,40 @@ __global__ void __launch_bounds__(RK_THREADS, RK_CTAS) forest_rank_keys_kernel(c
     const double* xt = a.X + row0 * (long)F + f;
     const uint32_t* pt = a.present ? a.present + row0 * (long)a.present_stride + pword : nullptr;
     uint16_t* const gout = reinterpret_cast<uint16_t*>(kt.keys + (size_t)tile * (kt.tile_bytes / 4) + (size_t)(f >> 1) * E) + (f & 1);
-    for (int i0 = tid; i0 < total; i0 += RK_THREADS * RK_BATCH) {
-      double val[RK_BATCH]; uint32_t pw[RK_BATCH], key[RK_BATCH]; int st[RK_BATCH], e[RK_BATCH];
+    // full tiles whose element count is a whole number of thread batches (E = 640: two) need none of the clamps
+    auto body = [&](auto full_c) {
+      constexpr bool FULL = decltype(full_c)::value;
+      for (int i0 = tid; i0 < total; i0 += RK_THREADS * RK_BATCH) {
+        double val[RK_BATCH]; uint32_t pw[RK_BATCH], key[RK_BATCH]; int st[RK_BATCH], e[RK_BATCH]; bool present[RK_BATCH];
 #pragma unroll
-      for (int k = 0; k < RK_BATCH; k++) {
-        e[k] = min(min(i0 + k * RK_THREADS, total - 1) >> 3, last);   // clamped: duplicates recompute a live element
-        val[k] = __ldcs(xt + e[k] * F);
-        pw[k] = pt ? __ldg(pt + e[k] * a.present_stride) : pbit;
-      }
+        for (int k = 0; k < RK_BATCH; k++) {
+          e[k] = FULL ? (i0 + k * RK_THREADS) >> 3 : min(min(i0 + k * RK_THREADS, total - 1) >> 3, last);   // clamped: duplicates recompute a live element
+          val[k] = __ldcs(xt + e[k] * F);
+          pw[k] = pt ? __ldg(pt + e[k] * a.present_stride) : pbit;
+        }
 #pragma unroll
-      for (int k = 0; k < RK_BATCH; k++) {
-        bool present = (pw[k] & pbit) != 0;
-        if (!present && a.replace) { double rep = a.replace[row0 + e[k]]; if (rep == rep) { val[k] = rep; present = true; } }
-        if (SIMPLE) { st[k] = present ? 0 : 1; if (WIDE && float_field) val[k] = (double)(float)val[k]; }   // JPMML casts to the field's dataType
-        else { double raw = val[k]; val[k] = 0.0; st[k] = prep_value(m.prep[f], m.prep_pool, present, raw, val[k]); }
-      }
-      if (WIDE) ck_rank_keys_wide(th_addr, tab_addr, cf, val, key);
-      else if (cf.nb_e) ck_rank_keys_direct(th_addr, ent_addr, cf, mode, val, key);
-      else ck_rank_keys(th_addr, tab_addr, cf, mode, val, key);
+        for (int k = 0; k < RK_BATCH; k++) present[k] = (pw[k] & pbit) != 0;
+        if (a.replace) {
 #pragma unroll
-      for (int k = 0; k < RK_BATCH; k++) {
-        const int ee = min(i0 + k * RK_THREADS, total - 1) >> 3;      // the unclamped event slot of the tile
-        if (!SIMPLE && st[k] == 2 && ee <= last) kt.fail[tile * E + ee] = 1;
-        if (owner) gout[2 * ee] = (uint16_t)(st[k] == 0 ? key[k] : 0x8000u);   // 0x8000 = missing
+          for (int k = 0; k < RK_BATCH; k++) if (!present[k]) { double rep = a.replace[row0 + e[k]]; if (rep == rep) { val[k] = rep; present[k] = true; } }
+        }
+#pragma unroll
+        for (int k = 0; k < RK_BATCH; k++) {
+          if (SIMPLE) { st[k] = present[k] ? 0 : 1; if (WIDE && float_field) val[k] = (double)(float)val[k]; }   // JPMML casts to the field's dataType
+          else { double raw = val[k]; val[k] = 0.0; st[k] = prep_value(m.prep[f], m.prep_pool, present[k], raw, val[k]); }
+        }
+        if (WIDE) ck_rank_keys_wide(th_addr, tab_addr, cf, val, key);
+        else if (cf.nb_e) ck_rank_keys_direct(th_addr, ent_addr, cf, mode, val, key);
+        else ck_rank_keys(th_addr, tab_addr, cf, mode, val, key);
+#pragma unroll
+        for (int k = 0; k < RK_BATCH; k++) {
+          const int ee = FULL ? e[k] : min(i0 + k * RK_THREADS, total - 1) >> 3;      // the unclamped event slot of the tile
+          if (!SIMPLE && st[k] == 2 && ee <= last) kt.fail[tile * E + ee] = 1;
+          if (owner) gout[2 * ee] = (uint16_t)(st[k] == 0 ? key[k] : 0x8000u);   // 0x8000 = missing
+        }
       }
-    }
+    };
+    if (last == E - 1 && total % (RK_THREADS * RK_BATCH) == 0) body(std::true_type{}); else body(std::false_type{});
   }
 }
 
