@@ -111,6 +111,7 @@ def _lib():
         "fjh_cofunction_metadata_size": (i32, [vp]),
         "fjh_cofunction_cached_models": (i32, [vp]),
         "fjh_cofunction_parked_events": (lng, [vp]),
+        "fjh_cofunction_flush_seconds": (dbl, [vp]),
         "fjh_cofunction_destroy": (None, [vp]),
     }
     for name, (res, args) in sig.items():
@@ -124,7 +125,7 @@ HOST_EXPORTS = ["fjh_model_id_parse", "fjh_model_id_hash", "fjh_predict", "fjh_e
                 "fjh_eval_function_process", "fjh_eval_function_process_dense", "fjh_eval_function_reserve", "fjh_eval_function_commit", "fjh_eval_function_flush", "fjh_eval_function_poll", "fjh_eval_function_close",
                 "fjh_cofunction_create", "fjh_cofunction_process_event", "fjh_cofunction_process_dense", "fjh_cofunction_process_control", "fjh_cofunction_flush",
                 "fjh_cofunction_poll", "fjh_cofunction_snapshot", "fjh_cofunction_restore", "fjh_cofunction_metadata_size",
-                "fjh_cofunction_cached_models", "fjh_cofunction_parked_events", "fjh_cofunction_destroy"]
+                "fjh_cofunction_cached_models", "fjh_cofunction_parked_events", "fjh_cofunction_flush_seconds", "fjh_cofunction_destroy"]
 
 
 def _raise(rc, err=b""):
@@ -338,6 +339,11 @@ class EvaluationCoFunction:
     def parkedEvents(self) -> int:
         """Events the bulk path parked behind a model load that was still running (they keep their output position)."""
         return _lib().fjh_cofunction_parked_events(self._h)
+
+    @property
+    def flushSeconds(self) -> float:
+        """Seconds the task thread spent handing micro-batches to the GPU and waiting for them (the rest is packing)."""
+        return _lib().fjh_cofunction_flush_seconds(self._h)
 
     def close(self):
         if self._h:

@@ -79,6 +79,7 @@ def lib():
         "fjp_score_device": (i32, [vp, vp, vp, vp, vp, lng, i32, vp, vp, vp, vp]),
         "fjp_score_sparse_noalloc": (i32, [vp, vp, vp, vp, vp, lng, i32, vp, vp, vp]),
         "fjp_submit": (i32, [vp, vp, vp, vp, vp, lng, i32, vp, vp, vp, C.POINTER(i32)]),
+        "fjp_submit_many": (i32, [vp, vp, i32, C.POINTER(i32)]),
         "fjp_wait": (i32, [vp, i32]),
     }
     for name, (res, args) in sig.items():
@@ -93,7 +94,7 @@ EXPORTS = ["fjp_version", "fjp_last_error", "fjp_max_inflight", "fjp_engine_crea
            "fjp_model_replicate", "fjp_model_num_fields", "fjp_model_field_name", "fjp_model_name", "fjp_model_family",
            "fjp_model_num_labels", "fjp_model_label", "fjp_model_num_segments", "fjp_model_describe", "fjp_model_device_bytes",
            "fjp_table_add", "fjp_table_del", "fjp_table_get", "fjp_table_size", "fjp_table_epoch", "fjp_host_alloc",
-           "fjp_host_free", "fjp_score_batch", "fjp_score_batch_ex", "fjp_score_sparse", "fjp_model_float_row_modes", "fjp_score_batch_f32", "fjp_score_sparse_noalloc", "fjp_score_device", "fjp_submit", "fjp_wait"]
+           "fjp_host_free", "fjp_score_batch", "fjp_score_batch_ex", "fjp_score_sparse", "fjp_model_float_row_modes", "fjp_score_batch_f32", "fjp_score_sparse_noalloc", "fjp_score_device", "fjp_submit", "fjp_submit_many", "fjp_wait"]
 
 
 def _ptr(a):

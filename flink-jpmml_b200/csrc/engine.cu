@@ -88,6 +88,7 @@ struct Slot {
   uint8_t* buf = nullptr; size_t cap = 0;   // one device arena per slot, carved per call
   bool busy = false; fjp_model* held = nullptr;
   const uint8_t* pending_status = nullptr; long pending_n = 0;   // submitted batch whose outcomes are counted at fjp_wait
+  std::vector<fjp_model*> held_more; std::vector<std::pair<const uint8_t*, long>> pending_more;   // fjp_submit_many: the other batches of the ticket
 };
 
 struct fjp_engine {
@@ -152,15 +153,19 @@ static void trace_mark(cudaStream_t st) {
 // copy_after: the previous chunk's `copied` event.  Two copy-ins issued on two streams would otherwise run side by side at half
 // the PCIe rate each, finish together, and leave the link idle while both chunks' kernels run; chained, every copy-in has the
 // link to itself and the kernels of chunk i run under the copy-in of chunk i + 1.
-static int enqueue_chunk(fjp_engine* e, fjp_model* m, Slot& s, const HostBatch& hb, long lo, long hi, cudaEvent_t copy_after = nullptr) {
+// shared: the arena is already reserved and carved from *shared on (several batches behind one ticket, fjp_submit_many);
+// dry_run: only advance *shared (sizing pass).
+static int enqueue_chunk(fjp_engine* e, fjp_model* m, Slot& s, const HostBatch& hb, long lo, long hi, cudaEvent_t copy_after = nullptr,
+                         Carve* shared = nullptr, bool dry_run = false) {
   const long n = hi - lo; const int F = hb.vec_size, W = (F + 31) / 32;
-  Carve c;
+  Carve own; Carve& c = shared ? *shared : own;
   size_t oX = c.take((size_t)n * F * 8), oP = hb.present ? c.take((size_t)n * W * 4) : 0, oR = hb.replace ? c.take((size_t)n * 8) : 0;
   size_t oF = hb.Xf ? c.take((size_t)n * F * 4) : 0;
   size_t oS = c.take((size_t)n * 8), oT = c.take((size_t)n), oA = hb.aux ? c.take((size_t)n * 4) : 0;
   size_t oN = hb.node_ids ? c.take((size_t)n * hb.node_stride * 4) : 0, oQ = hb.probs ? c.take((size_t)n * hb.prob_stride * 8) : 0;
   const size_t dsz = score_scratch_bytes(m, n, hb.probs != nullptr, hb.node_ids != nullptr); size_t oD = dsz ? c.take(dsz) : 0;   // augmented rows (derived fields) / leaf values (small-batch forest path) / digit planes
-  if (slot_reserve(s, c.off)) return -1;
+  if (dry_run) return 0;
+  if (!shared && slot_reserve(s, c.off)) return -1;
   BatchArgs a{}; a.stats = e->d_stats;
   a.X = reinterpret_cast<double*>(s.buf + oX); a.n = n; a.present_stride = W;
   int launches = 0;
@@ -556,14 +561,53 @@ int fjp_submit(fjp_engine* e, fjp_model* m, const double* X, const uint32_t* pre
   return 0;
 }
 
+// Several micro-batches, each for its own model, behind ONE ticket: one stream slot, one arena carved for all of them, copies and
+// kernels enqueued back to back without a host-side wait in between.  This is what the dynamic operator hands over per flush
+// (one bucket per model), so that the task thread can pack the next generation of events while the GPU scores this one.
+int fjp_submit_many(fjp_engine* e, const fjp_batch_desc* b, int count, int* ticket) {
+  *ticket = -1;
+  if (count <= 0) return fail("fjp_submit_many: no batches");
+  CK(cudaSetDevice(e->device));
+  for (int i = 0; i < count; i++) {
+    if (!b[i].model) return fail("fjp_submit_many: batch without a model");
+    if (!b[i].model->d_blob || b[i].model->device != e->device) return fail("model is not resident on this engine's device");
+    if (b[i].vec_size != b[i].model->cm.dev.F_in) return fail("fjp_submit_many: vector size differs from the model's field count");
+  }
+  const int si = try_acquire_slot(e);
+  if (si < 0) return FJP_BUSY;
+  Slot& s = e->slots[si];
+  auto give_up = [&](int rc) {
+    for (fjp_model* hm : s.held_more) fjp_model_release(hm);
+    s.held_more.clear(); s.pending_more.clear(); release_slot(e, si); return rc;
+  };
+  auto host_batch = [&](int i) { return HostBatch{b[i].X, b[i].present, b[i].replace, b[i].n, b[i].vec_size, b[i].score, b[i].status, nullptr, nullptr, 0, nullptr, 0, nullptr}; };
+  Carve sizing;
+  for (int i = 0; i < count; i++) if (b[i].n > 0) enqueue_chunk(e, b[i].model, s, host_batch(i), 0, b[i].n, nullptr, &sizing, true);
+  if (slot_reserve(s, sizing.off)) return give_up(-1);
+  Carve carve;
+  for (int i = 0; i < count; i++) {
+    if (b[i].n <= 0) continue;
+    fjp_model_retain(b[i].model); s.held_more.push_back(b[i].model);   // a batch keeps its model alive across a concurrent fjp_table_del
+    s.pending_more.emplace_back(b[i].status, b[i].n);
+    if (enqueue_chunk(e, b[i].model, s, host_batch(i), 0, b[i].n, nullptr, &carve, false)) { cudaStreamSynchronize(s.s); return give_up(-1); }
+  }
+  cudaError_t ce = cudaEventRecord(s.done, s.s);
+  if (ce != cudaSuccess) { cudaStreamSynchronize(s.s); return give_up(fail(std::string("cudaEventRecord: ") + cudaGetErrorString(ce))); }
+  *ticket = si;
+  return 0;
+}
+
 int fjp_wait(fjp_engine* e, int ticket) {
   if (ticket < 0 || ticket >= NSLOT) return fail("bad ticket");
   Slot& s = e->slots[ticket];
   CK(cudaSetDevice(e->device));
   cudaError_t ce = cudaStreamSynchronize(s.s);
   if (s.held) { fjp_model_release(s.held); s.held = nullptr; }
+  for (fjp_model* hm : s.held_more) fjp_model_release(hm);
+  s.held_more.clear();
   if (ce == cudaSuccess && s.pending_status) count_statuses(e, s.pending_status, s.pending_n);
-  s.pending_status = nullptr; s.pending_n = 0;
+  if (ce == cudaSuccess) for (auto& ps : s.pending_more) count_statuses(e, ps.first, ps.second);
+  s.pending_status = nullptr; s.pending_n = 0; s.pending_more.clear();
   release_slot(e, ticket);
   if (ce != cudaSuccess) return fail(std::string("scoring failed: ") + cudaGetErrorString(ce));
   return 0;

@@ -19,6 +19,7 @@
 // holds the model it was bound to when it arrived, so control messages keep their "takes effect between events"
 // meaning (T/RichConnectedStreamSpec.scala:83-95, 187-204) without flushing.
 #pragma once
+#include <algorithm>
 #include <cmath>
 #include <cstdint>
 #include <future>
@@ -127,6 +128,7 @@ class PredictionQueue {
   static constexpr uint8_t kOpen = 0xFF;   // placeholder: the prediction is still being computed; nothing behind it is handed out
   void push(uint8_t status, double score) { status_.push_back(status); score_.push_back(score); }
   size_t reserve() { status_.push_back(kOpen); score_.push_back(0); open_++; return status_.size() - 1; }   // stays valid until filled
+  size_t reserve_n(size_t n) { const size_t s0 = status_.size(); status_.insert(status_.end(), n, kOpen); score_.insert(score_.end(), n, 0.0); open_ += n; return s0; }
   void fill(size_t slot, uint8_t status, double score) { status_[slot] = status; score_[slot] = score; open_--; }
   // predictions that can be emitted now: everything up to the first placeholder
   size_t size() const { return ready_end() - head_; }
@@ -158,6 +160,7 @@ class MicroBatch {
   int room() const { return cap_ - n_; }
   int score(fjp_engine* e, fjp_model* m);                         // fills score()/status()
   int submit(fjp_engine* e, fjp_model* m, int* ticket);           // asynchronous: fjp_submit; results valid after fjp_wait(ticket)
+  fjp_batch_desc desc(fjp_model* m) const { return fjp_batch_desc{m, X_, any_sparse_ ? present_ : nullptr, any_replace_ ? replace_ : nullptr, n_, F_, score_, status_}; }
   const double* scores() const { return score_; }
   const uint8_t* statuses() const { return status_; }
  private:
@@ -201,6 +204,7 @@ class EvaluationFunction {
 class EvaluationCoFunction {
  public:
   EvaluationCoFunction(fjp_engine* e, int maxBatch) : engine_(e), max_batch_(maxBatch) {}
+  ~EvaluationCoFunction();
   void initializeState(const std::vector<Metadata>& restored);   // union of the restored maps (:81-96)
   Metadata snapshotState();                                      // flushes, then returns the metadata (:76-79)
   void processElement1(const std::string& modelId, const Vector& v, std::optional<double> replaceNan = std::nullopt);
@@ -216,8 +220,9 @@ class EvaluationCoFunction {
   const Metadata& servingMetadata() const { return metadata_; }
   int servingModels() const { return engine_ ? fjp_table_size(engine_) : 0; }
   long parkedEvents() const { return parked_events_; }
+  double flushSeconds() const { return flush_seconds_; }   // time the task thread spent handing batches to the GPU and waiting for them
  private:
-  long parked_events_ = 0;
+  long parked_events_ = 0; double flush_seconds_ = 0;
   struct Pending { int bucket; int row; };
   struct Bucket { PmmlModel model; std::unique_ptr<MicroBatch> batch; };
   fjp_engine* engine_; int max_batch_; Metadata metadata_;
@@ -242,7 +247,15 @@ class EvaluationCoFunction {
   int park_index(const std::string& modelId, int size);   // >= 0: the events of this id are parked there right now
   void settle(Parked& p);                                 // load finished: score the parked rows, fill their placeholders
   void flush_buckets(bool wait_for_parked);
+  // A flush hands all buckets to the GPU behind one ticket (fjp_submit_many) and returns to packing; the generation before it is
+  // collected then (its predictions come first).  Placeholders keep the output order while a generation is in flight.
+  struct Generation { std::vector<Bucket> buckets; std::vector<Pending> pending; size_t slot0 = 0; int ticket = -1; };
+  std::unique_ptr<Generation> inflight_;
+  void collect(Generation& g);
   std::unique_ptr<MicroBatch> take_batch(int fields);
+  // a generation holds at most max_batch events over all its buckets; one model's bucket gets an eighth of that (a full bucket
+  // flushes the generation), so two generations of 32 models stay at a few hundred MB of pinned memory
+  int bucket_rows() const { return std::min(max_batch_, std::max(1024, max_batch_ / 8)); }
   int bucket_for(const PmmlModel& m);
   PmmlModel resolve(const std::string& modelId);   // servingModels.getOrElse(id.hashCode, fromMetadata(id))
   void enqueue(const PmmlModel& model, const Vector* v, const double* dense, int size, std::optional<double> replaceNan);

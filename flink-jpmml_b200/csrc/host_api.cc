@@ -268,8 +268,8 @@ PmmlModel EvaluationCoFunction::fromMetadata(const std::string& modelId) {
 
 std::unique_ptr<MicroBatch> EvaluationCoFunction::take_batch(int fields) {
   for (size_t i = 0; i < pool_.size(); i++)
-    if (pool_[i]->fields() == fields && pool_[i]->capacity() == max_batch_) { auto mb = std::move(pool_[i]); pool_.erase(pool_.begin() + i); return mb; }
-  return std::make_unique<MicroBatch>(fields, max_batch_);
+    if (pool_[i]->fields() == fields && pool_[i]->capacity() == bucket_rows()) { auto mb = std::move(pool_[i]); pool_.erase(pool_.begin() + i); return mb; }
+  return std::make_unique<MicroBatch>(fields, bucket_rows());
 }
 int EvaluationCoFunction::bucket_for(const PmmlModel& m) {
   for (size_t i = 0; i < buckets_.size(); i++) if (buckets_[i].model.handle() == m.handle()) return (int)i;
@@ -405,7 +405,23 @@ void EvaluationCoFunction::processElement2(const ServingMessage& control) {
 
 void EvaluationCoFunction::flush() { flush_buckets(true); }
 
+EvaluationCoFunction::~EvaluationCoFunction() {
+  if (inflight_ && inflight_->ticket >= 0 && engine_) fjp_wait(engine_, inflight_->ticket);   // nothing may outlive the pinned buffers
+}
+
+void EvaluationCoFunction::collect(Generation& g) {
+  if (g.ticket >= 0) { const int t = g.ticket; g.ticket = -1; if (fjp_wait(engine_, t) != 0) throw std::runtime_error(fjp_last_error()); }
+  for (size_t i = 0; i < g.pending.size(); i++) {
+    const Pending& p = g.pending[i];
+    if (p.bucket >= 0) out_.fill(g.slot0 + i, g.buckets[p.bucket].batch->statuses()[p.row], g.buckets[p.bucket].batch->scores()[p.row]);
+  }
+  for (auto& b : g.buckets) { b.batch->clear(); if (pool_.size() < 96) pool_.push_back(std::move(b.batch)); }
+  g.buckets.clear(); g.pending.clear();   // dropping the buckets releases models deleted in the meantime
+}
+
 void EvaluationCoFunction::flush_buckets(bool wait_for_parked) {
+  struct Timer { double& acc; std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+                 ~Timer() { acc += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); } } timer{flush_seconds_};
   auto settle_parked = [&] {
     for (size_t i = 0; i < parked_.size();) {
       Parked& p = *parked_[i];
@@ -414,30 +430,30 @@ void EvaluationCoFunction::flush_buckets(bool wait_for_parked) {
       settle(*done);
     }
   };
-  if (pending_.empty()) { if (!parked_.empty()) { settle_parked(); flushes_++; } return; }
-  // every model's bucket is its own submission; up to fjp_max_inflight() of them overlap on the GPU
-  std::vector<int> tickets; const int maxfly = fjp_max_inflight(); size_t waited = 0;
-  for (auto& b : buckets_) {
-    if (!b.batch->size()) continue;
-    if ((int)(tickets.size() - waited) >= maxfly) { if (fjp_wait(engine_, tickets[waited++]) != 0) throw std::runtime_error(fjp_last_error()); }
-    int t = -1;
-    submit_or_throw(*b.batch, engine_, b.model.handle(), &t, [&] {
-      if (waited >= tickets.size()) return false;
-      if (fjp_wait(engine_, tickets[waited++]) != 0) throw std::runtime_error(fjp_last_error());
-      return true;
-    });
-    tickets.push_back(t);
+  if (!pending_.empty()) {
+    auto gen = std::make_unique<Generation>();
+    gen->buckets = std::move(buckets_); gen->pending = std::move(pending_); buckets_.clear(); pending_.clear();
+    gen->slot0 = out_.reserve_n(gen->pending.size());
+    for (size_t i = 0; i < gen->pending.size(); i++) {   // what needs no GPU is known now; parked events learn their output position
+      const Pending& p = gen->pending[i];
+      if (p.bucket <= -2) parked_[-2 - p.bucket]->slots.push_back(gen->slot0 + i);
+      else if (p.bucket < 0) out_.fill(gen->slot0 + i, (uint8_t)p.row, 0);
+    }
+    std::vector<fjp_batch_desc> descs;
+    for (auto& b : gen->buckets) if (b.batch->size()) descs.push_back(b.batch->desc(b.model.handle()));
+    while (!descs.empty()) {
+      const int rc = fjp_submit_many(engine_, descs.data(), (int)descs.size(), &gen->ticket);
+      if (rc == 0) break;
+      if (rc != FJP_BUSY) throw std::runtime_error(fjp_last_error());
+      if (inflight_ && inflight_->ticket >= 0) collect(*inflight_);   // every stream slot of the engine is taken: give back our own first
+      else std::this_thread::yield();                                  // the others are held by other subtasks, which always finish
+    }
+    if (inflight_) collect(*inflight_);   // the older generation: its predictions come first, its buffers go back to the pool
+    inflight_ = std::move(gen);
+    flushes_++;
   }
-  for (; waited < tickets.size(); waited++) if (fjp_wait(engine_, tickets[waited]) != 0) throw std::runtime_error(fjp_last_error());
-  for (auto& p : pending_) {
-    if (p.bucket <= -2) parked_[-2 - p.bucket]->slots.push_back(out_.reserve());
-    else if (p.bucket < 0) out_.push((uint8_t)p.row, 0);
-    else out_.push(buckets_[p.bucket].batch->statuses()[p.row], buckets_[p.bucket].batch->scores()[p.row]);
-  }
-  pending_.clear(); flushes_++;
-  settle_parked();   // nothing refers to parked_ by index any more
-  for (auto& b : buckets_) { b.batch->clear(); if (pool_.size() < 64) pool_.push_back(std::move(b.batch)); }
-  buckets_.clear();   // dropping the buckets releases models deleted in the meantime
+  if (wait_for_parked && inflight_) { collect(*inflight_); inflight_.reset(); }
+  if (!parked_.empty()) { settle_parked(); flushes_++; }   // nothing refers to parked_ by index any more
 }
 
 }  // namespace flinkjpmml
@@ -544,6 +560,7 @@ int fjh_cofunction_restore(fjh_cofunction* h, const char* const* snapshots, int 
 int fjh_cofunction_metadata_size(fjh_cofunction* h) { return (int)h->op->servingMetadata().size(); }
 int fjh_cofunction_cached_models(fjh_cofunction* h) { return h->op->servingModels(); }
 long fjh_cofunction_parked_events(fjh_cofunction* h) { return h->op->parkedEvents(); }
+double fjh_cofunction_flush_seconds(fjh_cofunction* h) { return h->op->flushSeconds(); }
 void fjh_cofunction_destroy(fjh_cofunction* h) { delete h; }
 
 }  // extern "C"

@@ -173,6 +173,14 @@ int fjp_score_device(fjp_engine* e, fjp_model* m, const double* dX, const uint32
 #define FJP_BUSY 1
 int fjp_submit(fjp_engine* e, fjp_model* m, const double* X, const uint32_t* present, const double* replace,
                long n, int vec_size, double* score, uint8_t* status, int32_t* aux, int* ticket);
+/* Several micro-batches, each for its own model, behind one ticket (one stream slot, copies and kernels enqueued back to back):
+ * what a dynamic operator hands over per flush -- one bucket per model id (S/api/functions/EvaluationCoFunction.scala:106-117 picks
+ * the model per event) -- so that its task thread packs the next events while these are scored.  Every batch must match its
+ * model's field count; FJP_BUSY as for fjp_submit; fjp_wait(ticket) completes all of them. */
+typedef struct fjp_batch_desc {
+  fjp_model* model; const double* X; const uint32_t* present; const double* replace; long n; int vec_size; double* score; uint8_t* status;
+} fjp_batch_desc;
+int fjp_submit_many(fjp_engine* e, const fjp_batch_desc* batches, int count, int* ticket);
 int fjp_wait(fjp_engine* e, int ticket);
 int fjp_max_inflight(void);
 

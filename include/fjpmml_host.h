@@ -82,6 +82,7 @@ int fjh_cofunction_restore(fjh_cofunction* op, const char* const* snapshots, int
 int fjh_cofunction_metadata_size(fjh_cofunction* op);
 int fjh_cofunction_cached_models(fjh_cofunction* op);
 long fjh_cofunction_parked_events(fjh_cofunction* op);   /* events that were parked behind a model load so far (statistic) */
+double fjh_cofunction_flush_seconds(fjh_cofunction* op); /* seconds the task thread spent submitting micro-batches and waiting for them (statistic) */
 void fjh_cofunction_destroy(fjh_cofunction* op);
 
 #ifdef __cplusplus
