@@ -315,3 +315,36 @@ def test_float_rows_score_identically(engine, gen, oracle, dtype, operator):
     assert np.array_equal(r["score"][:8000], o["score"], equal_nan=True) and np.array_equal(r["status"][:8000], o["status"])
     # a model whose tests need the doubles says so
     assert engine.float_row_modes(engine.compile(gen.config_c2(k=4, F=8)[0])) is None
+
+
+def test_submit_many_scores_every_batch_with_its_own_model(engine, oracle, gen):
+    """fjp_submit_many: several micro-batches, each for its own model (tree ensemble, k-means, MLP, an empty batch in between),
+    behind one ticket; after fjp_wait every batch holds what its model gives through fjp_score_batch and the oracle."""
+    import ctypes as C
+    from flink_jpmml_b200 import capi
+    L = capi.lib()
+
+    class Desc(C.Structure):
+        _fields_ = [("model", C.c_void_p), ("X", C.c_void_p), ("present", C.c_void_p), ("replace", C.c_void_p), ("n", C.c_long),
+                    ("vec_size", C.c_int), ("score", C.c_void_p), ("status", C.c_void_p)]
+    pms = [gen.gbt_pmml(T=30, depth=5, F=12, seed=801)[0], gen.kmeans_pmml(np.random.default_rng(802).standard_normal((5, 12))),
+           gen.nn_pmml(n_in=12, hidden=(16,), n_out=3, seed=803)[0]]
+    models = [engine.compile(pm) for pm in pms]
+    sizes = [3000, 0, 1777, 512]; which = [0, 1, 1, 2]
+    keep, descs = [], (Desc * len(sizes))()
+    for i, (n, k) in enumerate(zip(sizes, which)):
+        X, pres, pb = gen.events(max(n, 1), 12, 810 + i, 0.1 if k == 0 else 0.0)
+        X = np.ascontiguousarray(X[:n]); pb = np.ascontiguousarray(pb[:n]); sc = np.full(n, -1.0); st = np.full(n, 9, np.uint8)
+        keep.append((X, pb, sc, st))
+        descs[i] = Desc(models[k]._h, X.ctypes.data, pb.ctypes.data, None, n, 12, sc.ctypes.data, st.ctypes.data)
+    ticket = C.c_int(-1)
+    assert L.fjp_submit_many(engine._h, descs, len(sizes), C.byref(ticket)) == 0 and ticket.value >= 0
+    assert L.fjp_wait(engine._h, ticket.value) == 0
+    for (X, pb, sc, st), n, k in zip(keep, sizes, which):
+        if n == 0: continue
+        o = oracle.OracleModel(pms[k]).predict(X, pb, nthreads=4); r = engine.score(models[k], X, pb)
+        assert np.array_equal(st, o["status"]) and np.array_equal(st, r["status"])
+        ok = st == 0
+        assert np.array_equal(sc[ok].view(np.int64), r["score"][ok].view(np.int64)) and np.array_equal(sc[ok], o["score"][ok])
+    bad = (Desc * 1)(Desc(models[0]._h, keep[0][0].ctypes.data, None, None, 10, 7, keep[0][2].ctypes.data, keep[0][3].ctypes.data))
+    assert L.fjp_submit_many(engine._h, bad, 1, C.byref(ticket)) != 0 and ticket.value == -1      # wrong vector size: refused as a whole
