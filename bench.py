@@ -130,7 +130,7 @@ def other_configs():
         ("C2", "k-means k=64 F=128, dense", lambda: g.config_c2()[0], 128, 1 << 22, 0.0, {"flop": 24576, "hbm": 1032, "bound": "fp64"}),
         ("C2_missing5", "k-means k=64 F=128, 5% missing", lambda: g.config_c2()[0], 128, 1 << 22, 0.05, {"flop": 24576, "hbm": 1032, "bound": "fp64"}),
         ("C3", "multinomial logistic 1000 features x 20 classes", lambda: g.regression_pmml()[0], 1000, 1 << 20, 0.0, {"flop": 40000, "hbm": 8008, "bound": "hbm"}),
-        ("C5_RF", "random forest 200 trees depth 8 F=64 majorityVote", lambda: g.rf_pmml()[0], 64, 1 << 22, 0.0, {"gather": 12800, "hbm": 528, "bound": "gather"}),
+        ("C5_RF", "random forest 200 trees depth 8 F=64 majorityVote", lambda: g.rf_pmml()[0], 64, 1 << 22, 0.0, {"gather": 12800, "hbm": 528, "bound": "gather", "wavefronts": "c5rf_step_smem_wavefronts_per_event"}),
         ("C5_MLP", "NeuralNetwork 64-256-256-8 rectifier + softmax", lambda: g.nn_pmml()[0], 64, 1 << 21, 0.0, {"flop": 167936, "hbm": 520, "bound": "tensor"}),
     ]
 
@@ -211,8 +211,13 @@ def config_rooflines(rate, work, pk):
             r["frac_of_int8_tensor_peak"] = tf * 10.0 / (2.0 * pk["bf16_tflops_sustained"])
             r["int8_peak_note"] = "2 x bf16_tflops_sustained of MEASURED_PEAKS.json (nominal dense int8 = 2 x bf16 on B200)"
     b = work["bound"]
+    if micro.get(work.get("wavefronts", "")):   # tree walks gather from shared memory: the pipe issues one wavefront per SM and cycle
+        wf = micro[work["wavefronts"]]; peak = 148 * (pk.get("sm_mhz_sampled") or 1965.0) * 1e6 / 1e9
+        r.update({"smem_wavefronts_per_event": wf, "smem_wavefronts_source": micro.get(work["wavefronts"].replace("_per_event", "_note")),
+                  "smem_pipe_gwavefronts": rate * wf / 1e9, "smem_pipe_peak_gwavefronts": peak, "frac_of_smem_pipe": rate * wf / 1e9 / peak})
+        b = "smem_pipe"
     r["binding"] = b
-    r["frac"] = {"hbm": r["hbm_frac"], "fp64": r.get("frac_of_fp64_fma_peak"), "gather": r.get("frac_of_l2_gather_peak"),
+    r["frac"] = {"hbm": r["hbm_frac"], "fp64": r.get("frac_of_fp64_fma_peak"), "gather": r.get("frac_of_smem_gather_peak"), "smem_pipe": r.get("frac_of_smem_pipe"),
                  "tensor": r.get("frac_of_int8_tensor_peak"), "latency": None}[b]
     return r
 
@@ -493,7 +498,7 @@ def main():
                            "l2_gather_peak_gbs": micro.get("l2_gather_8B_2MB_GBs"), "smem_gather_peak_gbs": micro.get("smem_gather_8B_random_GBs"),
                            "frac_of_l2_gather": (gather / micro["l2_gather_8B_2MB_GBs"]) if micro.get("l2_gather_8B_2MB_GBs") else None,
                            "frac_of_smem_gather": (gather / micro["smem_gather_8B_random_GBs"]) if micro.get("smem_gather_8B_random_GBs") else None}}
-        configs = {}
+        configs = {}; pk["sm_mhz_sampled"] = sm_mhz
         for k in cfg_keys:
             c = cfg_out[k]; per_gpu = c["events_per_gpu_per_step"] / (c["ms_per_step"] / 1e3)
             c["events_per_s"] = per_gpu * world; c["roofline"] = config_rooflines(per_gpu, c.pop("work"), pk)

@@ -20,6 +20,7 @@ struct KeyTiles {
   long ntiles;
   int E;                 // events per tile
   uint32_t tile_bytes;   // ceil(F/2) * E * 4
+  int uniform_mode;      // the rounding every feature's keys want (1: up, 2: down, 0: cast) when they all agree, else -1
 };
 
 constexpr int RK_THREADS = 512;
@@ -65,18 +66,27 @@ __device__ __forceinline__ void ck_rank_keys(uint32_t th_addr, uint32_t tab_addr
 
 // Direct table (model.h CkFeat): ONE 8-byte shared-memory load per value -- the bucket's first threshold image, how many thresholds lie
 // in lower buckets, how many in this one.  A bucket with more than one threshold (rare at ~4 buckets per threshold) scans on.
-__device__ __forceinline__ void ck_rank_keys_direct(uint32_t th_addr, uint32_t ent_addr, const CkFeat& cf, int mode, const double (&val)[RK_BATCH], uint32_t (&key)[RK_BATCH]) {
+__device__ __forceinline__ void ck_rank_keys_direct(uint32_t th_addr, uint32_t ent_addr, const CkFeat& cf, int mode, int uniform_mode, const double (&val)[RK_BATCH], uint32_t (&key)[RK_BATCH]) {
   uint32_t img[RK_BATCH]; uint2 en[RK_BATCH]; bool nan[RK_BATCH];
   const float top = (float)(cf.nb_e - 1u);
   const uint32_t flip = mode == 2 ? 0x80000000u : 0u;  // RD(x) = -RU(-x)
+  float xfv[RK_BATCH];
+  if (uniform_mode == 1) {          // the whole launch rounds up (double fields tested with <= / >): no per-lane choice of conversion
+#pragma unroll
+    for (int k = 0; k < RK_BATCH; k++) xfv[k] = __double2float_ru(val[k]);
+  } else {
+#pragma unroll
+    for (int k = 0; k < RK_BATCH; k++) {
+      if (mode == 0) xfv[k] = (float)val[k];
+      else {
+        const double sx = __hiloint2double(__double2hiint(val[k]) ^ (int)flip, __double2loint(val[k]));
+        xfv[k] = __uint_as_float(__float_as_uint(__double2float_ru(sx)) ^ flip);
+      }
+    }
+  }
 #pragma unroll
   for (int k = 0; k < RK_BATCH; k++) {
-    float xf;
-    if (mode == 0) xf = (float)val[k];
-    else {
-      const double sx = __hiloint2double(__double2hiint(val[k]) ^ (int)flip, __double2loint(val[k]));
-      xf = __uint_as_float(__float_as_uint(__double2float_ru(sx)) ^ flip);
-    }
+    const float xf = xfv[k];
     const uint32_t u = __float_as_uint(xf);
     img[k] = u ^ ((uint32_t)((int32_t)u >> 31) | 0x80000000u);
     nan[k] = xf != xf;
@@ -163,22 +173,35 @@ __global__ void __launch_bounds__(RK_THREADS, RK_CTAS) forest_rank_keys_kernel(c
     const double* xt = a.X + row0 * (long)F + f;
     const uint32_t* pt = a.present ? a.present + row0 * (long)a.present_stride + pword : nullptr;
     uint16_t* const gout = reinterpret_cast<uint16_t*>(kt.keys + (size_t)tile * (kt.tile_bytes / 4) + (size_t)(f >> 1) * E) + (f & 1);
-    // full tiles whose element count is a whole number of thread batches (E = 640: two) need none of the clamps
+    // full tiles whose element count is a whole number of thread batches (E = 640: two) need none of the clamps, and their
+    // addresses advance by constants: event slot of (iteration it, value k) = tid / 8 + (it * RK_BATCH + k) * RK_THREADS / 8
     auto body = [&](auto full_c) {
       constexpr bool FULL = decltype(full_c)::value;
+      constexpr int EV_STEP = RK_THREADS / 8;                               // events between two values of a thread
+      const double* xp = xt + (long)(tid >> 3) * F; const long xstep = (long)EV_STEP * F;
+      const uint32_t* pp = pt ? pt + (long)(tid >> 3) * a.present_stride : nullptr; const long pstep = (long)EV_STEP * a.present_stride;
+      uint16_t* gp = gout + 2 * (tid >> 3);
       for (int i0 = tid; i0 < total; i0 += RK_THREADS * RK_BATCH) {
         double val[RK_BATCH]; uint32_t pw[RK_BATCH], key[RK_BATCH]; int st[RK_BATCH], e[RK_BATCH]; bool present[RK_BATCH];
 #pragma unroll
         for (int k = 0; k < RK_BATCH; k++) {
-          e[k] = FULL ? (i0 + k * RK_THREADS) >> 3 : min(min(i0 + k * RK_THREADS, total - 1) >> 3, last);   // clamped: duplicates recompute a live element
-          val[k] = __ldcs(xt + e[k] * F);
-          pw[k] = pt ? __ldg(pt + e[k] * a.present_stride) : pbit;
+          if (FULL) {
+            val[k] = __ldcs(xp + k * xstep);
+            pw[k] = pp ? __ldg(pp + k * pstep) : pbit;
+          } else {
+            e[k] = min(min(i0 + k * RK_THREADS, total - 1) >> 3, last);   // clamped: duplicates recompute a live element
+            val[k] = __ldcs(xt + e[k] * F);
+            pw[k] = pt ? __ldg(pt + e[k] * a.present_stride) : pbit;
+          }
         }
 #pragma unroll
         for (int k = 0; k < RK_BATCH; k++) present[k] = (pw[k] & pbit) != 0;
         if (a.replace) {
 #pragma unroll
-          for (int k = 0; k < RK_BATCH; k++) if (!present[k]) { double rep = a.replace[row0 + e[k]]; if (rep == rep) { val[k] = rep; present[k] = true; } }
+          for (int k = 0; k < RK_BATCH; k++) if (!present[k]) {
+            const int ek = FULL ? (i0 + k * RK_THREADS) >> 3 : e[k];
+            double rep = a.replace[row0 + ek]; if (rep == rep) { val[k] = rep; present[k] = true; }
+          }
         }
 #pragma unroll
         for (int k = 0; k < RK_BATCH; k++) {
@@ -186,14 +209,16 @@ __global__ void __launch_bounds__(RK_THREADS, RK_CTAS) forest_rank_keys_kernel(c
           else { double raw = val[k]; val[k] = 0.0; st[k] = prep_value(m.prep[f], m.prep_pool, present[k], raw, val[k]); }
         }
         if (WIDE) ck_rank_keys_wide(th_addr, tab_addr, cf, val, key);
-        else if (cf.nb_e) ck_rank_keys_direct(th_addr, ent_addr, cf, mode, val, key);
+        else if (cf.nb_e) ck_rank_keys_direct(th_addr, ent_addr, cf, mode, kt.uniform_mode, val, key);
         else ck_rank_keys(th_addr, tab_addr, cf, mode, val, key);
 #pragma unroll
         for (int k = 0; k < RK_BATCH; k++) {
-          const int ee = FULL ? e[k] : min(i0 + k * RK_THREADS, total - 1) >> 3;      // the unclamped event slot of the tile
+          const int ee = FULL ? (i0 + k * RK_THREADS) >> 3 : min(i0 + k * RK_THREADS, total - 1) >> 3;      // the unclamped event slot of the tile
           if (!SIMPLE && st[k] == 2 && ee <= last) kt.fail[tile * E + ee] = 1;
-          if (owner) gout[2 * ee] = (uint16_t)(st[k] == 0 ? key[k] : 0x8000u);   // 0x8000 = missing
+          const uint16_t kv = (uint16_t)(st[k] == 0 ? key[k] : 0x8000u);   // 0x8000 = missing
+          if (owner) { if (FULL) gp[2 * EV_STEP * k] = kv; else gout[2 * ee] = kv; }
         }
+        if (FULL) { xp += RK_BATCH * xstep; if (pp) pp += RK_BATCH * pstep; gp += 2 * EV_STEP * RK_BATCH; }
       }
     };
     if (last == E - 1 && total % (RK_THREADS * RK_BATCH) == 0) body(std::true_type{}); else body(std::false_type{});

@@ -1539,6 +1539,7 @@ static cudaError_t launch_forest_compact(const DeviceModel& m, const BatchArgs& 
   const CompactDesc& cd = m.forest.compact;
   const int E = fl.events_per_cta; const long ntiles = (a.n + E - 1) / E, pass = compact_tiles_per_pass(m, fl, ntiles);
   KeyTiles kt{}; kt.keys = static_cast<uint32_t*>(scratch); kt.E = E; kt.tile_bytes = (uint32_t)((size_t)((m.F + 1) / 2) * E * 4);
+  kt.uniform_mode = m.forest.compact.uniform_mode;
   uint8_t* fail = static_cast<uint8_t*>(scratch) + (size_t)pass * kt.tile_bytes;
   const size_t rk_smem = (size_t)cd.block_smem;   // the feature block's tables
   const int mode = m.forest.classify ? (m.forest.method == FM_VOTE ? 2 : 4) : (m.forest.method == FM_CHAIN ? 3 : ((m.forest.method == FM_WSUM || m.forest.method == FM_WAVERAGE) ? 1 : 0));

@@ -98,6 +98,7 @@ constexpr int CK_SG_HDR = 8 + 4 * CK_SG_MAX;   // 72 -> trees start at 80
 struct CompactDesc {
   int enabled, wide, tree_bytes, n_blocks, block_smem;   // wide: 64-bit threshold images (thresholds that are not floats); block_smem: largest table area of one feature block
   int sparse, n_groups, group_max_bytes;                 // sparse form: blobs = the groups back to back
+  int uniform_mode;            // the rounding mode (ForestDesc::feat_mode) all features share, or -1
   int leaf_bytes;              // complete form: 8, or 8 + 8 * (most entries of a leaf's class distribution) for ensembles that average them:
                                // {u64: label nibbles in document order, entry count in the top nibble; double probability[...]}
   const uint32_t* group_off;   // n_groups + 1 byte offsets into blobs (multiples of 16)

@@ -918,6 +918,11 @@ struct ForestBuilder {
     }
     fd.enc = float_ok ? ENC_FLOAT : ENC_RANK;
     b.put(&fd.feat_mode, feat_mode);
+    {  // the key pre-pass converts without a per-lane choice when every feature wants the same rounding
+      int um = F > 0 ? feat_mode[0] : -1;
+      for (int f = 1; f < F; f++) if (feat_mode[f] != um) um = -1;
+      fd.compact.uniform_mode = float_ok ? um : -1;
+    }
     // every test of the ensemble sees a feature only through that one float: float rows rounded the same way score identically
     // (fields whose preparation could tell the double from its float image -- intervals, value lists, integers -- keep double rows)
     if (float_ok && b.cm.dev.prep_simple && b.cm.dev.derived.n_derived == 0) {
