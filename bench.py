@@ -486,6 +486,10 @@ def main():
         wf_rate = (n * wf_event / per_launch_s / 1e9) if wf_event else None
         roof = {"bound": "smem_pipe", "achieved": wf_rate, "peak": wf_peak, "unit": "Gwavefronts/s", "frac": (wf_rate / wf_peak) if wf_rate else None,
                 "wavefronts_per_event": wf_event, "wavefronts_source": micro.get("forest_step_smem_wavefronts_note"),
+                # the same with only the wavefronts a conflict-free access pattern would need (ncu's "ideal"): the replays are work
+                # the pipe really does, but not work the algorithm asks for
+                "wavefronts_per_event_conflict_free": micro.get("forest_step_smem_wavefronts_ideal_per_event"),
+                "frac_conflict_free": (n * micro["forest_step_smem_wavefronts_ideal_per_event"] / per_launch_s / 1e9 / wf_peak) if micro.get("forest_step_smem_wavefronts_ideal_per_event") else None,
                 "peak_note": "148 SMs x SM clock sampled during the timed region (%.0f MHz): one shared-memory wavefront per SM and cycle" % sm_mhz,
                 "traffic": (micro["forest_kernel_dram_bytes_per_event"] * n) if micro.get("forest_kernel_dram_bytes_per_event") else None,
                 "traffic_source": micro.get("forest_kernel_dram_note"),
