@@ -23,7 +23,7 @@ static bool plan_sliced(const DeviceModel& m, const BatchArgs& a, SlicedPlan* ou
   if (mode != 2 && a.n < (long)SG_M * g_num_sms / 2) return false;
   const SgDesc& sg = m.nn.sg;
   for (int l = 0; l < sg.n_layers; l++) if (sg::smem_plan(sg.layers[l].Kp / SG_KC, sg.layers[l].Np).bytes > (uint32_t)g_smem_optin) return false;
-  SlicedPlan p{}; const long tiles = (a.n + SG_M - 1) / SG_M, cap = sg::PASS_TILES_PER_SM * g_num_sms;
+  SlicedPlan p{}; const long tiles = (a.n + SG_M - 1) / SG_M, cap = (long)env_int("FJP_SG_PASS_TILES", (int)sg::PASS_TILES_PER_SM) * g_num_sms;
   p.pass_tiles = tiles < cap ? tiles : cap; p.pass_rows = p.pass_tiles * SG_M;
   size_t off = 256;                                            // [0]: the re-scoring counter
   for (int k = 0; k < 2; k++) { p.off_rows[k] = off; off += ((size_t)p.pass_rows * sizeof(SgRow) + 255) & ~size_t(255); }

@@ -44,7 +44,9 @@ constexpr uint32_t B_STAGE = SG_S * SG_NC * SG_KC;     // 16 KB for S = 4, N = 6
 constexpr uint32_t B_PLANE = SG_NC * SG_KC;            // 4 KB
 constexpr int TMEM_COLS = SG_S * SG_NC * 2 <= 256 ? 256 : 512;   // two accumulator sets of SG_S x 32 columns
 constexpr int MAX_KC = 4;                    // K <= 256
-constexpr long PASS_TILES_PER_SM = 8;
+constexpr long PASS_TILES_PER_SM = 24;        // a pass = one launch per layer over this many tiles per SM: each launch pays its weight staging, tensor-memory
+                                             // allocation and pipeline fill once (measured on C5-MLP: 8 -> 6.06e8, 16 -> 6.58e8, 24 -> 6.77e8, 32 -> 6.87e8 events/s;
+                                             // the work area is 2.3 KB per row of a pass: 1.0 GB at 24)
 
 struct Pass {
   const int8_t* a_in;    // [tile][Kp / 64][S][4][128][16]
