@@ -750,6 +750,7 @@ struct DensePlan { int groups, event_blocks, events, chunk, kp, warps; uint32_t 
 // ClusteringModel (FAST = 2): wt = -2 c_t, icpt = |c_t|^2, so that y_t = |x - c_t|^2 - |x|^2 and the nearest centre is the smallest y.
 struct DenseView {
   const double* wt; const double* icpt; int C;
+  const double* csq;      // FAST = 3: ClusterDesc::fast_csq
   double amax, bmax;      // max_t sum_f |wt[f][t]|, max_t |icpt_t|   (FAST = 1)  /  max |c|, unused (FAST = 2)
   int32_t* fb_count; int32_t* fb_rows;   // events the margin test hands to the FAST = 0 kernel
 };
@@ -760,6 +761,9 @@ struct DenseView {
 // FAST = 1 / 2: fused multiply-add (twice the FP64 rate) for softmax classification / nearest centre.  y then differs from the
 //   reference's by at most eps = (2 F + 8) 2^-53 (|icpt| + sum |w| |x|), bounded per event from the largest |x|; a label is written
 //   only when the winner's margin exceeds 2 eps, every other event goes on the list the FAST = 0 kernel re-scores (a.row_map).
+// FAST = 3: nearest centre over rows with missing values (present bits, at most 128 fields): a missing field counts as x = 0 in the
+//   dot products and its c^2 (= (wt / 2)^2) is taken back out of |c|^2 afterwards, field by field from the event's missing bits;
+//   JPMML's adjustment factor sum(q) / sum(present q) scales all of an event's distances alike and does not move the winner.
 template <bool HASMISS, int TC, int EPT, int FAST>
 __global__ void __launch_bounds__(256, EPT == 1 ? 3 : 2) regression_tile_kernel(const __grid_constant__ DeviceModel m, const BatchArgs a, const DensePlan pl, const DenseView dv) {
   extern __shared__ __align__(128) uint8_t smem[];
@@ -769,6 +773,7 @@ __global__ void __launch_bounds__(256, EPT == 1 ? 3 : 2) regression_tile_kernel(
   uint8_t* sts = smem + pl.off_st;                                       // chunk x (E + 4)
   double* ys = reinterpret_cast<double*>(smem + pl.off_y);               // KP x EP
   int* eflags = reinterpret_cast<int*>(smem + pl.off_flags);             // E: bit0 preparation failure, bit1 missing predictor
+  uint32_t* pws = reinterpret_cast<uint32_t*>(smem + pl.off_flags) + E;  // FAST = 3: E x 4 present words
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int eb = warp % pl.event_blocks, cg = warp / pl.event_blocks, e = eb * 32 * EPT + lane;
   for (int i = tid; i < E; i += blockDim.x) eflags[i] = 0;
@@ -811,7 +816,37 @@ __global__ void __launch_bounds__(256, EPT == 1 ? 3 : 2) regression_tile_kernel(
       asm volatile("cp.async.commit_group;" ::: "memory");
     };
     __syncthreads();   // the previous tile's epilogue is done with ys / the buffers
+    if (FAST == 3) {
+      const int W = (F + 31) >> 5;
+      for (int i = tid; i < E * 4; i += blockDim.x) {
+        const int r = i >> 2, w = i & 3; const long it = row0 + r; uint32_t bits = 0;
+        if (it < n_items && w < W) { bits = a.present[it * (long)a.present_stride + w]; if (w == W - 1 && (F & 31)) bits &= (1u << (F & 31)) - 1u; }
+        pws[i] = bits;
+      }
+      __syncthreads();
+    }
     fill(0, 0);
+    if (FAST == 3) {   // |c|^2 (the accumulators' start) is summed over every field: take the missing ones back out, two fields per step, while
+                       // the first chunk's copies are in flight
+      const double* csq = dv.csq + cg * TC;
+#pragma unroll
+      for (int v = 0; v < EPT; v++) {
+        for (int w = 0; w < ((F + 31) >> 5); w++) {
+          uint32_t miss = ~pws[(e + 32 * v) * 4 + w]; if (w == ((F + 31) >> 5) - 1 && (F & 31)) miss &= (1u << (F & 31)) - 1u;
+          while (miss) {
+            const int fa = 32 * w + __ffs(miss) - 1; miss &= miss - 1u;
+            const int fb = miss ? 32 * w + __ffs(miss) - 1 : F; miss &= miss - 1u;     // row F is all zero; 0 & 0xFFFFFFFF stays 0
+            const double2* qa = reinterpret_cast<const double2*>(csq + (size_t)fa * KP); const double2* qb = reinterpret_cast<const double2*>(csq + (size_t)fb * KP);
+            double2 va[TC / 2], vb[TC / 2];
+#pragma unroll
+            for (int k = 0; k < TC / 2; k++) { va[k] = __ldg(qa + k); vb[k] = __ldg(qb + k); }
+#pragma unroll
+            for (int k = 0; k < TC / 2; k++) { acc[v][2 * k] -= va[k].x; acc[v][2 * k + 1] -= va[k].y; acc[v][2 * k] -= vb[k].x; acc[v][2 * k + 1] -= vb[k].y; }
+          }
+        }
+      }
+    }
+
     for (int c = 0; c < nchunks; c++) {
       const int f0 = c * pl.chunk, nfc = min(pl.chunk, F - f0), buf = c & 1;
       if (c + 1 < nchunks) { fill(buf ^ 1, f0 + pl.chunk); asm volatile("cp.async.wait_group 1;" ::: "memory"); }
@@ -819,6 +854,15 @@ __global__ void __launch_bounds__(256, EPT == 1 ? 3 : 2) regression_tile_kernel(
       __syncthreads();
       const double* wp = wt + (size_t)buf * pl.chunk * KP + cg * TC; const double* xb = xs + (size_t)buf * pl.chunk * EP;
       const uint8_t* sb = sts + (size_t)buf * pl.chunk * (E + 4);
+      if (FAST == 3) {   // whatever sits in a missing slot becomes 0 before the chunk is multiplied (chunks are powers of two: whole present words, or an aligned part of one)
+        double* xw = xs + (size_t)buf * pl.chunk * EP; const int nw = (nfc + 31) >> 5;
+        for (int i = tid; i < E * nw; i += blockDim.x) {
+          const int r = i % E, wq = i / E;
+          uint32_t miss = ~pws[r * 4 + (f0 >> 5) + wq] >> (f0 & 31); if (nfc - 32 * wq < 32) miss &= (1u << (nfc - 32 * wq)) - 1u;
+          while (miss) { const int bq = __ffs(miss) - 1; miss &= miss - 1u; xw[(32 * wq + bq) * EP + r] = 0.0; }
+        }
+        __syncthreads();
+      }
       for (int f = 0; f < nfc; f++, wp += KP) {
         double x[EPT];
 #pragma unroll
@@ -833,7 +877,7 @@ __global__ void __launch_bounds__(256, EPT == 1 ? 3 : 2) regression_tile_kernel(
           double2 w = w2[k];
 #pragma unroll
           for (int v = 0; v < EPT; v++) {
-            if (FAST) { acc[v][2 * k] = fma(w.x, x[v], acc[v][2 * k]); acc[v][2 * k + 1] = fma(w.y, x[v], acc[v][2 * k + 1]); }
+            if (FAST != 0) { acc[v][2 * k] = fma(w.x, x[v], acc[v][2 * k]); acc[v][2 * k + 1] = fma(w.y, x[v], acc[v][2 * k + 1]); }
             else { acc[v][2 * k] += w.x * x[v]; acc[v][2 * k + 1] += w.y * x[v]; }
           }
         }
@@ -856,13 +900,15 @@ __global__ void __launch_bounds__(256, EPT == 1 ? 3 : 2) regression_tile_kernel(
         int fl = HASMISS ? eflags[e] : 0;
         if (fl & 1) write_out(a, row, 0, ST_PREP, -1);
         else if (fl & 2) write_out(a, row, 0, m.target_status ? m.target_status : ST_EVAL, -1);
-        else if (FAST == 2) {
+        else if (FAST == 2 || FAST == 3) {
           // nearest centre: smallest y, the first one on ties -- decided here only when the runner-up is farther than the bound
           const double xmax = __hiloint2double(xm[v] + 1, 0), s = xmax + dv.amax;
           const double eps = (double)(2 * F + 8) * 2.220446049250313e-16 * (double)F * s * s;
           int best = 0; double yb = ys[e], y2 = __longlong_as_double(0x7FF0000000000000LL);
           for (int i = 1; i < C; i++) { const double y = ys[i * EP + e]; if (y < yb) { y2 = yb; yb = y; best = i; } else y2 = fmin(y2, y); }
-          if (C == 1 || (y2 - yb > 2.0 * eps && s < 1e150)) write_label(m, a, row, best, best + 1); else rescore = true;
+          bool any_present = true;
+          if (FAST == 3) { const uint32_t* pw = pws + e * 4; any_present = (pw[0] | pw[1] | pw[2] | pw[3]) != 0u; }   // no field at all: the exact kernel's business
+          if (any_present && (C == 1 || (y2 - yb > 2.0 * eps && s < 1e150))) write_label(m, a, row, best, best + 1); else rescore = true;
         }
         else if (!rd.classify) write_out(a, row, apply_target(m.tx, link_fn(rd.norm, ys[e])), m.target_status, -1);
         else {
@@ -1597,7 +1643,7 @@ static cudaError_t launch_dense_tile(const DeviceModel& m, const BatchArgs& a, c
     const size_t xbytes = (size_t)2 * chunk * EP * 8, ybytes = (size_t)pl.kp * EP * 8;
     pl.off_y = (uint32_t)off; off += xbytes > ybytes ? xbytes : ybytes;   // ys (epilogue only) reuses the input buffers
     pl.off_st = (uint32_t)off; if (hasmiss) off += (size_t)2 * chunk * (pl.events + 4); off = (off + 15) & ~size_t(15);
-    pl.off_flags = (uint32_t)off; off += (size_t)pl.events * 4; pl.smem_bytes = (uint32_t)((off + 127) & ~size_t(127));
+    pl.off_flags = (uint32_t)off; off += (size_t)pl.events * (fast == 3 ? 20 : 4); pl.smem_bytes = (uint32_t)((off + 127) & ~size_t(127));
     if (pl.smem_bytes <= smem_cap || chunk == 1) break;
   }
   pl.chunk = chunk;
@@ -1608,6 +1654,7 @@ static cudaError_t launch_dense_tile(const DeviceModel& m, const BatchArgs& a, c
 #define FJP_RT2(HM, TCV) do { if (ept == 2) FJP_RT(HM, TCV, 2, 0); else FJP_RT(HM, TCV, 1, 0); } while (0)
   if (fast == 1) { if (tc == 8) FJP_RT(false, 8, 2, 1); else if (tc == 10) FJP_RT(false, 10, 2, 1); else FJP_RT(false, 12, 2, 1); }
   else if (fast == 2) { if (tc == 8) FJP_RT(false, 8, 2, 2); else if (tc == 10) FJP_RT(false, 10, 2, 2); else FJP_RT(false, 12, 2, 2); }
+  else if (fast == 3) { if (tc == 8) FJP_RT(false, 8, 2, 3); else if (tc == 10) FJP_RT(false, 10, 2, 3); else FJP_RT(false, 12, 2, 3); }
   else if (hasmiss) { if (tc == 8) FJP_RT2(true, 8); else if (tc == 10) FJP_RT2(true, 10); else FJP_RT2(true, 12); }
   else { if (tc == 8) FJP_RT2(false, 8); else if (tc == 10) FJP_RT2(false, 10); else FJP_RT2(false, 12); }
 #undef FJP_RT2
@@ -1620,7 +1667,8 @@ static cudaError_t launch_dense_tile(const DeviceModel& m, const BatchArgs& a, c
 size_t dense_fma_scratch_bytes(const DeviceModel& m, const BatchArgs& a) {
   if (sliced_dense_takes(m, a)) return 256 + (((size_t)a.n * 4 + 255) & ~size_t(255));   // the fused tensor-core layer keeps the same re-scoring list
   const int mode = env_int("FJP_DENSE_FMA", 1);
-  if (!mode || a.present || a.replace || !m.prep_identity || a.row_map || a.node_ids) return 0;
+  const bool masked_centres = a.present && m.kind == MK_CLUSTERING && m.F <= 128 && m.F >= 32;   // FAST = 3 of the tile kernel
+  if (!mode || (a.present && !masked_centres) || a.replace || !m.prep_identity || a.row_map || a.node_ids) return 0;
   query_device();
   if (mode != 2 && a.n < 64L * g_num_sms) return 0;
   if (m.kind == MK_REGRESSION) { if (!(m.reg.dense && m.reg.classify && m.reg.norm == NORM_SOFTMAX && m.reg.n_tables <= REG_MAXC)) return 0; }
@@ -1675,10 +1723,10 @@ cudaError_t launch_score(const DeviceModel& m, const BatchArgs& a, cudaStream_t 
       if (slice_scratch && dense_fma_scratch_bytes(m, a)) {
         // |x - c|^2 = |x|^2 + (|c|^2 - 2 x.c): one fused multiply-add per term instead of sub, mul, add; the nearest centre is decided
         // here when the runner-up is farther than the rounding bound, the other events go to the exact kernel below
-        DenseView dv{}; dv.wt = m.cluster.fast_wt; dv.icpt = m.cluster.fast_icpt; dv.C = m.cluster.k; dv.amax = m.cluster.cmax;
+        DenseView dv{}; dv.wt = m.cluster.fast_wt; dv.icpt = m.cluster.fast_icpt; dv.C = m.cluster.k; dv.amax = m.cluster.cmax; dv.csq = m.cluster.fast_csq;
         dv.fb_count = static_cast<int32_t*>(slice_scratch); dv.fb_rows = dv.fb_count + 64;
         cudaError_t e = cudaMemsetAsync(dv.fb_count, 0, 4, s); if (e != cudaSuccess) return e;
-        e = launch_dense_tile(m, a, dv, false, 2, s); if (e != cudaSuccess) return e;
+        e = launch_dense_tile(m, a, dv, false, a.present ? 3 : 2, s); if (e != cudaSuccess) return e;
         if (launches) (*launches)++;
         BatchArgs fb = a; fb.row_map = dv.fb_rows; fb.n_dev = dv.fb_count;
         size_t sm = (size_t)nf * CL_XS * 8 + (((size_t)nf * CL_SS + 15) & ~size_t(15)) + CL_G * CL_E * 12;

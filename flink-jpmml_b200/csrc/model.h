@@ -153,6 +153,7 @@ struct ClusterDesc {
   // FMA form (fast models): |x - c_t|^2 - |x|^2 = fast_icpt[t] + sum_f fast_wt[f][t] x_f, fast_wt = -2 c transposed [nf][KP] (KP as for
   // the regression tables: k rounded up to 8 / 10 / 12 per thread), fast_icpt = |c_t|^2; cmax = largest |centre coordinate|
   const double* fast_wt; const double* fast_icpt; double cmax;
+  const double* fast_csq;     // c^2 transposed [nf + 1][KP], the last row zero: what a missing field takes back out of |c_t|^2
 };
 
 static constexpr int MAX_LAYERS = 8;

@@ -448,19 +448,19 @@ void compile_clustering(const XNode& m, Builder& b) {
   for (size_t i = 0; i < nf; i++) if (slot[i] != (int)i) d.slots_identity = 0;
   b.put(&d.slot, slot); b.put(&d.weight, w); b.put(&d.q, q); b.put(&d.compare, cmp); b.put(&d.sim_scale, scale); b.put(&d.centers, centers);
   {  // FMA form for the dense tile kernel (model.h): -2 c transposed, |c|^2
-    std::vector<double> fw, fi; d.cmax = 0; bool finite = true;
+    std::vector<double> fw, fi, fq; d.cmax = 0; bool finite = true;
     if (fast && d.slots_identity && d.k <= 64) {
       size_t tcs = 8, bestpad = ~size_t(0); for (size_t cand : {size_t(8), size_t(10), size_t(12)}) { size_t pad = ((size_t)d.k + cand - 1) / cand * cand - (size_t)d.k; if (pad < bestpad) { bestpad = pad; tcs = cand; } }
-      const size_t KP = ((size_t)d.k + tcs - 1) / tcs * tcs; fw.assign(KP * nf, 0.0); fi.assign(KP, 0.0);
+      const size_t KP = ((size_t)d.k + tcs - 1) / tcs * tcs; fw.assign(KP * nf, 0.0); fi.assign(KP, 0.0); fq.assign(KP * (nf + 1), 0.0);   // fq: one more, all-zero row
       for (int t = 0; t < d.k; t++) {
         double s2 = 0;
-        for (size_t f = 0; f < nf; f++) { const double c = centers[(size_t)t * nf + f]; finite = finite && std::isfinite(c); fw[f * KP + t] = -2.0 * c; s2 += c * c; d.cmax = std::max(d.cmax, std::fabs(c)); }
+        for (size_t f = 0; f < nf; f++) { const double c = centers[(size_t)t * nf + f]; finite = finite && std::isfinite(c); fw[f * KP + t] = -2.0 * c; fq[f * KP + t] = c * c; s2 += c * c; d.cmax = std::max(d.cmax, std::fabs(c)); }
         fi[t] = s2;
       }
-      if (!finite || !(d.cmax < 1e150)) { fw.clear(); fi.clear(); }
+      if (!finite || !(d.cmax < 1e150)) { fw.clear(); fi.clear(); fq.clear(); }
     }
-    if (fw.empty()) { d.fast_wt = nullptr; d.fast_icpt = nullptr; }
-    else { b.put(&d.fast_wt, fw); b.put(&d.fast_icpt, fi); }
+    if (fw.empty()) { d.fast_wt = nullptr; d.fast_icpt = nullptr; d.fast_csq = nullptr; }
+    else { b.put(&d.fast_wt, fw); b.put(&d.fast_icpt, fi); b.put(&d.fast_csq, fq); }
   }
   b.set_labels(ids, true);
   b.cm.dev.target_status = b.has_target ? ST_OK : ST_EXTRACT;  // no named target field -> nothing to extract

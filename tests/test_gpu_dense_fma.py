@@ -85,3 +85,31 @@ def test_kmeans_shapes_and_ties(engine, gen, oracle, monkeypatch, k, F, n):
     assert took == n
     if k >= 4:
         assert (o["aux"] != 4).all()
+
+
+@pytest.mark.parametrize("k,F,n,p_missing", [(64, 128, 64 * 148 * 2 + 91, 0.05), (13, 50, 3000, 0.3), (8, 32, 2000, 0.9), (20, 100, 4000, 0.02)])
+def test_kmeans_with_missing_values_on_the_fma_path(engine, gen, oracle, monkeypatch, k, F, n, p_missing):
+    """BASELINE.json config 2, 5 %-missing variant (and sparser / denser masks, a field count that is no multiple of 32, events
+    with no field at all): a missing field is x = 0 in the dot products and its c^2 comes back out of |c|^2; cluster ids
+    bit-exact with the oracle, which skips the field and applies JPMML's adjustment factor."""
+    monkeypatch.setenv("FJP_DENSE_FMA", "2")
+    rng = np.random.default_rng(k * 1000 + F)
+    cent = rng.standard_normal((k, F))
+    if k >= 4:
+        cent[3] = cent[1]
+    pm = gen.kmeans_pmml(cent)
+    X, pres, pb = gen.events(n, F, 35, p_missing)
+    X[~pres] = np.nan                                             # whatever sits in a missing slot must not matter
+    X[:20] = cent[rng.integers(0, k, 20)]; pres[:20] = True       # on a centre
+    pres[20:30] = False                                           # no field at all
+    pb = gen.pack_present(pres)
+    m = engine.compile(pm)
+    c0 = engine.fast_path_counts
+    r = engine.score(m, X, pb)
+    c1 = engine.fast_path_counts
+    o = oracle.OracleModel(pm).predict(X, pb, nthreads=os.cpu_count() or 4)
+    assert np.array_equal(r["status"], o["status"])
+    ok = o["status"] == 0
+    assert np.array_equal(r["score"][ok], o["score"][ok]) and np.array_equal(r["aux"][ok], o["aux"][ok])
+    took, back = c1[2] - c0[2], c1[3] - c0[3]
+    assert took == n and 10 <= back < (0.05 if p_missing < 0.5 else 0.5) * n + 40, (took, back)   # back: the events with no field, exact ties, thin margins

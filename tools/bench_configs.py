@@ -64,7 +64,9 @@ configs.append(("RF 200x8 F=64 average of leaf distributions (scikit-learn style
 configs.append(("GBT 300 unbalanced trees, max depth 14, F=50 (leaf-wise growth)", g.gbt_pruned_pmml(T=300, max_depth=14, F=50, seed=3, p_leaf=0.3), 50, 1 << 21, 0.10, {"hbm": 416}))
 for name, pm, F, n, pmiss, work in configs:
     if args.only and args.only not in name: continue
+    fp0 = eng.fast_path_counts
     m, rate, ms, ok, X, P = time_model(pm, F, n, pmiss)
+    fp1 = eng.fast_path_counts
     out = {"config": name, "events_per_s": rate, "ms": ms, "n": n, "rows_ok": ok, "model": m.describe,
            "hbm_frac": rate * work["hbm"] / 1e9 / peaks["hbm_gbs"]}
     if "gather" in work:
@@ -73,6 +75,8 @@ for name, pm, F, n, pmiss, work in configs:
     if "dp_instr" in work:   # unfused double mul+add: 2 flop per (mul, add) pair; compare with the measured unfused FP64 rate
         out["fp64_unfused_tflops"] = rate * work["dp_instr"] / 1e12
         out["frac_fp64_unfused"] = out["fp64_unfused_tflops"] / micro["fp64_mul_add_unfused_TFLOPs"]
+    if fp1[2] > fp0[2]: out["fma_path_rescored_fraction"] = (fp1[3] - fp0[3]) / (fp1[2] - fp0[2])
+    if fp1[0] > fp0[0]: out["tensor_path_rescored_fraction"] = (fp1[1] - fp0[1]) / (fp1[0] - fp0[0])
     if args.cpu: out["cpu_oracle"] = cpu_rate(pm, X, P)
     print(json.dumps(out), flush=True)
     del X, P; torch.cuda.empty_cache()
