@@ -348,3 +348,21 @@ def test_submit_many_scores_every_batch_with_its_own_model(engine, oracle, gen):
         assert np.array_equal(sc[ok].view(np.int64), r["score"][ok].view(np.int64)) and np.array_equal(sc[ok], o["score"][ok])
     bad = (Desc * 1)(Desc(models[0]._h, keep[0][0].ctypes.data, None, None, 10, 7, keep[0][2].ctypes.data, keep[0][3].ctypes.data))
     assert L.fjp_submit_many(engine._h, bad, 1, C.byref(ticket)) != 0 and ticket.value == -1      # wrong vector size: refused as a whole
+
+
+@pytest.mark.parametrize("rows,n", [(4096, 3 * 4096 + 1), (100000, 290000), (100000, 265537), (70000, 70001)])
+def test_host_entry_points_chunk_pipeline(engine, oracle, gen, monkeypatch, rows, n):
+    """The host-buffer entry points cut a batch into chunks over two stream slots, chain the copy-ins with an event and taper the
+    last chunk (half, then the rest): whatever the cut, every row gets its own score -- double rows and float rows against
+    the oracle (S/api/PmmlModel.scala:109-119 scores one event; here the batch boundary must not show)."""
+    monkeypatch.setenv("FJP_CHUNK_ROWS", str(rows))
+    pm, _ = gen.gbt_pmml(T=12, depth=4, F=8, seed=901)
+    m, om = engine.compile(pm), oracle.OracleModel(pm)
+    X, pres, pb = gen.events(n, 8, 902, 0.1)
+    o = om.predict(X, pb, nthreads=8)
+    r = engine.score(m, X, pb)
+    assert np.array_equal(r["status"], o["status"]) and np.array_equal(r["score"].view(np.int64), o["score"].view(np.int64))
+    modes = engine.float_row_modes(m)
+    assert modes is not None
+    f = engine.score_f32(m, engine.narrow_rows(X, modes), pb)
+    assert np.array_equal(f["status"], o["status"]) and np.array_equal(f["score"].view(np.int64), o["score"].view(np.int64))
