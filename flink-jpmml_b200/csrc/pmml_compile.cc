@@ -17,6 +17,7 @@
 #include <functional>
 #include <limits>
 #include <map>
+#include <optional>
 #include <stdexcept>
 #include <tuple>
 #include <unordered_map>
@@ -121,6 +122,30 @@ struct Builder {
   sv keep(sv name) { names_.emplace_back(name); return names_.back(); }
   std::vector<uint8_t> slot_dtype;
   std::string target_name; bool has_target = false; uint8_t target_dtype = DT_DOUBLE;
+  // LocalTransformations of models nested in Segments: every DerivedField has a slot of its own in the augmented row (its
+  // expression is a pure function of fields known before any model runs, so the pre-pass evaluates it with all the others); its
+  // NAME is bound to that slot only while the nested model is compiled (two segments may use one name for different things)
+  struct ScopedName { sv name; int dict_index, slot; };
+  std::unordered_map<const XNode*, std::vector<ScopedName>> nested_scopes;
+  struct Scope {
+    Builder& b; std::vector<std::tuple<sv, int, int>> saved;   // name, previous dict index (-1: none), previous slot (-2: none)
+    Scope(Builder& bb, const XNode* model) : b(bb) {
+      auto it = b.nested_scopes.find(model); if (it == b.nested_scopes.end()) return;
+      for (auto& sn : it->second) bind(sn);
+    }
+    void bind(const ScopedName& sn) {
+      auto di = b.dict_idx.find(sn.name); auto si = b.active_slot.find(sn.name);
+      saved.emplace_back(sn.name, di == b.dict_idx.end() ? -1 : di->second, si == b.active_slot.end() ? -2 : si->second);
+      b.dict_idx[sn.name] = sn.dict_index; b.active_slot[sn.name] = sn.slot;
+    }
+    ~Scope() {
+      for (auto it = saved.rbegin(); it != saved.rend(); ++it) {
+        const sv n = std::get<0>(*it);
+        if (std::get<1>(*it) < 0) b.dict_idx.erase(n); else b.dict_idx[n] = std::get<1>(*it);
+        if (std::get<2>(*it) == -2) b.active_slot.erase(n); else b.active_slot[n] = std::get<2>(*it);
+      }
+    }
+  };
 
   template <class T> void put(const T* const* field_addr, const std::vector<T>& v) {
     size_t off = (cm.blob.size() + 255) & ~size_t(255);
@@ -165,8 +190,8 @@ void read_dictionary(const XNode& root, Builder& b) {
   });
 }
 
-void check_nested_schema(const XNode& model) {
-  if (const XNode* lt = model.child("LocalTransformations")) if (lt->first) unsupported("LocalTransformations");
+void check_nested_schema(const XNode& model, bool transformations_ok = false) {
+  if (const XNode* lt = model.child("LocalTransformations")) if (lt->first && !transformations_ok) unsupported("LocalTransformations in this nested model");
   if (const XNode* ms = model.child("MiningSchema"))
     ms->each("MiningField", [&](const XNode& f) {
       if (f.has("missingValueReplacement") || f.attr("outliers", "asIs") != "asIs" ||
@@ -392,6 +417,36 @@ void read_derived(const XNode& root, const XNode& model, Builder& b) {
     Field fl{name, dt, f->attr("optype", "continuous") == "continuous", nullptr};
     b.dict_idx[b.keep(name)] = (int)b.dict.size(); b.dict.push_back(fl);
     b.active_slot[b.keep(name)] = b.cm.dev.F; b.slot_dtype.push_back(dt); b.cm.dev.F++;
+  }
+  {  // nested models (TreeModels of a Segmentation, the MiningModels inside a modelChain): their LocalTransformations, in document order
+    std::function<void(const XNode&)> scan = [&](const XNode& parent) {
+      const XNode* sg = parent.child("Segmentation"); if (!sg) return;
+      sg->each("Segment", [&](const XNode& seg) {
+        for (const XNode* nm = seg.first; nm; nm = nm->next) {
+          if (nm->name != "TreeModel" && nm->name != "MiningModel") continue;
+          Builder::Scope scope(b, nullptr);   // names of this model's fields become visible one by one, to the fields after them
+          if (const XNode* lt = nm->child("LocalTransformations")) lt->each("DerivedField", [&](const XNode& f) {
+            uint8_t dt = dtype_of(f.attr("dataType", "double"));
+            if (dt != DT_DOUBLE && dt != DT_FLOAT && dt != DT_INTEGER) unsupported("non-numeric DerivedField");
+            const XNode* ex = nullptr;
+            for (const XNode* k = f.first; k && !ex; k = k->next) if (k->name != "Extension" && k->name != "Value") ex = k;
+            if (!ex) malformed("DerivedField without expression");
+            dc.emit(*ex, 0);
+            prog_off.push_back((int32_t)dc.ops.size()); dtypes.push_back(dt);
+            const sv user = b.keep(f.attr("name"));
+            const sv unique = b.keep(std::string(user) + "\x01" + std::to_string(b.dict.size()));
+            Field fl{std::string(unique), dt, f.attr("optype", "continuous") == "continuous", nullptr};
+            const int di = (int)b.dict.size(), slot = b.cm.dev.F;
+            b.dict_idx[unique] = di; b.dict.push_back(fl); b.slot_dtype.push_back(dt); b.cm.dev.F++;
+            Builder::ScopedName sn{user, di, slot};
+            b.nested_scopes[nm].push_back(sn); scope.bind(sn);
+          });
+          if (nm->name == "MiningModel") scan(*nm);   // (with this model's names still bound)
+        }
+      });
+    };
+    scan(model);
+    dd.n_derived = (int)dtypes.size();
   }
   b.put(&dd.prog_off, prog_off); b.put(&dd.ops, dc.ops); b.put(&dd.pool, dc.pool); b.put(&dd.dtype, dtypes);
   if (dd.n_derived) {   // the family kernel reads already prepared values: identity preparation over the augmented row
@@ -660,7 +715,8 @@ struct ForestBuilder {
   }
 
   void add_tree(const XNode& tm, double weight, bool nested, const XNode* seg_pred = nullptr) {
-    if (nested) check_nested_schema(tm);
+    if (nested) check_nested_schema(tm, true);
+    std::optional<Builder::Scope> scope; scope.emplace(b, &tm);   // the tree's own LocalTransformations are visible inside the tree only
     TreeCtx cx; cx.epoch = next_epoch(); sv mvs = tm.attr("missingValueStrategy", "none");
     cx.mvs = mvs == "none" ? 0 : mvs == "defaultChild" ? 1 : mvs == "lastPrediction" ? 2 : mvs == "nullPrediction" ? 3 : -1;
     if (cx.mvs < 0) unsupported("missingValueStrategy " + std::string(mvs));
@@ -682,6 +738,7 @@ struct ForestBuilder {
     int32_t r;
     if (rp.name == "False") r = LEAF_NULL;
     else { int32_t body = enter(*root, LEAF_NULL, cx); cons++; r = emit_pred(rp, body, LEAF_NULL, LEAF_NULL); cons--; }   // a root test that is not TRUE: null prediction
+    scope.reset();   // the Segment's predicate belongs to the enclosing model's scope
     if (seg_pred && seg_pred->name != "True") { int32_t skip = skip_successor(); cons++; r = emit_pred(*seg_pred, r, skip, skip); cons--; }
     roots.push_back(r); weights.push_back(weight);
   }
@@ -1080,7 +1137,8 @@ void compile_model_chain(const XNode& m, const XNode& sg, Builder& b) {
     size_t before = fb.roots.size();
     if (tm && !inner) { fb.add_tree(*tm, 1.0, true); }   // the tree's own Targets are folded into its leaves by add_tree
     else {
-      check_nested_schema(*inner);
+      check_nested_schema(*inner, true);
+      Builder::Scope inner_scope(b, inner);   // the inner model's LocalTransformations, visible to its trees
       const XNode* isg = inner->child("Segmentation"); if (!isg) malformed("MiningModel without Segmentation");
       sv imm = isg->attr("multipleModelMethod");
       if (imm == "average") cs.average = 1; else if (imm != "sum") unsupported("modelChain: inner multipleModelMethod " + std::string(imm));

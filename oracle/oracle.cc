@@ -1107,6 +1107,45 @@ static DExpr load_dexpr(const Xml& e, const Doc& d, const FnEnv* env = nullptr) 
 
 static std::unique_ptr<Model> load_model(const Xml& e, const Doc& d);
 
+// LocalTransformations of a model nested in a Segment: its DerivedFields are visible inside that model only (two segments may use
+// one name for different things).  Expressions are pure functions of fields known before any model runs, so they are evaluated
+// up front with all the others -- each in a context slot of its own -- and the NAME is bound to that slot only while the nested
+// model is being loaded (everything after loading works on slots).
+struct NestedSink { std::vector<DerivedField>* derived; const FnEnv* env; int first_output_slot, end_output_slot; };
+static thread_local NestedSink* g_nested = nullptr;
+static bool dexpr_reads_slots(const DExpr& x, int lo, int hi) {
+  if (x.kind != DExpr::CONST && x.kind != DExpr::APPLY && x.kind != DExpr::PARAM && x.kind != DExpr::USERCALL && x.slot >= lo && x.slot < hi) return true;
+  for (auto& a : x.args) if (dexpr_reads_slots(a, lo, hi)) return true;
+  return false;
+}
+struct NestedScope {
+  Doc* doc = nullptr; std::vector<std::tuple<std::string, bool, int>> saved;   // name, had a binding before, that binding
+  NestedScope(const Xml& model, const Doc& d) {
+    const Xml* lt = model.child("LocalTransformations");
+    if (!lt || !g_nested) return;
+    doc = const_cast<Doc*>(&d);
+    for (auto* f : lt->children("DerivedField")) {
+      DType dt = parse_dtype(f->get("dataType", "double"));
+      if (dt == DT_STRING || dt == DT_OTHER || dt == DT_BOOLEAN) throw Unsupported("non-numeric DerivedField");
+      const Xml* ex = nullptr; for (auto& k : f->kids) if (k->name != "Extension" && k->name != "Value") { ex = k.get(); break; }
+      if (!ex) throw Unsupported("DerivedField without expression");
+      DExpr expr = load_dexpr(*ex, *doc, g_nested->env);
+      if (dexpr_reads_slots(expr, g_nested->first_output_slot, g_nested->end_output_slot)) throw Unsupported("nested DerivedField over another model's output");
+      const std::string user = f->get("name"); const int slot = (int)doc->fields.size();
+      DataField df; df.name = user + "\x01" + std::to_string(slot); df.op = parse_optype(f->get("optype", "continuous")); df.dt = dt;
+      doc->index[df.name] = slot; doc->fields.push_back(df);
+      g_nested->derived->push_back({slot, dt, std::move(expr)});
+      auto it = doc->index.find(user);
+      saved.emplace_back(user, it != doc->index.end(), it != doc->index.end() ? it->second : -1);
+      doc->index[user] = slot;
+    }
+  }
+  ~NestedScope() {
+    if (!doc) return;
+    for (auto it = saved.rbegin(); it != saved.rend(); ++it) { if (std::get<1>(*it)) doc->index[std::get<0>(*it)] = std::get<2>(*it); else doc->index.erase(std::get<0>(*it)); }
+  }
+};
+
 static void number_tree(TreeNode& n, int& counter) {
   counter++;
   double v;
@@ -1262,7 +1301,10 @@ static std::unique_ptr<Model> load_model(const Xml& e, const Doc& d) {
       seg.pred = load_pred(*pe, d);
       for (auto& k : s->kids) {
         const std::string& n = k->name;
-        if (n == "TreeModel" || n == "RegressionModel" || n == "MiningModel" || n == "ClusteringModel" || n == "NeuralNetwork" || n == "GeneralRegressionModel") seg.model = load_model(*k, d);
+        if (n == "TreeModel" || n == "RegressionModel" || n == "MiningModel" || n == "ClusteringModel" || n == "NeuralNetwork" || n == "GeneralRegressionModel") {
+          NestedScope scope(*k, d);   // the model's own LocalTransformations
+          seg.model = load_model(*k, d);
+        }
       }
       if (!seg.model) throw Unsupported("Segment without a supported model");
       m->segments.push_back(std::move(seg));
@@ -1412,13 +1454,6 @@ static std::unique_ptr<Loaded> load(const char* data, size_t len) {
   }
   if (!me) throw Unsupported("no supported model element");
   if (auto* lt = me->child("LocalTransformations")) for (auto* f : lt->children("DerivedField")) derived_xml.push_back(f);
-  {  // transformations inside nested models are out of scope
-    std::function<void(const Xml&, int)> scan = [&](const Xml& x, int depth) {
-      if (x.name == "LocalTransformations" && depth > 1 && !x.kids.empty()) throw Unsupported("LocalTransformations in a nested model");
-      for (auto& k : x.kids) scan(*k, depth + 1);
-    };
-    scan(*me, 0);
-  }
   for (auto* f : derived_xml) {   // each derived field gets a context slot; its expression may use the ones before it
     DType dt = parse_dtype(f->get("dataType", "double"));
     if (dt == DT_STRING || dt == DT_OTHER || dt == DT_BOOLEAN) throw Unsupported("non-numeric DerivedField");
@@ -1429,6 +1464,7 @@ static std::unique_ptr<Loaded> load(const char* data, size_t len) {
     L->doc.index[df.name] = (int)L->doc.fields.size(); L->doc.fields.push_back(df);
     L->derived.push_back({(int)L->doc.fields.size() - 1, dt, std::move(expr)});
   }
+  const int first_output_slot = (int)L->doc.fields.size();
   {  // Output fields anywhere in the model tree are addressable by later modelChain segments: give them context slots
     std::function<void(const Xml&)> scan = [&](const Xml& x) {
       if (x.name == "OutputField" && !L->doc.index.count(x.get("name"))) {
@@ -1440,7 +1476,10 @@ static std::unique_ptr<Loaded> load(const char* data, size_t len) {
     scan(*me);
   }
   g_doc = &L->doc;
-  L->model = load_model(*me, L->doc);
+  NestedSink sink{&L->derived, &fn_env, first_output_slot, (int)L->doc.fields.size()};
+  g_nested = &sink;
+  try { L->model = load_model(*me, L->doc); } catch (...) { g_nested = nullptr; throw; }
+  g_nested = nullptr;
   for (auto& mf : L->model->mining) {
     if (mf.usage == "active") { L->active.push_back(&mf); L->active_slots.push_back(L->doc.slot(mf.name)); L->active_names.push_back(mf.name); }
   }

@@ -191,6 +191,23 @@ def cases():
     Xr, Pr = _rows((1, -1), (-1, -1), (None, -1), (1, 1))
     out.append(("tree/root-predicate", doc(AB, tree_model(["a", "b"], rooted, strategy="lastPrediction", no_true="returnLastPrediction")), Xr, Pr, None,
                 [(0, 1.0, 2), (3, None, None), (3, None, None), (0, 9.0, 1)]))
+    # ---- LocalTransformations inside nested models: a DerivedField is visible in its own model only -- both trees call theirs "d"
+    apply2 = lambda fn, x, y: f'<Apply function="{fn}">{x}{y}</Apply>'
+    fref = lambda f: f'<FieldRef field="{f}"/>'
+    kdbl = lambda v: f'<Constant dataType="double">{v}</Constant>'
+    dfield = lambda n, ex: f'<DerivedField name="{n}" optype="continuous" dataType="double">{ex}</DerivedField>'
+    lt1 = f'<LocalTransformations>{dfield("d", apply2("*", fref("a"), kdbl(2)))}</LocalTransformations>'
+    lt2 = f'<LocalTransformations>{dfield("d", apply2("+", fref("b"), kdbl(1)))}{dfield("e", apply2("*", fref("d"), fref("d")))}</LocalTransformations>'
+    nt1 = ('<Node id="1" defaultChild="3"><True/><Node id="2" score="10"><SimplePredicate field="d" operator="lessOrEqual" value="3"/></Node>'
+           '<Node id="3" score="20"><SimplePredicate field="d" operator="greaterThan" value="3"/></Node></Node>')
+    nt2 = ('<Node id="1" defaultChild="3"><True/><Node id="2" score="1"><SimplePredicate field="e" operator="greaterThan" value="4"/></Node>'
+           '<Node id="3" score="2"><SimplePredicate field="e" operator="lessOrEqual" value="4"/></Node></Node>')
+    nseg = lambda i, pred, lt, nodes: f'<Segment id="{i}">{pred}{tree_model(["a", "b"], nodes, strategy="defaultChild", target=None, extra=lt)}</Segment>'
+    nested = pm_("sum", nseg(1, "<True/>", lt1, nt1), nseg(2, "<True/>", lt2, nt2), pseg(3, 1, gt("a", 1), const(100)))
+    #   (1,5): d1 = 2 -> 10; d2 = 6, e = 36 -> 1; a > 1 false.   (2,-1): d1 = 4 -> 20; d2 = 0, e = 0 -> 2; +100.
+    #   (None,None): both derived values missing -> defaultChild: 20 + 2; predicate UNKNOWN.   (2,5): 20 + 1 + 100
+    Xl, Pl = _rows((1, 5), (2, -1), (None, None), (2, 5))
+    out.append(("mining/nested-local-transformations", nested, Xl, Pl, None, [(0, 11.0, None), (0, 122.0, None), (0, 22.0, None), (0, 121.0, None)]))
     # ---- clustering variants: 1-D centres 0 and 10 plus a second field; cluster ids "5" and "x"
     def clu(measure, compare="absDiff", extra="", ids=("5", "x"), weights=""):
         body = (f'<ClusteringModel modelName="c" functionName="clustering" modelClass="centerBased" numberOfClusters="2">'

@@ -109,3 +109,36 @@ def test_radial_basis_layer(engine, oracle, gen):
     assert np.array_equal(r["score"][ok], o["score"][ok])
     np.testing.assert_allclose(r["probs"][ok], o["probs"][ok], rtol=1e-6)
     assert len(np.unique(o["score"][ok])) >= 2
+
+
+def test_local_transformations_of_nested_trees(engine, oracle, gen):
+    """Every tree of the ensemble defines its own DerivedField -- all of them named "d" -- in its LocalTransformations; the names are
+    scoped to their trees, the values are computed once per event by the derived-field pre-pass.  Against the oracle and numpy."""
+    from hand_pmml import doc, schema, tree_model
+    T, F, n = 24, 6, 30000
+    rng = np.random.default_rng(77)
+    names = [f"x{i}" for i in range(F)]
+    thr = np.round(rng.normal(0, 1.2, T), 3); va = np.round(rng.normal(0, 1, T), 3); vb = np.round(rng.normal(0, 1, T), 3); dflt = rng.integers(0, 2, T)
+    segs = []
+    for k in range(T):
+        i, j = k % F, (k + 1) % F
+        lt = (f'<LocalTransformations><DerivedField name="d" optype="continuous" dataType="double"><Apply function="+">'
+              f'<FieldRef field="x{i}"/><FieldRef field="x{j}"/></Apply></DerivedField></LocalTransformations>')
+        nodes = (f'<Node id="1" defaultChild="{2 + dflt[k]}"><True/><Node id="2" score="{float(va[k])!r}"><SimplePredicate field="d" operator="lessOrEqual" value="{float(thr[k])!r}"/></Node>'
+                 f'<Node id="3" score="{float(vb[k])!r}"><SimplePredicate field="d" operator="greaterThan" value="{float(thr[k])!r}"/></Node></Node>')
+        segs.append(f'<Segment id="{k + 1}"><True/>{tree_model(names, nodes, strategy="defaultChild", target=None, extra=lt)}</Segment>')
+    pm = doc([(nm, "continuous", "double") for nm in names],
+             f'<MiningModel functionName="regression">{schema(names)}<Segmentation multipleModelMethod="sum">{"".join(segs)}</Segmentation></MiningModel>')
+    m, om = engine.compile(pm), oracle.OracleModel(pm)
+    assert "derived=24" in m.describe, m.describe
+    X, pres, pb = gen.events(n, F, 78, 0.1)
+    o = om.predict(X, pb, nthreads=8); r = engine.score(m, X, pb)
+    assert np.array_equal(r["status"], o["status"]) and (o["status"] == 0).all()
+    assert np.array_equal(r["score"].view(np.int64), o["score"].view(np.int64))
+    want = np.zeros(n)
+    for k in range(T):
+        i, j = k % F, (k + 1) % F
+        d = X[:, i] + X[:, j]; known = pres[:, i] & pres[:, j]
+        left = np.where(known, d <= thr[k], dflt[k] == 0)
+        want = want + np.where(left, va[k], vb[k])
+    assert np.array_equal(r["score"], want)
