@@ -1633,11 +1633,12 @@ static cudaError_t launch_dense_tile(const DeviceModel& m, const BatchArgs& a, c
   for (int cand : {8, 10, 12}) { int pad = (dv.C + cand - 1) / cand * cand - dv.C; if (pad < best_pad) { best_pad = pad; tc = cand; } }
   DensePlan pl{}; pl.kp = ((dv.C + tc - 1) / tc) * tc; pl.groups = pl.kp / tc;
   // two events per thread once there are enough fields for the coefficient traffic to matter
-  const int ept = fast ? 2 : (env_int("FJP_REG_EPT", m.F >= 64 ? 2 : 1) >= 2 ? 2 : 1), per_sm = ept == 2 ? 2 : 3;
+  // nearest centre (fast >= 2): four events per thread -- 8 weights serve 32 fused multiply-adds, so the coefficient loads stop pacing the FP64 pipe
+  const int ept = fast >= 2 ? env_int("FJP_KM_EPT", 4) : (fast ? 2 : (env_int("FJP_REG_EPT", m.F >= 64 ? 2 : 1) >= 2 ? 2 : 1)), per_sm = ept >= 2 ? 2 : 3;
   pl.event_blocks = pl.groups >= 8 ? 1 : 8 / pl.groups; pl.warps = pl.event_blocks * pl.groups; pl.events = 32 * ept * pl.event_blocks;
   const int EP = pl.events + 1;
   int chunk = 64; while (chunk > m.F && chunk > 1) chunk /= 2;   // power of two: cheap row/column split
-  const unsigned smem_cap = (unsigned)env_int("FJP_REG_SMEM_KB", ept == 2 ? 110 : 72) * 1024u;   // per_sm CTAs per SM: one loads while the others compute
+  const unsigned smem_cap = (unsigned)env_int("FJP_REG_SMEM_KB", ept >= 2 ? 110 : 72) * 1024u;   // per_sm CTAs per SM: one loads while the others compute
   for (;; chunk /= 2) {
     size_t off = ((size_t)2 * chunk * pl.kp * 8 + 127) & ~size_t(127); pl.off_x = (uint32_t)off;
     const size_t xbytes = (size_t)2 * chunk * EP * 8, ybytes = (size_t)pl.kp * EP * 8;
@@ -1653,6 +1654,8 @@ static cudaError_t launch_dense_tile(const DeviceModel& m, const BatchArgs& a, c
                                      regression_tile_kernel<HM, TCV, EV, FV><<<grid, pl.warps * 32, pl.smem_bytes, s>>>(m, a, pl, dv); } while (0)
 #define FJP_RT2(HM, TCV) do { if (ept == 2) FJP_RT(HM, TCV, 2, 0); else FJP_RT(HM, TCV, 1, 0); } while (0)
   if (fast == 1) { if (tc == 8) FJP_RT(false, 8, 2, 1); else if (tc == 10) FJP_RT(false, 10, 2, 1); else FJP_RT(false, 12, 2, 1); }
+  else if (fast == 2 && ept == 4) { if (tc == 8) FJP_RT(false, 8, 4, 2); else if (tc == 10) FJP_RT(false, 10, 4, 2); else FJP_RT(false, 12, 4, 2); }
+  else if (fast == 3 && ept == 4) { if (tc == 8) FJP_RT(false, 8, 4, 3); else if (tc == 10) FJP_RT(false, 10, 4, 3); else FJP_RT(false, 12, 4, 3); }
   else if (fast == 2) { if (tc == 8) FJP_RT(false, 8, 2, 2); else if (tc == 10) FJP_RT(false, 10, 2, 2); else FJP_RT(false, 12, 2, 2); }
   else if (fast == 3) { if (tc == 8) FJP_RT(false, 8, 2, 3); else if (tc == 10) FJP_RT(false, 10, 2, 3); else FJP_RT(false, 12, 2, 3); }
   else if (hasmiss) { if (tc == 8) FJP_RT2(true, 8); else if (tc == 10) FJP_RT2(true, 10); else FJP_RT2(true, 12); }
