@@ -33,3 +33,32 @@ def test_gpu_matches_scikit_learn(engine, oracle, suite, k):
     Xb = np.tile(X, (reps, 1))
     rb = engine.score(m, Xb)
     assert np.array_equal(rb["score"], np.tile(r["score"], reps)) and (rb["status"] == 0).all(), name
+
+
+def test_gpu_matches_scikit_learn_kmeans(engine, oracle, gen):
+    """KMeans fitted by scikit-learn (config 2's family): the CUDA path -- the FMA path for the dense batch, the masked FMA path for
+    rows with missing values -- gives scikit-learn's own cluster for every event whose two nearest centres are not a rounding tie."""
+    pytest.importorskip("sklearn")
+    from sklearn.cluster import KMeans
+    rng = np.random.default_rng(21)
+    F, K = 40, 16
+    X = rng.standard_normal((3000, F)) + rng.integers(0, 3, (3000, 1))
+    km = KMeans(n_clusters=K, n_init=2, random_state=0).fit(X)
+    pm = gen.kmeans_pmml(km.cluster_centers_)
+    Xq = rng.standard_normal((64 * 148 * 2 + 77, F)) + rng.integers(0, 3, (64 * 148 * 2 + 77, 1))
+    d = ((Xq[:, None, :] - km.cluster_centers_[None, :, :]) ** 2).sum(axis=2); srt = np.sort(d, axis=1)
+    clear = srt[:, 1] - srt[:, 0] > 1e-9
+    m = engine.compile(pm)
+    r = engine.score(m, Xq)
+    assert (r["status"] == 0).all() and clear.mean() > 0.999
+    assert np.array_equal(r["aux"][clear], km.predict(Xq)[clear] + 1)            # ids are 1-based cluster positions
+    o = oracle.OracleModel(pm).predict(Xq, nthreads=8)
+    assert np.array_equal(r["aux"], o["aux"]) and np.array_equal(r["score"], o["score"])
+    # rows with missing values: JPMML compares over the present fields only (the adjustment factor scales every distance alike)
+    pres = rng.random(Xq.shape) > 0.1; pb = gen.pack_present(pres)
+    dm = (np.where(pres[:, None, :], (Xq[:, None, :] - km.cluster_centers_[None, :, :]) ** 2, 0.0)).sum(axis=2); srt = np.sort(dm, axis=1)
+    clear = srt[:, 1] - srt[:, 0] > 1e-9
+    rm = engine.score(m, Xq, pb)
+    assert np.array_equal(rm["aux"][clear], np.argmin(dm, axis=1)[clear] + 1)
+    om = oracle.OracleModel(pm).predict(Xq, pb, nthreads=8)
+    assert np.array_equal(rm["aux"], om["aux"]) and np.array_equal(rm["status"], om["status"])
