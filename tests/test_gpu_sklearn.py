@@ -62,3 +62,26 @@ def test_gpu_matches_scikit_learn_kmeans(engine, oracle, gen):
     assert np.array_equal(rm["aux"][clear], np.argmin(dm, axis=1)[clear] + 1)
     om = oracle.OracleModel(pm).predict(Xq, pb, nthreads=8)
     assert np.array_equal(rm["aux"], om["aux"]) and np.array_equal(rm["status"], om["status"])
+
+
+def test_gpu_matches_scikit_learn_gradient_boosting(engine, oracle, monkeypatch):
+    """GradientBoostingRegressor fitted by scikit-learn (config 4's family: a sum of regression trees plus a constant): the CUDA path
+    -- one-kernel walk and the rank-key pre-pass + compact walk -- within 1e-9 of scikit-learn's own predict (sklearn adds its stages
+    in another order) and bit for bit with the oracle."""
+    sk = pytest.importorskip("sklearn.ensemble")
+    rng = np.random.default_rng(0)
+    F = 10
+    X = rng.standard_normal((3000, F)).astype(np.float32).astype(np.float64)
+    y = X[:, 0] * 2 - X[:, 1] ** 2 + np.sin(X[:, 2] * 3) + rng.normal(0, 0.1, 3000)
+    gb = sk.GradientBoostingRegressor(n_estimators=60, max_depth=5, random_state=0).fit(X, y)
+    pm = hand_pmml.sklearn_gbr_to_pmml(gb, F)
+    Xq = rng.standard_normal((640 * 148 + 333, F)).astype(np.float32).astype(np.float64)
+    want = gb.predict(Xq)
+    m = engine.compile(pm)
+    o = oracle.OracleModel(pm).predict(Xq, nthreads=8)
+    for compact in ("0", "2"):
+        monkeypatch.setenv("FJP_FOREST_COMPACT", compact)
+        r = engine.score(m, Xq)
+        assert (r["status"] == 0).all()
+        np.testing.assert_allclose(r["score"], want, rtol=1e-9, atol=1e-12)
+        assert np.array_equal(r["score"].view(np.int64), o["score"].view(np.int64))
